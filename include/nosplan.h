@@ -1,0 +1,172 @@
+/* nosplan.h — C ABI of libnosplan.so, the B200-native GPU-partitioning planner hot path.
+ *
+ * Drop-in boundary for the walkai-nos (Nebuly nos fork) gpupartitioner.  The reference has NO FFI for
+ * this path today (build/gpupartitioner/Dockerfile:32 builds with CGO_ENABLED=0); its only cgo
+ * precedent is the `nvml` build tag (pkg/gpu/nvml/client.go:1, client_stub.go:1).  These entry points
+ * are what a `//go:build cuda` cgo shim binds (INTEGRATION.md shows the shim).  Every entry point
+ * cites the reference function(s) whose work it replaces; paths are relative to the reference root.
+ *
+ * Conventions
+ *  - Plain C: pointers + sizes, caller-owned host buffers unless the name ends in `_dev`.
+ *    The library copies what it needs during the call and keeps no caller pointer afterwards.
+ *  - Return value: 0 = ok, negative = error class (below); nosplan_last_error(h) gives the text.
+ *    A CUDA failure is always an error.  There is no CPU fallback anywhere in this library.
+ *  - A handle is bound to one CUDA device and is NOT re-entrant: one call at a time per handle
+ *    (the reference's planner is single-threaded too: MaxConcurrentReconciles 1,
+ *    internal/controllers/gpupartitioner/mig_controller.go:204).
+ *  - "Maps" of the reference (map[ProfileName]int) cross the boundary as dense rows over a
+ *    vocabulary: MIG rows have one int32 column per profile name, names strictly ascending bytewise
+ *    (the canonical order of SURVEY §D); MPS rows have one column per slice size in GB, strictly
+ *    ascending.  Demand vectors (pod requests) are CSR: off[D+1], key[nnz], qty[nnz], keys ascending
+ *    within a row; a key with qty 0 is a present map key (it matters for the gate).
+ *  - Nodes appear in the reference's list order (snapshot order); "first node wins" = lowest index.
+ *    GPUs of a node appear in the canonical order of SURVEY §D; gpu_off[N+1] is the CSR over GPUs.
+ *    valid[n] = 0 marks a node whose NewNode failed in the reference (mig/node.go:40-64): it is
+ *    skipped by the gate, by repartitioning and by scheduling, exactly as the controller does
+ *    (mig_controller.go:135-137, 153-157).
+ */
+#ifndef NOSPLAN_H_
+#define NOSPLAN_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct nosplan nosplan_t;
+
+/* limits (checked; exceeding one returns NOSPLAN_ERR_RANGE) */
+#define NOSPLAN_MAX_MIG_PROFILES 16   /* MIG vocabulary columns                                   */
+#define NOSPLAN_MAX_MODELS 32         /* GPU models in the geometry table                          */
+#define NOSPLAN_MAX_GEOMS 32          /* allowed geometries per model                              */
+#define NOSPLAN_MAX_MPS_SIZES 32      /* MPS vocabulary columns                                    */
+#define NOSPLAN_MAX_GPUS_PER_NODE 16
+#define NOSPLAN_MAX_COUNT 255         /* used[p] + free[p] per GPU and profile                     */
+#define NOSPLAN_MAX_MEM_GB 65535
+#define NOSPLAN_MAX_DEMAND_KEYS 8     /* distinct profiles one pod may request                     */
+#define NOSPLAN_MAX_DEMAND_QTY 1000000
+
+/* error classes */
+#define NOSPLAN_OK 0
+#define NOSPLAN_ERR_ARG (-1)    /* null pointer, bad size, call order                               */
+#define NOSPLAN_ERR_RANGE (-2)  /* a documented limit exceeded / value out of range                */
+#define NOSPLAN_ERR_CUDA (-3)   /* CUDA runtime or kernel failure                                   */
+#define NOSPLAN_ERR_CONFIG (-4) /* geometry table rejected (mirrors ValidateConfigs errors)        */
+
+/* plan flags */
+#define NOSPLAN_PLAN_GATE 1  /* apply profileAlreadyPresent before repartitioning (reference: on)  */
+#define NOSPLAN_PLAN_SCHED 2 /* simulate scheduling with Node.AddPod first-fit                    */
+
+/* ---- lifetime ---------------------------------------------------------------------------------- */
+/* Binds a planner to CUDA device `device` (ordinal).  Replaces nothing in the reference: it is where
+ * cmd/gpupartitioner/gpupartitioner.go:49-120 would construct the planner handle. */
+int nosplan_create(int device, nosplan_t** out);
+void nosplan_destroy(nosplan_t* h);
+/* Text of the last error on this handle ("" if none).  Valid until the next call on the handle. */
+const char* nosplan_last_error(const nosplan_t* h);
+const char* nosplan_version(void);
+
+/* ---- geometry tables ---------------------------------------------------------------------------- */
+/* Replaces mig.SetKnownGeometries + ValidateConfigs (pkg/gpu/mig/known_configs.go:144-185).
+ *   profile_names[n_profiles]  MIG vocabulary, strictly ascending bytewise; each must match
+ *                              \d+g\.\d+gb (pkg/constant/constants.go:40) if it occurs in a geometry
+ *   geom_off[n_models+1]       CSR over models; list order inside a model is kept (it decides
+ *                              InitGeometry, pkg/gpu/partitioning.go:67-79)
+ *   geom_counts[total][n_profiles]  quantity of each profile, 0 = key absent, negative rejected
+ * The library renders Geometry.Id() (pkg/gpu/partitioning.go:37-56) for every geometry and ranks
+ * the strings bytewise per model: that rank is the 4th key of the selection order (gpu.go:242). */
+int nosplan_set_mig_tables(nosplan_t* h, int n_profiles, const char* const* profile_names, int n_models,
+                           const int32_t* geom_off, const int32_t* geom_counts);
+
+/* ---- cluster snapshot ---------------------------------------------------------------------------- */
+/* Replaces, per node, mig.NewNode/extractGPUs (pkg/gpu/mig/node.go:40-100) once the Go side has
+ * parsed labels and annotations: the snapshot is the flattened []mig.Node.
+ *   model[total_gpus]               index into the model table (per GPU: tests build mixed nodes)
+ *   used/free_[total_gpus][n_profiles]  usedMigDevices / freeMigDevices (gpu.go:29-35), >= 0 */
+int nosplan_set_mig_snapshot(nosplan_t* h, int n_nodes, const int32_t* gpu_off, const uint8_t* valid,
+                             const int32_t* model, const int32_t* used, const int32_t* free_);
+
+/* Replaces slicing.NewNode/extractGPUs (pkg/gpu/slicing/node.go:32-105).
+ *   sizes_gb[n_sizes]               MPS vocabulary ("<k>gb", slicing/profile.go:48-59), ascending, >= 1
+ *   mem_gb[total_gpus]              gpu.GetMemoryGB of the node label (pkg/gpu/util.go:59-73)
+ *   used/free_[total_gpus][n_sizes] UsedProfiles / FreeProfiles (slicing/gpu.go:27-33)
+ *   free_mask[total_gpus]           bit s set = key s present in FreeProfiles (a present key with
+ *                                   value 0 behaves differently from an absent one in
+ *                                   slicing/gpu.go:199-216); NULL = present iff value > 0 */
+int nosplan_set_mps_snapshot(nosplan_t* h, int n_sizes, const int32_t* sizes_gb, int n_nodes,
+                             const int32_t* gpu_off, const uint8_t* valid, const int32_t* mem_gb,
+                             const int32_t* used, const int32_t* free_, const uint32_t* free_mask);
+
+/* ---- batched scorer (the throughput path) ----------------------------------------------------------- */
+/* For every demand row d and every valid node n, runs mig.Node.UpdateGeometryFor
+ * (pkg/gpu/mig/node.go:145-177 -> mig.GPU.UpdateGeometryFor pkg/gpu/mig/gpu.go:160-196: CanApplyGeometry :99,
+ * countProvidedProfiles :198, geometryDistance :245, totalSliceCount :262, isBetterGeometryScore
+ * :232, ApplyGeometry :134) on a fresh copy of the snapshot node, as updateNodeGeometry does
+ * (mig_controller.go:168-198).  One candidate evaluation = one iteration of gpu.go:168-188.
+ * Outputs (each may be NULL):
+ *   first_node[D]              lowest n that would update, -1 if none (tryRepartition, :146-166)
+ *   first_choice[D][max_gpus]  for that node, index of the geometry applied to each GPU, -1 = kept
+ *   updated[D][N]              1 if node n would update
+ *   choice[D][total_gpus]      applied geometry index per GPU for every (d, n), -1 = kept
+ * n_evals (may be NULL) receives the number of candidate evaluations performed. */
+int nosplan_score_mig(nosplan_t* h, int n_demands, const int32_t* dem_off, const int32_t* dem_key,
+                      const int32_t* dem_qty, int32_t* first_node, int8_t* first_choice, uint8_t* updated,
+                      int8_t* choice, int64_t* n_evals);
+
+/* MPS twin: slicing.Node.UpdateGeometryFor (pkg/gpu/slicing/node.go:120-152 ->
+ * slicing.GPU.UpdateGeometryFor pkg/gpu/slicing/gpu.go:162-220 with createSlices :238, canCreateMoreSlices :250).
+ * One evaluation = one (demand, node, GPU) greedy run.
+ *   out_free[D][total_gpus][n_sizes] (uint8) / out_free_mask[D][total_gpus]: FreeProfiles after the
+ *   trial update, for every (d, n). */
+int nosplan_score_mps(nosplan_t* h, int n_demands, const int32_t* dem_off, const int32_t* dem_key,
+                      const int32_t* dem_qty, int32_t* first_node, uint8_t* updated, uint8_t* out_free,
+                      uint32_t* out_free_mask, int64_t* n_evals);
+
+/* ---- planner ------------------------------------------------------------------------------------------ */
+/* Plan(snapshot, pendingPods): replays Controller.Reconcile (mig_controller.go:56-98) pod by pod on
+ * the evolving state, starting from the uploaded snapshot (the snapshot itself is not modified):
+ * gate profileAlreadyPresent (:121-144), tryRepartition first-node-wins (:146-166), then — with
+ * NOSPLAN_PLAN_SCHED — Node.AddPod first-fit (mig/node.go:201-210 -> gpu.go:289-303; slicing twins
+ * node.go:196-205, gpu.go:142-156).  Pods must already be filtered by shouldConsiderPod (:100-111)
+ * and ordered (priority desc — pkg/util/pod/pod.go:84-88 — then creation time, then ns/name).
+ *   kind[M]   0 = MIG pod (keys index the MIG vocabulary), 1 = MPS pod (keys index sizes)
+ * Outputs per pod (each may be NULL): gate_hit, repart_node (-1 none), sched_node, sched_gpu (slot in
+ * the node, -1 none).  The final state is read with nosplan_get_*_state. */
+int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* dem_off,
+                 const int32_t* dem_key, const int32_t* dem_qty, int flags, uint8_t* gate_hit,
+                 int32_t* repart_node, int32_t* sched_node, int32_t* sched_gpu);
+
+/* State after the last nosplan_plan (or the snapshot if none ran), same layout as the setters.
+ * mig: the desired geometry of GPU g is used+free where > 0 — BuildNodePartitioning
+ * (internal/partitioning/mig/state.go:25-45) over these rows gives state.NodePartitioning. */
+int nosplan_get_mig_state(nosplan_t* h, int32_t* used, int32_t* free_);
+int nosplan_get_mps_state(nosplan_t* h, int32_t* used, int32_t* free_, uint32_t* free_mask);
+
+/* Replaces NodeInitializer.InitNodePartitioning's per-GPU step (internal/partitioning/mig/
+ * initializer.go:40-79 -> GPU.InitGeometry gpu.go:120-129 -> GetFewestSlicesGeometry
+ * pkg/gpu/partitioning.go:67-79) over every GPU of the snapshot:
+ *   err[total_gpus]  1 where the reference returns an error (used devices would be deleted)
+ *   out_free[total_gpus][n_profiles]  free devices after the call (unchanged where err) */
+int nosplan_init_geometry_mig(nosplan_t* h, uint8_t* err, int32_t* out_free);
+
+/* ---- device-resident variants (inputs/outputs already in HBM; used for kernel-only timing) ------------ */
+/* Same as nosplan_score_mig/_mps but every pointer is a device pointer on the handle's device and the
+ * work is enqueued on `stream` (a cudaStream_t) without synchronising.  first_node must be
+ * pre-filled by the callee (it is); updated/choice may be NULL. */
+int nosplan_score_mig_dev(nosplan_t* h, int n_demands, const int32_t* dem_off, const int32_t* dem_key,
+                          const int32_t* dem_qty, int32_t* first_node, uint8_t* updated, int8_t* choice,
+                          void* stream);
+int nosplan_score_mps_dev(nosplan_t* h, int n_demands, const int32_t* dem_off, const int32_t* dem_key,
+                          const int32_t* dem_qty, int32_t* first_node, uint8_t* updated, uint8_t* out_free,
+                          uint32_t* out_free_mask, void* stream);
+
+/* Candidate evaluations one scorer pass performs for D demand rows on the current snapshot
+ * (sum over valid nodes and their GPUs of the model's geometry count; for MPS, GPUs of valid nodes). */
+int64_t nosplan_mig_evals_per_demand(const nosplan_t* h);
+int64_t nosplan_mps_evals_per_demand(const nosplan_t* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NOSPLAN_H_ */

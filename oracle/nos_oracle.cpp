@@ -789,7 +789,7 @@ int orc_score_mig(orc_t* o, const orc_mig_snapshot* s, int n_demands, const int3
   int N = s->n_nodes;
   int totalG = s->gpu_off[N];
   // demands are chunked so threads stay busy even when D is small
-  const int chunk = 8;
+  const int chunk = std::max(1, std::min(8, n_demands / std::max(1, n_threads * 4)));
   int n_chunks = (n_demands + chunk - 1) / chunk;
   run_threads_impl(n_threads, n_chunks, [&](int ci) {
     std::vector<MigGPU> node;
@@ -828,7 +828,7 @@ int orc_score_mps(orc_t* o, const orc_mps_snapshot* s, int n_demands, const int3
   int S = (int)o->c.mps_sizes.size();
   int N = s->n_nodes;
   int totalG = s->gpu_off[N];
-  const int chunk = 8;
+  const int chunk = std::max(1, std::min(8, n_demands / std::max(1, n_threads * 4)));
   int n_chunks = (n_demands + chunk - 1) / chunk;
   run_threads_impl(n_threads, n_chunks, [&](int ci) {
     std::vector<MpsGPU> node;
@@ -939,20 +939,21 @@ int orc_plan(orc_t* o, orc_mig_snapshot* mig, orc_mps_snapshot* mps, int n_pods,
       }
     }
     if (flags & ORC_FLAG_SCHED) {
-      // §A.5 3c: first node whose Node.AddPod succeeds is committed; failing nodes are trial copies
+      // §A.5 3c: first node whose Node.AddPod succeeds is committed; a failing node is a discarded
+      // trial copy.  Node.AddPod succeeds iff some GPU fits every key, so the (side-effect free)
+      // fit check below decides success and the literal AddPod then runs on the real node only.
       for (int n = 0; n < N; ++n) {
         if (!valid[n]) continue;
         int g0 = off[n], G = off[n + 1] - g0;
-        int slot;
-        if (is_mps) {
-          stmp.assign(sg.begin() + g0, sg.begin() + g0 + G);
-          slot = mps_node_add_pod(stmp.data(), G, rq);
-          if (slot >= 0) std::copy(stmp.begin(), stmp.end(), sg.begin() + g0);
-        } else {
-          mtmp.assign(mg.begin() + g0, mg.begin() + g0 + G);
-          slot = mig_node_add_pod(mtmp.data(), G, rq);
-          if (slot >= 0) std::copy(mtmp.begin(), mtmp.end(), mg.begin() + g0);
+        bool fits = false;
+        for (int g = g0; g < g0 + G && !fits; ++g) {
+          bool ok = true;
+          for (int p = 0; p < W && ok; ++p)
+            if (rq.has(p)) ok = (is_mps ? sg[g].free.get(p) : mg[g].free.get(p)) >= rq.v[p];
+          fits = ok;
         }
+        int slot = -1;
+        if (fits) slot = is_mps ? mps_node_add_pod(sg.data() + g0, G, rq) : mig_node_add_pod(mg.data() + g0, G, rq);
         if (slot >= 0) {
           sched_node[i] = n;
           sched_gpu[i] = slot;

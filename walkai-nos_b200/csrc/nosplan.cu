@@ -1,0 +1,858 @@
+// nosplan.cu — host side of libnosplan.so: handle, validation, uploads, launches, the C ABI of
+// include/nosplan.h.  No CPU fallback exists anywhere in this file: every compute entry point ends
+// in a kernel launch on the handle's device or returns an error.
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "nosplan.h"
+#include "nosplan_kernels.cuh"
+#include "nosplan_plan.cuh"
+
+using namespace nsp;
+
+namespace {
+
+// grow-only device buffer
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t reserve(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    size_t want = std::max<size_t>(bytes, 256);
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+  template <typename T>
+  T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+}  // namespace
+
+struct nosplan {
+  int device = 0;
+  cudaStream_t stream = nullptr, stream2 = nullptr;
+  std::string err;
+  int sm_count = 148;
+
+  // MIG tables
+  bool have_tables = false;
+  int P = 0;
+  std::vector<std::string> names;
+  MigTables h_tables;
+  DevBuf d_tables;
+  int cmax = 0;
+
+  // MIG snapshot
+  bool have_mig = false;
+  int mig_n = 0, mig_tg = 0, mig_gs = 0, mig_npad = 0;
+  int64_t mig_evals = 0;
+  DevBuf d_mig_off, d_mig_valid, d_mig_model, d_mig_used0, d_mig_free0, d_mig_used, d_mig_free;
+  DevBuf d_mig_sused, d_mig_sfree, d_mig_smodel, d_mig_scnt;
+  bool mig_state_dirty = false;  // working copy differs from the snapshot
+
+  // MPS snapshot
+  bool have_mps = false;
+  int S = 0;
+  int mps_n = 0, mps_tg = 0, mps_gs = 0;
+  int64_t mps_evals = 0;
+  DevBuf d_mps_sizes, d_mps_off, d_mps_valid, d_mps_gpu0, d_mps_ulo0, d_mps_uhi0, d_mps_gpu, d_mps_ulo, d_mps_uhi;
+  bool mps_state_dirty = false;
+
+  // scratch / staging
+  DevBuf d_in[6];    // staging for int32 host inputs
+  DevBuf d_dem[3];   // demand CSR
+  DevBuf d_out[6];   // outputs
+  DevBuf d_plan[16];
+};
+
+namespace {
+
+int fail(nosplan_t* h, int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  if (h) h->err = buf;
+  return code;
+}
+
+#define CU(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e__ = (call);                                                                      \
+    if (e__ != cudaSuccess)                                                                        \
+      return fail(h, NOSPLAN_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+  } while (0)
+
+int bind(nosplan_t* h) {
+  CU(cudaSetDevice(h->device));
+  return NOSPLAN_OK;
+}
+
+// MIG profile name must match \\d+g\\.\\d+gb somewhere (unanchored regexp.MatchString, profile.go:51-53)
+bool mig_name_valid(const std::string& s) {
+  const size_t n = s.size();
+  for (size_t i = 0; i < n; ++i) {
+    size_t j = i;
+    while (j < n && isdigit((unsigned char)s[j])) ++j;
+    if (j == i) continue;                                  // \d+
+    if (j + 1 >= n || s[j] != 'g' || s[j + 1] != '.') continue;  // g\.
+    size_t k = j + 2;
+    while (k < n && isdigit((unsigned char)s[k])) ++k;
+    if (k == j + 2) continue;                              // \d+
+    if (k + 1 < n && s[k] == 'g' && s[k + 1] == 'b') return true;  // gb
+  }
+  return false;
+}
+
+int upload(nosplan_t* h, DevBuf& b, const void* src, size_t bytes, cudaStream_t st) {
+  CU(b.reserve(bytes));
+  if (bytes) CU(cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, st));
+  return NOSPLAN_OK;
+}
+
+int check_demands(nosplan_t* h, int D, const int32_t* off, const int32_t* key, const int32_t* qty, int n_keys) {
+  if (D < 0) return fail(h, NOSPLAN_ERR_ARG, "negative demand count");
+  if (D == 0) return NOSPLAN_OK;
+  if (!off) return fail(h, NOSPLAN_ERR_ARG, "dem_off is null");
+  if (off[0] != 0) return fail(h, NOSPLAN_ERR_ARG, "dem_off[0] must be 0");
+  for (int d = 0; d < D; ++d) {
+    int k = off[d + 1] - off[d];
+    if (k < 0) return fail(h, NOSPLAN_ERR_ARG, "dem_off not ascending at row %d", d);
+    if (k > NOSPLAN_MAX_DEMAND_KEYS)
+      return fail(h, NOSPLAN_ERR_RANGE, "demand row %d has %d keys (max %d)", d, k, NOSPLAN_MAX_DEMAND_KEYS);
+    for (int e = off[d]; e < off[d + 1]; ++e) {
+      if (key[e] < 0 || key[e] >= n_keys) return fail(h, NOSPLAN_ERR_RANGE, "demand row %d: key %d out of range", d, key[e]);
+      if (e > off[d] && key[e] <= key[e - 1]) return fail(h, NOSPLAN_ERR_ARG, "demand row %d: keys must be strictly ascending", d);
+      if (qty[e] < 0 || qty[e] > NOSPLAN_MAX_DEMAND_QTY)
+        return fail(h, NOSPLAN_ERR_RANGE, "demand row %d: quantity %d out of range", d, qty[e]);
+    }
+  }
+  return NOSPLAN_OK;
+}
+
+// chunking of the demand axis so the grid is a small multiple of the SM count
+void pick_chunks(int sm_count, int tiles, int D, int min_chunk, int* d_chunk, int* gy) {
+  int want_ctas = sm_count * 4;
+  int y = std::max(1, want_ctas / std::max(1, tiles));
+  int chunk = std::max(min_chunk, (D + y - 1) / y);
+  chunk = std::min(chunk, std::max(D, 1));
+  *d_chunk = chunk;
+  *gy = (D + chunk - 1) / chunk;
+  if (*gy < 1) *gy = 1;
+}
+
+constexpr int kScoreTN = 128;
+
+size_t mig_score_smem(const nosplan_t* h, int tn) {
+  size_t cand = ((size_t)h->h_tables.n_geoms * 16 + 15) & ~(size_t)15;
+  size_t key0 = (size_t)h->mig_gs * h->cmax * tn * 4;
+  size_t words = (size_t)h->mig_gs * 4 * tn * 4 * 2;
+  size_t coff = (size_t)h->mig_gs * tn * 2;
+  size_t ccnt = (size_t)h->mig_gs * tn;
+  return cand + key0 + words + coff + ccnt + 16;
+}
+
+int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d_key, const int32_t* d_qty,
+                     int32_t* d_first, uint8_t* d_updated, int8_t* d_choice, cudaStream_t st) {
+  if (D == 0) return NOSPLAN_OK;
+  fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, kNoNode);
+  if (d_choice) CU(cudaMemsetAsync(d_choice, 0xff, (size_t)D * h->mig_tg, st));
+  if (h->mig_n > 0) {
+    MigScoreArgs a;
+    a.T = h->d_tables.as<MigTables>();
+    a.s_used = h->d_mig_sused.as<uint4>();
+    a.s_free = h->d_mig_sfree.as<uint4>();
+    a.s_model = h->d_mig_smodel.as<uint8_t>();
+    a.s_cnt = h->d_mig_scnt.as<uint8_t>();
+    a.gpu_off = h->d_mig_off.as<int32_t>();
+    a.N = h->mig_n;
+    a.npad = h->mig_npad;
+    a.gs = h->mig_gs;
+    a.cmax = h->cmax;
+    a.tg = h->mig_tg;
+    a.D = D;
+    a.dem_off = d_off;
+    a.dem_key = d_key;
+    a.dem_qty = d_qty;
+    a.first_node = d_first;
+    a.updated = d_updated;
+    a.choice = d_choice;
+    int tiles = (h->mig_n + kScoreTN - 1) / kScoreTN;
+    int gy;
+    pick_chunks(h->sm_count, tiles, D, 16, &a.d_chunk, &gy);
+    size_t smem = mig_score_smem(h, kScoreTN);
+    if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MIG scorer tile needs %zu bytes of shared memory", smem);
+    CU(cudaFuncSetAttribute(mig_score_kernel<kScoreTN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    mig_score_kernel<kScoreTN><<<dim3(tiles, gy), kScoreTN, smem, st>>>(a);
+  }
+  CU(cudaGetLastError());
+  return NOSPLAN_OK;
+}
+
+int launch_mps_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d_key, const int32_t* d_qty,
+                     int32_t* d_first, uint8_t* d_updated, uint8_t* d_free, uint32_t* d_mask, cudaStream_t st) {
+  if (D == 0) return NOSPLAN_OK;
+  fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, kNoNode);
+  if (h->mps_n > 0) {
+    MpsScoreArgs a;
+    a.sizes = h->d_mps_sizes.as<int32_t>();
+    a.S = h->S;
+    a.gp = h->d_mps_gpu0.as<MpsGpu>();
+    a.gpu_off = h->d_mps_off.as<int32_t>();
+    a.valid = h->d_mps_valid.as<uint8_t>();
+    a.N = h->mps_n;
+    a.tg = h->mps_tg;
+    a.D = D;
+    a.dem_off = d_off;
+    a.dem_key = d_key;
+    a.dem_qty = d_qty;
+    a.first_node = d_first;
+    a.updated = d_updated;
+    a.out_free = d_free;
+    a.out_mask = d_mask;
+    int tiles = (h->mps_n + kScoreTN - 1) / kScoreTN;
+    int gy;
+    pick_chunks(h->sm_count, tiles, D, 4, &a.d_chunk, &gy);
+    mps_score_kernel<kScoreTN><<<dim3(tiles, gy), kScoreTN, 0, st>>>(a);
+  }
+  nonode_to_minus1_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D);
+  CU(cudaGetLastError());
+  return NOSPLAN_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* nosplan_version(void) { return "nosplan 0.1 (sm_100a)"; }
+
+int nosplan_create(int device, nosplan_t** out) {
+  if (!out) return NOSPLAN_ERR_ARG;
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || device < 0 || device >= count) return NOSPLAN_ERR_CUDA;  // no device, no planner
+  nosplan_t* h = new nosplan();
+  h->device = device;
+  if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking) != cudaSuccess) {
+    delete h;
+    return NOSPLAN_ERR_CUDA;
+  }
+  cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device);
+  *out = h;
+  return NOSPLAN_OK;
+}
+
+void nosplan_destroy(nosplan_t* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  cudaDeviceSynchronize();
+  DevBuf* all[] = {&h->d_tables, &h->d_mig_off, &h->d_mig_valid, &h->d_mig_model, &h->d_mig_used0, &h->d_mig_free0,
+                   &h->d_mig_used, &h->d_mig_free, &h->d_mig_sused, &h->d_mig_sfree, &h->d_mig_smodel, &h->d_mig_scnt,
+                   &h->d_mps_sizes, &h->d_mps_off, &h->d_mps_valid, &h->d_mps_gpu0, &h->d_mps_ulo0, &h->d_mps_uhi0,
+                   &h->d_mps_gpu, &h->d_mps_ulo, &h->d_mps_uhi};
+  for (DevBuf* b : all) b->release();
+  for (auto& b : h->d_in) b.release();
+  for (auto& b : h->d_dem) b.release();
+  for (auto& b : h->d_out) b.release();
+  for (auto& b : h->d_plan) b.release();
+  if (h->stream) cudaStreamDestroy(h->stream);
+  if (h->stream2) cudaStreamDestroy(h->stream2);
+  delete h;
+}
+
+const char* nosplan_last_error(const nosplan_t* h) { return h ? h->err.c_str() : "null handle"; }
+
+int nosplan_set_mig_tables(nosplan_t* h, int n_profiles, const char* const* profile_names, int n_models,
+                           const int32_t* geom_off, const int32_t* geom_counts) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  if (!profile_names || !geom_off || (!geom_counts && n_models > 0 && geom_off[n_models] > 0))
+    return fail(h, NOSPLAN_ERR_ARG, "null argument");
+  if (n_profiles < 1 || n_profiles > NOSPLAN_MAX_MIG_PROFILES)
+    return fail(h, NOSPLAN_ERR_RANGE, "n_profiles %d out of range [1,%d]", n_profiles, NOSPLAN_MAX_MIG_PROFILES);
+  if (n_models < 1) return fail(h, NOSPLAN_ERR_CONFIG, "no known configs provided");  // known_configs.go:165-167
+  if (n_models > NOSPLAN_MAX_MODELS) return fail(h, NOSPLAN_ERR_RANGE, "too many models (%d > %d)", n_models, NOSPLAN_MAX_MODELS);
+  std::vector<std::string> names(n_profiles);
+  for (int p = 0; p < n_profiles; ++p) {
+    names[p] = profile_names[p] ? profile_names[p] : "";
+    if (p > 0 && !(names[p - 1] < names[p])) return fail(h, NOSPLAN_ERR_ARG, "profile names must be strictly ascending");
+  }
+  MigTables& T = h->h_tables;
+  std::memset(&T, 0, sizeof(T));
+  T.n_models = n_models;
+  T.n_prof = n_profiles;
+  if (geom_off[0] != 0) return fail(h, NOSPLAN_ERR_ARG, "geom_off[0] must be 0");
+  int cmax = 0;
+  for (int m = 0; m < n_models; ++m) {
+    int c = geom_off[m + 1] - geom_off[m];
+    if (c < 0) return fail(h, NOSPLAN_ERR_ARG, "geom_off not ascending");
+    if (c > NOSPLAN_MAX_GEOMS) return fail(h, NOSPLAN_ERR_RANGE, "model %d has %d geometries (max %d)", m, c, NOSPLAN_MAX_GEOMS);
+    cmax = std::max(cmax, c);
+    T.geom_off[m] = geom_off[m];
+  }
+  T.geom_off[n_models] = geom_off[n_models];
+  T.n_geoms = geom_off[n_models];
+  for (int m = 0; m < n_models; ++m) {
+    std::vector<std::string> ids;
+    int fewest = -1, fewest_kinds = 0;
+    for (int gi = geom_off[m]; gi < geom_off[m + 1]; ++gi) {
+      unsigned char bytes[16] = {0};
+      int total = 0, kinds = 0;
+      std::string id;  // Geometry.Id(): "%s:%d, " per profile, names ascending (partitioning.go:41-56)
+      for (int p = 0; p < n_profiles; ++p) {
+        int q = geom_counts[(size_t)gi * n_profiles + p];
+        if (q == 0) continue;
+        if (q < 1) return fail(h, NOSPLAN_ERR_CONFIG, "invalid quantity %d for profile %s", q, names[p].c_str());
+        if (!mig_name_valid(names[p])) return fail(h, NOSPLAN_ERR_CONFIG, "invalid profile %s", names[p].c_str());
+        if (q > NOSPLAN_MAX_COUNT) return fail(h, NOSPLAN_ERR_RANGE, "quantity %d exceeds %d", q, NOSPLAN_MAX_COUNT);
+        bytes[p] = (unsigned char)q;
+        total += q;
+        kinds++;
+        id += names[p] + ":" + std::to_string(q) + ", ";
+      }
+      std::memcpy(&T.cand[gi], bytes, 16);
+      T.total[gi] = (uint16_t)total;
+      ids.push_back(id);
+      if (fewest < 0 || kinds < fewest_kinds) {  // partitioning.go:67-79: first of the fewest kinds
+        fewest = gi - geom_off[m];
+        fewest_kinds = kinds;
+      }
+    }
+    T.init_choice[m] = fewest;
+    std::vector<std::string> sorted = ids;
+    std::sort(sorted.begin(), sorted.end());
+    sorted.erase(std::unique(sorted.begin(), sorted.end()), sorted.end());
+    for (size_t i = 0; i < ids.size(); ++i)
+      T.rank[geom_off[m] + i] = (uint8_t)(std::lower_bound(sorted.begin(), sorted.end(), ids[i]) - sorted.begin());
+  }
+  int rc = bind(h);
+  if (rc) return rc;
+  rc = upload(h, h->d_tables, &T, sizeof(T), h->stream);
+  if (rc) return rc;
+  CU(cudaStreamSynchronize(h->stream));
+  h->P = n_profiles;
+  h->names = names;
+  h->cmax = std::max(cmax, 1);
+  h->have_tables = true;
+  h->have_mig = false;  // a snapshot refers to model ids of the table it was uploaded against
+  return NOSPLAN_OK;
+}
+
+int nosplan_set_mig_snapshot(nosplan_t* h, int n_nodes, const int32_t* gpu_off, const uint8_t* valid,
+                             const int32_t* model, const int32_t* used, const int32_t* free_) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  if (!h->have_tables) return fail(h, NOSPLAN_ERR_ARG, "nosplan_set_mig_tables must be called first");
+  if (n_nodes < 0 || !gpu_off) return fail(h, NOSPLAN_ERR_ARG, "bad node list");
+  const int P = h->P;
+  if (gpu_off[0] != 0) return fail(h, NOSPLAN_ERR_ARG, "gpu_off[0] must be 0");
+  int gs = 0;
+  int64_t evals = 0;
+  for (int n = 0; n < n_nodes; ++n) {
+    int c = gpu_off[n + 1] - gpu_off[n];
+    if (c < 0) return fail(h, NOSPLAN_ERR_ARG, "gpu_off not ascending at node %d", n);
+    if (c > NOSPLAN_MAX_GPUS_PER_NODE) return fail(h, NOSPLAN_ERR_RANGE, "node %d has %d GPUs (max %d)", n, c, NOSPLAN_MAX_GPUS_PER_NODE);
+    gs = std::max(gs, c);
+  }
+  const int tg = gpu_off[n_nodes];
+  if (tg > 0 && (!model || !used || !free_)) return fail(h, NOSPLAN_ERR_ARG, "null state arrays");
+  std::vector<uint8_t> v(std::max(n_nodes, 1), 1);
+  if (valid) std::copy(valid, valid + n_nodes, v.begin());
+  // rows of invalid nodes are not interpreted (the controller never builds those nodes): they are
+  // replaced by zeros on the device and read back as zeros
+  std::vector<int32_t> zu, zf;
+  bool any_invalid = false;
+  for (int n = 0; n < n_nodes; ++n) any_invalid |= !v[n] && gpu_off[n + 1] > gpu_off[n];
+  if (any_invalid) {
+    zu.assign(used, used + (size_t)tg * P);
+    zf.assign(free_, free_ + (size_t)tg * P);
+    for (int n = 0; n < n_nodes; ++n)
+      if (!v[n])
+        for (size_t i = (size_t)gpu_off[n] * P; i < (size_t)gpu_off[n + 1] * P; ++i) zu[i] = zf[i] = 0;
+    used = zu.data();
+    free_ = zf.data();
+  }
+  for (int n = 0; n < n_nodes; ++n)
+    for (int g = gpu_off[n]; g < gpu_off[n + 1]; ++g) {
+      if (!v[n]) continue;
+      if (model[g] < 0 || model[g] >= h->h_tables.n_models)
+        return fail(h, NOSPLAN_ERR_RANGE, "GPU %d: model %d unknown (mark the node invalid instead)", g, model[g]);
+      evals += h->h_tables.geom_off[model[g] + 1] - h->h_tables.geom_off[model[g]];
+      for (int p = 0; p < P; ++p) {
+        int u = used[(size_t)g * P + p], f = free_[(size_t)g * P + p];
+        if (u < 0 || f < 0 || u + f > NOSPLAN_MAX_COUNT)
+          return fail(h, NOSPLAN_ERR_RANGE, "GPU %d profile %s: used %d free %d out of range [0,%d]", g, h->names[p].c_str(), u, f, NOSPLAN_MAX_COUNT);
+      }
+    }
+  int rc = bind(h);
+  if (rc) return rc;
+  const int npad = std::max(32, (n_nodes + 31) / 32 * 32);
+  // an invalid node's GPUs may carry an unknown model: clamp for the packed copy (never read)
+  std::vector<int32_t> mdl(std::max(tg, 1), 0);
+  for (int n = 0; n < n_nodes; ++n)
+    for (int g = gpu_off[n]; g < gpu_off[n + 1]; ++g) mdl[g] = v[n] ? model[g] : 0;
+  if ((rc = upload(h, h->d_mig_off, gpu_off, sizeof(int32_t) * (n_nodes + 1), h->stream))) return rc;
+  if ((rc = upload(h, h->d_mig_valid, v.data(), std::max(n_nodes, 1), h->stream))) return rc;
+  if ((rc = upload(h, h->d_in[0], mdl.data(), sizeof(int32_t) * std::max(tg, 1), h->stream))) return rc;
+  if ((rc = upload(h, h->d_in[1], used, sizeof(int32_t) * (size_t)tg * P, h->stream))) return rc;
+  if ((rc = upload(h, h->d_in[2], free_, sizeof(int32_t) * (size_t)tg * P, h->stream))) return rc;
+  const int gsl = std::max(gs, 1);
+  CU(h->d_mig_model.reserve(std::max(tg, 1)));
+  CU(h->d_mig_used0.reserve(sizeof(uint4) * std::max(tg, 1)));
+  CU(h->d_mig_free0.reserve(sizeof(uint4) * std::max(tg, 1)));
+  CU(h->d_mig_used.reserve(sizeof(uint4) * std::max(tg, 1)));
+  CU(h->d_mig_free.reserve(sizeof(uint4) * std::max(tg, 1)));
+  CU(h->d_mig_sused.reserve(sizeof(uint4) * (size_t)gsl * npad));
+  CU(h->d_mig_sfree.reserve(sizeof(uint4) * (size_t)gsl * npad));
+  CU(h->d_mig_smodel.reserve((size_t)gsl * npad));
+  CU(h->d_mig_scnt.reserve(npad));
+  mig_pack_kernel<<<(npad + 127) / 128, 128, 0, h->stream>>>(
+      n_nodes, P, gs, npad, h->d_mig_off.as<int32_t>(), h->d_mig_valid.as<uint8_t>(), h->d_in[0].as<int32_t>(),
+      h->d_in[1].as<int32_t>(), h->d_in[2].as<int32_t>(), h->d_mig_used0.as<uint4>(), h->d_mig_free0.as<uint4>(),
+      h->d_mig_model.as<uint8_t>(), h->d_mig_sused.as<uint4>(), h->d_mig_sfree.as<uint4>(), h->d_mig_smodel.as<uint8_t>(),
+      h->d_mig_scnt.as<uint8_t>());
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(h->d_mig_used.p, h->d_mig_used0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, h->stream));
+  CU(cudaMemcpyAsync(h->d_mig_free.p, h->d_mig_free0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  h->mig_n = n_nodes;
+  h->mig_tg = tg;
+  h->mig_gs = gsl;
+  h->mig_npad = npad;
+  h->mig_evals = evals;
+  h->have_mig = true;
+  h->mig_state_dirty = false;
+  return NOSPLAN_OK;
+}
+
+int nosplan_set_mps_snapshot(nosplan_t* h, int n_sizes, const int32_t* sizes_gb, int n_nodes, const int32_t* gpu_off,
+                             const uint8_t* valid, const int32_t* mem_gb, const int32_t* used, const int32_t* free_,
+                             const uint32_t* free_mask) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  if (n_sizes < 1 || n_sizes > NOSPLAN_MAX_MPS_SIZES || !sizes_gb)
+    return fail(h, NOSPLAN_ERR_RANGE, "n_sizes %d out of range [1,%d]", n_sizes, NOSPLAN_MAX_MPS_SIZES);
+  for (int s = 0; s < n_sizes; ++s) {
+    if (sizes_gb[s] < 1 || sizes_gb[s] > NOSPLAN_MAX_MEM_GB)  // MinSliceMemoryGB, slicing/constant.go:24
+      return fail(h, NOSPLAN_ERR_RANGE, "slice size %d GB out of range [1,%d]", sizes_gb[s], NOSPLAN_MAX_MEM_GB);
+    if (s > 0 && sizes_gb[s] <= sizes_gb[s - 1]) return fail(h, NOSPLAN_ERR_ARG, "sizes must be strictly ascending");
+  }
+  if (n_nodes < 0 || !gpu_off || gpu_off[0] != 0) return fail(h, NOSPLAN_ERR_ARG, "bad node list");
+  int gs = 0;
+  for (int n = 0; n < n_nodes; ++n) {
+    int c = gpu_off[n + 1] - gpu_off[n];
+    if (c < 0) return fail(h, NOSPLAN_ERR_ARG, "gpu_off not ascending at node %d", n);
+    if (c > NOSPLAN_MAX_GPUS_PER_NODE) return fail(h, NOSPLAN_ERR_RANGE, "node %d has %d GPUs (max %d)", n, c, NOSPLAN_MAX_GPUS_PER_NODE);
+    gs = std::max(gs, c);
+  }
+  const int tg = gpu_off[n_nodes];
+  const int S = n_sizes;
+  if (tg > 0 && (!mem_gb || !used || !free_)) return fail(h, NOSPLAN_ERR_ARG, "null state arrays");
+  std::vector<uint8_t> v(std::max(n_nodes, 1), 1);
+  if (valid) std::copy(valid, valid + n_nodes, v.begin());
+  int64_t evals = 0;
+  std::vector<int32_t> zu, zf, zm;
+  bool any_invalid = false;
+  for (int n = 0; n < n_nodes; ++n) any_invalid |= !v[n] && gpu_off[n + 1] > gpu_off[n];
+  if (any_invalid) {  // rows of invalid nodes are not interpreted; zeros on the device
+    zu.assign(used, used + (size_t)tg * S);
+    zf.assign(free_, free_ + (size_t)tg * S);
+    zm.assign(mem_gb, mem_gb + tg);
+    for (int n = 0; n < n_nodes; ++n)
+      if (!v[n]) {
+        for (size_t i = (size_t)gpu_off[n] * S; i < (size_t)gpu_off[n + 1] * S; ++i) zu[i] = zf[i] = 0;
+        for (int g = gpu_off[n]; g < gpu_off[n + 1]; ++g) zm[g] = 0;
+      }
+    used = zu.data();
+    free_ = zf.data();
+    mem_gb = zm.data();
+  }
+  for (int n = 0; n < n_nodes; ++n)
+    for (int g = gpu_off[n]; g < gpu_off[n + 1]; ++g) {
+      if (!v[n]) continue;
+      evals++;
+      if (mem_gb[g] < 0 || mem_gb[g] > NOSPLAN_MAX_MEM_GB) return fail(h, NOSPLAN_ERR_RANGE, "GPU %d: memory %d GB out of range", g, mem_gb[g]);
+      int64_t tot = 0;
+      for (int s = 0; s < S; ++s) {
+        int u = used[(size_t)g * S + s], f = free_[(size_t)g * S + s];
+        if (u < 0 || f < 0 || u + f > NOSPLAN_MAX_COUNT)
+          return fail(h, NOSPLAN_ERR_RANGE, "GPU %d size %dgb: used %d free %d out of range", g, sizes_gb[s], u, f);
+        if (free_mask && f > 0 && !((free_mask[g] >> s) & 1u) && v[n])
+          return fail(h, NOSPLAN_ERR_ARG, "GPU %d: free_mask misses a key with a non-zero value", g);
+        tot += (int64_t)sizes_gb[s] * (u + f);
+      }
+      // slicing.NewGPU rejects such a GPU (slicing/gpu.go:92-95): its node must be marked invalid
+      if (tot > mem_gb[g]) return fail(h, NOSPLAN_ERR_RANGE, "GPU %d: slices total %lld GB exceed memory %d GB", g, (long long)tot, mem_gb[g]);
+    }
+  int rc = bind(h);
+  if (rc) return rc;
+  if ((rc = upload(h, h->d_mps_sizes, sizes_gb, sizeof(int32_t) * S, h->stream))) return rc;
+  if ((rc = upload(h, h->d_mps_off, gpu_off, sizeof(int32_t) * (n_nodes + 1), h->stream))) return rc;
+  if ((rc = upload(h, h->d_mps_valid, v.data(), std::max(n_nodes, 1), h->stream))) return rc;
+  if ((rc = upload(h, h->d_in[0], mem_gb, sizeof(int32_t) * std::max(tg, 0), h->stream))) return rc;
+  if ((rc = upload(h, h->d_in[1], used, sizeof(int32_t) * (size_t)tg * S, h->stream))) return rc;
+  if ((rc = upload(h, h->d_in[2], free_, sizeof(int32_t) * (size_t)tg * S, h->stream))) return rc;
+  if (free_mask && (rc = upload(h, h->d_in[3], free_mask, sizeof(uint32_t) * std::max(tg, 0), h->stream))) return rc;
+  CU(h->d_mps_gpu0.reserve(sizeof(MpsGpu) * std::max(tg, 1)));
+  CU(h->d_mps_ulo0.reserve(sizeof(uint4) * std::max(tg, 1)));
+  CU(h->d_mps_uhi0.reserve(sizeof(uint4) * std::max(tg, 1)));
+  CU(h->d_mps_gpu.reserve(sizeof(MpsGpu) * std::max(tg, 1)));
+  CU(h->d_mps_ulo.reserve(sizeof(uint4) * std::max(tg, 1)));
+  CU(h->d_mps_uhi.reserve(sizeof(uint4) * std::max(tg, 1)));
+  if (tg > 0) {
+    mps_pack_kernel<<<(tg + 127) / 128, 128, 0, h->stream>>>(
+        n_nodes, S, h->d_mps_sizes.as<int32_t>(), h->d_mps_off.as<int32_t>(), h->d_in[0].as<int32_t>(),
+        h->d_in[1].as<int32_t>(), h->d_in[2].as<int32_t>(), free_mask ? h->d_in[3].as<uint32_t>() : nullptr,
+        h->d_mps_gpu0.as<MpsGpu>(), h->d_mps_ulo0.as<uint4>(), h->d_mps_uhi0.as<uint4>());
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(h->d_mps_gpu.p, h->d_mps_gpu0.p, sizeof(MpsGpu) * tg, cudaMemcpyDeviceToDevice, h->stream));
+    CU(cudaMemcpyAsync(h->d_mps_ulo.p, h->d_mps_ulo0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, h->stream));
+    CU(cudaMemcpyAsync(h->d_mps_uhi.p, h->d_mps_uhi0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, h->stream));
+  }
+  CU(cudaStreamSynchronize(h->stream));
+  h->S = S;
+  h->mps_n = n_nodes;
+  h->mps_tg = tg;
+  h->mps_gs = std::max(gs, 1);
+  h->mps_evals = evals;
+  h->have_mps = true;
+  h->mps_state_dirty = false;
+  return NOSPLAN_OK;
+}
+
+int64_t nosplan_mig_evals_per_demand(const nosplan_t* h) { return (h && h->have_mig) ? h->mig_evals : 0; }
+int64_t nosplan_mps_evals_per_demand(const nosplan_t* h) { return (h && h->have_mps) ? h->mps_evals : 0; }
+
+int nosplan_score_mig_dev(nosplan_t* h, int n_demands, const int32_t* dem_off, const int32_t* dem_key,
+                          const int32_t* dem_qty, int32_t* first_node, uint8_t* updated, int8_t* choice, void* stream) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  if (!h->have_mig) return fail(h, NOSPLAN_ERR_ARG, "no MIG snapshot");
+  if (!first_node) return fail(h, NOSPLAN_ERR_ARG, "first_node is required");
+  int rc = bind(h);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  rc = launch_mig_score(h, n_demands, dem_off, dem_key, dem_qty, first_node, updated, choice, st);
+  if (rc) return rc;
+  if (n_demands > 0) nonode_to_minus1_kernel<<<(n_demands + 255) / 256, 256, 0, st>>>(first_node, n_demands);
+  CU(cudaGetLastError());
+  return NOSPLAN_OK;
+}
+
+int nosplan_score_mps_dev(nosplan_t* h, int n_demands, const int32_t* dem_off, const int32_t* dem_key,
+                          const int32_t* dem_qty, int32_t* first_node, uint8_t* updated, uint8_t* out_free,
+                          uint32_t* out_free_mask, void* stream) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  if (!h->have_mps) return fail(h, NOSPLAN_ERR_ARG, "no MPS snapshot");
+  if (!first_node) return fail(h, NOSPLAN_ERR_ARG, "first_node is required");
+  if ((out_free == nullptr) != (out_free_mask == nullptr)) return fail(h, NOSPLAN_ERR_ARG, "out_free and out_free_mask go together");
+  int rc = bind(h);
+  if (rc) return rc;
+  return launch_mps_score(h, n_demands, dem_off, dem_key, dem_qty, first_node, updated, out_free, out_free_mask,
+                          (cudaStream_t)stream);
+}
+
+int nosplan_score_mig(nosplan_t* h, int n_demands, const int32_t* dem_off, const int32_t* dem_key,
+                      const int32_t* dem_qty, int32_t* first_node, int8_t* first_choice, uint8_t* updated, int8_t* choice,
+                      int64_t* n_evals) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  if (!h->have_mig) return fail(h, NOSPLAN_ERR_ARG, "no MIG snapshot");
+  int rc = check_demands(h, n_demands, dem_off, dem_key, dem_qty, h->P);
+  if (rc) return rc;
+  if ((rc = bind(h))) return rc;
+  if (n_evals) *n_evals = (int64_t)n_demands * h->mig_evals;
+  const int D = n_demands;
+  if (D == 0) return NOSPLAN_OK;
+  cudaStream_t st = h->stream;
+  const int nnz = dem_off[D];
+  if ((rc = upload(h, h->d_dem[0], dem_off, sizeof(int32_t) * (D + 1), st))) return rc;
+  if ((rc = upload(h, h->d_dem[1], dem_key, sizeof(int32_t) * std::max(nnz, 1), st))) return rc;
+  if ((rc = upload(h, h->d_dem[2], dem_qty, sizeof(int32_t) * std::max(nnz, 1), st))) return rc;
+  CU(h->d_out[0].reserve(sizeof(int32_t) * D));
+  if (updated) CU(h->d_out[1].reserve((size_t)D * std::max(h->mig_n, 1)));
+  if (choice) CU(h->d_out[2].reserve((size_t)D * std::max(h->mig_tg, 1)));
+  if (first_choice) CU(h->d_out[3].reserve((size_t)D * h->mig_gs));
+  rc = launch_mig_score(h, D, h->d_dem[0].as<int32_t>(), h->d_dem[1].as<int32_t>(), h->d_dem[2].as<int32_t>(),
+                        h->d_out[0].as<int32_t>(), updated ? h->d_out[1].as<uint8_t>() : nullptr,
+                        choice ? h->d_out[2].as<int8_t>() : nullptr, st);
+  if (rc) return rc;
+  mig_finalize_kernel<<<(D + 127) / 128, 128, 0, st>>>(
+      h->d_tables.as<MigTables>(), h->d_mig_used0.as<uint4>(), h->d_mig_free0.as<uint4>(), h->d_mig_model.as<uint8_t>(),
+      h->d_mig_off.as<int32_t>(), D, h->mig_gs, h->d_dem[0].as<int32_t>(), h->d_dem[1].as<int32_t>(),
+      h->d_dem[2].as<int32_t>(), h->d_out[0].as<int32_t>(), first_choice ? h->d_out[3].as<int8_t>() : nullptr);
+  CU(cudaGetLastError());
+  if (first_node) CU(cudaMemcpyAsync(first_node, h->d_out[0].p, sizeof(int32_t) * D, cudaMemcpyDeviceToHost, st));
+  if (first_choice) CU(cudaMemcpyAsync(first_choice, h->d_out[3].p, (size_t)D * h->mig_gs, cudaMemcpyDeviceToHost, st));
+  if (updated && h->mig_n) CU(cudaMemcpyAsync(updated, h->d_out[1].p, (size_t)D * h->mig_n, cudaMemcpyDeviceToHost, st));
+  if (choice && h->mig_tg) CU(cudaMemcpyAsync(choice, h->d_out[2].p, (size_t)D * h->mig_tg, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  return NOSPLAN_OK;
+}
+
+int nosplan_score_mps(nosplan_t* h, int n_demands, const int32_t* dem_off, const int32_t* dem_key,
+                      const int32_t* dem_qty, int32_t* first_node, uint8_t* updated, uint8_t* out_free,
+                      uint32_t* out_free_mask, int64_t* n_evals) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  if (!h->have_mps) return fail(h, NOSPLAN_ERR_ARG, "no MPS snapshot");
+  if ((out_free == nullptr) != (out_free_mask == nullptr)) return fail(h, NOSPLAN_ERR_ARG, "out_free and out_free_mask go together");
+  int rc = check_demands(h, n_demands, dem_off, dem_key, dem_qty, h->S);
+  if (rc) return rc;
+  if ((rc = bind(h))) return rc;
+  if (n_evals) *n_evals = (int64_t)n_demands * h->mps_evals;
+  const int D = n_demands;
+  if (D == 0) return NOSPLAN_OK;
+  cudaStream_t st = h->stream;
+  const int nnz = dem_off[D];
+  if ((rc = upload(h, h->d_dem[0], dem_off, sizeof(int32_t) * (D + 1), st))) return rc;
+  if ((rc = upload(h, h->d_dem[1], dem_key, sizeof(int32_t) * std::max(nnz, 1), st))) return rc;
+  if ((rc = upload(h, h->d_dem[2], dem_qty, sizeof(int32_t) * std::max(nnz, 1), st))) return rc;
+  CU(h->d_out[0].reserve(sizeof(int32_t) * D));
+  if (updated) CU(h->d_out[1].reserve((size_t)D * std::max(h->mps_n, 1)));
+  if (out_free) {
+    CU(h->d_out[2].reserve((size_t)D * std::max(h->mps_tg, 1) * h->S));
+    CU(h->d_out[3].reserve(sizeof(uint32_t) * (size_t)D * std::max(h->mps_tg, 1)));
+  }
+  rc = launch_mps_score(h, D, h->d_dem[0].as<int32_t>(), h->d_dem[1].as<int32_t>(), h->d_dem[2].as<int32_t>(),
+                        h->d_out[0].as<int32_t>(), updated ? h->d_out[1].as<uint8_t>() : nullptr,
+                        out_free ? h->d_out[2].as<uint8_t>() : nullptr, out_free ? h->d_out[3].as<uint32_t>() : nullptr, st);
+  if (rc) return rc;
+  if (first_node) CU(cudaMemcpyAsync(first_node, h->d_out[0].p, sizeof(int32_t) * D, cudaMemcpyDeviceToHost, st));
+  if (updated && h->mps_n) CU(cudaMemcpyAsync(updated, h->d_out[1].p, (size_t)D * h->mps_n, cudaMemcpyDeviceToHost, st));
+  if (out_free && h->mps_tg) {
+    CU(cudaMemcpyAsync(out_free, h->d_out[2].p, (size_t)D * h->mps_tg * h->S, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(out_free_mask, h->d_out[3].p, sizeof(uint32_t) * (size_t)D * h->mps_tg, cudaMemcpyDeviceToHost, st));
+  }
+  CU(cudaStreamSynchronize(st));
+  return NOSPLAN_OK;
+}
+
+int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* dem_off, const int32_t* dem_key,
+                 const int32_t* dem_qty, int flags, uint8_t* gate_hit, int32_t* repart_node, int32_t* sched_node,
+                 int32_t* sched_gpu) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  if (n_pods < 0) return fail(h, NOSPLAN_ERR_ARG, "negative pod count");
+  if (n_pods > 0 && (!kind || !dem_off)) return fail(h, NOSPLAN_ERR_ARG, "null pod arrays");
+  int rc = bind(h);
+  if (rc) return rc;
+  // split by kind (order kept) and deduplicate request vectors: pods with the same vector share a row
+  struct Side {
+    std::vector<int32_t> pod_idx, pod_sig, off{0}, key, qty;
+    std::map<std::vector<int32_t>, int> sigs;
+  } side[2];
+  for (int i = 0; i < n_pods; ++i) {
+    const int kd = kind[i] ? 1 : 0;
+    const int n_keys = kd ? h->S : h->P;
+    if (kd ? !h->have_mps : !h->have_mig) {
+      // no nodes of that kind: the controller returns before doing anything (mig_controller.go:78-81)
+      if (gate_hit) gate_hit[i] = 0;
+      if (repart_node) repart_node[i] = -1;
+      if (sched_node) sched_node[i] = -1;
+      if (sched_gpu) sched_gpu[i] = -1;
+      continue;
+    }
+    const int e0 = dem_off[i], e1 = dem_off[i + 1];
+    if (e1 < e0 || e1 - e0 > NOSPLAN_MAX_DEMAND_KEYS) return fail(h, NOSPLAN_ERR_RANGE, "pod %d: bad demand row", i);
+    std::vector<int32_t> sig;
+    for (int e = e0; e < e1; ++e) {
+      if (dem_key[e] < 0 || dem_key[e] >= n_keys) return fail(h, NOSPLAN_ERR_RANGE, "pod %d: key %d out of range", i, dem_key[e]);
+      if (e > e0 && dem_key[e] <= dem_key[e - 1]) return fail(h, NOSPLAN_ERR_ARG, "pod %d: keys must be strictly ascending", i);
+      if (dem_qty[e] < 0 || dem_qty[e] > NOSPLAN_MAX_DEMAND_QTY) return fail(h, NOSPLAN_ERR_RANGE, "pod %d: quantity out of range", i);
+      sig.push_back(dem_key[e]);
+      sig.push_back(dem_qty[e]);
+    }
+    Side& s = side[kd];
+    auto it = s.sigs.find(sig);
+    int id;
+    if (it == s.sigs.end()) {
+      id = (int)s.sigs.size();
+      s.sigs.emplace(sig, id);
+      for (size_t j = 0; j < sig.size(); j += 2) {
+        s.key.push_back(sig[j]);
+        s.qty.push_back(sig[j + 1]);
+      }
+      s.off.push_back((int32_t)s.key.size());
+    } else {
+      id = it->second;
+    }
+    s.pod_idx.push_back(i);
+    s.pod_sig.push_back(id);
+  }
+  // reset the working state to the snapshot
+  if (h->have_mig && h->mig_tg) {
+    CU(cudaMemcpyAsync(h->d_mig_used.p, h->d_mig_used0.p, sizeof(uint4) * h->mig_tg, cudaMemcpyDeviceToDevice, h->stream));
+    CU(cudaMemcpyAsync(h->d_mig_free.p, h->d_mig_free0.p, sizeof(uint4) * h->mig_tg, cudaMemcpyDeviceToDevice, h->stream));
+  }
+  if (h->have_mps && h->mps_tg) {
+    CU(cudaMemcpyAsync(h->d_mps_gpu.p, h->d_mps_gpu0.p, sizeof(MpsGpu) * h->mps_tg, cudaMemcpyDeviceToDevice, h->stream2));
+    CU(cudaMemcpyAsync(h->d_mps_ulo.p, h->d_mps_ulo0.p, sizeof(uint4) * h->mps_tg, cudaMemcpyDeviceToDevice, h->stream2));
+    CU(cudaMemcpyAsync(h->d_mps_uhi.p, h->d_mps_uhi0.p, sizeof(uint4) * h->mps_tg, cudaMemcpyDeviceToDevice, h->stream2));
+  }
+  std::vector<uint8_t> o_gate[2];
+  std::vector<int32_t> o_rep[2], o_node[2], o_gpu[2];
+  for (int kd = 0; kd < 2; ++kd) {
+    Side& s = side[kd];
+    const int M = (int)s.pod_idx.size();
+    if (M == 0) continue;
+    cudaStream_t st = kd ? h->stream2 : h->stream;
+    DevBuf* b = h->d_plan + kd * 8;
+    const int D = (int)s.sigs.size();
+    PlanArgs a;
+    std::memset(&a, 0, sizeof(a));
+    a.M = M;
+    a.D = D;
+    a.flags = flags;
+    if ((rc = upload(h, b[0], s.pod_sig.data(), sizeof(int32_t) * M, st))) return rc;
+    if ((rc = upload(h, b[1], s.off.data(), sizeof(int32_t) * (D + 1), st))) return rc;
+    if ((rc = upload(h, b[2], s.key.data(), sizeof(int32_t) * std::max<size_t>(s.key.size(), 1), st))) return rc;
+    if ((rc = upload(h, b[3], s.qty.data(), sizeof(int32_t) * std::max<size_t>(s.qty.size(), 1), st))) return rc;
+    a.pod_sig = b[0].as<int32_t>();
+    a.dem_off = b[1].as<int32_t>();
+    a.dem_key = b[2].as<int32_t>();
+    a.dem_qty = b[3].as<int32_t>();
+    if (kd == 0) {
+      a.N = h->mig_n;
+      a.tg = h->mig_tg;
+      a.n_keys = h->P;
+      a.gpu_off = h->d_mig_off.as<int32_t>();
+      a.valid = h->d_mig_valid.as<uint8_t>();
+      a.T = h->d_tables.as<MigTables>();
+      a.m_used = h->d_mig_used.as<uint4>();
+      a.m_free = h->d_mig_free.as<uint4>();
+      a.m_model = h->d_mig_model.as<uint8_t>();
+      h->mig_state_dirty = true;
+    } else {
+      a.N = h->mps_n;
+      a.tg = h->mps_tg;
+      a.n_keys = h->S;
+      a.gpu_off = h->d_mps_off.as<int32_t>();
+      a.valid = h->d_mps_valid.as<uint8_t>();
+      a.sizes = h->d_mps_sizes.as<int32_t>();
+      a.p_gpu = h->d_mps_gpu.as<MpsGpu>();
+      a.p_used_lo = h->d_mps_ulo.as<uint4>();
+      a.p_used_hi = h->d_mps_uhi.as<uint4>();
+      h->mps_state_dirty = true;
+    }
+    a.words = (a.tg + 31) / 32 + 1;
+    CU(b[4].reserve(sizeof(uint32_t) * (size_t)a.words * (a.n_keys + 1)));
+    CU(b[5].reserve(sizeof(int32_t) * 2 * (size_t)D));
+    CU(b[6].reserve((size_t)M * (1 + 3 * sizeof(int32_t)) + 64));
+    a.bitmaps = b[4].as<uint32_t>();
+    a.bounds = b[5].as<int32_t>();
+    // outputs packed in one buffer: rep | node | gpu (int32 each) | gate (u8)
+    a.repart_node = b[6].as<int32_t>();
+    a.sched_node = a.repart_node + M;
+    a.sched_gpu = a.sched_node + M;
+    a.gate_hit = reinterpret_cast<uint8_t*>(a.sched_gpu + M);
+    if (kd == 0) plan_kernel<false><<<1, kPlanThreads, 0, st>>>(a);
+    else plan_kernel<true><<<1, kPlanThreads, 0, st>>>(a);
+    CU(cudaGetLastError());
+    o_rep[kd].resize(M);
+    o_node[kd].resize(M);
+    o_gpu[kd].resize(M);
+    o_gate[kd].resize(M);
+    CU(cudaMemcpyAsync(o_rep[kd].data(), a.repart_node, sizeof(int32_t) * M, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(o_node[kd].data(), a.sched_node, sizeof(int32_t) * M, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(o_gpu[kd].data(), a.sched_gpu, sizeof(int32_t) * M, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(o_gate[kd].data(), a.gate_hit, M, cudaMemcpyDeviceToHost, st));
+  }
+  CU(cudaStreamSynchronize(h->stream));
+  CU(cudaStreamSynchronize(h->stream2));
+  for (int kd = 0; kd < 2; ++kd) {
+    Side& s = side[kd];
+    for (size_t j = 0; j < s.pod_idx.size(); ++j) {
+      const int i = s.pod_idx[j];
+      if (gate_hit) gate_hit[i] = o_gate[kd][j];
+      if (repart_node) repart_node[i] = o_rep[kd][j];
+      if (sched_node) sched_node[i] = o_node[kd][j];
+      if (sched_gpu) sched_gpu[i] = o_gpu[kd][j];
+    }
+  }
+  return NOSPLAN_OK;
+}
+
+int nosplan_get_mig_state(nosplan_t* h, int32_t* used, int32_t* free_) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  if (!h->have_mig) return fail(h, NOSPLAN_ERR_ARG, "no MIG snapshot");
+  if (!used || !free_) return fail(h, NOSPLAN_ERR_ARG, "null output");
+  int rc = bind(h);
+  if (rc) return rc;
+  const int tg = h->mig_tg, P = h->P;
+  if (tg == 0) return NOSPLAN_OK;
+  CU(h->d_in[4].reserve(sizeof(int32_t) * (size_t)tg * P));
+  CU(h->d_in[5].reserve(sizeof(int32_t) * (size_t)tg * P));
+  mig_unpack_kernel<<<(tg + 127) / 128, 128, 0, h->stream>>>(tg, P, h->d_mig_used.as<uint4>(), h->d_mig_free.as<uint4>(),
+                                                            h->d_in[4].as<int32_t>(), h->d_in[5].as<int32_t>());
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(used, h->d_in[4].p, sizeof(int32_t) * (size_t)tg * P, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaMemcpyAsync(free_, h->d_in[5].p, sizeof(int32_t) * (size_t)tg * P, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return NOSPLAN_OK;
+}
+
+int nosplan_get_mps_state(nosplan_t* h, int32_t* used, int32_t* free_, uint32_t* free_mask) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  if (!h->have_mps) return fail(h, NOSPLAN_ERR_ARG, "no MPS snapshot");
+  if (!used || !free_) return fail(h, NOSPLAN_ERR_ARG, "null output");
+  int rc = bind(h);
+  if (rc) return rc;
+  const int tg = h->mps_tg, S = h->S;
+  if (tg == 0) return NOSPLAN_OK;
+  CU(h->d_in[4].reserve(sizeof(int32_t) * (size_t)tg * S));
+  CU(h->d_in[5].reserve(sizeof(int32_t) * (size_t)tg * S));
+  CU(h->d_in[3].reserve(sizeof(uint32_t) * (size_t)tg));
+  mps_unpack_kernel<<<(tg + 127) / 128, 128, 0, h->stream>>>(tg, S, h->d_mps_gpu.as<MpsGpu>(), h->d_mps_ulo.as<uint4>(),
+                                                            h->d_mps_uhi.as<uint4>(), h->d_in[4].as<int32_t>(),
+                                                            h->d_in[5].as<int32_t>(), h->d_in[3].as<uint32_t>());
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(used, h->d_in[4].p, sizeof(int32_t) * (size_t)tg * S, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaMemcpyAsync(free_, h->d_in[5].p, sizeof(int32_t) * (size_t)tg * S, cudaMemcpyDeviceToHost, h->stream));
+  if (free_mask) CU(cudaMemcpyAsync(free_mask, h->d_in[3].p, sizeof(uint32_t) * (size_t)tg, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return NOSPLAN_OK;
+}
+
+int nosplan_init_geometry_mig(nosplan_t* h, uint8_t* err, int32_t* out_free) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  if (!h->have_mig) return fail(h, NOSPLAN_ERR_ARG, "no MIG snapshot");
+  if (!err || !out_free) return fail(h, NOSPLAN_ERR_ARG, "null output");
+  int rc = bind(h);
+  if (rc) return rc;
+  const int tg = h->mig_tg, P = h->P;
+  if (tg == 0) return NOSPLAN_OK;
+  CU(h->d_out[4].reserve(tg));
+  CU(h->d_out[5].reserve(sizeof(int32_t) * (size_t)tg * P));
+  mig_init_geometry_kernel<<<(tg + 127) / 128, 128, 0, h->stream>>>(
+      h->d_tables.as<MigTables>(), tg, P, h->d_mig_used0.as<uint4>(), h->d_mig_free0.as<uint4>(),
+      h->d_mig_model.as<uint8_t>(), h->d_out[4].as<uint8_t>(), h->d_out[5].as<int32_t>());
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(err, h->d_out[4].p, tg, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaMemcpyAsync(out_free, h->d_out[5].p, sizeof(int32_t) * (size_t)tg * P, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return NOSPLAN_OK;
+}
+
+}  // extern "C"

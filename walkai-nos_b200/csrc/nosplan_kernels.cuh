@@ -1,0 +1,630 @@
+// nosplan_kernels.cuh — device data layout and kernels of the planner hot path (sm_100a).
+//
+// Integer scoring, no tensor cores: the work is byte/small-int compares over SoA state, bounded by
+// HBM/L2 bandwidth for the streaming form and by the INT32 pipes once state is tiled in shared
+// memory (DESIGN.md "Kernels").  Reference semantics: SURVEY §A, cited per function below.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "nosplan.h"
+
+namespace nsp {
+
+constexpr int kMaxProf = NOSPLAN_MAX_MIG_PROFILES;               // 16 bytes = one uint4 per map
+constexpr int kMaxModels = NOSPLAN_MAX_MODELS;
+constexpr int kMaxGeoms = NOSPLAN_MAX_GEOMS;
+constexpr int kMaxTotalGeoms = kMaxModels * kMaxGeoms;
+constexpr int kMaxSizes = NOSPLAN_MAX_MPS_SIZES;                  // 32 bytes = two uint4 per map
+constexpr int kMaxKeys = NOSPLAN_MAX_DEMAND_KEYS;
+constexpr int kNoNode = 0x7fffffff;
+
+// ---- MIG geometry tables (global memory, one per handle) ---------------------------------------------
+struct MigTables {
+  int n_models;
+  int n_prof;
+  int n_geoms;                        // total over models
+  int geom_off[kMaxModels + 1];       // CSR over models
+  int init_choice[kMaxModels];        // GetFewestSlicesGeometry index (partitioning.go:67-79), -1 if empty
+  uint4 cand[kMaxTotalGeoms];         // 16 x u8 quantity per profile id
+  uint16_t total[kMaxTotalGeoms];     // totalSliceCount (gpu.go:262-268)
+  uint8_t rank[kMaxTotalGeoms];       // rank of Geometry.Id() among the model's ids, bytewise ascending
+};
+
+__device__ __forceinline__ uint32_t byte_of(const uint4& v, int i) {
+  uint32_t w = (i < 8) ? ((i < 4) ? v.x : v.y) : ((i < 12) ? v.z : v.w);
+  return (w >> ((i & 3) * 8)) & 0xffu;
+}
+__device__ __forceinline__ uint32_t word_of(const uint4& v, int i) {
+  return (i < 2) ? ((i == 0) ? v.x : v.y) : ((i == 2) ? v.z : v.w);
+}
+__device__ __forceinline__ uint4 add4(const uint4& a, const uint4& b) {  // bytewise, no carries (<=255 checked on host)
+  return make_uint4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+}
+__device__ __forceinline__ uint4 sub4(const uint4& a, const uint4& b) {  // bytewise a-b where a>=b bytewise
+  return make_uint4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w);
+}
+// every byte of a >= the matching byte of b  (CanApplyGeometry's used-device check, gpu.go:105-109)
+__device__ __forceinline__ bool all_ge4(const uint4& a, const uint4& b) {
+  return (__vcmpgeu4(a.x, b.x) & __vcmpgeu4(a.y, b.y) & __vcmpgeu4(a.z, b.z) & __vcmpgeu4(a.w, b.w)) == 0xffffffffu;
+}
+// sum over bytes |a-b|  (geometryDistance, gpu.go:245-260; missing keys are 0 on both sides)
+__device__ __forceinline__ uint32_t sad16(const uint4& a, const uint4& b) {
+  return __vsadu4(a.x, b.x) + __vsadu4(a.y, b.y) + __vsadu4(a.z, b.z) + __vsadu4(a.w, b.w);
+}
+// demand-independent part of geometrySelectionScore (gpu.go:225-243): total up, distance down, id down.
+// 0 is reserved for "cannot apply"; a feasible key is never 0 because 255-rank >= 223.
+__device__ __forceinline__ uint32_t key0_of(uint32_t total, uint32_t dist, uint32_t rank) {
+  return (total << 20) | ((4095u - dist) << 8) | (255u - rank);
+}
+
+// ---- generic (unpacked) node walk on AoS state ----------------------------------------------------------
+// mig.Node.UpdateGeometryFor (node.go:145-177) over GPUs [g0, g0+cnt) with demand (pid[], qty[]) of k
+// keys.  If commit, free[] is rewritten (ApplyGeometry, gpu.go:134-154); choice (may be null) gets
+// the applied geometry index per GPU or -1.  Returns anyGpuUpdated.
+template <bool CG>
+__device__ __forceinline__ uint4 ld_state(const uint4* p) {
+  if constexpr (CG) return __ldcg(p);
+  else return *p;
+}
+template <bool CG>
+__device__ __forceinline__ void st_state(uint4* p, const uint4& v) {
+  if constexpr (CG) __stcg(p, v);
+  else *p = v;
+}
+
+// CG = state loads/stores bypass L1 (the planner kernel mutates the state it reads within one launch).
+template <bool CG = false>
+__device__ inline bool mig_walk_node(const MigTables* __restrict__ T, const uint4* used, uint4* fr,
+                                     const uint8_t* __restrict__ model, int g0, int cnt, int k,
+                                     const int* __restrict__ pid, const int* __restrict__ qty, bool commit,
+                                     int8_t* choice) {
+  int resid[kMaxKeys];
+#pragma unroll
+  for (int j = 0; j < kMaxKeys; ++j) resid[j] = (j < k) ? max(qty[j], 0) : 0;
+  bool any = false;
+  if (k == 0) cnt = 0;  // node.go:150-152
+  for (int s = 0; s < cnt; ++s) {
+    const int g = g0 + s;
+    const uint4 u = ld_state<CG>(used + g);
+    const uint4 f = ld_state<CG>(fr + g);
+    const uint4 cur = add4(u, f);  // GetGeometry, gpu.go:84-95
+    const int m = model[g];
+    const int c0 = T->geom_off[m], c1 = T->geom_off[m + 1];
+    int best = -1;
+    uint32_t best_prov = 0, best_k0 = 0;
+    for (int c = c0; c < c1; ++c) {
+      const uint4 cd = T->cand[c];
+      if (!all_ge4(cd, u)) continue;  // CanApplyGeometry
+      int prov = 0;                   // countProvidedProfiles, gpu.go:198-223
+      for (int j = 0; j < k; ++j) {
+        const int fj = (int)byte_of(f, pid[j]);
+        const int needed = resid[j] - fj;
+        if (needed <= 0) continue;
+        const int add = (int)byte_of(cd, pid[j]) - (int)byte_of(cur, pid[j]);
+        if (add <= 0) continue;
+        prov += min(add, needed);
+      }
+      if (prov <= 0) continue;
+      const uint32_t k0 = key0_of(T->total[c], sad16(cd, cur), T->rank[c]);
+      if (best < 0 || (uint32_t)prov > best_prov || ((uint32_t)prov == best_prov && k0 > best_k0)) {
+        best = c;
+        best_prov = prov;
+        best_k0 = k0;
+      }
+    }
+    uint4 nf = f;
+    if (best >= 0) {
+      any = true;
+      nf = sub4(T->cand[best], u);  // free[p] = cand[p]-used[p]; keys outside cand vanish (cand[p]=0=used[p])
+      if (commit) st_state<CG>(fr + g, nf);
+    }
+    if (choice) choice[s] = (int8_t)(best >= 0 ? best - c0 : -1);
+    for (int j = 0; j < k; ++j) resid[j] = max(resid[j] - (int)byte_of(nf, pid[j]), 0);  // node.go:164-169
+  }
+  return any;
+}
+
+// ---- pack kernels: int32 rows from the host -> byte-packed device state ------------------------------------
+// MIG: used/free [tg][P] int32 -> uint4 per GPU (AoS, CSR order) and slot-major copies for the scorer:
+// sused/sfree[slot][npad] (uint4), smodel[slot][npad] (0xff = no such GPU).
+__global__ void mig_pack_kernel(int N, int P, int gs, int npad, const int32_t* __restrict__ gpu_off,
+                                const uint8_t* __restrict__ valid, const int32_t* __restrict__ model,
+                                const int32_t* __restrict__ used, const int32_t* __restrict__ fr, uint4* __restrict__ a_used,
+                                uint4* __restrict__ a_free, uint8_t* __restrict__ a_model, uint4* __restrict__ s_used,
+                                uint4* __restrict__ s_free, uint8_t* __restrict__ s_model, uint8_t* __restrict__ s_cnt) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= npad) return;
+  const int g0 = n < N ? gpu_off[n] : 0;
+  const int cnt = n < N ? gpu_off[n + 1] - g0 : 0;
+  const bool ok = n < N && valid[n];
+  s_cnt[n] = ok ? (uint8_t)cnt : 0;  // an invalid node behaves like a node the controller skips
+  for (int s = 0; s < gs; ++s) {
+    uint4 u = make_uint4(0, 0, 0, 0), f = u;
+    uint8_t m = 0xff;
+    if (s < cnt) {
+      const int g = g0 + s;
+      uint32_t uw[4] = {0, 0, 0, 0}, fw[4] = {0, 0, 0, 0};
+      for (int p = 0; p < P; ++p) {
+        uw[p >> 2] |= (uint32_t)(used[(size_t)g * P + p] & 0xff) << ((p & 3) * 8);
+        fw[p >> 2] |= (uint32_t)(fr[(size_t)g * P + p] & 0xff) << ((p & 3) * 8);
+      }
+      u = make_uint4(uw[0], uw[1], uw[2], uw[3]);
+      f = make_uint4(fw[0], fw[1], fw[2], fw[3]);
+      m = (uint8_t)model[g];
+      a_used[g] = u;
+      a_free[g] = f;
+      a_model[g] = m;
+    }
+    s_used[(size_t)s * npad + n] = u;
+    s_free[(size_t)s * npad + n] = f;
+    s_model[(size_t)s * npad + n] = ok ? m : (uint8_t)0xff;
+  }
+}
+
+__global__ void mig_unpack_kernel(int tg, int P, const uint4* __restrict__ a_used, const uint4* __restrict__ a_free,
+                                  int32_t* __restrict__ used, int32_t* __restrict__ fr) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= tg) return;
+  const uint4 u = a_used[g], f = a_free[g];
+  for (int p = 0; p < P; ++p) {
+    used[(size_t)g * P + p] = (int32_t)byte_of(u, p);
+    fr[(size_t)g * P + p] = (int32_t)byte_of(f, p);
+  }
+}
+
+// ---- MIG batched scorer ----------------------------------------------------------------------------------------
+// One thread per node of a tile, looping over a chunk of demand rows.  The demand-independent work
+// of gpu.go:168-188 (CanApplyGeometry, geometryDistance, totalSliceCount, the id rank) is hoisted
+// out of the demand loop: the prologue builds key0[slot][cand][node] in shared memory once per tile
+// and every (demand, node, GPU, candidate) evaluation then costs one conflict-free LDS, the
+// provided-profiles count for the demand's keys, and a compare.
+struct MigScoreArgs {
+  const MigTables* T;
+  const uint4* s_used;
+  const uint4* s_free;
+  const uint8_t* s_model;
+  const uint8_t* s_cnt;
+  const int32_t* gpu_off;
+  int N, npad, gs, cmax, tg;
+  int D, d_chunk;
+  const int32_t* dem_off;
+  const int32_t* dem_key;
+  const int32_t* dem_qty;
+  int32_t* first_node;  // atomicMin target, pre-filled with kNoNode
+  uint8_t* updated;     // [D][N] or null
+  int8_t* choice;       // [D][tg] or null
+};
+
+template <int TN>
+__global__ void __launch_bounds__(TN) mig_score_kernel(const MigScoreArgs a) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  // layout: cand bytes [n_geoms*16] | key0 [gs][cmax][TN] u32 | usedw [gs][4][TN] | freew [gs][4][TN] | coff [gs][TN] u16 | ccnt [gs][TN] u8
+  const MigTables* __restrict__ T = a.T;
+  const int n_geoms = T->n_geoms;
+  uint8_t* s_cand = smem;
+  uint32_t* s_key0 = reinterpret_cast<uint32_t*>(smem + (((size_t)n_geoms * 16 + 15) & ~(size_t)15));
+  uint32_t* s_usedw = s_key0 + (size_t)a.gs * a.cmax * TN;
+  uint32_t* s_freew = s_usedw + (size_t)a.gs * 4 * TN;
+  uint16_t* s_coff = reinterpret_cast<uint16_t*>(s_freew + (size_t)a.gs * 4 * TN);
+  uint8_t* s_ccnt = reinterpret_cast<uint8_t*>(s_coff + (size_t)a.gs * TN);
+
+  const int tid = threadIdx.x;
+  const int n = blockIdx.x * TN + tid;
+  for (int i = tid; i < n_geoms * 4; i += TN)
+    reinterpret_cast<uint32_t*>(s_cand)[i] = reinterpret_cast<const uint32_t*>(T->cand)[i];
+
+  const int cnt = (n < a.N) ? a.s_cnt[n] : 0;
+  const int g0 = (n < a.N) ? a.gpu_off[n] : 0;
+  for (int s = 0; s < cnt; ++s) {
+    const uint4 u = a.s_used[(size_t)s * a.npad + n];
+    const uint4 f = a.s_free[(size_t)s * a.npad + n];
+    const int m = a.s_model[(size_t)s * a.npad + n];
+    const uint4 cur = add4(u, f);
+    const int c0 = T->geom_off[m], c1 = T->geom_off[m + 1];
+    s_coff[s * TN + tid] = (uint16_t)c0;
+    s_ccnt[s * TN + tid] = (uint8_t)(c1 - c0);
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      s_usedw[(s * 4 + w) * TN + tid] = word_of(u, w);
+      s_freew[(s * 4 + w) * TN + tid] = word_of(f, w);
+    }
+    for (int c = c0; c < c1; ++c) {
+      const uint4 cd = T->cand[c];
+      const uint32_t k0 = all_ge4(cd, u) ? key0_of(T->total[c], sad16(cd, cur), T->rank[c]) : 0u;
+      s_key0[((size_t)s * a.cmax + (c - c0)) * TN + tid] = k0;
+    }
+  }
+  __syncthreads();
+
+  const int d_begin = blockIdx.y * a.d_chunk;
+  const int d_end = min(a.D, d_begin + a.d_chunk);
+  const int lane = tid & 31;
+  for (int d = d_begin; d < d_end; ++d) {
+    const int e0 = __ldg(a.dem_off + d), k = __ldg(a.dem_off + d + 1) - e0;  // uniform over the CTA
+    bool any = false;
+    if (k == 1) {
+      // fast path: single requested profile (every BASELINE config) — all state in registers
+      const int p = __ldg(a.dem_key + e0);
+      int resid = max(__ldg(a.dem_qty + e0), 0);
+      const int pw = p >> 2, psh = (p & 3) * 8;
+      for (int s = 0; s < cnt; ++s) {
+        const int uj = (s_usedw[(s * 4 + pw) * TN + tid] >> psh) & 0xff;
+        const int fj = (s_freew[(s * 4 + pw) * TN + tid] >> psh) & 0xff;
+        const int needed = resid - fj;
+        const int curj = uj + fj;
+        const int c0 = s_coff[s * TN + tid], cc = s_ccnt[s * TN + tid];
+        int best = -1;
+        uint32_t best_prov = 0, best_k0 = 0;
+        if (needed > 0) {
+          for (int c = 0; c < cc; ++c) {
+            const uint32_t k0 = s_key0[((size_t)s * a.cmax + c) * TN + tid];
+            const int add = (int)s_cand[(c0 + c) * 16 + p] - curj;
+            const uint32_t prov = (uint32_t)max(min(add, needed), 0);
+            const bool ok = (k0 != 0u) & (prov != 0u);
+            const bool better = ok & ((prov > best_prov) | ((prov == best_prov) & (k0 > best_k0)));
+            if (better) {
+              best = c;
+              best_prov = prov;
+              best_k0 = k0;
+            }
+          }
+        }
+        int nf = fj;
+        if (best >= 0) {
+          any = true;
+          nf = (int)s_cand[(c0 + best) * 16 + p] - uj;
+        }
+        if (a.choice) a.choice[(size_t)d * a.tg + g0 + s] = (int8_t)best;
+        resid = max(resid - nf, 0);
+      }
+    } else {
+      int pid[kMaxKeys], resid[kMaxKeys];
+      for (int j = 0; j < kMaxKeys; ++j) {
+        pid[j] = (j < k) ? __ldg(a.dem_key + e0 + j) : 0;
+        resid[j] = (j < k) ? max(__ldg(a.dem_qty + e0 + j), 0) : 0;
+      }
+      const int cnt_eff = (k == 0) ? 0 : cnt;
+      for (int s = 0; s < cnt; ++s) {
+        int best = -1;
+        if (s < cnt_eff) {
+          const int c0 = s_coff[s * TN + tid], cc = s_ccnt[s * TN + tid];
+          int uj[kMaxKeys], fj[kMaxKeys];
+          for (int j = 0; j < k; ++j) {
+            uj[j] = (s_usedw[(s * 4 + (pid[j] >> 2)) * TN + tid] >> ((pid[j] & 3) * 8)) & 0xff;
+            fj[j] = (s_freew[(s * 4 + (pid[j] >> 2)) * TN + tid] >> ((pid[j] & 3) * 8)) & 0xff;
+          }
+          uint32_t best_prov = 0, best_k0 = 0;
+          for (int c = 0; c < cc; ++c) {
+            const uint32_t k0 = s_key0[((size_t)s * a.cmax + c) * TN + tid];
+            int prov = 0;
+            for (int j = 0; j < k; ++j) {
+              const int needed = resid[j] - fj[j];
+              const int add = (int)s_cand[(c0 + c) * 16 + pid[j]] - (uj[j] + fj[j]);
+              if (needed > 0 && add > 0) prov += min(add, needed);
+            }
+            if (k0 != 0u && prov > 0 &&
+                ((uint32_t)prov > best_prov || ((uint32_t)prov == best_prov && k0 > best_k0))) {
+              best = c;
+              best_prov = prov;
+              best_k0 = k0;
+            }
+          }
+          for (int j = 0; j < k; ++j) {
+            const int nf = (best >= 0) ? (int)s_cand[(c0 + best) * 16 + pid[j]] - uj[j] : fj[j];
+            resid[j] = max(resid[j] - nf, 0);
+          }
+          if (best >= 0) any = true;
+        }
+        if (a.choice) a.choice[(size_t)d * a.tg + g0 + s] = (int8_t)best;
+      }
+    }
+    if (a.updated && n < a.N) a.updated[(size_t)d * a.N + n] = any ? 1 : 0;
+    const int mine = any ? n : kNoNode;
+    const int wmin = __reduce_min_sync(0xffffffffu, mine);
+    if (lane == 0 && wmin != kNoNode) atomicMin(a.first_node + d, wmin);
+  }
+}
+
+// first_node: kNoNode -> -1; optionally re-walk the winning node to emit its per-GPU choices
+__global__ void mig_finalize_kernel(const MigTables* __restrict__ T, const uint4* __restrict__ a_used,
+                                    const uint4* __restrict__ a_free, const uint8_t* __restrict__ a_model,
+                                    const int32_t* __restrict__ gpu_off, int D, int gs, const int32_t* __restrict__ dem_off,
+                                    const int32_t* __restrict__ dem_key, const int32_t* __restrict__ dem_qty,
+                                    int32_t* __restrict__ first_node, int8_t* __restrict__ first_choice) {
+  const int d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= D) return;
+  int fn = first_node[d];
+  if (fn == kNoNode) fn = -1;
+  first_node[d] = fn;
+  if (!first_choice) return;
+  int8_t ch[NOSPLAN_MAX_GPUS_PER_NODE];
+  for (int s = 0; s < NOSPLAN_MAX_GPUS_PER_NODE; ++s) ch[s] = -1;
+  if (fn >= 0) {
+    const int e0 = dem_off[d], k = dem_off[d + 1] - e0;
+    int pid[kMaxKeys], qty[kMaxKeys];
+    for (int j = 0; j < kMaxKeys; ++j) {
+      pid[j] = j < k ? dem_key[e0 + j] : 0;
+      qty[j] = j < k ? dem_qty[e0 + j] : 0;
+    }
+    const int g0 = gpu_off[fn], cnt = gpu_off[fn + 1] - g0;
+    mig_walk_node(T, a_used, const_cast<uint4*>(a_free), a_model, g0, cnt, k, pid, qty, false, ch);
+  }
+  for (int s = 0; s < gs; ++s) first_choice[(size_t)d * gs + s] = ch[s];
+}
+
+__global__ void fill_i32_kernel(int32_t* p, int n, int32_t v) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+__global__ void nonode_to_minus1_kernel(int32_t* p, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && p[i] == kNoNode) p[i] = -1;
+}
+
+// GPU.InitGeometry over every GPU (gpu.go:120-129): apply the model's fewest-kinds geometry unless a
+// used device would be deleted.
+__global__ void mig_init_geometry_kernel(const MigTables* __restrict__ T, int tg, int P, const uint4* __restrict__ a_used,
+                                         const uint4* __restrict__ a_free, const uint8_t* __restrict__ a_model,
+                                         uint8_t* __restrict__ err, int32_t* __restrict__ out_free) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= tg) return;
+  const uint4 u = a_used[g];
+  uint4 f = a_free[g];
+  const int m = a_model[g];
+  const int ic = T->init_choice[m];
+  bool e = true;
+  if (ic >= 0) {
+    const uint4 cd = T->cand[T->geom_off[m] + ic];
+    if (all_ge4(cd, u)) {
+      f = sub4(cd, u);
+      e = false;
+    }
+  } else {
+    // empty geometry list: nil geometry is not allowed by AllowsGeometry -> error
+    e = true;
+  }
+  err[g] = e ? 1 : 0;
+  for (int p = 0; p < P; ++p) out_free[(size_t)g * P + p] = (int32_t)byte_of(f, p);
+}
+
+// =================================================================================================================
+// MPS ("slicing")
+// Packed per-GPU state: free bytes [32] as two uint4 (key = size id), fmask = keys present in
+// FreeProfiles, cap = MemoryGB - sum(size*used) (what free slices may occupy), used bytes kept apart
+// (only AddPod and read-back need them).
+struct MpsGpu {
+  uint4 f0, f1;
+  uint32_t fmask;
+  uint32_t cap;
+};
+
+__device__ __forceinline__ uint32_t mps_byte(const uint4& lo, const uint4& hi, int i) {
+  return i < 16 ? byte_of(lo, i) : byte_of(hi, i - 16);
+}
+
+// slicing.GPU.UpdateGeometryFor (slicing/gpu.go:162-220) in closed form on one GPU.
+//   sz[]: size in GB per key; demand keys sid[0..k) ascending (= ascending size, the sort of :174-182),
+//   resid[]: remaining required quantity per key (0 = key absent).
+// Outputs: created[j] slices created for demand key j that survive, restored = orig keys whose
+// original count was put back (:214-216).  Returns updated.  FreeProfiles afterwards:
+//   free[key] = (restored bit ? orig : 0) + created(key);  present iff restored bit or created > 0.
+__device__ inline bool mps_gpu_update(const int* __restrict__ sz, const uint4& f0, const uint4& f1, uint32_t origmask,
+                                      uint32_t cap, int k, const int* sid, const int* resid, int* created,
+                                      uint32_t* restored_out) {
+  int miss[kMaxKeys];
+  bool any_missing = false;
+  for (int j = 0; j < k; ++j) {
+    created[j] = 0;
+    const int fj = (int)mps_byte(f0, f1, sid[j]);  // a present key holds its byte, an absent one 0
+    miss[j] = max(resid[j] - fj, 0);               // getMissingSlices, :222-232
+    any_missing |= miss[j] > 0;
+  }
+  *restored_out = origmask;
+  if (!any_missing) return false;  // :166-168
+  int origtot = 0;
+  for (uint32_t mk = origmask; mk; mk &= mk - 1) {
+    const int key = __ffs(mk) - 1;
+    origtot += sz[key] * (int)mps_byte(f0, f1, key);
+  }
+  int spare = (int)cap - origtot;  // MemoryGB - getTotSlicesMemory (:256-265)
+  uint32_t restored = origmask;
+  bool updated = false;
+  for (int j = 0; j < k; ++j) {
+    if (miss[j] <= 0) continue;
+    const int m = sz[sid[j]];
+    // (a) spare capacity first, :188-197 — createSlice until it fails == min(q, spare / m)
+    int k1 = min(miss[j], spare / m);
+    created[j] += k1;
+    spare -= k1 * m;
+    miss[j] -= k1;
+    updated |= k1 > 0;
+    // (b) delete every key of the ORIGINAL free map, :199-202 (whole entries: also what was just created under them)
+    for (uint32_t mk = restored; mk; mk &= mk - 1) {
+      const int key = __ffs(mk) - 1;
+      spare += sz[key] * (int)mps_byte(f0, f1, key);
+    }
+    restored = 0;
+    for (int i = 0; i < k; ++i)
+      if ((origmask >> sid[i]) & 1u) {
+        spare += created[i] * sz[sid[i]];
+        created[i] = 0;
+      }
+    // (c) create in the space made, :203-212
+    int k2 = min(miss[j], spare / m);
+    created[j] += k2;
+    spare -= k2 * m;
+    miss[j] -= k2;
+    updated |= k2 > 0;
+    // (d) restore the original free slices, ascending size, all-or-nothing per key, :214-216
+    for (uint32_t mk = origmask; mk; mk &= mk - 1) {
+      const int key = __ffs(mk) - 1;
+      const int need = sz[key] * (int)mps_byte(f0, f1, key);
+      if (spare >= need) {
+        restored |= 1u << key;
+        spare -= need;
+      }
+    }
+  }
+  *restored_out = restored;
+  return updated;
+}
+
+// slicing.Node.UpdateGeometryFor (slicing/node.go:120-152) over GPUs g[0..cnt).  If commit, the
+// packed state is rewritten.  out_free/out_mask (may be null): FreeProfiles after the walk.
+template <bool CG = false>
+__device__ inline bool mps_walk_node(const int* __restrict__ sz, int S, MpsGpu* gp, int g0, int cnt, int k,
+                                     const int* __restrict__ sid, const int* __restrict__ qty, bool commit,
+                                     uint8_t* out_free, uint32_t* out_mask) {
+  int resid[kMaxKeys];
+  for (int j = 0; j < kMaxKeys; ++j) resid[j] = (j < k) ? max(qty[j], 0) : 0;
+  bool any = false;
+  for (int s = 0; s < cnt; ++s) {
+    MpsGpu G;
+    G.f0 = ld_state<CG>(&gp[g0 + s].f0);
+    G.f1 = ld_state<CG>(&gp[g0 + s].f1);
+    if constexpr (CG) {
+      G.fmask = __ldcg(&gp[g0 + s].fmask);
+      G.cap = __ldcg(&gp[g0 + s].cap);
+    } else {
+      G.fmask = gp[g0 + s].fmask;
+      G.cap = gp[g0 + s].cap;
+    }
+    int created[kMaxKeys];
+    uint32_t restored = G.fmask;
+    bool upd = false;
+    if (k > 0) upd = mps_gpu_update(sz, G.f0, G.f1, G.fmask, G.cap, k, sid, resid, created, &restored);
+    any |= upd;
+    if (!upd) {
+      // untouched (when nothing was created every original key is restored: state identical)
+      for (int j = 0; j < k; ++j) resid[j] = max(resid[j] - (int)mps_byte(G.f0, G.f1, sid[j]), 0);
+      if (out_free) {
+        for (int key = 0; key < S; ++key) out_free[(size_t)s * S + key] = (uint8_t)mps_byte(G.f0, G.f1, key);
+        out_mask[s] = G.fmask;
+      }
+      continue;
+    }
+    uint32_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    uint32_t nmask = restored;
+    for (uint32_t mk = restored; mk; mk &= mk - 1) {
+      const int key = __ffs(mk) - 1;
+      w[key >> 2] |= mps_byte(G.f0, G.f1, key) << ((key & 3) * 8);
+    }
+    for (int j = 0; j < k; ++j) {
+      if (created[j] > 0) {
+        const int key = sid[j];
+        const uint32_t old = (w[key >> 2] >> ((key & 3) * 8)) & 0xffu;
+        w[key >> 2] = (w[key >> 2] & ~(0xffu << ((key & 3) * 8))) | ((old + (uint32_t)created[j]) << ((key & 3) * 8));
+        nmask |= 1u << key;
+      }
+    }
+    const uint4 n0 = make_uint4(w[0], w[1], w[2], w[3]), n1 = make_uint4(w[4], w[5], w[6], w[7]);
+    for (int j = 0; j < k; ++j) resid[j] = max(resid[j] - (int)mps_byte(n0, n1, sid[j]), 0);
+    if (commit) {
+      st_state<CG>(&gp[g0 + s].f0, n0);
+      st_state<CG>(&gp[g0 + s].f1, n1);
+      if constexpr (CG) __stcg(&gp[g0 + s].fmask, nmask);
+      else gp[g0 + s].fmask = nmask;
+    }
+    if (out_free) {
+      for (int key = 0; key < S; ++key) out_free[(size_t)s * S + key] = (uint8_t)mps_byte(n0, n1, key);
+      out_mask[s] = nmask;
+    }
+  }
+  return any;
+}
+
+__global__ void mps_pack_kernel(int N, int S, const int32_t* __restrict__ sizes, const int32_t* __restrict__ gpu_off,
+                                const int32_t* __restrict__ mem, const int32_t* __restrict__ used, const int32_t* __restrict__ fr,
+                                const uint32_t* __restrict__ fmask, MpsGpu* __restrict__ gp, uint4* __restrict__ used_lo,
+                                uint4* __restrict__ used_hi) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  const int tg = gpu_off[N];
+  if (g >= tg) return;
+  uint32_t uw[8] = {0, 0, 0, 0, 0, 0, 0, 0}, fw[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  int usedtot = 0;
+  uint32_t fm = 0;
+  for (int s = 0; s < S; ++s) {
+    const int u = used[(size_t)g * S + s], f = fr[(size_t)g * S + s];
+    uw[s >> 2] |= (uint32_t)(u & 0xff) << ((s & 3) * 8);
+    fw[s >> 2] |= (uint32_t)(f & 0xff) << ((s & 3) * 8);
+    usedtot += sizes[s] * u;
+    if (fmask ? ((fmask[g] >> s) & 1u) : (f > 0)) fm |= 1u << s;
+  }
+  MpsGpu G;
+  G.f0 = make_uint4(fw[0], fw[1], fw[2], fw[3]);
+  G.f1 = make_uint4(fw[4], fw[5], fw[6], fw[7]);
+  G.fmask = fm;
+  G.cap = (uint32_t)(mem[g] - usedtot);
+  gp[g] = G;
+  used_lo[g] = make_uint4(uw[0], uw[1], uw[2], uw[3]);
+  used_hi[g] = make_uint4(uw[4], uw[5], uw[6], uw[7]);
+}
+
+__global__ void mps_unpack_kernel(int tg, int S, const MpsGpu* __restrict__ gp, const uint4* __restrict__ used_lo,
+                                  const uint4* __restrict__ used_hi, int32_t* __restrict__ used, int32_t* __restrict__ fr,
+                                  uint32_t* __restrict__ fmask) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= tg) return;
+  const MpsGpu G = gp[g];
+  const uint4 u0 = used_lo[g], u1 = used_hi[g];
+  for (int s = 0; s < S; ++s) {
+    used[(size_t)g * S + s] = (int32_t)mps_byte(u0, u1, s);
+    fr[(size_t)g * S + s] = (int32_t)mps_byte(G.f0, G.f1, s);
+  }
+  if (fmask) fmask[g] = G.fmask;
+}
+
+// MPS batched scorer: one thread per (demand, node); lanes of a warp = consecutive nodes of one demand.
+struct MpsScoreArgs {
+  const int32_t* sizes;
+  int S;
+  const MpsGpu* gp;
+  const int32_t* gpu_off;
+  const uint8_t* valid;
+  int N, tg;
+  int D, d_chunk;
+  const int32_t* dem_off;
+  const int32_t* dem_key;
+  const int32_t* dem_qty;
+  int32_t* first_node;
+  uint8_t* updated;
+  uint8_t* out_free;    // [D][tg][S] or null
+  uint32_t* out_mask;   // [D][tg] or null
+};
+
+template <int TN>
+__global__ void __launch_bounds__(TN) mps_score_kernel(const MpsScoreArgs a) {
+  __shared__ int s_sz[kMaxSizes];
+  const int tid = threadIdx.x;
+  if (tid < kMaxSizes) s_sz[tid] = tid < a.S ? a.sizes[tid] : 1;
+  __syncthreads();
+  const int n = blockIdx.x * TN + tid;
+  const bool live = n < a.N && a.valid[n];
+  const int g0 = n < a.N ? a.gpu_off[n] : 0;
+  const int cnt = n < a.N ? a.gpu_off[n + 1] - g0 : 0;
+  const int lane = tid & 31;
+  const int d_begin = blockIdx.y * a.d_chunk;
+  const int d_end = min(a.D, d_begin + a.d_chunk);
+  for (int d = d_begin; d < d_end; ++d) {
+    const int e0 = __ldg(a.dem_off + d), k = __ldg(a.dem_off + d + 1) - e0;
+    int sid[kMaxKeys], qty[kMaxKeys];
+    for (int j = 0; j < kMaxKeys; ++j) {
+      sid[j] = j < k ? __ldg(a.dem_key + e0 + j) : 0;
+      qty[j] = j < k ? __ldg(a.dem_qty + e0 + j) : 0;
+    }
+    bool any = false;
+    if (n < a.N) {
+      uint8_t* of = a.out_free ? a.out_free + ((size_t)d * a.tg + g0) * a.S : nullptr;
+      uint32_t* om = a.out_mask ? a.out_mask + (size_t)d * a.tg + g0 : nullptr;
+      // an invalid node is never updated; its (untouched) layout is still reported
+      any = mps_walk_node(s_sz, a.S, const_cast<MpsGpu*>(a.gp), g0, cnt, live ? k : 0, sid, qty, false, of, om);
+      if (a.updated) a.updated[(size_t)d * a.N + n] = any ? 1 : 0;
+    }
+    const int mine = any ? n : kNoNode;
+    const int wmin = __reduce_min_sync(0xffffffffu, mine);
+    if (lane == 0 && wmin != kNoNode) atomicMin(a.first_node + d, wmin);
+  }
+}
+
+}  // namespace nsp

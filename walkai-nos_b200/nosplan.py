@@ -1,0 +1,234 @@
+"""ctypes binding of libnosplan.so (include/nosplan.h).  Thin marshalling only: numpy arrays in,
+numpy arrays out.  There is no fallback: if the library or a CUDA device is missing, it raises."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "libnosplan.so")
+
+i32p = C.POINTER(C.c_int32)
+u32p = C.POINTER(C.c_uint32)
+u8p = C.POINTER(C.c_uint8)
+i8p = C.POINTER(C.c_int8)
+i64p = C.POINTER(C.c_int64)
+
+PLAN_GATE = 1
+PLAN_SCHED = 2
+
+EXPORTS = [
+    "nosplan_create", "nosplan_destroy", "nosplan_last_error", "nosplan_version", "nosplan_set_mig_tables",
+    "nosplan_set_mig_snapshot", "nosplan_set_mps_snapshot", "nosplan_score_mig", "nosplan_score_mps", "nosplan_plan",
+    "nosplan_get_mig_state", "nosplan_get_mps_state", "nosplan_init_geometry_mig", "nosplan_score_mig_dev",
+    "nosplan_score_mps_dev", "nosplan_mig_evals_per_demand", "nosplan_mps_evals_per_demand",
+]
+
+
+class NosplanError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"nosplan error {code}: {msg}")
+        self.code = code
+
+
+def library_path() -> str:
+    return _LIB
+
+
+def build_library(force: bool = False) -> str:
+    """nvcc -gencode arch=compute_100a,code=sm_100a … (csrc/Makefile).  Cross-compiles without a GPU."""
+    src_dir = os.path.join(_HERE, "csrc")
+    srcs = [os.path.join(src_dir, f) for f in os.listdir(src_dir)] + [os.path.join(_HERE, "..", "include", "nosplan.h")]
+    stale = not os.path.exists(_LIB) or any(os.path.getmtime(s) > os.path.getmtime(_LIB) for s in srcs)
+    if force or stale:
+        subprocess.check_call(["make", "-C", src_dir] + (["-B"] if force else []), stdout=subprocess.DEVNULL,
+                              stderr=subprocess.DEVNULL)
+    return _LIB
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB):
+            raise FileNotFoundError(f"{_LIB} is missing: build it with __graft_entry__.build() (no CPU fallback exists)")
+        L = C.CDLL(_LIB)
+        L.nosplan_last_error.restype = C.c_char_p
+        L.nosplan_version.restype = C.c_char_p
+        L.nosplan_mig_evals_per_demand.restype = C.c_int64
+        L.nosplan_mps_evals_per_demand.restype = C.c_int64
+        L.nosplan_mig_evals_per_demand.argtypes = [C.c_void_p]
+        L.nosplan_mps_evals_per_demand.argtypes = [C.c_void_p]
+        L.nosplan_last_error.argtypes = [C.c_void_p]
+        L.nosplan_destroy.argtypes = [C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def _p(a, t):
+    return None if a is None else a.ctypes.data_as(t)
+
+
+def dense_to_csr(req: np.ndarray, mask: Optional[np.ndarray] = None):
+    """[D][K] dense request rows (+ optional key-presence masks) -> CSR (off, key, qty); keys ascending."""
+    req = np.asarray(req, np.int32)
+    D, K = req.shape if req.ndim == 2 else (0, 0)
+    off = [0]
+    key: List[int] = []
+    qty: List[int] = []
+    for d in range(D):
+        for k in range(K):
+            present = ((int(mask[d]) >> k) & 1) if mask is not None else (req[d, k] != 0)
+            if present:
+                key.append(k)
+                qty.append(int(req[d, k]))
+        off.append(len(key))
+    return (np.asarray(off, np.int32), np.asarray(key if key else [0], np.int32)[:max(len(key), 1)],
+            np.asarray(qty if qty else [0], np.int32)[:max(len(qty), 1)])
+
+
+class Planner:
+    """One libnosplan handle bound to a CUDA device."""
+
+    def __init__(self, device: int = 0):
+        self.L = lib()
+        h = C.c_void_p()
+        rc = self.L.nosplan_create(int(device), C.byref(h))
+        if rc != 0:
+            raise NosplanError(rc, "nosplan_create failed (no CUDA device? there is no CPU fallback)")
+        self.h = h
+        self.P = 0
+        self.S = 0
+        self.mig = None
+        self.mps = None
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.nosplan_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc: int):
+        if rc != 0:
+            raise NosplanError(rc, self.L.nosplan_last_error(self.h).decode())
+
+    # ---- tables / snapshots ----------------------------------------------------------------------
+    def set_mig_tables(self, profile_names: Sequence[str], geom_off: np.ndarray, geom_counts: np.ndarray):
+        names = (C.c_char_p * len(profile_names))(*[n.encode() for n in profile_names])
+        geom_off = np.ascontiguousarray(geom_off, np.int32)
+        geom_counts = np.ascontiguousarray(geom_counts, np.int32)
+        self._ck(self.L.nosplan_set_mig_tables(self.h, len(profile_names), names, len(geom_off) - 1, _p(geom_off, i32p),
+                                               _p(geom_counts, i32p)))
+        self.P = len(profile_names)
+
+    def set_mig_snapshot(self, snap: Dict[str, np.ndarray]):
+        s = {k: (np.ascontiguousarray(v) if isinstance(v, np.ndarray) else v) for k, v in snap.items()}
+        self._ck(self.L.nosplan_set_mig_snapshot(self.h, int(s["n_nodes"]), _p(s["gpu_off"].astype(np.int32), i32p),
+                                                 _p(s["valid"].astype(np.uint8), u8p), _p(s["model"].astype(np.int32), i32p),
+                                                 _p(s["used"].astype(np.int32), i32p), _p(s["free"].astype(np.int32), i32p)))
+        self.mig = dict(n_nodes=int(s["n_nodes"]), tg=int(s["gpu_off"][int(s["n_nodes"])]),
+                        gs=int(np.max(np.diff(s["gpu_off"]))) if int(s["n_nodes"]) else 0)
+        self.mig["gs"] = max(self.mig["gs"], 1)
+
+    def set_mps_snapshot(self, sizes_gb: Sequence[int], snap: Dict[str, np.ndarray], with_mask: bool = True):
+        s = {k: (np.ascontiguousarray(v) if isinstance(v, np.ndarray) else v) for k, v in snap.items()}
+        sizes = np.ascontiguousarray(sizes_gb, np.int32)
+        fm = s["free_mask"].astype(np.uint32) if (with_mask and "free_mask" in s) else None
+        self._ck(self.L.nosplan_set_mps_snapshot(self.h, len(sizes), _p(sizes, i32p), int(s["n_nodes"]),
+                                                 _p(s["gpu_off"].astype(np.int32), i32p), _p(s["valid"].astype(np.uint8), u8p),
+                                                 _p(s["mem_gb"].astype(np.int32), i32p), _p(s["used"].astype(np.int32), i32p),
+                                                 _p(s["free"].astype(np.int32), i32p), _p(fm, u32p)))
+        self.S = len(sizes)
+        self.mps = dict(n_nodes=int(s["n_nodes"]), tg=int(s["gpu_off"][int(s["n_nodes"])]))
+
+    # ---- scorers -----------------------------------------------------------------------------------
+    def score_mig(self, off, key, qty, want_updated=True, want_choice=True, want_first_choice=True):
+        D = len(off) - 1
+        N, tg, gs = self.mig["n_nodes"], self.mig["tg"], self.mig["gs"]
+        first = np.full(D, -2, np.int32)
+        fch = np.full((D, gs), -2, np.int8) if want_first_choice else None
+        upd = np.zeros((D, N), np.uint8) if want_updated else None
+        ch = np.full((D, tg), -2, np.int8) if want_choice else None
+        ne = C.c_int64(0)
+        off, key, qty = (np.ascontiguousarray(x, np.int32) for x in (off, key, qty))
+        self._ck(self.L.nosplan_score_mig(self.h, D, _p(off, i32p), _p(key, i32p), _p(qty, i32p), _p(first, i32p),
+                                          _p(fch, i8p), _p(upd, u8p), _p(ch, i8p), C.byref(ne)))
+        return dict(first_node=first, first_choice=fch, updated=upd, choice=ch, n_evals=ne.value)
+
+    def score_mps(self, off, key, qty, want_updated=True, want_free=True):
+        D = len(off) - 1
+        N, tg = self.mps["n_nodes"], self.mps["tg"]
+        first = np.full(D, -2, np.int32)
+        upd = np.zeros((D, N), np.uint8) if want_updated else None
+        of = np.zeros((D, tg, self.S), np.uint8) if want_free else None
+        om = np.zeros((D, tg), np.uint32) if want_free else None
+        ne = C.c_int64(0)
+        off, key, qty = (np.ascontiguousarray(x, np.int32) for x in (off, key, qty))
+        self._ck(self.L.nosplan_score_mps(self.h, D, _p(off, i32p), _p(key, i32p), _p(qty, i32p), _p(first, i32p),
+                                          _p(upd, u8p), _p(of, u8p), _p(om, u32p), C.byref(ne)))
+        return dict(first_node=first, updated=upd, out_free=of, out_free_mask=om, n_evals=ne.value)
+
+    # ---- planner -------------------------------------------------------------------------------------
+    def plan(self, kind, off, key, qty, gate=True, sched=True):
+        M = len(kind)
+        kind = np.ascontiguousarray(kind, np.uint8)
+        off, key, qty = (np.ascontiguousarray(x, np.int32) for x in (off, key, qty))
+        gate_hit = np.zeros(M, np.uint8)
+        rep = np.full(M, -2, np.int32)
+        node = np.full(M, -2, np.int32)
+        gpu = np.full(M, -2, np.int32)
+        flags = (PLAN_GATE if gate else 0) | (PLAN_SCHED if sched else 0)
+        self._ck(self.L.nosplan_plan(self.h, M, _p(kind, u8p), _p(off, i32p), _p(key, i32p), _p(qty, i32p), flags,
+                                     _p(gate_hit, u8p), _p(rep, i32p), _p(node, i32p), _p(gpu, i32p)))
+        return dict(gate_hit=gate_hit, repart_node=rep, sched_node=node, sched_gpu=gpu)
+
+    def get_mig_state(self):
+        tg = self.mig["tg"]
+        used = np.zeros((tg, self.P), np.int32)
+        free = np.zeros((tg, self.P), np.int32)
+        self._ck(self.L.nosplan_get_mig_state(self.h, _p(used, i32p), _p(free, i32p)))
+        return used, free
+
+    def get_mps_state(self):
+        tg = self.mps["tg"]
+        used = np.zeros((tg, self.S), np.int32)
+        free = np.zeros((tg, self.S), np.int32)
+        fm = np.zeros(tg, np.uint32)
+        self._ck(self.L.nosplan_get_mps_state(self.h, _p(used, i32p), _p(free, i32p), _p(fm, u32p)))
+        return used, free, fm
+
+    def init_geometry_mig(self):
+        tg = self.mig["tg"]
+        err = np.zeros(tg, np.uint8)
+        free = np.zeros((tg, self.P), np.int32)
+        self._ck(self.L.nosplan_init_geometry_mig(self.h, _p(err, u8p), _p(free, i32p)))
+        return err, free
+
+    # ---- device-resident (pointers are ints: torch tensor .data_ptr()) -------------------------------
+    def score_mig_dev(self, D, off_ptr, key_ptr, qty_ptr, first_ptr, updated_ptr=0, choice_ptr=0, stream=0):
+        self._ck(self.L.nosplan_score_mig_dev(self.h, int(D), C.c_void_p(off_ptr), C.c_void_p(key_ptr), C.c_void_p(qty_ptr),
+                                              C.c_void_p(first_ptr), C.c_void_p(updated_ptr or None),
+                                              C.c_void_p(choice_ptr or None), C.c_void_p(stream or None)))
+
+    def score_mps_dev(self, D, off_ptr, key_ptr, qty_ptr, first_ptr, updated_ptr=0, free_ptr=0, mask_ptr=0, stream=0):
+        self._ck(self.L.nosplan_score_mps_dev(self.h, int(D), C.c_void_p(off_ptr), C.c_void_p(key_ptr), C.c_void_p(qty_ptr),
+                                              C.c_void_p(first_ptr), C.c_void_p(updated_ptr or None),
+                                              C.c_void_p(free_ptr or None), C.c_void_p(mask_ptr or None),
+                                              C.c_void_p(stream or None)))
+
+    def mig_evals_per_demand(self) -> int:
+        return int(self.L.nosplan_mig_evals_per_demand(self.h))
+
+    def mps_evals_per_demand(self) -> int:
+        return int(self.L.nosplan_mps_evals_per_demand(self.h))
