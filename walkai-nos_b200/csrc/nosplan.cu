@@ -121,7 +121,7 @@ bool mig_name_valid(const std::string& s) {
 
 int upload(nosplan_t* h, DevBuf& b, const void* src, size_t bytes, cudaStream_t st) {
   CU(b.reserve(bytes));
-  if (bytes) CU(cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, st));
+  if (bytes && src) CU(cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, st));
   return NOSPLAN_OK;
 }
 
@@ -724,8 +724,12 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
     a.flags = flags;
     if ((rc = upload(h, b[0], s.pod_sig.data(), sizeof(int32_t) * M, st))) return rc;
     if ((rc = upload(h, b[1], s.off.data(), sizeof(int32_t) * (D + 1), st))) return rc;
-    if ((rc = upload(h, b[2], s.key.data(), sizeof(int32_t) * std::max<size_t>(s.key.size(), 1), st))) return rc;
-    if ((rc = upload(h, b[3], s.qty.data(), sizeof(int32_t) * std::max<size_t>(s.qty.size(), 1), st))) return rc;
+    if (s.key.empty()) {  // only empty request vectors: keep the device arrays non-null
+      s.key.push_back(0);
+      s.qty.push_back(0);
+    }
+    if ((rc = upload(h, b[2], s.key.data(), sizeof(int32_t) * s.key.size(), st))) return rc;
+    if ((rc = upload(h, b[3], s.qty.data(), sizeof(int32_t) * s.qty.size(), st))) return rc;
     a.pod_sig = b[0].as<int32_t>();
     a.dem_off = b[1].as<int32_t>();
     a.dem_key = b[2].as<int32_t>();

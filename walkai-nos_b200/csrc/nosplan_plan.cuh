@@ -51,6 +51,19 @@ struct PlanArgs {
   int32_t* sched_gpu;
 };
 
+// Out-of-line copies of the node walks for the planner kernel.  Inlining the MPS walk into the
+// sequencer let the compiler overlay the walk's scratch arrays with the caller's demand arrays
+// (observed on nvcc 12.9: the caller's key[] read back as 0 after the call); a real call gives the
+// walk its own frame.
+__device__ __noinline__ bool plan_mps_walk(const int* sz, int S, MpsGpu* gp, int g0, int cnt, int k, const int* sid,
+                                           const int* qty, bool commit) {
+  return mps_walk_node<true>(sz, S, gp, g0, cnt, k, sid, qty, commit, nullptr, nullptr);
+}
+__device__ __noinline__ bool plan_mig_walk(const MigTables* T, const uint4* used, uint4* fr, const uint8_t* model, int g0,
+                                           int cnt, int k, const int* pid, const int* qty, bool commit) {
+  return mig_walk_node<true>(T, used, fr, model, g0, cnt, k, pid, qty, commit, nullptr);
+}
+
 __device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 
 template <bool MPS>
@@ -154,8 +167,8 @@ __global__ void __launch_bounds__(kPlanThreads, 1) plan_kernel(const PlanArgs a)
       if (!a.valid[n]) continue;
       const int g0 = a.gpu_off[n], cnt = a.gpu_off[n + 1] - g0;
       bool u;
-      if constexpr (MPS) u = mps_walk_node<true>(sh_sz, a.n_keys, a.p_gpu, g0, cnt, k, key, qty, false, nullptr, nullptr);
-      else u = mig_walk_node<true>(a.T, a.m_used, a.m_free, a.m_model, g0, cnt, k, key, qty, false, nullptr);
+      if constexpr (MPS) u = plan_mps_walk(sh_sz, a.n_keys, a.p_gpu, g0, cnt, k, key, qty, false);
+      else u = plan_mig_walk(a.T, a.m_used, a.m_free, a.m_model, g0, cnt, k, key, qty, false);
       if (u) {
         atomicMin(&sh_best, n);
         break;
@@ -217,8 +230,8 @@ __global__ void __launch_bounds__(kPlanThreads, 1) plan_kernel(const PlanArgs a)
             for (int s = 0; s < cnt; ++s) before += (int)plan_free_of<MPS>(a, g0 + s, lane);
           __syncwarp();
           if (lane == 0) {
-            if constexpr (MPS) mps_walk_node<true>(sh_sz, a.n_keys, a.p_gpu, g0, cnt, k, key, qty, true, nullptr, nullptr);
-            else mig_walk_node<true>(a.T, a.m_used, a.m_free, a.m_model, g0, cnt, k, key, qty, true, nullptr);
+            if constexpr (MPS) plan_mps_walk(sh_sz, a.n_keys, a.p_gpu, g0, cnt, k, key, qty, true);
+            else plan_mig_walk(a.T, a.m_used, a.m_free, a.m_model, g0, cnt, k, key, qty, true);
             __threadfence_block();
           }
           __syncwarp();
