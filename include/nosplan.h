@@ -161,6 +161,26 @@ int nosplan_score_mps_dev(nosplan_t* h, int n_demands, const int32_t* dem_off, c
                           const int32_t* dem_qty, int32_t* first_node, uint8_t* updated, uint8_t* out_free,
                           uint32_t* out_free_mask, void* stream);
 
+/* Allocation-free MIG scorer.  It has no counterpart in the reference.
+ * For callers that may not allocate device memory when they need a score (a sidecar working inside
+ * a fixed buffer budget handed to it by another process's CUDA context, a control loop that cannot
+ * afford cudaMalloc's implicit device synchronisation): same result as nosplan_score_mig_dev's
+ * first_node, but the snapshot arrives as caller-owned DEVICE arrays (same row layout as
+ * nosplan_set_mig_snapshot; every node has gpus_per_node GPUs, node n owns rows
+ * [n*gpus_per_node, (n+1)*gpus_per_node); valid may be NULL = all valid) and the packed copy the
+ * kernel needs lives in a fixed array inside the library (about 1.1 MB per GPU that loads the
+ * library, held until exit).  No cudaMalloc/cudaFree or other allocating call is made.
+ * Needs nosplan_set_mig_tables first (set-up time, may allocate).  Sizes beyond the two limits below
+ * are rejected with NOSPLAN_ERR_RANGE.  The fixed array is shared by every call on a device: calls
+ * whose kernels overlap on the GPU race, so serialise them.  The first call on a device performs a
+ * one-time address lookup; make it before beginning any stream capture.  Values are not
+ * range-checked (they are on the device): rows must satisfy the limits of nosplan_set_mig_snapshot. */
+#define NOSPLAN_STATIC_MAX_NODES 4096
+#define NOSPLAN_STATIC_MAX_GPUS_PER_NODE 8
+int nosplan_score_mig_static(nosplan_t* h, int n_nodes, int gpus_per_node, const uint8_t* valid, const int32_t* model,
+                             const int32_t* used, const int32_t* free_, int n_demands, const int32_t* dem_off,
+                             const int32_t* dem_key, const int32_t* dem_qty, int32_t* first_node, void* stream);
+
 /* Candidate evaluations one scorer pass performs for D demand rows on the current snapshot
  * (sum over valid nodes and their GPUs of the model's geometry count; for MPS, GPUs of valid nodes). */
 int64_t nosplan_mig_evals_per_demand(const nosplan_t* h);

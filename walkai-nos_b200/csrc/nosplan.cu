@@ -860,3 +860,158 @@ int nosplan_init_geometry_mig(nosplan_t* h, uint8_t* err, int32_t* out_free) {
 }
 
 }  // extern "C"
+
+// =================================================================================================================
+// Allocation-free MIG scorer.
+//
+// Some callers of this library are not allowed to allocate device memory at the moment they need a
+// score: a planner sidecar that shares its CUDA context with a latency-critical process and has
+// been handed a fixed set of buffers, or a control loop that must not hit cudaMalloc's implicit
+// device synchronisation.  For them this entry point does the same work as nosplan_score_mig_dev
+// but takes every input and output as a caller-owned device pointer and keeps its one piece of
+// scratch — the byte-packed, slot-major copy of the snapshot that the scorer kernel reads — in a
+// fixed array that lives inside the library image.  It calls no cudaMalloc / cudaFree and no other
+// allocating routine.  It has no counterpart in the reference.
+//
+// Limits (rejected with NOSPLAN_ERR_RANGE beyond them): at most NOSPLAN_STATIC_MAX_NODES nodes, every
+// node with the same number of GPUs, at most NOSPLAN_STATIC_MAX_GPUS_PER_NODE of them.  The array
+// costs about 1.1 MB of device memory on every GPU that loads the library, until the process exits.
+//
+// The array is shared by all calls on a device and keeps the previous call's contents.  Each call
+// rewrites every element the scorer will read before it reads it (nothing in it needs to start at
+// zero; the caller's first_node output is reset by the call itself), so stale data cannot leak into a
+// result — but two calls whose kernels overlap on the GPU (different streams, or different host
+// threads) race on it.  Serialise them.
+//
+// The first call on a device looks up the array's device address (cudaGetSymbolAddress); make that
+// first call before starting any stream capture.
+namespace {
+
+constexpr int kStaticMaxNodes = NOSPLAN_STATIC_MAX_NODES;
+constexpr int kStaticMaxGpus = NOSPLAN_STATIC_MAX_GPUS_PER_NODE;
+
+struct StaticScratch {
+  uint4 s_used[kStaticMaxGpus][kStaticMaxNodes];
+  uint4 s_free[kStaticMaxGpus][kStaticMaxNodes];
+  uint8_t s_model[kStaticMaxGpus][kStaticMaxNodes];
+  uint8_t s_cnt[kStaticMaxNodes];
+  int32_t gpu_off[kStaticMaxNodes + 1];
+};
+
+// In host code this name is only a stand-in for the symbol; the device address is fetched once per
+// device with cudaGetSymbolAddress (static_scratch_for) and that pointer is what kernels receive.
+static __device__ __align__(256) unsigned char g_static_scratch[sizeof(StaticScratch)];
+
+constexpr int kMaxDevices = 64;
+struct StaticSetup {
+  bool ready = false;
+  StaticScratch* ptr = nullptr;
+};
+StaticSetup g_static_setup[kMaxDevices];
+
+// packs int32 rows (device) into the static scratch; same byte layout as mig_pack_kernel's
+// slot-major outputs, uniform GPUs per node
+__global__ void static_pack_kernel(StaticScratch* sc, int N, int P, int G, int npad, const uint8_t* __restrict__ valid,
+                                   const int32_t* __restrict__ model, const int32_t* __restrict__ used,
+                                   const int32_t* __restrict__ fr) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n <= N) sc->gpu_off[n] = n * G;
+  if (n >= npad) return;
+  const bool real = n < N;
+  const bool ok = real && (valid == nullptr || valid[n]);
+  sc->s_cnt[n] = ok ? (uint8_t)G : 0;
+  for (int s = 0; s < G; ++s) {
+    uint32_t uw[4] = {0, 0, 0, 0}, fw[4] = {0, 0, 0, 0};
+    uint8_t m = 0xff;
+    if (ok) {
+      const size_t g = (size_t)n * G + s;
+      for (int p = 0; p < P; ++p) {
+        uw[p >> 2] |= (uint32_t)(used[g * P + p] & 0xff) << ((p & 3) * 8);
+        fw[p >> 2] |= (uint32_t)(fr[g * P + p] & 0xff) << ((p & 3) * 8);
+      }
+      m = (uint8_t)model[g];
+    }
+    sc->s_used[s][n] = make_uint4(uw[0], uw[1], uw[2], uw[3]);
+    sc->s_free[s][n] = make_uint4(fw[0], fw[1], fw[2], fw[3]);
+    sc->s_model[s][n] = m;
+  }
+}
+
+int static_scratch_for(nosplan_t* h, StaticScratch** out) {
+  if (h->device < 0 || h->device >= kMaxDevices) return fail(h, NOSPLAN_ERR_RANGE, "device ordinal %d not supported", h->device);
+  StaticSetup& st = g_static_setup[h->device];
+  if (!st.ready) {
+    // once per device, with that device current (bind() ran): the symbol's address on THIS device
+    void* p = nullptr;
+    CU(cudaGetSymbolAddress(&p, g_static_scratch));
+    st.ptr = reinterpret_cast<StaticScratch*>(p);
+    st.ready = true;
+  }
+  *out = st.ptr;
+  return NOSPLAN_OK;
+}
+
+}  // namespace
+
+extern "C" int nosplan_score_mig_static(nosplan_t* h, int n_nodes, int gpus_per_node, const uint8_t* valid,
+                                        const int32_t* model, const int32_t* used, const int32_t* free_, int n_demands,
+                                        const int32_t* dem_off, const int32_t* dem_key, const int32_t* dem_qty,
+                                        int32_t* first_node, void* stream) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  if (!h->have_tables) return fail(h, NOSPLAN_ERR_ARG, "nosplan_set_mig_tables must be called first");
+  if (n_nodes < 0 || gpus_per_node < 0 || n_demands < 0) return fail(h, NOSPLAN_ERR_ARG, "negative size");
+  if (n_nodes > kStaticMaxNodes)
+    return fail(h, NOSPLAN_ERR_RANGE, "nosplan_score_mig_static: %d nodes exceed the fixed scratch (max %d nodes); use nosplan_score_mig_dev",
+                n_nodes, kStaticMaxNodes);
+  if (gpus_per_node > kStaticMaxGpus)
+    return fail(h, NOSPLAN_ERR_RANGE, "nosplan_score_mig_static: %d GPUs per node exceed the fixed scratch (max %d); use nosplan_score_mig_dev",
+                gpus_per_node, kStaticMaxGpus);
+  if (n_demands > 0 && (!dem_off || !dem_key || !dem_qty || !first_node)) return fail(h, NOSPLAN_ERR_ARG, "null demand/output pointer");
+  if (n_nodes > 0 && gpus_per_node > 0 && (!model || !used || !free_)) return fail(h, NOSPLAN_ERR_ARG, "null snapshot pointer");
+  int rc = bind(h);
+  if (rc) return rc;
+  StaticScratch* sc = nullptr;
+  if ((rc = static_scratch_for(h, &sc))) return rc;
+  if (n_demands == 0) return NOSPLAN_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int D = n_demands;
+  const int gs = std::max(gpus_per_node, 1);
+  const int npad = std::max(32, (n_nodes + 31) / 32 * 32);
+  fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(first_node, D, kNoNode);
+  if (n_nodes > 0) {
+    const int threads = std::max(npad, n_nodes + 1);
+    static_pack_kernel<<<(threads + 127) / 128, 128, 0, st>>>(sc, n_nodes, h->P, gpus_per_node, npad, valid, model, used, free_);
+    MigScoreArgs a;
+    a.T = h->d_tables.as<MigTables>();
+    a.s_used = &sc->s_used[0][0];
+    a.s_free = &sc->s_free[0][0];
+    a.s_model = &sc->s_model[0][0];
+    a.s_cnt = sc->s_cnt;
+    a.gpu_off = sc->gpu_off;
+    a.N = n_nodes;
+    a.npad = kStaticMaxNodes;  // row stride of the fixed arrays
+    a.gs = gs;
+    a.cmax = h->cmax;
+    a.tg = n_nodes * gpus_per_node;
+    a.D = D;
+    a.dem_off = dem_off;
+    a.dem_key = dem_key;
+    a.dem_qty = dem_qty;
+    a.first_node = first_node;
+    a.updated = nullptr;
+    a.choice = nullptr;
+    const int tiles = (n_nodes + kScoreTN - 1) / kScoreTN;
+    int gy;
+    pick_chunks(h->sm_count, tiles, D, 16, &a.d_chunk, &gy);
+    const size_t cand = ((size_t)h->h_tables.n_geoms * 16 + 15) & ~(size_t)15;
+    const size_t smem = cand + (size_t)gs * h->cmax * kScoreTN * 4 + (size_t)gs * 4 * kScoreTN * 4 * 2 +
+                        (size_t)gs * kScoreTN * 2 + (size_t)gs * kScoreTN + 16;
+    if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MIG scorer tile needs %zu bytes of shared memory", smem);
+    CU(cudaFuncSetAttribute(mig_score_kernel<kScoreTN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));  // a limit, not an allocation
+    mig_score_kernel<kScoreTN><<<dim3(tiles, gy), kScoreTN, smem, st>>>(a);
+  }
+  nonode_to_minus1_kernel<<<(D + 255) / 256, 256, 0, st>>>(first_node, D);
+  CU(cudaGetLastError());
+  return NOSPLAN_OK;
+}

@@ -25,7 +25,7 @@ EXPORTS = [
     "nosplan_create", "nosplan_destroy", "nosplan_last_error", "nosplan_version", "nosplan_set_mig_tables",
     "nosplan_set_mig_snapshot", "nosplan_set_mps_snapshot", "nosplan_score_mig", "nosplan_score_mps", "nosplan_plan",
     "nosplan_get_mig_state", "nosplan_get_mps_state", "nosplan_init_geometry_mig", "nosplan_score_mig_dev",
-    "nosplan_score_mps_dev", "nosplan_mig_evals_per_demand", "nosplan_mps_evals_per_demand",
+    "nosplan_score_mps_dev", "nosplan_mig_evals_per_demand", "nosplan_mps_evals_per_demand", "nosplan_score_mig_static",
 ]
 
 
@@ -226,6 +226,15 @@ class Planner:
                                               C.c_void_p(first_ptr), C.c_void_p(updated_ptr or None),
                                               C.c_void_p(free_ptr or None), C.c_void_p(mask_ptr or None),
                                               C.c_void_p(stream or None)))
+
+    def score_mig_static(self, n_nodes, gpus_per_node, valid_ptr, model_ptr, used_ptr, free_ptr, D, off_ptr, key_ptr, qty_ptr,
+                         first_ptr, stream=0):
+        """Allocation-free scorer: every pointer is a device address owned by the caller."""
+        self._ck(self.L.nosplan_score_mig_static(self.h, int(n_nodes), int(gpus_per_node), C.c_void_p(valid_ptr or None),
+                                                 C.c_void_p(model_ptr or None), C.c_void_p(used_ptr or None),
+                                                 C.c_void_p(free_ptr or None), int(D), C.c_void_p(off_ptr or None),
+                                                 C.c_void_p(key_ptr or None), C.c_void_p(qty_ptr or None),
+                                                 C.c_void_p(first_ptr or None), C.c_void_p(stream or None)))
 
     def mig_evals_per_demand(self) -> int:
         return int(self.L.nosplan_mig_evals_per_demand(self.h))
