@@ -147,6 +147,7 @@ def main():
     ap.add_argument("--nodes", type=int, default=0)
     ap.add_argument("--pods", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-plan", action="store_true", help="skip the planner-latency section (profiling runs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
 
@@ -281,13 +282,13 @@ def main():
     # ---- planner latency: Plan(snapshot, pods) through the C ABI (rank 0's shard; p50 over steps) -----------
     pods = cfg["pods"]
     lat = []
-    for i in range(args.warmup + args.steps):
+    for i in range(0 if args.no_plan else args.warmup + args.steps):
         t0 = time.perf_counter()
         planner.plan(pods["kind"], pods["off"], pods["key"], pods["qty"], gate=True, sched=True)
         if i >= args.warmup:
             lat.append((time.perf_counter() - t0) * 1e3)
     lat_off = []
-    for i in range(2 + min(args.steps, 5)):
+    for i in range(0 if args.no_plan else 2 + min(args.steps, 5)):
         t0 = time.perf_counter()
         planner.plan(pods["kind"], pods["off"], pods["key"], pods["qty"], gate=False, sched=True)
         if i >= 2:
@@ -307,8 +308,9 @@ def main():
             "e2e": {"value": e2e_val, "unit": "evals/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "ms_per_step": float(e2e_t.item()) * 1e3},
             "gpu_launches": int(args.steps * ((3 if Dm else 0) + (3 if Dp else 0))),
-            "planner_latency_ms_p50": float(np.median(lat)), "planner_latency_ms_p95": float(np.percentile(lat, 95)),
-            "planner_latency_gate_off_ms_p50": float(np.median(lat_off)),
+            "planner_latency_ms_p50": float(np.median(lat)) if lat else None,
+            "planner_latency_ms_p95": float(np.percentile(lat, 95)) if lat else None,
+            "planner_latency_gate_off_ms_p50": float(np.median(lat_off)) if lat_off else None,
             "evals_per_step": {"mig": ev_m, "mps": ev_p},
             "roofline": {"bound": "hbm", "kernel": "mig_score_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
                          "frac": ach / peak, "peak_source": peak_src, "traffic": None,

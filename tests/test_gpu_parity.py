@@ -57,6 +57,10 @@ def _check_score_mps(pkg, planner, o, cfg, off, key, qty, threads=8):
     assert np.array_equal(r["first_node"], ef)
     assert np.array_equal(r["out_free_mask"], emask)
     assert np.array_equal(r["out_free"].astype(np.int32), efree)
+    # without the full layout table the kernel takes its closed-form single-size path: same answers
+    r2 = planner.score_mps(off, key, qty, want_updated=True, want_free=False)
+    assert np.array_equal(r2["updated"], eu)
+    assert np.array_equal(r2["first_node"], ef)
 
 
 def _check_plan(pkg, planner, o, cfg, pods, gate, sched):

@@ -61,7 +61,7 @@ struct nosplan {
   int mig_n = 0, mig_tg = 0, mig_gs = 0, mig_npad = 0;
   int64_t mig_evals = 0;
   DevBuf d_mig_off, d_mig_valid, d_mig_model, d_mig_used0, d_mig_free0, d_mig_used, d_mig_free;
-  DevBuf d_mig_sused, d_mig_sfree, d_mig_smodel, d_mig_scnt;
+  DevBuf d_mig_sused, d_mig_sfree, d_mig_smodel, d_mig_scnt, d_mig_gnode;
   bool mig_state_dirty = false;  // working copy differs from the snapshot
 
   // MPS snapshot
@@ -69,14 +69,14 @@ struct nosplan {
   int S = 0;
   int mps_n = 0, mps_tg = 0, mps_gs = 0;
   int64_t mps_evals = 0;
-  DevBuf d_mps_sizes, d_mps_off, d_mps_valid, d_mps_gpu0, d_mps_ulo0, d_mps_uhi0, d_mps_gpu, d_mps_ulo, d_mps_uhi;
+  DevBuf d_mps_sizes, d_mps_off, d_mps_valid, d_mps_gpu0, d_mps_ulo0, d_mps_uhi0, d_mps_gpu, d_mps_ulo, d_mps_uhi, d_mps_gnode;
   bool mps_state_dirty = false;
 
   // scratch / staging
   DevBuf d_in[6];    // staging for int32 host inputs
   DevBuf d_dem[3];   // demand CSR
   DevBuf d_out[6];   // outputs
-  DevBuf d_plan[16];
+  DevBuf d_plan[32];
 };
 
 namespace {
@@ -146,8 +146,8 @@ int check_demands(nosplan_t* h, int D, const int32_t* off, const int32_t* key, c
 }
 
 // chunking of the demand axis so the grid is a small multiple of the SM count
-void pick_chunks(int sm_count, int tiles, int D, int min_chunk, int* d_chunk, int* gy) {
-  int want_ctas = sm_count * 4;
+void pick_chunks(int sm_count, int tiles, int D, int min_chunk, int* d_chunk, int* gy, int ctas_per_sm = 4) {
+  int want_ctas = sm_count * ctas_per_sm;
   int y = std::max(1, want_ctas / std::max(1, tiles));
   int chunk = std::max(min_chunk, (D + y - 1) / y);
   chunk = std::min(chunk, std::max(D, 1));
@@ -159,12 +159,7 @@ void pick_chunks(int sm_count, int tiles, int D, int min_chunk, int* d_chunk, in
 constexpr int kScoreTN = 128;
 
 size_t mig_score_smem(const nosplan_t* h, int tn) {
-  size_t cand = ((size_t)h->h_tables.n_geoms * 16 + 15) & ~(size_t)15;
-  size_t key0 = (size_t)h->mig_gs * h->cmax * tn * 4;
-  size_t words = (size_t)h->mig_gs * 4 * tn * 4 * 2;
-  size_t coff = (size_t)h->mig_gs * tn * 2;
-  size_t ccnt = (size_t)h->mig_gs * tn;
-  return cand + key0 + words + coff + ccnt + 16;
+  return mig_score_smem_bytes(h->h_tables.n_models, h->mig_gs, h->cmax, tn);
 }
 
 int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d_key, const int32_t* d_qty,
@@ -225,10 +220,14 @@ int launch_mps_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
     a.updated = d_updated;
     a.out_free = d_free;
     a.out_mask = d_mask;
+    a.gs = h->mps_gs;
     int tiles = (h->mps_n + kScoreTN - 1) / kScoreTN;
     int gy;
-    pick_chunks(h->sm_count, tiles, D, 4, &a.d_chunk, &gy);
-    mps_score_kernel<kScoreTN><<<dim3(tiles, gy), kScoreTN, 0, st>>>(a);
+    pick_chunks(h->sm_count, tiles, D, 16, &a.d_chunk, &gy, 8);
+    const size_t smem = mps_score_smem_bytes(h->mps_gs, h->S, kScoreTN);
+    if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MPS scorer tile needs %zu bytes of shared memory", smem);
+    CU(cudaFuncSetAttribute(mps_score_kernel<kScoreTN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    mps_score_kernel<kScoreTN><<<dim3(tiles, gy), kScoreTN, smem, st>>>(a);
   }
   nonode_to_minus1_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D);
   CU(cudaGetLastError());
@@ -266,7 +265,7 @@ void nosplan_destroy(nosplan_t* h) {
   DevBuf* all[] = {&h->d_tables, &h->d_mig_off, &h->d_mig_valid, &h->d_mig_model, &h->d_mig_used0, &h->d_mig_free0,
                    &h->d_mig_used, &h->d_mig_free, &h->d_mig_sused, &h->d_mig_sfree, &h->d_mig_smodel, &h->d_mig_scnt,
                    &h->d_mps_sizes, &h->d_mps_off, &h->d_mps_valid, &h->d_mps_gpu0, &h->d_mps_ulo0, &h->d_mps_uhi0,
-                   &h->d_mps_gpu, &h->d_mps_ulo, &h->d_mps_uhi};
+                   &h->d_mps_gpu, &h->d_mps_ulo, &h->d_mps_uhi, &h->d_mig_gnode, &h->d_mps_gnode};
   for (DevBuf* b : all) b->release();
   for (auto& b : h->d_in) b.release();
   for (auto& b : h->d_dem) b.release();
@@ -408,6 +407,10 @@ int nosplan_set_mig_snapshot(nosplan_t* h, int n_nodes, const int32_t* gpu_off, 
   std::vector<int32_t> mdl(std::max(tg, 1), 0);
   for (int n = 0; n < n_nodes; ++n)
     for (int g = gpu_off[n]; g < gpu_off[n + 1]; ++g) mdl[g] = v[n] ? model[g] : 0;
+  std::vector<int32_t> gnode(std::max(tg, 1), -1);
+  for (int n = 0; n < n_nodes; ++n)
+    for (int g = gpu_off[n]; g < gpu_off[n + 1]; ++g) gnode[g] = v[n] ? n : -1;
+  if ((rc = upload(h, h->d_mig_gnode, gnode.data(), sizeof(int32_t) * gnode.size(), h->stream))) return rc;
   if ((rc = upload(h, h->d_mig_off, gpu_off, sizeof(int32_t) * (n_nodes + 1), h->stream))) return rc;
   if ((rc = upload(h, h->d_mig_valid, v.data(), std::max(n_nodes, 1), h->stream))) return rc;
   if ((rc = upload(h, h->d_in[0], mdl.data(), sizeof(int32_t) * std::max(tg, 1), h->stream))) return rc;
@@ -503,6 +506,10 @@ int nosplan_set_mps_snapshot(nosplan_t* h, int n_sizes, const int32_t* sizes_gb,
     }
   int rc = bind(h);
   if (rc) return rc;
+  std::vector<int32_t> gnode(std::max(tg, 1), -1);
+  for (int n = 0; n < n_nodes; ++n)
+    for (int g = gpu_off[n]; g < gpu_off[n + 1]; ++g) gnode[g] = v[n] ? n : -1;
+  if ((rc = upload(h, h->d_mps_gnode, gnode.data(), sizeof(int32_t) * gnode.size(), h->stream))) return rc;
   if ((rc = upload(h, h->d_mps_sizes, sizes_gb, sizeof(int32_t) * S, h->stream))) return rc;
   if ((rc = upload(h, h->d_mps_off, gpu_off, sizeof(int32_t) * (n_nodes + 1), h->stream))) return rc;
   if ((rc = upload(h, h->d_mps_valid, v.data(), std::max(n_nodes, 1), h->stream))) return rc;
@@ -658,8 +665,12 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
   // split by kind (order kept) and deduplicate request vectors: pods with the same vector share a row
   struct Side {
     std::vector<int32_t> pod_idx, pod_sig, off{0}, key, qty;
-    std::map<std::vector<int32_t>, int> sigs;
+    std::map<std::vector<int32_t>, int> sigs;           // general case
+    std::vector<int> single;                             // [key * (kChainQ+1) + qty] -> row, single-key fast lookup
+    int n_sigs = 0;
+    bool chains_ok = true;                               // every pod: one key, 1 <= qty <= kChainQ
   } side[2];
+  for (int kd = 0; kd < 2; ++kd) side[kd].single.assign((size_t)(kd ? NOSPLAN_MAX_MPS_SIZES : NOSPLAN_MAX_MIG_PROFILES) * (kChainQ + 1), -1);
   for (int i = 0; i < n_pods; ++i) {
     const int kd = kind[i] ? 1 : 0;
     const int n_keys = kd ? h->S : h->P;
@@ -673,27 +684,36 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
     }
     const int e0 = dem_off[i], e1 = dem_off[i + 1];
     if (e1 < e0 || e1 - e0 > NOSPLAN_MAX_DEMAND_KEYS) return fail(h, NOSPLAN_ERR_RANGE, "pod %d: bad demand row", i);
-    std::vector<int32_t> sig;
     for (int e = e0; e < e1; ++e) {
       if (dem_key[e] < 0 || dem_key[e] >= n_keys) return fail(h, NOSPLAN_ERR_RANGE, "pod %d: key %d out of range", i, dem_key[e]);
       if (e > e0 && dem_key[e] <= dem_key[e - 1]) return fail(h, NOSPLAN_ERR_ARG, "pod %d: keys must be strictly ascending", i);
       if (dem_qty[e] < 0 || dem_qty[e] > NOSPLAN_MAX_DEMAND_QTY) return fail(h, NOSPLAN_ERR_RANGE, "pod %d: quantity out of range", i);
-      sig.push_back(dem_key[e]);
-      sig.push_back(dem_qty[e]);
     }
     Side& s = side[kd];
-    auto it = s.sigs.find(sig);
-    int id;
-    if (it == s.sigs.end()) {
-      id = (int)s.sigs.size();
-      s.sigs.emplace(sig, id);
-      for (size_t j = 0; j < sig.size(); j += 2) {
-        s.key.push_back(sig[j]);
-        s.qty.push_back(sig[j + 1]);
+    int id = -1;
+    int* slot = nullptr;
+    if (e1 - e0 == 1 && dem_qty[e0] >= 1 && dem_qty[e0] <= kChainQ) {
+      slot = &s.single[(size_t)dem_key[e0] * (kChainQ + 1) + dem_qty[e0]];
+      id = *slot;
+    } else {
+      s.chains_ok = false;
+      std::vector<int32_t> sig;
+      for (int e = e0; e < e1; ++e) {
+        sig.push_back(dem_key[e]);
+        sig.push_back(dem_qty[e]);
+      }
+      auto it = s.sigs.find(sig);
+      if (it != s.sigs.end()) id = it->second;
+      else s.sigs.emplace(sig, s.n_sigs);
+    }
+    if (id < 0) {
+      id = s.n_sigs++;
+      if (slot) *slot = id;
+      for (int e = e0; e < e1; ++e) {
+        s.key.push_back(dem_key[e]);
+        s.qty.push_back(dem_qty[e]);
       }
       s.off.push_back((int32_t)s.key.size());
-    } else {
-      id = it->second;
     }
     s.pod_idx.push_back(i);
     s.pod_sig.push_back(id);
@@ -715,8 +735,8 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
     const int M = (int)s.pod_idx.size();
     if (M == 0) continue;
     cudaStream_t st = kd ? h->stream2 : h->stream;
-    DevBuf* b = h->d_plan + kd * 8;
-    const int D = (int)s.sigs.size();
+    DevBuf* b = h->d_plan + kd * 16;
+    const int D = s.n_sigs;
     PlanArgs a;
     std::memset(&a, 0, sizeof(a));
     a.M = M;
@@ -768,6 +788,63 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
     a.sched_node = a.repart_node + M;
     a.sched_gpu = a.sched_node + M;
     a.gate_hit = reinterpret_cast<uint8_t*>(a.sched_gpu + M);
+    const bool want_chains = s.chains_ok && (flags == (NOSPLAN_PLAN_GATE | NOSPLAN_PLAN_SCHED)) && a.tg > 0;
+    if (want_chains) {
+      // pods grouped by requested key, planner order kept inside a group
+      std::vector<int32_t> ckey, coff{0}, cpod(M), cq(M);
+      std::vector<int> cnt(a.n_keys, 0), chain_of(a.n_keys, -1);
+      for (int j = 0; j < M; ++j) cnt[s.key[s.off[s.pod_sig[j]]]]++;
+      for (int k = 0; k < a.n_keys; ++k)
+        if (cnt[k]) {
+          chain_of[k] = (int)ckey.size();
+          ckey.push_back(k);
+          coff.push_back(coff.back() + cnt[k]);
+        }
+      std::vector<int32_t> fill(coff.begin(), coff.end() - 1);
+      for (int j = 0; j < M; ++j) {
+        const int e = s.off[s.pod_sig[j]];
+        const int c = chain_of[s.key[e]];
+        cpod[fill[c]] = j;
+        cq[fill[c]] = s.qty[e];
+        fill[c]++;
+      }
+      ChainArgs ca;
+      std::memset(&ca, 0, sizeof(ca));
+      ca.n_chains = (int)ckey.size();
+      if ((rc = upload(h, b[8], ckey.data(), sizeof(int32_t) * ckey.size(), st))) return rc;
+      if ((rc = upload(h, b[9], coff.data(), sizeof(int32_t) * coff.size(), st))) return rc;
+      if ((rc = upload(h, b[10], cpod.data(), sizeof(int32_t) * M, st))) return rc;
+      if ((rc = upload(h, b[11], cq.data(), sizeof(int32_t) * M, st))) return rc;
+      CU(b[12].reserve(sizeof(int32_t) * (kMaxSizes + 1)));
+      CU(cudaMemsetAsync(b[12].p, 0, sizeof(int32_t) * (kMaxSizes + 1), st));
+      ca.chain_key = b[8].as<int32_t>();
+      ca.chain_off = b[9].as<int32_t>();
+      ca.chain_pod = b[10].as<int32_t>();
+      ca.chain_q = b[11].as<int32_t>();
+      ca.present = b[12].as<int32_t>();
+      ca.eligible = ca.present + kMaxSizes;
+      ca.N = a.N;
+      ca.tg = a.tg;
+      ca.n_keys = a.n_keys;
+      ca.gpu_off = a.gpu_off;
+      ca.gpu_node = kd ? h->d_mps_gnode.as<int32_t>() : h->d_mig_gnode.as<int32_t>();
+      ca.m_used = a.m_used;
+      ca.m_free = a.m_free;
+      ca.sizes = a.sizes;
+      ca.p_gpu = a.p_gpu;
+      ca.p_used_lo = a.p_used_lo;
+      ca.p_used_hi = a.p_used_hi;
+      ca.gate_hit = a.gate_hit;
+      ca.repart_node = a.repart_node;
+      ca.sched_node = a.sched_node;
+      ca.sched_gpu = a.sched_gpu;
+      a.skip_if = ca.eligible;
+      if (kd == 0) plan_presence_kernel<false><<<(a.tg + 255) / 256, 256, 0, st>>>(ca);
+      else plan_presence_kernel<true><<<(a.tg + 255) / 256, 256, 0, st>>>(ca);
+      plan_eligible_kernel<<<1, 32, 0, st>>>(ca);
+      if (kd == 0) plan_chain_kernel<false><<<ca.n_chains, 32, 0, st>>>(ca);
+      else plan_chain_kernel<true><<<ca.n_chains, 32, 0, st>>>(ca);
+    }
     if (kd == 0) plan_kernel<false><<<1, kPlanThreads, 0, st>>>(a);
     else plan_kernel<true><<<1, kPlanThreads, 0, st>>>(a);
     CU(cudaGetLastError());
@@ -1004,9 +1081,7 @@ extern "C" int nosplan_score_mig_static(nosplan_t* h, int n_nodes, int gpus_per_
     const int tiles = (n_nodes + kScoreTN - 1) / kScoreTN;
     int gy;
     pick_chunks(h->sm_count, tiles, D, 16, &a.d_chunk, &gy);
-    const size_t cand = ((size_t)h->h_tables.n_geoms * 16 + 15) & ~(size_t)15;
-    const size_t smem = cand + (size_t)gs * h->cmax * kScoreTN * 4 + (size_t)gs * 4 * kScoreTN * 4 * 2 +
-                        (size_t)gs * kScoreTN * 2 + (size_t)gs * kScoreTN + 16;
+    const size_t smem = mig_score_smem_bytes(h->h_tables.n_models, gs, h->cmax, kScoreTN);
     if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MIG scorer tile needs %zu bytes of shared memory", smem);
     CU(cudaFuncSetAttribute(mig_score_kernel<kScoreTN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));  // a limit, not an allocation
     mig_score_kernel<kScoreTN><<<dim3(tiles, gy), kScoreTN, smem, st>>>(a);

@@ -196,24 +196,44 @@ struct MigScoreArgs {
   int8_t* choice;       // [D][tg] or null
 };
 
+// Shared-memory layout of one tile (TN nodes, gs GPU slots, cw = ceil(cmax/4) words of 4 candidates):
+//   candT [n_models][16][cw] u32   candidate quantities transposed: byte cc of word i = cand[4i+cc][p]
+//   rank4 [gs][cw][TN]       u32   per (node, slot): byte cc of word i = 0 if candidate 4i+cc cannot be
+//                                  applied, else 1 + the position of its demand-independent score
+//                                  key0 among the GPU's candidates (equal key0 -> equal byte)
+//   usedw/freew [gs][4][TN]  u32   the node's packed used / free maps
+//   model [gs][TN]           u8
+__host__ __device__ inline size_t mig_score_smem_bytes(int n_models, int gs, int cmax, int tn) {
+  const size_t cw = (size_t)(cmax + 3) / 4;
+  return (size_t)n_models * 16 * cw * 4 + (size_t)gs * cw * tn * 4 + (size_t)gs * 4 * tn * 4 * 2 + (size_t)gs * tn + 16;
+}
+
 template <int TN>
 __global__ void __launch_bounds__(TN) mig_score_kernel(const MigScoreArgs a) {
   extern __shared__ __align__(16) unsigned char smem[];
-  // layout: cand bytes [n_geoms*16] | key0 [gs][cmax][TN] u32 | usedw [gs][4][TN] | freew [gs][4][TN] | coff [gs][TN] u16 | ccnt [gs][TN] u8
   const MigTables* __restrict__ T = a.T;
-  const int n_geoms = T->n_geoms;
-  uint8_t* s_cand = smem;
-  uint32_t* s_key0 = reinterpret_cast<uint32_t*>(smem + (((size_t)n_geoms * 16 + 15) & ~(size_t)15));
-  uint32_t* s_usedw = s_key0 + (size_t)a.gs * a.cmax * TN;
+  const int cw = (a.cmax + 3) >> 2;
+  const int n_models = T->n_models;
+  uint32_t* s_candT = reinterpret_cast<uint32_t*>(smem);
+  uint32_t* s_rank4 = s_candT + (size_t)n_models * 16 * cw;
+  uint32_t* s_usedw = s_rank4 + (size_t)a.gs * cw * TN;
   uint32_t* s_freew = s_usedw + (size_t)a.gs * 4 * TN;
-  uint16_t* s_coff = reinterpret_cast<uint16_t*>(s_freew + (size_t)a.gs * 4 * TN);
-  uint8_t* s_ccnt = reinterpret_cast<uint8_t*>(s_coff + (size_t)a.gs * TN);
+  uint8_t* s_model = reinterpret_cast<uint8_t*>(s_freew + (size_t)a.gs * 4 * TN);
 
   const int tid = threadIdx.x;
   const int n = blockIdx.x * TN + tid;
-  for (int i = tid; i < n_geoms * 4; i += TN)
-    reinterpret_cast<uint32_t*>(s_cand)[i] = reinterpret_cast<const uint32_t*>(T->cand)[i];
-
+  // transposed candidate table (demand- and node-independent)
+  for (int i = tid; i < n_models * 16 * cw; i += TN) {
+    const int w = i % cw, p = (i / cw) & 15, m = i / (cw * 16);
+    const int c0 = T->geom_off[m], cc = T->geom_off[m + 1] - c0;
+    uint32_t v = 0;
+    for (int b = 0; b < 4; ++b) {
+      const int c = w * 4 + b;
+      if (c < cc) v |= byte_of(T->cand[c0 + c], p) << (8 * b);
+    }
+    s_candT[i] = v;
+  }
+  // per (node, slot): feasibility + demand-independent key of every candidate, reduced to a rank byte
   const int cnt = (n < a.N) ? a.s_cnt[n] : 0;
   const int g0 = (n < a.N) ? a.gpu_off[n] : 0;
   for (int s = 0; s < cnt; ++s) {
@@ -221,18 +241,29 @@ __global__ void __launch_bounds__(TN) mig_score_kernel(const MigScoreArgs a) {
     const uint4 f = a.s_free[(size_t)s * a.npad + n];
     const int m = a.s_model[(size_t)s * a.npad + n];
     const uint4 cur = add4(u, f);
-    const int c0 = T->geom_off[m], c1 = T->geom_off[m + 1];
-    s_coff[s * TN + tid] = (uint16_t)c0;
-    s_ccnt[s * TN + tid] = (uint8_t)(c1 - c0);
+    const int c0 = T->geom_off[m], cc = T->geom_off[m + 1] - c0;
+    s_model[s * TN + tid] = (uint8_t)m;
 #pragma unroll
     for (int w = 0; w < 4; ++w) {
       s_usedw[(s * 4 + w) * TN + tid] = word_of(u, w);
       s_freew[(s * 4 + w) * TN + tid] = word_of(f, w);
     }
-    for (int c = c0; c < c1; ++c) {
-      const uint4 cd = T->cand[c];
-      const uint32_t k0 = all_ge4(cd, u) ? key0_of(T->total[c], sad16(cd, cur), T->rank[c]) : 0u;
-      s_key0[((size_t)s * a.cmax + (c - c0)) * TN + tid] = k0;
+    uint32_t k0[kMaxGeoms];
+    for (int c = 0; c < cc; ++c) {
+      const uint4 cd = T->cand[c0 + c];
+      k0[c] = all_ge4(cd, u) ? key0_of(T->total[c0 + c], sad16(cd, cur), T->rank[c0 + c]) : 0u;
+    }
+    for (int w = 0; w < cw; ++w) {
+      uint32_t r4 = 0;
+      for (int b = 0; b < 4; ++b) {
+        const int c = w * 4 + b;
+        if (c < cc && k0[c] != 0u) {
+          uint32_t r = 1;
+          for (int c2 = 0; c2 < cc; ++c2) r += (k0[c2] != 0u && k0[c2] < k0[c]) ? 1u : 0u;
+          r4 |= r << (8 * b);
+        }
+      }
+      s_rank4[((size_t)s * cw + w) * TN + tid] = r4;
     }
   }
   __syncthreads();
@@ -244,7 +275,9 @@ __global__ void __launch_bounds__(TN) mig_score_kernel(const MigScoreArgs a) {
     const int e0 = __ldg(a.dem_off + d), k = __ldg(a.dem_off + d + 1) - e0;  // uniform over the CTA
     bool any = false;
     if (k == 1) {
-      // fast path: single requested profile (every BASELINE config) — all state in registers
+      // single requested profile (every BASELINE config): all per-demand state in registers.
+      // Every candidate of every GPU is evaluated: provided = clamp(cand[p]-cur[p], 0, needed), then a
+      // (provided, rank, lowest index) compare folded into one integer max.
       const int p = __ldg(a.dem_key + e0);
       int resid = max(__ldg(a.dem_qty + e0), 0);
       const int pw = p >> 2, psh = (p & 3) * 8;
@@ -253,29 +286,31 @@ __global__ void __launch_bounds__(TN) mig_score_kernel(const MigScoreArgs a) {
         const int fj = (s_freew[(s * 4 + pw) * TN + tid] >> psh) & 0xff;
         const int needed = resid - fj;
         const int curj = uj + fj;
-        const int c0 = s_coff[s * TN + tid], cc = s_ccnt[s * TN + tid];
-        int best = -1;
-        uint32_t best_prov = 0, best_k0 = 0;
+        const uint32_t* ct = s_candT + ((size_t)s_model[s * TN + tid] * 16 + p) * cw;
+        uint32_t best = 0;
         if (needed > 0) {
-          for (int c = 0; c < cc; ++c) {
-            const uint32_t k0 = s_key0[((size_t)s * a.cmax + c) * TN + tid];
-            const int add = (int)s_cand[(c0 + c) * 16 + p] - curj;
-            const uint32_t prov = (uint32_t)max(min(add, needed), 0);
-            const bool ok = (k0 != 0u) & (prov != 0u);
-            const bool better = ok & ((prov > best_prov) | ((prov == best_prov) & (k0 > best_k0)));
-            if (better) {
-              best = c;
-              best_prov = prov;
-              best_k0 = k0;
+          for (int w = 0; w < cw; ++w) {
+            const uint32_t r4 = s_rank4[((size_t)s * cw + w) * TN + tid];
+            const uint32_t cb4 = ct[w];
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+              const int r = (r4 >> (8 * b)) & 0xff;
+              const int cb = (cb4 >> (8 * b)) & 0xff;
+              const int prov = min(cb - curj, needed);
+              const uint32_t key = ((uint32_t)prov << 16) | ((uint32_t)r << 8) | (uint32_t)(255 - (w * 4 + b));
+              const bool ok = (prov > 0) & (r != 0);
+              best = max(best, ok ? key : 0u);
             }
           }
         }
         int nf = fj;
-        if (best >= 0) {
+        int ch = -1;
+        if (best != 0u) {
           any = true;
-          nf = (int)s_cand[(c0 + best) * 16 + p] - uj;
+          ch = 255 - (int)(best & 0xffu);
+          nf = (int)((ct[ch >> 2] >> (8 * (ch & 3))) & 0xffu) - uj;
         }
-        if (a.choice) a.choice[(size_t)d * a.tg + g0 + s] = (int8_t)best;
+        if (a.choice) a.choice[(size_t)d * a.tg + g0 + s] = (int8_t)ch;
         resid = max(resid - nf, 0);
       }
     } else {
@@ -284,39 +319,37 @@ __global__ void __launch_bounds__(TN) mig_score_kernel(const MigScoreArgs a) {
         pid[j] = (j < k) ? __ldg(a.dem_key + e0 + j) : 0;
         resid[j] = (j < k) ? max(__ldg(a.dem_qty + e0 + j), 0) : 0;
       }
-      const int cnt_eff = (k == 0) ? 0 : cnt;
       for (int s = 0; s < cnt; ++s) {
-        int best = -1;
-        if (s < cnt_eff) {
-          const int c0 = s_coff[s * TN + tid], cc = s_ccnt[s * TN + tid];
+        int ch = -1;
+        if (k > 0) {
+          const uint32_t* ctm = s_candT + (size_t)s_model[s * TN + tid] * 16 * cw;
           int uj[kMaxKeys], fj[kMaxKeys];
           for (int j = 0; j < k; ++j) {
             uj[j] = (s_usedw[(s * 4 + (pid[j] >> 2)) * TN + tid] >> ((pid[j] & 3) * 8)) & 0xff;
             fj[j] = (s_freew[(s * 4 + (pid[j] >> 2)) * TN + tid] >> ((pid[j] & 3) * 8)) & 0xff;
           }
-          uint32_t best_prov = 0, best_k0 = 0;
-          for (int c = 0; c < cc; ++c) {
-            const uint32_t k0 = s_key0[((size_t)s * a.cmax + c) * TN + tid];
+          uint32_t best = 0;
+          for (int c = 0; c < a.cmax; ++c) {
+            const int r = (s_rank4[((size_t)s * cw + (c >> 2)) * TN + tid] >> (8 * (c & 3))) & 0xff;
+            if (r == 0) continue;
             int prov = 0;
             for (int j = 0; j < k; ++j) {
               const int needed = resid[j] - fj[j];
-              const int add = (int)s_cand[(c0 + c) * 16 + pid[j]] - (uj[j] + fj[j]);
+              const int add = (int)((ctm[pid[j] * cw + (c >> 2)] >> (8 * (c & 3))) & 0xffu) - (uj[j] + fj[j]);
               if (needed > 0 && add > 0) prov += min(add, needed);
             }
-            if (k0 != 0u && prov > 0 &&
-                ((uint32_t)prov > best_prov || ((uint32_t)prov == best_prov && k0 > best_k0))) {
-              best = c;
-              best_prov = prov;
-              best_k0 = k0;
-            }
+            if (prov > 0) best = max(best, ((uint32_t)prov << 16) | ((uint32_t)r << 8) | (uint32_t)(255 - c));
+          }
+          if (best != 0u) {
+            any = true;
+            ch = 255 - (int)(best & 0xffu);
           }
           for (int j = 0; j < k; ++j) {
-            const int nf = (best >= 0) ? (int)s_cand[(c0 + best) * 16 + pid[j]] - uj[j] : fj[j];
+            const int nf = (ch >= 0) ? (int)((ctm[pid[j] * cw + (ch >> 2)] >> (8 * (ch & 3))) & 0xffu) - uj[j] : fj[j];
             resid[j] = max(resid[j] - nf, 0);
           }
-          if (best >= 0) any = true;
         }
-        if (a.choice) a.choice[(size_t)d * a.tg + g0 + s] = (int8_t)best;
+        if (a.choice) a.choice[(size_t)d * a.tg + g0 + s] = (int8_t)ch;
       }
     }
     if (a.updated && n < a.N) a.updated[(size_t)d * a.N + n] = any ? 1 : 0;
@@ -582,7 +615,7 @@ struct MpsScoreArgs {
   const MpsGpu* gp;
   const int32_t* gpu_off;
   const uint8_t* valid;
-  int N, tg;
+  int N, tg, gs;
   int D, d_chunk;
   const int32_t* dem_off;
   const int32_t* dem_key;
@@ -593,33 +626,109 @@ struct MpsScoreArgs {
   uint32_t* out_mask;   // [D][tg] or null
 };
 
+// Shared-memory tile: per (node, slot) the free bytes as nw = ceil(S/4) words, the key mask, and
+// spare0 = cap - sum(size*free) (low 16 bits) | sum(size*free) (high 16 bits).
+__host__ __device__ inline size_t mps_score_smem_bytes(int gs, int S, int tn) {
+  const size_t nw = (size_t)(S + 3) / 4;
+  return (size_t)gs * tn * 4 * (nw + 2);
+}
+
+// exact floor(n / m) for n, m < 2^16 with inv = (m == 1 ? 0 : 0xFFFFFFFF / m + 1)
+__device__ __forceinline__ int div_small(int n, int m, uint32_t inv) { return m == 1 ? n : (int)__umulhi((uint32_t)n, inv); }
+
 template <int TN>
 __global__ void __launch_bounds__(TN) mps_score_kernel(const MpsScoreArgs a) {
+  extern __shared__ __align__(16) unsigned char smem[];
   __shared__ int s_sz[kMaxSizes];
   const int tid = threadIdx.x;
+  const int nw = (a.S + 3) >> 2;
+  uint32_t* s_free = reinterpret_cast<uint32_t*>(smem);       // [gs][nw][TN]
+  uint32_t* s_mask = s_free + (size_t)a.gs * nw * TN;          // [gs][TN]
+  uint32_t* s_spare = s_mask + (size_t)a.gs * TN;              // [gs][TN]
   if (tid < kMaxSizes) s_sz[tid] = tid < a.S ? a.sizes[tid] : 1;
   __syncthreads();
   const int n = blockIdx.x * TN + tid;
   const bool live = n < a.N && a.valid[n];
   const int g0 = n < a.N ? a.gpu_off[n] : 0;
   const int cnt = n < a.N ? a.gpu_off[n + 1] - g0 : 0;
+  for (int s = 0; s < cnt; ++s) {
+    const MpsGpu G = a.gp[g0 + s];
+    int origtot = 0;
+    for (uint32_t mk = G.fmask; mk; mk &= mk - 1) {
+      const int key = __ffs(mk) - 1;
+      origtot += s_sz[key] * (int)mps_byte(G.f0, G.f1, key);
+    }
+    const uint32_t w[8] = {G.f0.x, G.f0.y, G.f0.z, G.f0.w, G.f1.x, G.f1.y, G.f1.z, G.f1.w};
+    for (int i = 0; i < nw; ++i) s_free[((size_t)s * nw + i) * TN + tid] = w[i];
+    s_mask[s * TN + tid] = G.fmask;
+    s_spare[s * TN + tid] = ((uint32_t)origtot << 16) | (uint32_t)((int)G.cap - origtot);
+  }
+  __syncthreads();
   const int lane = tid & 31;
   const int d_begin = blockIdx.y * a.d_chunk;
   const int d_end = min(a.D, d_begin + a.d_chunk);
   for (int d = d_begin; d < d_end; ++d) {
     const int e0 = __ldg(a.dem_off + d), k = __ldg(a.dem_off + d + 1) - e0;
-    int sid[kMaxKeys], qty[kMaxKeys];
-    for (int j = 0; j < kMaxKeys; ++j) {
-      sid[j] = j < k ? __ldg(a.dem_key + e0 + j) : 0;
-      qty[j] = j < k ? __ldg(a.dem_qty + e0 + j) : 0;
-    }
     bool any = false;
-    if (n < a.N) {
-      uint8_t* of = a.out_free ? a.out_free + ((size_t)d * a.tg + g0) * a.S : nullptr;
-      uint32_t* om = a.out_mask ? a.out_mask + (size_t)d * a.tg + g0 : nullptr;
-      // an invalid node is never updated; its (untouched) layout is still reported
-      any = mps_walk_node(s_sz, a.S, const_cast<MpsGpu*>(a.gp), g0, cnt, live ? k : 0, sid, qty, false, of, om);
-      if (a.updated) a.updated[(size_t)d * a.N + n] = any ? 1 : 0;
+    if (k == 1 && !a.out_free) {
+      // one requested size: slicing.GPU.UpdateGeometryFor in closed form, registers only
+      const int sid = __ldg(a.dem_key + e0);
+      int resid = max(__ldg(a.dem_qty + e0), 0);
+      const int m = s_sz[sid];
+      const uint32_t inv = m == 1 ? 0u : 0xFFFFFFFFu / (uint32_t)m + 1u;
+      const int wi = sid >> 2, sh = (sid & 3) * 8;
+      if (live) {
+        for (int s = 0; s < cnt && resid > 0; ++s) {
+          const int fj = (s_free[((size_t)s * nw + wi) * TN + tid] >> sh) & 0xff;
+          const int miss = resid - fj;  // getMissingSlices
+          if (miss <= 0) break;         // this GPU already provides it; the residual drops to 0
+          const uint32_t sp = s_spare[s * TN + tid];
+          const uint32_t omask = s_mask[s * TN + tid];
+          const int otot = (int)(sp >> 16);
+          int spare = (int)(sp & 0xffffu);
+          const bool in_orig = (omask >> sid) & 1u;
+          // (a) spare capacity first
+          const int k1 = min(miss, div_small(spare, m, inv));
+          // (b) every original free key is deleted — with it whatever (a) created under such a key
+          spare = spare - k1 * m + otot + (in_orig ? k1 * m : 0);
+          int created = in_orig ? 0 : k1;
+          // (c) create in the space made
+          const int k2 = min(miss - k1, div_small(spare, m, inv));
+          created += k2;
+          spare -= k2 * m;
+          const bool upd = (k1 | k2) > 0;
+          // (d) restore the original keys, ascending size, each all-or-nothing
+          bool restored_sid = in_orig;
+          if (spare < otot) {
+            restored_sid = false;
+            for (uint32_t mk = omask; mk; mk &= mk - 1) {
+              const int key = __ffs(mk) - 1;
+              const int need = s_sz[key] * (int)((s_free[((size_t)s * nw + (key >> 2)) * TN + tid] >> ((key & 3) * 8)) & 0xff);
+              if (spare >= need) {
+                spare -= need;
+                if (key == sid) restored_sid = true;
+              }
+            }
+          }
+          const int nf = upd ? created + (restored_sid ? fj : 0) : fj;
+          any |= upd;
+          resid = max(resid - nf, 0);
+        }
+      }
+      if (a.updated && n < a.N) a.updated[(size_t)d * a.N + n] = any ? 1 : 0;
+    } else {
+      int sid[kMaxKeys], qty[kMaxKeys];
+      for (int j = 0; j < kMaxKeys; ++j) {
+        sid[j] = j < k ? __ldg(a.dem_key + e0 + j) : 0;
+        qty[j] = j < k ? __ldg(a.dem_qty + e0 + j) : 0;
+      }
+      if (n < a.N) {
+        uint8_t* of = a.out_free ? a.out_free + ((size_t)d * a.tg + g0) * a.S : nullptr;
+        uint32_t* om = a.out_mask ? a.out_mask + (size_t)d * a.tg + g0 : nullptr;
+        // an invalid node is never updated; its (untouched) layout is still reported
+        any = mps_walk_node(s_sz, a.S, const_cast<MpsGpu*>(a.gp), g0, cnt, live ? k : 0, sid, qty, false, of, om);
+        if (a.updated) a.updated[(size_t)d * a.N + n] = any ? 1 : 0;
+      }
     }
     const int mine = any ? n : kNoNode;
     const int wmin = __reduce_min_sync(0xffffffffu, mine);

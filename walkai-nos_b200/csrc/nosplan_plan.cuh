@@ -49,6 +49,7 @@ struct PlanArgs {
   int32_t* repart_node;
   int32_t* sched_node;
   int32_t* sched_gpu;
+  const int32_t* skip_if;  // device flag: non-zero = the chain fast path owns this plan (may be null)
 };
 
 // Out-of-line copies of the node walks for the planner kernel.  Inlining the MPS walk into the
@@ -126,6 +127,7 @@ __global__ void __launch_bounds__(kPlanThreads, 1) plan_kernel(const PlanArgs a)
   __shared__ int sh_cmd, sh_sig, sh_from, sh_best;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int NT = kPlanThreads;
+  if (a.skip_if && *a.skip_if) return;
 
   // ---- init: presence counters, first-fit bitmaps, search bounds -------------------------------------
   if (tid < kMaxSizes) {
@@ -327,6 +329,145 @@ __global__ void __launch_bounds__(kPlanThreads, 1) plan_kernel(const PlanArgs a)
   if (lane == 0) sh_cmd = 0;
   __syncwarp();
   bar_sync(1, NT);
+}
+
+
+
+// =================================================================================================================
+// Fast path of the planner for the reference's own behaviour (gate on, scheduling on) when every pod
+// requests exactly one profile with quantity >= 1.
+//
+// If every requested profile already exists somewhere in the cluster (used+free > 0), the gate
+// (mig_controller.go:121-144) stops every pod before tryRepartition, and it keeps doing so: AddPod
+// moves devices from free to used and never changes used+free.  What is left is Node.AddPod
+// first-fit, and a single-profile pod only reads and writes its own profile's counters — so the pods
+// of different profiles are independent chains.  One warp walks each chain in pod order.  Within a
+// chain "first GPU with free >= q" is monotone (free only decreases), so the warp keeps one cursor
+// per quantity with the 32 GPUs under it cached in registers (lane = GPU), and each pod costs a
+// ballot plus two fire-and-forget atomics.  Chains update different bytes of the same packed words,
+// hence atomics.  plan_presence_kernel decides eligibility on the device; the general kernel runs
+// (and this one does nothing) when a requested profile is absent.
+struct ChainArgs {
+  int n_chains;
+  const int32_t* chain_key;   // [n_chains] profile / size id
+  const int32_t* chain_off;   // [n_chains+1] into chain_pod / chain_q
+  const int32_t* chain_pod;   // kind-local pod index, planner order
+  const int32_t* chain_q;     // requested quantity (>= 1)
+  int N, tg, n_keys;
+  const int32_t* gpu_off;
+  const int32_t* gpu_node;    // [tg] node of each GPU, -1 if the node is invalid
+  uint4* m_used;
+  uint4* m_free;
+  const int32_t* sizes;
+  MpsGpu* p_gpu;
+  uint4* p_used_lo;
+  uint4* p_used_hi;
+  int32_t* present;           // [n_keys] sum of used+free over valid nodes (plan_presence_kernel)
+  int32_t* eligible;          // [1] 1 = every chain's key is present -> this kernel owns the plan
+  uint8_t* gate_hit;
+  int32_t* repart_node;
+  int32_t* sched_node;
+  int32_t* sched_gpu;
+};
+
+template <bool MPS>
+__global__ void plan_presence_kernel(ChainArgs a) {
+  __shared__ int sh[kMaxSizes];
+  if (threadIdx.x < kMaxSizes) sh[threadIdx.x] = 0;
+  __syncthreads();
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g < a.tg && a.gpu_node[g] >= 0) {
+    for (int key = 0; key < a.n_keys; ++key) {
+      int v;
+      if constexpr (MPS) v = (int)mps_byte(a.p_gpu[g].f0, a.p_gpu[g].f1, key) + (int)mps_byte(a.p_used_lo[g], a.p_used_hi[g], key);
+      else v = (int)byte_of(a.m_free[g], key) + (int)byte_of(a.m_used[g], key);
+      if (v) atomicAdd(&sh[key], v);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < a.n_keys && sh[threadIdx.x]) atomicAdd(&a.present[threadIdx.x], sh[threadIdx.x]);
+}
+
+__global__ void plan_eligible_kernel(ChainArgs a) {
+  // one warp: eligible iff every chain's key is present
+  bool ok = true;
+  for (int c = threadIdx.x; c < a.n_chains; c += 32) ok &= a.present[a.chain_key[c]] > 0;
+  ok = __all_sync(0xffffffffu, ok);
+  if (threadIdx.x == 0) *a.eligible = ok ? 1 : 0;
+}
+
+constexpr int kChainQ = 8;  // quantities 1..kChainQ each get a cursor; the host keeps larger ones off this path
+
+template <bool MPS>
+__global__ void __launch_bounds__(32) plan_chain_kernel(ChainArgs a) {
+  if (*a.eligible == 0) return;
+  const int c = blockIdx.x, lane = threadIdx.x;
+  const int key = a.chain_key[c];
+  const int j0 = a.chain_off[c], j1 = a.chain_off[c + 1];
+  const int sz = MPS ? a.sizes[key] : 0;
+  int base[kChainQ], cache[kChainQ];  // window start (multiple of 32) and this lane's GPU free count
+  // read through an atomic so the value is ordered after this warp's earlier deductions at L2
+  auto load_free = [&](int g) -> int {
+    if (g >= a.tg || a.gpu_node[g] < 0) return 0;
+    uint32_t* w;
+    if constexpr (MPS) w = reinterpret_cast<uint32_t*>(&a.p_gpu[g].f0) + (key >> 2);
+    else w = reinterpret_cast<uint32_t*>(a.m_free + g) + (key >> 2);
+    return (int)((atomicOr(w, 0u) >> ((key & 3) * 8)) & 0xffu);
+  };
+#pragma unroll
+  for (int qi = 0; qi < kChainQ; ++qi) {
+    base[qi] = 0;
+    cache[qi] = load_free(lane);
+  }
+  for (int j = j0; j < j1; ++j) {
+    const int q = __ldg(a.chain_q + j);
+    const int pod = __ldg(a.chain_pod + j);
+    const int qi = q - 1;
+    int found = -1;
+#pragma unroll
+    for (int t = 0; t < kChainQ; ++t) {
+      if (t != qi) continue;
+      while (base[t] < a.tg) {
+        const uint32_t hit = __ballot_sync(0xffffffffu, cache[t] >= q);
+        if (hit) {
+          found = base[t] + __ffs(hit) - 1;
+          break;
+        }
+        base[t] += 32;
+        cache[t] = load_free(base[t] + lane);
+      }
+    }
+    int node = -1, slot = -1;
+    if (found >= 0) {
+      node = a.gpu_node[found];
+      slot = found - a.gpu_off[node];
+      // every cursor whose window covers the GPU sees the deduction
+#pragma unroll
+      for (int t = 0; t < kChainQ; ++t)
+        if (found - base[t] == lane) cache[t] -= q;
+      if (lane == 0) {
+        const int sh = (key & 3) * 8;
+        if constexpr (MPS) {
+          uint32_t* fw = reinterpret_cast<uint32_t*>(&a.p_gpu[found].f0) + (key >> 2);  // f0,f1 are contiguous
+          uint32_t* uw = (key < 16 ? reinterpret_cast<uint32_t*>(a.p_used_lo + found) + (key >> 2)
+                                   : reinterpret_cast<uint32_t*>(a.p_used_hi + found) + ((key - 16) >> 2));
+          atomicSub(fw, (uint32_t)q << sh);
+          atomicAdd(uw, (uint32_t)q << sh);
+          atomicOr(&a.p_gpu[found].fmask, 1u << key);
+          atomicSub(&a.p_gpu[found].cap, (uint32_t)(q * sz));
+        } else {
+          atomicSub(reinterpret_cast<uint32_t*>(a.m_free + found) + (key >> 2), (uint32_t)q << sh);
+          atomicAdd(reinterpret_cast<uint32_t*>(a.m_used + found) + (key >> 2), (uint32_t)q << sh);
+        }
+      }
+    }
+    if (lane == 0) {
+      a.gate_hit[pod] = 1;
+      a.repart_node[pod] = -1;
+      a.sched_node[pod] = node;
+      a.sched_gpu[pod] = slot;
+    }
+  }
 }
 
 }  // namespace nsp
