@@ -287,22 +287,29 @@ __global__ void __launch_bounds__(TN) mig_score_kernel(const MigScoreArgs a) {
         const int needed = resid - fj;
         const int curj = uj + fj;
         const uint32_t* ct = s_candT + ((size_t)s_model[s * TN + tid] * 16 + p) * cw;
+        // key = provided << 16 | rank << 8 | (255 - index); provided is forced to 0 for a candidate that
+        // cannot be applied (rank byte 0), so "updated" <=> best >= 0x10000.  DPX min/max (VIADDMNMX.RELU,
+        // VIMNMX3) keep this at ~6 instructions per candidate.
         uint32_t best = 0;
         if (needed > 0) {
+          const int ncur = -curj;
           for (int w = 0; w < cw; ++w) {
             const uint32_t r4 = s_rank4[((size_t)s * cw + w) * TN + tid];
             const uint32_t cb4 = ct[w];
+            const uint32_t kc = 255u - 4u * (uint32_t)w;  // low two bits are 11: kc - b == kc ^ b
+            uint32_t key[4];
 #pragma unroll
             for (int b = 0; b < 4; ++b) {
-              const int r = (r4 >> (8 * b)) & 0xff;
-              const int cb = (cb4 >> (8 * b)) & 0xff;
-              const int prov = min(cb - curj, needed);
-              const uint32_t key = ((uint32_t)prov << 16) | ((uint32_t)r << 8) | (uint32_t)(255 - (w * 4 + b));
-              const bool ok = (prov > 0) & (r != 0);
-              best = max(best, ok ? key : 0u);
+              const int cb = (int)__byte_perm(cb4, 0u, 0x4440u | (uint32_t)b);
+              const uint32_t rs = __byte_perm(r4, 0u, 0x4404u | ((uint32_t)b << 4));  // rank << 8, 0 if not applicable
+              const int prov = min(__viaddmin_s32_relu(cb, ncur, needed), (int)rs);
+              key[b] = (uint32_t)prov * 65536u + (rs | (kc ^ (uint32_t)b));
             }
+            best = __vimax3_u32(best, key[0], key[1]);
+            best = __vimax3_u32(best, key[2], key[3]);
           }
         }
+        if (best < 0x10000u) best = 0u;
         int nf = fj;
         int ch = -1;
         if (best != 0u) {
