@@ -69,20 +69,6 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons}
 
 
-def shard_snapshot(snap, rank, world):
-    """Contiguous node range [rank*N/world, (rank+1)*N/world) of a snapshot."""
-    if snap is None:
-        return None, 0
-    N = int(snap["n_nodes"])
-    lo, hi = rank * N // world, (rank + 1) * N // world
-    g0, g1 = int(snap["gpu_off"][lo]), int(snap["gpu_off"][hi])
-    out = dict(n_nodes=hi - lo, gpu_off=(snap["gpu_off"][lo:hi + 1] - g0).astype(np.int32), valid=snap["valid"][lo:hi])
-    for k in ("model", "mem_gb", "used", "free", "used_mask", "free_mask"):
-        if k in snap:
-            out[k] = snap[k][g0:g1]
-    return out, lo
-
-
 def run_reference(args, cfg, rank):
     """--impl reference: the reference's CPU implementation of the path.  The reference is Go and
     cannot be built in this image (no Go toolchain), so this leg times the C++ oracle
@@ -173,8 +159,8 @@ def main():
 
     planner = pkg.Planner(local_rank)
     planner.set_mig_tables(cfg["names"], cfg["geom_off"], cfg["geom_counts"])
-    mig, mig_lo = shard_snapshot(cfg["mig"], rank, world)
-    mps, mps_lo = shard_snapshot(cfg["mps"], rank, world)
+    mig, mig_lo = pkg.dist.shard_snapshot(cfg["mig"], rank, world)
+    mps, mps_lo = pkg.dist.shard_snapshot(cfg["mps"], rank, world)
     if mig is not None:
         planner.set_mig_snapshot(mig)
     if mps is not None:
@@ -207,9 +193,7 @@ def main():
         if world > 1:
             # first node wins across shards: global index = local + shard offset, min over ranks
             for f, lo in ((first_m, mig_lo), (first_p, mps_lo)):
-                key = torch.where(f >= 0, f + lo, torch.full_like(f, BIG))
-                dist.all_reduce(key, op=dist.ReduceOp.MIN)
-                f.copy_(torch.where(key == BIG, torch.full_like(key, -1), key))
+                f.copy_(pkg.dist.merge_first_node(f, lo))
         if ev:
             ev[2].record()
 
@@ -279,20 +263,33 @@ def main():
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
     e2e_val = (ev_m + ev_p) / float(e2e_t.item())
 
-    # ---- planner latency: Plan(snapshot, pods) through the C ABI (rank 0's shard; p50 over steps) -----------
+    # ---- planner latency: Plan(snapshot, pods) through the C ABI, p50 over steps ---------------------------
+    # The plan is one dependency chain over the pod order: it is not sharded.  With
+    # N > 1 rank 0 plans the whole snapshot on its GPU (the state is a few MB) while the others wait.
     pods = cfg["pods"]
-    lat = []
-    for i in range(0 if args.no_plan else args.warmup + args.steps):
-        t0 = time.perf_counter()
-        planner.plan(pods["kind"], pods["off"], pods["key"], pods["qty"], gate=True, sched=True)
-        if i >= args.warmup:
-            lat.append((time.perf_counter() - t0) * 1e3)
-    lat_off = []
-    for i in range(0 if args.no_plan else 2 + min(args.steps, 5)):
-        t0 = time.perf_counter()
-        planner.plan(pods["kind"], pods["off"], pods["key"], pods["qty"], gate=False, sched=True)
-        if i >= 2:
-            lat_off.append((time.perf_counter() - t0) * 1e3)
+    lat, lat_off = [], []
+    if rank == 0 and not args.no_plan:
+        pl = planner
+        if world > 1:
+            pl = pkg.Planner(local_rank)
+            pl.set_mig_tables(cfg["names"], cfg["geom_off"], cfg["geom_counts"])
+            if cfg["mig"] is not None:
+                pl.set_mig_snapshot(cfg["mig"])
+            if cfg["mps"] is not None:
+                pl.set_mps_snapshot(cfg["sizes"], cfg["mps"])
+        for i in range(args.warmup + args.steps):
+            t0 = time.perf_counter()
+            pl.plan(pods["kind"], pods["off"], pods["key"], pods["qty"], gate=True, sched=True)
+            if i >= args.warmup:
+                lat.append((time.perf_counter() - t0) * 1e3)
+        for i in range(1 + min(args.steps, 3)):
+            t0 = time.perf_counter()
+            pl.plan(pods["kind"], pods["off"], pods["key"], pods["qty"], gate=False, sched=True)
+            if i >= 1:
+                lat_off.append((time.perf_counter() - t0) * 1e3)
+        if world > 1:
+            pl.close()
+    barrier()
     sampler.stop_flag = True
     sampler.join(timeout=2)
 

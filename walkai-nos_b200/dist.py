@@ -1,0 +1,40 @@
+"""Multi-GPU plumbing for the scorer: one process per GPU, nodes sharded contiguously
+across ranks, pods replicated.  Scoring needs no data-path collective; the only exchange is the
+per-demand "first node that would update" key, merged with one all-reduce(MIN) per pass — first node
+wins across shards exactly as tryRepartition does over the whole list (mig_controller.go:146-166).
+Works on CPU tensors with the gloo backend (tests) and CUDA tensors with NCCL (bench)."""
+from __future__ import annotations
+
+import numpy as np
+
+NO_NODE = 0x7FFFFFFF
+
+
+def shard_bounds(n_nodes: int, rank: int, world: int):
+    """Rank r owns nodes [r*N/world, (r+1)*N/world): contiguous, so the lowest global index wins."""
+    return rank * n_nodes // world, (rank + 1) * n_nodes // world
+
+
+def shard_snapshot(snap, rank: int, world: int):
+    """The rank's slice of a flattened snapshot (dict of arrays) and its first global node index."""
+    if snap is None:
+        return None, 0
+    N = int(snap["n_nodes"])
+    lo, hi = shard_bounds(N, rank, world)
+    g0, g1 = int(snap["gpu_off"][lo]), int(snap["gpu_off"][hi])
+    out = dict(n_nodes=hi - lo, gpu_off=(snap["gpu_off"][lo:hi + 1] - g0).astype(np.int32), valid=snap["valid"][lo:hi])
+    for k in ("model", "mem_gb", "used", "free", "used_mask", "free_mask"):
+        if k in snap:
+            out[k] = snap[k][g0:g1]
+    return out, lo
+
+
+def merge_first_node(first_local, lo: int, group=None):
+    """first_local: int32 torch tensor [D] of LOCAL node indices (-1 = none) on any device.
+    Returns the GLOBAL winner per demand (-1 = none) after one all-reduce(MIN)."""
+    import torch
+    import torch.distributed as dist
+    key = torch.where(first_local >= 0, first_local + lo, torch.full_like(first_local, NO_NODE))
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(key, op=dist.ReduceOp.MIN, group=group)
+    return torch.where(key == NO_NODE, torch.full_like(key, -1), key)
