@@ -5,5 +5,5 @@ holds only what the path needs: the CUDA sources, a ctypes binding used by the t
 the synthetic-cluster generator of SURVEY §8(d), and the host-side mirror of the reference's
 planner interface.
 """
-from . import dist, nosplan, synth  # noqa: F401
+from . import dist, host, nosplan, synth  # noqa: F401
 from .nosplan import Planner, NosplanError, build_library, library_path  # noqa: F401

@@ -45,7 +45,7 @@ def build_library(force: bool = False) -> str:
     srcs = [os.path.join(src_dir, f) for f in os.listdir(src_dir)] + [os.path.join(_HERE, "..", "include", "nosplan.h")]
     stale = not os.path.exists(_LIB) or any(os.path.getmtime(s) > os.path.getmtime(_LIB) for s in srcs)
     if force or stale:
-        subprocess.check_call(["make", "-C", src_dir] + (["-B"] if force else []), stdout=subprocess.DEVNULL,
+        subprocess.check_call(["make", "-C", src_dir, "all"] + (["-B"] if force else []), stdout=subprocess.DEVNULL,
                               stderr=subprocess.DEVNULL)
     return _LIB
 
