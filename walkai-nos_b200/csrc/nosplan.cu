@@ -12,6 +12,7 @@
 #include "nosplan.h"
 #include "nosplan_kernels.cuh"
 #include "nosplan_plan.cuh"
+#include "nosplan_seq.cuh"
 
 using namespace nsp;
 
@@ -730,6 +731,7 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
   }
   std::vector<uint8_t> o_gate[2];
   std::vector<int32_t> o_rep[2], o_node[2], o_gpu[2];
+  const int32_t* out_ptr[2] = {nullptr, nullptr};
   for (int kd = 0; kd < 2; ++kd) {
     Side& s = side[kd];
     const int M = (int)s.pod_idx.size();
@@ -788,7 +790,7 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
     a.sched_node = a.repart_node + M;
     a.sched_gpu = a.sched_node + M;
     a.gate_hit = reinterpret_cast<uint8_t*>(a.sched_gpu + M);
-    const bool want_chains = s.chains_ok && (flags == (NOSPLAN_PLAN_GATE | NOSPLAN_PLAN_SCHED)) && a.tg > 0;
+    const bool want_chains = s.chains_ok && (flags & NOSPLAN_PLAN_GATE) && a.tg > 0;
     if (want_chains) {
       // pods grouped by requested key, planner order kept inside a group
       std::vector<int32_t> ckey, coff{0}, cpod(M), cq(M);
@@ -834,6 +836,7 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
       ca.p_gpu = a.p_gpu;
       ca.p_used_lo = a.p_used_lo;
       ca.p_used_hi = a.p_used_hi;
+      ca.sched = (flags & NOSPLAN_PLAN_SCHED) ? 1 : 0;
       ca.gate_hit = a.gate_hit;
       ca.repart_node = a.repart_node;
       ca.sched_node = a.sched_node;
@@ -845,17 +848,62 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
       if (kd == 0) plan_chain_kernel<false><<<ca.n_chains, 32, 0, st>>>(ca);
       else plan_chain_kernel<true><<<ca.n_chains, 32, 0, st>>>(ca);
     }
-    if (kd == 0) plan_kernel<false><<<1, kPlanThreads, 0, st>>>(a);
-    else plan_kernel<true><<<1, kPlanThreads, 0, st>>>(a);
+    {
+      // general path: derive the masks/bitmaps from the working state, then one sequencer warp
+      SeqArgs q;
+      std::memset(&q, 0, sizeof(q));
+      q.M = a.M; q.pod_sig = a.pod_sig; q.D = a.D; q.dem_off = a.dem_off; q.dem_key = a.dem_key; q.dem_qty = a.dem_qty;
+      q.flags = a.flags; q.N = a.N; q.tg = a.tg; q.n_keys = a.n_keys; q.gpu_off = a.gpu_off; q.valid = a.valid;
+      q.gpu_node = kd ? h->d_mps_gnode.as<int32_t>() : h->d_mig_gnode.as<int32_t>();
+      q.T = a.T; q.m_used = a.m_used; q.m_free = a.m_free; q.m_model = a.m_model;
+      q.sizes = a.sizes; q.p_gpu = a.p_gpu; q.p_used_lo = a.p_used_lo; q.p_used_hi = a.p_used_hi;
+      q.nw = (a.N + 31) / 32 + 1;
+      q.gw = (a.tg + 31) / 32 + 1;
+      const size_t n_gm = (size_t)std::max(a.tg, 1), n_nb = (size_t)a.n_keys * q.nw, n_fb = (size_t)(a.n_keys + 1) * q.gw;
+      const size_t words = 2 * n_gm + 2 * n_nb + n_fb + kMaxSizes;
+      CU(b[13].reserve(words * 4));
+      q.gm = b[13].as<uint32_t>();
+      q.f1 = q.gm + n_gm;
+      q.nbt = q.f1 + n_gm;
+      q.nu1t = q.nbt + n_nb;
+      q.fbt = q.nu1t + n_nb;
+      q.present = reinterpret_cast<int32_t*>(q.fbt + n_fb);
+      q.gate_hit = a.gate_hit; q.repart_node = a.repart_node; q.sched_node = a.sched_node; q.sched_gpu = a.sched_gpu;
+      q.skip_if = a.skip_if;
+      CU(cudaMemsetAsync(q.nbt, 0, (2 * n_nb + n_fb + kMaxSizes) * 4, st));
+      const size_t smem = (2 * n_nb + n_fb) * 4;
+      q.use_smem = smem <= 160 * 1024 ? 1 : 0;
+      if (a.tg > 0) {
+        if (kd == 0) seq_prep_gpu_kernel<false><<<(a.tg + 127) / 128, 128, 0, st>>>(q);
+        else seq_prep_gpu_kernel<true><<<(a.tg + 127) / 128, 128, 0, st>>>(q);
+      }
+      if (a.N > 0) seq_prep_node_kernel<<<(a.N + 127) / 128, 128, 0, st>>>(q);
+      if (kd == 0) {
+        CU(cudaFuncSetAttribute(plan_seq_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        plan_seq_kernel<false><<<1, kSeqThreads, q.use_smem ? smem : 0, st>>>(q);
+      } else {
+        CU(cudaFuncSetAttribute(plan_seq_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        plan_seq_kernel<true><<<1, kSeqThreads, q.use_smem ? smem : 0, st>>>(q);
+      }
+    }
     CU(cudaGetLastError());
+    out_ptr[kd] = a.repart_node;
+  }
+  // results back only after both kinds are in flight: a device-to-host copy into pageable memory blocks
+  // the host until its stream drains, which would serialise the MIG and MPS chains
+  for (int kd = 0; kd < 2; ++kd) {
+    const int M = (int)side[kd].pod_idx.size();
+    if (M == 0) continue;
+    cudaStream_t st = kd ? h->stream2 : h->stream;
     o_rep[kd].resize(M);
     o_node[kd].resize(M);
     o_gpu[kd].resize(M);
     o_gate[kd].resize(M);
-    CU(cudaMemcpyAsync(o_rep[kd].data(), a.repart_node, sizeof(int32_t) * M, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(o_node[kd].data(), a.sched_node, sizeof(int32_t) * M, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(o_gpu[kd].data(), a.sched_gpu, sizeof(int32_t) * M, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(o_gate[kd].data(), a.gate_hit, M, cudaMemcpyDeviceToHost, st));
+    const int32_t* rep = out_ptr[kd];
+    CU(cudaMemcpyAsync(o_rep[kd].data(), rep, sizeof(int32_t) * M, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(o_node[kd].data(), rep + M, sizeof(int32_t) * M, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(o_gpu[kd].data(), rep + 2 * (size_t)M, sizeof(int32_t) * M, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(o_gate[kd].data(), reinterpret_cast<const uint8_t*>(rep + 3 * (size_t)M), M, cudaMemcpyDeviceToHost, st));
   }
   CU(cudaStreamSynchronize(h->stream));
   CU(cudaStreamSynchronize(h->stream2));

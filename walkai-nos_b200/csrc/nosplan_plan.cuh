@@ -1,8 +1,6 @@
-// nosplan_plan.cuh — the planner proper: Plan(snapshot, pendingPods) as ONE persistent CTA per
-// partitioning kind (MIG and MPS chains touch disjoint nodes and profiles, so they run
-// concurrently).  The pod order is a true dependency chain (each commit changes what the next pod
-// sees), so one "sequencer" warp walks the pods; the other warps of the CTA are parked on a named
-// barrier and are woken only for the data-parallel step — the first-node-wins search over nodes.
+// nosplan_plan.cuh — the planner: argument carrier shared by both planner paths and the per-profile
+// chain fast path.  MIG and MPS pods touch disjoint nodes and profiles, so the two kinds are planned
+// concurrently on two streams.  The general path is in nosplan_seq.cuh.
 //
 // Reference semantics replayed per pod:
 //   gate        Controller.profileAlreadyPresent   mig_controller.go:121-144
@@ -13,8 +11,6 @@
 #include "nosplan_kernels.cuh"
 
 namespace nsp {
-
-constexpr int kPlanThreads = 1024;
 
 struct PlanArgs {
   // pods of this kind, in planner order
@@ -52,287 +48,6 @@ struct PlanArgs {
   const int32_t* skip_if;  // device flag: non-zero = the chain fast path owns this plan (may be null)
 };
 
-// Out-of-line copies of the node walks for the planner kernel.  Inlining the MPS walk into the
-// sequencer let the compiler overlay the walk's scratch arrays with the caller's demand arrays
-// (observed on nvcc 12.9: the caller's key[] read back as 0 after the call); a real call gives the
-// walk its own frame.
-__device__ __noinline__ bool plan_mps_walk(const int* sz, int S, MpsGpu* gp, int g0, int cnt, int k, const int* sid,
-                                           const int* qty, bool commit) {
-  return mps_walk_node<true>(sz, S, gp, g0, cnt, k, sid, qty, commit, nullptr, nullptr);
-}
-__device__ __noinline__ bool plan_mig_walk(const MigTables* T, const uint4* used, uint4* fr, const uint8_t* model, int g0,
-                                           int cnt, int k, const int* pid, const int* qty, bool commit) {
-  return mig_walk_node<true>(T, used, fr, model, g0, cnt, k, pid, qty, commit, nullptr);
-}
-
-__device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
-
-template <bool MPS>
-__device__ __forceinline__ uint32_t plan_free_of(const PlanArgs& a, int g, int key) {
-  if constexpr (MPS) {
-    const MpsGpu* G = a.p_gpu + g;
-    return mps_byte(__ldcg(&G->f0), __ldcg(&G->f1), key);
-  } else {
-    return byte_of(__ldcg(a.m_free + g), key);
-  }
-}
-template <bool MPS>
-__device__ __forceinline__ uint32_t plan_used_of(const PlanArgs& a, int g, int key) {
-  if constexpr (MPS) {
-    return mps_byte(__ldcg(a.p_used_lo + g), __ldcg(a.p_used_hi + g), key);
-  } else {
-    return byte_of(__ldcg(a.m_used + g), key);
-  }
-}
-
-// add delta to byte `key` of a packed 16-byte map in global memory
-__device__ __forceinline__ void bump_byte(uint4* v, int key, int delta) {
-  uint32_t* w = reinterpret_cast<uint32_t*>(v) + (key >> 2);
-  const int sh = (key & 3) * 8;
-  const uint32_t old = __ldcg(w);
-  const uint32_t b = (((old >> sh) & 0xffu) + (uint32_t)delta) & 0xffu;
-  __stcg(w, (old & ~(0xffu << sh)) | (b << sh));
-}
-
-// GPU.AddPod on GPU g (mig/gpu.go:289-303, slicing/gpu.go:142-156): keys in ascending order; stops at
-// the first key that does not fit, KEEPING the deductions already made.  Returns true if all fit.
-// Maintains the first-fit bitmaps.
-template <bool MPS>
-__device__ inline bool plan_gpu_add_pod(const PlanArgs& a, int g, int k, const int* key, const int* qty) {
-  for (int j = 0; j < k; ++j) {
-    const int q = qty[j];
-    const int f = (int)plan_free_of<MPS>(a, g, key[j]);
-    if (f < q) return false;
-    if constexpr (MPS) {
-      MpsGpu* G = a.p_gpu + g;
-      if (key[j] < 16) bump_byte(&G->f0, key[j], -q);
-      else bump_byte(&G->f1, key[j] - 16, -q);
-      if (key[j] < 16) bump_byte(a.p_used_lo + g, key[j], q);
-      else bump_byte(a.p_used_hi + g, key[j] - 16, q);
-      __stcg(&G->fmask, __ldcg(&G->fmask) | (1u << key[j]));  // FreeProfiles[r] -= q creates the key
-      __stcg(&G->cap, __ldcg(&G->cap) - (uint32_t)(q * a.sizes[key[j]]));
-    } else {
-      bump_byte(a.m_free + g, key[j], -q);
-      bump_byte(a.m_used + g, key[j], q);
-    }
-    if (f - q == 0 && q > 0) a.bitmaps[(size_t)key[j] * a.words + (g >> 5)] &= ~(1u << (g & 31));
-  }
-  return true;
-}
-
-template <bool MPS>
-__global__ void __launch_bounds__(kPlanThreads, 1) plan_kernel(const PlanArgs a) {
-  __shared__ int sh_present[kMaxSizes];  // Node.Geometry()[key] summed over valid nodes (gate)
-  __shared__ int sh_sz[kMaxSizes];
-  __shared__ int sh_cmd, sh_sig, sh_from, sh_best;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int NT = kPlanThreads;
-  if (a.skip_if && *a.skip_if) return;
-
-  // ---- init: presence counters, first-fit bitmaps, search bounds -------------------------------------
-  if (tid < kMaxSizes) {
-    sh_present[tid] = 0;
-    sh_sz[tid] = (MPS && tid < a.n_keys) ? a.sizes[tid] : 1;
-  }
-  __syncthreads();
-  for (int w = tid; w < a.words * (a.n_keys + 1); w += NT) a.bitmaps[w] = 0;
-  for (int i = tid; i < 2 * a.D; i += NT) a.bounds[i] = 0;
-  __syncthreads();
-  for (int n = tid; n < a.N; n += NT) {
-    if (!a.valid[n]) continue;
-    for (int g = a.gpu_off[n]; g < a.gpu_off[n + 1]; ++g) {
-      atomicOr(&a.bitmaps[(size_t)a.n_keys * a.words + (g >> 5)], 1u << (g & 31));
-      for (int key = 0; key < a.n_keys; ++key) {
-        const int f = (int)plan_free_of<MPS>(a, g, key), u = (int)plan_used_of<MPS>(a, g, key);
-        if (f + u) atomicAdd(&sh_present[key], f + u);
-        if (f > 0) atomicOr(&a.bitmaps[(size_t)key * a.words + (g >> 5)], 1u << (g & 31));
-      }
-    }
-  }
-  __threadfence_block();
-  __syncthreads();
-
-  int32_t* lb_rep = a.bounds;         // [D] no node below it can update for this demand
-  int32_t* lb_fit = a.bounds + a.D;   // [D] no GPU below it can take this demand
-
-  // the node search executed by every thread of the CTA when the sequencer asks for it
-  auto scan_part = [&]() {
-    const int sig = sh_sig;
-    const int e0 = __ldg(a.dem_off + sig), k = __ldg(a.dem_off + sig + 1) - e0;
-    int key[kMaxKeys], qty[kMaxKeys];
-    for (int j = 0; j < kMaxKeys; ++j) {
-      key[j] = j < k ? __ldg(a.dem_key + e0 + j) : 0;
-      qty[j] = j < k ? __ldg(a.dem_qty + e0 + j) : 0;
-    }
-    for (int n = sh_from + tid; n < a.N; n += NT) {
-      if (n > *(volatile int*)&sh_best) break;
-      if (!a.valid[n]) continue;
-      const int g0 = a.gpu_off[n], cnt = a.gpu_off[n + 1] - g0;
-      bool u;
-      if constexpr (MPS) u = plan_mps_walk(sh_sz, a.n_keys, a.p_gpu, g0, cnt, k, key, qty, false);
-      else u = plan_mig_walk(a.T, a.m_used, a.m_free, a.m_model, g0, cnt, k, key, qty, false);
-      if (u) {
-        atomicMin(&sh_best, n);
-        break;
-      }
-    }
-  };
-
-  if (warp != 0) {
-    // helpers: parked until the sequencer needs a node search
-    for (;;) {
-      bar_sync(1, NT);
-      if (sh_cmd == 0) break;
-      scan_part();
-      bar_sync(2, NT);
-    }
-    return;
-  }
-
-  // ---- sequencer warp ------------------------------------------------------------------------------------
-  for (int i = 0; i < a.M; ++i) {
-    const int sig = __ldg(a.pod_sig + i);
-    const int e0 = __ldg(a.dem_off + sig), k = __ldg(a.dem_off + sig + 1) - e0;
-    int key[kMaxKeys], qty[kMaxKeys];
-    for (int j = 0; j < kMaxKeys; ++j) {
-      key[j] = j < k ? __ldg(a.dem_key + e0 + j) : 0;
-      qty[j] = j < k ? __ldg(a.dem_qty + e0 + j) : 0;
-    }
-    int out_gate = 0, out_rep = -1, out_node = -1, out_gpu = -1;
-    if (k > 0 && a.N > 0) {  // mig_controller.go:68-71, :78-81
-      // gate: every requested profile has used+free > 0 on some valid node
-      bool present = false;
-      if (a.flags & NOSPLAN_PLAN_GATE) {
-        present = true;
-        for (int j = 0; j < k; ++j) present &= sh_present[key[j]] > 0;
-      }
-      out_gate = present;
-      if (!present) {
-        int from = lb_rep[sig];
-        int best = kNoNode;
-        if (from < a.N) {
-          if (lane == 0) {
-            sh_cmd = 1;
-            sh_sig = sig;
-            sh_from = from;
-            sh_best = kNoNode;
-          }
-          __syncwarp();
-          bar_sync(1, NT);
-          scan_part();
-          bar_sync(2, NT);
-          best = sh_best;
-          __syncwarp();
-        }
-        if (best != kNoNode) {
-          // commit on node `best`: lanes = key for the presence delta, lane 0 applies
-          const int g0 = a.gpu_off[best], cnt = a.gpu_off[best + 1] - g0;
-          int before = 0;
-          if (lane < a.n_keys)
-            for (int s = 0; s < cnt; ++s) before += (int)plan_free_of<MPS>(a, g0 + s, lane);
-          __syncwarp();
-          if (lane == 0) {
-            if constexpr (MPS) plan_mps_walk(sh_sz, a.n_keys, a.p_gpu, g0, cnt, k, key, qty, true);
-            else plan_mig_walk(a.T, a.m_used, a.m_free, a.m_model, g0, cnt, k, key, qty, true);
-            __threadfence_block();
-          }
-          __syncwarp();
-          if (lane < a.n_keys) {
-            int after = 0;
-            for (int s = 0; s < cnt; ++s) {
-              const int g = g0 + s;
-              const int f = (int)plan_free_of<MPS>(a, g, lane);
-              after += f;
-              uint32_t* w = &a.bitmaps[(size_t)lane * a.words + (g >> 5)];
-              if (f > 0) *w |= 1u << (g & 31);
-              else *w &= ~(1u << (g & 31));
-            }
-            sh_present[lane] += after - before;
-          }
-          __syncwarp();
-          out_rep = best;
-          // every cached bound at or above this node is stale
-          for (int d = lane; d < a.D; d += 32) {
-            lb_rep[d] = min(lb_rep[d], best);
-            lb_fit[d] = min(lb_fit[d], g0);
-          }
-          __syncwarp();
-          lb_rep[sig] = best;
-        } else if (lane == 0) {
-          lb_rep[sig] = a.N;
-        }
-        __syncwarp();
-      }
-      if (a.flags & NOSPLAN_PLAN_SCHED) {
-        // first GPU (global GPU order == node order, then slot order) where every key fits
-        int found = -1;
-        for (int wbase = lb_fit[sig] >> 5; wbase < a.words && found < 0; wbase += 32) {
-          const int w = wbase + lane;
-          uint32_t bits = 0;
-          if (w < a.words) {
-            bits = a.bitmaps[(size_t)a.n_keys * a.words + w];
-            for (int j = 0; j < k; ++j)
-              if (qty[j] > 0) bits &= a.bitmaps[(size_t)key[j] * a.words + w];
-          }
-          int mine = -1;
-          while (bits) {
-            const int g = (w << 5) + __ffs(bits) - 1;
-            bits &= bits - 1;
-            bool fits = true;
-            for (int j = 0; j < k; ++j)
-              if (qty[j] > 1) fits &= (int)plan_free_of<MPS>(a, g, key[j]) >= qty[j];
-            if (fits) {
-              mine = g;
-              break;
-            }
-          }
-          const uint32_t hit = __ballot_sync(0xffffffffu, mine >= 0);
-          if (hit) found = __shfl_sync(0xffffffffu, mine, __ffs(hit) - 1);
-        }
-        if (found >= 0) {
-          // node of the winning GPU: binary search in gpu_off
-          int lo = 0, hi = a.N - 1;
-          while (lo < hi) {
-            const int mid = (lo + hi + 1) >> 1;
-            if (a.gpu_off[mid] <= found) lo = mid;
-            else hi = mid - 1;
-          }
-          // skip empty nodes that share the offset
-          while (a.gpu_off[lo + 1] <= found) ++lo;
-          const int g0 = a.gpu_off[lo];
-          if (lane == 0) {
-            // Node.AddPod tries the node's GPUs in order: the ones before the winner fail, keeping
-            // their partial deductions (multi-key pods only)
-            if (k > 1)
-              for (int g = g0; g < found; ++g) plan_gpu_add_pod<MPS>(a, g, k, key, qty);
-            plan_gpu_add_pod<MPS>(a, found, k, key, qty);
-            __threadfence_block();
-          }
-          __syncwarp();
-          out_node = lo;
-          out_gpu = found - g0;
-          if (lane == 0) lb_fit[sig] = found;
-          for (int d = lane; d < a.D; d += 32) lb_rep[d] = min(lb_rep[d], lo);
-        } else if (lane == 0) {
-          lb_fit[sig] = a.tg;
-        }
-        __syncwarp();
-      }
-    }
-    if (lane == 0) {
-      if (a.gate_hit) a.gate_hit[i] = (uint8_t)out_gate;
-      if (a.repart_node) a.repart_node[i] = out_rep;
-      if (a.sched_node) a.sched_node[i] = out_node;
-      if (a.sched_gpu) a.sched_gpu[i] = out_gpu;
-    }
-  }
-  if (lane == 0) sh_cmd = 0;
-  __syncwarp();
-  bar_sync(1, NT);
-}
-
-
-
 // =================================================================================================================
 // Fast path of the planner for the reference's own behaviour (gate on, scheduling on) when every pod
 // requests exactly one profile with quantity >= 1.
@@ -364,6 +79,7 @@ struct ChainArgs {
   uint4* p_used_hi;
   int32_t* present;           // [n_keys] sum of used+free over valid nodes (plan_presence_kernel)
   int32_t* eligible;          // [1] 1 = every chain's key is present -> this kernel owns the plan
+  int sched;                  // 0: gate only (NOSPLAN_PLAN_SCHED off): every pod is stopped by the gate, nothing else
   uint8_t* gate_hit;
   int32_t* repart_node;
   int32_t* sched_node;
@@ -404,11 +120,28 @@ __global__ void __launch_bounds__(32) plan_chain_kernel(ChainArgs a) {
   const int c = blockIdx.x, lane = threadIdx.x;
   const int key = a.chain_key[c];
   const int j0 = a.chain_off[c], j1 = a.chain_off[c + 1];
+  if (!a.sched) {
+    for (int j = j0 + lane; j < j1; j += 32) {
+      const int pod = a.chain_pod[j];
+      a.gate_hit[pod] = 1;
+      a.repart_node[pod] = -1;
+      a.sched_node[pod] = -1;
+      a.sched_gpu[pod] = -1;
+    }
+    return;
+  }
   const int sz = MPS ? a.sizes[key] : 0;
   int base[kChainQ], cache[kChainQ];  // window start (multiple of 32) and this lane's GPU free count
+  int wnode[kChainQ], wslot[kChainQ];  // node and slot of this lane's GPU in each window (-1: not a valid GPU)
   // read through an atomic so the value is ordered after this warp's earlier deductions at L2
-  auto load_free = [&](int g) -> int {
-    if (g >= a.tg || a.gpu_node[g] < 0) return 0;
+  auto load_win = [&](int g, int* node, int* slot) -> int {
+    *node = -1;
+    *slot = -1;
+    if (g >= a.tg) return 0;
+    const int n = a.gpu_node[g];
+    if (n < 0) return 0;
+    *node = n;
+    *slot = g - a.gpu_off[n];
     uint32_t* w;
     if constexpr (MPS) w = reinterpret_cast<uint32_t*>(&a.p_gpu[g].f0) + (key >> 2);
     else w = reinterpret_cast<uint32_t*>(a.m_free + g) + (key >> 2);
@@ -417,30 +150,36 @@ __global__ void __launch_bounds__(32) plan_chain_kernel(ChainArgs a) {
 #pragma unroll
   for (int qi = 0; qi < kChainQ; ++qi) {
     base[qi] = 0;
-    cache[qi] = load_free(lane);
+    cache[qi] = load_win(lane, &wnode[qi], &wslot[qi]);
   }
-  for (int j = j0; j < j1; ++j) {
-    const int q = __ldg(a.chain_q + j);
-    const int pod = __ldg(a.chain_pod + j);
+  for (int jb = j0; jb < j1; jb += 32) {
+    // the next 32 pods of the chain: one coalesced load, then a shuffle per pod
+    const int jl = jb + lane;
+    const int q32 = jl < j1 ? __ldg(a.chain_q + jl) : 1;
+    const int pod32 = jl < j1 ? __ldg(a.chain_pod + jl) : 0;
+    const int nj = min(32, j1 - jb);
+    for (int t32 = 0; t32 < nj; ++t32) {
+    const int q = __shfl_sync(0xffffffffu, q32, t32);
+    const int pod = __shfl_sync(0xffffffffu, pod32, t32);
     const int qi = q - 1;
-    int found = -1;
+    int found = -1, node = -1, slot = -1;
 #pragma unroll
     for (int t = 0; t < kChainQ; ++t) {
       if (t != qi) continue;
       while (base[t] < a.tg) {
         const uint32_t hit = __ballot_sync(0xffffffffu, cache[t] >= q);
         if (hit) {
-          found = base[t] + __ffs(hit) - 1;
+          const int src = __ffs(hit) - 1;
+          found = base[t] + src;
+          node = __shfl_sync(0xffffffffu, wnode[t], src);
+          slot = __shfl_sync(0xffffffffu, wslot[t], src);
           break;
         }
         base[t] += 32;
-        cache[t] = load_free(base[t] + lane);
+        cache[t] = load_win(base[t] + lane, &wnode[t], &wslot[t]);
       }
     }
-    int node = -1, slot = -1;
     if (found >= 0) {
-      node = a.gpu_node[found];
-      slot = found - a.gpu_off[node];
       // every cursor whose window covers the GPU sees the deduction
 #pragma unroll
       for (int t = 0; t < kChainQ; ++t)
@@ -466,6 +205,7 @@ __global__ void __launch_bounds__(32) plan_chain_kernel(ChainArgs a) {
       a.repart_node[pod] = -1;
       a.sched_node[pod] = node;
       a.sched_gpu[pod] = slot;
+    }
     }
   }
 }
