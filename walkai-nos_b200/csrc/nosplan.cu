@@ -158,14 +158,33 @@ void pick_chunks(int sm_count, int tiles, int D, int min_chunk, int* d_chunk, in
 }
 
 constexpr int kScoreTN = 128;
+constexpr int kScoreDS = 2;  // threads per node in the MIG scorer
 
 size_t mig_score_smem(const nosplan_t* h, int tn) {
   return mig_score_smem_bytes(h->h_tables.n_models, h->mig_gs, h->cmax, tn);
 }
 
+// picks the instantiation for the table's candidate count (CW words of 4 candidates; 0 = any)
+template <int CW>
+int launch_mig_score_cw(nosplan_t* h, const MigScoreArgs& a, dim3 grid, size_t smem, cudaStream_t st) {
+  CU(cudaFuncSetAttribute(mig_score_kernel<kScoreTN, kScoreDS, CW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  mig_score_kernel<kScoreTN, kScoreDS, CW><<<grid, kScoreTN * kScoreDS, smem, st>>>(a);
+  return NOSPLAN_OK;
+}
+int launch_mig_score_kernel(nosplan_t* h, const MigScoreArgs& a, dim3 grid, size_t smem, cudaStream_t st) {
+  switch ((a.cmax + 3) / 4) {
+    case 1: return launch_mig_score_cw<1>(h, a, grid, smem, st);
+    case 2: return launch_mig_score_cw<2>(h, a, grid, smem, st);
+    case 3: return launch_mig_score_cw<3>(h, a, grid, smem, st);
+    case 4: return launch_mig_score_cw<4>(h, a, grid, smem, st);
+    default: return launch_mig_score_cw<0>(h, a, grid, smem, st);
+  }
+}
+
 int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d_key, const int32_t* d_qty,
                      int32_t* d_first, uint8_t* d_updated, int8_t* d_choice, cudaStream_t st) {
   if (D == 0) return NOSPLAN_OK;
+  int rc = NOSPLAN_OK;
   fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, kNoNode);
   if (d_choice) CU(cudaMemsetAsync(d_choice, 0xff, (size_t)D * h->mig_tg, st));
   if (h->mig_n > 0) {
@@ -193,8 +212,7 @@ int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
     pick_chunks(h->sm_count, tiles, D, 16, &a.d_chunk, &gy);
     size_t smem = mig_score_smem(h, kScoreTN);
     if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MIG scorer tile needs %zu bytes of shared memory", smem);
-    CU(cudaFuncSetAttribute(mig_score_kernel<kScoreTN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    mig_score_kernel<kScoreTN><<<dim3(tiles, gy), kScoreTN, smem, st>>>(a);
+    if ((rc = launch_mig_score_kernel(h, a, dim3(tiles, gy), smem, st))) return rc;
   }
   CU(cudaGetLastError());
   return NOSPLAN_OK;
@@ -1131,8 +1149,7 @@ extern "C" int nosplan_score_mig_static(nosplan_t* h, int n_nodes, int gpus_per_
     pick_chunks(h->sm_count, tiles, D, 16, &a.d_chunk, &gy);
     const size_t smem = mig_score_smem_bytes(h->h_tables.n_models, gs, h->cmax, kScoreTN);
     if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MIG scorer tile needs %zu bytes of shared memory", smem);
-    CU(cudaFuncSetAttribute(mig_score_kernel<kScoreTN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));  // a limit, not an allocation
-    mig_score_kernel<kScoreTN><<<dim3(tiles, gy), kScoreTN, smem, st>>>(a);
+    if ((rc = launch_mig_score_kernel(h, a, dim3(tiles, gy), smem, st))) return rc;  // sets a smem limit, allocates nothing
   }
   nonode_to_minus1_kernel<<<(D + 255) / 256, 256, 0, st>>>(first_node, D);
   CU(cudaGetLastError());

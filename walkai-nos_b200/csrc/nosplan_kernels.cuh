@@ -208,11 +208,14 @@ __host__ __device__ inline size_t mig_score_smem_bytes(int n_models, int gs, int
   return (size_t)n_models * 16 * cw * 4 + (size_t)gs * cw * tn * 4 + (size_t)gs * 4 * tn * 4 * 2 + (size_t)gs * tn + 16;
 }
 
-template <int TN>
-__global__ void __launch_bounds__(TN) mig_score_kernel(const MigScoreArgs a) {
+// TN nodes per tile; DS threads share one node's tile (thread j of them takes every DS-th demand row of
+// the chunk), which raises occupancy without more shared memory; CW = words of 4 candidates per GPU
+// (0 = runtime), a template parameter so the candidate loop unrolls completely.
+template <int TN, int DS, int CW>
+__global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a) {
   extern __shared__ __align__(16) unsigned char smem[];
   const MigTables* __restrict__ T = a.T;
-  const int cw = (a.cmax + 3) >> 2;
+  const int cw = CW ? CW : ((a.cmax + 3) >> 2);
   const int n_models = T->n_models;
   uint32_t* s_candT = reinterpret_cast<uint32_t*>(smem);
   uint32_t* s_rank4 = s_candT + (size_t)n_models * 16 * cw;
@@ -220,10 +223,11 @@ __global__ void __launch_bounds__(TN) mig_score_kernel(const MigScoreArgs a) {
   uint32_t* s_freew = s_usedw + (size_t)a.gs * 4 * TN;
   uint8_t* s_model = reinterpret_cast<uint8_t*>(s_freew + (size_t)a.gs * 4 * TN);
 
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x % TN;   // node of the tile
+  const int dsub = threadIdx.x / TN;  // which share of the demand chunk
   const int n = blockIdx.x * TN + tid;
   // transposed candidate table (demand- and node-independent)
-  for (int i = tid; i < n_models * 16 * cw; i += TN) {
+  for (int i = threadIdx.x; i < n_models * 16 * cw; i += TN * DS) {
     const int w = i % cw, p = (i / cw) & 15, m = i / (cw * 16);
     const int c0 = T->geom_off[m], cc = T->geom_off[m + 1] - c0;
     uint32_t v = 0;
@@ -236,7 +240,7 @@ __global__ void __launch_bounds__(TN) mig_score_kernel(const MigScoreArgs a) {
   // per (node, slot): feasibility + demand-independent key of every candidate, reduced to a rank byte
   const int cnt = (n < a.N) ? a.s_cnt[n] : 0;
   const int g0 = (n < a.N) ? a.gpu_off[n] : 0;
-  for (int s = 0; s < cnt; ++s) {
+  for (int s = dsub; s < cnt; s += DS) {  // the DS threads of a node split its GPUs
     const uint4 u = a.s_used[(size_t)s * a.npad + n];
     const uint4 f = a.s_free[(size_t)s * a.npad + n];
     const int m = a.s_model[(size_t)s * a.npad + n];
@@ -270,8 +274,8 @@ __global__ void __launch_bounds__(TN) mig_score_kernel(const MigScoreArgs a) {
 
   const int d_begin = blockIdx.y * a.d_chunk;
   const int d_end = min(a.D, d_begin + a.d_chunk);
-  const int lane = tid & 31;
-  for (int d = d_begin; d < d_end; ++d) {
+  const int lane = threadIdx.x & 31;
+  for (int d = d_begin + dsub; d < d_end; d += DS) {
     const int e0 = __ldg(a.dem_off + d), k = __ldg(a.dem_off + d + 1) - e0;  // uniform over the CTA
     bool any = false;
     if (k == 1) {
@@ -293,6 +297,7 @@ __global__ void __launch_bounds__(TN) mig_score_kernel(const MigScoreArgs a) {
         uint32_t best = 0;
         if (needed > 0) {
           const int ncur = -curj;
+#pragma unroll
           for (int w = 0; w < cw; ++w) {
             const uint32_t r4 = s_rank4[((size_t)s * cw + w) * TN + tid];
             const uint32_t cb4 = ct[w];
