@@ -158,7 +158,7 @@ void pick_chunks(int sm_count, int tiles, int D, int min_chunk, int* d_chunk, in
 }
 
 constexpr int kScoreTN = 128;
-constexpr int kScoreDS = 2;  // threads per node in the MIG scorer
+constexpr int kScoreDS = 4;  // threads per node in the MIG scorer
 
 size_t mig_score_smem(const nosplan_t* h, int tn) {
   return mig_score_smem_bytes(h->h_tables.n_models, h->mig_gs, h->cmax, tn);

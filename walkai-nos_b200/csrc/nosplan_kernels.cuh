@@ -198,14 +198,15 @@ struct MigScoreArgs {
 
 // Shared-memory layout of one tile (TN nodes, gs GPU slots, cw = ceil(cmax/4) words of 4 candidates):
 //   candT [n_models][16][cw] u32   candidate quantities transposed: byte cc of word i = cand[4i+cc][p]
-//   rank4 [gs][cw][TN]       u32   per (node, slot): byte cc of word i = 0 if candidate 4i+cc cannot be
-//                                  applied, else 1 + the position of its demand-independent score
-//                                  key0 among the GPU's candidates (equal key0 -> equal byte)
+//   rank2 [gs][2cw][TN]      u32   per (node, slot): half-word h of word i describes candidate c = 2i+h:
+//                                  0 if it cannot be applied, else rank << 8 | (255 - c), rank = 1 + the
+//                                  position of its demand-independent score key0 among the GPU's
+//                                  candidates (equal key0 -> equal rank; the index bits break that tie)
 //   usedw/freew [gs][4][TN]  u32   the node's packed used / free maps
 //   model [gs][TN]           u8
 __host__ __device__ inline size_t mig_score_smem_bytes(int n_models, int gs, int cmax, int tn) {
   const size_t cw = (size_t)(cmax + 3) / 4;
-  return (size_t)n_models * 16 * cw * 4 + (size_t)gs * cw * tn * 4 + (size_t)gs * 4 * tn * 4 * 2 + (size_t)gs * tn + 16;
+  return (size_t)n_models * 16 * cw * 4 + (size_t)gs * 2 * cw * tn * 4 + (size_t)gs * 4 * tn * 4 * 2 + (size_t)gs * tn + 16;
 }
 
 // TN nodes per tile; DS threads share one node's tile (thread j of them takes every DS-th demand row of
@@ -218,8 +219,8 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
   const int cw = CW ? CW : ((a.cmax + 3) >> 2);
   const int n_models = T->n_models;
   uint32_t* s_candT = reinterpret_cast<uint32_t*>(smem);
-  uint32_t* s_rank4 = s_candT + (size_t)n_models * 16 * cw;
-  uint32_t* s_usedw = s_rank4 + (size_t)a.gs * cw * TN;
+  uint32_t* s_rank2 = s_candT + (size_t)n_models * 16 * cw;
+  uint32_t* s_usedw = s_rank2 + (size_t)a.gs * 2 * cw * TN;
   uint32_t* s_freew = s_usedw + (size_t)a.gs * 4 * TN;
   uint8_t* s_model = reinterpret_cast<uint8_t*>(s_freew + (size_t)a.gs * 4 * TN);
 
@@ -257,17 +258,17 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
       const uint4 cd = T->cand[c0 + c];
       k0[c] = all_ge4(cd, u) ? key0_of(T->total[c0 + c], sad16(cd, cur), T->rank[c0 + c]) : 0u;
     }
-    for (int w = 0; w < cw; ++w) {
-      uint32_t r4 = 0;
-      for (int b = 0; b < 4; ++b) {
-        const int c = w * 4 + b;
+    for (int w = 0; w < 2 * cw; ++w) {
+      uint32_t r2 = 0;
+      for (int b = 0; b < 2; ++b) {
+        const int c = w * 2 + b;
         if (c < cc && k0[c] != 0u) {
           uint32_t r = 1;
           for (int c2 = 0; c2 < cc; ++c2) r += (k0[c2] != 0u && k0[c2] < k0[c]) ? 1u : 0u;
-          r4 |= r << (8 * b);
+          r2 |= ((r << 8) | (uint32_t)(255 - c)) << (16 * b);
         }
       }
-      s_rank4[((size_t)s * cw + w) * TN + tid] = r4;
+      s_rank2[((size_t)s * 2 * cw + w) * TN + tid] = r2;
     }
   }
   __syncthreads();
@@ -292,23 +293,24 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
         const int curj = uj + fj;
         const uint32_t* ct = s_candT + ((size_t)s_model[s * TN + tid] * 16 + p) * cw;
         // key = provided << 16 | rank << 8 | (255 - index); provided is forced to 0 for a candidate that
-        // cannot be applied (rank byte 0), so "updated" <=> best >= 0x10000.  DPX min/max (VIADDMNMX.RELU,
-        // VIMNMX3) keep this at ~6 instructions per candidate.
+        // cannot be applied (its rank half-word is 0), so "updated" <=> best >= 0x10000.  DPX min/max
+        // (VIADDMNMX.RELU, VIMNMX3) keep this at ~5.5 instructions per candidate.
         uint32_t best = 0;
         if (needed > 0) {
           const int ncur = -curj;
 #pragma unroll
           for (int w = 0; w < cw; ++w) {
-            const uint32_t r4 = s_rank4[((size_t)s * cw + w) * TN + tid];
+            const uint32_t ra = s_rank2[((size_t)s * 2 * cw + 2 * w) * TN + tid];
+            const uint32_t rb = s_rank2[((size_t)s * 2 * cw + 2 * w + 1) * TN + tid];
             const uint32_t cb4 = ct[w];
-            const uint32_t kc = 255u - 4u * (uint32_t)w;  // low two bits are 11: kc - b == kc ^ b
             uint32_t key[4];
 #pragma unroll
             for (int b = 0; b < 4; ++b) {
               const int cb = (int)__byte_perm(cb4, 0u, 0x4440u | (uint32_t)b);
-              const uint32_t rs = __byte_perm(r4, 0u, 0x4404u | ((uint32_t)b << 4));  // rank << 8, 0 if not applicable
-              const int prov = min(__viaddmin_s32_relu(cb, ncur, needed), (int)rs);
-              key[b] = (uint32_t)prov * 65536u + (rs | (kc ^ (uint32_t)b));
+              const uint32_t rw = (b < 2) ? ra : rb;
+              const uint32_t rk = (b & 1) ? (rw >> 16) : (rw & 0xffffu);  // rank << 8 | 255-index, 0 if not applicable
+              const int prov = min(__viaddmin_s32_relu(cb, ncur, needed), (int)rk);
+              key[b] = (uint32_t)prov * 65536u + rk;
             }
             best = __vimax3_u32(best, key[0], key[1]);
             best = __vimax3_u32(best, key[2], key[3]);
@@ -342,15 +344,15 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
           }
           uint32_t best = 0;
           for (int c = 0; c < a.cmax; ++c) {
-            const int r = (s_rank4[((size_t)s * cw + (c >> 2)) * TN + tid] >> (8 * (c & 3))) & 0xff;
-            if (r == 0) continue;
+            const uint32_t rk = (s_rank2[((size_t)s * 2 * cw + (c >> 1)) * TN + tid] >> (16 * (c & 1))) & 0xffffu;
+            if (rk == 0u) continue;
             int prov = 0;
             for (int j = 0; j < k; ++j) {
               const int needed = resid[j] - fj[j];
               const int add = (int)((ctm[pid[j] * cw + (c >> 2)] >> (8 * (c & 3))) & 0xffu) - (uj[j] + fj[j]);
               if (needed > 0 && add > 0) prov += min(add, needed);
             }
-            if (prov > 0) best = max(best, ((uint32_t)prov << 16) | ((uint32_t)r << 8) | (uint32_t)(255 - c));
+            if (prov > 0) best = max(best, ((uint32_t)prov << 16) | rk);
           }
           if (best != 0u) {
             any = true;
