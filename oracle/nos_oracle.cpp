@@ -990,3 +990,43 @@ int orc_build_partitioning(int total_gpus, int P, const int32_t* used, const uin
 }
 
 }  // extern "C"
+
+// ---- agent-side diff planner, count level ----------------------------------------------------
+// plan.NewMigConfigPlan (internal/controllers/migagent/plan/plan.go:31-92) reduced to counts per
+// (GPU, profile); the device-level restatement pinned by the reference's table tests is
+// oracle/diff_plan.py, and tests/test_diff_plan.py checks the two against each other.
+//   used/free_ [G][P]   devices of the profile on the GPU ("unknown" status counts as used: not free)
+//   spec [G][P], spec_mask[G] bit p = a spec annotation names (GPU, profile)
+//   create[G][P]     devices to create (new ones + re-created free ones)
+//   del_free[G][P]   free devices to delete,  del_used[G][P]  non-free devices to delete
+extern "C" int orc_mig_diff_counts(int G, int P, const int32_t* used, const int32_t* free_, const int32_t* spec,
+                                   const uint32_t* spec_mask, int32_t* create, int32_t* del_free, int32_t* del_used) {
+  for (int g = 0; g < G; ++g) {
+    bool any_create = false;
+    for (int p = 0; p < P; ++p) {
+      const size_t i = (size_t)g * P + p;
+      create[i] = del_free[i] = del_used[i] = 0;
+      if (!((spec_mask[g] >> p) & 1u)) {  // not included in spec: everything goes (plan.go:37-41, :168-182)
+        del_free[i] = free_[i];
+        del_used[i] = used[i];
+        continue;
+      }
+      const int diff = spec[i] - (used[i] + free_[i]);  // plan.go:60
+      if (diff > 0) {
+        create[i] = diff;
+        any_create = true;
+      } else if (diff < 0) {  // free devices first, then used (plan.go:112-137)
+        del_free[i] = std::min(-diff, free_[i]);
+        del_used[i] = -diff - del_free[i];
+      }
+    }
+    if (any_create)  // plan.go:73-88: re-create the free devices that are not already being deleted
+      for (int p = 0; p < P; ++p) {
+        const size_t i = (size_t)g * P + p;
+        const int again = free_[i] - del_free[i];
+        del_free[i] += again;
+        create[i] += again;
+      }
+  }
+  return 0;
+}

@@ -471,3 +471,18 @@ def extract_gpus(labels: Dict[str, str], annotations: Dict[str, str], known_mode
         else:
             gpus.append(dict(index=i, model=model, mem_gb=mem, used={}, free={}))
     return gpus
+
+
+def mig_diff_counts(used: np.ndarray, free: np.ndarray, spec: np.ndarray, spec_mask: np.ndarray):
+    """Count-level plan.NewMigConfigPlan (orc_mig_diff_counts): returns (create, del_free, del_used) [G][P]."""
+    used = np.ascontiguousarray(used, np.int32)
+    free = np.ascontiguousarray(free, np.int32)
+    spec = np.ascontiguousarray(spec, np.int32)
+    spec_mask = np.ascontiguousarray(spec_mask, np.uint32)
+    G, P = used.shape
+    create = np.zeros((G, P), np.int32)
+    df = np.zeros((G, P), np.int32)
+    du = np.zeros((G, P), np.int32)
+    lib().orc_mig_diff_counts(G, P, _p(used, i32p), _p(free, i32p), _p(spec, i32p), _p(spec_mask, u32p), _p(create, i32p),
+                              _p(df, i32p), _p(du, i32p))
+    return create, df, du
