@@ -150,6 +150,16 @@ int nosplan_get_mps_state(nosplan_t* h, int32_t* used, int32_t* free_, uint32_t*
  *   out_free[total_gpus][n_profiles]  free devices after the call (unchanged where err) */
 int nosplan_init_geometry_mig(nosplan_t* h, uint8_t* err, int32_t* out_free);
 
+/* Agent-side diff planner, count level: plan.NewMigConfigPlan (internal/controllers/migagent/plan/plan.go:31-92,
+ * extractCandidatesForDeletion :112-137, extractResourcesToRecreate :94-110, getResourcesNotIncludedInSpec
+ * :168-182) for every GPU of a batch.  Rows are [n_gpus][n_profiles]: used/free_ = devices the GPU has
+ * ("unknown" status counts as used), spec = summed spec-annotation quantities, spec_mask[g] bit p = a spec
+ * annotation names (g, p).  Outputs: create (new + re-created free devices), del_free, del_used — which
+ * concrete device ids go is the host's choice (free first, ascending id, as the reference does). */
+int nosplan_diff_plan_mig(nosplan_t* h, int n_gpus, int n_profiles, const int32_t* used, const int32_t* free_,
+                          const int32_t* spec, const uint32_t* spec_mask, int32_t* create, int32_t* del_free,
+                          int32_t* del_used);
+
 /* ---- device-resident variants (inputs/outputs already in HBM; used for kernel-only timing) ------------ */
 /* Same as nosplan_score_mig/_mps but every pointer is a device pointer on the handle's device and the
  * work is enqueued on `stream` (a cudaStream_t) without synchronising.  first_node must be

@@ -1155,3 +1155,79 @@ extern "C" int nosplan_score_mig_static(nosplan_t* h, int n_nodes, int gpus_per_
   CU(cudaGetLastError());
   return NOSPLAN_OK;
 }
+
+// =================================================================================================================
+// Agent-side diff planner, count level: plan.NewMigConfigPlan
+// (internal/controllers/migagent/plan/plan.go:31-92) over every (GPU, profile) of a batch of nodes.
+namespace {
+// 16 lanes per GPU (one per profile column): coalesced rows, "any create on this GPU" by half-warp ballot
+__global__ void mig_diff_plan_kernel(int G, int P, const int32_t* __restrict__ used, const int32_t* __restrict__ fr,
+                                     const int32_t* __restrict__ spec, const uint32_t* __restrict__ spec_mask,
+                                     int32_t* __restrict__ create, int32_t* __restrict__ del_free, int32_t* __restrict__ del_used) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int g = idx >> 4, p = idx & 15;
+  const bool live = g < G && p < P;
+  int c = 0, df = 0, du = 0, f = 0;
+  if (live) {
+    const size_t i = (size_t)g * P + p;
+    const int u = used[i];
+    f = fr[i];
+    if (!((spec_mask[g] >> p) & 1u)) {  // not named by a spec annotation: delete everything (plan.go:37-41)
+      df = f;
+      du = u;
+    } else {
+      const int diff = spec[i] - (u + f);  // plan.go:60
+      if (diff > 0) c = diff;
+      else if (diff < 0) {  // free devices first, then used ones (plan.go:112-137)
+        df = min(-diff, f);
+        du = -diff - df;
+      }
+    }
+  }
+  const uint32_t creating = __ballot_sync(0xffffffffu, c > 0);
+  const uint32_t half = (threadIdx.x & 16) ? 0xffff0000u : 0x0000ffffu;
+  if (live) {
+    if (creating & half) {  // plan.go:73-88: re-create the free devices that are not already being deleted
+      const int again = f - df;
+      df += again;
+      c += again;
+    }
+    const size_t i = (size_t)g * P + p;
+    create[i] = c;
+    del_free[i] = df;
+    del_used[i] = du;
+  }
+}
+}  // namespace
+
+extern "C" int nosplan_diff_plan_mig(nosplan_t* h, int n_gpus, int n_profiles, const int32_t* used, const int32_t* free_,
+                                     const int32_t* spec, const uint32_t* spec_mask, int32_t* create, int32_t* del_free,
+                                     int32_t* del_used) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  if (n_gpus < 0 || n_profiles < 1 || n_profiles > NOSPLAN_MAX_MIG_PROFILES)
+    return fail(h, NOSPLAN_ERR_RANGE, "n_profiles %d out of range [1,%d]", n_profiles, NOSPLAN_MAX_MIG_PROFILES);
+  if (n_gpus == 0) return NOSPLAN_OK;
+  if (!used || !free_ || !spec || !spec_mask || !create || !del_free || !del_used) return fail(h, NOSPLAN_ERR_ARG, "null argument");
+  int rc = bind(h);
+  if (rc) return rc;
+  const size_t n = (size_t)n_gpus * n_profiles, bytes = n * sizeof(int32_t);
+  cudaStream_t st = h->stream;
+  if ((rc = upload(h, h->d_in[0], used, bytes, st))) return rc;
+  if ((rc = upload(h, h->d_in[1], free_, bytes, st))) return rc;
+  if ((rc = upload(h, h->d_in[2], spec, bytes, st))) return rc;
+  if ((rc = upload(h, h->d_in[3], spec_mask, sizeof(uint32_t) * n_gpus, st))) return rc;
+  CU(h->d_out[0].reserve(bytes));
+  CU(h->d_out[1].reserve(bytes));
+  CU(h->d_out[2].reserve(bytes));
+  const long long threads = (long long)n_gpus * 16;
+  mig_diff_plan_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(
+      n_gpus, n_profiles, h->d_in[0].as<int32_t>(), h->d_in[1].as<int32_t>(), h->d_in[2].as<int32_t>(),
+      h->d_in[3].as<uint32_t>(), h->d_out[0].as<int32_t>(), h->d_out[1].as<int32_t>(), h->d_out[2].as<int32_t>());
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(create, h->d_out[0].p, bytes, cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(del_free, h->d_out[1].p, bytes, cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(del_used, h->d_out[2].p, bytes, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  return NOSPLAN_OK;
+}

@@ -25,7 +25,7 @@ EXPORTS = [
     "nosplan_create", "nosplan_destroy", "nosplan_last_error", "nosplan_version", "nosplan_set_mig_tables",
     "nosplan_set_mig_snapshot", "nosplan_set_mps_snapshot", "nosplan_score_mig", "nosplan_score_mps", "nosplan_plan",
     "nosplan_get_mig_state", "nosplan_get_mps_state", "nosplan_init_geometry_mig", "nosplan_score_mig_dev",
-    "nosplan_score_mps_dev", "nosplan_mig_evals_per_demand", "nosplan_mps_evals_per_demand", "nosplan_score_mig_static",
+    "nosplan_score_mps_dev", "nosplan_mig_evals_per_demand", "nosplan_mps_evals_per_demand", "nosplan_score_mig_static", "nosplan_diff_plan_mig",
 ]
 
 
@@ -214,6 +214,15 @@ class Planner:
         free = np.zeros((tg, self.P), np.int32)
         self._ck(self.L.nosplan_init_geometry_mig(self.h, _p(err, u8p), _p(free, i32p)))
         return err, free
+
+    def diff_plan_mig(self, used, free, spec, spec_mask):
+        used, free, spec = (np.ascontiguousarray(x, np.int32) for x in (used, free, spec))
+        spec_mask = np.ascontiguousarray(spec_mask, np.uint32)
+        G, P = used.shape
+        create, df, du = (np.zeros((G, P), np.int32) for _ in range(3))
+        self._ck(self.L.nosplan_diff_plan_mig(self.h, G, P, _p(used, i32p), _p(free, i32p), _p(spec, i32p),
+                                              _p(spec_mask, u32p), _p(create, i32p), _p(df, i32p), _p(du, i32p)))
+        return create, df, du
 
     # ---- device-resident (pointers are ints: torch tensor .data_ptr()) -------------------------------
     def score_mig_dev(self, D, off_ptr, key_ptr, qty_ptr, first_ptr, updated_ptr=0, choice_ptr=0, stream=0):
