@@ -129,7 +129,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--config", type=int, default=5)
     ap.add_argument("--impl", default="b200")
-    ap.add_argument("--ref-sample", type=int, default=96)
+    ap.add_argument("--ref-sample", type=int, default=4096)
     ap.add_argument("--nodes", type=int, default=0)
     ap.add_argument("--pods", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
