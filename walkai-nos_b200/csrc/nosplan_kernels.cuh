@@ -275,127 +275,101 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
 
   const int d_begin = blockIdx.y * a.d_chunk;
   const int d_end = min(a.D, d_begin + a.d_chunk);
-  // emit the outcome of one (demand, node): the full table entry and the first-node-wins minimum
-  auto emit = [&](int d, bool any) {
-    if (n >= a.N) return;
-    if (a.updated) a.updated[(size_t)d * a.N + n] = any ? 1 : 0;
-    if (any && n < __ldcg(a.first_node + d)) atomicMin(a.first_node + d, n);
-  };
-  // rows with zero or several keys: the whole node walk at once (rare; every BASELINE config has one key)
-  auto generic_item = [&](int d, int e0, int k) -> bool {
+  const int lane = threadIdx.x & 31;
+  for (int d = d_begin + dsub; d < d_end; d += DS) {
+    const int e0 = __ldg(a.dem_off + d), k = __ldg(a.dem_off + d + 1) - e0;  // uniform over the CTA
     bool any = false;
-    int pid[kMaxKeys], resid[kMaxKeys];
-    for (int j = 0; j < kMaxKeys; ++j) {
-      pid[j] = (j < k) ? __ldg(a.dem_key + e0 + j) : 0;
-      resid[j] = (j < k) ? max(__ldg(a.dem_qty + e0 + j), 0) : 0;
-    }
-    for (int s = 0; s < cnt; ++s) {
-      int ch = -1;
-      if (k > 0) {
-        const uint32_t* ctm = s_candT + (size_t)s_model[s * TN + tid] * 16 * cw;
-        int uj[kMaxKeys], fj[kMaxKeys];
-        for (int j = 0; j < k; ++j) {
-          uj[j] = (s_usedw[(s * 4 + (pid[j] >> 2)) * TN + tid] >> ((pid[j] & 3) * 8)) & 0xff;
-          fj[j] = (s_freew[(s * 4 + (pid[j] >> 2)) * TN + tid] >> ((pid[j] & 3) * 8)) & 0xff;
-        }
+    if (k == 1) {
+      // single requested profile (every BASELINE config): all per-demand state in registers.
+      // Every candidate of every GPU is evaluated: provided = clamp(cand[p]-cur[p], 0, needed), then a
+      // (provided, rank, lowest index) compare folded into one integer max.
+      const int p = __ldg(a.dem_key + e0);
+      int resid = max(__ldg(a.dem_qty + e0), 0);
+      const int pw = p >> 2, psh = (p & 3) * 8;
+      for (int s = 0; s < cnt; ++s) {
+        const int uj = (s_usedw[(s * 4 + pw) * TN + tid] >> psh) & 0xff;
+        const int fj = (s_freew[(s * 4 + pw) * TN + tid] >> psh) & 0xff;
+        const int needed = resid - fj;
+        const int curj = uj + fj;
+        const uint32_t* ct = s_candT + ((size_t)s_model[s * TN + tid] * 16 + p) * cw;
+        // key = provided << 16 | rank << 8 | (255 - index); provided is forced to 0 for a candidate that
+        // cannot be applied (its rank half-word is 0), so "updated" <=> best >= 0x10000.  DPX min/max
+        // (VIADDMNMX.RELU, VIMNMX3) keep this at ~5.5 instructions per candidate.
         uint32_t best = 0;
-        for (int c = 0; c < a.cmax; ++c) {
-          const uint32_t rk = (s_rank2[((size_t)s * 2 * cw + (c >> 1)) * TN + tid] >> (16 * (c & 1))) & 0xffffu;
-          if (rk == 0u) continue;
-          int prov = 0;
-          for (int j = 0; j < k; ++j) {
-            const int needed = resid[j] - fj[j];
-            const int add = (int)((ctm[pid[j] * cw + (c >> 2)] >> (8 * (c & 3))) & 0xffu) - (uj[j] + fj[j]);
-            if (needed > 0 && add > 0) prov += min(add, needed);
+        if (needed > 0) {
+          const int ncur = -curj;
+#pragma unroll
+          for (int w = 0; w < cw; ++w) {
+            const uint32_t ra = s_rank2[((size_t)s * 2 * cw + 2 * w) * TN + tid];
+            const uint32_t rb = s_rank2[((size_t)s * 2 * cw + 2 * w + 1) * TN + tid];
+            const uint32_t cb4 = ct[w];
+            uint32_t key[4];
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+              const int cb = (int)__byte_perm(cb4, 0u, 0x4440u | (uint32_t)b);
+              const uint32_t rw = (b < 2) ? ra : rb;
+              const uint32_t rk = (b & 1) ? (rw >> 16) : (rw & 0xffffu);  // rank << 8 | 255-index, 0 if not applicable
+              const int prov = min(__viaddmin_s32_relu(cb, ncur, needed), (int)rk);
+              key[b] = (uint32_t)prov * 65536u + rk;
+            }
+            best = __vimax3_u32(best, key[0], key[1]);
+            best = __vimax3_u32(best, key[2], key[3]);
           }
-          if (prov > 0) best = max(best, ((uint32_t)prov << 16) | rk);
         }
+        if (best < 0x10000u) best = 0u;
+        int nf = fj;
+        int ch = -1;
         if (best != 0u) {
           any = true;
           ch = 255 - (int)(best & 0xffu);
+          nf = (int)((ct[ch >> 2] >> (8 * (ch & 3))) & 0xffu) - uj;
         }
-        for (int j = 0; j < k; ++j) {
-          const int nf = (ch >= 0) ? (int)((ctm[pid[j] * cw + (ch >> 2)] >> (8 * (ch & 3))) & 0xffu) - uj[j] : fj[j];
-          resid[j] = max(resid[j] - nf, 0);
+        if (a.choice) a.choice[(size_t)d * a.tg + g0 + s] = (int8_t)ch;
+        resid = max(resid - nf, 0);
+      }
+    } else {
+      int pid[kMaxKeys], resid[kMaxKeys];
+      for (int j = 0; j < kMaxKeys; ++j) {
+        pid[j] = (j < k) ? __ldg(a.dem_key + e0 + j) : 0;
+        resid[j] = (j < k) ? max(__ldg(a.dem_qty + e0 + j), 0) : 0;
+      }
+      for (int s = 0; s < cnt; ++s) {
+        int ch = -1;
+        if (k > 0) {
+          const uint32_t* ctm = s_candT + (size_t)s_model[s * TN + tid] * 16 * cw;
+          int uj[kMaxKeys], fj[kMaxKeys];
+          for (int j = 0; j < k; ++j) {
+            uj[j] = (s_usedw[(s * 4 + (pid[j] >> 2)) * TN + tid] >> ((pid[j] & 3) * 8)) & 0xff;
+            fj[j] = (s_freew[(s * 4 + (pid[j] >> 2)) * TN + tid] >> ((pid[j] & 3) * 8)) & 0xff;
+          }
+          uint32_t best = 0;
+          for (int c = 0; c < a.cmax; ++c) {
+            const uint32_t rk = (s_rank2[((size_t)s * 2 * cw + (c >> 1)) * TN + tid] >> (16 * (c & 1))) & 0xffffu;
+            if (rk == 0u) continue;
+            int prov = 0;
+            for (int j = 0; j < k; ++j) {
+              const int needed = resid[j] - fj[j];
+              const int add = (int)((ctm[pid[j] * cw + (c >> 2)] >> (8 * (c & 3))) & 0xffu) - (uj[j] + fj[j]);
+              if (needed > 0 && add > 0) prov += min(add, needed);
+            }
+            if (prov > 0) best = max(best, ((uint32_t)prov << 16) | rk);
+          }
+          if (best != 0u) {
+            any = true;
+            ch = 255 - (int)(best & 0xffu);
+          }
+          for (int j = 0; j < k; ++j) {
+            const int nf = (ch >= 0) ? (int)((ctm[pid[j] * cw + (ch >> 2)] >> (8 * (ch & 3))) & 0xffu) - uj[j] : fj[j];
+            resid[j] = max(resid[j] - nf, 0);
+          }
         }
+        if (a.choice) a.choice[(size_t)d * a.tg + g0 + s] = (int8_t)ch;
       }
-      if (a.choice && ch >= 0) a.choice[(size_t)d * a.tg + g0 + s] = (int8_t)ch;
     }
-    return any;
-  };
-
-  // Each lane walks its OWN sequence of (demand, GPU) steps: as soon as a node's free devices cover the
-  // residual of a demand, that lane moves on to its next demand row instead of idling while its
-  // neighbours finish theirs.  Every trip of the outer loop is one full candidate evaluation of one
-  // GPU for every lane still working, so the expensive block runs with (nearly) full warps.
-  int d = d_begin + dsub - DS;
-  int s = cnt, resid = 0, p = 0, pw = 0, psh = 0;
-  bool any = false, have = false;
-  for (;;) {
-    int uj = 0, fj = 0, needed = 0;
-    bool work = false;
-    for (;;) {  // cheap part: close finished items, fetch the next row
-      if (have && s < cnt) {
-        uj = (s_usedw[(s * 4 + pw) * TN + tid] >> psh) & 0xff;
-        fj = (s_freew[(s * 4 + pw) * TN + tid] >> psh) & 0xff;
-        needed = resid - fj;
-        if (needed > 0) {
-          work = true;
-          break;
-        }
-        s = cnt;  // free devices cover the residual: it drops to 0 and no later GPU can update (node.go:164-169)
-      }
-      if (have) emit(d, any);
-      have = false;
-      d += DS;
-      if (d >= d_end) break;
-      const int e0 = __ldg(a.dem_off + d), k = __ldg(a.dem_off + d + 1) - e0;
-      if (k != 1) {
-        emit(d, generic_item(d, e0, k));
-        continue;
-      }
-      p = __ldg(a.dem_key + e0);
-      resid = max(__ldg(a.dem_qty + e0), 0);
-      pw = p >> 2;
-      psh = (p & 3) * 8;
-      s = 0;
-      any = false;
-      have = true;
-    }
-    if (!work) break;
-    // expensive part: every candidate of GPU s for this lane's demand.
-    // key = provided << 16 | rank << 8 | (255 - index); provided is forced to 0 for a candidate that cannot
-    // be applied (its rank half-word is 0), so "updated" <=> best >= 0x10000.  DPX min/max (VIADDMNMX.RELU,
-    // VIMNMX3) keep this at ~5.5 instructions per candidate.
-    const uint32_t* ct = s_candT + ((size_t)s_model[s * TN + tid] * 16 + p) * cw;
-    const int ncur = -(uj + fj);
-    uint32_t best = 0;
-#pragma unroll
-    for (int w = 0; w < cw; ++w) {
-      const uint32_t ra = s_rank2[((size_t)s * 2 * cw + 2 * w) * TN + tid];
-      const uint32_t rb = s_rank2[((size_t)s * 2 * cw + 2 * w + 1) * TN + tid];
-      const uint32_t cb4 = ct[w];
-      uint32_t key[4];
-#pragma unroll
-      for (int b = 0; b < 4; ++b) {
-        const int cb = (int)__byte_perm(cb4, 0u, 0x4440u | (uint32_t)b);
-        const uint32_t rw = (b < 2) ? ra : rb;
-        const uint32_t rk = (b & 1) ? (rw >> 16) : (rw & 0xffffu);  // rank << 8 | 255-index, 0 if not applicable
-        const int prov = min(__viaddmin_s32_relu(cb, ncur, needed), (int)rk);
-        key[b] = (uint32_t)prov * 65536u + rk;
-      }
-      best = __vimax3_u32(best, key[0], key[1]);
-      best = __vimax3_u32(best, key[2], key[3]);
-    }
-    int nf = fj;
-    if (best >= 0x10000u) {
-      any = true;
-      const int ch = 255 - (int)(best & 0xffu);
-      nf = (int)((ct[ch >> 2] >> (8 * (ch & 3))) & 0xffu) - uj;
-      if (a.choice) a.choice[(size_t)d * a.tg + g0 + s] = (int8_t)ch;
-    }
-    resid = max(resid - nf, 0);
-    ++s;
+    if (a.updated && n < a.N) a.updated[(size_t)d * a.N + n] = any ? 1 : 0;
+    const int mine = any ? n : kNoNode;
+    const int wmin = __reduce_min_sync(0xffffffffu, mine);
+    if (lane == 0 && wmin != kNoNode) atomicMin(a.first_node + d, wmin);
   }
 }
 
