@@ -217,7 +217,7 @@ __global__ void __launch_bounds__(kSeqThreads, 1) plan_seq_kernel(const SeqArgs 
         const uint4 u = __ldcg(a.m_used + g), f = __ldcg(a.m_free + g);
         uint32_t* r = sh_node[lane];
         r[0] = u.x; r[1] = u.y; r[2] = u.z; r[3] = u.w; r[4] = f.x; r[5] = f.y; r[6] = f.z; r[7] = f.w;
-        sh_model[lane] = a.m_model[g];
+        sh_model[lane] = __ldg(a.m_model + g);
       }
       sh_gm[lane] = a.gm[g];
       sh_f1[lane] = a.f1[g];
@@ -354,9 +354,22 @@ __global__ void __launch_bounds__(kSeqThreads, 1) plan_seq_kernel(const SeqArgs 
     return false;
   };
 
+#ifdef NOSPLAN_SEQ_PROFILE
+  long long tp[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  long long t0 = clock64();
+#define SEQ_TICK(i) { long long t1 = clock64(); tp[i] += t1 - t0; t0 = t1; }
+#else
+#define SEQ_TICK(i)
+#endif
+  int e0_32 = 0, k_32 = 0;
   for (int i = 0; i < a.M; ++i) {
-    const int sig = __ldg(a.pod_sig + i);
-    const int e0 = __ldg(a.dem_off + sig), k = __ldg(a.dem_off + sig + 1) - e0;
+    if ((i & 31) == 0) {  // the next 32 pods: one coalesced load, then a shuffle per pod
+      const int il = i + lane;
+      const int sg = il < a.M ? __ldg(a.pod_sig + il) : 0;
+      e0_32 = __ldg(a.dem_off + sg);
+      k_32 = __ldg(a.dem_off + sg + 1) - e0_32;
+    }
+    const int e0 = __shfl_sync(0xffffffffu, e0_32, i & 31), k = __shfl_sync(0xffffffffu, k_32, i & 31);
     __syncwarp();
     if (lane < kMaxKeys) {
       key[lane] = lane < k ? __ldg(a.dem_key + e0 + lane) : 0;
@@ -401,18 +414,76 @@ __global__ void __launch_bounds__(kSeqThreads, 1) plan_seq_kernel(const SeqArgs 
             if (hit) best = ((wbase + src) << 5) + __ffs(hit) - 1;
           }
         }
+        SEQ_TICK(0)
         if (best >= 0) {
-          const int g0 = a.gpu_off[best], cnt = a.gpu_off[best + 1] - g0;
+          const int g0 = __ldg(a.gpu_off + best), cnt = __ldg(a.gpu_off + best + 1) - g0;
           load_node(g0, cnt);
           const int before = node_sum(cnt);
+          SEQ_TICK(1)
           uint32_t changed = 0;
           if constexpr (MPS) {
             // slicing.Node.UpdateGeometryFor on the image: lane 0 runs the closed-form walk GPU by GPU
-            if (lane == 0) {
+            if (lane == 0 && k == 1) {
+              // one requested size: slicing/gpu.go:162-220 in closed form (same algebra as mps_score_kernel)
+              const int sid = key[0], m = sh_sz[sid];
+              int resid = qty[0];
+              for (int s = 0; s < cnt && resid > 0; ++s) {
+                const int fj = img_free(s, sid);
+                const int miss = resid - fj;
+                if (miss <= 0) break;  // covered: the residual drops to 0
+                if (!((sh_gm[s] >> sid) & 1u)) {  // the size does not fit in cap: this GPU cannot update
+                  resid -= fj;
+                  continue;
+                }
+                uint32_t* r = sh_node[s];
+                uint8_t* fb = reinterpret_cast<uint8_t*>(r);
+                const uint32_t omask = r[16];
+                int otot = 0;
+                for (uint32_t mk = omask; mk; mk &= mk - 1) otot += sh_sz[__ffs(mk) - 1] * (int)fb[__ffs(mk) - 1];
+                int spare = (int)r[17] - otot;
+                const bool in_orig = (omask >> sid) & 1u;
+                const int k1 = min(miss, spare / m);                       // (a) spare capacity first
+                spare = spare - k1 * m + otot + (in_orig ? k1 * m : 0);    // (b) every original free key deleted
+                int created = in_orig ? 0 : k1;
+                const int k2 = min(miss - k1, spare / m);                  // (c) create in the space made
+                created += k2;
+                spare -= k2 * m;
+                uint32_t restored = 0;                                     // (d) restore, ascending size
+                for (uint32_t mk = omask; mk; mk &= mk - 1) {
+                  const int kk = __ffs(mk) - 1;
+                  const int need = sh_sz[kk] * (int)fb[kk];
+                  if (spare >= need) {
+                    restored |= 1u << kk;
+                    spare -= need;
+                  } else {
+                    fb[kk] = 0;
+                  }
+                }
+                const int nf = (((restored >> sid) & 1u) ? fj : 0) + created;
+                fb[sid] = (uint8_t)nf;
+                r[16] = restored | (created > 0 ? (1u << sid) : 0u);
+                changed |= 1u << s;
+                resid = max(resid - nf, 0);
+              }
+            } else if (lane == 0) {
               int resid[kMaxKeys];
               for (int j = 0; j < kMaxKeys; ++j) resid[j] = j < k ? qty[j] : 0;
               for (int s = 0; s < cnt; ++s) {
                 uint32_t* r = sh_node[s];
+                // this GPU updates only if the smallest missing size fits in its cap (gm is that prefix mask)
+                bool left = false, can = false;
+                for (int j = 0; j < k; ++j) {
+                  left |= resid[j] > 0;
+                  if (resid[j] - img_free(s, key[j]) > 0) {
+                    can = (sh_gm[s] >> key[j]) & 1u;
+                    break;
+                  }
+                }
+                if (!left) break;  // nothing required any more
+                if (!can) {
+                  for (int j = 0; j < k; ++j) resid[j] = max(resid[j] - img_free(s, key[j]), 0);
+                  continue;
+                }
                 const uint4 f0 = make_uint4(r[0], r[1], r[2], r[3]), f1 = make_uint4(r[4], r[5], r[6], r[7]);
                 int created[kMaxKeys];
                 uint32_t restored = r[16];
@@ -496,10 +567,12 @@ __global__ void __launch_bounds__(kSeqThreads, 1) plan_seq_kernel(const SeqArgs 
             }
           }
           __syncwarp();
+          SEQ_TICK(2)
           store_node(g0, cnt, changed);
           const int after = node_sum(cnt);
           if (lane < K) sh_present[lane] += after - before;
           refresh_node(best, g0, cnt, changed);
+          SEQ_TICK(3)
           out_rep = best;
         }
       }
@@ -537,9 +610,10 @@ __global__ void __launch_bounds__(kSeqThreads, 1) plan_seq_kernel(const SeqArgs 
           const uint32_t hit = __ballot_sync(0xffffffffu, mine >= 0);
           if (hit) found = __shfl_sync(0xffffffffu, mine, __ffs(hit) - 1);
         }
+        SEQ_TICK(4)
         if (found >= 0) {
-          const int node = a.gpu_node[found];
-          const int g0 = a.gpu_off[node], cnt = a.gpu_off[node + 1] - g0;
+          const int node = __ldg(a.gpu_node + found);
+          const int g0 = __ldg(a.gpu_off + node), cnt = __ldg(a.gpu_off + node + 1) - g0;
           // single-key quantity-1 pods: everything before `found` for this key is exhausted
           if (k == 1 && qty[0] == 1 && lane == 0) sh_hint[key[0]] = found >> 5;
           load_node(g0, cnt);
@@ -563,11 +637,16 @@ __global__ void __launch_bounds__(kSeqThreads, 1) plan_seq_kernel(const SeqArgs 
             }
           }
           __syncwarp();
+          SEQ_TICK(5)
           store_node(g0, cnt, changed);
           refresh_node(node, g0, cnt, changed);
+          SEQ_TICK(6)
           out_node = node;
           out_gpu = found - g0;
+        } else if (k == 1 && qty[0] == 1 && lane == 0) {
+          sh_hint[key[0]] = a.gw;  // no GPU holds a free one: nothing to scan until a commit sets a bit again
         }
+        __syncwarp();
       }
     }
     if (lane == 0) {
@@ -576,7 +655,13 @@ __global__ void __launch_bounds__(kSeqThreads, 1) plan_seq_kernel(const SeqArgs 
       if (a.sched_node) a.sched_node[i] = out_node;
       if (a.sched_gpu) a.sched_gpu[i] = out_gpu;
     }
+    SEQ_TICK(7)
   }
+#ifdef NOSPLAN_SEQ_PROFILE
+  if (lane == 0)
+    printf("seq profile (Mcycles) mps=%d search %lld load %lld commit %lld refresh %lld fit %lld addpod %lld refresh2 %lld rest %lld\n",
+           (int)MPS, tp[0] >> 20, tp[1] >> 20, tp[2] >> 20, tp[3] >> 20, tp[4] >> 20, tp[5] >> 20, tp[6] >> 20, tp[7] >> 20);
+#endif
 }
 
 }  // namespace nsp
