@@ -158,54 +158,89 @@ __global__ void __launch_bounds__(32) plan_chain_kernel(ChainArgs a) {
     const int q32 = jl < j1 ? __ldg(a.chain_q + jl) : 1;
     const int pod32 = jl < j1 ? __ldg(a.chain_pod + jl) : 0;
     const int nj = min(32, j1 - jb);
-    for (int t32 = 0; t32 < nj; ++t32) {
-    const int q = __shfl_sync(0xffffffffu, q32, t32);
-    const int pod = __shfl_sync(0xffffffffu, pod32, t32);
-    const int qi = q - 1;
-    int found = -1, node = -1, slot = -1;
+    // Runs of pods asking for the same quantity are placed together: GPU l of the window can take
+    // floor(free/q) of them, an inclusive warp prefix sum of those capacities tells every pod of the
+    // run (one per lane) which GPU it lands on — first-fit in pod order, 32 pods per step.
+    int t32 = 0;
+    while (t32 < nj) {
+      const int q = __shfl_sync(0xffffffffu, q32, t32);
+      const int qi = q - 1;
+      const uint32_t same = __ballot_sync(0xffffffffu, lane >= t32 && lane < nj && q32 == q);
+      const uint32_t rest = ~(same >> t32);
+      const int r = rest ? __ffs(rest) - 1 : 32 - t32;  // run length (>= 1)
 #pragma unroll
-    for (int t = 0; t < kChainQ; ++t) {
-      if (t != qi) continue;
-      while (base[t] < a.tg) {
-        const uint32_t hit = __ballot_sync(0xffffffffu, cache[t] >= q);
-        if (hit) {
-          const int src = __ffs(hit) - 1;
-          found = base[t] + src;
-          node = __shfl_sync(0xffffffffu, wnode[t], src);
-          slot = __shfl_sync(0xffffffffu, wslot[t], src);
-          break;
-        }
-        base[t] += 32;
-        cache[t] = load_win(base[t] + lane, &wnode[t], &wslot[t]);
-      }
-    }
-    if (found >= 0) {
-      // every cursor whose window covers the GPU sees the deduction
+      for (int t = 0; t < kChainQ; ++t) {
+        if (t != qi) continue;
+        int served = 0;
+        while (served < r) {
+          const int jl0 = t32 + served;  // lane of the first pod still to place
+          if (base[t] >= a.tg) {         // no GPU left for this quantity: the rest of the run stays pending
+            if (lane >= jl0 && lane < t32 + r) {
+              a.gate_hit[pod32] = 1;
+              a.repart_node[pod32] = -1;
+              a.sched_node[pod32] = -1;
+              a.sched_gpu[pod32] = -1;
+            }
+            break;
+          }
+          const int capl = q == 1 ? cache[t] : cache[t] / q;
+          int P = capl;  // inclusive prefix sum over the window's GPUs
 #pragma unroll
-      for (int t = 0; t < kChainQ; ++t)
-        if (found - base[t] == lane) cache[t] -= q;
-      if (lane == 0) {
-        const int sh = (key & 3) * 8;
-        if constexpr (MPS) {
-          uint32_t* fw = reinterpret_cast<uint32_t*>(&a.p_gpu[found].f0) + (key >> 2);  // f0,f1 are contiguous
-          uint32_t* uw = (key < 16 ? reinterpret_cast<uint32_t*>(a.p_used_lo + found) + (key >> 2)
-                                   : reinterpret_cast<uint32_t*>(a.p_used_hi + found) + ((key - 16) >> 2));
-          atomicSub(fw, (uint32_t)q << sh);
-          atomicAdd(uw, (uint32_t)q << sh);
-          atomicOr(&a.p_gpu[found].fmask, 1u << key);
-          atomicSub(&a.p_gpu[found].cap, (uint32_t)(q * sz));
-        } else {
-          atomicSub(reinterpret_cast<uint32_t*>(a.m_free + found) + (key >> 2), (uint32_t)q << sh);
-          atomicAdd(reinterpret_cast<uint32_t*>(a.m_used + found) + (key >> 2), (uint32_t)q << sh);
+          for (int off = 1; off < 32; off <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, P, off);
+            if (lane >= off) P += v;
+          }
+          const int tot = __shfl_sync(0xffffffffu, P, 31);
+          if (tot == 0) {  // window exhausted for this quantity: every GPU before the next one has free < q
+            base[t] += 32;
+            cache[t] = load_win(base[t] + lane, &wnode[t], &wslot[t]);
+            continue;
+          }
+          const int m = min(r - served, tot);
+          const int j = lane - jl0;  // this lane's pod is the j-th of the run still to place
+          const bool mine = j >= 0 && j < m;
+          int lo = 0;  // number of GPUs whose inclusive prefix is <= j  ==  index of the GPU that takes pod j
+#pragma unroll
+          for (int step = 16; step >= 1; step >>= 1) {
+            const int pv = __shfl_sync(0xffffffffu, P, (lo + step - 1) & 31);
+            if (pv <= j) lo += step;
+          }
+          lo = min(lo, 31);
+          const int node = __shfl_sync(0xffffffffu, wnode[t], lo);
+          const int slot = __shfl_sync(0xffffffffu, wslot[t], lo);
+          if (mine) {
+            a.gate_hit[pod32] = 1;
+            a.repart_node[pod32] = -1;
+            a.sched_node[pod32] = node;
+            a.sched_gpu[pod32] = slot;
+          }
+          // what each GPU of the window gives up
+          const int take = min(max(m - (P - capl), 0), capl);
+          const int dq = take * q;
+          const int wb = base[t];
+#pragma unroll
+          for (int t2 = 0; t2 < kChainQ; ++t2)
+            if (base[t2] == wb) cache[t2] -= dq;  // windows are 32-aligned: same base == same GPUs
+          if (dq > 0) {
+            const int g = wb + lane;
+            const int sh = (key & 3) * 8;
+            if constexpr (MPS) {
+              uint32_t* fw = reinterpret_cast<uint32_t*>(&a.p_gpu[g].f0) + (key >> 2);  // f0,f1 are contiguous
+              uint32_t* uw = (key < 16 ? reinterpret_cast<uint32_t*>(a.p_used_lo + g) + (key >> 2)
+                                       : reinterpret_cast<uint32_t*>(a.p_used_hi + g) + ((key - 16) >> 2));
+              atomicSub(fw, (uint32_t)dq << sh);
+              atomicAdd(uw, (uint32_t)dq << sh);
+              atomicOr(&a.p_gpu[g].fmask, 1u << key);
+              atomicSub(&a.p_gpu[g].cap, (uint32_t)(dq * sz));
+            } else {
+              atomicSub(reinterpret_cast<uint32_t*>(a.m_free + g) + (key >> 2), (uint32_t)dq << sh);
+              atomicAdd(reinterpret_cast<uint32_t*>(a.m_used + g) + (key >> 2), (uint32_t)dq << sh);
+            }
+          }
+          served += m;
         }
       }
-    }
-    if (lane == 0) {
-      a.gate_hit[pod] = 1;
-      a.repart_node[pod] = -1;
-      a.sched_node[pod] = node;
-      a.sched_gpu[pod] = slot;
-    }
+      t32 += r;
     }
   }
 }
