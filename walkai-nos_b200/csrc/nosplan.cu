@@ -62,7 +62,7 @@ struct nosplan {
   int mig_n = 0, mig_tg = 0, mig_gs = 0, mig_npad = 0;
   int64_t mig_evals = 0;
   DevBuf d_mig_off, d_mig_valid, d_mig_model, d_mig_used0, d_mig_free0, d_mig_used, d_mig_free;
-  DevBuf d_mig_sused, d_mig_sfree, d_mig_smodel, d_mig_scnt, d_mig_gnode;
+  DevBuf d_mig_sused, d_mig_sfree, d_mig_smodel, d_mig_scnt, d_mig_gnode, d_mig_gslot;
   bool mig_state_dirty = false;  // working copy differs from the snapshot
 
   // MPS snapshot
@@ -70,7 +70,7 @@ struct nosplan {
   int S = 0;
   int mps_n = 0, mps_tg = 0, mps_gs = 0;
   int64_t mps_evals = 0;
-  DevBuf d_mps_sizes, d_mps_off, d_mps_valid, d_mps_gpu0, d_mps_ulo0, d_mps_uhi0, d_mps_gpu, d_mps_ulo, d_mps_uhi, d_mps_gnode;
+  DevBuf d_mps_sizes, d_mps_off, d_mps_valid, d_mps_gpu0, d_mps_ulo0, d_mps_uhi0, d_mps_gpu, d_mps_ulo, d_mps_uhi, d_mps_gnode, d_mps_gslot;
   bool mps_state_dirty = false;
 
   // scratch / staging
@@ -284,7 +284,7 @@ void nosplan_destroy(nosplan_t* h) {
   DevBuf* all[] = {&h->d_tables, &h->d_mig_off, &h->d_mig_valid, &h->d_mig_model, &h->d_mig_used0, &h->d_mig_free0,
                    &h->d_mig_used, &h->d_mig_free, &h->d_mig_sused, &h->d_mig_sfree, &h->d_mig_smodel, &h->d_mig_scnt,
                    &h->d_mps_sizes, &h->d_mps_off, &h->d_mps_valid, &h->d_mps_gpu0, &h->d_mps_ulo0, &h->d_mps_uhi0,
-                   &h->d_mps_gpu, &h->d_mps_ulo, &h->d_mps_uhi, &h->d_mig_gnode, &h->d_mps_gnode};
+                   &h->d_mps_gpu, &h->d_mps_ulo, &h->d_mps_uhi, &h->d_mig_gnode, &h->d_mps_gnode, &h->d_mig_gslot, &h->d_mps_gslot};
   for (DevBuf* b : all) b->release();
   for (auto& b : h->d_in) b.release();
   for (auto& b : h->d_dem) b.release();
@@ -426,10 +426,14 @@ int nosplan_set_mig_snapshot(nosplan_t* h, int n_nodes, const int32_t* gpu_off, 
   std::vector<int32_t> mdl(std::max(tg, 1), 0);
   for (int n = 0; n < n_nodes; ++n)
     for (int g = gpu_off[n]; g < gpu_off[n + 1]; ++g) mdl[g] = v[n] ? model[g] : 0;
-  std::vector<int32_t> gnode(std::max(tg, 1), -1);
+  std::vector<int32_t> gnode(std::max(tg, 1), -1), gslot(std::max(tg, 1), 0);
   for (int n = 0; n < n_nodes; ++n)
-    for (int g = gpu_off[n]; g < gpu_off[n + 1]; ++g) gnode[g] = v[n] ? n : -1;
+    for (int g = gpu_off[n]; g < gpu_off[n + 1]; ++g) {
+      gnode[g] = v[n] ? n : -1;
+      gslot[g] = g - gpu_off[n];
+    }
   if ((rc = upload(h, h->d_mig_gnode, gnode.data(), sizeof(int32_t) * gnode.size(), h->stream))) return rc;
+  if ((rc = upload(h, h->d_mig_gslot, gslot.data(), sizeof(int32_t) * gslot.size(), h->stream))) return rc;
   if ((rc = upload(h, h->d_mig_off, gpu_off, sizeof(int32_t) * (n_nodes + 1), h->stream))) return rc;
   if ((rc = upload(h, h->d_mig_valid, v.data(), std::max(n_nodes, 1), h->stream))) return rc;
   if ((rc = upload(h, h->d_in[0], mdl.data(), sizeof(int32_t) * std::max(tg, 1), h->stream))) return rc;
@@ -525,10 +529,14 @@ int nosplan_set_mps_snapshot(nosplan_t* h, int n_sizes, const int32_t* sizes_gb,
     }
   int rc = bind(h);
   if (rc) return rc;
-  std::vector<int32_t> gnode(std::max(tg, 1), -1);
+  std::vector<int32_t> gnode(std::max(tg, 1), -1), gslot(std::max(tg, 1), 0);
   for (int n = 0; n < n_nodes; ++n)
-    for (int g = gpu_off[n]; g < gpu_off[n + 1]; ++g) gnode[g] = v[n] ? n : -1;
+    for (int g = gpu_off[n]; g < gpu_off[n + 1]; ++g) {
+      gnode[g] = v[n] ? n : -1;
+      gslot[g] = g - gpu_off[n];
+    }
   if ((rc = upload(h, h->d_mps_gnode, gnode.data(), sizeof(int32_t) * gnode.size(), h->stream))) return rc;
+  if ((rc = upload(h, h->d_mps_gslot, gslot.data(), sizeof(int32_t) * gslot.size(), h->stream))) return rc;
   if ((rc = upload(h, h->d_mps_sizes, sizes_gb, sizeof(int32_t) * S, h->stream))) return rc;
   if ((rc = upload(h, h->d_mps_off, gpu_off, sizeof(int32_t) * (n_nodes + 1), h->stream))) return rc;
   if ((rc = upload(h, h->d_mps_valid, v.data(), std::max(n_nodes, 1), h->stream))) return rc;
@@ -848,6 +856,7 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
       ca.n_keys = a.n_keys;
       ca.gpu_off = a.gpu_off;
       ca.gpu_node = kd ? h->d_mps_gnode.as<int32_t>() : h->d_mig_gnode.as<int32_t>();
+      ca.gpu_slot = kd ? h->d_mps_gslot.as<int32_t>() : h->d_mig_gslot.as<int32_t>();
       ca.m_used = a.m_used;
       ca.m_free = a.m_free;
       ca.sizes = a.sizes;

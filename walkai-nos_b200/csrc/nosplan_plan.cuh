@@ -71,6 +71,7 @@ struct ChainArgs {
   int N, tg, n_keys;
   const int32_t* gpu_off;
   const int32_t* gpu_node;    // [tg] node of each GPU, -1 if the node is invalid
+  const int32_t* gpu_slot;    // [tg] position of the GPU inside its node
   uint4* m_used;
   uint4* m_free;
   const int32_t* sizes;
@@ -138,14 +139,17 @@ __global__ void __launch_bounds__(32) plan_chain_kernel(ChainArgs a) {
     *node = -1;
     *slot = -1;
     if (g >= a.tg) return 0;
-    const int n = a.gpu_node[g];
-    if (n < 0) return 0;
-    *node = n;
-    *slot = g - a.gpu_off[n];
     uint32_t* w;
     if constexpr (MPS) w = reinterpret_cast<uint32_t*>(&a.p_gpu[g].f0) + (key >> 2);
     else w = reinterpret_cast<uint32_t*>(a.m_free + g) + (key >> 2);
-    return (int)((atomicOr(w, 0u) >> ((key & 3) * 8)) & 0xffu);
+    // three independent loads (one L2 latency per window); rows of invalid nodes are zero
+    const uint32_t word = atomicOr(w, 0u);
+    const int n = __ldg(a.gpu_node + g);
+    const int sl = __ldg(a.gpu_slot + g);
+    if (n < 0) return 0;
+    *node = n;
+    *slot = sl;
+    return (int)((word >> ((key & 3) * 8)) & 0xffu);
   };
 #pragma unroll
   for (int qi = 0; qi < kChainQ; ++qi) {
