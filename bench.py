@@ -174,8 +174,10 @@ def main():
     t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
     d_mo, d_mk, d_mq = t(mo), t(mk), t(mq)
     d_po, d_pk, d_pq = t(po), t(pk), t(pq)
-    first_m = torch.empty(max(Dm, 1), dtype=torch.int32, device=dev)
-    first_p = torch.empty(max(Dp, 1), dtype=torch.int32, device=dev)
+    first_all = torch.empty(max(Dm, 1) + max(Dp, 1), dtype=torch.int32, device=dev)
+    first_m, first_p = first_all[:max(Dm, 1)], first_all[max(Dm, 1):]
+    lo_vec = torch.cat([torch.full((max(Dm, 1),), mig_lo, dtype=torch.int32, device=dev),
+                        torch.full((max(Dp, 1),), mps_lo, dtype=torch.int32, device=dev)])
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
     BIG = 0x7FFFFFFF
@@ -192,8 +194,7 @@ def main():
             planner.score_mps_dev(Dp, d_po.data_ptr(), d_pk.data_ptr(), d_pq.data_ptr(), first_p.data_ptr(), 0, 0, 0, stream)
         if world > 1:
             # first node wins across shards: global index = local + shard offset, min over ranks
-            for f, lo in ((first_m, mig_lo), (first_p, mps_lo)):
-                f.copy_(pkg.dist.merge_first_node(f, lo))
+            first_all.copy_(pkg.dist.merge_first_node_keys(first_all, lo_vec))
         if ev:
             ev[2].record()
 

@@ -42,6 +42,8 @@ def _worker(rank, world, port, out_dir):
             _, _, _, first = o.score_mps(shard, req, mask, want_free=False)
             _, _, _, full = o.score_mps(cfg[name], req, mask, want_free=False)
         merged = pkg.dist.merge_first_node(torch.from_numpy(first.copy()), lo).numpy()
+        both = pkg.dist.merge_first_node_keys(torch.from_numpy(first.copy()), torch.full((len(first),), lo, dtype=torch.int32)).numpy()
+        assert np.array_equal(merged, both)
         res[name] = (merged, full)
     ok = all(np.array_equal(m, f) for m, f in res.values())
     some = any((f >= 0).any() for _, f in res.values())

@@ -38,3 +38,15 @@ def merge_first_node(first_local, lo: int, group=None):
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(key, op=dist.ReduceOp.MIN, group=group)
     return torch.where(key == NO_NODE, torch.full_like(key, -1), key)
+
+
+def merge_first_node_keys(first_local, lo_vec, group=None):
+    """Same as merge_first_node for several demand sets at once: first_local [D_total] holds local indices
+    of different node lists back to back and lo_vec [D_total] the matching shard offsets, so one
+    all-reduce(MIN) resolves all of them (collectives here are latency-bound: issue as few as possible)."""
+    import torch
+    import torch.distributed as dist
+    key = torch.where(first_local >= 0, first_local + lo_vec, NO_NODE)
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(key, op=dist.ReduceOp.MIN, group=group)
+    return torch.where(key == NO_NODE, -1, key)
