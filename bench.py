@@ -311,14 +311,14 @@ def main():
             "planner_latency_gate_off_ms_p50": float(np.median(lat_off)) if lat_off else None,
             "evals_per_step": {"mig": ev_m, "mps": ev_p},
             # achieved/frac follow SURVEY §8(d): algorithmic bytes (no credit for on-chip reuse) / kernel time.
-            # traffic = ncu dram__bytes_read+write per launch of the same command (profiles/r1_mig_score_final.md):
+            # traffic = ncu dram__bytes_read+write per launch of the same command (profiles/r1_final_bench_cfg5.md):
             # the tile state is re-used from shared memory, HBM is idle and the binding roof is the integer
-            # ALU pipe (ncu: 85 % of its peak), which is why frac is above 1.
+            # instruction issue / ALU pipe (ncu: issue-active 79 %, ALU 74 %), which is why frac is above 1.
             "roofline": {"bound": "hbm", "kernel": "mig_score_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
-                         "frac": ach / peak, "peak_source": peak_src, "traffic": 983040 if args.config == 5 and world == 1 else None,
+                         "frac": ach / peak, "peak_source": peak_src, "traffic": 981760 if args.config == 5 and world == 1 else None,
                          "algorithmic_bytes_per_eval": BYTES_PER_EVAL_MIG, "kernel_ms": mig_ms / args.steps,
                          "mps_kernel_ms": mps_ms / args.steps, "binding_roof": "int ALU pipe",
-                         "alu_pipe_pct_of_peak_ncu": 85.4},
+                         "alu_pipe_pct_of_peak_ncu": 74.0, "issue_active_pct_ncu": 78.8},
             "clocks": sampler.summary(),
         }
         if not args.no_cpu_baseline and world == 1:

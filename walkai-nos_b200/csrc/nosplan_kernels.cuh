@@ -276,6 +276,9 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
   const int d_begin = blockIdx.y * a.d_chunk;
   const int d_end = min(a.D, d_begin + a.d_chunk);
   const int lane = threadIdx.x & 31;
+  uint32_t k16, k8;  // opaque 2^16 and 2^8 (see the inner loop)
+  asm("mov.u32 %0, 65536;" : "=r"(k16));
+  asm("mov.u32 %0, 256;" : "=r"(k8));
   for (int d = d_begin + dsub; d < d_end; d += DS) {
     const int e0 = __ldg(a.dem_off + d), k = __ldg(a.dem_off + d + 1) - e0;  // uniform over the CTA
     bool any = false;
@@ -303,14 +306,21 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
             const uint32_t ra = s_rank2[((size_t)s * 2 * cw + 2 * w) * TN + tid];
             const uint32_t rb = s_rank2[((size_t)s * 2 * cw + 2 * w + 1) * TN + tid];
             const uint32_t cb4 = ct[w];
+            // The kernel is bound by the integer ALU pipe (PRMT/SHF/LOP3/VIMNMX); the FMA pipe is nearly
+            // idle.  Field extraction is therefore done with multiplies (IMAD / IMAD.HI run on the FMA
+            // pipe): x >> 16 == mulhi(x, 2^16), x & 0xffff == x - (x >> 16) * 2^16, x >> 24 == mulhi(x, 2^8).
+            // The constants come from asm so the compiler cannot turn them back into shifts.
+            const uint32_t ah = __umulhi(ra, k16), bh = __umulhi(rb, k16);
+            const uint32_t rk4[4] = {ra - ah * k16, ah, rb - bh * k16, bh};
+            const int cb3 = (int)__umulhi(cb4, k8);
+            const int cb2 = (int)__umulhi(cb4 * k8, k8);  // (x << 8) >> 24
             uint32_t key[4];
 #pragma unroll
             for (int b = 0; b < 4; ++b) {
-              const int cb = (int)__byte_perm(cb4, 0u, 0x4440u | (uint32_t)b);
-              const uint32_t rw = (b < 2) ? ra : rb;
-              const uint32_t rk = (b & 1) ? (rw >> 16) : (rw & 0xffffu);  // rank << 8 | 255-index, 0 if not applicable
+              const int cb = (b == 3) ? cb3 : (b == 2) ? cb2 : (int)__byte_perm(cb4, 0u, 0x4440u | (uint32_t)b);
+              const uint32_t rk = rk4[b];  // rank << 8 | 255-index, 0 if not applicable
               const int prov = min(__viaddmin_s32_relu(cb, ncur, needed), (int)rk);
-              key[b] = (uint32_t)prov * 65536u + rk;
+              key[b] = (uint32_t)prov * k16 + rk;
             }
             best = __vimax3_u32(best, key[0], key[1]);
             best = __vimax3_u32(best, key[2], key[3]);
