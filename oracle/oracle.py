@@ -70,11 +70,11 @@ class Oracle:
     """One oracle context: MIG vocabulary + model tables, MPS size vocabulary."""
 
     def __init__(self, tables: Dict[str, List[Dict[str, int]]], extra_mig_profiles: Iterable[str] = (),
-                 mps_sizes: Iterable[int] = ()):
+                 mps_sizes: Iterable[int] = (), builtin_profiles: bool = True):
         L = lib()
         self.L = L
         self.h = C.c_void_p(L.orc_new())
-        names = set(BUILTIN_MIG_PROFILES) | set(extra_mig_profiles)
+        names = (set(BUILTIN_MIG_PROFILES) if builtin_profiles else set()) | set(extra_mig_profiles)
         for geoms in tables.values():
             for g in geoms:
                 names |= set(g.keys())
