@@ -53,3 +53,29 @@ def test_product_does_not_touch_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp", ".cpp", "Makefile")):
                 txt = open(os.path.join(dirpath, f)).read()
                 assert not pat.search(txt), f"{f} imports/links the oracle"
+
+
+def _build_c_client():
+    import subprocess
+
+    import walkai_nos_b200 as pkg
+    pkg.build_library()
+    libdir = os.path.dirname(pkg.library_path())
+    exe = os.path.join(ROOT, "tests", "abi_client.bin")
+    subprocess.check_call(["gcc", "-std=c11", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "tests", "abi_client.c"), "-o", exe, "-L", libdir, "-lnosplan", "-lnoshost",
+                           "-Wl,-rpath," + libdir, "-L/usr/local/cuda/lib64", "-Wl,-rpath,/usr/local/cuda/lib64"])
+    return exe
+
+
+def test_plain_c_client_links_and_fails_loudly_without_gpu():
+    import subprocess
+    exe = _build_c_client()
+    assert subprocess.call([exe]) == 0
+
+
+@pytest.mark.gpu
+def test_plain_c_client_plans_on_gpu():
+    import subprocess
+    exe = _build_c_client()
+    assert subprocess.call([exe, "gpu"]) == 0

@@ -664,12 +664,17 @@ template <int TN>
 __global__ void __launch_bounds__(TN) mps_score_kernel(const MpsScoreArgs a) {
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ int s_sz[kMaxSizes];
+  __shared__ uint32_t s_inv[kMaxSizes];  // per size: multiplier of the exact multiply-high division
   const int tid = threadIdx.x;
   const int nw = (a.S + 3) >> 2;
   uint32_t* s_free = reinterpret_cast<uint32_t*>(smem);       // [gs][nw][TN]
   uint32_t* s_mask = s_free + (size_t)a.gs * nw * TN;          // [gs][TN]
   uint32_t* s_spare = s_mask + (size_t)a.gs * TN;              // [gs][TN]
-  if (tid < kMaxSizes) s_sz[tid] = tid < a.S ? a.sizes[tid] : 1;
+  if (tid < kMaxSizes) {
+    const int m = tid < a.S ? a.sizes[tid] : 1;
+    s_sz[tid] = m;
+    s_inv[tid] = m == 1 ? 0u : 0xFFFFFFFFu / (uint32_t)m + 1u;
+  }
   __syncthreads();
   const int n = blockIdx.x * TN + tid;
   const bool live = n < a.N && a.valid[n];
@@ -699,7 +704,7 @@ __global__ void __launch_bounds__(TN) mps_score_kernel(const MpsScoreArgs a) {
       const int sid = __ldg(a.dem_key + e0);
       int resid = max(__ldg(a.dem_qty + e0), 0);
       const int m = s_sz[sid];
-      const uint32_t inv = m == 1 ? 0u : 0xFFFFFFFFu / (uint32_t)m + 1u;
+      const uint32_t inv = s_inv[sid];
       const int wi = sid >> 2, sh = (sid & 3) * 8;
       if (live) {
         for (int s = 0; s < cnt && resid > 0; ++s) {
