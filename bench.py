@@ -231,6 +231,14 @@ def main():
     value = (ev_m + ev_p) / (ms_per_step * 1e-3)
 
     # ---- end to end through the C ABI with host buffers (snapshot + pods in, winners out) -----------------
+    # the step's inputs live in pinned host memory (numpy views of pinned torch tensors)
+    pin = lambda x: torch.from_numpy(np.ascontiguousarray(x)).pin_memory().numpy()
+    if mig is not None:
+        mig = {k: (pin(v) if isinstance(v, np.ndarray) else v) for k, v in mig.items()}
+    if mps is not None:
+        mps = {k: (pin(v) if isinstance(v, np.ndarray) else v) for k, v in mps.items()}
+    mo, mk, mq, po, pk, pq = (pin(x) for x in (mo, mk, mq, po, pk, pq))
+
     def step_e2e():
         if mig is not None:
             planner.set_mig_snapshot(mig)

@@ -133,22 +133,25 @@ class Planner:
         self.P = len(profile_names)
 
     def set_mig_snapshot(self, snap: Dict[str, np.ndarray]):
-        s = {k: (np.ascontiguousarray(v) if isinstance(v, np.ndarray) else v) for k, v in snap.items()}
-        self._ck(self.L.nosplan_set_mig_snapshot(self.h, int(s["n_nodes"]), _p(s["gpu_off"].astype(np.int32), i32p),
-                                                 _p(s["valid"].astype(np.uint8), u8p), _p(s["model"].astype(np.int32), i32p),
-                                                 _p(s["used"].astype(np.int32), i32p), _p(s["free"].astype(np.int32), i32p)))
+        # ascontiguousarray does not copy when dtype and layout already match (pinned buffers stay pinned)
+        a = lambda k, t: np.ascontiguousarray(snap[k], t)
+        s = dict(n_nodes=snap["n_nodes"], gpu_off=a("gpu_off", np.int32), valid=a("valid", np.uint8),
+                 model=a("model", np.int32), used=a("used", np.int32), free=a("free", np.int32))
+        self._ck(self.L.nosplan_set_mig_snapshot(self.h, int(s["n_nodes"]), _p(s["gpu_off"], i32p), _p(s["valid"], u8p),
+                                                 _p(s["model"], i32p), _p(s["used"], i32p), _p(s["free"], i32p)))
         self.mig = dict(n_nodes=int(s["n_nodes"]), tg=int(s["gpu_off"][int(s["n_nodes"])]),
                         gs=int(np.max(np.diff(s["gpu_off"]))) if int(s["n_nodes"]) else 0)
         self.mig["gs"] = max(self.mig["gs"], 1)
 
     def set_mps_snapshot(self, sizes_gb: Sequence[int], snap: Dict[str, np.ndarray], with_mask: bool = True):
-        s = {k: (np.ascontiguousarray(v) if isinstance(v, np.ndarray) else v) for k, v in snap.items()}
+        a = lambda k, t: np.ascontiguousarray(snap[k], t)
+        s = dict(n_nodes=snap["n_nodes"], gpu_off=a("gpu_off", np.int32), valid=a("valid", np.uint8),
+                 mem_gb=a("mem_gb", np.int32), used=a("used", np.int32), free=a("free", np.int32))
         sizes = np.ascontiguousarray(sizes_gb, np.int32)
-        fm = s["free_mask"].astype(np.uint32) if (with_mask and "free_mask" in s) else None
+        fm = a("free_mask", np.uint32) if (with_mask and "free_mask" in snap) else None
         self._ck(self.L.nosplan_set_mps_snapshot(self.h, len(sizes), _p(sizes, i32p), int(s["n_nodes"]),
-                                                 _p(s["gpu_off"].astype(np.int32), i32p), _p(s["valid"].astype(np.uint8), u8p),
-                                                 _p(s["mem_gb"].astype(np.int32), i32p), _p(s["used"].astype(np.int32), i32p),
-                                                 _p(s["free"].astype(np.int32), i32p), _p(fm, u32p)))
+                                                 _p(s["gpu_off"], i32p), _p(s["valid"], u8p), _p(s["mem_gb"], i32p),
+                                                 _p(s["used"], i32p), _p(s["free"], i32p), _p(fm, u32p)))
         self.S = len(sizes)
         self.mps = dict(n_nodes=int(s["n_nodes"]), tg=int(s["gpu_off"][int(s["n_nodes"])]))
 
