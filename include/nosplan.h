@@ -83,7 +83,11 @@ int nosplan_set_mig_tables(nosplan_t* h, int n_profiles, const char* const* prof
 /* Replaces, per node, mig.NewNode/extractGPUs (pkg/gpu/mig/node.go:40-100) once the Go side has
  * parsed labels and annotations: the snapshot is the flattened []mig.Node.
  *   model[total_gpus]               index into the model table (per GPU: tests build mixed nodes)
- *   used/free_[total_gpus][n_profiles]  usedMigDevices / freeMigDevices (gpu.go:29-35), >= 0 */
+ *   used/free_[total_gpus][n_profiles]  usedMigDevices / freeMigDevices (gpu.go:29-35), >= 0
+ * The arrays are uploaded as they are and range-checked on the device while they are packed; the
+ * error reported is the first bad entry in GPU order (model before counts).  Rows of invalid nodes
+ * are not interpreted.  A rejected snapshot leaves the handle without one (the same holds for
+ * nosplan_set_mps_snapshot). */
 int nosplan_set_mig_snapshot(nosplan_t* h, int n_nodes, const int32_t* gpu_off, const uint8_t* valid,
                              const int32_t* model, const int32_t* used, const int32_t* free_);
 

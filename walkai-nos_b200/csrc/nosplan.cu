@@ -78,6 +78,7 @@ struct nosplan {
   DevBuf d_dem[3];   // demand CSR
   DevBuf d_out[6];   // outputs
   DevBuf d_plan[32];
+  DevBuf d_status;
 };
 
 namespace {
@@ -123,6 +124,19 @@ bool mig_name_valid(const std::string& s) {
 int upload(nosplan_t* h, DevBuf& b, const void* src, size_t bytes, cudaStream_t st) {
   CU(b.reserve(bytes));
   if (bytes && src) CU(cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, st));
+  return NOSPLAN_OK;
+}
+
+// status words of the pack kernels: [0] lowest failing code (~0 = clean), [1] evaluations per demand row
+int status_reset(nosplan_t* h, cudaStream_t st) {
+  CU(h->d_status.reserve(16));
+  CU(cudaMemsetAsync(h->d_status.p, 0xff, 8, st));
+  CU(cudaMemsetAsync(static_cast<char*>(h->d_status.p) + 8, 0, 8, st));
+  return NOSPLAN_OK;
+}
+int status_fetch(nosplan_t* h, cudaStream_t st, unsigned long long out[2]) {
+  CU(cudaMemcpyAsync(out, h->d_status.p, 16, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
   return NOSPLAN_OK;
 }
 
@@ -284,7 +298,7 @@ void nosplan_destroy(nosplan_t* h) {
   DevBuf* all[] = {&h->d_tables, &h->d_mig_off, &h->d_mig_valid, &h->d_mig_model, &h->d_mig_used0, &h->d_mig_free0,
                    &h->d_mig_used, &h->d_mig_free, &h->d_mig_sused, &h->d_mig_sfree, &h->d_mig_smodel, &h->d_mig_scnt,
                    &h->d_mps_sizes, &h->d_mps_off, &h->d_mps_valid, &h->d_mps_gpu0, &h->d_mps_ulo0, &h->d_mps_uhi0,
-                   &h->d_mps_gpu, &h->d_mps_ulo, &h->d_mps_uhi, &h->d_mig_gnode, &h->d_mps_gnode, &h->d_mig_gslot, &h->d_mps_gslot};
+                   &h->d_mps_gpu, &h->d_mps_ulo, &h->d_mps_uhi, &h->d_mig_gnode, &h->d_mps_gnode, &h->d_mig_gslot, &h->d_mps_gslot, &h->d_status};
   for (DevBuf* b : all) b->release();
   for (auto& b : h->d_in) b.release();
   for (auto& b : h->d_dem) b.release();
@@ -382,7 +396,6 @@ int nosplan_set_mig_snapshot(nosplan_t* h, int n_nodes, const int32_t* gpu_off, 
   const int P = h->P;
   if (gpu_off[0] != 0) return fail(h, NOSPLAN_ERR_ARG, "gpu_off[0] must be 0");
   int gs = 0;
-  int64_t evals = 0;
   for (int n = 0; n < n_nodes; ++n) {
     int c = gpu_off[n + 1] - gpu_off[n];
     if (c < 0) return fail(h, NOSPLAN_ERR_ARG, "gpu_off not ascending at node %d", n);
@@ -391,55 +404,24 @@ int nosplan_set_mig_snapshot(nosplan_t* h, int n_nodes, const int32_t* gpu_off, 
   }
   const int tg = gpu_off[n_nodes];
   if (tg > 0 && (!model || !used || !free_)) return fail(h, NOSPLAN_ERR_ARG, "null state arrays");
-  std::vector<uint8_t> v(std::max(n_nodes, 1), 1);
-  if (valid) std::copy(valid, valid + n_nodes, v.begin());
-  // rows of invalid nodes are not interpreted (the controller never builds those nodes): they are
-  // replaced by zeros on the device and read back as zeros
-  std::vector<int32_t> zu, zf;
-  bool any_invalid = false;
-  for (int n = 0; n < n_nodes; ++n) any_invalid |= !v[n] && gpu_off[n + 1] > gpu_off[n];
-  if (any_invalid) {
-    zu.assign(used, used + (size_t)tg * P);
-    zf.assign(free_, free_ + (size_t)tg * P);
-    for (int n = 0; n < n_nodes; ++n)
-      if (!v[n])
-        for (size_t i = (size_t)gpu_off[n] * P; i < (size_t)gpu_off[n + 1] * P; ++i) zu[i] = zf[i] = 0;
-    used = zu.data();
-    free_ = zf.data();
-  }
-  for (int n = 0; n < n_nodes; ++n)
-    for (int g = gpu_off[n]; g < gpu_off[n + 1]; ++g) {
-      if (!v[n]) continue;
-      if (model[g] < 0 || model[g] >= h->h_tables.n_models)
-        return fail(h, NOSPLAN_ERR_RANGE, "GPU %d: model %d unknown (mark the node invalid instead)", g, model[g]);
-      evals += h->h_tables.geom_off[model[g] + 1] - h->h_tables.geom_off[model[g]];
-      for (int p = 0; p < P; ++p) {
-        int u = used[(size_t)g * P + p], f = free_[(size_t)g * P + p];
-        if (u < 0 || f < 0 || u + f > NOSPLAN_MAX_COUNT)
-          return fail(h, NOSPLAN_ERR_RANGE, "GPU %d profile %s: used %d free %d out of range [0,%d]", g, h->names[p].c_str(), u, f, NOSPLAN_MAX_COUNT);
-      }
-    }
   int rc = bind(h);
   if (rc) return rc;
   const int npad = std::max(32, (n_nodes + 31) / 32 * 32);
-  // an invalid node's GPUs may carry an unknown model: clamp for the packed copy (never read)
-  std::vector<int32_t> mdl(std::max(tg, 1), 0);
-  for (int n = 0; n < n_nodes; ++n)
-    for (int g = gpu_off[n]; g < gpu_off[n + 1]; ++g) mdl[g] = v[n] ? model[g] : 0;
-  std::vector<int32_t> gnode(std::max(tg, 1), -1), gslot(std::max(tg, 1), 0);
-  for (int n = 0; n < n_nodes; ++n)
-    for (int g = gpu_off[n]; g < gpu_off[n + 1]; ++g) {
-      gnode[g] = v[n] ? n : -1;
-      gslot[g] = g - gpu_off[n];
-    }
-  if ((rc = upload(h, h->d_mig_gnode, gnode.data(), sizeof(int32_t) * gnode.size(), h->stream))) return rc;
-  if ((rc = upload(h, h->d_mig_gslot, gslot.data(), sizeof(int32_t) * gslot.size(), h->stream))) return rc;
+  const int gsl = std::max(gs, 1);
+  // the arrays go up as they are; range checks, the zeroing of invalid nodes' rows and the per-GPU
+  // node/slot tables are the pack kernel's work (the host only walked gpu_off)
   if ((rc = upload(h, h->d_mig_off, gpu_off, sizeof(int32_t) * (n_nodes + 1), h->stream))) return rc;
-  if ((rc = upload(h, h->d_mig_valid, v.data(), std::max(n_nodes, 1), h->stream))) return rc;
-  if ((rc = upload(h, h->d_in[0], mdl.data(), sizeof(int32_t) * std::max(tg, 1), h->stream))) return rc;
+  CU(h->d_mig_valid.reserve(std::max(n_nodes, 1)));
+  if (valid) {
+    if ((rc = upload(h, h->d_mig_valid, valid, n_nodes, h->stream))) return rc;
+  } else {
+    CU(cudaMemsetAsync(h->d_mig_valid.p, 1, std::max(n_nodes, 1), h->stream));
+  }
+  if ((rc = upload(h, h->d_in[0], model, sizeof(int32_t) * (size_t)tg, h->stream))) return rc;
   if ((rc = upload(h, h->d_in[1], used, sizeof(int32_t) * (size_t)tg * P, h->stream))) return rc;
   if ((rc = upload(h, h->d_in[2], free_, sizeof(int32_t) * (size_t)tg * P, h->stream))) return rc;
-  const int gsl = std::max(gs, 1);
+  CU(h->d_mig_gnode.reserve(sizeof(int32_t) * std::max(tg, 1)));
+  CU(h->d_mig_gslot.reserve(sizeof(int32_t) * std::max(tg, 1)));
   CU(h->d_mig_model.reserve(std::max(tg, 1)));
   CU(h->d_mig_used0.reserve(sizeof(uint4) * std::max(tg, 1)));
   CU(h->d_mig_free0.reserve(sizeof(uint4) * std::max(tg, 1)));
@@ -449,15 +431,27 @@ int nosplan_set_mig_snapshot(nosplan_t* h, int n_nodes, const int32_t* gpu_off, 
   CU(h->d_mig_sfree.reserve(sizeof(uint4) * (size_t)gsl * npad));
   CU(h->d_mig_smodel.reserve((size_t)gsl * npad));
   CU(h->d_mig_scnt.reserve(npad));
+  if ((rc = status_reset(h, h->stream))) return rc;
+  h->have_mig = false;  // the device copy is being replaced: a failed call leaves no snapshot behind
   mig_pack_kernel<<<(npad + 127) / 128, 128, 0, h->stream>>>(
-      n_nodes, P, gs, npad, h->d_mig_off.as<int32_t>(), h->d_mig_valid.as<uint8_t>(), h->d_in[0].as<int32_t>(),
-      h->d_in[1].as<int32_t>(), h->d_in[2].as<int32_t>(), h->d_mig_used0.as<uint4>(), h->d_mig_free0.as<uint4>(),
-      h->d_mig_model.as<uint8_t>(), h->d_mig_sused.as<uint4>(), h->d_mig_sfree.as<uint4>(), h->d_mig_smodel.as<uint8_t>(),
-      h->d_mig_scnt.as<uint8_t>());
+      n_nodes, P, gs, npad, NOSPLAN_MAX_COUNT, h->d_tables.as<MigTables>(), h->d_mig_off.as<int32_t>(),
+      h->d_mig_valid.as<uint8_t>(), h->d_in[0].as<int32_t>(), h->d_in[1].as<int32_t>(), h->d_in[2].as<int32_t>(),
+      h->d_mig_used0.as<uint4>(), h->d_mig_free0.as<uint4>(), h->d_mig_model.as<uint8_t>(), h->d_mig_sused.as<uint4>(),
+      h->d_mig_sfree.as<uint4>(), h->d_mig_smodel.as<uint8_t>(), h->d_mig_scnt.as<uint8_t>(), h->d_mig_gnode.as<int32_t>(),
+      h->d_mig_gslot.as<int32_t>(), h->d_status.as<unsigned long long>());
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(h->d_mig_used.p, h->d_mig_used0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, h->stream));
   CU(cudaMemcpyAsync(h->d_mig_free.p, h->d_mig_free0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, h->stream));
-  CU(cudaStreamSynchronize(h->stream));
+  unsigned long long st[2];
+  if ((rc = status_fetch(h, h->stream, st))) return rc;
+  if (st[0] != ~0ull) {  // first bad entry in GPU order, reported as the host walk used to
+    const int g = (int)(st[0] / 64), sub = (int)(st[0] % 64);
+    if (sub == 0) return fail(h, NOSPLAN_ERR_RANGE, "GPU %d: model %d unknown (mark the node invalid instead)", g, model[g]);
+    const int p = sub - 1;
+    return fail(h, NOSPLAN_ERR_RANGE, "GPU %d profile %s: used %d free %d out of range [0,%d]", g, h->names[p].c_str(),
+                used[(size_t)g * P + p], free_[(size_t)g * P + p], NOSPLAN_MAX_COUNT);
+  }
+  const int64_t evals = (int64_t)st[1];
   h->mig_n = n_nodes;
   h->mig_tg = tg;
   h->mig_gs = gsl;
@@ -491,76 +485,60 @@ int nosplan_set_mps_snapshot(nosplan_t* h, int n_sizes, const int32_t* sizes_gb,
   const int tg = gpu_off[n_nodes];
   const int S = n_sizes;
   if (tg > 0 && (!mem_gb || !used || !free_)) return fail(h, NOSPLAN_ERR_ARG, "null state arrays");
-  std::vector<uint8_t> v(std::max(n_nodes, 1), 1);
-  if (valid) std::copy(valid, valid + n_nodes, v.begin());
-  int64_t evals = 0;
-  std::vector<int32_t> zu, zf, zm;
-  bool any_invalid = false;
-  for (int n = 0; n < n_nodes; ++n) any_invalid |= !v[n] && gpu_off[n + 1] > gpu_off[n];
-  if (any_invalid) {  // rows of invalid nodes are not interpreted; zeros on the device
-    zu.assign(used, used + (size_t)tg * S);
-    zf.assign(free_, free_ + (size_t)tg * S);
-    zm.assign(mem_gb, mem_gb + tg);
-    for (int n = 0; n < n_nodes; ++n)
-      if (!v[n]) {
-        for (size_t i = (size_t)gpu_off[n] * S; i < (size_t)gpu_off[n + 1] * S; ++i) zu[i] = zf[i] = 0;
-        for (int g = gpu_off[n]; g < gpu_off[n + 1]; ++g) zm[g] = 0;
-      }
-    used = zu.data();
-    free_ = zf.data();
-    mem_gb = zm.data();
-  }
-  for (int n = 0; n < n_nodes; ++n)
-    for (int g = gpu_off[n]; g < gpu_off[n + 1]; ++g) {
-      if (!v[n]) continue;
-      evals++;
-      if (mem_gb[g] < 0 || mem_gb[g] > NOSPLAN_MAX_MEM_GB) return fail(h, NOSPLAN_ERR_RANGE, "GPU %d: memory %d GB out of range", g, mem_gb[g]);
-      int64_t tot = 0;
-      for (int s = 0; s < S; ++s) {
-        int u = used[(size_t)g * S + s], f = free_[(size_t)g * S + s];
-        if (u < 0 || f < 0 || u + f > NOSPLAN_MAX_COUNT)
-          return fail(h, NOSPLAN_ERR_RANGE, "GPU %d size %dgb: used %d free %d out of range", g, sizes_gb[s], u, f);
-        if (free_mask && f > 0 && !((free_mask[g] >> s) & 1u) && v[n])
-          return fail(h, NOSPLAN_ERR_ARG, "GPU %d: free_mask misses a key with a non-zero value", g);
-        tot += (int64_t)sizes_gb[s] * (u + f);
-      }
-      // slicing.NewGPU rejects such a GPU (slicing/gpu.go:92-95): its node must be marked invalid
-      if (tot > mem_gb[g]) return fail(h, NOSPLAN_ERR_RANGE, "GPU %d: slices total %lld GB exceed memory %d GB", g, (long long)tot, mem_gb[g]);
-    }
   int rc = bind(h);
   if (rc) return rc;
-  std::vector<int32_t> gnode(std::max(tg, 1), -1), gslot(std::max(tg, 1), 0);
-  for (int n = 0; n < n_nodes; ++n)
-    for (int g = gpu_off[n]; g < gpu_off[n + 1]; ++g) {
-      gnode[g] = v[n] ? n : -1;
-      gslot[g] = g - gpu_off[n];
-    }
-  if ((rc = upload(h, h->d_mps_gnode, gnode.data(), sizeof(int32_t) * gnode.size(), h->stream))) return rc;
-  if ((rc = upload(h, h->d_mps_gslot, gslot.data(), sizeof(int32_t) * gslot.size(), h->stream))) return rc;
   if ((rc = upload(h, h->d_mps_sizes, sizes_gb, sizeof(int32_t) * S, h->stream))) return rc;
   if ((rc = upload(h, h->d_mps_off, gpu_off, sizeof(int32_t) * (n_nodes + 1), h->stream))) return rc;
-  if ((rc = upload(h, h->d_mps_valid, v.data(), std::max(n_nodes, 1), h->stream))) return rc;
-  if ((rc = upload(h, h->d_in[0], mem_gb, sizeof(int32_t) * std::max(tg, 0), h->stream))) return rc;
+  CU(h->d_mps_valid.reserve(std::max(n_nodes, 1)));
+  if (valid) {
+    if ((rc = upload(h, h->d_mps_valid, valid, n_nodes, h->stream))) return rc;
+  } else {
+    CU(cudaMemsetAsync(h->d_mps_valid.p, 1, std::max(n_nodes, 1), h->stream));
+  }
+  if ((rc = upload(h, h->d_in[0], mem_gb, sizeof(int32_t) * (size_t)tg, h->stream))) return rc;
   if ((rc = upload(h, h->d_in[1], used, sizeof(int32_t) * (size_t)tg * S, h->stream))) return rc;
   if ((rc = upload(h, h->d_in[2], free_, sizeof(int32_t) * (size_t)tg * S, h->stream))) return rc;
-  if (free_mask && (rc = upload(h, h->d_in[3], free_mask, sizeof(uint32_t) * std::max(tg, 0), h->stream))) return rc;
+  if (free_mask && (rc = upload(h, h->d_in[3], free_mask, sizeof(uint32_t) * (size_t)tg, h->stream))) return rc;
+  CU(h->d_mps_gnode.reserve(sizeof(int32_t) * std::max(tg, 1)));
+  CU(h->d_mps_gslot.reserve(sizeof(int32_t) * std::max(tg, 1)));
   CU(h->d_mps_gpu0.reserve(sizeof(MpsGpu) * std::max(tg, 1)));
   CU(h->d_mps_ulo0.reserve(sizeof(uint4) * std::max(tg, 1)));
   CU(h->d_mps_uhi0.reserve(sizeof(uint4) * std::max(tg, 1)));
   CU(h->d_mps_gpu.reserve(sizeof(MpsGpu) * std::max(tg, 1)));
   CU(h->d_mps_ulo.reserve(sizeof(uint4) * std::max(tg, 1)));
   CU(h->d_mps_uhi.reserve(sizeof(uint4) * std::max(tg, 1)));
-  if (tg > 0) {
-    mps_pack_kernel<<<(tg + 127) / 128, 128, 0, h->stream>>>(
-        n_nodes, S, h->d_mps_sizes.as<int32_t>(), h->d_mps_off.as<int32_t>(), h->d_in[0].as<int32_t>(),
-        h->d_in[1].as<int32_t>(), h->d_in[2].as<int32_t>(), free_mask ? h->d_in[3].as<uint32_t>() : nullptr,
-        h->d_mps_gpu0.as<MpsGpu>(), h->d_mps_ulo0.as<uint4>(), h->d_mps_uhi0.as<uint4>());
+  if ((rc = status_reset(h, h->stream))) return rc;
+  h->have_mps = false;  // a failed call leaves no snapshot behind
+  if (n_nodes > 0) {
+    mps_pack_kernel<<<(n_nodes + 127) / 128, 128, 0, h->stream>>>(
+        n_nodes, S, NOSPLAN_MAX_COUNT, NOSPLAN_MAX_MEM_GB, h->d_mps_sizes.as<int32_t>(), h->d_mps_off.as<int32_t>(),
+        h->d_mps_valid.as<uint8_t>(), h->d_in[0].as<int32_t>(), h->d_in[1].as<int32_t>(), h->d_in[2].as<int32_t>(),
+        free_mask ? h->d_in[3].as<uint32_t>() : nullptr, h->d_mps_gpu0.as<MpsGpu>(), h->d_mps_ulo0.as<uint4>(),
+        h->d_mps_uhi0.as<uint4>(), h->d_mps_gnode.as<int32_t>(), h->d_mps_gslot.as<int32_t>(),
+        h->d_status.as<unsigned long long>());
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(h->d_mps_gpu.p, h->d_mps_gpu0.p, sizeof(MpsGpu) * tg, cudaMemcpyDeviceToDevice, h->stream));
     CU(cudaMemcpyAsync(h->d_mps_ulo.p, h->d_mps_ulo0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, h->stream));
     CU(cudaMemcpyAsync(h->d_mps_uhi.p, h->d_mps_uhi0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, h->stream));
   }
-  CU(cudaStreamSynchronize(h->stream));
+  unsigned long long st[2];
+  if ((rc = status_fetch(h, h->stream, st))) return rc;
+  if (st[0] != ~0ull) {
+    const int g = (int)(st[0] / 128), sub = (int)(st[0] % 128);
+    if (sub == 0) return fail(h, NOSPLAN_ERR_RANGE, "GPU %d: memory %d GB out of range", g, mem_gb[g]);
+    if (sub == 127) {
+      long long tot = 0;
+      for (int s = 0; s < S; ++s) tot += (long long)sizes_gb[s] * ((long long)used[(size_t)g * S + s] + free_[(size_t)g * S + s]);
+      // slicing.NewGPU rejects such a GPU (slicing/gpu.go:92-95): its node must be marked invalid
+      return fail(h, NOSPLAN_ERR_RANGE, "GPU %d: slices total %lld GB exceed memory %d GB", g, tot, mem_gb[g]);
+    }
+    const int s = (sub - 1) / 2;
+    if ((sub - 1) % 2 == 0)
+      return fail(h, NOSPLAN_ERR_RANGE, "GPU %d size %dgb: used %d free %d out of range", g, sizes_gb[s],
+                  used[(size_t)g * S + s], free_[(size_t)g * S + s]);
+    return fail(h, NOSPLAN_ERR_ARG, "GPU %d: free_mask misses a key with a non-zero value", g);
+  }
+  const int64_t evals = (int64_t)st[1];
   h->S = S;
   h->mps_n = n_nodes;
   h->mps_tg = tg;

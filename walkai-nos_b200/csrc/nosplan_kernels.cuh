@@ -126,40 +126,66 @@ __device__ inline bool mig_walk_node(const MigTables* __restrict__ T, const uint
 }
 
 // ---- pack kernels: int32 rows from the host -> byte-packed device state ------------------------------------
+// The range checks of the snapshot run here as well, so the host never walks the state arrays:
+// status[0] = lowest failing code (atomicMin; ~0 = clean), status[1] = evaluations per demand row.
+// MIG code = gpu * 64 + (0: unknown model | 1 + profile: count out of range); the host turns the
+// winning code back into the message of the first bad entry in GPU order.
+//
 // MIG: used/free [tg][P] int32 -> uint4 per GPU (AoS, CSR order) and slot-major copies for the scorer:
-// sused/sfree[slot][npad] (uint4), smodel[slot][npad] (0xff = no such GPU).
-__global__ void mig_pack_kernel(int N, int P, int gs, int npad, const int32_t* __restrict__ gpu_off,
-                                const uint8_t* __restrict__ valid, const int32_t* __restrict__ model,
-                                const int32_t* __restrict__ used, const int32_t* __restrict__ fr, uint4* __restrict__ a_used,
-                                uint4* __restrict__ a_free, uint8_t* __restrict__ a_model, uint4* __restrict__ s_used,
-                                uint4* __restrict__ s_free, uint8_t* __restrict__ s_model, uint8_t* __restrict__ s_cnt) {
+// sused/sfree[slot][npad] (uint4), smodel[slot][npad] (0xff = no such GPU); gnode/gslot per GPU.
+// Rows of invalid nodes are not interpreted (the controller never builds those nodes): zeros.
+__global__ void mig_pack_kernel(int N, int P, int gs, int npad, int max_count, const MigTables* __restrict__ T,
+                                const int32_t* __restrict__ gpu_off, const uint8_t* __restrict__ valid,
+                                const int32_t* __restrict__ model, const int32_t* __restrict__ used,
+                                const int32_t* __restrict__ fr, uint4* __restrict__ a_used, uint4* __restrict__ a_free,
+                                uint8_t* __restrict__ a_model, uint4* __restrict__ s_used, uint4* __restrict__ s_free,
+                                uint8_t* __restrict__ s_model, uint8_t* __restrict__ s_cnt, int32_t* __restrict__ gnode,
+                                int32_t* __restrict__ gslot, unsigned long long* __restrict__ status) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= npad) return;
   const int g0 = n < N ? gpu_off[n] : 0;
   const int cnt = n < N ? gpu_off[n + 1] - g0 : 0;
   const bool ok = n < N && valid[n];
   s_cnt[n] = ok ? (uint8_t)cnt : 0;  // an invalid node behaves like a node the controller skips
+  unsigned long long bad = ~0ull, evals = 0;
   for (int s = 0; s < gs; ++s) {
     uint4 u = make_uint4(0, 0, 0, 0), f = u;
     uint8_t m = 0xff;
     if (s < cnt) {
       const int g = g0 + s;
       uint32_t uw[4] = {0, 0, 0, 0}, fw[4] = {0, 0, 0, 0};
-      for (int p = 0; p < P; ++p) {
-        uw[p >> 2] |= (uint32_t)(used[(size_t)g * P + p] & 0xff) << ((p & 3) * 8);
-        fw[p >> 2] |= (uint32_t)(fr[(size_t)g * P + p] & 0xff) << ((p & 3) * 8);
+      int md = 0;
+      if (ok) {
+        md = model[g];
+        if (md < 0 || md >= T->n_models) {
+          bad = min(bad, (unsigned long long)g * 64ull);
+          md = 0;
+        } else {
+          evals += (unsigned long long)(T->geom_off[md + 1] - T->geom_off[md]);
+        }
+        for (int p = 0; p < P; ++p) {
+          const int uv = used[(size_t)g * P + p], fv = fr[(size_t)g * P + p];
+          if (uv < 0 || fv < 0 || uv > max_count || fv > max_count || uv + fv > max_count)
+            bad = min(bad, (unsigned long long)g * 64ull + 1ull + (unsigned long long)p);
+          uw[p >> 2] |= (uint32_t)(uv & 0xff) << ((p & 3) * 8);
+          fw[p >> 2] |= (uint32_t)(fv & 0xff) << ((p & 3) * 8);
+        }
       }
       u = make_uint4(uw[0], uw[1], uw[2], uw[3]);
       f = make_uint4(fw[0], fw[1], fw[2], fw[3]);
-      m = (uint8_t)model[g];
+      m = (uint8_t)md;
       a_used[g] = u;
       a_free[g] = f;
       a_model[g] = m;
+      gnode[g] = ok ? n : -1;
+      gslot[g] = s;
     }
     s_used[(size_t)s * npad + n] = u;
     s_free[(size_t)s * npad + n] = f;
     s_model[(size_t)s * npad + n] = ok ? m : (uint8_t)0xff;
   }
+  if (bad != ~0ull) atomicMin(&status[0], bad);
+  if (evals) atomicAdd(&status[1], evals);
 }
 
 __global__ void mig_unpack_kernel(int tg, int P, const uint4* __restrict__ a_used, const uint4* __restrict__ a_free,
@@ -591,31 +617,53 @@ __device__ inline bool mps_walk_node(const int* __restrict__ sz, int S, MpsGpu* 
   return any;
 }
 
-__global__ void mps_pack_kernel(int N, int S, const int32_t* __restrict__ sizes, const int32_t* __restrict__ gpu_off,
+// MPS: one thread per node walks its GPUs.  code = gpu * 128 + (0: memory out of range | 1 + 2s: count
+// of size s out of range | 2 + 2s: free_mask misses a non-zero free count | 127: slices exceed memory,
+// the GPU slicing.NewGPU rejects, slicing/gpu.go:92-95).
+__global__ void mps_pack_kernel(int N, int S, int max_count, int max_mem, const int32_t* __restrict__ sizes,
+                                const int32_t* __restrict__ gpu_off, const uint8_t* __restrict__ valid,
                                 const int32_t* __restrict__ mem, const int32_t* __restrict__ used, const int32_t* __restrict__ fr,
                                 const uint32_t* __restrict__ fmask, MpsGpu* __restrict__ gp, uint4* __restrict__ used_lo,
-                                uint4* __restrict__ used_hi) {
-  const int g = blockIdx.x * blockDim.x + threadIdx.x;
-  const int tg = gpu_off[N];
-  if (g >= tg) return;
-  uint32_t uw[8] = {0, 0, 0, 0, 0, 0, 0, 0}, fw[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  int usedtot = 0;
-  uint32_t fm = 0;
-  for (int s = 0; s < S; ++s) {
-    const int u = used[(size_t)g * S + s], f = fr[(size_t)g * S + s];
-    uw[s >> 2] |= (uint32_t)(u & 0xff) << ((s & 3) * 8);
-    fw[s >> 2] |= (uint32_t)(f & 0xff) << ((s & 3) * 8);
-    usedtot += sizes[s] * u;
-    if (fmask ? ((fmask[g] >> s) & 1u) : (f > 0)) fm |= 1u << s;
+                                uint4* __restrict__ used_hi, int32_t* __restrict__ gnode, int32_t* __restrict__ gslot,
+                                unsigned long long* __restrict__ status) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  const bool ok = valid[n] != 0;
+  unsigned long long bad = ~0ull;
+  const int g0 = gpu_off[n], g1 = gpu_off[n + 1];
+  for (int g = g0; g < g1; ++g) {
+    uint32_t uw[8] = {0, 0, 0, 0, 0, 0, 0, 0}, fw[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    long long tot = 0;
+    int usedtot = 0;
+    uint32_t fm = 0;
+    const int mg = ok ? mem[g] : 0;
+    const unsigned long long base = (unsigned long long)g * 128ull;
+    if (mg < 0 || mg > max_mem) bad = min(bad, base);
+    for (int s = 0; s < S; ++s) {
+      const int u = ok ? used[(size_t)g * S + s] : 0, f = ok ? fr[(size_t)g * S + s] : 0;
+      const bool bit = fmask ? ((fmask[g] >> s) & 1u) : (f > 0);
+      if (u < 0 || f < 0 || u > max_count || f > max_count || u + f > max_count) bad = min(bad, base + 1ull + 2ull * s);
+      else if (f > 0 && !bit) bad = min(bad, base + 2ull + 2ull * s);
+      uw[s >> 2] |= (uint32_t)(u & 0xff) << ((s & 3) * 8);
+      fw[s >> 2] |= (uint32_t)(f & 0xff) << ((s & 3) * 8);
+      usedtot += sizes[s] * u;
+      tot += (long long)sizes[s] * ((long long)u + f);
+      if (bit) fm |= 1u << s;
+    }
+    if (ok && tot > mg) bad = min(bad, base + 127ull);
+    MpsGpu G;
+    G.f0 = make_uint4(fw[0], fw[1], fw[2], fw[3]);
+    G.f1 = make_uint4(fw[4], fw[5], fw[6], fw[7]);
+    G.fmask = fm;
+    G.cap = (uint32_t)(mg - usedtot);
+    gp[g] = G;
+    used_lo[g] = make_uint4(uw[0], uw[1], uw[2], uw[3]);
+    used_hi[g] = make_uint4(uw[4], uw[5], uw[6], uw[7]);
+    gnode[g] = ok ? n : -1;
+    gslot[g] = g - g0;
   }
-  MpsGpu G;
-  G.f0 = make_uint4(fw[0], fw[1], fw[2], fw[3]);
-  G.f1 = make_uint4(fw[4], fw[5], fw[6], fw[7]);
-  G.fmask = fm;
-  G.cap = (uint32_t)(mem[g] - usedtot);
-  gp[g] = G;
-  used_lo[g] = make_uint4(uw[0], uw[1], uw[2], uw[3]);
-  used_hi[g] = make_uint4(uw[4], uw[5], uw[6], uw[7]);
+  if (bad != ~0ull) atomicMin(&status[0], bad);
+  if (ok && g1 > g0) atomicAdd(&status[1], (unsigned long long)(g1 - g0));
 }
 
 __global__ void mps_unpack_kernel(int tg, int S, const MpsGpu* __restrict__ gp, const uint4* __restrict__ used_lo,

@@ -137,6 +137,7 @@ class Planner:
         a = lambda k, t: np.ascontiguousarray(snap[k], t)
         s = dict(n_nodes=snap["n_nodes"], gpu_off=a("gpu_off", np.int32), valid=a("valid", np.uint8),
                  model=a("model", np.int32), used=a("used", np.int32), free=a("free", np.int32))
+        self.mig = None  # a rejected snapshot leaves the handle without one
         self._ck(self.L.nosplan_set_mig_snapshot(self.h, int(s["n_nodes"]), _p(s["gpu_off"], i32p), _p(s["valid"], u8p),
                                                  _p(s["model"], i32p), _p(s["used"], i32p), _p(s["free"], i32p)))
         self.mig = dict(n_nodes=int(s["n_nodes"]), tg=int(s["gpu_off"][int(s["n_nodes"])]),
@@ -149,6 +150,7 @@ class Planner:
                  mem_gb=a("mem_gb", np.int32), used=a("used", np.int32), free=a("free", np.int32))
         sizes = np.ascontiguousarray(sizes_gb, np.int32)
         fm = a("free_mask", np.uint32) if (with_mask and "free_mask" in snap) else None
+        self.mps = None
         self._ck(self.L.nosplan_set_mps_snapshot(self.h, len(sizes), _p(sizes, i32p), int(s["n_nodes"]),
                                                  _p(s["gpu_off"], i32p), _p(s["valid"], u8p), _p(s["mem_gb"], i32p),
                                                  _p(s["used"], i32p), _p(s["free"], i32p), _p(fm, u32p)))
@@ -158,6 +160,8 @@ class Planner:
     # ---- scorers -----------------------------------------------------------------------------------
     def score_mig(self, off, key, qty, want_updated=True, want_choice=True, want_first_choice=True):
         D = len(off) - 1
+        if self.mig is None:
+            raise NosplanError(-1, "no MIG snapshot")
         N, tg, gs = self.mig["n_nodes"], self.mig["tg"], self.mig["gs"]
         first = np.full(D, -2, np.int32)
         fch = np.full((D, gs), -2, np.int8) if want_first_choice else None
@@ -171,6 +175,8 @@ class Planner:
 
     def score_mps(self, off, key, qty, want_updated=True, want_free=True):
         D = len(off) - 1
+        if self.mps is None:
+            raise NosplanError(-1, "no MPS snapshot")
         N, tg = self.mps["n_nodes"], self.mps["tg"]
         first = np.full(D, -2, np.int32)
         upd = np.zeros((D, N), np.uint8) if want_updated else None
