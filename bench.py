@@ -155,6 +155,7 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # stdout carries the JSON line only
         dist.init_process_group("nccl", device_id=dev)
 
     planner = pkg.Planner(local_rank)
@@ -174,8 +175,24 @@ def main():
     t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
     d_mo, d_mk, d_mq = t(mo), t(mk), t(mq)
     d_po, d_pk, d_pq = t(po), t(pk), t(pq)
-    first_all = torch.empty(max(Dm, 1) + max(Dp, 1), dtype=torch.int32, device=dev)
+    first_all = torch.full((max(Dm, 1) + max(Dp, 1),), -1, dtype=torch.int32, device=dev)
     first_m, first_p = first_all[:max(Dm, 1)], first_all[max(Dm, 1):]
+    # N > 1: the per-row "first node" keys of all shards are merged by the library's own exchange
+    # (atomicMin into every peer's buffer over NVLink + step flags); NCCL is only the cross-check
+    first_glob = torch.empty_like(first_all)
+    exchange = "none"
+    if world > 1:
+        exchange = "peer atomicMin over NVLink (libnosplan)"
+        try:
+            pkg.dist.open_exchange(planner, first_all.numel())
+        except pkg.NosplanError as e:  # no peer mapping on this box: say so, use the library collective
+            exchange = f"nccl all-reduce (peer mapping failed: {e})"
+        flags_t = torch.tensor([0 if exchange.startswith("peer") else 1], device=dev)
+        dist.all_reduce(flags_t, op=dist.ReduceOp.MAX)
+        if int(flags_t.item()) and exchange.startswith("peer"):
+            exchange = "nccl all-reduce (a peer could not map)"
+        if exchange.startswith("peer"):
+            planner.set_node_base(mig_lo, mps_lo)  # the scorers report global node indices
     lo_vec = torch.cat([torch.full((max(Dm, 1),), mig_lo, dtype=torch.int32, device=dev),
                         torch.full((max(Dp, 1),), mps_lo, dtype=torch.int32, device=dev)])
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
@@ -194,7 +211,10 @@ def main():
             planner.score_mps_dev(Dp, d_po.data_ptr(), d_pk.data_ptr(), d_pq.data_ptr(), first_p.data_ptr(), 0, 0, 0, stream)
         if world > 1:
             # first node wins across shards: global index = local + shard offset, min over ranks
-            first_all.copy_(pkg.dist.merge_first_node_keys(first_all, lo_vec))
+            if exchange.startswith("peer"):
+                planner.exchange_min_dev(first_all.numel(), first_all.data_ptr(), first_glob.data_ptr(), stream)
+            else:
+                first_glob.copy_(pkg.dist.merge_first_node_keys(first_all, lo_vec))
         if ev:
             ev[2].record()
 
@@ -207,6 +227,12 @@ def main():
         flush.zero_()
         step_device()
     barrier()
+    if world > 1 and exchange.startswith("peer"):
+        # cross-check of the library's exchange against the NCCL all-reduce on the same keys
+        planner.exchange_status()
+        ref = pkg.dist.merge_first_node_keys(first_all, torch.zeros_like(first_all))
+        if not torch.equal(ref, first_glob):
+            raise SystemExit("bench.py: the peer-memory exchange disagrees with the NCCL all-reduce")
     sampler = ClockSampler(local_rank)
     sampler.start()
     total_ms = mig_ms = mps_ms = 0.0
@@ -244,11 +270,23 @@ def main():
             planner.set_mig_snapshot(mig)
         if mps is not None:
             planner.set_mps_snapshot(cfg["sizes"], mps)
-        out = []
+        out, keys = [], []
         if Dm:
             out.append(planner.score_mig(mo, mk, mq, want_updated=False, want_choice=False, want_first_choice=True))
+            keys.append((out[-1]["first_node"], mig_lo))
         if Dp:
             out.append(planner.score_mps(po, pk, pq, want_updated=False, want_free=False))
+            keys.append((out[-1]["first_node"], mps_lo))
+        if world > 1 and keys:
+            # the shards' winners (host arrays, local indices) -> global keys -> exchanged on the GPUs -> host
+            k = np.concatenate([np.where(f >= 0, f + lo, -1).astype(np.int32) for f, lo in keys])
+            kin = torch.from_numpy(k).to(dev)
+            kout = first_glob[:kin.numel()]
+            if exchange.startswith("peer"):
+                planner.exchange_min_dev(kin.numel(), kin.data_ptr(), kout.data_ptr(), stream)
+            else:
+                kout.copy_(pkg.dist.merge_first_node_keys(kin, torch.zeros_like(kin)))
+            out.append(kout.cpu())
         return out
     h2d = d2h = 0
     if mig is not None:
@@ -259,6 +297,9 @@ def main():
         h2d += mps["used"].nbytes + mps["free"].nbytes + mps["mem_gb"].nbytes + mps["gpu_off"].nbytes + mps["valid"].nbytes + mps["free_mask"].nbytes
         h2d += po.nbytes + pk.nbytes + pq.nbytes
         d2h += Dp * 4
+    if world > 1:
+        h2d += (Dm + Dp) * 4
+        d2h += (Dm + Dp) * 4
     for _ in range(args.warmup):
         step_e2e()
     barrier()
@@ -313,7 +354,8 @@ def main():
             "config": workload_config(cfg, args),
             "e2e": {"value": e2e_val, "unit": "evals/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "ms_per_step": float(e2e_t.item()) * 1e3},
-            "gpu_launches": int(args.steps * ((3 if Dm else 0) + (3 if Dp else 0))),
+            "gpu_launches": int(args.steps * ((3 if Dm else 0) + (3 if Dp else 0) + (2 if exchange.startswith("peer") else 0))),
+            "exchange": exchange,
             "planner_latency_ms_p50": float(np.median(lat)) if lat else None,
             "planner_latency_ms_p95": float(np.percentile(lat, 95)) if lat else None,
             "planner_latency_gate_off_ms_p50": float(np.median(lat_off)) if lat_off else None,

@@ -200,6 +200,33 @@ int nosplan_score_mig_static(nosplan_t* h, int n_nodes, int gpus_per_node, const
 int64_t nosplan_mig_evals_per_demand(const nosplan_t* h);
 int64_t nosplan_mps_evals_per_demand(const nosplan_t* h);
 
+/* ---- sharded scoring: one process per GPU, nodes split into contiguous ranges ------------- */
+/* tryRepartition walks the whole node list and commits the first node whose UpdateGeometryFor
+ * returns true (internal/controllers/gpupartitioner/mig_controller.go:146-166).  With the list split
+ * across ranks that is the minimum global node index over ranks, one exchange per scoring pass.
+ *
+ * nosplan_set_node_base: the global index of this handle's first MIG / MPS node; the _dev scorers
+ * then report first_node as a global index (-1 stays -1). */
+int nosplan_set_node_base(nosplan_t* h, int mig_first_node, int mps_first_node);
+
+/* The exchange itself, done by the library's own kernels over peer memory (NVLink): every rank folds
+ * its keys into every rank's buffer with atomicMin and signals a per-rank step flag; no library
+ * collective is involved.  Set-up (allocates; once per process group):
+ *   1. nosplan_exchange_create on every rank -> a 64-byte CUDA IPC handle of the rank's buffer
+ *   2. gather the handles of all ranks (any transport) into handles[world][64]
+ *   3. nosplan_exchange_open on every rank
+ * Per pass, on every rank, in the same order: nosplan_exchange_min_dev(n_keys, keys_in, keys_out):
+ * keys_in[d] = this rank's global node index for row d or -1; keys_out[d] = the minimum over ranks of
+ * the non-negative entries, or -1.  Device pointers; enqueued on `stream`, not synchronised; n_keys must
+ * be the same on all ranks and at most max_keys.  A rank that waits more than 2 s for a peer stops
+ * waiting and nosplan_exchange_status (synchronises) reports NOSPLAN_ERR_CUDA.  world <= 16. */
+#define NOSPLAN_IPC_HANDLE_BYTES 64
+int nosplan_exchange_create(nosplan_t* h, int rank, int world, int max_keys, unsigned char* handle_out);
+int nosplan_exchange_open(nosplan_t* h, const unsigned char* handles);
+int nosplan_exchange_min_dev(nosplan_t* h, int n_keys, const int32_t* keys_in, int32_t* keys_out, void* stream);
+int nosplan_exchange_status(nosplan_t* h);
+int nosplan_exchange_destroy(nosplan_t* h);
+
 #ifdef __cplusplus
 }
 #endif

@@ -13,6 +13,7 @@
 #include "nosplan_kernels.cuh"
 #include "nosplan_plan.cuh"
 #include "nosplan_seq.cuh"
+#include "nosplan_xchg.cuh"
 
 using namespace nsp;
 
@@ -79,6 +80,19 @@ struct nosplan {
   DevBuf d_out[6];   // outputs
   DevBuf d_plan[32];
   DevBuf d_status;
+
+  // sharded scoring (nosplan_set_node_base, nosplan_exchange_*)
+  int mig_base = 0, mps_base = 0;
+  struct {
+    bool created = false, open = false;
+    int rank = 0, world = 1, max_keys = 0;
+    void* local = nullptr;             // keys[2][max_keys] + flags[world]
+    size_t flags_off = 0;
+    void* mapped[kMaxWorld] = {};      // peers' buffers as mapped here (own slot = local)
+    XchgPeers peers;
+    uint32_t step = 0;
+    DevBuf done, err;
+  } xch;
 };
 
 namespace {
@@ -233,7 +247,7 @@ int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
 }
 
 int launch_mps_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d_key, const int32_t* d_qty,
-                     int32_t* d_first, uint8_t* d_updated, uint8_t* d_free, uint32_t* d_mask, cudaStream_t st) {
+                     int32_t* d_first, uint8_t* d_updated, uint8_t* d_free, uint32_t* d_mask, cudaStream_t st, int base = 0) {
   if (D == 0) return NOSPLAN_OK;
   fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, kNoNode);
   if (h->mps_n > 0) {
@@ -262,7 +276,7 @@ int launch_mps_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
     CU(cudaFuncSetAttribute(mps_score_kernel<kScoreTN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     mps_score_kernel<kScoreTN><<<dim3(tiles, gy), kScoreTN, smem, st>>>(a);
   }
-  nonode_to_minus1_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D);
+  nonode_to_minus1_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, base);
   CU(cudaGetLastError());
   return NOSPLAN_OK;
 }
@@ -295,6 +309,13 @@ void nosplan_destroy(nosplan_t* h) {
   if (!h) return;
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
+  if (h->xch.created) {
+    for (int r = 0; r < h->xch.world; ++r)
+      if (h->xch.open && r != h->xch.rank && h->xch.mapped[r]) cudaIpcCloseMemHandle(h->xch.mapped[r]);
+    if (h->xch.local) cudaFree(h->xch.local);
+    h->xch.done.release();
+    h->xch.err.release();
+  }
   DevBuf* all[] = {&h->d_tables, &h->d_mig_off, &h->d_mig_valid, &h->d_mig_model, &h->d_mig_used0, &h->d_mig_free0,
                    &h->d_mig_used, &h->d_mig_free, &h->d_mig_sused, &h->d_mig_sfree, &h->d_mig_smodel, &h->d_mig_scnt,
                    &h->d_mps_sizes, &h->d_mps_off, &h->d_mps_valid, &h->d_mps_gpu0, &h->d_mps_ulo0, &h->d_mps_uhi0,
@@ -563,7 +584,7 @@ int nosplan_score_mig_dev(nosplan_t* h, int n_demands, const int32_t* dem_off, c
   cudaStream_t st = (cudaStream_t)stream;
   rc = launch_mig_score(h, n_demands, dem_off, dem_key, dem_qty, first_node, updated, choice, st);
   if (rc) return rc;
-  if (n_demands > 0) nonode_to_minus1_kernel<<<(n_demands + 255) / 256, 256, 0, st>>>(first_node, n_demands);
+  if (n_demands > 0) nonode_to_minus1_kernel<<<(n_demands + 255) / 256, 256, 0, st>>>(first_node, n_demands, h->mig_base);
   CU(cudaGetLastError());
   return NOSPLAN_OK;
 }
@@ -579,7 +600,7 @@ int nosplan_score_mps_dev(nosplan_t* h, int n_demands, const int32_t* dem_off, c
   int rc = bind(h);
   if (rc) return rc;
   return launch_mps_score(h, n_demands, dem_off, dem_key, dem_qty, first_node, updated, out_free, out_free_mask,
-                          (cudaStream_t)stream);
+                          (cudaStream_t)stream, h->mps_base);
 }
 
 int nosplan_score_mig(nosplan_t* h, int n_demands, const int32_t* dem_off, const int32_t* dem_key,
@@ -1138,7 +1159,7 @@ extern "C" int nosplan_score_mig_static(nosplan_t* h, int n_nodes, int gpus_per_
     if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MIG scorer tile needs %zu bytes of shared memory", smem);
     if ((rc = launch_mig_score_kernel(h, a, dim3(tiles, gy), smem, st))) return rc;  // sets a smem limit, allocates nothing
   }
-  nonode_to_minus1_kernel<<<(D + 255) / 256, 256, 0, st>>>(first_node, D);
+  nonode_to_minus1_kernel<<<(D + 255) / 256, 256, 0, st>>>(first_node, D, 0);
   CU(cudaGetLastError());
   return NOSPLAN_OK;
 }
@@ -1217,4 +1238,127 @@ extern "C" int nosplan_diff_plan_mig(nosplan_t* h, int n_gpus, int n_profiles, c
   CU(cudaMemcpyAsync(del_used, h->d_out[2].p, bytes, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
   return NOSPLAN_OK;
+}
+
+// ---- sharded scoring: node base + the first-node exchange over peer memory (nosplan_xchg.cuh) ---------------
+namespace {
+int xchg_release(nosplan_t* h) {
+  auto& x = h->xch;
+  if (!x.created) return NOSPLAN_OK;
+  cudaSetDevice(h->device);
+  cudaDeviceSynchronize();
+  for (int r = 0; r < x.world; ++r)
+    if (x.open && r != x.rank && x.mapped[r]) cudaIpcCloseMemHandle(x.mapped[r]);
+  if (x.local) cudaFree(x.local);
+  x.done.release();
+  x.err.release();
+  x = {};
+  return NOSPLAN_OK;
+}
+}  // namespace
+
+extern "C" int nosplan_set_node_base(nosplan_t* h, int mig_first_node, int mps_first_node) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  if (mig_first_node < 0 || mps_first_node < 0) return fail(h, NOSPLAN_ERR_ARG, "negative node base");
+  h->mig_base = mig_first_node;
+  h->mps_base = mps_first_node;
+  return NOSPLAN_OK;
+}
+
+extern "C" int nosplan_exchange_create(nosplan_t* h, int rank, int world, int max_keys, unsigned char* handle_out) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  if (world < 1 || world > kMaxWorld || rank < 0 || rank >= world)
+    return fail(h, NOSPLAN_ERR_RANGE, "rank %d / world %d out of range (max %d ranks)", rank, world, kMaxWorld);
+  if (max_keys < 1) return fail(h, NOSPLAN_ERR_ARG, "max_keys must be positive");
+  if (!handle_out) return fail(h, NOSPLAN_ERR_ARG, "handle_out is null");
+  int rc = bind(h);
+  if (rc) return rc;
+  xchg_release(h);
+  auto& x = h->xch;
+  x.rank = rank;
+  x.world = world;
+  x.max_keys = max_keys;
+  x.flags_off = ((size_t)2 * max_keys * sizeof(int32_t) + 255) / 256 * 256;
+  const size_t bytes = x.flags_off + 256;
+  CU(cudaMalloc(&x.local, bytes));
+  x.created = true;
+  CU(x.done.reserve(sizeof(unsigned int)));
+  CU(x.err.reserve(sizeof(int)));
+  fill_i32_kernel<<<(2 * max_keys + 255) / 256, 256, 0, h->stream>>>(static_cast<int32_t*>(x.local), 2 * max_keys, kNoNode);
+  CU(cudaGetLastError());
+  CU(cudaMemsetAsync(static_cast<char*>(x.local) + x.flags_off, 0, 256, h->stream));
+  CU(cudaMemsetAsync(x.done.p, 0, sizeof(unsigned int), h->stream));
+  CU(cudaMemsetAsync(x.err.p, 0, sizeof(int), h->stream));
+  CU(cudaStreamSynchronize(h->stream));  // at rest before any peer can learn the handle
+  static_assert(sizeof(cudaIpcMemHandle_t) == NOSPLAN_IPC_HANDLE_BYTES, "IPC handle size");
+  cudaIpcMemHandle_t ipc;
+  std::memset(&ipc, 0, sizeof(ipc));
+  if (world > 1) CU(cudaIpcGetMemHandle(&ipc, x.local));
+  std::memcpy(handle_out, &ipc, sizeof(ipc));
+  return NOSPLAN_OK;
+}
+
+extern "C" int nosplan_exchange_open(nosplan_t* h, const unsigned char* handles) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  auto& x = h->xch;
+  if (!x.created) return fail(h, NOSPLAN_ERR_ARG, "nosplan_exchange_create must be called first");
+  if (x.open) return fail(h, NOSPLAN_ERR_ARG, "exchange already open");
+  if (!handles && x.world > 1) return fail(h, NOSPLAN_ERR_ARG, "handles is null");
+  int rc = bind(h);
+  if (rc) return rc;
+  for (int r = 0; r < x.world; ++r) {
+    if (r == x.rank) {
+      x.mapped[r] = x.local;
+    } else {
+      cudaIpcMemHandle_t ipc;
+      std::memcpy(&ipc, handles + (size_t)r * NOSPLAN_IPC_HANDLE_BYTES, sizeof(ipc));
+      CU(cudaIpcOpenMemHandle(&x.mapped[r], ipc, cudaIpcMemLazyEnablePeerAccess));
+    }
+    x.peers.keys[r] = static_cast<int32_t*>(x.mapped[r]);
+    x.peers.flags[r] = reinterpret_cast<uint32_t*>(static_cast<char*>(x.mapped[r]) + x.flags_off);
+  }
+  x.open = true;
+  x.step = 0;
+  return NOSPLAN_OK;
+}
+
+extern "C" int nosplan_exchange_min_dev(nosplan_t* h, int n_keys, const int32_t* keys_in, int32_t* keys_out, void* stream) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  auto& x = h->xch;
+  if (!x.open) return fail(h, NOSPLAN_ERR_ARG, "exchange is not open");
+  if (n_keys < 0 || n_keys > x.max_keys) return fail(h, NOSPLAN_ERR_RANGE, "%d keys exceed the exchange buffer (%d)", n_keys, x.max_keys);
+  if (n_keys > 0 && (!keys_in || !keys_out)) return fail(h, NOSPLAN_ERR_ARG, "null key arrays");
+  int rc = bind(h);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const uint32_t step = ++x.step;
+  const int blocks = std::max(1, std::min((n_keys + 255) / 256, h->sm_count));
+  xchg_push_kernel<<<blocks, 256, 0, st>>>(x.peers, x.world, x.rank, x.max_keys, step, n_keys, keys_in, x.done.as<unsigned int>());
+  xchg_finish_kernel<<<blocks, 256, 0, st>>>(x.peers.keys[x.rank], x.peers.flags[x.rank], x.world, x.max_keys, step, n_keys,
+                                             keys_out, 2000000000ull, x.err.as<int>());
+  CU(cudaGetLastError());
+  return NOSPLAN_OK;
+}
+
+extern "C" int nosplan_exchange_status(nosplan_t* h) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  auto& x = h->xch;
+  if (!x.created) return fail(h, NOSPLAN_ERR_ARG, "no exchange");
+  int rc = bind(h);
+  if (rc) return rc;
+  int e = 0;
+  CU(cudaMemcpy(&e, x.err.p, sizeof(int), cudaMemcpyDeviceToHost));
+  if (e) return fail(h, NOSPLAN_ERR_CUDA, "exchange: rank %d never signalled a step (waited 2 s)", e - 1);
+  return NOSPLAN_OK;
+}
+
+extern "C" int nosplan_exchange_destroy(nosplan_t* h) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  return xchg_release(h);
 }

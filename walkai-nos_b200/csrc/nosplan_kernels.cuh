@@ -440,9 +440,12 @@ __global__ void fill_i32_kernel(int32_t* p, int n, int32_t v) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) p[i] = v;
 }
-__global__ void nonode_to_minus1_kernel(int32_t* p, int n) {
+// kNoNode -> -1; a winner gets the shard's first global node index added (0 unless sharded)
+__global__ void nonode_to_minus1_kernel(int32_t* p, int n, int base) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n && p[i] == kNoNode) p[i] = -1;
+  if (i >= n) return;
+  const int v = p[i];
+  p[i] = v == kNoNode ? -1 : v + base;
 }
 
 // GPU.InitGeometry over every GPU (gpu.go:120-129): apply the model's fewest-kinds geometry unless a

@@ -50,3 +50,21 @@ def merge_first_node_keys(first_local, lo_vec, group=None):
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(key, op=dist.ReduceOp.MIN, group=group)
     return torch.where(key == NO_NODE, -1, key)
+
+
+def open_exchange(planner, max_keys: int, group=None):
+    """Sets up the library's own first-node exchange (peer-memory atomicMin over NVLink, include/nosplan.h
+    "sharded scoring"): every rank creates its buffer, the 64-byte IPC handles travel through the
+    process group once, every rank maps its peers.  After this, planner.exchange_min_dev replaces
+    merge_first_node_keys' all-reduce.  Raises NosplanError when peer mapping is not possible."""
+    import torch.distributed as dist
+    world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+    rank = dist.get_rank(group) if world > 1 else 0
+    handle = planner.exchange_create(rank, world, max_keys)
+    handles = [handle]
+    if world > 1:
+        handles = [None] * world
+        dist.all_gather_object(handles, handle, group=group)
+    planner.exchange_open(handles)
+    if world > 1:
+        dist.barrier(group=group)  # nobody pushes before everybody has mapped

@@ -26,7 +26,12 @@ EXPORTS = [
     "nosplan_set_mig_snapshot", "nosplan_set_mps_snapshot", "nosplan_score_mig", "nosplan_score_mps", "nosplan_plan",
     "nosplan_get_mig_state", "nosplan_get_mps_state", "nosplan_init_geometry_mig", "nosplan_score_mig_dev",
     "nosplan_score_mps_dev", "nosplan_mig_evals_per_demand", "nosplan_mps_evals_per_demand", "nosplan_score_mig_static", "nosplan_diff_plan_mig",
+    "nosplan_set_node_base", "nosplan_exchange_create", "nosplan_exchange_open", "nosplan_exchange_min_dev",
+    "nosplan_exchange_status", "nosplan_exchange_destroy",
 ]
+
+
+IPC_HANDLE_BYTES = 64
 
 
 class NosplanError(RuntimeError):
@@ -253,6 +258,31 @@ class Planner:
                                                  C.c_void_p(free_ptr or None), int(D), C.c_void_p(off_ptr or None),
                                                  C.c_void_p(key_ptr or None), C.c_void_p(qty_ptr or None),
                                                  C.c_void_p(first_ptr or None), C.c_void_p(stream or None)))
+
+    # ---- sharded scoring (one process per GPU) -----------------------------------------------------
+    def set_node_base(self, mig_first_node: int, mps_first_node: int):
+        self._ck(self.L.nosplan_set_node_base(self.h, int(mig_first_node), int(mps_first_node)))
+
+    def exchange_create(self, rank: int, world: int, max_keys: int) -> bytes:
+        """Allocates this rank's exchange buffer; returns its 64-byte CUDA IPC handle."""
+        out = (C.c_ubyte * IPC_HANDLE_BYTES)()
+        self._ck(self.L.nosplan_exchange_create(self.h, int(rank), int(world), int(max_keys), out))
+        return bytes(out)
+
+    def exchange_open(self, handles: Sequence[bytes]):
+        blob = b"".join(handles)
+        buf = (C.c_ubyte * max(len(blob), 1)).from_buffer_copy(blob or b"\0")
+        self._ck(self.L.nosplan_exchange_open(self.h, buf))
+
+    def exchange_min_dev(self, n_keys, in_ptr, out_ptr, stream=0):
+        self._ck(self.L.nosplan_exchange_min_dev(self.h, int(n_keys), C.c_void_p(in_ptr or None), C.c_void_p(out_ptr or None),
+                                                 C.c_void_p(stream or None)))
+
+    def exchange_status(self):
+        self._ck(self.L.nosplan_exchange_status(self.h))
+
+    def exchange_destroy(self):
+        self._ck(self.L.nosplan_exchange_destroy(self.h))
 
     def mig_evals_per_demand(self) -> int:
         return int(self.L.nosplan_mig_evals_per_demand(self.h))
