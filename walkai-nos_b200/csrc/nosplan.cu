@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <string>
@@ -57,6 +58,7 @@ struct nosplan {
   MigTables h_tables;
   DevBuf d_tables;
   int cmax = 0;
+  bool k16ok = false;  // <= 16 geometries per model, every quantity <= 127 (16-bit score keys)
 
   // MIG snapshot
   bool have_mig = false;
@@ -192,20 +194,29 @@ size_t mig_score_smem(const nosplan_t* h, int tn) {
   return mig_score_smem_bytes(h->h_tables.n_models, h->mig_gs, h->cmax, tn);
 }
 
-// picks the instantiation for the table's candidate count (CW words of 4 candidates; 0 = any)
-template <int CW>
+// picks the instantiation for the table's candidate count (CW words of 4 candidates; 0 = any) and key width
+template <int CW, bool K16>
 int launch_mig_score_cw(nosplan_t* h, const MigScoreArgs& a, dim3 grid, size_t smem, cudaStream_t st) {
-  CU(cudaFuncSetAttribute(mig_score_kernel<kScoreTN, kScoreDS, CW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  mig_score_kernel<kScoreTN, kScoreDS, CW><<<grid, kScoreTN * kScoreDS, smem, st>>>(a);
+  CU(cudaFuncSetAttribute(mig_score_kernel<kScoreTN, kScoreDS, CW, K16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  mig_score_kernel<kScoreTN, kScoreDS, CW, K16><<<grid, kScoreTN * kScoreDS, smem, st>>>(a);
   return NOSPLAN_OK;
 }
 int launch_mig_score_kernel(nosplan_t* h, const MigScoreArgs& a, dim3 grid, size_t smem, cudaStream_t st) {
-  switch ((a.cmax + 3) / 4) {
-    case 1: return launch_mig_score_cw<1>(h, a, grid, smem, st);
-    case 2: return launch_mig_score_cw<2>(h, a, grid, smem, st);
-    case 3: return launch_mig_score_cw<3>(h, a, grid, smem, st);
-    case 4: return launch_mig_score_cw<4>(h, a, grid, smem, st);
-    default: return launch_mig_score_cw<0>(h, a, grid, smem, st);
+  const int cw = (a.cmax + 3) / 4;
+  if (a.k16 && cw <= 4) {  // <= 16 geometries per model and quantities <= 127: two candidates per DPX instruction
+    switch (cw) {
+      case 1: return launch_mig_score_cw<1, true>(h, a, grid, smem, st);
+      case 2: return launch_mig_score_cw<2, true>(h, a, grid, smem, st);
+      case 3: return launch_mig_score_cw<3, true>(h, a, grid, smem, st);
+      default: return launch_mig_score_cw<4, true>(h, a, grid, smem, st);
+    }
+  }
+  switch (cw) {
+    case 1: return launch_mig_score_cw<1, false>(h, a, grid, smem, st);
+    case 2: return launch_mig_score_cw<2, false>(h, a, grid, smem, st);
+    case 3: return launch_mig_score_cw<3, false>(h, a, grid, smem, st);
+    case 4: return launch_mig_score_cw<4, false>(h, a, grid, smem, st);
+    default: return launch_mig_score_cw<0, false>(h, a, grid, smem, st);
   }
 }
 
@@ -227,6 +238,7 @@ int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
     a.npad = h->mig_npad;
     a.gs = h->mig_gs;
     a.cmax = h->cmax;
+    a.k16 = h->k16ok ? 1 : 0;
     a.tg = h->mig_tg;
     a.D = D;
     a.dem_off = d_off;
@@ -403,6 +415,11 @@ int nosplan_set_mig_tables(nosplan_t* h, int n_profiles, const char* const* prof
   h->P = n_profiles;
   h->names = names;
   h->cmax = std::max(cmax, 1);
+  int maxq = 0;
+  for (size_t i = 0; i < (size_t)geom_off[n_models] * n_profiles; ++i) maxq = std::max(maxq, (int)geom_counts[i]);
+  h->k16ok = h->cmax <= 16 && maxq <= 127;
+  if (const char* e = std::getenv("NOSPLAN_KEY_BITS"))  // measurement knob: 32 forces the wide-key scorer
+    if (std::atoi(e) == 32) h->k16ok = false;
   h->have_tables = true;
   h->have_mig = false;  // a snapshot refers to model ids of the table it was uploaded against
   return NOSPLAN_OK;
@@ -1144,6 +1161,7 @@ extern "C" int nosplan_score_mig_static(nosplan_t* h, int n_nodes, int gpus_per_
     a.npad = kStaticMaxNodes;  // row stride of the fixed arrays
     a.gs = gs;
     a.cmax = h->cmax;
+    a.k16 = h->k16ok ? 1 : 0;
     a.tg = n_nodes * gpus_per_node;
     a.D = D;
     a.dem_off = dem_off;

@@ -213,6 +213,7 @@ struct MigScoreArgs {
   const uint8_t* s_cnt;
   const int32_t* gpu_off;
   int N, npad, gs, cmax, tg;
+  int k16;  // tables allow the 16-bit key path: <= 16 geometries per model, every quantity <= 127
   int D, d_chunk;
   const int32_t* dem_off;
   const int32_t* dem_key;
@@ -224,28 +225,35 @@ struct MigScoreArgs {
 
 // Shared-memory layout of one tile (TN nodes, gs GPU slots, cw = ceil(cmax/4) words of 4 candidates):
 //   candT [n_models][16][cw] u32   candidate quantities transposed: byte cc of word i = cand[4i+cc][p]
+//   candT2 [n_models][16][2cw] u32 the same, one candidate per 16-bit lane (K16 path)
 //   rank2 [gs][2cw][TN]      u32   per (node, slot): half-word h of word i describes candidate c = 2i+h:
 //                                  0 if it cannot be applied, else rank << 8 | (255 - c), rank = 1 + the
 //                                  position of its demand-independent score key0 among the GPU's
-//                                  candidates (equal key0 -> equal rank; the index bits break that tie)
+//                                  candidates (equal key0 -> equal rank; the index bits break that tie).
+//                                  K16 path: (rank + 7) << 4 | (15 - c), so that a whole key
+//                                  provided << 9 | that fits one 16-bit lane and two candidates are scored
+//                                  per DPX instruction (VIADDMNMX.S16x2, VIMNMX.S16x2.RELU, VIMNMX3.U16x2);
+//                                  rank + 7 >= 8 keeps an applicable half-word (>= 128) above any
+//                                  provided count (<= 127), which is what zeroes inapplicable lanes
 //   usedw/freew [gs][4][TN]  u32   the node's packed used / free maps
 //   model [gs][TN]           u8
 __host__ __device__ inline size_t mig_score_smem_bytes(int n_models, int gs, int cmax, int tn) {
   const size_t cw = (size_t)(cmax + 3) / 4;
-  return (size_t)n_models * 16 * cw * 4 + (size_t)gs * 2 * cw * tn * 4 + (size_t)gs * 4 * tn * 4 * 2 + (size_t)gs * tn + 16;
+  return (size_t)n_models * 16 * cw * 4 * 3 + (size_t)gs * 2 * cw * tn * 4 + (size_t)gs * 4 * tn * 4 * 2 + (size_t)gs * tn + 16;
 }
 
 // TN nodes per tile; DS threads share one node's tile (thread j of them takes every DS-th demand row of
 // the chunk), which raises occupancy without more shared memory; CW = words of 4 candidates per GPU
 // (0 = runtime), a template parameter so the candidate loop unrolls completely.
-template <int TN, int DS, int CW>
+template <int TN, int DS, int CW, bool K16>
 __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a) {
   extern __shared__ __align__(16) unsigned char smem[];
   const MigTables* __restrict__ T = a.T;
   const int cw = CW ? CW : ((a.cmax + 3) >> 2);
   const int n_models = T->n_models;
   uint32_t* s_candT = reinterpret_cast<uint32_t*>(smem);
-  uint32_t* s_rank2 = s_candT + (size_t)n_models * 16 * cw;
+  uint32_t* s_candT2 = s_candT + (size_t)n_models * 16 * cw;
+  uint32_t* s_rank2 = s_candT2 + (size_t)n_models * 16 * cw * 2;
   uint32_t* s_usedw = s_rank2 + (size_t)a.gs * 2 * cw * TN;
   uint32_t* s_freew = s_usedw + (size_t)a.gs * 4 * TN;
   uint8_t* s_model = reinterpret_cast<uint8_t*>(s_freew + (size_t)a.gs * 4 * TN);
@@ -263,6 +271,10 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
       if (c < cc) v |= byte_of(T->cand[c0 + c], p) << (8 * b);
     }
     s_candT[i] = v;
+    if (K16) {
+      s_candT2[2 * i] = (v & 0xffu) | ((v & 0xff00u) << 8);
+      s_candT2[2 * i + 1] = ((v >> 16) & 0xffu) | ((v >> 24) << 16);
+    }
   }
   // per (node, slot): feasibility + demand-independent key of every candidate, reduced to a rank byte
   const int cnt = (n < a.N) ? a.s_cnt[n] : 0;
@@ -291,7 +303,7 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
         if (c < cc && k0[c] != 0u) {
           uint32_t r = 1;
           for (int c2 = 0; c2 < cc; ++c2) r += (k0[c2] != 0u && k0[c2] < k0[c]) ? 1u : 0u;
-          r2 |= ((r << 8) | (uint32_t)(255 - c)) << (16 * b);
+          r2 |= (K16 ? (((r + 7u) << 4) | (uint32_t)(15 - c)) : ((r << 8) | (uint32_t)(255 - c))) << (16 * b);
         }
       }
       s_rank2[((size_t)s * 2 * cw + w) * TN + tid] = r2;
@@ -305,6 +317,8 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
   uint32_t k16, k8;  // opaque 2^16 and 2^8 (see the inner loop)
   asm("mov.u32 %0, 65536;" : "=r"(k16));
   asm("mov.u32 %0, 256;" : "=r"(k8));
+  uint32_t k512;
+  asm("mov.u32 %0, 512;" : "=r"(k512));
   for (int d = d_begin + dsub; d < d_end; d += DS) {
     const int e0 = __ldg(a.dem_off + d), k = __ldg(a.dem_off + d + 1) - e0;  // uniform over the CTA
     bool any = false;
@@ -325,6 +339,31 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
         // cannot be applied (its rank half-word is 0), so "updated" <=> best >= 0x10000.  DPX min/max
         // (VIADDMNMX.RELU, VIMNMX3) keep this at ~5.5 instructions per candidate.
         uint32_t best = 0;
+        int nf = fj;
+        int ch = -1;
+        if constexpr (K16) {
+          // two candidates per instruction: key = provided << 9 | (rank + 7) << 4 | (15 - index) per 16-bit lane
+          const uint32_t* ct2 = s_candT2 + ((size_t)s_model[s * TN + tid] * 16 + p) * (2 * cw);
+          uint32_t best2 = 0;
+          if (needed > 0) {
+            const uint32_t nd2 = (uint32_t)min(needed, 32767) * 0x10001u;
+            const uint32_t nc2 = ((uint32_t)(-curj) & 0xffffu) * 0x10001u;
+#pragma unroll
+            for (int w = 0; w < cw; ++w) {
+              const uint32_t ra = s_rank2[((size_t)s * 2 * cw + 2 * w) * TN + tid];
+              const uint32_t rb = s_rank2[((size_t)s * 2 * cw + 2 * w + 1) * TN + tid];
+              const uint32_t pa = __vimin_s16x2_relu(__viaddmin_s16x2(ct2[2 * w], nc2, nd2), ra);
+              const uint32_t pb = __vimin_s16x2_relu(__viaddmin_s16x2(ct2[2 * w + 1], nc2, nd2), rb);
+              best2 = __vimax3_u16x2(best2, pa * k512 + ra, pb * k512 + rb);  // IMAD: the FMA pipe, not the ALU
+            }
+          }
+          best = max(best2 & 0xffffu, best2 >> 16);
+          if (best >= 512u) {
+            any = true;
+            ch = 15 - (int)(best & 15u);
+            nf = (int)((ct2[ch >> 1] >> (16 * (ch & 1))) & 0xffffu) - uj;
+          }
+        } else {
         if (needed > 0) {
           const int ncur = -curj;
 #pragma unroll
@@ -353,12 +392,11 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
           }
         }
         if (best < 0x10000u) best = 0u;
-        int nf = fj;
-        int ch = -1;
         if (best != 0u) {
           any = true;
           ch = 255 - (int)(best & 0xffu);
           nf = (int)((ct[ch >> 2] >> (8 * (ch & 3))) & 0xffu) - uj;
+        }
         }
         if (a.choice) a.choice[(size_t)d * a.tg + g0 + s] = (int8_t)ch;
         resid = max(resid - nf, 0);
@@ -381,7 +419,7 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
           uint32_t best = 0;
           for (int c = 0; c < a.cmax; ++c) {
             const uint32_t rk = (s_rank2[((size_t)s * 2 * cw + (c >> 1)) * TN + tid] >> (16 * (c & 1))) & 0xffffu;
-            if (rk == 0u) continue;
+            if (rk == 0u) continue;  // either encoding: ordered by (rank, lowest index), 0 = not applicable
             int prov = 0;
             for (int j = 0; j < k; ++j) {
               const int needed = resid[j] - fj[j];
@@ -392,7 +430,7 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
           }
           if (best != 0u) {
             any = true;
-            ch = 255 - (int)(best & 0xffu);
+            ch = K16 ? 15 - (int)(best & 15u) : 255 - (int)(best & 0xffu);
           }
           for (int j = 0; j < k; ++j) {
             const int nf = (ch >= 0) ? (int)((ctm[pid[j] * cw + (ch >> 2)] >> (8 * (ch & 3))) & 0xffu) - uj[j] : fj[j];
