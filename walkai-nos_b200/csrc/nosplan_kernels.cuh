@@ -235,11 +235,11 @@ struct MigScoreArgs {
 //                                  per DPX instruction (VIADDMNMX.S16x2, VIMNMX.S16x2.RELU, VIMNMX3.U16x2);
 //                                  rank + 7 >= 8 keeps an applicable half-word (>= 128) above any
 //                                  provided count (<= 127), which is what zeroes inapplicable lanes
-//   usedw/freew [gs][4][TN]  u32   the node's packed used / free maps
+//   uf [gs][16][TN]          u16   per (node, slot, profile): free | (used + free) << 8
 //   model [gs][TN]           u8
 __host__ __device__ inline size_t mig_score_smem_bytes(int n_models, int gs, int cmax, int tn) {
   const size_t cw = (size_t)(cmax + 3) / 4;
-  return (size_t)n_models * 16 * cw * 4 * 3 + (size_t)gs * 2 * cw * tn * 4 + (size_t)gs * 4 * tn * 4 * 2 + (size_t)gs * tn + 16;
+  return (size_t)n_models * 16 * cw * 4 * 3 + (size_t)gs * 2 * cw * tn * 4 + (size_t)gs * 16 * tn * 2 + (size_t)gs * tn + 16;
 }
 
 // TN nodes per tile; DS threads share one node's tile (thread j of them takes every DS-th demand row of
@@ -254,9 +254,8 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
   uint32_t* s_candT = reinterpret_cast<uint32_t*>(smem);
   uint32_t* s_candT2 = s_candT + (size_t)n_models * 16 * cw;
   uint32_t* s_rank2 = s_candT2 + (size_t)n_models * 16 * cw * 2;
-  uint32_t* s_usedw = s_rank2 + (size_t)a.gs * 2 * cw * TN;
-  uint32_t* s_freew = s_usedw + (size_t)a.gs * 4 * TN;
-  uint8_t* s_model = reinterpret_cast<uint8_t*>(s_freew + (size_t)a.gs * 4 * TN);
+  uint16_t* s_uf = reinterpret_cast<uint16_t*>(s_rank2 + (size_t)a.gs * 2 * cw * TN);
+  uint8_t* s_model = reinterpret_cast<uint8_t*>(s_uf + (size_t)a.gs * 16 * TN);
 
   const int tid = threadIdx.x % TN;   // node of the tile
   const int dsub = threadIdx.x / TN;  // which share of the demand chunk
@@ -287,10 +286,7 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
     const int c0 = T->geom_off[m], cc = T->geom_off[m + 1] - c0;
     s_model[s * TN + tid] = (uint8_t)m;
 #pragma unroll
-    for (int w = 0; w < 4; ++w) {
-      s_usedw[(s * 4 + w) * TN + tid] = word_of(u, w);
-      s_freew[(s * 4 + w) * TN + tid] = word_of(f, w);
-    }
+    for (int q = 0; q < 16; ++q) s_uf[(s * 16 + q) * TN + tid] = (uint16_t)(byte_of(f, q) | (byte_of(cur, q) << 8));
     uint32_t k0[kMaxGeoms];
     for (int c = 0; c < cc; ++c) {
       const uint4 cd = T->cand[c0 + c];
@@ -328,79 +324,79 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
       // (provided, rank, lowest index) compare folded into one integer max.
       const int p = __ldg(a.dem_key + e0);
       int resid = max(__ldg(a.dem_qty + e0), 0);
-      const int pw = p >> 2, psh = (p & 3) * 8;
-      for (int s = 0; s < cnt; ++s) {
-        const int uj = (s_usedw[(s * 4 + pw) * TN + tid] >> psh) & 0xff;
-        const int fj = (s_freew[(s * 4 + pw) * TN + tid] >> psh) & 0xff;
+      // running pointers: one add per slot instead of re-deriving every shared-memory address
+      const uint16_t* uf = s_uf + (size_t)p * TN + tid;
+      const uint32_t* rk = s_rank2 + tid;
+      const uint8_t* md = s_model + tid;
+      uint32_t anyacc = 0;
+      for (int s = 0; s < cnt; ++s, uf += 16 * TN, rk += 2 * cw * TN, md += TN) {
+        const uint32_t x = *uf;
+        const int fj = (int)(x & 0xffu), curj = (int)(x >> 8);
         const int needed = resid - fj;
-        const int curj = uj + fj;
-        const uint32_t* ct = s_candT + ((size_t)s_model[s * TN + tid] * 16 + p) * cw;
-        // key = provided << 16 | rank << 8 | (255 - index); provided is forced to 0 for a candidate that
-        // cannot be applied (its rank half-word is 0), so "updated" <=> best >= 0x10000.  DPX min/max
-        // (VIADDMNMX.RELU, VIMNMX3) keep this at ~5.5 instructions per candidate.
-        uint32_t best = 0;
-        int nf = fj;
-        int ch = -1;
+        // Every candidate of the GPU is evaluated when something is still needed:
+        // provided = clamp(cand[p] - cur[p], 0, needed), forced to 0 for a candidate that cannot be applied
+        // (its rank half-word is 0), then (provided, rank, lowest index) folded into one integer max.
+        uint32_t best = 0, prov;
         if constexpr (K16) {
           // two candidates per instruction: key = provided << 9 | (rank + 7) << 4 | (15 - index) per 16-bit lane
-          const uint32_t* ct2 = s_candT2 + ((size_t)s_model[s * TN + tid] * 16 + p) * (2 * cw);
           uint32_t best2 = 0;
           if (needed > 0) {
+            const uint32_t* ct2 = s_candT2 + ((size_t)(*md) * 16 + p) * (2 * cw);
             const uint32_t nd2 = (uint32_t)min(needed, 32767) * 0x10001u;
             const uint32_t nc2 = ((uint32_t)(-curj) & 0xffffu) * 0x10001u;
 #pragma unroll
             for (int w = 0; w < cw; ++w) {
-              const uint32_t ra = s_rank2[((size_t)s * 2 * cw + 2 * w) * TN + tid];
-              const uint32_t rb = s_rank2[((size_t)s * 2 * cw + 2 * w + 1) * TN + tid];
+              const uint32_t ra = rk[(2 * w) * TN];
+              const uint32_t rb = rk[(2 * w + 1) * TN];
               const uint32_t pa = __vimin_s16x2_relu(__viaddmin_s16x2(ct2[2 * w], nc2, nd2), ra);
               const uint32_t pb = __vimin_s16x2_relu(__viaddmin_s16x2(ct2[2 * w + 1], nc2, nd2), rb);
               best2 = __vimax3_u16x2(best2, pa * k512 + ra, pb * k512 + rb);  // IMAD: the FMA pipe, not the ALU
             }
           }
           best = max(best2 & 0xffffu, best2 >> 16);
-          if (best >= 512u) {
-            any = true;
-            ch = 15 - (int)(best & 15u);
-            nf = (int)((ct2[ch >> 1] >> (16 * (ch & 1))) & 0xffffu) - uj;
-          }
+          prov = best >> 9;  // 0 unless some applicable candidate provides something
         } else {
-        if (needed > 0) {
-          const int ncur = -curj;
+          // key = provided << 16 | rank << 8 | (255 - index)
+          if (needed > 0) {
+            const uint32_t* ct = s_candT + ((size_t)(*md) * 16 + p) * cw;
+            const int ncur = -curj;
 #pragma unroll
-          for (int w = 0; w < cw; ++w) {
-            const uint32_t ra = s_rank2[((size_t)s * 2 * cw + 2 * w) * TN + tid];
-            const uint32_t rb = s_rank2[((size_t)s * 2 * cw + 2 * w + 1) * TN + tid];
-            const uint32_t cb4 = ct[w];
-            // The kernel is bound by the integer ALU pipe (PRMT/SHF/LOP3/VIMNMX); the FMA pipe is nearly
-            // idle.  Field extraction is therefore done with multiplies (IMAD / IMAD.HI run on the FMA
-            // pipe): x >> 16 == mulhi(x, 2^16), x & 0xffff == x - (x >> 16) * 2^16, x >> 24 == mulhi(x, 2^8).
-            // The constants come from asm so the compiler cannot turn them back into shifts.
-            const uint32_t ah = __umulhi(ra, k16), bh = __umulhi(rb, k16);
-            const uint32_t rk4[4] = {ra - ah * k16, ah, rb - bh * k16, bh};
-            const int cb3 = (int)__umulhi(cb4, k8);
-            const int cb2 = (int)__umulhi(cb4 * k8, k8);  // (x << 8) >> 24
-            uint32_t key[4];
+            for (int w = 0; w < cw; ++w) {
+              const uint32_t ra = rk[(2 * w) * TN];
+              const uint32_t rb = rk[(2 * w + 1) * TN];
+              const uint32_t cb4 = ct[w];
+              // Field extraction with multiplies (IMAD / IMAD.HI run on the FMA pipe, the ALU pipe is the
+              // busy one): x >> 16 == mulhi(x, 2^16), x & 0xffff == x - (x >> 16) * 2^16, x >> 24 ==
+              // mulhi(x, 2^8).  The constants come from asm so the compiler cannot turn them back into shifts.
+              const uint32_t ah = __umulhi(ra, k16), bh = __umulhi(rb, k16);
+              const uint32_t rk4[4] = {ra - ah * k16, ah, rb - bh * k16, bh};
+              const int cb3 = (int)__umulhi(cb4, k8);
+              const int cb2 = (int)__umulhi(cb4 * k8, k8);  // (x << 8) >> 24
+              uint32_t key[4];
 #pragma unroll
-            for (int b = 0; b < 4; ++b) {
-              const int cb = (b == 3) ? cb3 : (b == 2) ? cb2 : (int)__byte_perm(cb4, 0u, 0x4440u | (uint32_t)b);
-              const uint32_t rk = rk4[b];  // rank << 8 | 255-index, 0 if not applicable
-              const int prov = min(__viaddmin_s32_relu(cb, ncur, needed), (int)rk);
-              key[b] = (uint32_t)prov * k16 + rk;
+              for (int b = 0; b < 4; ++b) {
+                const int cb = (b == 3) ? cb3 : (b == 2) ? cb2 : (int)__byte_perm(cb4, 0u, 0x4440u | (uint32_t)b);
+                const uint32_t r = rk4[b];  // rank << 8 | 255-index, 0 if not applicable
+                const int pv = min(__viaddmin_s32_relu(cb, ncur, needed), (int)r);
+                key[b] = (uint32_t)pv * k16 + r;
+              }
+              best = __vimax3_u32(best, key[0], key[1]);
+              best = __vimax3_u32(best, key[2], key[3]);
             }
-            best = __vimax3_u32(best, key[0], key[1]);
-            best = __vimax3_u32(best, key[2], key[3]);
           }
+          prov = best >> 16;
         }
-        if (best < 0x10000u) best = 0u;
-        if (best != 0u) {
-          any = true;
-          ch = 255 - (int)(best & 0xffu);
-          nf = (int)((ct[ch >> 2] >> (8 * (ch & 3))) & 0xffu) - uj;
+        anyacc |= prov;
+        if (a.choice) {
+          const int ch = prov == 0u ? -1 : (K16 ? 15 - (int)(best & 15u) : 255 - (int)(best & 0xffu));
+          a.choice[(size_t)d * a.tg + g0 + s] = (int8_t)ch;
         }
-        }
-        if (a.choice) a.choice[(size_t)d * a.tg + g0 + s] = (int8_t)ch;
-        resid = max(resid - nf, 0);
+        // node.go:164-169 with the winner applied (gpu.go:134-154): the GPU's free count of the profile
+        // becomes cand - used = free + (cand - cur) >= free + provided, with equality unless the request is
+        // covered; either way what is still missing afterwards is needed - provided (0 if nothing was)
+        resid = max(needed, 0) - (int)prov;
       }
+      any = anyacc != 0u;
     } else {
       int pid[kMaxKeys], resid[kMaxKeys];
       for (int j = 0; j < kMaxKeys; ++j) {
@@ -413,8 +409,9 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
           const uint32_t* ctm = s_candT + (size_t)s_model[s * TN + tid] * 16 * cw;
           int uj[kMaxKeys], fj[kMaxKeys];
           for (int j = 0; j < k; ++j) {
-            uj[j] = (s_usedw[(s * 4 + (pid[j] >> 2)) * TN + tid] >> ((pid[j] & 3) * 8)) & 0xff;
-            fj[j] = (s_freew[(s * 4 + (pid[j] >> 2)) * TN + tid] >> ((pid[j] & 3) * 8)) & 0xff;
+            const uint32_t x = s_uf[(s * 16 + pid[j]) * TN + tid];
+            fj[j] = (int)(x & 0xffu);
+            uj[j] = (int)(x >> 8) - fj[j];
           }
           uint32_t best = 0;
           for (int c = 0; c < a.cmax; ++c) {
