@@ -58,7 +58,7 @@ struct nosplan {
   MigTables h_tables;
   DevBuf d_tables;
   int cmax = 0;
-  bool k16ok = false;  // <= 16 geometries per model, every quantity <= 127 (16-bit score keys)
+  bool k16ok = false;  // <= 16 geometries per model, every quantity <= 63 (16-bit score keys)
 
   // MIG snapshot
   bool have_mig = false;
@@ -203,7 +203,7 @@ int launch_mig_score_cw(nosplan_t* h, const MigScoreArgs& a, dim3 grid, size_t s
 }
 int launch_mig_score_kernel(nosplan_t* h, const MigScoreArgs& a, dim3 grid, size_t smem, cudaStream_t st) {
   const int cw = (a.cmax + 3) / 4;
-  if (a.k16 && cw <= 4) {  // <= 16 geometries per model and quantities <= 127: two candidates per DPX instruction
+  if (a.k16 && cw <= 4) {  // <= 16 geometries per model and quantities <= 63: two candidates per DPX instruction
     switch (cw) {
       case 1: return launch_mig_score_cw<1, true>(h, a, grid, smem, st);
       case 2: return launch_mig_score_cw<2, true>(h, a, grid, smem, st);
@@ -282,11 +282,11 @@ int launch_mps_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
     a.gs = h->mps_gs;
     int tiles = (h->mps_n + kScoreTN - 1) / kScoreTN;
     int gy;
-    pick_chunks(h->sm_count, tiles, D, 16, &a.d_chunk, &gy, 8);
+    pick_chunks(h->sm_count, tiles, D, 16, &a.d_chunk, &gy, 3);
     const size_t smem = mps_score_smem_bytes(h->mps_gs, h->S, kScoreTN);
     if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MPS scorer tile needs %zu bytes of shared memory", smem);
-    CU(cudaFuncSetAttribute(mps_score_kernel<kScoreTN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    mps_score_kernel<kScoreTN><<<dim3(tiles, gy), kScoreTN, smem, st>>>(a);
+    CU(cudaFuncSetAttribute(mps_score_kernel<kScoreTN, kScoreDS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    mps_score_kernel<kScoreTN, kScoreDS><<<dim3(tiles, gy), kScoreTN * kScoreDS, smem, st>>>(a);
   }
   nonode_to_minus1_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, base);
   CU(cudaGetLastError());
@@ -417,7 +417,7 @@ int nosplan_set_mig_tables(nosplan_t* h, int n_profiles, const char* const* prof
   h->cmax = std::max(cmax, 1);
   int maxq = 0;
   for (size_t i = 0; i < (size_t)geom_off[n_models] * n_profiles; ++i) maxq = std::max(maxq, (int)geom_counts[i]);
-  h->k16ok = h->cmax <= 16 && maxq <= 127;
+  h->k16ok = h->cmax <= 16 && maxq <= 63;
   if (const char* e = std::getenv("NOSPLAN_KEY_BITS"))  // measurement knob: 32 forces the wide-key scorer
     if (std::atoi(e) == 32) h->k16ok = false;
   h->have_tables = true;

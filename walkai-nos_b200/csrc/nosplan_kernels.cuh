@@ -213,7 +213,7 @@ struct MigScoreArgs {
   const uint8_t* s_cnt;
   const int32_t* gpu_off;
   int N, npad, gs, cmax, tg;
-  int k16;  // tables allow the 16-bit key path: <= 16 geometries per model, every quantity <= 127
+  int k16;  // tables allow the 16-bit key path: <= 16 geometries per model, every quantity <= 63
   int D, d_chunk;
   const int32_t* dem_off;
   const int32_t* dem_key;
@@ -230,11 +230,11 @@ struct MigScoreArgs {
 //                                  0 if it cannot be applied, else rank << 8 | (255 - c), rank = 1 + the
 //                                  position of its demand-independent score key0 among the GPU's
 //                                  candidates (equal key0 -> equal rank; the index bits break that tie).
-//                                  K16 path: (rank + 7) << 4 | (15 - c), so that a whole key
-//                                  provided << 9 | that fits one 16-bit lane and two candidates are scored
-//                                  per DPX instruction (VIADDMNMX.S16x2, VIMNMX.S16x2.RELU, VIMNMX3.U16x2);
-//                                  rank + 7 >= 8 keeps an applicable half-word (>= 128) above any
-//                                  provided count (<= 127), which is what zeroes inapplicable lanes
+//                                  K16 path: rank << 4 | (15 - c), or 0x8000 if it cannot be applied, so
+//                                  that a whole key provided << 9 | that fits one SIGNED 16-bit lane
+//                                  (provided <= 63) and two candidates are scored per DPX instruction
+//                                  (VIADDMNMX.S16x2.RELU, VIMNMX3.S16x2); an inapplicable lane is negative
+//                                  whatever it provides and never wins against the running maximum
 //   uf [gs][16][TN]          u16   per (node, slot, profile): free | (used + free) << 8
 //   model [gs][TN]           u8
 __host__ __device__ inline size_t mig_score_smem_bytes(int n_models, int gs, int cmax, int tn) {
@@ -299,7 +299,9 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
         if (c < cc && k0[c] != 0u) {
           uint32_t r = 1;
           for (int c2 = 0; c2 < cc; ++c2) r += (k0[c2] != 0u && k0[c2] < k0[c]) ? 1u : 0u;
-          r2 |= (K16 ? (((r + 7u) << 4) | (uint32_t)(15 - c)) : ((r << 8) | (uint32_t)(255 - c))) << (16 * b);
+          r2 |= (K16 ? ((r << 4) | (uint32_t)(15 - c)) : ((r << 8) | (uint32_t)(255 - c))) << (16 * b);
+        } else if (K16) {
+          r2 |= 0x8000u << (16 * b);  // not applicable (or no such candidate): the lane's key stays negative
         }
       }
       s_rank2[((size_t)s * 2 * cw + w) * TN + tid] = r2;
@@ -330,6 +332,8 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
       const uint8_t* md = s_model + tid;
       uint32_t anyacc = 0;
       for (int s = 0; s < cnt; ++s, uf += 16 * TN, rk += 2 * cw * TN, md += TN) {
+        // request covered: every candidate of the remaining GPUs provides 0 (gpu.go:172-175), nothing can change
+        if (resid == 0 && !a.choice) break;
         const uint32_t x = *uf;
         const int fj = (int)(x & 0xffu), curj = (int)(x >> 8);
         const int needed = resid - fj;
@@ -338,7 +342,8 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
         // (its rank half-word is 0), then (provided, rank, lowest index) folded into one integer max.
         uint32_t best = 0, prov;
         if constexpr (K16) {
-          // two candidates per instruction: key = provided << 9 | (rank + 7) << 4 | (15 - index) per 16-bit lane
+          // two candidates per instruction: key = provided << 9 | rank << 4 | (15 - index) per signed 16-bit
+          // lane; a lane that cannot be applied carries 0x8000 and stays below the running maximum (>= 0)
           uint32_t best2 = 0;
           if (needed > 0) {
             const uint32_t* ct2 = s_candT2 + ((size_t)(*md) * 16 + p) * (2 * cw);
@@ -348,9 +353,9 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
             for (int w = 0; w < cw; ++w) {
               const uint32_t ra = rk[(2 * w) * TN];
               const uint32_t rb = rk[(2 * w + 1) * TN];
-              const uint32_t pa = __vimin_s16x2_relu(__viaddmin_s16x2(ct2[2 * w], nc2, nd2), ra);
-              const uint32_t pb = __vimin_s16x2_relu(__viaddmin_s16x2(ct2[2 * w + 1], nc2, nd2), rb);
-              best2 = __vimax3_u16x2(best2, pa * k512 + ra, pb * k512 + rb);  // IMAD: the FMA pipe, not the ALU
+              const uint32_t pa = __viaddmin_s16x2_relu(ct2[2 * w], nc2, nd2);
+              const uint32_t pb = __viaddmin_s16x2_relu(ct2[2 * w + 1], nc2, nd2);
+              best2 = __vimax3_s16x2(best2, pa * k512 + ra, pb * k512 + rb);  // IMAD: the FMA pipe, not the ALU
             }
           }
           best = max(best2 & 0xffffu, best2 >> 16);
@@ -416,7 +421,7 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
           uint32_t best = 0;
           for (int c = 0; c < a.cmax; ++c) {
             const uint32_t rk = (s_rank2[((size_t)s * 2 * cw + (c >> 1)) * TN + tid] >> (16 * (c & 1))) & 0xffffu;
-            if (rk == 0u) continue;  // either encoding: ordered by (rank, lowest index), 0 = not applicable
+            if (K16 ? (rk & 0x8000u) != 0u : rk == 0u) continue;  // not applicable; else ordered by (rank, lowest index)
             int prov = 0;
             for (int j = 0; j < k; ++j) {
               const int needed = resid[j] - fj[j];
@@ -746,27 +751,30 @@ __host__ __device__ inline size_t mps_score_smem_bytes(int gs, int S, int tn) {
 // exact floor(n / m) for n, m < 2^16 with inv = (m == 1 ? 0 : 0xFFFFFFFF / m + 1)
 __device__ __forceinline__ int div_small(int n, int m, uint32_t inv) { return m == 1 ? n : (int)__umulhi((uint32_t)n, inv); }
 
-template <int TN>
-__global__ void __launch_bounds__(TN) mps_score_kernel(const MpsScoreArgs a) {
+// TN nodes per tile, DS threads per node: thread j of them takes every DS-th demand row of the chunk
+// (more resident warps over the same shared-memory tile; the per-row work is a dependent chain).
+template <int TN, int DS>
+__global__ void __launch_bounds__(TN * DS, 3) mps_score_kernel(const MpsScoreArgs a) {
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ int s_sz[kMaxSizes];
   __shared__ uint32_t s_inv[kMaxSizes];  // per size: multiplier of the exact multiply-high division
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x % TN;
+  const int dsub = threadIdx.x / TN;
   const int nw = (a.S + 3) >> 2;
   uint32_t* s_free = reinterpret_cast<uint32_t*>(smem);       // [gs][nw][TN]
   uint32_t* s_mask = s_free + (size_t)a.gs * nw * TN;          // [gs][TN]
   uint32_t* s_spare = s_mask + (size_t)a.gs * TN;              // [gs][TN]
-  if (tid < kMaxSizes) {
-    const int m = tid < a.S ? a.sizes[tid] : 1;
-    s_sz[tid] = m;
-    s_inv[tid] = m == 1 ? 0u : 0xFFFFFFFFu / (uint32_t)m + 1u;
+  if (threadIdx.x < kMaxSizes) {
+    const int m = threadIdx.x < a.S ? a.sizes[threadIdx.x] : 1;
+    s_sz[threadIdx.x] = m;
+    s_inv[threadIdx.x] = m == 1 ? 0u : 0xFFFFFFFFu / (uint32_t)m + 1u;
   }
   __syncthreads();
   const int n = blockIdx.x * TN + tid;
   const bool live = n < a.N && a.valid[n];
   const int g0 = n < a.N ? a.gpu_off[n] : 0;
   const int cnt = n < a.N ? a.gpu_off[n + 1] - g0 : 0;
-  for (int s = 0; s < cnt; ++s) {
+  for (int s = dsub; s < cnt; s += DS) {  // the DS threads of a node split its GPUs
     const MpsGpu G = a.gp[g0 + s];
     int origtot = 0;
     for (uint32_t mk = G.fmask; mk; mk &= mk - 1) {
@@ -779,10 +787,10 @@ __global__ void __launch_bounds__(TN) mps_score_kernel(const MpsScoreArgs a) {
     s_spare[s * TN + tid] = ((uint32_t)origtot << 16) | (uint32_t)((int)G.cap - origtot);
   }
   __syncthreads();
-  const int lane = tid & 31;
+  const int lane = threadIdx.x & 31;
   const int d_begin = blockIdx.y * a.d_chunk;
   const int d_end = min(a.D, d_begin + a.d_chunk);
-  for (int d = d_begin; d < d_end; ++d) {
+  for (int d = d_begin + dsub; d < d_end; d += DS) {
     const int e0 = __ldg(a.dem_off + d), k = __ldg(a.dem_off + d + 1) - e0;
     bool any = false;
     if (k == 1 && !a.out_free) {
