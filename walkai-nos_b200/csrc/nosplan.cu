@@ -14,6 +14,7 @@
 #include "nosplan_kernels.cuh"
 #include "nosplan_plan.cuh"
 #include "nosplan_seq.cuh"
+#include "nosplan_score16.cuh"
 #include "nosplan_xchg.cuh"
 
 using namespace nsp;
@@ -67,6 +68,8 @@ struct nosplan {
   DevBuf d_mig_off, d_mig_valid, d_mig_model, d_mig_used0, d_mig_free0, d_mig_used, d_mig_free;
   DevBuf d_mig_sused, d_mig_sfree, d_mig_smodel, d_mig_scnt, d_mig_gnode, d_mig_gslot;
   bool mig_state_dirty = false;  // working copy differs from the snapshot
+  DevBuf d_mig_cost, d_mig_perm;  // per-profile node order of the 16-bit-key scorer (nosplan_score16.cuh)
+  DevBuf d_rows, d_rowb, d_work, d_meta, d_rowcnt, d_profcost;  // per call: demand rows grouped by profile, work items
 
   // MPS snapshot
   bool have_mps = false;
@@ -187,6 +190,23 @@ void pick_chunks(int sm_count, int tiles, int D, int min_chunk, int* d_chunk, in
   if (*gy < 1) *gy = 1;
 }
 
+bool wide_keys_forced() {  // measurement knob: NOSPLAN_KEY_BITS=32 forces the wide-key scorer
+  static const bool f = [] {
+    const char* e = std::getenv("NOSPLAN_KEY_BITS");
+    return e && std::atoi(e) == 32;
+  }();
+  return f;
+}
+
+int score_waves() {  // measurement knob: waves of CTAs per scorer launch
+  static const int w = [] {
+    const char* e = std::getenv("NOSPLAN_SCORE_WAVES");
+    const int v = e ? std::atoi(e) : 2;
+    return v >= 1 && v <= 16 ? v : 2;
+  }();
+  return w;
+}
+
 constexpr int kScoreTN = 128;
 constexpr int kScoreDS = 4;  // threads per node in the MIG scorer
 
@@ -195,28 +215,86 @@ size_t mig_score_smem(const nosplan_t* h, int tn) {
 }
 
 // picks the instantiation for the table's candidate count (CW words of 4 candidates; 0 = any) and key width
-template <int CW, bool K16>
-int launch_mig_score_cw(nosplan_t* h, const MigScoreArgs& a, dim3 grid, size_t smem, cudaStream_t st) {
-  CU(cudaFuncSetAttribute(mig_score_kernel<kScoreTN, kScoreDS, CW, K16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  mig_score_kernel<kScoreTN, kScoreDS, CW, K16><<<grid, kScoreTN * kScoreDS, smem, st>>>(a);
+template <typename Kern>
+int launch_mig_score_grid(nosplan_t* h, Kern kern, const MigScoreArgs& a, int tiles, size_t smem, int chunk_cap, cudaStream_t st) {
+  CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // the demand axis is cut so that the grid is a whole number of waves of what really fits on an SM
+  // (registers and shared memory decide); two waves: the rows' costs differ, smaller CTAs even them out
+  int occ = 0;
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kScoreTN * kScoreDS, smem));
+  MigScoreArgs b = a;
+  int gy = 1;
+  pick_chunks(h->sm_count, tiles, a.D, 16, &b.d_chunk, &gy, std::max(occ, 1) * score_waves());
+  if (chunk_cap > 0 && b.d_chunk > chunk_cap) {
+    b.d_chunk = chunk_cap;
+    gy = (a.D + chunk_cap - 1) / chunk_cap;
+  }
+  kern<<<dim3(tiles, gy), kScoreTN * kScoreDS, smem, st>>>(b);
   return NOSPLAN_OK;
 }
 int launch_mig_score_kernel(nosplan_t* h, const MigScoreArgs& a, dim3 grid, size_t smem, cudaStream_t st) {
   const int cw = (a.cmax + 3) / 4;
-  if (a.k16 && cw <= 4) {  // <= 16 geometries per model and quantities <= 63: two candidates per DPX instruction
+  const int tiles = (int)grid.x;
+  if (a.k16 && cw <= 4 && !wide_keys_forced()) {
+    // <= 16 geometries per model and quantities <= 63: 16-bit keys, two candidates per DPX instruction
     switch (cw) {
-      case 1: return launch_mig_score_cw<1, true>(h, a, grid, smem, st);
-      case 2: return launch_mig_score_cw<2, true>(h, a, grid, smem, st);
-      case 3: return launch_mig_score_cw<3, true>(h, a, grid, smem, st);
-      default: return launch_mig_score_cw<4, true>(h, a, grid, smem, st);
+      case 1: return launch_mig_score_grid(h, mig_score_kernel<kScoreTN, kScoreDS, 1, true>, a, tiles, smem, 0, st);
+      case 2: return launch_mig_score_grid(h, mig_score_kernel<kScoreTN, kScoreDS, 2, true>, a, tiles, smem, 0, st);
+      case 3: return launch_mig_score_grid(h, mig_score_kernel<kScoreTN, kScoreDS, 3, true>, a, tiles, smem, 0, st);
+      default: return launch_mig_score_grid(h, mig_score_kernel<kScoreTN, kScoreDS, 4, true>, a, tiles, smem, 0, st);
     }
   }
   switch (cw) {
-    case 1: return launch_mig_score_cw<1, false>(h, a, grid, smem, st);
-    case 2: return launch_mig_score_cw<2, false>(h, a, grid, smem, st);
-    case 3: return launch_mig_score_cw<3, false>(h, a, grid, smem, st);
-    case 4: return launch_mig_score_cw<4, false>(h, a, grid, smem, st);
-    default: return launch_mig_score_cw<0, false>(h, a, grid, smem, st);
+    case 1: return launch_mig_score_grid(h, mig_score_kernel<kScoreTN, kScoreDS, 1, false>, a, tiles, smem, 0, st);
+    case 2: return launch_mig_score_grid(h, mig_score_kernel<kScoreTN, kScoreDS, 2, false>, a, tiles, smem, 0, st);
+    case 3: return launch_mig_score_grid(h, mig_score_kernel<kScoreTN, kScoreDS, 3, false>, a, tiles, smem, 0, st);
+    case 4: return launch_mig_score_grid(h, mig_score_kernel<kScoreTN, kScoreDS, 4, false>, a, tiles, smem, 0, st);
+    default: return launch_mig_score_grid(h, mig_score_kernel<kScoreTN, kScoreDS, 0, false>, a, tiles, smem, 0, st);
+  }
+}
+
+template <int CW>
+int launch_mig_score16_cw(nosplan_t* h, const MigScoreArgs& a, int tiles, cudaStream_t st) {
+  auto kern = mig_score16_kernel<kScoreTN, kScoreDS, CW>;
+  const size_t smem = mig_score16_smem_bytes(h->h_tables.n_models, a.gs, a.cmax, kScoreTN);
+  if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MIG scorer tile needs %zu bytes of shared memory", smem);
+  CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 0;
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kScoreTN * kScoreDS, smem));
+  int chunk = 16, gy = 1;
+  pick_chunks(h->sm_count, tiles, a.D, 16, &chunk, &gy, std::max(occ, 1) * score_waves());
+  chunk = std::min(chunk, kRowCap);
+  const int max_work = (a.D + chunk - 1) / chunk + h->P;  // every profile may end with a short item
+  CU(h->d_rows.reserve(sizeof(int32_t) * (size_t)a.D));
+  CU(h->d_rowb.reserve((size_t)a.D));
+  CU(h->d_work.reserve(sizeof(int32_t) * 3 * (size_t)max_work));
+  CU(h->d_meta.reserve(sizeof(int32_t) * 4));
+  if (!h->d_rowcnt.p) {  // counters + cursors; the plan kernel leaves the counters at zero for the next call
+    CU(h->d_rowcnt.reserve(sizeof(int32_t) * 34));
+    CU(cudaMemsetAsync(h->d_rowcnt.p, 0, sizeof(int32_t) * 34, st));
+  }
+  int32_t* cnt = h->d_rowcnt.as<int32_t>();
+  const int rb = (a.D + 255) / 256;
+  mig_rows_count_kernel<<<rb, 256, 0, st>>>(a.D, h->P, a.dem_off, a.dem_key, h->d_rowb.as<uint8_t>(), cnt);
+  mig_rows_plan_kernel<<<1, 32, 0, st>>>(h->P, chunk, h->d_profcost.as<int32_t>(), cnt, cnt + 17, h->d_work.as<int32_t>(),
+                                         h->d_meta.as<int32_t>());
+  mig_rows_scatter_kernel<<<rb, 256, 0, st>>>(a.D, h->d_rowb.as<uint8_t>(), cnt + 17, h->d_rows.as<int32_t>());
+  MigScore16Args A;
+  A.base = a;
+  A.perm = h->d_mig_perm.as<int32_t>();
+  A.rows = h->d_rows.as<int32_t>();
+  A.work = h->d_work.as<int32_t>();
+  A.meta = h->d_meta.as<int32_t>();
+  kern<<<dim3(max_work, tiles), kScoreTN * kScoreDS, smem, st>>>(A);
+  CU(cudaGetLastError());
+  return NOSPLAN_OK;
+}
+int launch_mig_score16(nosplan_t* h, const MigScoreArgs& a, int tiles, int cw, cudaStream_t st) {
+  switch (cw) {
+    case 1: return launch_mig_score16_cw<1>(h, a, tiles, st);
+    case 2: return launch_mig_score16_cw<2>(h, a, tiles, st);
+    case 3: return launch_mig_score16_cw<3>(h, a, tiles, st);
+    default: return launch_mig_score16_cw<4>(h, a, tiles, st);
   }
 }
 
@@ -247,11 +325,21 @@ int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
     a.first_node = d_first;
     a.updated = d_updated;
     a.choice = d_choice;
+    a.row_list = nullptr;
+    a.row_meta = nullptr;
     int tiles = (h->mig_n + kScoreTN - 1) / kScoreTN;
     int gy;
     pick_chunks(h->sm_count, tiles, D, 16, &a.d_chunk, &gy);
     size_t smem = mig_score_smem(h, kScoreTN);
     if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MIG scorer tile needs %zu bytes of shared memory", smem);
+    const int cw = (h->cmax + 3) / 4;
+    if (h->k16ok && cw <= 4 && tiles <= 65535 && !wide_keys_forced()) {
+      // common tables: rows grouped by profile, nodes ordered per profile, 16-bit keys (nosplan_score16.cuh);
+      // rows with several keys go through the general kernel below, restricted to their list
+      if ((rc = launch_mig_score16(h, a, tiles, cw, st))) return rc;
+      a.row_list = h->d_rows.as<int32_t>();
+      a.row_meta = h->d_meta.as<int32_t>();
+    }
     if ((rc = launch_mig_score_kernel(h, a, dim3(tiles, gy), smem, st))) return rc;
   }
   CU(cudaGetLastError());
@@ -331,7 +419,8 @@ void nosplan_destroy(nosplan_t* h) {
   DevBuf* all[] = {&h->d_tables, &h->d_mig_off, &h->d_mig_valid, &h->d_mig_model, &h->d_mig_used0, &h->d_mig_free0,
                    &h->d_mig_used, &h->d_mig_free, &h->d_mig_sused, &h->d_mig_sfree, &h->d_mig_smodel, &h->d_mig_scnt,
                    &h->d_mps_sizes, &h->d_mps_off, &h->d_mps_valid, &h->d_mps_gpu0, &h->d_mps_ulo0, &h->d_mps_uhi0,
-                   &h->d_mps_gpu, &h->d_mps_ulo, &h->d_mps_uhi, &h->d_mig_gnode, &h->d_mps_gnode, &h->d_mig_gslot, &h->d_mps_gslot, &h->d_status};
+                   &h->d_mps_gpu, &h->d_mps_ulo, &h->d_mps_uhi, &h->d_mig_gnode, &h->d_mps_gnode, &h->d_mig_gslot, &h->d_mps_gslot, &h->d_status,
+                   &h->d_mig_cost, &h->d_mig_perm, &h->d_rows, &h->d_work, &h->d_meta, &h->d_rowb, &h->d_rowcnt, &h->d_profcost};
   for (DevBuf* b : all) b->release();
   for (auto& b : h->d_in) b.release();
   for (auto& b : h->d_dem) b.release();
@@ -418,8 +507,6 @@ int nosplan_set_mig_tables(nosplan_t* h, int n_profiles, const char* const* prof
   int maxq = 0;
   for (size_t i = 0; i < (size_t)geom_off[n_models] * n_profiles; ++i) maxq = std::max(maxq, (int)geom_counts[i]);
   h->k16ok = h->cmax <= 16 && maxq <= 63;
-  if (const char* e = std::getenv("NOSPLAN_KEY_BITS"))  // measurement knob: 32 forces the wide-key scorer
-    if (std::atoi(e) == 32) h->k16ok = false;
   h->have_tables = true;
   h->have_mig = false;  // a snapshot refers to model ids of the table it was uploaded against
   return NOSPLAN_OK;
@@ -480,6 +567,17 @@ int nosplan_set_mig_snapshot(nosplan_t* h, int n_nodes, const int32_t* gpu_off, 
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(h->d_mig_used.p, h->d_mig_used0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, h->stream));
   CU(cudaMemcpyAsync(h->d_mig_free.p, h->d_mig_free0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, h->stream));
+  if (h->k16ok) {  // node order per profile for the 16-bit-key scorer: scheduling data, not results
+    CU(h->d_mig_cost.reserve((size_t)P * npad));
+    CU(h->d_mig_perm.reserve(sizeof(int32_t) * (size_t)P * npad));
+    mig_cost_kernel<<<(npad + 127) / 128, 128, 0, h->stream>>>(
+        h->d_tables.as<MigTables>(), n_nodes, npad, P, h->d_mig_sused.as<uint4>(), h->d_mig_sfree.as<uint4>(),
+        h->d_mig_smodel.as<uint8_t>(), h->d_mig_scnt.as<uint8_t>(), h->d_mig_cost.as<uint8_t>());
+    CU(h->d_profcost.reserve(sizeof(int32_t) * 16));
+    mig_perm_kernel<<<P, 1024, 0, h->stream>>>(npad, h->d_mig_cost.as<uint8_t>(), h->d_mig_perm.as<int32_t>(),
+                                               h->d_profcost.as<int32_t>());
+    CU(cudaGetLastError());
+  }
   unsigned long long st[2];
   if ((rc = status_fetch(h, h->stream, st))) return rc;
   if (st[0] != ~0ull) {  // first bad entry in GPU order, reported as the host walk used to
@@ -1170,6 +1268,8 @@ extern "C" int nosplan_score_mig_static(nosplan_t* h, int n_nodes, int gpus_per_
     a.first_node = first_node;
     a.updated = nullptr;
     a.choice = nullptr;
+    a.row_list = nullptr;
+    a.row_meta = nullptr;
     const int tiles = (n_nodes + kScoreTN - 1) / kScoreTN;
     int gy;
     pick_chunks(h->sm_count, tiles, D, 16, &a.d_chunk, &gy);

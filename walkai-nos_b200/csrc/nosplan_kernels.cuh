@@ -221,6 +221,9 @@ struct MigScoreArgs {
   int32_t* first_node;  // atomicMin target, pre-filled with kNoNode
   uint8_t* updated;     // [D][N] or null
   int8_t* choice;       // [D][tg] or null
+  // optional: score only the rows row_list[row_meta[1] .. + row_meta[2]) (device-side list and counts)
+  const int32_t* row_list;
+  const int32_t* row_meta;
 };
 
 // Shared-memory layout of one tile (TN nodes, gs GPU slots, cw = ceil(cmax/4) words of 4 candidates):
@@ -242,24 +245,37 @@ __host__ __device__ inline size_t mig_score_smem_bytes(int n_models, int gs, int
   return (size_t)n_models * 16 * cw * 4 * 3 + (size_t)gs * 2 * cw * tn * 4 + (size_t)gs * 16 * tn * 2 + (size_t)gs * tn + 16;
 }
 
-// TN nodes per tile; DS threads share one node's tile (thread j of them takes every DS-th demand row of
-// the chunk), which raises occupancy without more shared memory; CW = words of 4 candidates per GPU
-// (0 = runtime), a template parameter so the candidate loop unrolls completely.
-template <int TN, int DS, int CW, bool K16>
-__global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a) {
-  extern __shared__ __align__(16) unsigned char smem[];
-  const MigTables* __restrict__ T = a.T;
-  const int cw = CW ? CW : ((a.cmax + 3) >> 2);
-  const int n_models = T->n_models;
-  uint32_t* s_candT = reinterpret_cast<uint32_t*>(smem);
-  uint32_t* s_candT2 = s_candT + (size_t)n_models * 16 * cw;
-  uint32_t* s_rank2 = s_candT2 + (size_t)n_models * 16 * cw * 2;
-  uint16_t* s_uf = reinterpret_cast<uint16_t*>(s_rank2 + (size_t)a.gs * 2 * cw * TN);
-  uint8_t* s_model = reinterpret_cast<uint8_t*>(s_uf + (size_t)a.gs * 16 * TN);
+// Shared-memory tile of the MIG scorers (layout above).
+struct MigTile {
+  uint32_t* candT;
+  uint32_t* candT2;
+  uint32_t* rank2;
+  uint16_t* uf;
+  uint8_t* model;
+};
+template <int TN>
+__device__ __forceinline__ MigTile mig_tile_carve(unsigned char* smem, int n_models, int gs, int cw) {
+  MigTile t;
+  t.candT = reinterpret_cast<uint32_t*>(smem);
+  t.candT2 = t.candT + (size_t)n_models * 16 * cw;
+  t.rank2 = t.candT2 + (size_t)n_models * 16 * cw * 2;
+  t.uf = reinterpret_cast<uint16_t*>(t.rank2 + (size_t)gs * 2 * cw * TN);
+  t.model = reinterpret_cast<uint8_t*>(t.uf + (size_t)gs * 16 * TN);
+  return t;
+}
 
-  const int tid = threadIdx.x % TN;   // node of the tile
-  const int dsub = threadIdx.x / TN;  // which share of the demand chunk
-  const int n = blockIdx.x * TN + tid;
+// Fills the tile: the transposed candidate tables and, per (node, slot), feasibility + the
+// demand-independent key of every candidate reduced to a rank half-word.  Ends with __syncthreads().
+template <int TN, int DS, bool K16>
+__device__ __forceinline__ void mig_tile_prologue(const MigScoreArgs& a, int cw, const MigTile& t, int tid, int dsub, int n,
+                                                  int cnt) {
+  const MigTables* __restrict__ T = a.T;
+  const int n_models = T->n_models;
+  uint32_t* s_candT = t.candT;
+  uint32_t* s_candT2 = t.candT2;
+  uint32_t* s_rank2 = t.rank2;
+  uint16_t* s_uf = t.uf;
+  uint8_t* s_model = t.model;
   // transposed candidate table (demand- and node-independent)
   for (int i = threadIdx.x; i < n_models * 16 * cw; i += TN * DS) {
     const int w = i % cw, p = (i / cw) & 15, m = i / (cw * 16);
@@ -276,8 +292,6 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
     }
   }
   // per (node, slot): feasibility + demand-independent key of every candidate, reduced to a rank byte
-  const int cnt = (n < a.N) ? a.s_cnt[n] : 0;
-  const int g0 = (n < a.N) ? a.gpu_off[n] : 0;
   for (int s = dsub; s < cnt; s += DS) {  // the DS threads of a node split its GPUs
     const uint4 u = a.s_used[(size_t)s * a.npad + n];
     const uint4 f = a.s_free[(size_t)s * a.npad + n];
@@ -308,16 +322,97 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
     }
   }
   __syncthreads();
+}
 
+// One demand row with any number of keys against one node (the general form of gpu.go:160-223 +
+// node.go:161-170); returns "the node would be updated".
+template <int TN, bool K16>
+__device__ __forceinline__ bool mig_row_generic(const MigScoreArgs& a, int cw, const MigTile& t, int tid, int cnt, int g0, int d,
+                                                int k, int e0) {
+  const uint32_t* s_candT = t.candT;
+  const uint32_t* s_rank2 = t.rank2;
+  const uint16_t* s_uf = t.uf;
+  const uint8_t* s_model = t.model;
+  bool any = false;
+  int pid[kMaxKeys], resid[kMaxKeys];
+  for (int j = 0; j < kMaxKeys; ++j) {
+    pid[j] = (j < k) ? __ldg(a.dem_key + e0 + j) : 0;
+    resid[j] = (j < k) ? max(__ldg(a.dem_qty + e0 + j), 0) : 0;
+  }
+  for (int s = 0; s < cnt; ++s) {
+    int ch = -1;
+    if (k > 0) {
+      const uint32_t* ctm = s_candT + (size_t)s_model[s * TN + tid] * 16 * cw;
+      int uj[kMaxKeys], fj[kMaxKeys];
+      for (int j = 0; j < k; ++j) {
+        const uint32_t x = s_uf[(s * 16 + pid[j]) * TN + tid];
+        fj[j] = (int)(x & 0xffu);
+        uj[j] = (int)(x >> 8) - fj[j];
+      }
+      uint32_t best = 0;
+      for (int c = 0; c < a.cmax; ++c) {
+        const uint32_t rk = (s_rank2[((size_t)s * 2 * cw + (c >> 1)) * TN + tid] >> (16 * (c & 1))) & 0xffffu;
+        if (K16 ? (rk & 0x8000u) != 0u : rk == 0u) continue;  // not applicable; else ordered by (rank, lowest index)
+        int prov = 0;
+        for (int j = 0; j < k; ++j) {
+          const int needed = resid[j] - fj[j];
+          const int add = (int)((ctm[pid[j] * cw + (c >> 2)] >> (8 * (c & 3))) & 0xffu) - (uj[j] + fj[j]);
+          if (needed > 0 && add > 0) prov += min(add, needed);
+        }
+        if (prov > 0) best = max(best, ((uint32_t)prov << 16) | rk);
+      }
+      if (best != 0u) {
+        any = true;
+        ch = K16 ? 15 - (int)(best & 15u) : 255 - (int)(best & 0xffu);
+      }
+      for (int j = 0; j < k; ++j) {
+        const int nf = (ch >= 0) ? (int)((ctm[pid[j] * cw + (ch >> 2)] >> (8 * (ch & 3))) & 0xffu) - uj[j] : fj[j];
+        resid[j] = max(resid[j] - nf, 0);
+      }
+    }
+    if (a.choice) a.choice[(size_t)d * a.tg + g0 + s] = (int8_t)ch;
+  }
+      return any;
+}
+
+// TN nodes per tile; DS threads share one node's tile (thread j of them takes every DS-th demand row of
+// the chunk), which raises occupancy without more shared memory; CW = words of 4 candidates per GPU
+// (0 = runtime), a template parameter so the candidate loop unrolls completely.
+template <int TN, int DS, int CW, bool K16>
+__global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int cw = CW ? CW : ((a.cmax + 3) >> 2);
+  const MigTile tile = mig_tile_carve<TN>(smem, a.T->n_models, a.gs, cw);
+  uint32_t* const s_candT = tile.candT;
+  uint32_t* const s_candT2 = tile.candT2;
+  uint32_t* const s_rank2 = tile.rank2;
+  uint16_t* const s_uf = tile.uf;
+  uint8_t* const s_model = tile.model;
+
+  const int tid = threadIdx.x % TN;   // node of the tile
+  const int dsub = threadIdx.x / TN;  // which share of the demand chunk
+  const int n = blockIdx.x * TN + tid;
+  const int cnt = (n < a.N) ? a.s_cnt[n] : 0;
+  const int g0 = (n < a.N) ? a.gpu_off[n] : 0;
   const int d_begin = blockIdx.y * a.d_chunk;
-  const int d_end = min(a.D, d_begin + a.d_chunk);
+  const int32_t* rl = nullptr;
+  int n_rows = a.D;
+  if (a.row_list) {
+    rl = a.row_list + a.row_meta[1];
+    n_rows = a.row_meta[2];
+    if (d_begin >= n_rows) return;  // uniform over the CTA, before any barrier
+  }
+  mig_tile_prologue<TN, DS, K16>(a, cw, tile, tid, dsub, n, cnt);
+
+  const int d_end = min(n_rows, d_begin + a.d_chunk);
   const int lane = threadIdx.x & 31;
   uint32_t k16, k8;  // opaque 2^16 and 2^8 (see the inner loop)
   asm("mov.u32 %0, 65536;" : "=r"(k16));
   asm("mov.u32 %0, 256;" : "=r"(k8));
   uint32_t k512;
   asm("mov.u32 %0, 512;" : "=r"(k512));
-  for (int d = d_begin + dsub; d < d_end; d += DS) {
+  for (int di = d_begin + dsub; di < d_end; di += DS) {
+    const int d = rl ? rl[di] : di;
     const int e0 = __ldg(a.dem_off + d), k = __ldg(a.dem_off + d + 1) - e0;  // uniform over the CTA
     bool any = false;
     if (k == 1) {
@@ -403,44 +498,7 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
       }
       any = anyacc != 0u;
     } else {
-      int pid[kMaxKeys], resid[kMaxKeys];
-      for (int j = 0; j < kMaxKeys; ++j) {
-        pid[j] = (j < k) ? __ldg(a.dem_key + e0 + j) : 0;
-        resid[j] = (j < k) ? max(__ldg(a.dem_qty + e0 + j), 0) : 0;
-      }
-      for (int s = 0; s < cnt; ++s) {
-        int ch = -1;
-        if (k > 0) {
-          const uint32_t* ctm = s_candT + (size_t)s_model[s * TN + tid] * 16 * cw;
-          int uj[kMaxKeys], fj[kMaxKeys];
-          for (int j = 0; j < k; ++j) {
-            const uint32_t x = s_uf[(s * 16 + pid[j]) * TN + tid];
-            fj[j] = (int)(x & 0xffu);
-            uj[j] = (int)(x >> 8) - fj[j];
-          }
-          uint32_t best = 0;
-          for (int c = 0; c < a.cmax; ++c) {
-            const uint32_t rk = (s_rank2[((size_t)s * 2 * cw + (c >> 1)) * TN + tid] >> (16 * (c & 1))) & 0xffffu;
-            if (K16 ? (rk & 0x8000u) != 0u : rk == 0u) continue;  // not applicable; else ordered by (rank, lowest index)
-            int prov = 0;
-            for (int j = 0; j < k; ++j) {
-              const int needed = resid[j] - fj[j];
-              const int add = (int)((ctm[pid[j] * cw + (c >> 2)] >> (8 * (c & 3))) & 0xffu) - (uj[j] + fj[j]);
-              if (needed > 0 && add > 0) prov += min(add, needed);
-            }
-            if (prov > 0) best = max(best, ((uint32_t)prov << 16) | rk);
-          }
-          if (best != 0u) {
-            any = true;
-            ch = K16 ? 15 - (int)(best & 15u) : 255 - (int)(best & 0xffu);
-          }
-          for (int j = 0; j < k; ++j) {
-            const int nf = (ch >= 0) ? (int)((ctm[pid[j] * cw + (ch >> 2)] >> (8 * (ch & 3))) & 0xffu) - uj[j] : fj[j];
-            resid[j] = max(resid[j] - nf, 0);
-          }
-        }
-        if (a.choice) a.choice[(size_t)d * a.tg + g0 + s] = (int8_t)ch;
-      }
+      any = mig_row_generic<TN, K16>(a, cw, tile, tid, cnt, g0, d, k, e0);
     }
     if (a.updated && n < a.N) a.updated[(size_t)d * a.N + n] = any ? 1 : 0;
     const int mine = any ? n : kNoNode;

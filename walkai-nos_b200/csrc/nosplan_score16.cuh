@@ -1,0 +1,303 @@
+// nosplan_score16.cuh — the MIG batched scorer for the common tables (<= 16 geometries per model,
+// quantities <= 63: 16-bit keys), organised so that the lanes of a warp stay together.
+//
+// What ncu showed on the plain tile kernel (profiles/r1e_bench_cfg5.md): one warp = 32 consecutive
+// nodes of one demand row, and a node leaves the GPU loop at the first GPU that covers the request
+// (node.go:164-169), so ~14 of 32 lanes were alive in the candidate core.  How far a node walks depends
+// on the requested profile much more than on the node.  Hence:
+//   * at snapshot time every node gets, per profile, the cost of a quantity-1 walk (GPUs visited, GPUs
+//     whose candidates get evaluated) and the nodes are counting-sorted by it, once per profile:
+//     perm[p][position] = node.  This is scheduling data only; nothing of the result is precomputed.
+//   * per scoring call the demand rows are bucketed by their profile (single-key rows; rows with
+//     several keys go to the general kernel) and cut into work items (profile, row range).
+//   * one CTA = (tile of 128 consecutive POSITIONS of perm[p], work item of profile p): its warps hold
+//     nodes that walk about equally far for that profile.  The tile only needs profile p's column of
+//     the state, so it is 28 KB instead of 60 KB.
+// The arithmetic per (row, node, GPU, candidate) is the K16 path of mig_score_kernel, unchanged.
+#pragma once
+#include "nosplan_seq.cuh"
+
+namespace nsp {
+
+constexpr int kRowCap = 512;     // rows per work item (their ids and quantities are staged in shared memory)
+constexpr int kCostBuckets = 96;  // 2 * visited + 3 * evaluated <= 5 * 16
+
+// ---- snapshot time ------------------------------------------------------------------------------------
+// cost[p][n]: relative cost of scoring a quantity-1 request of profile p on node n.
+__global__ void mig_cost_kernel(const MigTables* __restrict__ T, int N, int npad, int P, const uint4* __restrict__ s_used,
+                                const uint4* __restrict__ s_free, const uint8_t* __restrict__ s_model,
+                                const uint8_t* __restrict__ s_cnt, uint8_t* __restrict__ cost) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= npad) return;
+  const int cnt = n < N ? s_cnt[n] : 0;
+  uint32_t open = (1u << P) - 1u;  // profiles whose walk is still going
+  uint8_t c[16];
+#pragma unroll
+  for (int p = 0; p < 16; ++p) c[p] = 0;
+  for (int s = 0; s < cnt && open; ++s) {
+    const uint4 u = s_used[(size_t)s * npad + n], f = s_free[(size_t)s * npad + n];
+    const uint32_t f1 = nonzero_bytes16(f);
+    const uint32_t gm = mig_grow_mask(T, s_model[(size_t)s * npad + n], u, f);
+#pragma unroll
+    for (int p = 0; p < 16; ++p) {
+      if (!((open >> p) & 1u)) continue;
+      c[p] += 2;                         // visited
+      if (!((f1 >> p) & 1u)) c[p] += 3;  // nothing free here: its candidates get evaluated
+    }
+    open &= ~(f1 | gm);  // a free device or a geometry that adds one covers a quantity-1 request
+  }
+  for (int p = 0; p < P; ++p) cost[(size_t)p * npad + n] = c[p];
+}
+
+// perm[p][.]: nodes by descending cost (heavy tiles are scheduled first); one block per profile.
+__global__ void mig_perm_kernel(int npad, const uint8_t* __restrict__ cost, int32_t* __restrict__ perm,
+                                int32_t* __restrict__ prof_cost) {
+  __shared__ int s_off[kCostBuckets];
+  const int p = blockIdx.x;
+  const uint8_t* c = cost + (size_t)p * npad;
+  int32_t* out = perm + (size_t)p * npad;
+  for (int i = threadIdx.x; i < kCostBuckets; i += blockDim.x) s_off[i] = 0;
+  __syncthreads();
+  for (int n = threadIdx.x; n < npad; n += blockDim.x) atomicAdd(&s_off[min((int)c[n], kCostBuckets - 1)], 1);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int run = 0;
+    long long tot = 0;
+    for (int b = kCostBuckets - 1; b >= 0; --b) {
+      const int v = s_off[b];
+      s_off[b] = run;
+      run += v;
+      tot += (long long)v * b;
+    }
+    prof_cost[p] = (int32_t)min(tot, 0x7fffffffLL);  // orders the work items of a scoring call
+  }
+  __syncthreads();
+  for (int n = threadIdx.x; n < npad; n += blockDim.x) out[atomicAdd(&s_off[min((int)c[n], kCostBuckets - 1)], 1)] = n;
+}
+
+// ---- per call: rows by profile ------------------------------------------------------------------------------
+// rows[]: row ids grouped by bucket (bucket p < P: single-key rows of profile p; bucket P: every other
+// row).  meta[0] = number of work items, meta[1] = start of bucket P in rows[], meta[2] = its size.
+// work[i] = {profile, start in rows[], length <= chunk}, heaviest profile first.  Three small kernels:
+// count (grid) -> plan (one thread) -> scatter (grid).  cnt[17] must be zero on entry; plan re-zeroes it.
+__device__ __forceinline__ int mig_row_bucket(int d, int P, const int32_t* __restrict__ dem_off,
+                                              const int32_t* __restrict__ dem_key) {
+  const int e0 = __ldg(dem_off + d), k = __ldg(dem_off + d + 1) - e0;
+  if (k != 1) return P;
+  const int key = __ldg(dem_key + e0);
+  return (unsigned)key < (unsigned)P ? key : P;
+}
+
+__global__ void mig_rows_count_kernel(int D, int P, const int32_t* __restrict__ dem_off, const int32_t* __restrict__ dem_key,
+                                      uint8_t* __restrict__ rowb, int32_t* __restrict__ cnt) {
+  __shared__ int s_cnt[17];
+  if (threadIdx.x < 17) s_cnt[threadIdx.x] = 0;
+  __syncthreads();
+  const int d = blockIdx.x * blockDim.x + threadIdx.x;  // blockDim is a multiple of 32: whole warps reach the match
+  int b = 31;                                            // no row
+  if (d < D) {
+    b = mig_row_bucket(d, P, dem_off, dem_key);
+    rowb[d] = (uint8_t)b;
+  }
+  const uint32_t peers = __match_any_sync(0xffffffffu, b);  // one shared-memory atomic per bucket per warp
+  if (b != 31 && (int)(threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&s_cnt[b], __popc(peers));
+  __syncthreads();
+  if (threadIdx.x < 17 && s_cnt[threadIdx.x]) atomicAdd(&cnt[threadIdx.x], s_cnt[threadIdx.x]);
+}
+
+__global__ void mig_rows_plan_kernel(int P, int chunk, const int32_t* __restrict__ prof_cost, int32_t* __restrict__ cnt,
+                                     int32_t* __restrict__ cursor, int32_t* __restrict__ work, int32_t* __restrict__ meta) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  int off[17], run = 0;
+  for (int b = 0; b <= P; ++b) {
+    off[b] = run;
+    cursor[b] = run;
+    run += cnt[b];
+  }
+  // work items by descending profile cost: the long CTAs start first, the tail of the launch is short ones
+  int order[16];
+  for (int i = 0; i < P; ++i) {
+    int j = i;
+    while (j > 0 && prof_cost[order[j - 1]] < prof_cost[i]) {
+      order[j] = order[j - 1];
+      --j;
+    }
+    order[j] = i;
+  }
+  int nw = 0;
+  for (int i = 0; i < P; ++i) {
+    const int b = order[i];
+    for (int st = 0; st < cnt[b]; st += chunk) {
+      work[3 * nw + 0] = b;
+      work[3 * nw + 1] = off[b] + st;
+      work[3 * nw + 2] = min(chunk, cnt[b] - st);
+      ++nw;
+    }
+  }
+  meta[0] = nw;
+  meta[1] = off[P];
+  meta[2] = cnt[P];
+  for (int b = 0; b <= 16; ++b) cnt[b] = 0;  // ready for the next call
+}
+
+__global__ void mig_rows_scatter_kernel(int D, const uint8_t* __restrict__ rowb, int32_t* __restrict__ cursor,
+                                        int32_t* __restrict__ rows) {
+  const int d = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  const int b = d < D ? (int)rowb[d] : 31;
+  const uint32_t peers = __match_any_sync(0xffffffffu, b);
+  const int leader = __ffs(peers) - 1;
+  int base = 0;
+  if (b != 31 && lane == leader) base = atomicAdd(&cursor[b], __popc(peers));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  if (b != 31) rows[base + __popc(peers & ((1u << lane) - 1u))] = d;
+}
+
+// ---- the scorer -------------------------------------------------------------------------------------------
+struct MigScore16Args {
+  MigScoreArgs base;          // tables, slot-major state, demand CSR, outputs
+  const int32_t* perm;        // [P][npad]
+  const int32_t* rows;        // grouped row ids
+  const int32_t* work;        // work items
+  const int32_t* meta;
+};
+
+// Shared memory of one CTA:
+//   ct2   [n_models][2cw]  u32  profile p's quantity in every candidate, one candidate per 16-bit lane
+//   rank2 [gs][2cw][TN]    u32  per (node, slot) and candidate: rank << 4 | (15 - c), 0x8000 = cannot be applied
+//   uf    [gs][TN]         u16  free | (used + free) << 8 of profile p
+//   model [gs][TN]         u8
+//   row/qty [kRowCap]      i32  the work item's rows
+__host__ __device__ inline size_t mig_score16_smem_bytes(int n_models, int gs, int cmax, int tn) {
+  const size_t cw = (size_t)(cmax + 3) / 4;
+  return (size_t)n_models * 2 * cw * 4 + (size_t)gs * 2 * cw * tn * 4 + (size_t)gs * tn * 2 + (size_t)gs * tn + 16 +
+         (size_t)kRowCap * 8;
+}
+
+template <int TN, int DS, int CW>
+__global__ void __launch_bounds__(TN * DS, 3) mig_score16_kernel(const MigScore16Args A) {
+  const MigScoreArgs& a = A.base;
+  if ((int)blockIdx.x >= A.meta[0]) return;  // the grid is sized for the worst split of the rows
+  extern __shared__ __align__(16) unsigned char smem[];
+  constexpr int cw = CW;
+  const MigTables* __restrict__ T = a.T;
+  const int n_models = T->n_models;
+  uint32_t* const s_ct2 = reinterpret_cast<uint32_t*>(smem);
+  uint32_t* const s_rank2 = s_ct2 + (size_t)n_models * 2 * cw;
+  uint16_t* const s_uf = reinterpret_cast<uint16_t*>(s_rank2 + (size_t)a.gs * 2 * cw * TN);
+  uint8_t* const s_model = reinterpret_cast<uint8_t*>(s_uf + (size_t)a.gs * TN);
+  int32_t* const s_row = reinterpret_cast<int32_t*>(smem + ((size_t)n_models * 2 * cw * 4 + (size_t)a.gs * 2 * cw * TN * 4 +
+                                                            (size_t)a.gs * TN * 2 + (size_t)a.gs * TN + 15) / 16 * 16);
+  int32_t* const s_qty = s_row + kRowCap;
+
+  // grid: x = work item (heaviest profile first), y = tile of perm[p] (heaviest nodes first), so CTAs are
+  // handed out roughly longest-first
+  const int p = A.work[3 * blockIdx.x + 0];
+  const int r0 = A.work[3 * blockIdx.x + 1];
+  const int len = A.work[3 * blockIdx.x + 2];
+  const int tid = threadIdx.x % TN;
+  const int dsub = threadIdx.x / TN;
+  const int pos = blockIdx.y * TN + tid;
+  const int n = pos < a.npad ? A.perm[(size_t)p * a.npad + pos] : a.N;  // positions past the nodes: nothing to do
+  const int cnt = (n < a.N) ? a.s_cnt[n] : 0;
+  const int g0 = (n < a.N) ? a.gpu_off[n] : 0;
+
+  for (int i = threadIdx.x; i < len; i += TN * DS) {
+    const int d = A.rows[r0 + i];
+    s_row[i] = d;
+    s_qty[i] = min(max(__ldg(a.dem_qty + __ldg(a.dem_off + d)), 0), 65535);  // beyond 16 x 255 nothing changes
+  }
+  for (int i = threadIdx.x; i < n_models * 2 * cw; i += TN * DS) {
+    const int w = i % (2 * cw), m = i / (2 * cw);
+    const int c0 = T->geom_off[m], cc = T->geom_off[m + 1] - c0;
+    uint32_t v = 0;
+    for (int b = 0; b < 2; ++b) {
+      const int c = w * 2 + b;
+      if (c < cc) v |= byte_of(T->cand[c0 + c], p) << (16 * b);
+    }
+    s_ct2[i] = v;
+  }
+  // per (node, slot): feasibility + the demand-independent key of every candidate (gpu.go:168-188 minus
+  // countProvidedProfiles), reduced to a rank half-word
+  for (int s = dsub; s < cnt; s += DS) {
+    const uint4 u = a.s_used[(size_t)s * a.npad + n];
+    const uint4 f = a.s_free[(size_t)s * a.npad + n];
+    const int m = a.s_model[(size_t)s * a.npad + n];
+    const uint4 cur = add4(u, f);
+    const int c0 = T->geom_off[m], cc = T->geom_off[m + 1] - c0;
+    s_model[s * TN + tid] = (uint8_t)m;
+    s_uf[s * TN + tid] = (uint16_t)(byte_of(f, p) | (byte_of(cur, p) << 8));
+    uint32_t k0[16];
+#pragma unroll
+    for (int c = 0; c < 4 * cw; ++c) {
+      k0[c] = 0u;
+      if (c < cc) {
+        const uint4 cd = T->cand[c0 + c];
+        if (all_ge4(cd, u)) k0[c] = key0_of(T->total[c0 + c], sad16(cd, cur), T->rank[c0 + c]);
+      }
+    }
+#pragma unroll
+    for (int w = 0; w < 2 * cw; ++w) {
+      uint32_t r2 = 0;
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        const int c = w * 2 + b;
+        if (k0[c] != 0u) {
+          uint32_t r = 1;
+#pragma unroll
+          for (int c2 = 0; c2 < 4 * cw; ++c2) r += (k0[c2] != 0u && k0[c2] < k0[c]) ? 1u : 0u;
+          r2 |= ((r << 4) | (uint32_t)(15 - c)) << (16 * b);
+        } else {
+          r2 |= 0x8000u << (16 * b);
+        }
+      }
+      s_rank2[((size_t)s * 2 * cw + w) * TN + tid] = r2;
+    }
+  }
+  __syncthreads();
+
+  const int lane = threadIdx.x & 31;
+  uint32_t k512;  // opaque 2^9: keeps "provided << 9 | rank" an IMAD (FMA pipe) instead of ALU shift + add
+  asm("mov.u32 %0, 512;" : "=r"(k512));
+  for (int i = dsub; i < len; i += DS) {
+    const int d = s_row[i];
+    int resid = s_qty[i];
+    const uint16_t* uf = s_uf + tid;
+    const uint32_t* rk = s_rank2 + tid;
+    const uint8_t* md = s_model + tid;
+    uint32_t anyacc = 0;
+    for (int s = 0; s < cnt; ++s, uf += TN, rk += 2 * cw * TN, md += TN) {
+      // request covered: every candidate of the remaining GPUs provides 0 (gpu.go:172-175), nothing can change
+      if (resid == 0) break;
+      const uint32_t x = *uf;
+      const int needed = resid - (int)(x & 0xffu);
+      // two candidates per instruction: key = provided << 9 | rank << 4 | (15 - index) per signed 16-bit
+      // lane; a lane that cannot be applied carries 0x8000 and stays below the running maximum (>= 0)
+      uint32_t best2 = 0;
+      if (needed > 0) {
+        const uint32_t* ct2 = s_ct2 + (size_t)(*md) * (2 * cw);
+        const uint32_t nd2 = (uint32_t)min(needed, 32767) * 0x10001u;
+        const uint32_t nc2 = ((0u - (x >> 8)) & 0xffffu) * 0x10001u;  // -(used + free) in both lanes
+#pragma unroll
+        for (int w = 0; w < cw; ++w) {
+          const uint32_t ra = rk[(2 * w) * TN];
+          const uint32_t rb = rk[(2 * w + 1) * TN];
+          const uint32_t pa = __viaddmin_s16x2_relu(ct2[2 * w], nc2, nd2);
+          const uint32_t pb = __viaddmin_s16x2_relu(ct2[2 * w + 1], nc2, nd2);
+          best2 = __vimax3_s16x2(best2, pa * k512 + ra, pb * k512 + rb);
+        }
+      }
+      const uint32_t best = max(best2 & 0xffffu, best2 >> 16);
+      const uint32_t prov = best >> 9;  // 0 unless some applicable candidate provides something
+      anyacc |= prov;
+      if (a.choice && prov != 0u) a.choice[(size_t)d * a.tg + g0 + s] = (int8_t)(15 - (int)(best & 15u));
+      resid = max(needed, 0) - (int)prov;  // what is still missing after this GPU (see mig_score_kernel)
+    }
+    if (a.updated && n < a.N) a.updated[(size_t)d * a.N + n] = anyacc ? 1 : 0;
+    const int mine = anyacc ? n : kNoNode;
+    const int wmin = __reduce_min_sync(0xffffffffu, mine);
+    if (lane == 0 && wmin != kNoNode) atomicMin(a.first_node + d, wmin);
+  }
+}
+
+}  // namespace nsp
