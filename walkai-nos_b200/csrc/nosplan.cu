@@ -69,7 +69,11 @@ struct nosplan {
   DevBuf d_mig_sused, d_mig_sfree, d_mig_smodel, d_mig_scnt, d_mig_gnode, d_mig_gslot;
   bool mig_state_dirty = false;  // working copy differs from the snapshot
   DevBuf d_mig_cost, d_mig_perm;  // per-profile node order of the 16-bit-key scorer (nosplan_score16.cuh)
-  DevBuf d_rows, d_rowb, d_work, d_meta, d_rowcnt, d_profcost;  // per call: demand rows grouped by profile, work items
+  DevBuf d_profcost;
+  struct RowPlan {  // per scoring call and kind: demand rows grouped by key, work items (rows_*_kernel)
+    DevBuf rows, rowb, work, meta, cnt;
+  } rp[2];
+  DevBuf d_mps_cost, d_mps_perm, d_mps_sizecost;  // per-size node order of the MPS scorer
 
   // MPS snapshot
   bool have_mps = false;
@@ -198,6 +202,14 @@ bool wide_keys_forced() {  // measurement knob: NOSPLAN_KEY_BITS=32 forces the w
   return f;
 }
 
+bool plain_order_forced() {  // measurement knob: NOSPLAN_PLAIN_ORDER=1 scores rows and nodes in input order
+  static const bool f = [] {
+    const char* e = std::getenv("NOSPLAN_PLAIN_ORDER");
+    return e && std::atoi(e) == 1;
+  }();
+  return f;
+}
+
 int score_waves() {  // measurement knob: waves of CTAs per scorer launch
   static const int w = [] {
     const char* e = std::getenv("NOSPLAN_SCORE_WAVES");
@@ -253,6 +265,29 @@ int launch_mig_score_kernel(nosplan_t* h, const MigScoreArgs& a, dim3 grid, size
   }
 }
 
+// Groups the demand rows of one scoring call by key and cuts them into work items (rows_*_kernel);
+// max_work = the grid extent that covers any split of the rows.
+int plan_rows(nosplan_t* h, int kind, int D, int n_keys, int chunk, const int32_t* dem_off, const int32_t* dem_key,
+              const int32_t* key_cost, cudaStream_t st, int* max_work) {
+  auto& rp = h->rp[kind];
+  *max_work = (D + chunk - 1) / chunk + n_keys;  // every key may end with a short item
+  CU(rp.rows.reserve(sizeof(int32_t) * (size_t)D));
+  CU(rp.rowb.reserve((size_t)D));
+  CU(rp.work.reserve(sizeof(int32_t) * 3 * (size_t)*max_work));
+  CU(rp.meta.reserve(sizeof(int32_t) * 4));
+  if (!rp.cnt.p) {  // counters + cursors; the plan kernel leaves the counters at zero for the next call
+    CU(rp.cnt.reserve(sizeof(int32_t) * 2 * kRowBuckets));
+    CU(cudaMemsetAsync(rp.cnt.p, 0, sizeof(int32_t) * 2 * kRowBuckets, st));
+  }
+  int32_t* cnt = rp.cnt.as<int32_t>();
+  const int rb = (D + 255) / 256;
+  rows_count_kernel<<<rb, 256, 0, st>>>(D, n_keys, dem_off, dem_key, rp.rowb.as<uint8_t>(), cnt);
+  rows_plan_kernel<<<1, 32, 0, st>>>(n_keys, chunk, key_cost, cnt, cnt + kRowBuckets, rp.work.as<int32_t>(), rp.meta.as<int32_t>());
+  rows_scatter_kernel<<<rb, 256, 0, st>>>(D, rp.rowb.as<uint8_t>(), cnt + kRowBuckets, rp.rows.as<int32_t>());
+  CU(cudaGetLastError());
+  return NOSPLAN_OK;
+}
+
 template <int CW>
 int launch_mig_score16_cw(nosplan_t* h, const MigScoreArgs& a, int tiles, cudaStream_t st) {
   auto kern = mig_score16_kernel<kScoreTN, kScoreDS, CW>;
@@ -264,27 +299,16 @@ int launch_mig_score16_cw(nosplan_t* h, const MigScoreArgs& a, int tiles, cudaSt
   int chunk = 16, gy = 1;
   pick_chunks(h->sm_count, tiles, a.D, 16, &chunk, &gy, std::max(occ, 1) * score_waves());
   chunk = std::min(chunk, kRowCap);
-  const int max_work = (a.D + chunk - 1) / chunk + h->P;  // every profile may end with a short item
-  CU(h->d_rows.reserve(sizeof(int32_t) * (size_t)a.D));
-  CU(h->d_rowb.reserve((size_t)a.D));
-  CU(h->d_work.reserve(sizeof(int32_t) * 3 * (size_t)max_work));
-  CU(h->d_meta.reserve(sizeof(int32_t) * 4));
-  if (!h->d_rowcnt.p) {  // counters + cursors; the plan kernel leaves the counters at zero for the next call
-    CU(h->d_rowcnt.reserve(sizeof(int32_t) * 34));
-    CU(cudaMemsetAsync(h->d_rowcnt.p, 0, sizeof(int32_t) * 34, st));
-  }
-  int32_t* cnt = h->d_rowcnt.as<int32_t>();
-  const int rb = (a.D + 255) / 256;
-  mig_rows_count_kernel<<<rb, 256, 0, st>>>(a.D, h->P, a.dem_off, a.dem_key, h->d_rowb.as<uint8_t>(), cnt);
-  mig_rows_plan_kernel<<<1, 32, 0, st>>>(h->P, chunk, h->d_profcost.as<int32_t>(), cnt, cnt + 17, h->d_work.as<int32_t>(),
-                                         h->d_meta.as<int32_t>());
-  mig_rows_scatter_kernel<<<rb, 256, 0, st>>>(a.D, h->d_rowb.as<uint8_t>(), cnt + 17, h->d_rows.as<int32_t>());
+  int max_work = 0;
+  int rc = plan_rows(h, 0, a.D, h->P, chunk, a.dem_off, a.dem_key, h->d_profcost.as<int32_t>(), st, &max_work);
+  if (rc) return rc;
+  auto& rp = h->rp[0];
   MigScore16Args A;
   A.base = a;
   A.perm = h->d_mig_perm.as<int32_t>();
-  A.rows = h->d_rows.as<int32_t>();
-  A.work = h->d_work.as<int32_t>();
-  A.meta = h->d_meta.as<int32_t>();
+  A.rows = rp.rows.as<int32_t>();
+  A.work = rp.work.as<int32_t>();
+  A.meta = rp.meta.as<int32_t>();
   kern<<<dim3(max_work, tiles), kScoreTN * kScoreDS, smem, st>>>(A);
   CU(cudaGetLastError());
   return NOSPLAN_OK;
@@ -333,12 +357,12 @@ int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
     size_t smem = mig_score_smem(h, kScoreTN);
     if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MIG scorer tile needs %zu bytes of shared memory", smem);
     const int cw = (h->cmax + 3) / 4;
-    if (h->k16ok && cw <= 4 && tiles <= 65535 && !wide_keys_forced()) {
+    if (h->k16ok && cw <= 4 && tiles <= 65535 && !wide_keys_forced() && !plain_order_forced()) {
       // common tables: rows grouped by profile, nodes ordered per profile, 16-bit keys (nosplan_score16.cuh);
       // rows with several keys go through the general kernel below, restricted to their list
       if ((rc = launch_mig_score16(h, a, tiles, cw, st))) return rc;
-      a.row_list = h->d_rows.as<int32_t>();
-      a.row_meta = h->d_meta.as<int32_t>();
+      a.row_list = h->rp[0].rows.as<int32_t>();
+      a.row_meta = h->rp[0].meta.as<int32_t>();
     }
     if ((rc = launch_mig_score_kernel(h, a, dim3(tiles, gy), smem, st))) return rc;
   }
@@ -370,10 +394,25 @@ int launch_mps_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
     a.gs = h->mps_gs;
     int tiles = (h->mps_n + kScoreTN - 1) / kScoreTN;
     int gy;
-    pick_chunks(h->sm_count, tiles, D, 16, &a.d_chunk, &gy, 3);
+    pick_chunks(h->sm_count, tiles, D, 16, &a.d_chunk, &gy, 3 * score_waves());
     const size_t smem = mps_score_smem_bytes(h->mps_gs, h->S, kScoreTN);
     if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MPS scorer tile needs %zu bytes of shared memory", smem);
     CU(cudaFuncSetAttribute(mps_score_kernel<kScoreTN, kScoreDS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    a.mode = 0;
+    a.perm = a.rows = a.work = a.meta = nullptr;
+    if (tiles <= 65535 && !plain_order_forced()) {
+      // single-size rows grouped by size over nodes ordered per size; the rest over plain tiles
+      int max_work = 0;
+      int rc = plan_rows(h, 1, D, h->S, a.d_chunk, d_off, d_key, h->d_mps_sizecost.as<int32_t>(), st, &max_work);
+      if (rc) return rc;
+      a.perm = h->d_mps_perm.as<int32_t>();
+      a.rows = h->rp[1].rows.as<int32_t>();
+      a.work = h->rp[1].work.as<int32_t>();
+      a.meta = h->rp[1].meta.as<int32_t>();
+      a.mode = 1;
+      mps_score_kernel<kScoreTN, kScoreDS><<<dim3(max_work, tiles), kScoreTN * kScoreDS, smem, st>>>(a);
+      a.mode = 2;
+    }
     mps_score_kernel<kScoreTN, kScoreDS><<<dim3(tiles, gy), kScoreTN * kScoreDS, smem, st>>>(a);
   }
   nonode_to_minus1_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, base);
@@ -420,7 +459,9 @@ void nosplan_destroy(nosplan_t* h) {
                    &h->d_mig_used, &h->d_mig_free, &h->d_mig_sused, &h->d_mig_sfree, &h->d_mig_smodel, &h->d_mig_scnt,
                    &h->d_mps_sizes, &h->d_mps_off, &h->d_mps_valid, &h->d_mps_gpu0, &h->d_mps_ulo0, &h->d_mps_uhi0,
                    &h->d_mps_gpu, &h->d_mps_ulo, &h->d_mps_uhi, &h->d_mig_gnode, &h->d_mps_gnode, &h->d_mig_gslot, &h->d_mps_gslot, &h->d_status,
-                   &h->d_mig_cost, &h->d_mig_perm, &h->d_rows, &h->d_work, &h->d_meta, &h->d_rowb, &h->d_rowcnt, &h->d_profcost};
+                   &h->d_mig_cost, &h->d_mig_perm, &h->d_profcost, &h->d_mps_cost, &h->d_mps_perm, &h->d_mps_sizecost,
+                   &h->rp[0].rows, &h->rp[0].rowb, &h->rp[0].work, &h->rp[0].meta, &h->rp[0].cnt,
+                   &h->rp[1].rows, &h->rp[1].rowb, &h->rp[1].work, &h->rp[1].meta, &h->rp[1].cnt};
   for (DevBuf* b : all) b->release();
   for (auto& b : h->d_in) b.release();
   for (auto& b : h->d_dem) b.release();
@@ -573,7 +614,7 @@ int nosplan_set_mig_snapshot(nosplan_t* h, int n_nodes, const int32_t* gpu_off, 
     mig_cost_kernel<<<(npad + 127) / 128, 128, 0, h->stream>>>(
         h->d_tables.as<MigTables>(), n_nodes, npad, P, h->d_mig_sused.as<uint4>(), h->d_mig_sfree.as<uint4>(),
         h->d_mig_smodel.as<uint8_t>(), h->d_mig_scnt.as<uint8_t>(), h->d_mig_cost.as<uint8_t>());
-    CU(h->d_profcost.reserve(sizeof(int32_t) * 16));
+    CU(h->d_profcost.reserve(sizeof(int32_t) * 32));
     mig_perm_kernel<<<P, 1024, 0, h->stream>>>(npad, h->d_mig_cost.as<uint8_t>(), h->d_mig_perm.as<int32_t>(),
                                                h->d_profcost.as<int32_t>());
     CU(cudaGetLastError());
@@ -656,6 +697,16 @@ int nosplan_set_mps_snapshot(nosplan_t* h, int n_sizes, const int32_t* sizes_gb,
     CU(cudaMemcpyAsync(h->d_mps_gpu.p, h->d_mps_gpu0.p, sizeof(MpsGpu) * tg, cudaMemcpyDeviceToDevice, h->stream));
     CU(cudaMemcpyAsync(h->d_mps_ulo.p, h->d_mps_ulo0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, h->stream));
     CU(cudaMemcpyAsync(h->d_mps_uhi.p, h->d_mps_uhi0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, h->stream));
+    // node order per size for the scorer (scheduling data, see nosplan_score16.cuh)
+    CU(h->d_mps_cost.reserve((size_t)S * n_nodes));
+    CU(h->d_mps_perm.reserve(sizeof(int32_t) * (size_t)S * n_nodes));
+    CU(h->d_mps_sizecost.reserve(sizeof(int32_t) * 32));
+    mps_cost_kernel<<<(n_nodes + 127) / 128, 128, 0, h->stream>>>(n_nodes, S, h->d_mps_sizes.as<int32_t>(), h->d_mps_off.as<int32_t>(),
+                                                                  h->d_mps_valid.as<uint8_t>(), h->d_mps_gpu0.as<MpsGpu>(),
+                                                                  h->d_mps_cost.as<uint8_t>());
+    mig_perm_kernel<<<S, 1024, 0, h->stream>>>(n_nodes, h->d_mps_cost.as<uint8_t>(), h->d_mps_perm.as<int32_t>(),
+                                               h->d_mps_sizecost.as<int32_t>());
+    CU(cudaGetLastError());
   }
   unsigned long long st[2];
   if ((rc = status_fetch(h, h->stream, st))) return rc;

@@ -797,6 +797,15 @@ struct MpsScoreArgs {
   uint8_t* updated;
   uint8_t* out_free;    // [D][tg][S] or null
   uint32_t* out_mask;   // [D][tg] or null
+  // mode 0: rows [blockIdx.y * d_chunk, ...) of all D, tile = blockIdx.x (plain)
+  // mode 1: work item blockIdx.x = (size id, row range of rows[]), tile blockIdx.y of perm[size id]: the
+  //         nodes of a warp walk about equally far for that size (see nosplan_score16.cuh)
+  // mode 2: rows[meta[1] .. + meta[2]) (the rows with several keys), plain tiles
+  int mode;
+  const int32_t* perm;  // [S][N]
+  const int32_t* rows;
+  const int32_t* work;
+  const int32_t* meta;
 };
 
 // Shared-memory tile: per (node, slot) the free bytes as nw = ceil(S/4) words, the key mask, and
@@ -827,8 +836,27 @@ __global__ void __launch_bounds__(TN * DS, 3) mps_score_kernel(const MpsScoreArg
     s_sz[threadIdx.x] = m;
     s_inv[threadIdx.x] = m == 1 ? 0u : 0xFFFFFFFFu / (uint32_t)m + 1u;
   }
+  // which rows, which nodes (uniform over the CTA; a CTA without work leaves before any barrier)
+  const int32_t* rl = nullptr;
+  int r0 = 0, rlen = 0, tile = blockIdx.x, bucket = -1;
+  if (a.mode == 1) {
+    if ((int)blockIdx.x >= a.meta[0]) return;
+    bucket = a.work[3 * blockIdx.x];
+    rl = a.rows + a.work[3 * blockIdx.x + 1];
+    rlen = a.work[3 * blockIdx.x + 2];
+    tile = blockIdx.y;
+  } else if (a.mode == 2) {
+    r0 = blockIdx.y * a.d_chunk;
+    if (r0 >= a.meta[2]) return;
+    rl = a.rows + a.meta[1] + r0;
+    rlen = min(a.d_chunk, a.meta[2] - r0);
+  } else {
+    r0 = blockIdx.y * a.d_chunk;
+    rlen = min(a.d_chunk, a.D - r0);
+  }
   __syncthreads();
-  const int n = blockIdx.x * TN + tid;
+  const int pos = tile * TN + tid;
+  const int n = bucket >= 0 ? (pos < a.N ? a.perm[(size_t)bucket * a.N + pos] : a.N) : pos;
   const bool live = n < a.N && a.valid[n];
   const int g0 = n < a.N ? a.gpu_off[n] : 0;
   const int cnt = n < a.N ? a.gpu_off[n + 1] - g0 : 0;
@@ -846,9 +874,8 @@ __global__ void __launch_bounds__(TN * DS, 3) mps_score_kernel(const MpsScoreArg
   }
   __syncthreads();
   const int lane = threadIdx.x & 31;
-  const int d_begin = blockIdx.y * a.d_chunk;
-  const int d_end = min(a.D, d_begin + a.d_chunk);
-  for (int d = d_begin + dsub; d < d_end; d += DS) {
+  for (int i = dsub; i < rlen; i += DS) {
+    const int d = rl ? rl[i] : r0 + i;
     const int e0 = __ldg(a.dem_off + d), k = __ldg(a.dem_off + d + 1) - e0;
     bool any = false;
     if (k == 1 && !a.out_free) {

@@ -75,12 +75,45 @@ __global__ void mig_perm_kernel(int npad, const uint8_t* __restrict__ cost, int3
   for (int n = threadIdx.x; n < npad; n += blockDim.x) out[atomicAdd(&s_off[min((int)c[n], kCostBuckets - 1)], 1)] = n;
 }
 
+// MPS twin: cost[sid][n] of a quantity-1 request of size sid on node n (a GPU covers it if it has a free
+// slice of the size, or room for one once its free slices are deleted, slicing/gpu.go:188-212).
+__global__ void mps_cost_kernel(int N, int S, const int32_t* __restrict__ sizes, const int32_t* __restrict__ gpu_off,
+                                const uint8_t* __restrict__ valid, const MpsGpu* __restrict__ gp, uint8_t* __restrict__ cost) {
+  __shared__ int s_sz[kMaxSizes];
+  if (threadIdx.x < kMaxSizes) s_sz[threadIdx.x] = threadIdx.x < S ? sizes[threadIdx.x] : 0x7fffffff;
+  __syncthreads();
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  const int g0 = gpu_off[n], cnt = valid[n] ? gpu_off[n + 1] - g0 : 0;
+  uint32_t open = S >= 32 ? 0xffffffffu : ((1u << S) - 1u);
+  uint8_t c[kMaxSizes];
+#pragma unroll
+  for (int k = 0; k < kMaxSizes; ++k) c[k] = 0;
+  for (int s = 0; s < cnt && open; ++s) {
+    const MpsGpu G = gp[g0 + s];
+    const uint32_t f1 = mps_free1_mask(G.f0, G.f1);
+    uint32_t room = 0;
+#pragma unroll
+    for (int k = 0; k < kMaxSizes; ++k) room |= ((uint32_t)s_sz[k] <= G.cap) ? (1u << k) : 0u;
+#pragma unroll
+    for (int k = 0; k < kMaxSizes; ++k) {
+      if (!((open >> k) & 1u)) continue;
+      c[k] = (uint8_t)min(c[k] + 2 + (((f1 >> k) & 1u) ? 0 : 3), 255);
+    }
+    open &= ~(f1 | room);
+  }
+  for (int k = 0; k < S; ++k) cost[(size_t)k * N + n] = c[k];
+}
+
 // ---- per call: rows by profile ------------------------------------------------------------------------------
-// rows[]: row ids grouped by bucket (bucket p < P: single-key rows of profile p; bucket P: every other
+constexpr int kRowBuckets = 33;  // up to 32 keys + "any other row"
+constexpr int kNoRow = 63;
+// (MIG profiles and MPS sizes alike: "P" below is the number of keys of the kind, <= 32.)
+// rows[]: row ids grouped by bucket (bucket p < P: single-key rows of key p; bucket P: every other
 // row).  meta[0] = number of work items, meta[1] = start of bucket P in rows[], meta[2] = its size.
 // work[i] = {profile, start in rows[], length <= chunk}, heaviest profile first.  Three small kernels:
-// count (grid) -> plan (one thread) -> scatter (grid).  cnt[17] must be zero on entry; plan re-zeroes it.
-__device__ __forceinline__ int mig_row_bucket(int d, int P, const int32_t* __restrict__ dem_off,
+// count (grid) -> plan (one thread) -> scatter (grid).  cnt[kRowBuckets] must be zero on entry; plan re-zeroes it.
+__device__ __forceinline__ int row_bucket(int d, int P, const int32_t* __restrict__ dem_off,
                                               const int32_t* __restrict__ dem_key) {
   const int e0 = __ldg(dem_off + d), k = __ldg(dem_off + d + 1) - e0;
   if (k != 1) return P;
@@ -88,34 +121,34 @@ __device__ __forceinline__ int mig_row_bucket(int d, int P, const int32_t* __res
   return (unsigned)key < (unsigned)P ? key : P;
 }
 
-__global__ void mig_rows_count_kernel(int D, int P, const int32_t* __restrict__ dem_off, const int32_t* __restrict__ dem_key,
+__global__ void rows_count_kernel(int D, int P, const int32_t* __restrict__ dem_off, const int32_t* __restrict__ dem_key,
                                       uint8_t* __restrict__ rowb, int32_t* __restrict__ cnt) {
-  __shared__ int s_cnt[17];
-  if (threadIdx.x < 17) s_cnt[threadIdx.x] = 0;
+  __shared__ int s_cnt[kRowBuckets];
+  if (threadIdx.x < kRowBuckets) s_cnt[threadIdx.x] = 0;
   __syncthreads();
   const int d = blockIdx.x * blockDim.x + threadIdx.x;  // blockDim is a multiple of 32: whole warps reach the match
-  int b = 31;                                            // no row
+  int b = kNoRow;
   if (d < D) {
-    b = mig_row_bucket(d, P, dem_off, dem_key);
+    b = row_bucket(d, P, dem_off, dem_key);
     rowb[d] = (uint8_t)b;
   }
   const uint32_t peers = __match_any_sync(0xffffffffu, b);  // one shared-memory atomic per bucket per warp
-  if (b != 31 && (int)(threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&s_cnt[b], __popc(peers));
+  if (b != kNoRow && (int)(threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&s_cnt[b], __popc(peers));
   __syncthreads();
-  if (threadIdx.x < 17 && s_cnt[threadIdx.x]) atomicAdd(&cnt[threadIdx.x], s_cnt[threadIdx.x]);
+  if (threadIdx.x < kRowBuckets && s_cnt[threadIdx.x]) atomicAdd(&cnt[threadIdx.x], s_cnt[threadIdx.x]);
 }
 
-__global__ void mig_rows_plan_kernel(int P, int chunk, const int32_t* __restrict__ prof_cost, int32_t* __restrict__ cnt,
+__global__ void rows_plan_kernel(int P, int chunk, const int32_t* __restrict__ prof_cost, int32_t* __restrict__ cnt,
                                      int32_t* __restrict__ cursor, int32_t* __restrict__ work, int32_t* __restrict__ meta) {
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
-  int off[17], run = 0;
+  int off[kRowBuckets], run = 0;
   for (int b = 0; b <= P; ++b) {
     off[b] = run;
     cursor[b] = run;
     run += cnt[b];
   }
   // work items by descending profile cost: the long CTAs start first, the tail of the launch is short ones
-  int order[16];
+  int order[kRowBuckets - 1];
   for (int i = 0; i < P; ++i) {
     int j = i;
     while (j > 0 && prof_cost[order[j - 1]] < prof_cost[i]) {
@@ -137,20 +170,20 @@ __global__ void mig_rows_plan_kernel(int P, int chunk, const int32_t* __restrict
   meta[0] = nw;
   meta[1] = off[P];
   meta[2] = cnt[P];
-  for (int b = 0; b <= 16; ++b) cnt[b] = 0;  // ready for the next call
+  for (int b = 0; b < kRowBuckets; ++b) cnt[b] = 0;  // ready for the next call
 }
 
-__global__ void mig_rows_scatter_kernel(int D, const uint8_t* __restrict__ rowb, int32_t* __restrict__ cursor,
+__global__ void rows_scatter_kernel(int D, const uint8_t* __restrict__ rowb, int32_t* __restrict__ cursor,
                                         int32_t* __restrict__ rows) {
   const int d = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31;
-  const int b = d < D ? (int)rowb[d] : 31;
+  const int b = d < D ? (int)rowb[d] : kNoRow;
   const uint32_t peers = __match_any_sync(0xffffffffu, b);
   const int leader = __ffs(peers) - 1;
   int base = 0;
-  if (b != 31 && lane == leader) base = atomicAdd(&cursor[b], __popc(peers));
+  if (b != kNoRow && lane == leader) base = atomicAdd(&cursor[b], __popc(peers));
   base = __shfl_sync(0xffffffffu, base, leader);
-  if (b != 31) rows[base + __popc(peers & ((1u << lane) - 1u))] = d;
+  if (b != kNoRow) rows[base + __popc(peers & ((1u << lane) - 1u))] = d;
 }
 
 // ---- the scorer -------------------------------------------------------------------------------------------
