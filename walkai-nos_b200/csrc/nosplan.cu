@@ -69,6 +69,7 @@ struct nosplan {
   DevBuf d_mig_sused, d_mig_sfree, d_mig_smodel, d_mig_scnt, d_mig_gnode, d_mig_gslot;
   bool mig_state_dirty = false;  // working copy differs from the snapshot
   DevBuf d_mig_cost, d_mig_perm;  // per-profile node order of the 16-bit-key scorer (nosplan_score16.cuh)
+  DevBuf d_mig_rankg, d_mig_ufg;  // its snapshot-time tables
   DevBuf d_profcost;
   struct RowPlan {  // per scoring call and kind: demand rows grouped by key, work items (rows_*_kernel)
     DevBuf rows, rowb, work, meta, cnt;
@@ -213,8 +214,8 @@ bool plain_order_forced() {  // measurement knob: NOSPLAN_PLAIN_ORDER=1 scores r
 int score_waves() {  // measurement knob: waves of CTAs per scorer launch
   static const int w = [] {
     const char* e = std::getenv("NOSPLAN_SCORE_WAVES");
-    const int v = e ? std::atoi(e) : 2;
-    return v >= 1 && v <= 16 ? v : 2;
+    const int v = e ? std::atoi(e) : 4;
+    return v >= 1 && v <= 16 ? v : 4;
   }();
   return w;
 }
@@ -306,6 +307,8 @@ int launch_mig_score16_cw(nosplan_t* h, const MigScoreArgs& a, int tiles, cudaSt
   MigScore16Args A;
   A.base = a;
   A.perm = h->d_mig_perm.as<int32_t>();
+  A.rankg = h->d_mig_rankg.as<uint32_t>();
+  A.ufg = h->d_mig_ufg.as<uint16_t>();
   A.rows = rp.rows.as<int32_t>();
   A.work = rp.work.as<int32_t>();
   A.meta = rp.meta.as<int32_t>();
@@ -459,7 +462,7 @@ void nosplan_destroy(nosplan_t* h) {
                    &h->d_mig_used, &h->d_mig_free, &h->d_mig_sused, &h->d_mig_sfree, &h->d_mig_smodel, &h->d_mig_scnt,
                    &h->d_mps_sizes, &h->d_mps_off, &h->d_mps_valid, &h->d_mps_gpu0, &h->d_mps_ulo0, &h->d_mps_uhi0,
                    &h->d_mps_gpu, &h->d_mps_ulo, &h->d_mps_uhi, &h->d_mig_gnode, &h->d_mps_gnode, &h->d_mig_gslot, &h->d_mps_gslot, &h->d_status,
-                   &h->d_mig_cost, &h->d_mig_perm, &h->d_profcost, &h->d_mps_cost, &h->d_mps_perm, &h->d_mps_sizecost,
+                   &h->d_mig_cost, &h->d_mig_perm, &h->d_mig_rankg, &h->d_mig_ufg, &h->d_profcost, &h->d_mps_cost, &h->d_mps_perm, &h->d_mps_sizecost,
                    &h->rp[0].rows, &h->rp[0].rowb, &h->rp[0].work, &h->rp[0].meta, &h->rp[0].cnt,
                    &h->rp[1].rows, &h->rp[1].rowb, &h->rp[1].work, &h->rp[1].meta, &h->rp[1].cnt};
   for (DevBuf* b : all) b->release();
@@ -617,6 +620,12 @@ int nosplan_set_mig_snapshot(nosplan_t* h, int n_nodes, const int32_t* gpu_off, 
     CU(h->d_profcost.reserve(sizeof(int32_t) * 32));
     mig_perm_kernel<<<P, 1024, 0, h->stream>>>(npad, h->d_mig_cost.as<uint8_t>(), h->d_mig_perm.as<int32_t>(),
                                                h->d_profcost.as<int32_t>());
+    const int cwk = (h->cmax + 3) / 4;
+    CU(h->d_mig_rankg.reserve(sizeof(uint32_t) * (size_t)npad * gsl * 2 * cwk));
+    CU(h->d_mig_ufg.reserve(sizeof(uint16_t) * (size_t)npad * 16 * gsl));
+    mig_rank16_kernel<<<(npad * gsl + 127) / 128, 128, 0, h->stream>>>(
+        h->d_tables.as<MigTables>(), npad, gsl, cwk, h->d_mig_sused.as<uint4>(), h->d_mig_sfree.as<uint4>(),
+        h->d_mig_smodel.as<uint8_t>(), h->d_mig_scnt.as<uint8_t>(), h->d_mig_rankg.as<uint32_t>(), h->d_mig_ufg.as<uint16_t>());
     CU(cudaGetLastError());
   }
   unsigned long long st[2];

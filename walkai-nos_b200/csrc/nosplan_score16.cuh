@@ -13,6 +13,8 @@
 //   * one CTA = (tile of 128 consecutive POSITIONS of perm[p], work item of profile p): its warps hold
 //     nodes that walk about equally far for that profile.  The tile only needs profile p's column of
 //     the state, so it is 28 KB instead of 60 KB.
+//   * the demand-independent part of a candidate's score is evaluated when the snapshot arrives
+//     (mig_rank16_kernel) instead of in every CTA's prologue.
 // The arithmetic per (row, node, GPU, candidate) is the K16 path of mig_score_kernel, unchanged.
 #pragma once
 #include "nosplan_seq.cuh"
@@ -47,6 +49,53 @@ __global__ void mig_cost_kernel(const MigTables* __restrict__ T, int N, int npad
     open &= ~(f1 | gm);  // a free device or a geometry that adds one covers a quantity-1 request
   }
   for (int p = 0; p < P; ++p) cost[(size_t)p * npad + n] = c[p];
+}
+
+// The demand-independent part of gpu.go:168-188 (CanApplyGeometry, geometryDistance, totalSliceCount, the
+// id rank) depends only on the snapshot, so it is evaluated once when the snapshot arrives instead of in
+// the prologue of every CTA of every scoring call: per (node, slot) the rank half-words of all
+// candidates, and per (node, profile, slot) free | (used + free) << 8.
+//   rankg [npad][gs][2cw] u32, ufg [npad][16][gs] u16
+__global__ void mig_rank16_kernel(const MigTables* __restrict__ T, int npad, int gs, int cw, const uint4* __restrict__ s_used,
+                                  const uint4* __restrict__ s_free, const uint8_t* __restrict__ s_model,
+                                  const uint8_t* __restrict__ s_cnt, uint32_t* __restrict__ rankg, uint16_t* __restrict__ ufg) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= npad * gs) return;
+  const int n = i / gs, s = i % gs;
+  uint32_t* out = rankg + ((size_t)n * gs + s) * (2 * cw);
+  if (s >= s_cnt[n]) {
+    for (int w = 0; w < 2 * cw; ++w) out[w] = 0x80008000u;
+    for (int p = 0; p < 16; ++p) ufg[((size_t)n * 16 + p) * gs + s] = 0;
+    return;
+  }
+  const uint4 u = s_used[(size_t)s * npad + n];
+  const uint4 f = s_free[(size_t)s * npad + n];
+  const int m = s_model[(size_t)s * npad + n];
+  const uint4 cur = add4(u, f);
+  const int c0 = T->geom_off[m], cc = T->geom_off[m + 1] - c0;
+  for (int p = 0; p < 16; ++p) ufg[((size_t)n * 16 + p) * gs + s] = (uint16_t)(byte_of(f, p) | (byte_of(cur, p) << 8));
+  uint32_t k0[16];
+  for (int c = 0; c < 16; ++c) {
+    k0[c] = 0u;
+    if (c < cc) {
+      const uint4 cd = T->cand[c0 + c];
+      if (all_ge4(cd, u)) k0[c] = key0_of(T->total[c0 + c], sad16(cd, cur), T->rank[c0 + c]);
+    }
+  }
+  for (int w = 0; w < 2 * cw; ++w) {
+    uint32_t r2 = 0;
+    for (int b = 0; b < 2; ++b) {
+      const int c = w * 2 + b;
+      if (k0[c] != 0u) {
+        uint32_t r = 1;
+        for (int c2 = 0; c2 < 16; ++c2) r += (k0[c2] != 0u && k0[c2] < k0[c]) ? 1u : 0u;
+        r2 |= ((r << 4) | (uint32_t)(15 - c)) << (16 * b);
+      } else {
+        r2 |= 0x8000u << (16 * b);  // cannot be applied (or no such candidate): the lane's key stays negative
+      }
+    }
+    out[w] = r2;
+  }
 }
 
 // perm[p][.]: nodes by descending cost (heavy tiles are scheduled first); one block per profile.
@@ -190,6 +239,8 @@ __global__ void rows_scatter_kernel(int D, const uint8_t* __restrict__ rowb, int
 struct MigScore16Args {
   MigScoreArgs base;          // tables, slot-major state, demand CSR, outputs
   const int32_t* perm;        // [P][npad]
+  const uint32_t* rankg;      // [npad][gs][2cw]  (mig_rank16_kernel)
+  const uint16_t* ufg;        // [npad][16][gs]
   const int32_t* rows;        // grouped row ids
   const int32_t* work;        // work items
   const int32_t* meta;
@@ -250,42 +301,14 @@ __global__ void __launch_bounds__(TN * DS, 3) mig_score16_kernel(const MigScore1
     }
     s_ct2[i] = v;
   }
-  // per (node, slot): feasibility + the demand-independent key of every candidate (gpu.go:168-188 minus
-  // countProvidedProfiles), reduced to a rank half-word
+  // per (node, slot): the rank half-words of the candidates and profile p's counts, made when the snapshot
+  // arrived (mig_rank16_kernel); the DS threads of a node split its GPUs
   for (int s = dsub; s < cnt; s += DS) {
-    const uint4 u = a.s_used[(size_t)s * a.npad + n];
-    const uint4 f = a.s_free[(size_t)s * a.npad + n];
-    const int m = a.s_model[(size_t)s * a.npad + n];
-    const uint4 cur = add4(u, f);
-    const int c0 = T->geom_off[m], cc = T->geom_off[m + 1] - c0;
-    s_model[s * TN + tid] = (uint8_t)m;
-    s_uf[s * TN + tid] = (uint16_t)(byte_of(f, p) | (byte_of(cur, p) << 8));
-    uint32_t k0[16];
+    const uint32_t* src = A.rankg + ((size_t)n * a.gs + s) * (2 * cw);
 #pragma unroll
-    for (int c = 0; c < 4 * cw; ++c) {
-      k0[c] = 0u;
-      if (c < cc) {
-        const uint4 cd = T->cand[c0 + c];
-        if (all_ge4(cd, u)) k0[c] = key0_of(T->total[c0 + c], sad16(cd, cur), T->rank[c0 + c]);
-      }
-    }
-#pragma unroll
-    for (int w = 0; w < 2 * cw; ++w) {
-      uint32_t r2 = 0;
-#pragma unroll
-      for (int b = 0; b < 2; ++b) {
-        const int c = w * 2 + b;
-        if (k0[c] != 0u) {
-          uint32_t r = 1;
-#pragma unroll
-          for (int c2 = 0; c2 < 4 * cw; ++c2) r += (k0[c2] != 0u && k0[c2] < k0[c]) ? 1u : 0u;
-          r2 |= ((r << 4) | (uint32_t)(15 - c)) << (16 * b);
-        } else {
-          r2 |= 0x8000u << (16 * b);
-        }
-      }
-      s_rank2[((size_t)s * 2 * cw + w) * TN + tid] = r2;
-    }
+    for (int w = 0; w < 2 * cw; ++w) s_rank2[((size_t)s * 2 * cw + w) * TN + tid] = __ldg(src + w);
+    s_uf[s * TN + tid] = __ldg(A.ufg + ((size_t)n * 16 + p) * a.gs + s);
+    s_model[s * TN + tid] = a.s_model[(size_t)s * a.npad + n];
   }
   __syncthreads();
 
