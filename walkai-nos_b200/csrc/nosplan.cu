@@ -289,9 +289,9 @@ int plan_rows(nosplan_t* h, int kind, int D, int n_keys, int chunk, const int32_
   return NOSPLAN_OK;
 }
 
-template <int CW>
+template <int CW, bool OUT>
 int launch_mig_score16_cw(nosplan_t* h, const MigScoreArgs& a, int tiles, cudaStream_t st) {
-  auto kern = mig_score16_kernel<kScoreTN, kScoreDS, CW>;
+  auto kern = mig_score16_kernel<kScoreTN, kScoreDS, CW, OUT>;
   const size_t smem = mig_score16_smem_bytes(h->h_tables.n_models, a.gs, a.cmax, kScoreTN);
   if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MIG scorer tile needs %zu bytes of shared memory", smem);
   CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -317,11 +317,12 @@ int launch_mig_score16_cw(nosplan_t* h, const MigScoreArgs& a, int tiles, cudaSt
   return NOSPLAN_OK;
 }
 int launch_mig_score16(nosplan_t* h, const MigScoreArgs& a, int tiles, int cw, cudaStream_t st) {
+  const bool out = a.updated || a.choice;
   switch (cw) {
-    case 1: return launch_mig_score16_cw<1>(h, a, tiles, st);
-    case 2: return launch_mig_score16_cw<2>(h, a, tiles, st);
-    case 3: return launch_mig_score16_cw<3>(h, a, tiles, st);
-    default: return launch_mig_score16_cw<4>(h, a, tiles, st);
+    case 1: return out ? launch_mig_score16_cw<1, true>(h, a, tiles, st) : launch_mig_score16_cw<1, false>(h, a, tiles, st);
+    case 2: return out ? launch_mig_score16_cw<2, true>(h, a, tiles, st) : launch_mig_score16_cw<2, false>(h, a, tiles, st);
+    case 3: return out ? launch_mig_score16_cw<3, true>(h, a, tiles, st) : launch_mig_score16_cw<3, false>(h, a, tiles, st);
+    default: return out ? launch_mig_score16_cw<4, true>(h, a, tiles, st) : launch_mig_score16_cw<4, false>(h, a, tiles, st);
   }
 }
 

@@ -246,33 +246,48 @@ struct MigScore16Args {
   const int32_t* meta;
 };
 
-// Shared memory of one CTA:
-//   ct2   [n_models][2cw]  u32  profile p's quantity in every candidate, one candidate per 16-bit lane
-//   rank2 [gs][2cw][TN]    u32  per (node, slot) and candidate: rank << 4 | (15 - c), 0x8000 = cannot be applied
-//   uf    [gs][TN]         u16  free | (used + free) << 8 of profile p
-//   model [gs][TN]         u8
-//   row/qty [kRowCap]      i32  the work item's rows
+// Shared memory of one CTA (all u32, addressed through 32-bit shared-window addresses):
+//   ct2   [n_models][2cw]        profile p's quantity in every candidate, one candidate per 16-bit lane
+//   slot  [gs][2cw + 2][TN]      per GPU slot, one column per node: 2cw words of rank half-words
+//                                (rank << 4 | (15 - c), 0x8000 = cannot be applied), then
+//                                uf = free | (-(used + free) & 0xffff) << 16 of profile p, then
+//                                mo = shared address of the ct2 row of the GPU's model
+//   row/qty [kRowCap]            the work item's rows
+// One pointer walks the slots (stride (2cw + 2) * TN words), every load has a constant offset from it.
 __host__ __device__ inline size_t mig_score16_smem_bytes(int n_models, int gs, int cmax, int tn) {
   const size_t cw = (size_t)(cmax + 3) / 4;
-  return (size_t)n_models * 2 * cw * 4 + (size_t)gs * 2 * cw * tn * 4 + (size_t)gs * tn * 2 + (size_t)gs * tn + 16 +
-         (size_t)kRowCap * 8;
+  return ((size_t)n_models * 2 * cw * 4 + 15) / 16 * 16 + (size_t)gs * (2 * cw + 2) * tn * 4 + (size_t)kRowCap * 8;
 }
 
-template <int TN, int DS, int CW>
+__device__ __forceinline__ uint32_t lds_u32(uint32_t saddr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(saddr));
+  return v;
+}
+__device__ __forceinline__ uint2 lds_v2(uint32_t saddr) {
+  uint2 v;
+  asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(saddr));
+  return v;
+}
+
+// OUT: the call wants updated[] / choice[] (the per-row stores stay out of the hot instantiation)
+template <int TN, int DS, int CW, bool OUT>
 __global__ void __launch_bounds__(TN * DS, 3) mig_score16_kernel(const MigScore16Args A) {
   const MigScoreArgs& a = A.base;
   if ((int)blockIdx.x >= A.meta[0]) return;  // the grid is sized for the worst split of the rows
   extern __shared__ __align__(16) unsigned char smem[];
   constexpr int cw = CW;
+  constexpr uint32_t kSlotStride = (2 * cw + 2) * TN * 4;  // bytes
+  constexpr uint32_t kUfOff = 2 * cw * TN * 4;
+  constexpr uint32_t kMoOff = (2 * cw + 1) * TN * 4;
   const MigTables* __restrict__ T = a.T;
   const int n_models = T->n_models;
+  const size_t ct2_bytes = ((size_t)n_models * 2 * cw * 4 + 15) / 16 * 16;
   uint32_t* const s_ct2 = reinterpret_cast<uint32_t*>(smem);
-  uint32_t* const s_rank2 = s_ct2 + (size_t)n_models * 2 * cw;
-  uint16_t* const s_uf = reinterpret_cast<uint16_t*>(s_rank2 + (size_t)a.gs * 2 * cw * TN);
-  uint8_t* const s_model = reinterpret_cast<uint8_t*>(s_uf + (size_t)a.gs * TN);
-  int32_t* const s_row = reinterpret_cast<int32_t*>(smem + ((size_t)n_models * 2 * cw * 4 + (size_t)a.gs * 2 * cw * TN * 4 +
-                                                            (size_t)a.gs * TN * 2 + (size_t)a.gs * TN + 15) / 16 * 16);
+  uint32_t* const s_slot = reinterpret_cast<uint32_t*>(smem + ct2_bytes);
+  int32_t* const s_row = reinterpret_cast<int32_t*>(smem + ct2_bytes + (size_t)a.gs * kSlotStride);
   int32_t* const s_qty = s_row + kRowCap;
+  const uint32_t ct2_saddr = (uint32_t)__cvta_generic_to_shared(s_ct2);
 
   // grid: x = work item (heaviest profile first), y = tile of perm[p] (heaviest nodes first), so CTAs are
   // handed out roughly longest-first
@@ -289,7 +304,8 @@ __global__ void __launch_bounds__(TN * DS, 3) mig_score16_kernel(const MigScore1
   for (int i = threadIdx.x; i < len; i += TN * DS) {
     const int d = A.rows[r0 + i];
     s_row[i] = d;
-    s_qty[i] = min(max(__ldg(a.dem_qty + __ldg(a.dem_off + d)), 0), 65535);  // beyond 16 x 255 nothing changes
+    // beyond 16 GPUs x 255 devices a quantity can never be covered: larger values behave the same
+    s_qty[i] = min(max(__ldg(a.dem_qty + __ldg(a.dem_off + d)), 0), 32767);
   }
   for (int i = threadIdx.x; i < n_models * 2 * cw; i += TN * DS) {
     const int w = i % (2 * cw), m = i / (2 * cw);
@@ -304,52 +320,58 @@ __global__ void __launch_bounds__(TN * DS, 3) mig_score16_kernel(const MigScore1
   // per (node, slot): the rank half-words of the candidates and profile p's counts, made when the snapshot
   // arrived (mig_rank16_kernel); the DS threads of a node split its GPUs
   for (int s = dsub; s < cnt; s += DS) {
+    uint32_t* col = s_slot + (size_t)s * (2 * cw + 2) * TN + tid;
     const uint32_t* src = A.rankg + ((size_t)n * a.gs + s) * (2 * cw);
 #pragma unroll
-    for (int w = 0; w < 2 * cw; ++w) s_rank2[((size_t)s * 2 * cw + w) * TN + tid] = __ldg(src + w);
-    s_uf[s * TN + tid] = __ldg(A.ufg + ((size_t)n * 16 + p) * a.gs + s);
-    s_model[s * TN + tid] = a.s_model[(size_t)s * a.npad + n];
+    for (int w = 0; w < 2 * cw; ++w) col[w * TN] = __ldg(src + w);
+    const uint32_t x = __ldg(A.ufg + ((size_t)n * 16 + p) * a.gs + s);  // free | (used + free) << 8
+    col[2 * cw * TN] = (x & 0xffu) | (((0u - (x >> 8)) & 0xffffu) << 16);
+    col[(2 * cw + 1) * TN] = ct2_saddr + (uint32_t)a.s_model[(size_t)s * a.npad + n] * (2 * cw * 4);
   }
   __syncthreads();
 
   const int lane = threadIdx.x & 31;
   uint32_t k512;  // opaque 2^9: keeps "provided << 9 | rank" an IMAD (FMA pipe) instead of ALU shift + add
   asm("mov.u32 %0, 512;" : "=r"(k512));
+  const uint32_t ps0 = (uint32_t)__cvta_generic_to_shared(s_slot) + (uint32_t)tid * 4u;
   for (int i = dsub; i < len; i += DS) {
-    const int d = s_row[i];
     int resid = s_qty[i];
-    const uint16_t* uf = s_uf + tid;
-    const uint32_t* rk = s_rank2 + tid;
-    const uint8_t* md = s_model + tid;
     uint32_t anyacc = 0;
-    for (int s = 0; s < cnt; ++s, uf += TN, rk += 2 * cw * TN, md += TN) {
+    uint32_t ps = ps0;
+    for (int s = 0; s < cnt; ++s, ps += kSlotStride) {
       // request covered: every candidate of the remaining GPUs provides 0 (gpu.go:172-175), nothing can change
       if (resid == 0) break;
-      const uint32_t x = *uf;
+      const uint32_t x = lds_u32(ps + kUfOff);
       const int needed = resid - (int)(x & 0xffu);
       // two candidates per instruction: key = provided << 9 | rank << 4 | (15 - index) per signed 16-bit
       // lane; a lane that cannot be applied carries 0x8000 and stays below the running maximum (>= 0)
       uint32_t best2 = 0;
       if (needed > 0) {
-        const uint32_t* ct2 = s_ct2 + (size_t)(*md) * (2 * cw);
-        const uint32_t nd2 = (uint32_t)min(needed, 32767) * 0x10001u;
-        const uint32_t nc2 = ((0u - (x >> 8)) & 0xffffu) * 0x10001u;  // -(used + free) in both lanes
+        const uint32_t mo = lds_u32(ps + kMoOff);
+        const uint32_t nd2 = (uint32_t)needed * 0x10001u;
+        const uint32_t nc2 = __byte_perm(x, 0u, 0x3232u);  // -(used + free) in both lanes
 #pragma unroll
         for (int w = 0; w < cw; ++w) {
-          const uint32_t ra = rk[(2 * w) * TN];
-          const uint32_t rb = rk[(2 * w + 1) * TN];
-          const uint32_t pa = __viaddmin_s16x2_relu(ct2[2 * w], nc2, nd2);
-          const uint32_t pb = __viaddmin_s16x2_relu(ct2[2 * w + 1], nc2, nd2);
+          const uint32_t ra = lds_u32(ps + (2 * w) * TN * 4);
+          const uint32_t rb = lds_u32(ps + (2 * w + 1) * TN * 4);
+          const uint2 c2 = lds_v2(mo + 8 * w);
+          const uint32_t pa = __viaddmin_s16x2_relu(c2.x, nc2, nd2);
+          const uint32_t pb = __viaddmin_s16x2_relu(c2.y, nc2, nd2);
           best2 = __vimax3_s16x2(best2, pa * k512 + ra, pb * k512 + rb);
         }
       }
       const uint32_t best = max(best2 & 0xffffu, best2 >> 16);
       const uint32_t prov = best >> 9;  // 0 unless some applicable candidate provides something
       anyacc |= prov;
-      if (a.choice && prov != 0u) a.choice[(size_t)d * a.tg + g0 + s] = (int8_t)(15 - (int)(best & 15u));
+      if constexpr (OUT) {
+        if (a.choice && prov != 0u) a.choice[(size_t)s_row[i] * a.tg + g0 + s] = (int8_t)(15 - (int)(best & 15u));
+      }
       resid = max(needed, 0) - (int)prov;  // what is still missing after this GPU (see mig_score_kernel)
     }
-    if (a.updated && n < a.N) a.updated[(size_t)d * a.N + n] = anyacc ? 1 : 0;
+    const int d = s_row[i];
+    if constexpr (OUT) {
+      if (a.updated && n < a.N) a.updated[(size_t)d * a.N + n] = anyacc ? 1 : 0;
+    }
     const int mine = anyacc ? n : kNoNode;
     const int wmin = __reduce_min_sync(0xffffffffu, mine);
     if (lane == 0 && wmin != kNoNode) atomicMin(a.first_node + d, wmin);
