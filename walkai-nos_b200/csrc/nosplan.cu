@@ -407,14 +407,26 @@ int launch_mps_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
     if (tiles <= 65535 && !plain_order_forced()) {
       // single-size rows grouped by size over nodes ordered per size; the rest over plain tiles
       int max_work = 0;
-      int rc = plan_rows(h, 1, D, h->S, a.d_chunk, d_off, d_key, h->d_mps_sizecost.as<int32_t>(), st, &max_work);
+      int rc = plan_rows(h, 1, D, h->S, std::min(a.d_chunk, kRowCap), d_off, d_key, h->d_mps_sizecost.as<int32_t>(), st, &max_work);
       if (rc) return rc;
       a.perm = h->d_mps_perm.as<int32_t>();
       a.rows = h->rp[1].rows.as<int32_t>();
       a.work = h->rp[1].work.as<int32_t>();
       a.meta = h->rp[1].meta.as<int32_t>();
       a.mode = 1;
-      mps_score_kernel<kScoreTN, kScoreDS><<<dim3(max_work, tiles), kScoreTN * kScoreDS, smem, st>>>(a);
+      if (!d_free) {  // first_node / updated only: the per-size kernel
+        const size_t smem1 = mps_score1_smem_bytes(h->mps_gs, h->S, kScoreTN);
+        if (smem1 > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MPS scorer tile needs %zu bytes of shared memory", smem1);
+        if (d_updated) {
+          CU(cudaFuncSetAttribute(mps_score1_kernel<kScoreTN, kScoreDS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
+          mps_score1_kernel<kScoreTN, kScoreDS, true><<<dim3(max_work, tiles), kScoreTN * kScoreDS, smem1, st>>>(a);
+        } else {
+          CU(cudaFuncSetAttribute(mps_score1_kernel<kScoreTN, kScoreDS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
+          mps_score1_kernel<kScoreTN, kScoreDS, false><<<dim3(max_work, tiles), kScoreTN * kScoreDS, smem1, st>>>(a);
+        }
+      } else {
+        mps_score_kernel<kScoreTN, kScoreDS><<<dim3(max_work, tiles), kScoreTN * kScoreDS, smem, st>>>(a);
+      }
       a.mode = 2;
     }
     mps_score_kernel<kScoreTN, kScoreDS><<<dim3(tiles, gy), kScoreTN * kScoreDS, smem, st>>>(a);

@@ -378,4 +378,113 @@ __global__ void __launch_bounds__(TN * DS, 3) mig_score16_kernel(const MigScore1
   }
 }
 
+// ---- MPS scorer for the rows of one size (mode 1 of mps_score_kernel, first_node / updated only) ---------------
+// Same closed form of slicing.GPU.UpdateGeometryFor as mps_score_kernel's single-size path; the size is
+// uniform over the CTA, so everything that depends on it is hoisted, the rows are staged in shared
+// memory and one pointer walks the GPU slots.
+// Shared memory (u32): slot [gs][3 + nw][TN]: A = free[sid] | (sid in FreeProfiles) << 8,
+// B = spare | origtot << 16 (spare = cap - origtot, origtot = GB held by free slices), M = key mask,
+// then the nw words of free bytes (only the restore walk reads them); row/qty [kRowCap].
+__host__ __device__ inline size_t mps_score1_smem_bytes(int gs, int S, int tn) {
+  const size_t nw = (size_t)(S + 3) / 4;
+  return (size_t)gs * (3 + nw) * tn * 4 + (size_t)kRowCap * 8;
+}
+
+template <int TN, int DS, bool OUT>
+__global__ void __launch_bounds__(TN * DS, 3) mps_score1_kernel(const MpsScoreArgs a) {
+  if ((int)blockIdx.x >= a.meta[0]) return;
+  extern __shared__ __align__(16) unsigned char smem[];
+  __shared__ int s_sz[kMaxSizes];
+  const int nw = (a.S + 3) >> 2;
+  const uint32_t slot_stride = (uint32_t)(3 + nw) * TN * 4;  // bytes
+  uint32_t* const s_slot = reinterpret_cast<uint32_t*>(smem);
+  int32_t* const s_row = reinterpret_cast<int32_t*>(smem + (size_t)a.gs * slot_stride);
+  int32_t* const s_qty = s_row + kRowCap;
+  const int sid = a.work[3 * blockIdx.x];
+  const int32_t* rl = a.rows + a.work[3 * blockIdx.x + 1];
+  const int len = a.work[3 * blockIdx.x + 2];
+  const int tid = threadIdx.x % TN;
+  const int dsub = threadIdx.x / TN;
+  const int pos = blockIdx.y * TN + tid;
+  const int n = pos < a.N ? a.perm[(size_t)sid * a.N + pos] : a.N;
+  const bool live = n < a.N && a.valid[n];
+  const int g0 = n < a.N ? a.gpu_off[n] : 0;
+  const int cnt = live ? a.gpu_off[n + 1] - g0 : 0;  // an invalid node is never updated
+  if (threadIdx.x < kMaxSizes) s_sz[threadIdx.x] = threadIdx.x < a.S ? a.sizes[threadIdx.x] : 1;
+  for (int i = threadIdx.x; i < len; i += TN * DS) {
+    const int d = rl[i];
+    s_row[i] = d;
+    s_qty[i] = max(__ldg(a.dem_qty + __ldg(a.dem_off + d)), 0);
+  }
+  __syncthreads();
+  for (int s = dsub; s < cnt; s += DS) {  // the DS threads of a node split its GPUs
+    const MpsGpu G = a.gp[g0 + s];
+    int origtot = 0;
+    for (uint32_t mk = G.fmask; mk; mk &= mk - 1) {
+      const int key = __ffs(mk) - 1;
+      origtot += s_sz[key] * (int)mps_byte(G.f0, G.f1, key);
+    }
+    uint32_t* col = s_slot + (size_t)s * (3 + nw) * TN + tid;
+    col[0] = mps_byte(G.f0, G.f1, sid) | (((G.fmask >> sid) & 1u) << 8);
+    col[TN] = ((uint32_t)origtot << 16) | (uint32_t)((int)G.cap - origtot);
+    col[2 * TN] = G.fmask;
+    const uint32_t w[8] = {G.f0.x, G.f0.y, G.f0.z, G.f0.w, G.f1.x, G.f1.y, G.f1.z, G.f1.w};
+    for (int i = 0; i < nw; ++i) col[(3 + i) * TN] = w[i];
+  }
+  __syncthreads();
+
+  const int lane = threadIdx.x & 31;
+  const int m = s_sz[sid];
+  const uint32_t inv = m == 1 ? 0u : 0xFFFFFFFFu / (uint32_t)m + 1u;  // exact multiply-high division (div_small)
+  const uint32_t ps0 = (uint32_t)__cvta_generic_to_shared(s_slot) + (uint32_t)tid * 4u;
+  for (int i = dsub; i < len; i += DS) {
+    int resid = s_qty[i];
+    bool any = false;
+    uint32_t ps = ps0;
+    for (int s = 0; s < cnt && resid > 0; ++s, ps += slot_stride) {
+      const uint32_t A = lds_u32(ps);
+      const int fj = (int)(A & 0xffu);
+      const int miss = resid - fj;  // getMissingSlices
+      if (miss <= 0) break;         // this GPU already provides it; the residual drops to 0
+      const uint32_t sp = lds_u32(ps + TN * 4);
+      const int otot = (int)(sp >> 16);
+      int spare = (int)(sp & 0xffffu);
+      const bool in_orig = (A >> 8) != 0u;
+      // (a) spare capacity first
+      const int k1 = min(miss, div_small(spare, m, inv));
+      // (b) every original free key is deleted — with it whatever (a) created under such a key
+      spare = spare - k1 * m + otot + (in_orig ? k1 * m : 0);
+      int created = in_orig ? 0 : k1;
+      // (c) create in the space made
+      const int k2 = min(miss - k1, div_small(spare, m, inv));
+      created += k2;
+      spare -= k2 * m;
+      const bool upd = (k1 | k2) > 0;
+      // (d) restore the original keys, ascending size, each all-or-nothing
+      bool restored_sid = in_orig;
+      if (spare < otot) {
+        restored_sid = false;
+        for (uint32_t mk = lds_u32(ps + 2 * TN * 4); mk; mk &= mk - 1) {
+          const int key = __ffs(mk) - 1;
+          const int need = s_sz[key] * (int)((lds_u32(ps + (3 + (key >> 2)) * TN * 4) >> ((key & 3) * 8)) & 0xffu);
+          if (spare >= need) {
+            spare -= need;
+            if (key == sid) restored_sid = true;
+          }
+        }
+      }
+      const int nf = upd ? created + (restored_sid ? fj : 0) : fj;
+      any |= upd;
+      resid = max(resid - nf, 0);
+    }
+    const int d = s_row[i];
+    if constexpr (OUT) {
+      if (a.updated && n < a.N) a.updated[(size_t)d * a.N + n] = any ? 1 : 0;
+    }
+    const int mine = any ? n : kNoNode;
+    const int wmin = __reduce_min_sync(0xffffffffu, mine);
+    if (lane == 0 && wmin != kNoNode) atomicMin(a.first_node + d, wmin);
+  }
+}
+
 }  // namespace nsp
