@@ -171,7 +171,7 @@ __device__ __forceinline__ int row_bucket(int d, int P, const int32_t* __restric
 }
 
 __global__ void rows_count_kernel(int D, int P, const int32_t* __restrict__ dem_off, const int32_t* __restrict__ dem_key,
-                                      uint8_t* __restrict__ rowb, int32_t* __restrict__ cnt) {
+                                  uint8_t* __restrict__ rowb, int32_t* __restrict__ cnt) {
   __shared__ int s_cnt[kRowBuckets];
   if (threadIdx.x < kRowBuckets) s_cnt[threadIdx.x] = 0;
   __syncthreads();
@@ -188,38 +188,51 @@ __global__ void rows_count_kernel(int D, int P, const int32_t* __restrict__ dem_
 }
 
 __global__ void rows_plan_kernel(int P, int chunk, const int32_t* __restrict__ prof_cost, int32_t* __restrict__ cnt,
-                                     int32_t* __restrict__ cursor, int32_t* __restrict__ work, int32_t* __restrict__ meta) {
-  if (threadIdx.x != 0 || blockIdx.x != 0) return;
-  int off[kRowBuckets], run = 0;
-  for (int b = 0; b <= P; ++b) {
-    off[b] = run;
-    cursor[b] = run;
-    run += cnt[b];
+                                 int32_t* __restrict__ cursor, int32_t* __restrict__ work, int32_t* __restrict__ meta) {
+  // one warp: lane b holds bucket b (P <= 32; bucket P is read by lane 0 as well)
+  const int lane = threadIdx.x;
+  const uint32_t full = 0xffffffffu;
+  const int my_cnt = lane < P ? cnt[lane] : 0;
+  const int my_cost = lane < P ? prof_cost[lane] : -1;
+  const int rest = cnt[P];
+  // offsets in rows[] (bucket order) by an exclusive prefix sum over the lanes
+  int incl = my_cnt;
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(full, incl, o);
+    if (lane >= o) incl += v;
   }
-  // work items by descending profile cost: the long CTAs start first, the tail of the launch is short ones
-  int order[kRowBuckets - 1];
-  for (int i = 0; i < P; ++i) {
-    int j = i;
-    while (j > 0 && prof_cost[order[j - 1]] < prof_cost[i]) {
-      order[j] = order[j - 1];
-      --j;
+  const int my_off = incl - my_cnt;
+  const int total = __shfl_sync(full, incl, 31);
+  if (lane < P) cursor[lane] = my_off;
+  if (lane == 0) cursor[P] = total;
+  // work items by descending key cost (ties: lower key first): the long CTAs start first
+  int rank = 0;
+  for (int j = 0; j < 32; ++j) {
+    const int cj = __shfl_sync(full, my_cost, j);
+    if (j < P && (cj > my_cost || (cj == my_cost && j < lane))) ++rank;
+  }
+  const int my_items = (my_cnt + chunk - 1) / chunk;
+  // items of the keys ranked before mine
+  int before = 0;
+  for (int j = 0; j < 32; ++j) {
+    const int rj = __shfl_sync(full, rank, j), ij = __shfl_sync(full, my_items, j);
+    if (j < P && rj < rank) before += ij;
+  }
+  if (lane < P)
+    for (int it = 0; it < my_items; ++it) {
+      work[3 * (before + it) + 0] = lane;
+      work[3 * (before + it) + 1] = my_off + it * chunk;
+      work[3 * (before + it) + 2] = min(chunk, my_cnt - it * chunk);
     }
-    order[j] = i;
+  int nw = lane < P ? my_items : 0;
+  for (int o = 16; o; o >>= 1) nw += __shfl_xor_sync(full, nw, o);
+  if (lane == 0) {
+    meta[0] = nw;
+    meta[1] = total;
+    meta[2] = rest;
   }
-  int nw = 0;
-  for (int i = 0; i < P; ++i) {
-    const int b = order[i];
-    for (int st = 0; st < cnt[b]; st += chunk) {
-      work[3 * nw + 0] = b;
-      work[3 * nw + 1] = off[b] + st;
-      work[3 * nw + 2] = min(chunk, cnt[b] - st);
-      ++nw;
-    }
-  }
-  meta[0] = nw;
-  meta[1] = off[P];
-  meta[2] = cnt[P];
-  for (int b = 0; b < kRowBuckets; ++b) cnt[b] = 0;  // ready for the next call
+  __syncwarp();
+  for (int b = lane; b < kRowBuckets; b += 32) cnt[b] = 0;  // ready for the next call
 }
 
 __global__ void rows_scatter_kernel(int D, const uint8_t* __restrict__ rowb, int32_t* __restrict__ cursor,
