@@ -72,7 +72,7 @@ struct nosplan {
   DevBuf d_mig_rankg, d_mig_ufg;  // its snapshot-time tables
   DevBuf d_profcost;
   struct RowPlan {  // per scoring call and kind: demand rows grouped by key, work items (rows_*_kernel)
-    DevBuf rows, rowb, work, meta, cnt;
+    DevBuf rows, work, meta, cnt;
   } rp[2];
   DevBuf d_mps_cost, d_mps_perm, d_mps_sizecost;  // per-size node order of the MPS scorer
 
@@ -266,25 +266,22 @@ int launch_mig_score_kernel(nosplan_t* h, const MigScoreArgs& a, dim3 grid, size
   }
 }
 
-// Groups the demand rows of one scoring call by key and cuts them into work items (rows_*_kernel);
-// max_work = the grid extent that covers any split of the rows.
+// Groups the demand rows of one scoring call by key and cuts them into work items (rows_group_kernel, which
+// also puts first_node[] to rest); max_work = the grid extent that covers any split of the rows.
 int plan_rows(nosplan_t* h, int kind, int D, int n_keys, int chunk, const int32_t* dem_off, const int32_t* dem_key,
-              const int32_t* key_cost, cudaStream_t st, int* max_work) {
+              const int32_t* key_cost, int32_t* first_node, cudaStream_t st, int* max_work) {
   auto& rp = h->rp[kind];
   *max_work = (D + chunk - 1) / chunk + n_keys;  // every key may end with a short item
-  CU(rp.rows.reserve(sizeof(int32_t) * (size_t)D));
-  CU(rp.rowb.reserve((size_t)D));
+  CU(rp.rows.reserve(sizeof(int32_t) * (size_t)D * (n_keys + 1)));
   CU(rp.work.reserve(sizeof(int32_t) * 3 * (size_t)*max_work));
   CU(rp.meta.reserve(sizeof(int32_t) * 4));
-  if (!rp.cnt.p) {  // counters + cursors; the plan kernel leaves the counters at zero for the next call
-    CU(rp.cnt.reserve(sizeof(int32_t) * 2 * kRowBuckets));
-    CU(cudaMemsetAsync(rp.cnt.p, 0, sizeof(int32_t) * 2 * kRowBuckets, st));
+  if (!rp.cnt.p) {  // cursors + ticket; the kernel leaves them at zero for the next call
+    CU(rp.cnt.reserve(sizeof(int32_t) * (kRowBuckets + 1)));
+    CU(cudaMemsetAsync(rp.cnt.p, 0, sizeof(int32_t) * (kRowBuckets + 1), st));
   }
-  int32_t* cnt = rp.cnt.as<int32_t>();
-  const int rb = (D + 255) / 256;
-  rows_count_kernel<<<rb, 256, 0, st>>>(D, n_keys, dem_off, dem_key, rp.rowb.as<uint8_t>(), cnt);
-  rows_plan_kernel<<<1, 32, 0, st>>>(n_keys, chunk, key_cost, cnt, cnt + kRowBuckets, rp.work.as<int32_t>(), rp.meta.as<int32_t>());
-  rows_scatter_kernel<<<rb, 256, 0, st>>>(D, rp.rowb.as<uint8_t>(), cnt + kRowBuckets, rp.rows.as<int32_t>());
+  rows_group_kernel<<<(D + 255) / 256, 256, 0, st>>>(D, n_keys, chunk, dem_off, dem_key, key_cost, rp.cnt.as<int32_t>(),
+                                                     rp.rows.as<int32_t>(), rp.work.as<int32_t>(), rp.meta.as<int32_t>(),
+                                                     first_node);
   CU(cudaGetLastError());
   return NOSPLAN_OK;
 }
@@ -301,7 +298,7 @@ int launch_mig_score16_cw(nosplan_t* h, const MigScoreArgs& a, int tiles, cudaSt
   pick_chunks(h->sm_count, tiles, a.D, 16, &chunk, &gy, std::max(occ, 1) * score_waves());
   chunk = std::min(chunk, kRowCap);
   int max_work = 0;
-  int rc = plan_rows(h, 0, a.D, h->P, chunk, a.dem_off, a.dem_key, h->d_profcost.as<int32_t>(), st, &max_work);
+  int rc = plan_rows(h, 0, a.D, h->P, chunk, a.dem_off, a.dem_key, h->d_profcost.as<int32_t>(), a.first_node, st, &max_work);
   if (rc) return rc;
   auto& rp = h->rp[0];
   MigScore16Args A;
@@ -330,7 +327,9 @@ int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
                      int32_t* d_first, uint8_t* d_updated, int8_t* d_choice, cudaStream_t st) {
   if (D == 0) return NOSPLAN_OK;
   int rc = NOSPLAN_OK;
-  fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, kNoNode);
+  const bool ordered = h->mig_n > 0 && h->k16ok && (h->cmax + 3) / 4 <= 4 && (h->mig_n + kScoreTN - 1) / kScoreTN <= 65535 &&
+                       !wide_keys_forced() && !plain_order_forced();
+  if (!ordered) fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, kNoNode);  // else rows_group_kernel does it
   if (d_choice) CU(cudaMemsetAsync(d_choice, 0xff, (size_t)D * h->mig_tg, st));
   if (h->mig_n > 0) {
     MigScoreArgs a;
@@ -361,7 +360,7 @@ int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
     size_t smem = mig_score_smem(h, kScoreTN);
     if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MIG scorer tile needs %zu bytes of shared memory", smem);
     const int cw = (h->cmax + 3) / 4;
-    if (h->k16ok && cw <= 4 && tiles <= 65535 && !wide_keys_forced() && !plain_order_forced()) {
+    if (ordered) {
       // common tables: rows grouped by profile, nodes ordered per profile, 16-bit keys (nosplan_score16.cuh);
       // rows with several keys go through the general kernel below, restricted to their list
       if ((rc = launch_mig_score16(h, a, tiles, cw, st))) return rc;
@@ -377,7 +376,8 @@ int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
 int launch_mps_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d_key, const int32_t* d_qty,
                      int32_t* d_first, uint8_t* d_updated, uint8_t* d_free, uint32_t* d_mask, cudaStream_t st, int base = 0) {
   if (D == 0) return NOSPLAN_OK;
-  fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, kNoNode);
+  const bool ordered = h->mps_n > 0 && (h->mps_n + kScoreTN - 1) / kScoreTN <= 65535 && !plain_order_forced();
+  if (!ordered) fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, kNoNode);  // else rows_group_kernel does it
   if (h->mps_n > 0) {
     MpsScoreArgs a;
     a.sizes = h->d_mps_sizes.as<int32_t>();
@@ -404,10 +404,10 @@ int launch_mps_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
     CU(cudaFuncSetAttribute(mps_score_kernel<kScoreTN, kScoreDS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     a.mode = 0;
     a.perm = a.rows = a.work = a.meta = nullptr;
-    if (tiles <= 65535 && !plain_order_forced()) {
+    if (ordered) {
       // single-size rows grouped by size over nodes ordered per size; the rest over plain tiles
       int max_work = 0;
-      int rc = plan_rows(h, 1, D, h->S, std::min(a.d_chunk, kRowCap), d_off, d_key, h->d_mps_sizecost.as<int32_t>(), st, &max_work);
+      int rc = plan_rows(h, 1, D, h->S, std::min(a.d_chunk, kRowCap), d_off, d_key, h->d_mps_sizecost.as<int32_t>(), d_first, st, &max_work);
       if (rc) return rc;
       a.perm = h->d_mps_perm.as<int32_t>();
       a.rows = h->rp[1].rows.as<int32_t>();
@@ -476,8 +476,8 @@ void nosplan_destroy(nosplan_t* h) {
                    &h->d_mps_sizes, &h->d_mps_off, &h->d_mps_valid, &h->d_mps_gpu0, &h->d_mps_ulo0, &h->d_mps_uhi0,
                    &h->d_mps_gpu, &h->d_mps_ulo, &h->d_mps_uhi, &h->d_mig_gnode, &h->d_mps_gnode, &h->d_mig_gslot, &h->d_mps_gslot, &h->d_status,
                    &h->d_mig_cost, &h->d_mig_perm, &h->d_mig_rankg, &h->d_mig_ufg, &h->d_profcost, &h->d_mps_cost, &h->d_mps_perm, &h->d_mps_sizecost,
-                   &h->rp[0].rows, &h->rp[0].rowb, &h->rp[0].work, &h->rp[0].meta, &h->rp[0].cnt,
-                   &h->rp[1].rows, &h->rp[1].rowb, &h->rp[1].work, &h->rp[1].meta, &h->rp[1].cnt};
+                   &h->rp[0].rows, &h->rp[0].work, &h->rp[0].meta, &h->rp[0].cnt,
+                   &h->rp[1].rows, &h->rp[1].work, &h->rp[1].meta, &h->rp[1].cnt};
   for (DevBuf* b : all) b->release();
   for (auto& b : h->d_in) b.release();
   for (auto& b : h->d_dem) b.release();

@@ -154,57 +154,54 @@ __global__ void mps_cost_kernel(int N, int S, const int32_t* __restrict__ sizes,
   for (int k = 0; k < S; ++k) cost[(size_t)k * N + n] = c[k];
 }
 
-// ---- per call: rows by profile ------------------------------------------------------------------------------
+// ---- per call: rows by key -------------------------------------------------------------------------------------
+// (MIG profiles and MPS sizes alike: "P" below is the number of keys of the kind, <= 32.)
+// One launch.  Every row goes to the list of its bucket (bucket p < P: single-key rows of key p;
+// bucket P: every other row); bucket b owns rows[b * D, (b + 1) * D), filled through an atomic cursor.
+// The block that finishes last turns the counts into work items {key, start in rows[], length <= chunk},
+// heaviest key first, and meta[0] = number of items, meta[1] = start of bucket P, meta[2] = its size; it
+// leaves the cursors and the ticket at zero for the next call.  first_node[] is put to rest on the way.
 constexpr int kRowBuckets = 33;  // up to 32 keys + "any other row"
 constexpr int kNoRow = 63;
-// (MIG profiles and MPS sizes alike: "P" below is the number of keys of the kind, <= 32.)
-// rows[]: row ids grouped by bucket (bucket p < P: single-key rows of key p; bucket P: every other
-// row).  meta[0] = number of work items, meta[1] = start of bucket P in rows[], meta[2] = its size.
-// work[i] = {profile, start in rows[], length <= chunk}, heaviest profile first.  Three small kernels:
-// count (grid) -> plan (one thread) -> scatter (grid).  cnt[kRowBuckets] must be zero on entry; plan re-zeroes it.
+
 __device__ __forceinline__ int row_bucket(int d, int P, const int32_t* __restrict__ dem_off,
-                                              const int32_t* __restrict__ dem_key) {
+                                          const int32_t* __restrict__ dem_key) {
   const int e0 = __ldg(dem_off + d), k = __ldg(dem_off + d + 1) - e0;
   if (k != 1) return P;
   const int key = __ldg(dem_key + e0);
   return (unsigned)key < (unsigned)P ? key : P;
 }
 
-__global__ void rows_count_kernel(int D, int P, const int32_t* __restrict__ dem_off, const int32_t* __restrict__ dem_key,
-                                  uint8_t* __restrict__ rowb, int32_t* __restrict__ cnt) {
-  __shared__ int s_cnt[kRowBuckets];
-  if (threadIdx.x < kRowBuckets) s_cnt[threadIdx.x] = 0;
-  __syncthreads();
+// state[0 .. kRowBuckets) = cursors, state[kRowBuckets] = ticket; all zero on entry and on exit
+__global__ void rows_group_kernel(int D, int P, int chunk, const int32_t* __restrict__ dem_off,
+                                  const int32_t* __restrict__ dem_key, const int32_t* __restrict__ key_cost,
+                                  int32_t* __restrict__ state, int32_t* __restrict__ rows, int32_t* __restrict__ work,
+                                  int32_t* __restrict__ meta, int32_t* __restrict__ first_node) {
+  __shared__ int s_last;
   const int d = blockIdx.x * blockDim.x + threadIdx.x;  // blockDim is a multiple of 32: whole warps reach the match
+  const int lane = threadIdx.x & 31;
   int b = kNoRow;
   if (d < D) {
     b = row_bucket(d, P, dem_off, dem_key);
-    rowb[d] = (uint8_t)b;
+    first_node[d] = kNoNode;
   }
-  const uint32_t peers = __match_any_sync(0xffffffffu, b);  // one shared-memory atomic per bucket per warp
-  if (b != kNoRow && (int)(threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&s_cnt[b], __popc(peers));
+  const uint32_t peers = __match_any_sync(0xffffffffu, b);  // one atomic per bucket per warp
+  const int leader = __ffs(peers) - 1;
+  int base = 0;
+  if (b != kNoRow && lane == leader) base = atomicAdd(&state[b], __popc(peers));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  if (b != kNoRow) rows[(size_t)b * D + base + __popc(peers & ((1u << lane) - 1u))] = d;
+  __threadfence();
   __syncthreads();
-  if (threadIdx.x < kRowBuckets && s_cnt[threadIdx.x]) atomicAdd(&cnt[threadIdx.x], s_cnt[threadIdx.x]);
-}
-
-__global__ void rows_plan_kernel(int P, int chunk, const int32_t* __restrict__ prof_cost, int32_t* __restrict__ cnt,
-                                 int32_t* __restrict__ cursor, int32_t* __restrict__ work, int32_t* __restrict__ meta) {
-  // one warp: lane b holds bucket b (P <= 32; bucket P is read by lane 0 as well)
-  const int lane = threadIdx.x;
+  if (threadIdx.x == 0) s_last = atomicAdd(&state[kRowBuckets], 1) == (int)gridDim.x - 1;
+  __syncthreads();
+  if (!s_last || threadIdx.x >= 32) return;
+  __threadfence();
+  // the last block, one warp: lane b holds bucket b
   const uint32_t full = 0xffffffffu;
-  const int my_cnt = lane < P ? cnt[lane] : 0;
-  const int my_cost = lane < P ? prof_cost[lane] : -1;
-  const int rest = cnt[P];
-  // offsets in rows[] (bucket order) by an exclusive prefix sum over the lanes
-  int incl = my_cnt;
-  for (int o = 1; o < 32; o <<= 1) {
-    const int v = __shfl_up_sync(full, incl, o);
-    if (lane >= o) incl += v;
-  }
-  const int my_off = incl - my_cnt;
-  const int total = __shfl_sync(full, incl, 31);
-  if (lane < P) cursor[lane] = my_off;
-  if (lane == 0) cursor[P] = total;
+  const int my_cnt = lane < P ? __ldcg(&state[lane]) : 0;
+  const int my_cost = lane < P ? key_cost[lane] : -1;
+  const int rest = __ldcg(&state[P]);
   // work items by descending key cost (ties: lower key first): the long CTAs start first
   int rank = 0;
   for (int j = 0; j < 32; ++j) {
@@ -212,8 +209,7 @@ __global__ void rows_plan_kernel(int P, int chunk, const int32_t* __restrict__ p
     if (j < P && (cj > my_cost || (cj == my_cost && j < lane))) ++rank;
   }
   const int my_items = (my_cnt + chunk - 1) / chunk;
-  // items of the keys ranked before mine
-  int before = 0;
+  int before = 0;  // items of the keys ranked before mine
   for (int j = 0; j < 32; ++j) {
     const int rj = __shfl_sync(full, rank, j), ij = __shfl_sync(full, my_items, j);
     if (j < P && rj < rank) before += ij;
@@ -221,31 +217,18 @@ __global__ void rows_plan_kernel(int P, int chunk, const int32_t* __restrict__ p
   if (lane < P)
     for (int it = 0; it < my_items; ++it) {
       work[3 * (before + it) + 0] = lane;
-      work[3 * (before + it) + 1] = my_off + it * chunk;
+      work[3 * (before + it) + 1] = lane * D + it * chunk;
       work[3 * (before + it) + 2] = min(chunk, my_cnt - it * chunk);
     }
   int nw = lane < P ? my_items : 0;
   for (int o = 16; o; o >>= 1) nw += __shfl_xor_sync(full, nw, o);
   if (lane == 0) {
     meta[0] = nw;
-    meta[1] = total;
+    meta[1] = P * D;
     meta[2] = rest;
   }
   __syncwarp();
-  for (int b = lane; b < kRowBuckets; b += 32) cnt[b] = 0;  // ready for the next call
-}
-
-__global__ void rows_scatter_kernel(int D, const uint8_t* __restrict__ rowb, int32_t* __restrict__ cursor,
-                                        int32_t* __restrict__ rows) {
-  const int d = blockIdx.x * blockDim.x + threadIdx.x;
-  const int lane = threadIdx.x & 31;
-  const int b = d < D ? (int)rowb[d] : kNoRow;
-  const uint32_t peers = __match_any_sync(0xffffffffu, b);
-  const int leader = __ffs(peers) - 1;
-  int base = 0;
-  if (b != kNoRow && lane == leader) base = atomicAdd(&cursor[b], __popc(peers));
-  base = __shfl_sync(0xffffffffu, base, leader);
-  if (b != kNoRow) rows[base + __popc(peers & ((1u << lane) - 1u))] = d;
+  for (int i = lane; i <= kRowBuckets; i += 32) state[i] = 0;
 }
 
 // ---- the scorer -------------------------------------------------------------------------------------------
