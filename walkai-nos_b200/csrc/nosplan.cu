@@ -69,7 +69,7 @@ struct nosplan {
   DevBuf d_mig_sused, d_mig_sfree, d_mig_smodel, d_mig_scnt, d_mig_gnode, d_mig_gslot;
   bool mig_state_dirty = false;  // working copy differs from the snapshot
   DevBuf d_mig_cost, d_mig_perm;  // per-profile node order of the 16-bit-key scorer (nosplan_score16.cuh)
-  DevBuf d_mig_rankg, d_mig_ufg;  // its snapshot-time tables
+  DevBuf d_mig_rankg, d_mig_ufg, d_mig_maskg;  // its snapshot-time tables
   DevBuf d_profcost;
   struct RowPlan {  // per scoring call and kind: demand rows grouped by key, work items (rows_*_kernel)
     DevBuf rows, work, meta, cnt;
@@ -90,6 +90,8 @@ struct nosplan {
   DevBuf d_out[6];   // outputs
   DevBuf d_plan[32];
   DevBuf d_status;
+  unsigned long long* h_status = nullptr;  // pinned
+  cudaEvent_t status_ev = nullptr;
 
   // sharded scoring (nosplan_set_node_base, nosplan_exchange_*)
   int mig_base = 0, mps_base = 0;
@@ -158,9 +160,17 @@ int status_reset(nosplan_t* h, cudaStream_t st) {
   CU(cudaMemsetAsync(static_cast<char*>(h->d_status.p) + 8, 0, 8, st));
   return NOSPLAN_OK;
 }
-int status_fetch(nosplan_t* h, cudaStream_t st, unsigned long long out[2]) {
-  CU(cudaMemcpyAsync(out, h->d_status.p, 16, cudaMemcpyDeviceToHost, st));
-  CU(cudaStreamSynchronize(st));
+// the read-back is enqueued right behind the pack kernel; work enqueued after it (tables that only the
+// scorers need) is not waited for: the stream orders it before any later call
+int status_enqueue(nosplan_t* h, cudaStream_t st) {
+  CU(cudaMemcpyAsync(h->h_status, h->d_status.p, 16, cudaMemcpyDeviceToHost, st));
+  CU(cudaEventRecord(h->status_ev, st));
+  return NOSPLAN_OK;
+}
+int status_wait(nosplan_t* h, unsigned long long out[2]) {
+  CU(cudaEventSynchronize(h->status_ev));
+  out[0] = h->h_status[0];
+  out[1] = h->h_status[1];
   return NOSPLAN_OK;
 }
 
@@ -456,6 +466,11 @@ int nosplan_create(int device, nosplan_t** out) {
     return NOSPLAN_ERR_CUDA;
   }
   cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device);
+  if (cudaHostAlloc(reinterpret_cast<void**>(&h->h_status), 16, cudaHostAllocDefault) != cudaSuccess ||
+      cudaEventCreateWithFlags(&h->status_ev, cudaEventDisableTiming) != cudaSuccess) {
+    nosplan_destroy(h);
+    return NOSPLAN_ERR_CUDA;
+  }
   *out = h;
   return NOSPLAN_OK;
 }
@@ -475,7 +490,7 @@ void nosplan_destroy(nosplan_t* h) {
                    &h->d_mig_used, &h->d_mig_free, &h->d_mig_sused, &h->d_mig_sfree, &h->d_mig_smodel, &h->d_mig_scnt,
                    &h->d_mps_sizes, &h->d_mps_off, &h->d_mps_valid, &h->d_mps_gpu0, &h->d_mps_ulo0, &h->d_mps_uhi0,
                    &h->d_mps_gpu, &h->d_mps_ulo, &h->d_mps_uhi, &h->d_mig_gnode, &h->d_mps_gnode, &h->d_mig_gslot, &h->d_mps_gslot, &h->d_status,
-                   &h->d_mig_cost, &h->d_mig_perm, &h->d_mig_rankg, &h->d_mig_ufg, &h->d_profcost, &h->d_mps_cost, &h->d_mps_perm, &h->d_mps_sizecost,
+                   &h->d_mig_cost, &h->d_mig_perm, &h->d_mig_rankg, &h->d_mig_ufg, &h->d_mig_maskg, &h->d_profcost, &h->d_mps_cost, &h->d_mps_perm, &h->d_mps_sizecost,
                    &h->rp[0].rows, &h->rp[0].work, &h->rp[0].meta, &h->rp[0].cnt,
                    &h->rp[1].rows, &h->rp[1].work, &h->rp[1].meta, &h->rp[1].cnt};
   for (DevBuf* b : all) b->release();
@@ -483,6 +498,8 @@ void nosplan_destroy(nosplan_t* h) {
   for (auto& b : h->d_dem) b.release();
   for (auto& b : h->d_out) b.release();
   for (auto& b : h->d_plan) b.release();
+  if (h->h_status) cudaFreeHost(h->h_status);
+  if (h->status_ev) cudaEventDestroy(h->status_ev);
   if (h->stream) cudaStreamDestroy(h->stream);
   if (h->stream2) cudaStreamDestroy(h->stream2);
   delete h;
@@ -615,8 +632,8 @@ int nosplan_set_mig_snapshot(nosplan_t* h, int n_nodes, const int32_t* gpu_off, 
   CU(h->d_mig_scnt.reserve(npad));
   if ((rc = status_reset(h, h->stream))) return rc;
   h->have_mig = false;  // the device copy is being replaced: a failed call leaves no snapshot behind
-  mig_pack_kernel<<<(npad + 127) / 128, 128, 0, h->stream>>>(
-      n_nodes, P, gs, npad, NOSPLAN_MAX_COUNT, h->d_tables.as<MigTables>(), h->d_mig_off.as<int32_t>(),
+  mig_pack_kernel<<<(npad * gsl + 127) / 128, 128, 0, h->stream>>>(
+      n_nodes, P, gsl, npad, NOSPLAN_MAX_COUNT, h->d_tables.as<MigTables>(), h->d_mig_off.as<int32_t>(),
       h->d_mig_valid.as<uint8_t>(), h->d_in[0].as<int32_t>(), h->d_in[1].as<int32_t>(), h->d_in[2].as<int32_t>(),
       h->d_mig_used0.as<uint4>(), h->d_mig_free0.as<uint4>(), h->d_mig_model.as<uint8_t>(), h->d_mig_sused.as<uint4>(),
       h->d_mig_sfree.as<uint4>(), h->d_mig_smodel.as<uint8_t>(), h->d_mig_scnt.as<uint8_t>(), h->d_mig_gnode.as<int32_t>(),
@@ -624,25 +641,29 @@ int nosplan_set_mig_snapshot(nosplan_t* h, int n_nodes, const int32_t* gpu_off, 
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(h->d_mig_used.p, h->d_mig_used0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, h->stream));
   CU(cudaMemcpyAsync(h->d_mig_free.p, h->d_mig_free0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, h->stream));
-  if (h->k16ok) {  // node order per profile for the 16-bit-key scorer: scheduling data, not results
-    CU(h->d_mig_cost.reserve((size_t)P * npad));
-    CU(h->d_mig_perm.reserve(sizeof(int32_t) * (size_t)P * npad));
-    mig_cost_kernel<<<(npad + 127) / 128, 128, 0, h->stream>>>(
-        h->d_tables.as<MigTables>(), n_nodes, npad, P, h->d_mig_sused.as<uint4>(), h->d_mig_sfree.as<uint4>(),
-        h->d_mig_smodel.as<uint8_t>(), h->d_mig_scnt.as<uint8_t>(), h->d_mig_cost.as<uint8_t>());
-    CU(h->d_profcost.reserve(sizeof(int32_t) * 32));
-    mig_perm_kernel<<<P, 1024, 0, h->stream>>>(npad, h->d_mig_cost.as<uint8_t>(), h->d_mig_perm.as<int32_t>(),
-                                               h->d_profcost.as<int32_t>());
+  if ((rc = status_enqueue(h, h->stream))) return rc;
+  if (h->k16ok) {
+    // 16-bit-key scorer: the demand-independent candidate ranks of every GPU, then the node order per
+    // profile (scheduling data, not results)
     const int cwk = (h->cmax + 3) / 4;
     CU(h->d_mig_rankg.reserve(sizeof(uint32_t) * (size_t)npad * gsl * 2 * cwk));
     CU(h->d_mig_ufg.reserve(sizeof(uint16_t) * (size_t)npad * 16 * gsl));
+    CU(h->d_mig_maskg.reserve(sizeof(uint32_t) * (size_t)npad * gsl));
+    CU(h->d_mig_cost.reserve((size_t)P * npad));
+    CU(h->d_mig_perm.reserve(sizeof(int32_t) * (size_t)P * npad));
+    CU(h->d_profcost.reserve(sizeof(int32_t) * 32));
     mig_rank16_kernel<<<(npad * gsl + 127) / 128, 128, 0, h->stream>>>(
         h->d_tables.as<MigTables>(), npad, gsl, cwk, h->d_mig_sused.as<uint4>(), h->d_mig_sfree.as<uint4>(),
-        h->d_mig_smodel.as<uint8_t>(), h->d_mig_scnt.as<uint8_t>(), h->d_mig_rankg.as<uint32_t>(), h->d_mig_ufg.as<uint16_t>());
+        h->d_mig_smodel.as<uint8_t>(), h->d_mig_scnt.as<uint8_t>(), h->d_mig_rankg.as<uint32_t>(), h->d_mig_ufg.as<uint16_t>(),
+        h->d_mig_maskg.as<uint32_t>());
+    mig_cost_kernel<<<(npad + 127) / 128, 128, 0, h->stream>>>(n_nodes, npad, gsl, P, h->d_mig_scnt.as<uint8_t>(),
+                                                               h->d_mig_maskg.as<uint32_t>(), h->d_mig_cost.as<uint8_t>());
+    mig_perm_kernel<<<P, 1024, 0, h->stream>>>(npad, h->d_mig_cost.as<uint8_t>(), h->d_mig_perm.as<int32_t>(),
+                                               h->d_profcost.as<int32_t>());
     CU(cudaGetLastError());
   }
   unsigned long long st[2];
-  if ((rc = status_fetch(h, h->stream, st))) return rc;
+  if ((rc = status_wait(h, st))) return rc;
   if (st[0] != ~0ull) {  // first bad entry in GPU order, reported as the host walk used to
     const int g = (int)(st[0] / 64), sub = (int)(st[0] % 64);
     if (sub == 0) return fail(h, NOSPLAN_ERR_RANGE, "GPU %d: model %d unknown (mark the node invalid instead)", g, model[g]);
@@ -719,6 +740,7 @@ int nosplan_set_mps_snapshot(nosplan_t* h, int n_sizes, const int32_t* sizes_gb,
     CU(cudaMemcpyAsync(h->d_mps_gpu.p, h->d_mps_gpu0.p, sizeof(MpsGpu) * tg, cudaMemcpyDeviceToDevice, h->stream));
     CU(cudaMemcpyAsync(h->d_mps_ulo.p, h->d_mps_ulo0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, h->stream));
     CU(cudaMemcpyAsync(h->d_mps_uhi.p, h->d_mps_uhi0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, h->stream));
+    if ((rc = status_enqueue(h, h->stream))) return rc;
     // node order per size for the scorer (scheduling data, see nosplan_score16.cuh)
     CU(h->d_mps_cost.reserve((size_t)S * n_nodes));
     CU(h->d_mps_perm.reserve(sizeof(int32_t) * (size_t)S * n_nodes));
@@ -730,8 +752,9 @@ int nosplan_set_mps_snapshot(nosplan_t* h, int n_sizes, const int32_t* sizes_gb,
                                                h->d_mps_sizecost.as<int32_t>());
     CU(cudaGetLastError());
   }
+  if (n_nodes == 0 && (rc = status_enqueue(h, h->stream))) return rc;
   unsigned long long st[2];
-  if ((rc = status_fetch(h, h->stream, st))) return rc;
+  if ((rc = status_wait(h, st))) return rc;
   if (st[0] != ~0ull) {
     const int g = (int)(st[0] / 128), sub = (int)(st[0] % 128);
     if (sub == 0) return fail(h, NOSPLAN_ERR_RANGE, "GPU %d: memory %d GB out of range", g, mem_gb[g]);

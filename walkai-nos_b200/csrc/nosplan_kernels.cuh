@@ -141,14 +141,16 @@ __global__ void mig_pack_kernel(int N, int P, int gs, int npad, int max_count, c
                                 uint8_t* __restrict__ a_model, uint4* __restrict__ s_used, uint4* __restrict__ s_free,
                                 uint8_t* __restrict__ s_model, uint8_t* __restrict__ s_cnt, int32_t* __restrict__ gnode,
                                 int32_t* __restrict__ gslot, unsigned long long* __restrict__ status) {
-  const int n = blockIdx.x * blockDim.x + threadIdx.x;
-  if (n >= npad) return;
-  const int g0 = n < N ? gpu_off[n] : 0;
-  const int cnt = n < N ? gpu_off[n + 1] - g0 : 0;
-  const bool ok = n < N && valid[n];
-  s_cnt[n] = ok ? (uint8_t)cnt : 0;  // an invalid node behaves like a node the controller skips
-  unsigned long long bad = ~0ull, evals = 0;
-  for (int s = 0; s < gs; ++s) {
+  // one thread per (node, slot); the grid covers npad * gs of them in whole warps
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int n = i / gs, s = i - n * gs;
+  unsigned long long bad = ~0ull;
+  unsigned int evals = 0;
+  if (n < npad) {
+    const int g0 = n < N ? gpu_off[n] : 0;
+    const int cnt = n < N ? gpu_off[n + 1] - g0 : 0;
+    const bool ok = n < N && valid[n];
+    if (s == 0) s_cnt[n] = ok ? (uint8_t)cnt : 0;  // an invalid node behaves like a node the controller skips
     uint4 u = make_uint4(0, 0, 0, 0), f = u;
     uint8_t m = 0xff;
     if (s < cnt) {
@@ -158,10 +160,10 @@ __global__ void mig_pack_kernel(int N, int P, int gs, int npad, int max_count, c
       if (ok) {
         md = model[g];
         if (md < 0 || md >= T->n_models) {
-          bad = min(bad, (unsigned long long)g * 64ull);
+          bad = (unsigned long long)g * 64ull;
           md = 0;
         } else {
-          evals += (unsigned long long)(T->geom_off[md + 1] - T->geom_off[md]);
+          evals = (unsigned int)(T->geom_off[md + 1] - T->geom_off[md]);
         }
         for (int p = 0; p < P; ++p) {
           const int uv = used[(size_t)g * P + p], fv = fr[(size_t)g * P + p];
@@ -184,8 +186,11 @@ __global__ void mig_pack_kernel(int N, int P, int gs, int npad, int max_count, c
     s_free[(size_t)s * npad + n] = f;
     s_model[(size_t)s * npad + n] = ok ? m : (uint8_t)0xff;
   }
-  if (bad != ~0ull) atomicMin(&status[0], bad);
-  if (evals) atomicAdd(&status[1], evals);
+  // one atomic per warp for each of the two status words
+  evals = __reduce_add_sync(0xffffffffu, evals);
+  const bool anybad = __any_sync(0xffffffffu, bad != ~0ull);
+  if (anybad && bad != ~0ull) atomicMin(&status[0], bad);
+  if ((threadIdx.x & 31) == 0 && evals) atomicAdd(&status[1], (unsigned long long)evals);
 }
 
 __global__ void mig_unpack_kernel(int tg, int P, const uint4* __restrict__ a_used, const uint4* __restrict__ a_free,

@@ -26,9 +26,8 @@ constexpr int kCostBuckets = 96;  // 2 * visited + 3 * evaluated <= 5 * 16
 
 // ---- snapshot time ------------------------------------------------------------------------------------
 // cost[p][n]: relative cost of scoring a quantity-1 request of profile p on node n.
-__global__ void mig_cost_kernel(const MigTables* __restrict__ T, int N, int npad, int P, const uint4* __restrict__ s_used,
-                                const uint4* __restrict__ s_free, const uint8_t* __restrict__ s_model,
-                                const uint8_t* __restrict__ s_cnt, uint8_t* __restrict__ cost) {
+__global__ void mig_cost_kernel(int N, int npad, int gs, int P, const uint8_t* __restrict__ s_cnt,
+                                const uint32_t* __restrict__ maskg, uint8_t* __restrict__ cost) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= npad) return;
   const int cnt = n < N ? s_cnt[n] : 0;
@@ -37,9 +36,8 @@ __global__ void mig_cost_kernel(const MigTables* __restrict__ T, int N, int npad
 #pragma unroll
   for (int p = 0; p < 16; ++p) c[p] = 0;
   for (int s = 0; s < cnt && open; ++s) {
-    const uint4 u = s_used[(size_t)s * npad + n], f = s_free[(size_t)s * npad + n];
-    const uint32_t f1 = nonzero_bytes16(f);
-    const uint32_t gm = mig_grow_mask(T, s_model[(size_t)s * npad + n], u, f);
+    const uint32_t mk = maskg[(size_t)n * gs + s];
+    const uint32_t f1 = mk & 0xffffu, gm = mk >> 16;
 #pragma unroll
     for (int p = 0; p < 16; ++p) {
       if (!((open >> p) & 1u)) continue;
@@ -55,10 +53,12 @@ __global__ void mig_cost_kernel(const MigTables* __restrict__ T, int N, int npad
 // id rank) depends only on the snapshot, so it is evaluated once when the snapshot arrives instead of in
 // the prologue of every CTA of every scoring call: per (node, slot) the rank half-words of all
 // candidates, and per (node, profile, slot) free | (used + free) << 8.
-//   rankg [npad][gs][2cw] u32, ufg [npad][16][gs] u16
+//   rankg [npad][gs][2cw] u32, ufg [npad][16][gs] u16, maskg [npad][gs] u32 (profiles with a free device |
+//   profiles some applicable geometry adds to, << 16)
 __global__ void mig_rank16_kernel(const MigTables* __restrict__ T, int npad, int gs, int cw, const uint4* __restrict__ s_used,
                                   const uint4* __restrict__ s_free, const uint8_t* __restrict__ s_model,
-                                  const uint8_t* __restrict__ s_cnt, uint32_t* __restrict__ rankg, uint16_t* __restrict__ ufg) {
+                                  const uint8_t* __restrict__ s_cnt, uint32_t* __restrict__ rankg, uint16_t* __restrict__ ufg,
+                                  uint32_t* __restrict__ maskg) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= npad * gs) return;
   const int n = i / gs, s = i % gs;
@@ -66,6 +66,7 @@ __global__ void mig_rank16_kernel(const MigTables* __restrict__ T, int npad, int
   if (s >= s_cnt[n]) {
     for (int w = 0; w < 2 * cw; ++w) out[w] = 0x80008000u;
     for (int p = 0; p < 16; ++p) ufg[((size_t)n * 16 + p) * gs + s] = 0;
+    maskg[(size_t)n * gs + s] = 0;
     return;
   }
   const uint4 u = s_used[(size_t)s * npad + n];
@@ -75,13 +76,18 @@ __global__ void mig_rank16_kernel(const MigTables* __restrict__ T, int npad, int
   const int c0 = T->geom_off[m], cc = T->geom_off[m + 1] - c0;
   for (int p = 0; p < 16; ++p) ufg[((size_t)n * 16 + p) * gs + s] = (uint16_t)(byte_of(f, p) | (byte_of(cur, p) << 8));
   uint32_t k0[16];
+  uint32_t gm = 0;  // profiles some applicable geometry would add to
   for (int c = 0; c < 16; ++c) {
     k0[c] = 0u;
     if (c < cc) {
       const uint4 cd = T->cand[c0 + c];
-      if (all_ge4(cd, u)) k0[c] = key0_of(T->total[c0 + c], sad16(cd, cur), T->rank[c0 + c]);
+      if (all_ge4(cd, u)) {
+        k0[c] = key0_of(T->total[c0 + c], sad16(cd, cur), T->rank[c0 + c]);
+        gm |= gt_bytes16(cd, cur);
+      }
     }
   }
+  maskg[(size_t)n * gs + s] = nonzero_bytes16(f) | (gm << 16);  // for mig_cost_kernel
   for (int w = 0; w < 2 * cw; ++w) {
     uint32_t r2 = 0;
     for (int b = 0; b < 2; ++b) {
