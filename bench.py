@@ -354,21 +354,22 @@ def main():
             "config": workload_config(cfg, args),
             "e2e": {"value": e2e_val, "unit": "evals/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "ms_per_step": float(e2e_t.item()) * 1e3},
-            "gpu_launches": int(args.steps * ((3 if Dm else 0) + (3 if Dp else 0) + (2 if exchange.startswith("peer") else 0))),
+            "gpu_launches": int(args.steps * ((4 if Dm else 0) + (4 if Dp else 0) + (2 if exchange.startswith("peer") else 0))),
             "exchange": exchange,
             "planner_latency_ms_p50": float(np.median(lat)) if lat else None,
             "planner_latency_ms_p95": float(np.percentile(lat, 95)) if lat else None,
             "planner_latency_gate_off_ms_p50": float(np.median(lat_off)) if lat_off else None,
             "evals_per_step": {"mig": ev_m, "mps": ev_p},
-            # achieved/frac follow SURVEY §8(d): algorithmic bytes (no credit for on-chip reuse) / kernel time.
-            # traffic = ncu dram__bytes_read+write per launch of the same command (profiles/r1_final_bench_cfg5.md):
-            # the tile state is re-used from shared memory, HBM is idle and the binding roof is the integer
-            # instruction issue / ALU pipe (ncu: issue-active 79 %, ALU 74 %), which is why frac is above 1.
-            "roofline": {"bound": "hbm", "kernel": "mig_score_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
-                         "frac": ach / peak, "peak_source": peak_src, "traffic": 981760 if args.config == 5 and world == 1 else None,
+            # achieved/frac follow SURVEY §8(d): algorithmic bytes (no credit for on-chip reuse) / time of the MIG
+            # scorer's launches (row grouping, mig_score16_kernel, the multi-key pass, the finishing pass; CUDA
+            # events).  traffic = ncu dram__bytes_read+write per mig_score16_kernel launch of the same command
+            # (profiles/r1h_bench_cfg5.md): the tile state is re-used from shared memory, HBM is idle and the
+            # binding roof is instruction issue (ncu: issue-active 77 %, ALU pipe 64 %, LSU 61 %): frac is above 1.
+            "roofline": {"bound": "hbm", "kernel": "mig_score16_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
+                         "frac": ach / peak, "peak_source": peak_src, "traffic": 1402368 if args.config == 5 and world == 1 else None,
                          "algorithmic_bytes_per_eval": BYTES_PER_EVAL_MIG, "kernel_ms": mig_ms / args.steps,
-                         "mps_kernel_ms": mps_ms / args.steps, "binding_roof": "int ALU pipe",
-                         "alu_pipe_pct_of_peak_ncu": 74.0, "issue_active_pct_ncu": 78.8},
+                         "mps_kernel_ms": mps_ms / args.steps, "binding_roof": "instruction issue (integer pipes)",
+                         "alu_pipe_pct_of_peak_ncu": 64.5, "issue_active_pct_ncu": 77.4},
             "clocks": sampler.summary(),
         }
         if not args.no_cpu_baseline and world == 1:
