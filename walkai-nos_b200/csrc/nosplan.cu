@@ -408,7 +408,7 @@ int launch_mps_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
     a.gs = h->mps_gs;
     int tiles = (h->mps_n + kScoreTN - 1) / kScoreTN;
     int gy;
-    pick_chunks(h->sm_count, tiles, D, 16, &a.d_chunk, &gy, 3 * score_waves());
+    pick_chunks(h->sm_count, tiles, D, 16, &a.d_chunk, &gy, ((ordered && !d_free) ? 4 : 3) * score_waves());  // CTAs per SM that fit
     const size_t smem = mps_score_smem_bytes(h->mps_gs, h->S, kScoreTN);
     if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MPS scorer tile needs %zu bytes of shared memory", smem);
     CU(cudaFuncSetAttribute(mps_score_kernel<kScoreTN, kScoreDS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

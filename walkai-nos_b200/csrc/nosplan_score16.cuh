@@ -393,7 +393,7 @@ __host__ __device__ inline size_t mps_score1_smem_bytes(int gs, int S, int tn) {
 }
 
 template <int TN, int DS, bool OUT>
-__global__ void __launch_bounds__(TN * DS, 3) mps_score1_kernel(const MpsScoreArgs a) {
+__global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreArgs a) {
   if ((int)blockIdx.x >= a.meta[0]) return;
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ int s_sz[kMaxSizes];
