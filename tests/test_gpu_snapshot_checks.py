@@ -135,3 +135,53 @@ def test_mps_error_classes(planner):
     assert planner.mps_evals_per_demand() == evals - (g1 - g0)
     used, free, _ = planner.get_mps_state()
     assert not used[g0:g1].any() and not free[g0:g1].any()
+
+
+def test_demand_rows_are_checked_on_the_device(planner):
+    """The scorers validate the demand rows while grouping them (rows_group_kernel): same codes and messages as
+    the host walk, the first bad row in row order wins, and a bad row never reaches a scorer."""
+    import walkai_nos_b200 as pkg
+    cfg, snap = _mig(pkg, planner)
+    planner.set_mig_snapshot(snap)
+    mcfg, msnap = _mps(pkg)
+    planner.set_mps_snapshot(mcfg["sizes"], msnap)
+    P, S = len(cfg["names"]), len(mcfg["sizes"])
+    good_off = np.arange(0, 41, dtype=np.int32)
+    good_key = (np.arange(40) % 6).astype(np.int32)
+    good_qty = np.ones(40, np.int32)
+
+    def both(off, key, qty, code, text, kinds=(0, 1)):
+        for kind in kinds:
+            k = key
+            fn = planner.score_mig if kind == 0 else planner.score_mps
+            kw = dict(want_updated=False, want_choice=False) if kind == 0 else dict(want_updated=False, want_free=False)
+            with pytest.raises(pkg.NosplanError) as e:
+                fn(off, k, qty, **kw)
+            assert e.value.code == code, (kind, str(e.value))
+            assert text in str(e.value), (kind, str(e.value))
+
+    # key out of range (RANGE), later rows are bad too: the first one is reported
+    key = good_key.copy(); key[7] = 99; key[30] = -4
+    both(good_off, key, good_qty, -2, "demand row 7: key 99 out of range", kinds=(0,))
+    key = good_key.copy() % S; key[7] = 99
+    both(good_off, key, good_qty, -2, "demand row 7: key 99 out of range", kinds=(1,))
+    # quantity out of range
+    qty = good_qty.copy(); qty[3] = -1; qty[9] = 2_000_000
+    both(good_off, good_key % S, qty, -2, "demand row 3: quantity -1 out of range")
+    qty = good_qty.copy(); qty[9] = 2_000_000
+    both(good_off, good_key % S, qty, -2, "demand row 9: quantity 2000000 out of range")
+    # keys of a row must be strictly ascending (ARG)
+    off = np.asarray([0, 1, 4, 5], np.int32)
+    key = np.asarray([0, 1, 3, 3, 2], np.int32)
+    qty = np.ones(5, np.int32)
+    both(off, key, qty, -1, "demand row 1: keys must be strictly ascending")
+    # too many keys in a row (RANGE)
+    off = np.asarray([0, 1, 10], np.int32)
+    both(off, np.arange(10, dtype=np.int32) % 3, np.ones(10, np.int32), -2, "demand row 1 has 9 keys")
+    # dem_off going backwards (ARG)
+    off = np.asarray([0, 3, 2, 4], np.int32)
+    both(off, np.asarray([0, 1, 2, 3], np.int32), np.ones(4, np.int32), -1, "dem_off not ascending at row 1")
+    # and the handle still scores good rows afterwards, identically to before
+    r1 = planner.score_mig(good_off, good_key, good_qty, want_updated=False, want_choice=False)
+    r2 = planner.score_mig(good_off, good_key, good_qty, want_updated=False, want_choice=False)
+    assert np.array_equal(r1["first_node"], r2["first_node"]) and (r1["first_node"] >= -1).all()

@@ -89,7 +89,7 @@ struct nosplan {
   DevBuf d_dem[3];   // demand CSR
   DevBuf d_out[6];   // outputs
   DevBuf d_plan[32];
-  DevBuf d_status;
+  DevBuf d_status, d_rowstatus;
   unsigned long long* h_status = nullptr;  // pinned
   cudaEvent_t status_ev = nullptr;
 
@@ -279,7 +279,7 @@ int launch_mig_score_kernel(nosplan_t* h, const MigScoreArgs& a, dim3 grid, size
 // Groups the demand rows of one scoring call by key and cuts them into work items (rows_group_kernel, which
 // also puts first_node[] to rest); max_work = the grid extent that covers any split of the rows.
 int plan_rows(nosplan_t* h, int kind, int D, int n_keys, int chunk, const int32_t* dem_off, const int32_t* dem_key,
-              const int32_t* key_cost, int32_t* first_node, cudaStream_t st, int* max_work) {
+              const int32_t* dem_qty, const int32_t* key_cost, int32_t* first_node, cudaStream_t st, int* max_work) {
   auto& rp = h->rp[kind];
   *max_work = (D + chunk - 1) / chunk + n_keys;  // every key may end with a short item
   CU(rp.rows.reserve(sizeof(int32_t) * (size_t)D * (n_keys + 1)));
@@ -289,9 +289,12 @@ int plan_rows(nosplan_t* h, int kind, int D, int n_keys, int chunk, const int32_
     CU(rp.cnt.reserve(sizeof(int32_t) * (kRowBuckets + 1)));
     CU(cudaMemsetAsync(rp.cnt.p, 0, sizeof(int32_t) * (kRowBuckets + 1), st));
   }
-  rows_group_kernel<<<(D + 255) / 256, 256, 0, st>>>(D, n_keys, chunk, dem_off, dem_key, key_cost, rp.cnt.as<int32_t>(),
-                                                     rp.rows.as<int32_t>(), rp.work.as<int32_t>(), rp.meta.as<int32_t>(),
-                                                     first_node);
+  CU(h->d_rowstatus.reserve(8));
+  CU(cudaMemsetAsync(h->d_rowstatus.p, 0xff, 8, st));  // "no bad row"
+  rows_group_kernel<<<(D + 255) / 256, 256, 0, st>>>(D, n_keys, chunk, NOSPLAN_MAX_DEMAND_KEYS, NOSPLAN_MAX_DEMAND_QTY, dem_off,
+                                                     dem_key, dem_qty, key_cost, rp.cnt.as<int32_t>(), rp.rows.as<int32_t>(),
+                                                     rp.work.as<int32_t>(), rp.meta.as<int32_t>(), first_node,
+                                                     h->d_rowstatus.as<unsigned long long>());
   CU(cudaGetLastError());
   return NOSPLAN_OK;
 }
@@ -308,7 +311,7 @@ int launch_mig_score16_cw(nosplan_t* h, const MigScoreArgs& a, int tiles, cudaSt
   pick_chunks(h->sm_count, tiles, a.D, 16, &chunk, &gy, std::max(occ, 1) * score_waves());
   chunk = std::min(chunk, kRowCap);
   int max_work = 0;
-  int rc = plan_rows(h, 0, a.D, h->P, chunk, a.dem_off, a.dem_key, h->d_profcost.as<int32_t>(), a.first_node, st, &max_work);
+  int rc = plan_rows(h, 0, a.D, h->P, chunk, a.dem_off, a.dem_key, a.dem_qty, h->d_profcost.as<int32_t>(), a.first_node, st, &max_work);
   if (rc) return rc;
   auto& rp = h->rp[0];
   MigScore16Args A;
@@ -333,12 +336,45 @@ int launch_mig_score16(nosplan_t* h, const MigScoreArgs& a, int tiles, int cw, c
   }
 }
 
+// the rows-by-key path is taken (and with it the demand rows are validated on the device)
+bool mig_ordered(const nosplan_t* h) {
+  return h->mig_n > 0 && h->k16ok && (h->cmax + 3) / 4 <= 4 && (h->mig_n + kScoreTN - 1) / kScoreTN <= 65535 &&
+         !wide_keys_forced() && !plain_order_forced();
+}
+bool mps_ordered(const nosplan_t* h) {
+  return h->mps_n > 0 && (h->mps_n + kScoreTN - 1) / kScoreTN <= 65535 && !plain_order_forced();
+}
+
+// What the host walk (check_demands) would have said about the row the device flagged.
+int describe_bad_row(nosplan_t* h, unsigned long long code, const int32_t* off, const int32_t* key, const int32_t* qty, int n_keys) {
+  const int d = (int)(code / 64);
+  const int k = off[d + 1] - off[d];
+  if (k < 0 || off[d] < 0 || (code % 64) == 0) return fail(h, NOSPLAN_ERR_ARG, "dem_off not ascending at row %d", d);
+  if (k > NOSPLAN_MAX_DEMAND_KEYS)
+    return fail(h, NOSPLAN_ERR_RANGE, "demand row %d has %d keys (max %d)", d, k, NOSPLAN_MAX_DEMAND_KEYS);
+  for (int e = off[d]; e < off[d + 1]; ++e) {
+    if (key[e] < 0 || key[e] >= n_keys) return fail(h, NOSPLAN_ERR_RANGE, "demand row %d: key %d out of range", d, key[e]);
+    if (e > off[d] && key[e] <= key[e - 1]) return fail(h, NOSPLAN_ERR_ARG, "demand row %d: keys must be strictly ascending", d);
+    if (qty[e] < 0 || qty[e] > NOSPLAN_MAX_DEMAND_QTY)
+      return fail(h, NOSPLAN_ERR_RANGE, "demand row %d: quantity %d out of range", d, qty[e]);
+  }
+  return fail(h, NOSPLAN_ERR_ARG, "demand row %d rejected on the device", d);
+}
+// head of check_demands: what does not need a walk over the rows
+int check_demands_head(nosplan_t* h, int D, const int32_t* off, const int32_t* key, const int32_t* qty) {
+  if (D < 0) return fail(h, NOSPLAN_ERR_ARG, "negative demand count");
+  if (D == 0) return NOSPLAN_OK;
+  if (!off) return fail(h, NOSPLAN_ERR_ARG, "dem_off is null");
+  if (off[0] != 0) return fail(h, NOSPLAN_ERR_ARG, "dem_off[0] must be 0");
+  if (off[D] > 0 && (!key || !qty)) return fail(h, NOSPLAN_ERR_ARG, "null demand arrays");
+  return NOSPLAN_OK;
+}
+
 int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d_key, const int32_t* d_qty,
                      int32_t* d_first, uint8_t* d_updated, int8_t* d_choice, cudaStream_t st) {
   if (D == 0) return NOSPLAN_OK;
   int rc = NOSPLAN_OK;
-  const bool ordered = h->mig_n > 0 && h->k16ok && (h->cmax + 3) / 4 <= 4 && (h->mig_n + kScoreTN - 1) / kScoreTN <= 65535 &&
-                       !wide_keys_forced() && !plain_order_forced();
+  const bool ordered = mig_ordered(h);
   if (!ordered) fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, kNoNode);  // else rows_group_kernel does it
   if (d_choice) CU(cudaMemsetAsync(d_choice, 0xff, (size_t)D * h->mig_tg, st));
   if (h->mig_n > 0) {
@@ -386,7 +422,7 @@ int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
 int launch_mps_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d_key, const int32_t* d_qty,
                      int32_t* d_first, uint8_t* d_updated, uint8_t* d_free, uint32_t* d_mask, cudaStream_t st, int base = 0) {
   if (D == 0) return NOSPLAN_OK;
-  const bool ordered = h->mps_n > 0 && (h->mps_n + kScoreTN - 1) / kScoreTN <= 65535 && !plain_order_forced();
+  const bool ordered = mps_ordered(h);
   if (!ordered) fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, kNoNode);  // else rows_group_kernel does it
   if (h->mps_n > 0) {
     MpsScoreArgs a;
@@ -417,7 +453,7 @@ int launch_mps_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
     if (ordered) {
       // single-size rows grouped by size over nodes ordered per size; the rest over plain tiles
       int max_work = 0;
-      int rc = plan_rows(h, 1, D, h->S, std::min(a.d_chunk, kRowCap), d_off, d_key, h->d_mps_sizecost.as<int32_t>(), d_first, st, &max_work);
+      int rc = plan_rows(h, 1, D, h->S, std::min(a.d_chunk, kRowCap), d_off, d_key, d_qty, h->d_mps_sizecost.as<int32_t>(), d_first, st, &max_work);
       if (rc) return rc;
       a.perm = h->d_mps_perm.as<int32_t>();
       a.rows = h->rp[1].rows.as<int32_t>();
@@ -489,7 +525,7 @@ void nosplan_destroy(nosplan_t* h) {
   DevBuf* all[] = {&h->d_tables, &h->d_mig_off, &h->d_mig_valid, &h->d_mig_model, &h->d_mig_used0, &h->d_mig_free0,
                    &h->d_mig_used, &h->d_mig_free, &h->d_mig_sused, &h->d_mig_sfree, &h->d_mig_smodel, &h->d_mig_scnt,
                    &h->d_mps_sizes, &h->d_mps_off, &h->d_mps_valid, &h->d_mps_gpu0, &h->d_mps_ulo0, &h->d_mps_uhi0,
-                   &h->d_mps_gpu, &h->d_mps_ulo, &h->d_mps_uhi, &h->d_mig_gnode, &h->d_mps_gnode, &h->d_mig_gslot, &h->d_mps_gslot, &h->d_status,
+                   &h->d_mps_gpu, &h->d_mps_ulo, &h->d_mps_uhi, &h->d_mig_gnode, &h->d_mps_gnode, &h->d_mig_gslot, &h->d_mps_gslot, &h->d_status, &h->d_rowstatus,
                    &h->d_mig_cost, &h->d_mig_perm, &h->d_mig_rankg, &h->d_mig_ufg, &h->d_mig_maskg, &h->d_profcost, &h->d_mps_cost, &h->d_mps_perm, &h->d_mps_sizecost,
                    &h->rp[0].rows, &h->rp[0].work, &h->rp[0].meta, &h->rp[0].cnt,
                    &h->rp[1].rows, &h->rp[1].work, &h->rp[1].meta, &h->rp[1].cnt};
@@ -820,7 +856,10 @@ int nosplan_score_mig(nosplan_t* h, int n_demands, const int32_t* dem_off, const
   if (!h) return NOSPLAN_ERR_ARG;
   h->err.clear();
   if (!h->have_mig) return fail(h, NOSPLAN_ERR_ARG, "no MIG snapshot");
-  int rc = check_demands(h, n_demands, dem_off, dem_key, dem_qty, h->P);
+  // with the rows-by-key scorer the rows are validated on the device while they are grouped
+  const bool dev_check = mig_ordered(h);
+  int rc = dev_check ? check_demands_head(h, n_demands, dem_off, dem_key, dem_qty)
+                     : check_demands(h, n_demands, dem_off, dem_key, dem_qty, h->P);
   if (rc) return rc;
   if ((rc = bind(h))) return rc;
   if (n_evals) *n_evals = (int64_t)n_demands * h->mig_evals;
@@ -848,7 +887,9 @@ int nosplan_score_mig(nosplan_t* h, int n_demands, const int32_t* dem_off, const
   if (first_choice) CU(cudaMemcpyAsync(first_choice, h->d_out[3].p, (size_t)D * h->mig_gs, cudaMemcpyDeviceToHost, st));
   if (updated && h->mig_n) CU(cudaMemcpyAsync(updated, h->d_out[1].p, (size_t)D * h->mig_n, cudaMemcpyDeviceToHost, st));
   if (choice && h->mig_tg) CU(cudaMemcpyAsync(choice, h->d_out[2].p, (size_t)D * h->mig_tg, cudaMemcpyDeviceToHost, st));
+  if (dev_check) CU(cudaMemcpyAsync(h->h_status, h->d_rowstatus.p, 8, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
+  if (dev_check && h->h_status[0] != ~0ull) return describe_bad_row(h, h->h_status[0], dem_off, dem_key, dem_qty, h->P);
   return NOSPLAN_OK;
 }
 
@@ -859,7 +900,9 @@ int nosplan_score_mps(nosplan_t* h, int n_demands, const int32_t* dem_off, const
   h->err.clear();
   if (!h->have_mps) return fail(h, NOSPLAN_ERR_ARG, "no MPS snapshot");
   if ((out_free == nullptr) != (out_free_mask == nullptr)) return fail(h, NOSPLAN_ERR_ARG, "out_free and out_free_mask go together");
-  int rc = check_demands(h, n_demands, dem_off, dem_key, dem_qty, h->S);
+  const bool dev_check = mps_ordered(h);
+  int rc = dev_check ? check_demands_head(h, n_demands, dem_off, dem_key, dem_qty)
+                     : check_demands(h, n_demands, dem_off, dem_key, dem_qty, h->S);
   if (rc) return rc;
   if ((rc = bind(h))) return rc;
   if (n_evals) *n_evals = (int64_t)n_demands * h->mps_evals;
@@ -886,7 +929,9 @@ int nosplan_score_mps(nosplan_t* h, int n_demands, const int32_t* dem_off, const
     CU(cudaMemcpyAsync(out_free, h->d_out[2].p, (size_t)D * h->mps_tg * h->S, cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(out_free_mask, h->d_out[3].p, sizeof(uint32_t) * (size_t)D * h->mps_tg, cudaMemcpyDeviceToHost, st));
   }
+  if (dev_check) CU(cudaMemcpyAsync(h->h_status, h->d_rowstatus.p, 8, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
+  if (dev_check && h->h_status[0] != ~0ull) return describe_bad_row(h, h->h_status[0], dem_off, dem_key, dem_qty, h->S);
   return NOSPLAN_OK;
 }
 

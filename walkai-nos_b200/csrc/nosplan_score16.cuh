@@ -170,26 +170,42 @@ __global__ void mps_cost_kernel(int N, int S, const int32_t* __restrict__ sizes,
 constexpr int kRowBuckets = 33;  // up to 32 keys + "any other row"
 constexpr int kNoRow = 63;
 
-__device__ __forceinline__ int row_bucket(int d, int P, const int32_t* __restrict__ dem_off,
-                                          const int32_t* __restrict__ dem_key) {
-  const int e0 = __ldg(dem_off + d), k = __ldg(dem_off + d + 1) - e0;
-  if (k != 1) return P;
-  const int key = __ldg(dem_key + e0);
-  return (unsigned)key < (unsigned)P ? key : P;
-}
-
+// The rows are validated here as well (the host does not walk them): a row that breaks a limit of the ABI
+// joins no bucket, so no scorer ever sees it, and the lowest failing code row * 64 + sub lands in *status
+// (sub 0: dem_off descending, 1: too many keys, 2 + 3j / 3 + 3j / 4 + 3j: key j out of range / not
+// ascending / quantity out of range); the host turns the code back into its message.
 // state[0 .. kRowBuckets) = cursors, state[kRowBuckets] = ticket; all zero on entry and on exit
-__global__ void rows_group_kernel(int D, int P, int chunk, const int32_t* __restrict__ dem_off,
-                                  const int32_t* __restrict__ dem_key, const int32_t* __restrict__ key_cost,
-                                  int32_t* __restrict__ state, int32_t* __restrict__ rows, int32_t* __restrict__ work,
-                                  int32_t* __restrict__ meta, int32_t* __restrict__ first_node) {
+__global__ void rows_group_kernel(int D, int P, int chunk, int max_keys, int max_qty, const int32_t* __restrict__ dem_off,
+                                  const int32_t* __restrict__ dem_key, const int32_t* __restrict__ dem_qty,
+                                  const int32_t* __restrict__ key_cost, int32_t* __restrict__ state,
+                                  int32_t* __restrict__ rows, int32_t* __restrict__ work, int32_t* __restrict__ meta,
+                                  int32_t* __restrict__ first_node, unsigned long long* __restrict__ status) {
   __shared__ int s_last;
   const int d = blockIdx.x * blockDim.x + threadIdx.x;  // blockDim is a multiple of 32: whole warps reach the match
   const int lane = threadIdx.x & 31;
   int b = kNoRow;
   if (d < D) {
-    b = row_bucket(d, P, dem_off, dem_key);
     first_node[d] = kNoNode;
+    const int e0 = __ldg(dem_off + d), k = __ldg(dem_off + d + 1) - e0, nnz = __ldg(dem_off + D);
+    int sub = -1, key0 = 0;
+    if (k < 0 || e0 < 0 || e0 + k > nnz) {  // entries outside [0, dem_off[D]) are never read
+      sub = 0;
+    } else if (k > max_keys) {
+      sub = 1;
+    } else {
+      int prev = -1;
+      for (int j = 0; j < k; ++j) {
+        const int key = __ldg(dem_key + e0 + j), q = __ldg(dem_qty + e0 + j);
+        if (key < 0 || key >= P) sub = 2 + 3 * j;
+        else if (j > 0 && key <= prev) sub = 3 + 3 * j;
+        else if (q < 0 || q > max_qty) sub = 4 + 3 * j;
+        if (sub >= 0) break;
+        if (j == 0) key0 = key;
+        prev = key;
+      }
+    }
+    if (sub >= 0) atomicMin(status, (unsigned long long)d * 64ull + (unsigned long long)sub);
+    else b = k == 1 ? key0 : P;
   }
   const uint32_t peers = __match_any_sync(0xffffffffu, b);  // one atomic per bucket per warp
   const int leader = __ffs(peers) - 1;
@@ -254,11 +270,11 @@ struct MigScore16Args {
 //                                (rank << 4 | (15 - c), 0x8000 = cannot be applied), then
 //                                uf = free | (-(used + free) & 0xffff) << 16 of profile p, then
 //                                mo = shared address of the ct2 row of the GPU's model
-//   row/qty [kRowCap]            the work item's rows
+//   row/qty/first [kRowCap]      the work item's rows, their quantities, their first updating node so far
 // One pointer walks the slots (stride (2cw + 2) * TN words), every load has a constant offset from it.
 __host__ __device__ inline size_t mig_score16_smem_bytes(int n_models, int gs, int cmax, int tn) {
   const size_t cw = (size_t)(cmax + 3) / 4;
-  return ((size_t)n_models * 2 * cw * 4 + 15) / 16 * 16 + (size_t)gs * (2 * cw + 2) * tn * 4 + (size_t)kRowCap * 8;
+  return ((size_t)n_models * 2 * cw * 4 + 15) / 16 * 16 + (size_t)gs * (2 * cw + 2) * tn * 4 + (size_t)kRowCap * 12;
 }
 
 __device__ __forceinline__ uint32_t lds_u32(uint32_t saddr) {
@@ -289,6 +305,7 @@ __global__ void __launch_bounds__(TN * DS, 3) mig_score16_kernel(const MigScore1
   uint32_t* const s_slot = reinterpret_cast<uint32_t*>(smem + ct2_bytes);
   int32_t* const s_row = reinterpret_cast<int32_t*>(smem + ct2_bytes + (size_t)a.gs * kSlotStride);
   int32_t* const s_qty = s_row + kRowCap;
+  int32_t* const s_first = s_qty + kRowCap;
   const uint32_t ct2_saddr = (uint32_t)__cvta_generic_to_shared(s_ct2);
 
   // grid: x = work item (heaviest profile first), y = tile of perm[p] (heaviest nodes first), so CTAs are
@@ -308,6 +325,7 @@ __global__ void __launch_bounds__(TN * DS, 3) mig_score16_kernel(const MigScore1
     s_row[i] = d;
     // beyond 16 GPUs x 255 devices a quantity can never be covered: larger values behave the same
     s_qty[i] = min(max(__ldg(a.dem_qty + __ldg(a.dem_off + d)), 0), 32767);
+    s_first[i] = kNoNode;
   }
   for (int i = threadIdx.x; i < n_models * 2 * cw; i += TN * DS) {
     const int w = i % (2 * cw), m = i / (2 * cw);
@@ -382,22 +400,20 @@ __global__ void __launch_bounds__(TN * DS, 3) mig_score16_kernel(const MigScore1
       res0 = max(need0, 0) - (int)prov0;
       res1 = max(need1, 0) - (int)prov1;
     }
-    {
-      const int d = s_row[i];
-      if constexpr (OUT) {
-        if (a.updated && n < a.N) a.updated[(size_t)d * a.N + n] = any0 ? 1 : 0;
+    if constexpr (OUT) {
+      if (a.updated && n < a.N) {
+        a.updated[(size_t)s_row[i] * a.N + n] = any0 ? 1 : 0;
+        if (two) a.updated[(size_t)s_row[i1] * a.N + n] = any1 ? 1 : 0;
       }
-      const int wmin = __reduce_min_sync(0xffffffffu, any0 ? n : kNoNode);
-      if (lane == 0 && wmin != kNoNode) atomicMin(a.first_node + d, wmin);
     }
-    if (two) {
-      const int d = s_row[i1];
-      if constexpr (OUT) {
-        if (a.updated && n < a.N) a.updated[(size_t)d * a.N + n] = any1 ? 1 : 0;
-      }
-      const int wmin = __reduce_min_sync(0xffffffffu, any1 ? n : kNoNode);
-      if (lane == 0 && wmin != kNoNode) atomicMin(a.first_node + d, wmin);
-    }
+    // the rows' first node: a checked atomicMin in shared memory, one global atomic per row at the end
+    if (any0 && n < s_first[i]) atomicMin(&s_first[i], n);
+    if (any1 && n < s_first[i1]) atomicMin(&s_first[i1], n);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < len; i += TN * DS) {
+    const int v = s_first[i];
+    if (v != kNoNode) atomicMin(a.first_node + s_row[i], v);
   }
 }
 
@@ -410,7 +426,7 @@ __global__ void __launch_bounds__(TN * DS, 3) mig_score16_kernel(const MigScore1
 // then the nw words of free bytes (only the restore walk reads them); row/qty [kRowCap].
 __host__ __device__ inline size_t mps_score1_smem_bytes(int gs, int S, int tn) {
   const size_t nw = (size_t)(S + 3) / 4;
-  return (size_t)gs * (3 + nw) * tn * 4 + (size_t)kRowCap * 8;
+  return (size_t)gs * (3 + nw) * tn * 4 + (size_t)kRowCap * 12;
 }
 
 template <int TN, int DS, bool OUT>
@@ -423,6 +439,7 @@ __global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreAr
   uint32_t* const s_slot = reinterpret_cast<uint32_t*>(smem);
   int32_t* const s_row = reinterpret_cast<int32_t*>(smem + (size_t)a.gs * slot_stride);
   int32_t* const s_qty = s_row + kRowCap;
+  int32_t* const s_first = s_qty + kRowCap;
   const int sid = a.work[3 * blockIdx.x];
   const int32_t* rl = a.rows + a.work[3 * blockIdx.x + 1];
   const int len = a.work[3 * blockIdx.x + 2];
@@ -438,6 +455,7 @@ __global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreAr
     const int d = rl[i];
     s_row[i] = d;
     s_qty[i] = max(__ldg(a.dem_qty + __ldg(a.dem_off + d)), 0);
+    s_first[i] = kNoNode;
   }
   __syncthreads();
   for (int s = dsub; s < cnt; s += DS) {  // the DS threads of a node split its GPUs
@@ -483,11 +501,12 @@ __global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreAr
       created += k2;
       spare -= k2 * m;
       const bool upd = (k1 | k2) > 0;
-      // (d) restore the original keys, ascending size, each all-or-nothing
+      // (d) restore the original keys, ascending size, each all-or-nothing.  Only whether key sid itself
+      // comes back matters here, and only if it held something: walk the keys up to sid in that case.
       bool restored_sid = in_orig;
-      if (spare < otot) {
+      if (spare < otot && fj > 0) {
         restored_sid = false;
-        for (uint32_t mk = lds_u32(ps + 2 * TN * 4); mk; mk &= mk - 1) {
+        for (uint32_t mk = lds_u32(ps + 2 * TN * 4) & ((2u << sid) - 1u); mk; mk &= mk - 1) {
           const int key = __ffs(mk) - 1;
           const int need = s_sz[key] * (int)((lds_u32(ps + (3 + (key >> 2)) * TN * 4) >> ((key & 3) * 8)) & 0xffu);
           if (spare >= need) {
@@ -500,13 +519,16 @@ __global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreAr
       any |= upd;
       resid = max(resid - nf, 0);
     }
-    const int d = s_row[i];
     if constexpr (OUT) {
-      if (a.updated && n < a.N) a.updated[(size_t)d * a.N + n] = any ? 1 : 0;
+      if (a.updated && n < a.N) a.updated[(size_t)s_row[i] * a.N + n] = any ? 1 : 0;
     }
-    const int mine = any ? n : kNoNode;
-    const int wmin = __reduce_min_sync(0xffffffffu, mine);
-    if (lane == 0 && wmin != kNoNode) atomicMin(a.first_node + d, wmin);
+    // the row's first node: a checked atomicMin in shared memory, one global atomic per row at the end
+    if (any && n < s_first[i]) atomicMin(&s_first[i], n);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < len; i += TN * DS) {
+    const int v = s_first[i];
+    if (v != kNoNode) atomicMin(a.first_node + s_row[i], v);
   }
 }
 
