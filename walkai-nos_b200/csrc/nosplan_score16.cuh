@@ -350,7 +350,6 @@ __global__ void __launch_bounds__(TN * DS, 3) mig_score16_kernel(const MigScore1
   }
   __syncthreads();
 
-  const int lane = threadIdx.x & 31;
   uint32_t k512;  // opaque 2^9: keeps "provided << 9 | rank" an IMAD (FMA pipe) instead of ALU shift + add
   asm("mov.u32 %0, 512;" : "=r"(k512));
   const uint32_t ps0 = (uint32_t)__cvta_generic_to_shared(s_slot) + (uint32_t)tid * 4u;
@@ -474,7 +473,6 @@ __global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreAr
   }
   __syncthreads();
 
-  const int lane = threadIdx.x & 31;
   const int m = s_sz[sid];
   const uint32_t inv = m == 1 ? 0u : 0xFFFFFFFFu / (uint32_t)m + 1u;  // exact multiply-high division (div_small)
   const uint32_t ps0 = (uint32_t)__cvta_generic_to_shared(s_slot) + (uint32_t)tid * 4u;
