@@ -230,6 +230,9 @@ int score_waves() {  // measurement knob: waves of CTAs per scorer launch
   return w;
 }
 
+#ifndef NOSPLAN_RB
+#define NOSPLAN_RB 2
+#endif
 constexpr int kScoreTN = 128;
 constexpr int kScoreDS = 4;  // threads per node in the MIG scorer
 
@@ -301,7 +304,7 @@ int plan_rows(nosplan_t* h, int kind, int D, int n_keys, int chunk, const int32_
 
 template <int CW, bool OUT>
 int launch_mig_score16_cw(nosplan_t* h, const MigScoreArgs& a, int tiles, cudaStream_t st) {
-  auto kern = mig_score16_kernel<kScoreTN, kScoreDS, CW, OUT>;
+  auto kern = mig_score16_kernel<kScoreTN, kScoreDS, CW, OUT, NOSPLAN_RB>;
   const size_t smem = mig_score16_smem_bytes(h->h_tables.n_models, a.gs, a.cmax, kScoreTN);
   if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MIG scorer tile needs %zu bytes of shared memory", smem);
   CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

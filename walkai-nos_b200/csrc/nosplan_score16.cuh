@@ -289,8 +289,9 @@ __device__ __forceinline__ uint2 lds_v2(uint32_t saddr) {
 }
 
 // OUT: the call wants updated[] / choice[] (the per-row stores stay out of the hot instantiation)
-template <int TN, int DS, int CW, bool OUT>
-__global__ void __launch_bounds__(TN * DS, 3) mig_score16_kernel(const MigScore16Args A) {
+// RB: demand rows a thread scores per pass over its node's GPUs
+template <int TN, int DS, int CW, bool OUT, int RB>
+__global__ void __launch_bounds__(TN * DS, RB > 2 ? 2 : 3) mig_score16_kernel(const MigScore16Args A) {
   const MigScoreArgs& a = A.base;
   if ((int)blockIdx.x >= A.meta[0]) return;  // the grid is sized for the worst split of the rows
   extern __shared__ __align__(16) unsigned char smem[];
@@ -353,61 +354,75 @@ __global__ void __launch_bounds__(TN * DS, 3) mig_score16_kernel(const MigScore1
   uint32_t k512;  // opaque 2^9: keeps "provided << 9 | rank" an IMAD (FMA pipe) instead of ALU shift + add
   asm("mov.u32 %0, 512;" : "=r"(k512));
   const uint32_t ps0 = (uint32_t)__cvta_generic_to_shared(s_slot) + (uint32_t)tid * 4u;
-  // Two rows per thread and pass over the node's GPUs: the rank words and the candidate row of a GPU are
-  // loaded once and scored against both rows (each keeps its own residual; a row that is already covered
+  // RB rows per thread and pass over the node's GPUs: the rank words and the candidate row of a GPU are
+  // loaded once and scored against all of them (each keeps its own residual; a row that is already covered
   // has needed <= 0, which makes every provided count 0 without a branch).
-  for (int i = dsub; i < len; i += 2 * DS) {
-    const int i1 = i + DS;
-    const bool two = i1 < len;  // uniform over the warp
-    int res0 = s_qty[i], res1 = two ? s_qty[i1] : 0;
-    uint32_t any0 = 0, any1 = 0;
+  for (int i = dsub; i < len; i += RB * DS) {
+    int res[RB];
+    uint32_t any[RB];
+#pragma unroll
+    for (int r = 0; r < RB; ++r) {
+      res[r] = (i + r * DS < len) ? s_qty[i + r * DS] : 0;  // uniform over the warp
+      any[r] = 0;
+    }
     uint32_t ps = ps0;
     for (int s = 0; s < cnt; ++s, ps += kSlotStride) {
-      // both requests covered: every candidate of the remaining GPUs provides 0 (gpu.go:172-175)
-      if ((res0 | res1) == 0) break;
+      // every request covered: every candidate of the remaining GPUs provides 0 (gpu.go:172-175)
+      int left = 0;
+#pragma unroll
+      for (int r = 0; r < RB; ++r) left |= res[r];
+      if (left == 0) break;
       const uint32_t x = lds_u32(ps + kUfOff);
       const int fj = (int)(x & 0xffu);
-      const int need0 = res0 - fj, need1 = res1 - fj;
+      int need[RB], most = 0;
+      uint32_t bst[RB];
+#pragma unroll
+      for (int r = 0; r < RB; ++r) {
+        need[r] = res[r] - fj;
+        most = max(most, need[r]);
+        bst[r] = 0;
+      }
       // two candidates per instruction: key = provided << 9 | rank << 4 | (15 - index) per signed 16-bit
       // lane; a lane that cannot be applied carries 0x8000 and stays below the running maximum (>= 0)
-      uint32_t b0 = 0, b1 = 0;
-      if (max(need0, need1) > 0) {
+      if (most > 0) {
         const uint32_t mo = lds_u32(ps + kMoOff);
         const uint32_t nc2 = __byte_perm(x, 0u, 0x3232u);  // -(used + free) in both lanes
-        const uint32_t nd0 = (uint32_t)need0 * 0x10001u;   // a negative value stays negative in both lanes
-        const uint32_t nd1 = (uint32_t)need1 * 0x10001u;
+        uint32_t nd[RB];
+#pragma unroll
+        for (int r = 0; r < RB; ++r) nd[r] = (uint32_t)need[r] * 0x10001u;  // a negative value stays negative in both lanes
 #pragma unroll
         for (int w = 0; w < cw; ++w) {
           const uint32_t ra = lds_u32(ps + (2 * w) * TN * 4);
           const uint32_t rb = lds_u32(ps + (2 * w + 1) * TN * 4);
           const uint2 c2 = lds_v2(mo + 8 * w);
-          b0 = __vimax3_s16x2(b0, __viaddmin_s16x2_relu(c2.x, nc2, nd0) * k512 + ra,
-                              __viaddmin_s16x2_relu(c2.y, nc2, nd0) * k512 + rb);
-          b1 = __vimax3_s16x2(b1, __viaddmin_s16x2_relu(c2.x, nc2, nd1) * k512 + ra,
-                              __viaddmin_s16x2_relu(c2.y, nc2, nd1) * k512 + rb);
+#pragma unroll
+          for (int r = 0; r < RB; ++r)
+            bst[r] = __vimax3_s16x2(bst[r], __viaddmin_s16x2_relu(c2.x, nc2, nd[r]) * k512 + ra,
+                                    __viaddmin_s16x2_relu(c2.y, nc2, nd[r]) * k512 + rb);
         }
       }
-      const uint32_t best0 = max(b0 & 0xffffu, b0 >> 16), best1 = max(b1 & 0xffffu, b1 >> 16);
-      const uint32_t prov0 = best0 >> 9, prov1 = best1 >> 9;  // 0 unless some applicable candidate provides something
-      any0 |= prov0;
-      any1 |= prov1;
-      if constexpr (OUT) {
-        if (a.choice && prov0 != 0u) a.choice[(size_t)s_row[i] * a.tg + g0 + s] = (int8_t)(15 - (int)(best0 & 15u));
-        if (a.choice && prov1 != 0u) a.choice[(size_t)s_row[i1] * a.tg + g0 + s] = (int8_t)(15 - (int)(best1 & 15u));
-      }
-      // what is still missing after this GPU (see mig_score_kernel)
-      res0 = max(need0, 0) - (int)prov0;
-      res1 = max(need1, 0) - (int)prov1;
-    }
-    if constexpr (OUT) {
-      if (a.updated && n < a.N) {
-        a.updated[(size_t)s_row[i] * a.N + n] = any0 ? 1 : 0;
-        if (two) a.updated[(size_t)s_row[i1] * a.N + n] = any1 ? 1 : 0;
+#pragma unroll
+      for (int r = 0; r < RB; ++r) {
+        const uint32_t best = max(bst[r] & 0xffffu, bst[r] >> 16);
+        const uint32_t prov = best >> 9;  // 0 unless some applicable candidate provides something
+        any[r] |= prov;
+        if constexpr (OUT) {
+          if (a.choice && prov != 0u) a.choice[(size_t)s_row[i + r * DS] * a.tg + g0 + s] = (int8_t)(15 - (int)(best & 15u));
+        }
+        res[r] = max(need[r], 0) - (int)prov;  // what is still missing after this GPU (see mig_score_kernel)
       }
     }
-    // the rows' first node: a checked atomicMin in shared memory, one global atomic per row at the end
-    if (any0 && n < s_first[i]) atomicMin(&s_first[i], n);
-    if (any1 && n < s_first[i1]) atomicMin(&s_first[i1], n);
+#pragma unroll
+    for (int r = 0; r < RB; ++r) {
+      const int ir = i + r * DS;
+      if (ir < len) {
+        if constexpr (OUT) {
+          if (a.updated && n < a.N) a.updated[(size_t)s_row[ir] * a.N + n] = any[r] ? 1 : 0;
+        }
+        // the row's first node: a checked atomicMin in shared memory, one global atomic per row at the end
+        if (any[r] && n < s_first[ir]) atomicMin(&s_first[ir], n);
+      }
+    }
   }
   __syncthreads();
   for (int i = threadIdx.x; i < len; i += TN * DS) {

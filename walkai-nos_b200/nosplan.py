@@ -10,7 +10,7 @@ from typing import Dict, List, Optional, Sequence
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB = os.path.join(_HERE, "libnosplan.so")
+_LIB = os.environ.get("NOSPLAN_LIB") or os.path.join(_HERE, "libnosplan.so")  # NOSPLAN_LIB: A/B builds of the same library
 
 i32p = C.POINTER(C.c_int32)
 u32p = C.POINTER(C.c_uint32)
