@@ -311,7 +311,8 @@ int launch_mig_score16_cw(nosplan_t* h, const MigScoreArgs& a, int tiles, cudaSt
   int occ = 0;
   CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kScoreTN * kScoreDS, smem));
   int chunk = 16, gy = 1;
-  pick_chunks(h->sm_count, tiles, a.D, 16, &chunk, &gy, std::max(occ, 1) * score_waves());
+  // at least 64 rows per work item: on a small shard the tile load would otherwise outweigh the rows
+  pick_chunks(h->sm_count, tiles, a.D, 64, &chunk, &gy, std::max(occ, 1) * score_waves());
   chunk = std::min(chunk, kRowCap);
   int max_work = 0;
   int rc = plan_rows(h, 0, a.D, h->P, chunk, a.dem_off, a.dem_key, a.dem_qty, h->d_profcost.as<int32_t>(), a.first_node, st, &max_work);
@@ -447,7 +448,8 @@ int launch_mps_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
     a.gs = h->mps_gs;
     int tiles = (h->mps_n + kScoreTN - 1) / kScoreTN;
     int gy;
-    pick_chunks(h->sm_count, tiles, D, 16, &a.d_chunk, &gy, ((ordered && !d_free) ? 4 : 3) * score_waves());  // CTAs per SM that fit
+    pick_chunks(h->sm_count, tiles, D, (ordered && !d_free) ? 128 : 16, &a.d_chunk, &gy,
+                ((ordered && !d_free) ? 4 : 3) * score_waves());  // CTAs per SM that fit; >= 128 rows per item
     const size_t smem = mps_score_smem_bytes(h->mps_gs, h->S, kScoreTN);
     if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MPS scorer tile needs %zu bytes of shared memory", smem);
     CU(cudaFuncSetAttribute(mps_score_kernel<kScoreTN, kScoreDS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
