@@ -354,7 +354,7 @@ def main():
             "config": workload_config(cfg, args),
             "e2e": {"value": e2e_val, "unit": "evals/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "ms_per_step": float(e2e_t.item()) * 1e3},
-            "gpu_launches": int(args.steps * ((4 if Dm else 0) + (4 if Dp else 0) + (2 if exchange.startswith("peer") else 0))),
+            "gpu_launches": int(args.steps * ((3 if Dm else 0) + (3 if Dp else 0) + (2 if exchange.startswith("peer") else 0))),
             "exchange": exchange,
             "planner_latency_ms_p50": float(np.median(lat)) if lat else None,
             "planner_latency_ms_p95": float(np.percentile(lat, 95)) if lat else None,

@@ -375,11 +375,11 @@ int check_demands_head(nosplan_t* h, int D, const int32_t* off, const int32_t* k
 }
 
 int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d_key, const int32_t* d_qty,
-                     int32_t* d_first, uint8_t* d_updated, int8_t* d_choice, cudaStream_t st) {
+                     int32_t* d_first, uint8_t* d_updated, int8_t* d_choice, cudaStream_t st, int base = 0) {
   if (D == 0) return NOSPLAN_OK;
   int rc = NOSPLAN_OK;
   const bool ordered = mig_ordered(h);
-  if (!ordered) fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, kNoNode);  // else rows_group_kernel does it
+  if (!ordered) fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, -1);  // else rows_group_kernel does it
   if (d_choice) CU(cudaMemsetAsync(d_choice, 0xff, (size_t)D * h->mig_tg, st));
   if (h->mig_n > 0) {
     MigScoreArgs a;
@@ -400,6 +400,7 @@ int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
     a.dem_key = d_key;
     a.dem_qty = d_qty;
     a.first_node = d_first;
+    a.node_base = base;
     a.updated = d_updated;
     a.choice = d_choice;
     a.row_list = nullptr;
@@ -427,7 +428,7 @@ int launch_mps_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
                      int32_t* d_first, uint8_t* d_updated, uint8_t* d_free, uint32_t* d_mask, cudaStream_t st, int base = 0) {
   if (D == 0) return NOSPLAN_OK;
   const bool ordered = mps_ordered(h);
-  if (!ordered) fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, kNoNode);  // else rows_group_kernel does it
+  if (!ordered) fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, -1);  // else rows_group_kernel does it
   if (h->mps_n > 0) {
     MpsScoreArgs a;
     a.sizes = h->d_mps_sizes.as<int32_t>();
@@ -442,6 +443,7 @@ int launch_mps_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
     a.dem_key = d_key;
     a.dem_qty = d_qty;
     a.first_node = d_first;
+    a.node_base = base;
     a.updated = d_updated;
     a.out_free = d_free;
     a.out_mask = d_mask;
@@ -482,7 +484,6 @@ int launch_mps_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
     }
     mps_score_kernel<kScoreTN, kScoreDS><<<dim3(tiles, gy), kScoreTN * kScoreDS, smem, st>>>(a);
   }
-  nonode_to_minus1_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, base);
   CU(cudaGetLastError());
   return NOSPLAN_OK;
 }
@@ -834,9 +835,8 @@ int nosplan_score_mig_dev(nosplan_t* h, int n_demands, const int32_t* dem_off, c
   int rc = bind(h);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  rc = launch_mig_score(h, n_demands, dem_off, dem_key, dem_qty, first_node, updated, choice, st);
+  rc = launch_mig_score(h, n_demands, dem_off, dem_key, dem_qty, first_node, updated, choice, st, h->mig_base);
   if (rc) return rc;
-  if (n_demands > 0) nonode_to_minus1_kernel<<<(n_demands + 255) / 256, 256, 0, st>>>(first_node, n_demands, h->mig_base);
   CU(cudaGetLastError());
   return NOSPLAN_OK;
 }
@@ -1390,7 +1390,7 @@ extern "C" int nosplan_score_mig_static(nosplan_t* h, int n_nodes, int gpus_per_
   const int D = n_demands;
   const int gs = std::max(gpus_per_node, 1);
   const int npad = std::max(32, (n_nodes + 31) / 32 * 32);
-  fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(first_node, D, kNoNode);
+  fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(first_node, D, -1);
   if (n_nodes > 0) {
     const int threads = std::max(npad, n_nodes + 1);
     static_pack_kernel<<<(threads + 127) / 128, 128, 0, st>>>(sc, n_nodes, h->P, gpus_per_node, npad, valid, model, used, free_);
@@ -1412,6 +1412,7 @@ extern "C" int nosplan_score_mig_static(nosplan_t* h, int n_nodes, int gpus_per_
     a.dem_key = dem_key;
     a.dem_qty = dem_qty;
     a.first_node = first_node;
+    a.node_base = 0;
     a.updated = nullptr;
     a.choice = nullptr;
     a.row_list = nullptr;
@@ -1423,7 +1424,6 @@ extern "C" int nosplan_score_mig_static(nosplan_t* h, int n_nodes, int gpus_per_
     if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MIG scorer tile needs %zu bytes of shared memory", smem);
     if ((rc = launch_mig_score_kernel(h, a, dim3(tiles, gy), smem, st))) return rc;  // sets a smem limit, allocates nothing
   }
-  nonode_to_minus1_kernel<<<(D + 255) / 256, 256, 0, st>>>(first_node, D, 0);
   CU(cudaGetLastError());
   return NOSPLAN_OK;
 }

@@ -223,7 +223,8 @@ struct MigScoreArgs {
   const int32_t* dem_off;
   const int32_t* dem_key;
   const int32_t* dem_qty;
-  int32_t* first_node;  // atomicMin target, pre-filled with kNoNode
+  int32_t* first_node;  // unsigned atomicMin target, pre-filled with -1 (0xffffffff = no node)
+  int node_base;        // global index of node 0 (0 unless the node list is sharded)
   uint8_t* updated;     // [D][N] or null
   int8_t* choice;       // [D][tg] or null
   // optional: score only the rows row_list[row_meta[1] .. + row_meta[2]) (device-side list and counts)
@@ -506,13 +507,14 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
       any = mig_row_generic<TN, K16>(a, cw, tile, tid, cnt, g0, d, k, e0);
     }
     if (a.updated && n < a.N) a.updated[(size_t)d * a.N + n] = any ? 1 : 0;
-    const int mine = any ? n : kNoNode;
-    const int wmin = __reduce_min_sync(0xffffffffu, mine);
-    if (lane == 0 && wmin != kNoNode) atomicMin(a.first_node + d, wmin);
+    // -1 read as unsigned is above every node index: the minimum needs no final pass
+    const unsigned mine = any ? (unsigned)(n + a.node_base) : 0xffffffffu;
+    const unsigned wmin = __reduce_min_sync(0xffffffffu, mine);
+    if (lane == 0 && wmin != 0xffffffffu) atomicMin(reinterpret_cast<unsigned*>(a.first_node) + d, wmin);
   }
 }
 
-// first_node: kNoNode -> -1; optionally re-walk the winning node to emit its per-GPU choices
+// re-walks the winning node of every row to emit its per-GPU choices
 __global__ void mig_finalize_kernel(const MigTables* __restrict__ T, const uint4* __restrict__ a_used,
                                     const uint4* __restrict__ a_free, const uint8_t* __restrict__ a_model,
                                     const int32_t* __restrict__ gpu_off, int D, int gs, const int32_t* __restrict__ dem_off,
@@ -520,9 +522,7 @@ __global__ void mig_finalize_kernel(const MigTables* __restrict__ T, const uint4
                                     int32_t* __restrict__ first_node, int8_t* __restrict__ first_choice) {
   const int d = blockIdx.x * blockDim.x + threadIdx.x;
   if (d >= D) return;
-  int fn = first_node[d];
-  if (fn == kNoNode) fn = -1;
-  first_node[d] = fn;
+  const int fn = first_node[d];
   if (!first_choice) return;
   int8_t ch[NOSPLAN_MAX_GPUS_PER_NODE];
   for (int s = 0; s < NOSPLAN_MAX_GPUS_PER_NODE; ++s) ch[s] = -1;
@@ -542,13 +542,6 @@ __global__ void mig_finalize_kernel(const MigTables* __restrict__ T, const uint4
 __global__ void fill_i32_kernel(int32_t* p, int n, int32_t v) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) p[i] = v;
-}
-// kNoNode -> -1; a winner gets the shard's first global node index added (0 unless sharded)
-__global__ void nonode_to_minus1_kernel(int32_t* p, int n, int base) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const int v = p[i];
-  p[i] = v == kNoNode ? -1 : v + base;
 }
 
 // GPU.InitGeometry over every GPU (gpu.go:120-129): apply the model's fewest-kinds geometry unless a
@@ -798,7 +791,8 @@ struct MpsScoreArgs {
   const int32_t* dem_off;
   const int32_t* dem_key;
   const int32_t* dem_qty;
-  int32_t* first_node;
+  int32_t* first_node;  // unsigned atomicMin target, pre-filled with -1
+  int node_base;
   uint8_t* updated;
   uint8_t* out_free;    // [D][tg][S] or null
   uint32_t* out_mask;   // [D][tg] or null
@@ -943,9 +937,10 @@ __global__ void __launch_bounds__(TN * DS, 3) mps_score_kernel(const MpsScoreArg
         if (a.updated) a.updated[(size_t)d * a.N + n] = any ? 1 : 0;
       }
     }
-    const int mine = any ? n : kNoNode;
-    const int wmin = __reduce_min_sync(0xffffffffu, mine);
-    if (lane == 0 && wmin != kNoNode) atomicMin(a.first_node + d, wmin);
+    // -1 read as unsigned is above every node index: the minimum needs no final pass
+    const unsigned mine = any ? (unsigned)(n + a.node_base) : 0xffffffffu;
+    const unsigned wmin = __reduce_min_sync(0xffffffffu, mine);
+    if (lane == 0 && wmin != 0xffffffffu) atomicMin(reinterpret_cast<unsigned*>(a.first_node) + d, wmin);
   }
 }
 

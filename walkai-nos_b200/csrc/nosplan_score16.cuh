@@ -166,7 +166,7 @@ __global__ void mps_cost_kernel(int N, int S, const int32_t* __restrict__ sizes,
 // bucket P: every other row); bucket b owns rows[b * D, (b + 1) * D), filled through an atomic cursor.
 // The block that finishes last turns the counts into work items {key, start in rows[], length <= chunk},
 // heaviest key first, and meta[0] = number of items, meta[1] = start of bucket P, meta[2] = its size; it
-// leaves the cursors and the ticket at zero for the next call.  first_node[] is put to rest on the way.
+// leaves the cursors and the ticket at zero for the next call.  first_node[] is put to rest (-1) on the way.
 constexpr int kRowBuckets = 33;  // up to 32 keys + "any other row"
 constexpr int kNoRow = 63;
 
@@ -185,7 +185,7 @@ __global__ void rows_group_kernel(int D, int P, int chunk, int max_keys, int max
   const int lane = threadIdx.x & 31;
   int b = kNoRow;
   if (d < D) {
-    first_node[d] = kNoNode;
+    first_node[d] = -1;  // "no node"; the scorers fold winners in with an unsigned atomicMin
     const int e0 = __ldg(dem_off + d), k = __ldg(dem_off + d + 1) - e0, nnz = __ldg(dem_off + D);
     int sub = -1, key0 = 0;
     if (k < 0 || e0 < 0 || e0 + k > nnz) {  // entries outside [0, dem_off[D]) are never read
@@ -427,7 +427,7 @@ __global__ void __launch_bounds__(TN * DS, RB > 2 ? 2 : 3) mig_score16_kernel(co
   __syncthreads();
   for (int i = threadIdx.x; i < len; i += TN * DS) {
     const int v = s_first[i];
-    if (v != kNoNode) atomicMin(a.first_node + s_row[i], v);
+    if (v != kNoNode) atomicMin(reinterpret_cast<unsigned*>(a.first_node) + s_row[i], (unsigned)(v + a.node_base));
   }
 }
 
@@ -541,7 +541,7 @@ __global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreAr
   __syncthreads();
   for (int i = threadIdx.x; i < len; i += TN * DS) {
     const int v = s_first[i];
-    if (v != kNoNode) atomicMin(a.first_node + s_row[i], v);
+    if (v != kNoNode) atomicMin(reinterpret_cast<unsigned*>(a.first_node) + s_row[i], (unsigned)(v + a.node_base));
   }
 }
 
