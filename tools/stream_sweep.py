@@ -51,7 +51,10 @@ for _ in range(reps):
 ev[1].record()
 torch.cuda.synchronize()
 ms = ev[0].elapsed_time(ev[1]) / reps
-state_bytes = tg * 32 + tg + N            # slot-major used+free (16 B each), model byte, count byte
+# what one launch has to read per node and per profile that occurs in the rows: the snapshot-time rank table
+# (gs * 2cw words), profile p's free|cur column (gs u16), the model bytes, the node order entry, the count
+n_prof = len(set(key.tolist()))
+state_bytes = n_prof * N * (G * 6 * 4 + G * 2 + G + 4 + 1)
 evals = D * p.mig_evals_per_demand()
 peak = 6542.1
 try:
