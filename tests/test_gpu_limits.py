@@ -154,3 +154,40 @@ def test_mps_limits():
                 assert np.array_equal(u2, ps["used"]) and np.array_equal(f2, ps["free"]) and np.array_equal(fm2, ps["free_mask"])
     finally:
         p.close()
+
+
+def test_huge_quantities_behave_like_uncoverable_ones():
+    """The scorers clamp a requested quantity (MIG: 32767) because nothing beyond 16 GPUs x 255 devices can be
+    covered; the oracle does no such thing, so the outputs must still agree up to NOSPLAN_MAX_DEMAND_QTY."""
+    import walkai_nos_b200 as pkg
+    cfg = pkg.synth.make_config(4, scale_nodes=96, scale_pods=10)
+    p = pkg.Planner(0)
+    try:
+        p.set_mig_tables(cfg["names"], cfg["geom_off"], cfg["geom_counts"])
+        p.set_mig_snapshot(cfg["mig"])
+        p.set_mps_snapshot(cfg["sizes"], cfg["mps"])
+        o = orc.Oracle(cfg["tables"], mps_sizes=cfg["sizes"])
+        qs = [1, 2, 7, 255, 256, 4079, 4080, 4081, 32767, 32768, 65535, 65536, 999999, 1000000]
+        h100 = [cfg["names"].index(x) for x in ["1g.10gb", "2g.20gb", "3g.40gb", "7g.79gb"]]
+        key = np.asarray([k for k in h100 for _ in qs], np.int32)
+        qty = np.asarray(qs * len(h100), np.int32)
+        off = np.arange(len(key) + 1, dtype=np.int32)
+        req, mask = pkg.synth.csr_to_dense(off, key, qty, len(cfg["names"]))
+        eu, ec, ef = o.score_mig(cfg["mig"], req, mask, threads=4)
+        r = p.score_mig(off, key, qty)
+        assert np.array_equal(r["updated"], eu) and np.array_equal(r["choice"], ec) and np.array_equal(r["first_node"], ef)
+        r = p.score_mig(off, key, qty, want_updated=False, want_choice=False)
+        assert np.array_equal(r["first_node"], ef)
+        S = len(cfg["sizes"])
+        key = np.asarray([s for s in range(S) for _ in qs], np.int32)
+        qty = np.asarray(qs * S, np.int32)
+        off = np.arange(len(key) + 1, dtype=np.int32)
+        req, mask = pkg.synth.csr_to_dense(off, key, qty, S)
+        eu, efree, emask, ef = o.score_mps(cfg["mps"], req, mask, threads=4)
+        r = p.score_mps(off, key, qty)
+        assert np.array_equal(r["updated"], eu) and np.array_equal(r["first_node"], ef)
+        assert np.array_equal(r["out_free_mask"], emask) and np.array_equal(r["out_free"].astype(np.int32), efree)
+        r = p.score_mps(off, key, qty, want_free=False)
+        assert np.array_equal(r["updated"], eu) and np.array_equal(r["first_node"], ef)
+    finally:
+        p.close()
