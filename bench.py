@@ -265,18 +265,26 @@ def main():
         mps = {k: (pin(v) if isinstance(v, np.ndarray) else v) for k, v in mps.items()}
     mo, mk, mq, po, pk, pq = (pin(x) for x in (mo, mk, mq, po, pk, pq))
 
+    # dtypes the ABI takes (score_snapshot passes the arrays as they are)
+    _dt = dict(gpu_off=np.int32, valid=np.uint8, model=np.int32, used=np.int32, free=np.int32, mem_gb=np.int32,
+               free_mask=np.uint32, used_mask=np.uint32)
+    for snap in (mig, mps):
+        if snap is not None:
+            for k, v in list(snap.items()):
+                if isinstance(v, np.ndarray) and v.dtype != _dt.get(k, v.dtype):
+                    snap[k] = pin(v.astype(_dt[k]))
+    mig_rows = (mo, mk, mq) if mig is not None else None
+    mps_rows = (po, pk, pq) if mps is not None else None
+
     def step_e2e():
-        if mig is not None:
-            planner.set_mig_snapshot(mig)
-        if mps is not None:
-            planner.set_mps_snapshot(cfg["sizes"], mps)
-        out, keys = [], []
-        if Dm:
-            out.append(planner.score_mig(mo, mk, mq, want_updated=False, want_choice=False, want_first_choice=True))
-            keys.append((out[-1]["first_node"], mig_lo))
-        if Dp:
-            out.append(planner.score_mps(po, pk, pq, want_updated=False, want_free=False))
-            keys.append((out[-1]["first_node"], mps_lo))
+        # one C-ABI call per pass: both snapshots in, both kinds scored (side by side inside the library), winners out
+        got = planner.score_snapshot(mig, mig_rows, cfg["sizes"], mps, mps_rows)
+        out = [got]
+        keys = []
+        if mig is not None and Dm:
+            keys.append((got["mig_first_node"], mig_lo))
+        if mps is not None and Dp:
+            keys.append((got["mps_first_node"], mps_lo))
         if world > 1 and keys:
             # the shards' winners (host arrays, local indices) -> global keys -> exchanged on the GPUs -> host
             k = np.concatenate([np.where(f >= 0, f + lo, -1).astype(np.int32) for f, lo in keys])

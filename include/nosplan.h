@@ -200,6 +200,46 @@ int nosplan_score_mig_static(nosplan_t* h, int n_nodes, int gpus_per_node, const
 int64_t nosplan_mig_evals_per_demand(const nosplan_t* h);
 int64_t nosplan_mps_evals_per_demand(const nosplan_t* h);
 
+/* ---- a whole scoring pass in one call ----------------------------------------------------------------- */
+/* nosplan_set_mig_snapshot + nosplan_score_mig and nosplan_set_mps_snapshot + nosplan_score_mps for one
+ * cluster snapshot (the structs carry exactly those calls' arguments), with the MIG half and the MPS half
+ * running side by side inside the library (two private lanes with their own streams and buffers, the
+ * second one on a worker thread owned by the handle), so that the copies and kernels of one kind overlap
+ * those of the other.  This is the call the reference's Reconcile would make once per batch of pending
+ * pods (mig_controller.go:56-98 lists nodes and pods, then decides): snapshot in, per request vector the
+ * first node that would be re-partitioned out.  Either kind may be NULL.  Needs nosplan_set_mig_tables for
+ * the MIG half.  The snapshots are NOT installed on the handle (later nosplan_plan / nosplan_score_* calls
+ * still see what nosplan_set_*_snapshot installed).  Errors of a half come back with its code and its
+ * message prefixed by "MIG: " / "MPS: ".  n_evals (may be NULL): evaluations of both halves. */
+typedef struct nosplan_mig_snapshot {
+  int32_t n_nodes;
+  const int32_t* gpu_off;
+  const uint8_t* valid;
+  const int32_t* model;
+  const int32_t* used;
+  const int32_t* free_;
+} nosplan_mig_snapshot_t;
+typedef struct nosplan_mps_snapshot {
+  int32_t n_sizes;
+  const int32_t* sizes_gb;
+  int32_t n_nodes;
+  const int32_t* gpu_off;
+  const uint8_t* valid;
+  const int32_t* mem_gb;
+  const int32_t* used;
+  const int32_t* free_;
+  const uint32_t* free_mask;
+} nosplan_mps_snapshot_t;
+typedef struct nosplan_demands {
+  int32_t n_rows;
+  const int32_t* off;
+  const int32_t* key;
+  const int32_t* qty;
+} nosplan_demands_t;
+int nosplan_score_snapshot(nosplan_t* h, const nosplan_mig_snapshot_t* mig, const nosplan_demands_t* mig_rows,
+                           int32_t* mig_first_node, int8_t* mig_first_choice, const nosplan_mps_snapshot_t* mps,
+                           const nosplan_demands_t* mps_rows, int32_t* mps_first_node, int64_t* n_evals);
+
 /* ---- sharded scoring: one process per GPU, nodes split into contiguous ranges ------------- */
 /* tryRepartition walks the whole node list and commits the first node whose UpdateGeometryFor
  * returns true (internal/controllers/gpupartitioner/mig_controller.go:146-166).  With the list split

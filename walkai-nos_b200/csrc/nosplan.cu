@@ -6,6 +6,10 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
+#include <thread>
 #include <map>
 #include <string>
 #include <vector>
@@ -93,6 +97,12 @@ struct nosplan {
   unsigned long long* h_status = nullptr;  // pinned
   cudaEvent_t status_ev = nullptr;
 
+  // nosplan_score_snapshot: two private lanes (child handles), the MPS one driven by a worker thread
+  std::vector<int32_t> tab_geom_off, tab_geom_counts;  // what nosplan_set_mig_tables was given (for the MIG lane)
+  int tab_models = 0;
+  uint64_t tab_version = 0;
+  struct Lanes* lanes = nullptr;
+
   // sharded scoring (nosplan_set_node_base, nosplan_exchange_*)
   int mig_base = 0, mps_base = 0;
   struct {
@@ -106,6 +116,8 @@ struct nosplan {
     DevBuf done, err;
   } xch;
 };
+
+void lanes_release(nosplan_t* h);  // defined with nosplan_score_snapshot
 
 namespace {
 
@@ -519,6 +531,7 @@ int nosplan_create(int device, nosplan_t** out) {
 
 void nosplan_destroy(nosplan_t* h) {
   if (!h) return;
+  lanes_release(h);
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
   if (h->xch.created) {
@@ -619,6 +632,10 @@ int nosplan_set_mig_tables(nosplan_t* h, int n_profiles, const char* const* prof
   CU(cudaStreamSynchronize(h->stream));
   h->P = n_profiles;
   h->names = names;
+  h->tab_models = n_models;
+  h->tab_geom_off.assign(geom_off, geom_off + n_models + 1);
+  h->tab_geom_counts.assign(geom_counts, geom_counts + (size_t)geom_off[n_models] * n_profiles);
+  ++h->tab_version;
   h->cmax = std::max(cmax, 1);
   int maxq = 0;
   for (size_t i = 0; i < (size_t)geom_off[n_models] * n_profiles; ++i) maxq = std::max(maxq, (int)geom_counts[i]);
@@ -1625,4 +1642,124 @@ extern "C" int nosplan_exchange_destroy(nosplan_t* h) {
   if (!h) return NOSPLAN_ERR_ARG;
   h->err.clear();
   return xchg_release(h);
+}
+
+// ---- one call for a whole scoring pass: nosplan_score_snapshot ---------------------------------------------------
+// The four calls of a pass (two snapshots in, two scorers) are each synchronous, so their copies and
+// kernels line up one after the other.  Here the MIG half and the MPS half run side by side on two private
+// child handles (own streams and buffers): the calling thread drives the MIG lane, a worker thread that
+// lives as long as the handle drives the MPS lane.  Nothing is installed on the caller's handle.
+struct Lanes {
+  nosplan_t* mig = nullptr;
+  nosplan_t* mps = nullptr;
+  uint64_t tab_version = 0;
+  std::thread worker;
+  std::mutex m;
+  std::condition_variable cv;
+  std::function<int()> job;
+  bool has_job = false, done = false, quit = false;
+  int rc = 0;
+};
+
+void lanes_release(nosplan_t* h) {
+  Lanes* L = h->lanes;
+  if (!L) return;
+  if (L->worker.joinable()) {
+    {
+      std::lock_guard<std::mutex> g(L->m);
+      L->quit = true;
+    }
+    L->cv.notify_all();
+    L->worker.join();
+  }
+  if (L->mig) nosplan_destroy(L->mig);
+  if (L->mps) nosplan_destroy(L->mps);
+  delete L;
+  h->lanes = nullptr;
+}
+
+namespace {
+int lanes_get(nosplan_t* h, Lanes** out) {
+  if (!h->lanes) {
+    Lanes* L = new Lanes();
+    if (nosplan_create(h->device, &L->mig) != NOSPLAN_OK || nosplan_create(h->device, &L->mps) != NOSPLAN_OK) {
+      if (L->mig) nosplan_destroy(L->mig);
+      if (L->mps) nosplan_destroy(L->mps);
+      delete L;
+      return fail(h, NOSPLAN_ERR_CUDA, "could not create the scoring lanes");
+    }
+    L->worker = std::thread([L] {
+      std::unique_lock<std::mutex> lk(L->m);
+      for (;;) {
+        L->cv.wait(lk, [L] { return L->has_job || L->quit; });
+        if (L->quit) return;
+        L->has_job = false;
+        std::function<int()> job = std::move(L->job);
+        lk.unlock();
+        const int rc = job();
+        lk.lock();
+        L->rc = rc;
+        L->done = true;
+        L->cv.notify_all();
+      }
+    });
+    h->lanes = L;
+  }
+  *out = h->lanes;
+  return NOSPLAN_OK;
+}
+}  // namespace
+
+extern "C" int nosplan_score_snapshot(nosplan_t* h, const nosplan_mig_snapshot_t* mig, const nosplan_demands_t* mig_rows,
+                                      int32_t* mig_first_node, int8_t* mig_first_choice, const nosplan_mps_snapshot_t* mps,
+                                      const nosplan_demands_t* mps_rows, int32_t* mps_first_node, int64_t* n_evals) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  if (n_evals) *n_evals = 0;
+  if (mig && !h->have_tables) return fail(h, NOSPLAN_ERR_ARG, "nosplan_set_mig_tables must be called first");
+  if ((mig && (!mig_rows || (mig_rows->n_rows > 0 && !mig_first_node))) || (mps && (!mps_rows || (mps_rows->n_rows > 0 && !mps_first_node))))
+    return fail(h, NOSPLAN_ERR_ARG, "a snapshot needs its demand rows and an output array");
+  Lanes* L = nullptr;
+  int rc = lanes_get(h, &L);
+  if (rc) return rc;
+  if (mig && L->tab_version != h->tab_version) {  // the MIG lane scores against the caller's tables
+    std::vector<const char*> names;
+    for (auto& n : h->names) names.push_back(n.c_str());
+    rc = nosplan_set_mig_tables(L->mig, h->P, names.data(), h->tab_models, h->tab_geom_off.data(), h->tab_geom_counts.data());
+    if (rc) return fail(h, rc, "%s", nosplan_last_error(L->mig));
+    L->tab_version = h->tab_version;
+  }
+  int64_t ev_mig = 0, ev_mps = 0;
+  if (mps) {
+    nosplan_t* c = L->mps;
+    std::lock_guard<std::mutex> g(L->m);
+    L->job = [c, mps, mps_rows, mps_first_node, &ev_mps]() -> int {
+      int r = nosplan_set_mps_snapshot(c, mps->n_sizes, mps->sizes_gb, mps->n_nodes, mps->gpu_off, mps->valid, mps->mem_gb,
+                                       mps->used, mps->free_, mps->free_mask);
+      if (r) return r;
+      return nosplan_score_mps(c, mps_rows->n_rows, mps_rows->off, mps_rows->key, mps_rows->qty, mps_first_node, nullptr,
+                               nullptr, nullptr, &ev_mps);
+    };
+    L->has_job = true;
+    L->done = false;
+    L->cv.notify_all();
+  }
+  int rc_mig = NOSPLAN_OK;
+  if (mig) {
+    nosplan_t* c = L->mig;
+    rc_mig = nosplan_set_mig_snapshot(c, mig->n_nodes, mig->gpu_off, mig->valid, mig->model, mig->used, mig->free_);
+    if (!rc_mig)
+      rc_mig = nosplan_score_mig(c, mig_rows->n_rows, mig_rows->off, mig_rows->key, mig_rows->qty, mig_first_node, mig_first_choice,
+                                 nullptr, nullptr, &ev_mig);
+  }
+  int rc_mps = NOSPLAN_OK;
+  if (mps) {
+    std::unique_lock<std::mutex> lk(L->m);
+    L->cv.wait(lk, [L] { return L->done; });
+    rc_mps = L->rc;
+  }
+  if (rc_mig) return fail(h, rc_mig, "MIG: %s", nosplan_last_error(L->mig));
+  if (rc_mps) return fail(h, rc_mps, "MPS: %s", nosplan_last_error(L->mps));
+  if (n_evals) *n_evals = ev_mig + ev_mps;
+  return NOSPLAN_OK;
 }

@@ -27,11 +27,30 @@ EXPORTS = [
     "nosplan_get_mig_state", "nosplan_get_mps_state", "nosplan_init_geometry_mig", "nosplan_score_mig_dev",
     "nosplan_score_mps_dev", "nosplan_mig_evals_per_demand", "nosplan_mps_evals_per_demand", "nosplan_score_mig_static", "nosplan_diff_plan_mig",
     "nosplan_set_node_base", "nosplan_exchange_create", "nosplan_exchange_open", "nosplan_exchange_min_dev",
-    "nosplan_exchange_status", "nosplan_exchange_destroy",
+    "nosplan_exchange_status", "nosplan_exchange_destroy", "nosplan_score_snapshot",
 ]
 
 
 IPC_HANDLE_BYTES = 64
+
+
+class _MigSnap(C.Structure):
+    _fields_ = [("n_nodes", C.c_int32), ("gpu_off", C.c_void_p), ("valid", C.c_void_p), ("model", C.c_void_p),
+                ("used", C.c_void_p), ("free_", C.c_void_p)]
+
+
+class _MpsSnap(C.Structure):
+    _fields_ = [("n_sizes", C.c_int32), ("sizes_gb", C.c_void_p), ("n_nodes", C.c_int32), ("gpu_off", C.c_void_p),
+                ("valid", C.c_void_p), ("mem_gb", C.c_void_p), ("used", C.c_void_p), ("free_", C.c_void_p),
+                ("free_mask", C.c_void_p)]
+
+
+class _Demands(C.Structure):
+    _fields_ = [("n_rows", C.c_int32), ("off", C.c_void_p), ("key", C.c_void_p), ("qty", C.c_void_p)]
+
+
+def _addr(a):
+    return None if a is None else a.ctypes.data
 
 
 class NosplanError(RuntimeError):
@@ -202,6 +221,40 @@ class Planner:
         self._ck(self.L.nosplan_score_mps(self.h, D, _p(off, i32p), _p(key, i32p), _p(qty, i32p), _p(first, i32p),
                                           _p(upd, u8p), _p(of, u8p), _p(om, u32p), C.byref(ne)))
         return dict(first_node=first, updated=upd, out_free=of, out_free_mask=om, n_evals=ne.value)
+
+    def score_snapshot(self, mig=None, mig_rows=None, sizes_gb=None, mps=None, mps_rows=None, want_first_choice=True):
+        """One call for a whole scoring pass (nosplan_score_snapshot): mig / mps are snapshot dicts as for
+        set_*_snapshot, *_rows = (off, key, qty).  Nothing is installed on the handle.  Arrays must already be
+        contiguous int32 / uint8 / uint32 (they are passed as they are)."""
+        keep = []
+        ms = ps = md = pd = None
+        out = {}
+        fm = ff = fp = None
+        if mig is not None:
+            N = int(mig["n_nodes"])
+            ms = _MigSnap(N, *[_addr(mig[k]) for k in ("gpu_off", "valid", "model", "used", "free")])
+            off, key, qty = mig_rows
+            md = _Demands(len(off) - 1, _addr(off), _addr(key), _addr(qty))
+            go = mig["gpu_off"]
+            if getattr(self, "_gs_of", None) is not go:
+                self._gs_of, self._gs = go, (int(np.max(np.diff(go))) if N else 0)
+            fm = np.empty(len(off) - 1, np.int32)
+            ff = np.empty((len(off) - 1, max(self._gs, 1)), np.int8) if want_first_choice else None
+            out.update(mig_first_node=fm, mig_first_choice=ff)
+        if mps is not None:
+            sizes = np.ascontiguousarray(sizes_gb, np.int32)
+            keep.append(sizes)
+            ps = _MpsSnap(len(sizes), _addr(sizes), int(mps["n_nodes"]),
+                          *[_addr(mps.get(k)) for k in ("gpu_off", "valid", "mem_gb", "used", "free", "free_mask")])
+            off, key, qty = mps_rows
+            pd = _Demands(len(off) - 1, _addr(off), _addr(key), _addr(qty))
+            fp = np.empty(len(off) - 1, np.int32)
+            out.update(mps_first_node=fp)
+        ne = C.c_int64(0)
+        ref = lambda x: None if x is None else C.byref(x)
+        self._ck(self.L.nosplan_score_snapshot(self.h, ref(ms), ref(md), _p(fm), _p(ff), ref(ps), ref(pd), _p(fp), C.byref(ne)))
+        out["n_evals"] = ne.value
+        return out
 
     # ---- planner -------------------------------------------------------------------------------------
     def plan(self, kind, off, key, qty, gate=True, sched=True):
