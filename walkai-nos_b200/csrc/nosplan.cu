@@ -900,10 +900,18 @@ int nosplan_score_mig(nosplan_t* h, int n_demands, const int32_t* dem_off, const
                         h->d_out[0].as<int32_t>(), updated ? h->d_out[1].as<uint8_t>() : nullptr,
                         choice ? h->d_out[2].as<int8_t>() : nullptr, st);
   if (rc) return rc;
-  mig_finalize_kernel<<<(D + 127) / 128, 128, 0, st>>>(
-      h->d_tables.as<MigTables>(), h->d_mig_used0.as<uint4>(), h->d_mig_free0.as<uint4>(), h->d_mig_model.as<uint8_t>(),
-      h->d_mig_off.as<int32_t>(), D, h->mig_gs, h->d_dem[0].as<int32_t>(), h->d_dem[1].as<int32_t>(),
-      h->d_dem[2].as<int32_t>(), h->d_out[0].as<int32_t>(), first_choice ? h->d_out[3].as<int8_t>() : nullptr);
+  if (first_choice && dev_check) {  // 16-bit-key tables: re-walk the winners with the snapshot-time ranks
+    mig_finalize16_kernel<<<(D + 127) / 128, 128, 0, st>>>(
+        h->d_tables.as<MigTables>(), h->d_mig_rankg.as<uint32_t>(), h->d_mig_ufg.as<uint16_t>(), h->d_mig_used0.as<uint4>(),
+        h->d_mig_free0.as<uint4>(), h->d_mig_model.as<uint8_t>(), h->d_mig_off.as<int32_t>(), D, h->mig_gs, (h->cmax + 3) / 4,
+        h->d_dem[0].as<int32_t>(), h->d_dem[1].as<int32_t>(), h->d_dem[2].as<int32_t>(), h->d_out[0].as<int32_t>(),
+        h->d_out[3].as<int8_t>());
+  } else if (first_choice) {
+    mig_finalize_kernel<<<(D + 127) / 128, 128, 0, st>>>(
+        h->d_tables.as<MigTables>(), h->d_mig_used0.as<uint4>(), h->d_mig_free0.as<uint4>(), h->d_mig_model.as<uint8_t>(),
+        h->d_mig_off.as<int32_t>(), D, h->mig_gs, h->d_dem[0].as<int32_t>(), h->d_dem[1].as<int32_t>(),
+        h->d_dem[2].as<int32_t>(), h->d_out[0].as<int32_t>(), h->d_out[3].as<int8_t>());
+  }
   CU(cudaGetLastError());
   if (first_node) CU(cudaMemcpyAsync(first_node, h->d_out[0].p, sizeof(int32_t) * D, cudaMemcpyDeviceToHost, st));
   if (first_choice) CU(cudaMemcpyAsync(first_choice, h->d_out[3].p, (size_t)D * h->mig_gs, cudaMemcpyDeviceToHost, st));

@@ -431,6 +431,60 @@ __global__ void __launch_bounds__(TN * DS, RB > 2 ? 2 : 3) mig_score16_kernel(co
   }
 }
 
+// The winner's per-GPU choices (nosplan_score_mig's first_choice): one thread per row re-walks the row's
+// first node with the snapshot-time rank table; rows with several keys use the general walker.
+__global__ void mig_finalize16_kernel(const MigTables* __restrict__ T, const uint32_t* __restrict__ rankg,
+                                      const uint16_t* __restrict__ ufg, const uint4* __restrict__ a_used,
+                                      const uint4* __restrict__ a_free, const uint8_t* __restrict__ a_model,
+                                      const int32_t* __restrict__ gpu_off, int D, int gs, int cw,
+                                      const int32_t* __restrict__ dem_off, const int32_t* __restrict__ dem_key,
+                                      const int32_t* __restrict__ dem_qty, const int32_t* __restrict__ first_node,
+                                      int8_t* __restrict__ first_choice) {
+  const int d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= D) return;
+  const int fn = first_node[d];
+  int8_t ch[NOSPLAN_MAX_GPUS_PER_NODE];
+  for (int s = 0; s < NOSPLAN_MAX_GPUS_PER_NODE; ++s) ch[s] = -1;
+  if (fn >= 0) {
+    const int e0 = dem_off[d], k = dem_off[d + 1] - e0;
+    const int g0 = gpu_off[fn], cnt = gpu_off[fn + 1] - g0;
+    if (k == 1) {
+      const int p = dem_key[e0];
+      int resid = min(max(dem_qty[e0], 0), 32767);
+      for (int s = 0; s < cnt && resid > 0; ++s) {
+        const uint32_t x = ufg[((size_t)fn * 16 + p) * gs + s];
+        const int needed = resid - (int)(x & 0xffu);
+        uint32_t best2 = 0;
+        if (needed > 0) {
+          const int m = a_model[g0 + s];
+          const int c0 = T->geom_off[m], cc = T->geom_off[m + 1] - c0;
+          const uint32_t nd2 = (uint32_t)needed * 0x10001u;
+          const uint32_t nc2 = ((0u - (x >> 8)) & 0xffffu) * 0x10001u;
+          const uint32_t* rk = rankg + ((size_t)fn * gs + s) * (2 * cw);
+          for (int w = 0; w < 2 * cw; ++w) {
+            uint32_t c2 = 0;
+            if (2 * w < cc) c2 |= byte_of(T->cand[c0 + 2 * w], p);
+            if (2 * w + 1 < cc) c2 |= byte_of(T->cand[c0 + 2 * w + 1], p) << 16;
+            best2 = __vimax3_s16x2(best2, __viaddmin_s16x2_relu(c2, nc2, nd2) * 512u + rk[w], 0u);
+          }
+        }
+        const uint32_t best = max(best2 & 0xffffu, best2 >> 16);
+        const uint32_t prov = best >> 9;
+        if (prov) ch[s] = (int8_t)(15 - (int)(best & 15u));
+        resid = max(needed, 0) - (int)prov;
+      }
+    } else {
+      int pid[kMaxKeys], qty[kMaxKeys];
+      for (int j = 0; j < kMaxKeys; ++j) {
+        pid[j] = j < k ? dem_key[e0 + j] : 0;
+        qty[j] = j < k ? dem_qty[e0 + j] : 0;
+      }
+      mig_walk_node(T, a_used, const_cast<uint4*>(a_free), a_model, g0, cnt, k, pid, qty, false, ch);
+    }
+  }
+  for (int s = 0; s < gs; ++s) first_choice[(size_t)d * gs + s] = ch[s];
+}
+
 // ---- MPS scorer for the rows of one size (mode 1 of mps_score_kernel, first_node / updated only) ---------------
 // Same closed form of slicing.GPU.UpdateGeometryFor as mps_score_kernel's single-size path; the size is
 // uniform over the CTA, so everything that depends on it is hoisted, the rows are staged in shared
