@@ -368,6 +368,10 @@ def main():
             "planner_latency_ms_p95": float(np.percentile(lat, 95)) if lat else None,
             "planner_latency_gate_off_ms_p50": float(np.median(lat_off)) if lat_off else None,
             "evals_per_step": {"mig": ev_m, "mps": ev_p},
+            "evals_definition": "MIG: one per (row, node, GPU, allowed geometry) = iterations of the loop body gpu.go:168-188, "
+                                "identical rows included; its demand-independent half (CanApplyGeometry, distance, total, id rank) "
+                                "is evaluated once per snapshot (inside e2e, outside value), the demand-dependent half per tuple in "
+                                "the timed kernels.  MPS: one per (row, node, GPU) run of slicing/gpu.go:162-220",
             # achieved/frac follow SURVEY §8(d): algorithmic bytes (no credit for on-chip reuse) / time of the MIG
             # scorer's launches (row grouping, mig_score16_kernel, the multi-key pass, the finishing pass; CUDA
             # events).  traffic = ncu dram__bytes_read+write per mig_score16_kernel launch of the same command
