@@ -5,6 +5,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
+#include <chrono>
 #include <cstring>
 #include <condition_variable>
 #include <functional>
@@ -221,6 +222,14 @@ bool wide_keys_forced() {  // measurement knob: NOSPLAN_KEY_BITS=32 forces the w
   static const bool f = [] {
     const char* e = std::getenv("NOSPLAN_KEY_BITS");
     return e && std::atoi(e) == 32;
+  }();
+  return f;
+}
+
+bool trace_on() {  // NOSPLAN_TRACE=1: host-side phase times of nosplan_plan on stderr
+  static const bool f = [] {
+    const char* e = std::getenv("NOSPLAN_TRACE");
+    return e && std::atoi(e) == 1;
   }();
   return f;
 }
@@ -974,6 +983,8 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
   if (n_pods > 0 && (!kind || !dem_off)) return fail(h, NOSPLAN_ERR_ARG, "null pod arrays");
   int rc = bind(h);
   if (rc) return rc;
+  const bool trace = trace_on();
+  const auto t_begin = std::chrono::steady_clock::now();
   // split by kind (order kept) and deduplicate request vectors: pods with the same vector share a row
   struct Side {
     std::vector<int32_t> pod_idx, pod_sig, off{0}, key, qty;
@@ -1030,6 +1041,7 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
     s.pod_idx.push_back(i);
     s.pod_sig.push_back(id);
   }
+  const auto t_split = std::chrono::steady_clock::now();
   // reset the working state to the snapshot
   if (h->have_mig && h->mig_tg) {
     CU(cudaMemcpyAsync(h->d_mig_used.p, h->d_mig_used0.p, sizeof(uint4) * h->mig_tg, cudaMemcpyDeviceToDevice, h->stream));
@@ -1217,8 +1229,15 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
     CU(cudaMemcpyAsync(o_gpu[kd].data(), rep + 2 * (size_t)M, sizeof(int32_t) * M, cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(o_gate[kd].data(), reinterpret_cast<const uint8_t*>(rep + 3 * (size_t)M), M, cudaMemcpyDeviceToHost, st));
   }
+  const auto t_enq = std::chrono::steady_clock::now();
   CU(cudaStreamSynchronize(h->stream));
   CU(cudaStreamSynchronize(h->stream2));
+  const auto t_sync = std::chrono::steady_clock::now();
+  if (trace) {  // the device-to-host copies above block until their stream drains: "enqueue" includes the kernels
+    auto us = [](auto a, auto b) { return std::chrono::duration<double, std::micro>(b - a).count(); };
+    std::fprintf(stderr, "nosplan_plan: host split %.0f us, enqueue + kernels %.0f us, wait %.0f us\n", us(t_begin, t_split),
+                 us(t_split, t_enq), us(t_enq, t_sync));
+  }
   for (int kd = 0; kd < 2; ++kd) {
     Side& s = side[kd];
     for (size_t j = 0; j < s.pod_idx.size(); ++j) {
