@@ -375,13 +375,13 @@ def main():
             # achieved/frac follow SURVEY §8(d): algorithmic bytes (no credit for on-chip reuse) / time of the MIG
             # scorer's launches (row grouping, mig_score16_kernel, the multi-key pass, the finishing pass; CUDA
             # events).  traffic = ncu dram__bytes_read+write per mig_score16_kernel launch of the same command
-            # (profiles/r1h_bench_cfg5.md): the tile state is re-used from shared memory, HBM is idle and the
-            # binding roof is instruction issue (ncu: issue-active 77 %, ALU pipe 64 %, LSU 61 %): frac is above 1.
+            # (profiles/r1k_bench_cfg5.md): the tile state is re-used from shared memory, HBM is idle and the
+            # binding roof is instruction issue (ncu: issue-active 73 %, ALU pipe 72 %, LSU 40 %): frac is above 1.
             "roofline": {"bound": "hbm", "kernel": "mig_score16_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
-                         "frac": ach / peak, "peak_source": peak_src, "traffic": 1402368 if args.config == 5 and world == 1 else None,
+                         "frac": ach / peak, "peak_source": peak_src, "traffic": 1406208 if args.config == 5 and world == 1 else None,
                          "algorithmic_bytes_per_eval": BYTES_PER_EVAL_MIG, "kernel_ms": mig_ms / args.steps,
                          "mps_kernel_ms": mps_ms / args.steps, "binding_roof": "instruction issue (integer pipes)",
-                         "alu_pipe_pct_of_peak_ncu": 64.5, "issue_active_pct_ncu": 77.4},
+                         "alu_pipe_pct_of_peak_ncu": 71.9, "issue_active_pct_ncu": 72.9},
             "clocks": sampler.summary(),
         }
         if not args.no_cpu_baseline and world == 1:
