@@ -501,7 +501,6 @@ template <int TN, int DS, bool OUT>
 __global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreArgs a) {
   if ((int)blockIdx.x >= a.meta[0]) return;
   extern __shared__ __align__(16) unsigned char smem[];
-  __shared__ int s_sz[kMaxSizes];
   const int nw = (a.S + 3) >> 2;
   const uint32_t slot_stride = (uint32_t)(3 + nw) * TN * 4;  // bytes
   uint32_t* const s_slot = reinterpret_cast<uint32_t*>(smem);
@@ -518,20 +517,19 @@ __global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreAr
   const bool live = n < a.N && a.valid[n];
   const int g0 = n < a.N ? a.gpu_off[n] : 0;
   const int cnt = live ? a.gpu_off[n + 1] - g0 : 0;  // an invalid node is never updated
-  if (threadIdx.x < kMaxSizes) s_sz[threadIdx.x] = threadIdx.x < a.S ? a.sizes[threadIdx.x] : 1;
   for (int i = threadIdx.x; i < len; i += TN * DS) {
     const int d = rl[i];
     s_row[i] = d;
     s_qty[i] = max(__ldg(a.dem_qty + __ldg(a.dem_off + d)), 0);
     s_first[i] = kNoNode;
   }
-  __syncthreads();
+  // (sizes come straight from global memory: a handful of L1-resident words, one barrier less per CTA)
   for (int s = dsub; s < cnt; s += DS) {  // the DS threads of a node split its GPUs
     const MpsGpu G = a.gp[g0 + s];
     int origtot = 0;
     for (uint32_t mk = G.fmask; mk; mk &= mk - 1) {
       const int key = __ffs(mk) - 1;
-      origtot += s_sz[key] * (int)mps_byte(G.f0, G.f1, key);
+      origtot += __ldg(a.sizes + key) * (int)mps_byte(G.f0, G.f1, key);
     }
     uint32_t* col = s_slot + (size_t)s * (3 + nw) * TN + tid;
     col[0] = mps_byte(G.f0, G.f1, sid) | (((G.fmask >> sid) & 1u) << 8);
@@ -542,7 +540,7 @@ __global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreAr
   }
   __syncthreads();
 
-  const int m = s_sz[sid];
+  const int m = __ldg(a.sizes + sid);
   const uint32_t inv = m == 1 ? 0u : 0xFFFFFFFFu / (uint32_t)m + 1u;  // exact multiply-high division (div_small)
   const uint32_t ps0 = (uint32_t)__cvta_generic_to_shared(s_slot) + (uint32_t)tid * 4u;
   for (int i = dsub; i < len; i += DS) {
@@ -575,7 +573,7 @@ __global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreAr
         restored_sid = false;
         for (uint32_t mk = lds_u32(ps + 2 * TN * 4) & ((2u << sid) - 1u); mk; mk &= mk - 1) {
           const int key = __ffs(mk) - 1;
-          const int need = s_sz[key] * (int)((lds_u32(ps + (3 + (key >> 2)) * TN * 4) >> ((key & 3) * 8)) & 0xffu);
+          const int need = __ldg(a.sizes + key) * (int)((lds_u32(ps + (3 + (key >> 2)) * TN * 4) >> ((key & 3) * 8)) & 0xffu);
           if (spare >= need) {
             spare -= need;
             if (key == sid) restored_sid = true;
