@@ -1118,20 +1118,28 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
       // pods grouped by requested key, planner order kept inside a group
       std::vector<int32_t> ckey, coff{0}, cpod(M), cq(M);
       std::vector<int> cnt(a.n_keys, 0), chain_of(a.n_keys, -1);
-      for (int j = 0; j < M; ++j) cnt[s.key[s.off[s.pod_sig[j]]]]++;
+      // every row is one (key, quantity) here: a small per-row table instead of two indirections per pod
+      std::vector<int32_t> row_key(D), row_qty(D), row_cnt(D, 0);
+      for (int r = 0; r < D; ++r) {
+        row_key[r] = s.key[s.off[r]];
+        row_qty[r] = s.qty[s.off[r]];
+      }
+      const int32_t* sig = s.pod_sig.data();
+      for (int j = 0; j < M; ++j) row_cnt[sig[j]]++;
+      for (int r = 0; r < D; ++r) cnt[row_key[r]] += row_cnt[r];
       for (int k = 0; k < a.n_keys; ++k)
         if (cnt[k]) {
           chain_of[k] = (int)ckey.size();
           ckey.push_back(k);
           coff.push_back(coff.back() + cnt[k]);
         }
-      std::vector<int32_t> fill(coff.begin(), coff.end() - 1);
+      std::vector<int32_t> fill(coff.begin(), coff.end() - 1), row_chain(D);
+      for (int r = 0; r < D; ++r) row_chain[r] = chain_of[row_key[r]];
       for (int j = 0; j < M; ++j) {
-        const int e = s.off[s.pod_sig[j]];
-        const int c = chain_of[s.key[e]];
-        cpod[fill[c]] = j;
-        cq[fill[c]] = s.qty[e];
-        fill[c]++;
+        const int r = sig[j];
+        const int at = fill[row_chain[r]]++;
+        cpod[at] = j;
+        cq[at] = row_qty[r];
       }
       ChainArgs ca;
       std::memset(&ca, 0, sizeof(ca));
