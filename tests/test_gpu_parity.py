@@ -303,3 +303,25 @@ def test_full_size_cfg5_properties(pkg, planner):
     assert np.array_equal(again["sched_node"], exp["sched_node"])
     used, free = planner.get_mig_state()
     assert np.array_equal((used + free).sum(axis=0), (cfg["mig"]["used"] + cfg["mig"]["free"]).sum(axis=0))
+    # (3) MPS at full size, and the full per-node tables of one row per distinct request (both kinds)
+    poff, pkey, pqty, psel = pkg.synth.pods_of_kind(pods, 1)
+    rp = planner.score_mps(poff, pkey, pqty, want_free=False)
+    psig = pkey.astype(np.int64) * 100 + pqty
+    puniq, pfirst = np.unique(psig, return_index=True)
+    S = len(cfg["sizes"])
+    preq, pmask = pkg.synth.csr_to_dense(np.arange(len(puniq) + 1, dtype=np.int32), pkey[pfirst], pqty[pfirst], S)
+    peu, _, _, pef = o.score_mps(cfg["mps"], preq, pmask, threads=8, want_free=False)
+    for j, s in enumerate(puniq):
+        rows = np.nonzero(psig == s)[0]
+        assert np.all(rp["first_node"][rows] == pef[j])
+        assert np.array_equal(rp["updated"][rows[0]], peu[j]) and np.array_equal(rp["updated"][rows[-1]], peu[j])
+    assert rp["n_evals"] == len(psel) * 2048 * 8
+    rm = planner.score_mig(off, key, qty, want_updated=True, want_choice=False, want_first_choice=False)
+    for j, s in enumerate(uniq):
+        rows = np.nonzero(sig == s)[0]
+        assert np.array_equal(rm["updated"][rows[0]], eu[j]) and np.array_equal(rm["updated"][rows[-1]], eu[j])
+    # (4) the one-call form agrees with the separate calls at full size
+    c32 = lambda *xs: tuple(np.ascontiguousarray(x, np.int32) for x in xs)
+    both = planner.score_snapshot(cfg["mig"], c32(off, key, qty), cfg["sizes"], cfg["mps"], c32(poff, pkey, pqty))
+    assert np.array_equal(both["mig_first_node"], r["first_node"]) and np.array_equal(both["mig_first_choice"], r["first_choice"])
+    assert np.array_equal(both["mps_first_node"], rp["first_node"])

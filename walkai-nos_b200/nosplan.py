@@ -224,9 +224,21 @@ class Planner:
 
     def score_snapshot(self, mig=None, mig_rows=None, sizes_gb=None, mps=None, mps_rows=None, want_first_choice=True):
         """One call for a whole scoring pass (nosplan_score_snapshot): mig / mps are snapshot dicts as for
-        set_*_snapshot, *_rows = (off, key, qty).  Nothing is installed on the handle.  Arrays must already be
-        contiguous int32 / uint8 / uint32 (they are passed as they are)."""
+        set_*_snapshot, *_rows = (off, key, qty).  Nothing is installed on the handle.  Arrays of the right dtype
+        and layout are passed as they are (pinned buffers stay pinned); others are converted first."""
         keep = []
+        _dt = dict(gpu_off=np.int32, valid=np.uint8, model=np.int32, used=np.int32, free=np.int32, mem_gb=np.int32,
+                   free_mask=np.uint32)
+        conv = lambda d: {k: (np.ascontiguousarray(v, _dt[k]) if k in _dt else v) for k, v in d.items()}
+        if mig is not None:
+            go0 = mig["gpu_off"]
+            mig = conv(mig)
+            mig_rows = tuple(np.ascontiguousarray(x, np.int32) for x in mig_rows)
+            if mig["gpu_off"] is not go0:
+                self._gs_of = None
+        if mps is not None:
+            mps = conv(mps)
+            mps_rows = tuple(np.ascontiguousarray(x, np.int32) for x in mps_rows)
         ms = ps = md = pd = None
         out = {}
         fm = ff = fp = None
