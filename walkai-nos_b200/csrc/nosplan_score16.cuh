@@ -489,9 +489,9 @@ __global__ void mig_finalize16_kernel(const MigTables* __restrict__ T, const uin
 // Same closed form of slicing.GPU.UpdateGeometryFor as mps_score_kernel's single-size path; the size is
 // uniform over the CTA, so everything that depends on it is hoisted, the rows are staged in shared
 // memory and one pointer walks the GPU slots.
-// Shared memory (u32): slot [gs][3 + nw][TN]: A = free[sid] | (sid in FreeProfiles) << 8,
-// B = spare | origtot << 16 (spare = cap - origtot, origtot = GB held by free slices), M = key mask,
-// then the nw words of free bytes (only the restore walk reads them); row/qty [kRowCap].
+// Shared memory (u32): per slot (3 + nw) * TN words: TN pairs {A = free[sid] | (sid in FreeProfiles) << 8,
+// B = spare | origtot << 16 (spare = cap - origtot, origtot = GB held by free slices)}, then M[TN] = key
+// mask, then the nw x TN words of free bytes (only the restore walk reads M and those); row/qty/first [kRowCap].
 __host__ __device__ inline size_t mps_score1_smem_bytes(int gs, int S, int tn) {
   const size_t nw = (size_t)(S + 3) / 4;
   return (size_t)gs * (3 + nw) * tn * 4 + (size_t)kRowCap * 12;
@@ -531,9 +531,10 @@ __global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreAr
       const int key = __ffs(mk) - 1;
       origtot += __ldg(a.sizes + key) * (int)mps_byte(G.f0, G.f1, key);
     }
-    uint32_t* col = s_slot + (size_t)s * (3 + nw) * TN + tid;
-    col[0] = mps_byte(G.f0, G.f1, sid) | (((G.fmask >> sid) & 1u) << 8);
-    col[TN] = ((uint32_t)origtot << 16) | (uint32_t)((int)G.cap - origtot);
+    uint32_t* reg = s_slot + (size_t)s * (3 + nw) * TN;
+    uint32_t* col = reg + tid;
+    reg[2 * tid] = mps_byte(G.f0, G.f1, sid) | (((G.fmask >> sid) & 1u) << 8);      // A and B side by side:
+    reg[2 * tid + 1] = ((uint32_t)origtot << 16) | (uint32_t)((int)G.cap - origtot);  // one 64-bit load per slot
     col[2 * TN] = G.fmask;
     const uint32_t w[8] = {G.f0.x, G.f0.y, G.f0.z, G.f0.w, G.f1.x, G.f1.y, G.f1.z, G.f1.w};
     for (int i = 0; i < nw; ++i) col[(3 + i) * TN] = w[i];
@@ -542,17 +543,19 @@ __global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreAr
 
   const int m = __ldg(a.sizes + sid);
   const uint32_t inv = m == 1 ? 0u : 0xFFFFFFFFu / (uint32_t)m + 1u;  // exact multiply-high division (div_small)
-  const uint32_t ps0 = (uint32_t)__cvta_generic_to_shared(s_slot) + (uint32_t)tid * 4u;
+  const uint32_t ps0 = (uint32_t)__cvta_generic_to_shared(s_slot);
+  const uint32_t t4 = (uint32_t)tid * 4u;
   for (int i = dsub; i < len; i += DS) {
     int resid = s_qty[i];
     bool any = false;
     uint32_t ps = ps0;
     for (int s = 0; s < cnt && resid > 0; ++s, ps += slot_stride) {
-      const uint32_t A = lds_u32(ps);
+      const uint2 ab = lds_v2(ps + 2 * t4);
+      const uint32_t A = ab.x;
       const int fj = (int)(A & 0xffu);
       const int miss = resid - fj;  // getMissingSlices
       if (miss <= 0) break;         // this GPU already provides it; the residual drops to 0
-      const uint32_t sp = lds_u32(ps + TN * 4);
+      const uint32_t sp = ab.y;
       const int otot = (int)(sp >> 16);
       int spare = (int)(sp & 0xffffu);
       const bool in_orig = (A >> 8) != 0u;
@@ -571,9 +574,9 @@ __global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreAr
       bool restored_sid = in_orig;
       if (spare < otot && fj > 0) {
         restored_sid = false;
-        for (uint32_t mk = lds_u32(ps + 2 * TN * 4) & ((2u << sid) - 1u); mk; mk &= mk - 1) {
+        for (uint32_t mk = lds_u32(ps + 2 * TN * 4 + t4) & ((2u << sid) - 1u); mk; mk &= mk - 1) {
           const int key = __ffs(mk) - 1;
-          const int need = __ldg(a.sizes + key) * (int)((lds_u32(ps + (3 + (key >> 2)) * TN * 4) >> ((key & 3) * 8)) & 0xffu);
+          const int need = __ldg(a.sizes + key) * (int)((lds_u32(ps + (3 + (key >> 2)) * TN * 4 + t4) >> ((key & 3) * 8)) & 0xffu);
           if (spare >= need) {
             spare -= need;
             if (key == sid) restored_sid = true;
