@@ -1174,8 +1174,15 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
       ca.sched_node = a.sched_node;
       ca.sched_gpu = a.sched_gpu;
       a.skip_if = ca.eligible;
+      ca.n_win = (a.tg + 31) / 32;
+      CU(b[14].reserve((size_t)a.n_keys * ca.n_win));
+      ca.winmax = b[14].as<uint8_t>();
       if (kd == 0) plan_presence_kernel<false><<<(a.tg + 255) / 256, 256, 0, st>>>(ca);
       else plan_presence_kernel<true><<<(a.tg + 255) / 256, 256, 0, st>>>(ca);
+      if (ca.sched) {
+        if (kd == 0) plan_winmax_kernel<false><<<ca.n_win, 32, 0, st>>>(ca);
+        else plan_winmax_kernel<true><<<ca.n_win, 32, 0, st>>>(ca);
+      }
       plan_eligible_kernel<<<1, 32, 0, st>>>(ca);
       if (kd == 0) plan_chain_kernel<false><<<ca.n_chains, 32, 0, st>>>(ca);
       else plan_chain_kernel<true><<<ca.n_chains, 32, 0, st>>>(ca);

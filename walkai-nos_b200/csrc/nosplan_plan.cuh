@@ -80,6 +80,8 @@ struct ChainArgs {
   uint4* p_used_hi;
   int32_t* present;           // [n_keys] sum of used+free over valid nodes (plan_presence_kernel)
   int32_t* eligible;          // [1] 1 = every chain's key is present -> this kernel owns the plan
+  uint8_t* winmax;            // [n_keys][n_win] largest free count of the key among the 32 GPUs of a window
+  int n_win;                  //                 (plan_winmax_kernel; an upper bound while the chains run)
   int sched;                  // 0: gate only (NOSPLAN_PLAN_SCHED off): every pod is stopped by the gate, nothing else
   uint8_t* gate_hit;
   int32_t* repart_node;
@@ -103,6 +105,30 @@ __global__ void plan_presence_kernel(ChainArgs a) {
   }
   __syncthreads();
   if (threadIdx.x < a.n_keys && sh[threadIdx.x]) atomicAdd(&a.present[threadIdx.x], sh[threadIdx.x]);
+}
+
+// One warp per window of 32 GPUs (the windows of plan_chain_kernel).  First-fit only ever takes free
+// devices away, so the maxima stay upper bounds while the chains run: a window whose maximum is below the
+// requested quantity can be skipped without loading it.
+template <bool MPS>
+__global__ void __launch_bounds__(32) plan_winmax_kernel(ChainArgs a) {
+  const int w = blockIdx.x, lane = threadIdx.x;
+  const int g = w * 32 + lane;
+  const bool live = g < a.tg && a.gpu_node[g] >= 0;
+  uint4 f0 = make_uint4(0, 0, 0, 0), f1 = f0;
+  if (live) {
+    if constexpr (MPS) {
+      f0 = a.p_gpu[g].f0;
+      f1 = a.p_gpu[g].f1;
+    } else {
+      f0 = a.m_free[g];
+    }
+  }
+  for (int key = 0; key < a.n_keys; ++key) {
+    const unsigned v = MPS ? mps_byte(f0, f1, key) : byte_of(f0, key);
+    const unsigned m = __reduce_max_sync(0xffffffffu, v);
+    if (lane == 0) a.winmax[(size_t)key * a.n_win + w] = (uint8_t)m;
+  }
 }
 
 __global__ void plan_eligible_kernel(ChainArgs a) {
@@ -196,7 +222,20 @@ __global__ void __launch_bounds__(32) plan_chain_kernel(ChainArgs a) {
           }
           const int tot = __shfl_sync(0xffffffffu, P, 31);
           if (tot == 0) {  // window exhausted for this quantity: every GPU before the next one has free < q
-            base[t] += 32;
+            // next window that may still hold free >= q: 32 window maxima per load (1024 GPUs per L2 round trip
+            // instead of 32); the maxima are upper bounds, the window itself is then loaded and decides
+            int w = base[t] / 32 + 1;
+            const uint8_t* wm = a.winmax + (size_t)key * a.n_win;
+            while (w < a.n_win) {
+              const int mx = (w + lane < a.n_win) ? (int)__ldg(wm + w + lane) : 0;
+              const uint32_t hit = __ballot_sync(0xffffffffu, mx >= q);
+              if (hit) {
+                w += __ffs(hit) - 1;
+                break;
+              }
+              w += 32;
+            }
+            base[t] = min(w, a.n_win) * 32;  // n_win * 32 >= tg: nothing left for this quantity
             cache[t] = load_win(base[t] + lane, &wnode[t], &wslot[t]);
             continue;
           }
