@@ -1184,8 +1184,15 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
         else plan_winmax_kernel<true><<<ca.n_win, 32, 0, st>>>(ca);
       }
       plan_eligible_kernel<<<1, 32, 0, st>>>(ca);
-      if (kd == 0) plan_chain_kernel<false><<<ca.n_chains, 32, 0, st>>>(ca);
-      else plan_chain_kernel<true><<<ca.n_chains, 32, 0, st>>>(ca);
+      int maxq = 1;
+      for (int q : s.qty) maxq = std::max(maxq, q);
+      if (maxq <= 2) {
+        if (kd == 0) plan_chain_kernel<false, 2><<<ca.n_chains, 32, 0, st>>>(ca);
+        else plan_chain_kernel<true, 2><<<ca.n_chains, 32, 0, st>>>(ca);
+      } else {
+        if (kd == 0) plan_chain_kernel<false, kChainQ><<<ca.n_chains, 32, 0, st>>>(ca);
+        else plan_chain_kernel<true, kChainQ><<<ca.n_chains, 32, 0, st>>>(ca);
+      }
     }
     {
       // general path: derive the masks/bitmaps from the working state, then one sequencer warp

@@ -141,7 +141,9 @@ __global__ void plan_eligible_kernel(ChainArgs a) {
 
 constexpr int kChainQ = 8;  // quantities 1..kChainQ each get a cursor; the host keeps larger ones off this path
 
-template <bool MPS>
+// NQ: cursors kept (quantities 1..NQ occur in the chains; 2 for every BASELINE config): the per-step
+// bookkeeping over all cursors is what a single latency-bound warp spends its time on
+template <bool MPS, int NQ>
 __global__ void __launch_bounds__(32) plan_chain_kernel(ChainArgs a) {
   if (*a.eligible == 0) return;
   const int c = blockIdx.x, lane = threadIdx.x;
@@ -158,8 +160,8 @@ __global__ void __launch_bounds__(32) plan_chain_kernel(ChainArgs a) {
     return;
   }
   const int sz = MPS ? a.sizes[key] : 0;
-  int base[kChainQ], cache[kChainQ];  // window start (multiple of 32) and this lane's GPU free count
-  int wnode[kChainQ], wslot[kChainQ];  // node and slot of this lane's GPU in each window (-1: not a valid GPU)
+  int base[NQ], cache[NQ];  // window start (multiple of 32) and this lane's GPU free count
+  int wnode[NQ], wslot[NQ];  // node and slot of this lane's GPU in each window (-1: not a valid GPU)
   // read through an atomic so the value is ordered after this warp's earlier deductions at L2
   auto load_win = [&](int g, int* node, int* slot) -> int {
     *node = -1;
@@ -178,7 +180,7 @@ __global__ void __launch_bounds__(32) plan_chain_kernel(ChainArgs a) {
     return (int)((word >> ((key & 3) * 8)) & 0xffu);
   };
 #pragma unroll
-  for (int qi = 0; qi < kChainQ; ++qi) {
+  for (int qi = 0; qi < NQ; ++qi) {
     base[qi] = 0;
     cache[qi] = load_win(lane, &wnode[qi], &wslot[qi]);
   }
@@ -199,7 +201,7 @@ __global__ void __launch_bounds__(32) plan_chain_kernel(ChainArgs a) {
       const uint32_t rest = ~(same >> t32);
       const int r = rest ? __ffs(rest) - 1 : 32 - t32;  // run length (>= 1)
 #pragma unroll
-      for (int t = 0; t < kChainQ; ++t) {
+      for (int t = 0; t < NQ; ++t) {
         if (t != qi) continue;
         int served = 0;
         while (served < r) {
@@ -262,7 +264,7 @@ __global__ void __launch_bounds__(32) plan_chain_kernel(ChainArgs a) {
           const int dq = take * q;
           const int wb = base[t];
 #pragma unroll
-          for (int t2 = 0; t2 < kChainQ; ++t2)
+          for (int t2 = 0; t2 < NQ; ++t2)
             if (base[t2] == wb) cache[t2] -= dq;  // windows are 32-aligned: same base == same GPUs
           if (dq > 0) {
             const int g = wb + lane;
