@@ -1,7 +1,7 @@
 // nosplan_score16.cuh — the MIG batched scorer for the common tables (<= 16 geometries per model,
 // quantities <= 63: 16-bit keys), organised so that the lanes of a warp stay together.
 //
-// What ncu showed on the plain tile kernel (profiles/r1e_bench_cfg5.md): one warp = 32 consecutive
+// What ncu showed on the plain tile kernel (profiles/r1_divergence.md): one warp = 32 consecutive
 // nodes of one demand row, and a node leaves the GPU loop at the first GPU that covers the request
 // (node.go:164-169), so ~14 of 32 lanes were alive in the candidate core.  How far a node walks depends
 // on the requested profile much more than on the node.  Hence:
@@ -12,7 +12,7 @@
 //     several keys go to the general kernel) and cut into work items (profile, row range).
 //   * one CTA = (tile of 128 consecutive POSITIONS of perm[p], work item of profile p): its warps hold
 //     nodes that walk about equally far for that profile.  The tile only needs profile p's column of
-//     the state, so it is 28 KB instead of 60 KB.
+//     the state, so it is 33 KB instead of 60 KB.
 //   * the demand-independent part of a candidate's score is evaluated when the snapshot arrives
 //     (mig_rank16_kernel) instead of in every CTA's prologue.
 // The arithmetic per (row, node, GPU, candidate) is the K16 path of mig_score_kernel, unchanged.
