@@ -249,6 +249,13 @@ int nosplan_score_snapshot(nosplan_t* h, const nosplan_mig_snapshot_t* mig, cons
  * then report first_node as a global index (-1 stays -1). */
 int nosplan_set_node_base(nosplan_t* h, int mig_first_node, int mps_first_node);
 
+/* The gate's ingredient, per shard: Controller.profileAlreadyPresent (mig_controller.go:121-144) asks, for
+ * every requested profile, whether some node's geometry holds it: the sum over valid nodes and their GPUs
+ * of used + free.  count[n_keys] (host array, n_keys = profiles for kind 0, sizes for kind 1) receives those
+ * sums for the handle's WORKING state of the kind (the snapshot, or what the last nosplan_plan left); with
+ * the node list sharded the gate is "sum over ranks > 0" (one all-reduce SUM over n_keys integers). */
+int nosplan_presence(nosplan_t* h, int kind, int64_t* count);
+
 /* The exchange itself, done by the library's own kernels over peer memory (NVLink): every rank folds
  * its keys into every rank's buffer with atomicMin and signals a per-rank step flag; no library
  * collective is involved.  Set-up (allocates; once per process group):

@@ -45,7 +45,19 @@ def _worker(rank, world, port, out_dir):
         both = pkg.dist.merge_first_node_keys(torch.from_numpy(first.copy()), torch.full((len(first),), lo, dtype=torch.int32)).numpy()
         assert np.array_equal(merged, both)
         res[name] = (merged, full)
-    ok = all(np.array_equal(m, f) for m, f in res.values())
+    # the gate's ingredient: per-shard sums of used + free per key, one all-reduce(SUM)
+    pres_ok = True
+    for name in ("mig", "mps"):
+        shard, _ = pkg.dist.shard_snapshot(cfg[name], rank, world)
+        v = shard["valid"].astype(bool)
+        per_gpu_valid = np.repeat(v, np.diff(shard["gpu_off"]))
+        local = (shard["used"] + shard["free"])[per_gpu_valid].sum(axis=0).astype(np.int64)
+        whole = cfg[name]
+        wv = np.repeat(whole["valid"].astype(bool), np.diff(whole["gpu_off"]))
+        full_sum = (whole["used"] + whole["free"])[wv].sum(axis=0).astype(np.int64)
+        merged_p = pkg.dist.merge_presence(torch.from_numpy(local)).numpy()
+        pres_ok &= bool(np.array_equal(merged_p, full_sum))
+    ok = pres_ok and all(np.array_equal(m, f) for m, f in res.values())
     some = any((f >= 0).any() for _, f in res.values())
     np.save(os.path.join(out_dir, f"r{rank}.npy"), np.asarray([int(ok), int(some)]))
     dist.barrier()

@@ -90,3 +90,33 @@ def test_two_ranks_min_over_peer_memory():
                        timeout=240)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "exchange ok" in r.stdout
+
+
+def test_presence_counts_follow_the_working_state():
+    """nosplan_presence = the sums Controller.profileAlreadyPresent looks at (mig_controller.go:121-144): used + free
+    per key over valid nodes, of the snapshot and of what a plan left behind."""
+    import walkai_nos_b200 as pkg
+    cfg = pkg.synth.make_config(4, scale_nodes=96, scale_pods=600)
+    p = pkg.Planner(0)
+    try:
+        with pytest.raises(pkg.NosplanError):
+            p.presence(0)
+        p.set_mig_tables(cfg["names"], cfg["geom_off"], cfg["geom_counts"])
+        mig = {k: (v.copy() if isinstance(v, np.ndarray) else v) for k, v in cfg["mig"].items()}
+        mig["valid"][3] = 0
+        p.set_mig_snapshot(mig)
+        p.set_mps_snapshot(cfg["sizes"], cfg["mps"])
+
+        def expect(snap, used, free):
+            v = np.repeat(snap["valid"].astype(bool), np.diff(snap["gpu_off"]))
+            return (used + free)[v].sum(axis=0).astype(np.int64)
+        assert np.array_equal(p.presence(0), expect(mig, mig["used"], mig["free"]))
+        assert np.array_equal(p.presence(1), expect(cfg["mps"], cfg["mps"]["used"], cfg["mps"]["free"]))
+        pods = cfg["pods"]
+        p.plan(pods["kind"], pods["off"], pods["key"], pods["qty"], gate=False, sched=True)
+        u, f = p.get_mig_state()
+        assert np.array_equal(p.presence(0), expect(mig, u, f))
+        u, f, _ = p.get_mps_state()
+        assert np.array_equal(p.presence(1), expect(cfg["mps"], u, f))
+    finally:
+        p.close()

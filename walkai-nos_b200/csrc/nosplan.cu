@@ -1812,3 +1812,52 @@ extern "C" int nosplan_score_snapshot(nosplan_t* h, const nosplan_mig_snapshot_t
   if (n_evals) *n_evals = ev_mig + ev_mps;
   return NOSPLAN_OK;
 }
+
+// ---- presence counts (the gate's ingredient; per shard when the node list is sharded) ------------------------
+namespace {
+template <bool MPS>
+__global__ void presence_kernel(int tg, int n_keys, const int32_t* __restrict__ gpu_node, const uint4* __restrict__ m_used,
+                                const uint4* __restrict__ m_free, const MpsGpu* __restrict__ p_gpu,
+                                const uint4* __restrict__ p_ulo, const uint4* __restrict__ p_uhi,
+                                unsigned long long* __restrict__ count) {
+  __shared__ unsigned int sh[kMaxSizes];
+  if (threadIdx.x < kMaxSizes) sh[threadIdx.x] = 0;
+  __syncthreads();
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g < tg && gpu_node[g] >= 0) {  // GPUs of invalid nodes are skipped, as the controller skips those nodes
+    for (int key = 0; key < n_keys; ++key) {
+      unsigned int v;
+      if constexpr (MPS) v = mps_byte(p_gpu[g].f0, p_gpu[g].f1, key) + mps_byte(p_ulo[g], p_uhi[g], key);
+      else v = byte_of(m_free[g], key) + byte_of(m_used[g], key);
+      if (v) atomicAdd(&sh[key], v);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < n_keys && sh[threadIdx.x]) atomicAdd(&count[threadIdx.x], (unsigned long long)sh[threadIdx.x]);
+}
+}  // namespace
+
+extern "C" int nosplan_presence(nosplan_t* h, int kind, int64_t* count) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  if (!count) return fail(h, NOSPLAN_ERR_ARG, "count is null");
+  if (kind != 0 && kind != 1) return fail(h, NOSPLAN_ERR_ARG, "kind must be 0 (MIG) or 1 (MPS)");
+  if (kind ? !h->have_mps : !h->have_mig) return fail(h, NOSPLAN_ERR_ARG, "no snapshot of that kind");
+  int rc = bind(h);
+  if (rc) return rc;
+  const int n_keys = kind ? h->S : h->P, tg = kind ? h->mps_tg : h->mig_tg;
+  CU(h->d_out[5].reserve(sizeof(unsigned long long) * kMaxSizes));
+  CU(cudaMemsetAsync(h->d_out[5].p, 0, sizeof(unsigned long long) * kMaxSizes, h->stream));
+  if (tg > 0) {
+    if (kind) presence_kernel<true><<<(tg + 255) / 256, 256, 0, h->stream>>>(
+        tg, n_keys, h->d_mps_gnode.as<int32_t>(), nullptr, nullptr, h->d_mps_gpu.as<MpsGpu>(), h->d_mps_ulo.as<uint4>(),
+        h->d_mps_uhi.as<uint4>(), h->d_out[5].as<unsigned long long>());
+    else presence_kernel<false><<<(tg + 255) / 256, 256, 0, h->stream>>>(
+        tg, n_keys, h->d_mig_gnode.as<int32_t>(), h->d_mig_used.as<uint4>(), h->d_mig_free.as<uint4>(), nullptr, nullptr, nullptr,
+        h->d_out[5].as<unsigned long long>());
+    CU(cudaGetLastError());
+  }
+  CU(cudaMemcpyAsync(count, h->d_out[5].p, sizeof(int64_t) * n_keys, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return NOSPLAN_OK;
+}

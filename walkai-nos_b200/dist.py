@@ -68,3 +68,14 @@ def open_exchange(planner, max_keys: int, group=None):
     planner.exchange_open(handles)
     if world > 1:
         dist.barrier(group=group)  # nobody pushes before everybody has mapped
+
+
+def merge_presence(count_local, group=None):
+    """count_local: int64 torch tensor [n_keys], this shard's sum of used + free per key (Planner.presence).
+    Returns the cluster-wide sums after one all-reduce(SUM): Controller.profileAlreadyPresent
+    (mig_controller.go:121-144) holds for a pod iff every key it requests has a positive sum."""
+    import torch.distributed as dist
+    out = count_local.clone()
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(out, op=dist.ReduceOp.SUM, group=group)
+    return out

@@ -27,7 +27,7 @@ EXPORTS = [
     "nosplan_get_mig_state", "nosplan_get_mps_state", "nosplan_init_geometry_mig", "nosplan_score_mig_dev",
     "nosplan_score_mps_dev", "nosplan_mig_evals_per_demand", "nosplan_mps_evals_per_demand", "nosplan_score_mig_static", "nosplan_diff_plan_mig",
     "nosplan_set_node_base", "nosplan_exchange_create", "nosplan_exchange_open", "nosplan_exchange_min_dev",
-    "nosplan_exchange_status", "nosplan_exchange_destroy", "nosplan_score_snapshot",
+    "nosplan_exchange_status", "nosplan_exchange_destroy", "nosplan_score_snapshot", "nosplan_presence",
 ]
 
 
@@ -337,6 +337,12 @@ class Planner:
     # ---- sharded scoring (one process per GPU) -----------------------------------------------------
     def set_node_base(self, mig_first_node: int, mps_first_node: int):
         self._ck(self.L.nosplan_set_node_base(self.h, int(mig_first_node), int(mps_first_node)))
+
+    def presence(self, kind: int) -> np.ndarray:
+        """Sum of used + free per key over the valid nodes of the handle's working state (the gate's ingredient)."""
+        out = np.zeros(self.S if kind else self.P, np.int64)
+        self._ck(self.L.nosplan_presence(self.h, int(kind), _p(out)))
+        return out
 
     def exchange_create(self, rank: int, world: int, max_keys: int) -> bytes:
         """Allocates this rank's exchange buffer; returns its 64-byte CUDA IPC handle."""
