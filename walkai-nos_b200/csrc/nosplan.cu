@@ -362,12 +362,13 @@ int launch_mig_score16(nosplan_t* h, const MigScoreArgs& a, int tiles, int cw, c
 }
 
 // the rows-by-key path is taken (and with it the demand rows are validated on the device)
-bool mig_ordered(const nosplan_t* h) {
-  return h->mig_n > 0 && h->k16ok && (h->cmax + 3) / 4 <= 4 && (h->mig_n + kScoreTN - 1) / kScoreTN <= 65535 &&
+constexpr int kMaxOrderedRows = 60 * 1000 * 1000;  // rows[] positions (key * D + i) stay 32-bit
+bool mig_ordered(const nosplan_t* h, int D) {
+  return D <= kMaxOrderedRows && h->mig_n > 0 && h->k16ok && (h->cmax + 3) / 4 <= 4 && (h->mig_n + kScoreTN - 1) / kScoreTN <= 65535 &&
          !wide_keys_forced() && !plain_order_forced();
 }
-bool mps_ordered(const nosplan_t* h) {
-  return h->mps_n > 0 && (h->mps_n + kScoreTN - 1) / kScoreTN <= 65535 && !plain_order_forced();
+bool mps_ordered(const nosplan_t* h, int D) {
+  return D <= kMaxOrderedRows && h->mps_n > 0 && (h->mps_n + kScoreTN - 1) / kScoreTN <= 65535 && !plain_order_forced();
 }
 
 // What the host walk (check_demands) would have said about the row the device flagged.
@@ -399,7 +400,7 @@ int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
                      int32_t* d_first, uint8_t* d_updated, int8_t* d_choice, cudaStream_t st, int base = 0) {
   if (D == 0) return NOSPLAN_OK;
   int rc = NOSPLAN_OK;
-  const bool ordered = mig_ordered(h);
+  const bool ordered = mig_ordered(h, D);
   if (!ordered) fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, -1);  // else rows_group_kernel does it
   if (d_choice) CU(cudaMemsetAsync(d_choice, 0xff, (size_t)D * h->mig_tg, st));
   if (h->mig_n > 0) {
@@ -448,7 +449,7 @@ int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
 int launch_mps_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d_key, const int32_t* d_qty,
                      int32_t* d_first, uint8_t* d_updated, uint8_t* d_free, uint32_t* d_mask, cudaStream_t st, int base = 0) {
   if (D == 0) return NOSPLAN_OK;
-  const bool ordered = mps_ordered(h);
+  const bool ordered = mps_ordered(h, D);
   if (!ordered) fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, -1);  // else rows_group_kernel does it
   if (h->mps_n > 0) {
     MpsScoreArgs a;
@@ -888,7 +889,7 @@ int nosplan_score_mig(nosplan_t* h, int n_demands, const int32_t* dem_off, const
   h->err.clear();
   if (!h->have_mig) return fail(h, NOSPLAN_ERR_ARG, "no MIG snapshot");
   // with the rows-by-key scorer the rows are validated on the device while they are grouped
-  const bool dev_check = mig_ordered(h);
+  const bool dev_check = mig_ordered(h, n_demands);
   int rc = dev_check ? check_demands_head(h, n_demands, dem_off, dem_key, dem_qty)
                      : check_demands(h, n_demands, dem_off, dem_key, dem_qty, h->P);
   if (rc) return rc;
@@ -939,7 +940,7 @@ int nosplan_score_mps(nosplan_t* h, int n_demands, const int32_t* dem_off, const
   h->err.clear();
   if (!h->have_mps) return fail(h, NOSPLAN_ERR_ARG, "no MPS snapshot");
   if ((out_free == nullptr) != (out_free_mask == nullptr)) return fail(h, NOSPLAN_ERR_ARG, "out_free and out_free_mask go together");
-  const bool dev_check = mps_ordered(h);
+  const bool dev_check = mps_ordered(h, n_demands);
   int rc = dev_check ? check_demands_head(h, n_demands, dem_off, dem_key, dem_qty)
                      : check_demands(h, n_demands, dem_off, dem_key, dem_qty, h->S);
   if (rc) return rc;
