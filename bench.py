@@ -113,6 +113,26 @@ def run_reference(args, cfg, rank):
     print(json.dumps(line), flush=True)
 
 
+def oracle_agrees_on_distinct_rows(pkg, cfg, kind, rows, first_node):
+    """first_node of every row == the oracle's answer for the row's request vector (one oracle row per distinct
+    vector; bench rows are single-key)."""
+    from oracle import oracle as orc
+    off, key, qty = rows
+    D = len(off) - 1
+    if not np.all(np.diff(off) == 1):
+        raise SystemExit("bench.py: the parity check expects single-key rows")
+    sig = key[:D].astype(np.int64) * 1000003 + qty[:D]
+    uniq, fi = np.unique(sig, return_index=True)
+    o = orc.Oracle(cfg["tables"], mps_sizes=cfg["sizes"])
+    width = len(cfg["sizes"]) if kind else len(cfg["names"])
+    req, mask = pkg.synth.csr_to_dense(np.arange(len(uniq) + 1, dtype=np.int32), key[fi], qty[fi], width)
+    if kind == 0:
+        _, _, ef = o.score_mig(cfg["mig"], req, mask, threads=os.cpu_count() or 1, want_choice=False)
+    else:
+        _, _, _, ef = o.score_mps(cfg["mps"], req, mask, threads=os.cpu_count() or 1, want_free=False)
+    return bool(np.array_equal(ef[np.searchsorted(uniq, sig)], np.asarray(first_node)[:D]))
+
+
 def workload_config(cfg, args):
     nm = int(cfg["mig"]["n_nodes"]) if cfg["mig"] else 0
     np_ = int(cfg["mps"]["n_nodes"]) if cfg["mps"] else 0
@@ -233,6 +253,38 @@ def main():
         ref = pkg.dist.merge_first_node_keys(first_all, torch.zeros_like(first_all))
         if not torch.equal(ref, first_glob):
             raise SystemExit("bench.py: the peer-memory exchange disagrees with the NCCL all-reduce")
+    sharded_parity = None
+    if world > 1:
+        # The sharded answer must be the unsharded one: rank 0 scores the WHOLE snapshot on its GPU (one handle, no
+        # exchange) and checks that against the oracle on the distinct request vectors; every rank then compares
+        # what the sharded pass + exchange left in first_glob with rank 0's unsharded winners.
+        full = torch.full_like(first_all, -1)
+        oracle_ok = 1
+        if rank == 0:
+            fp = pkg.Planner(local_rank)
+            fp.set_mig_tables(cfg["names"], cfg["geom_off"], cfg["geom_counts"])
+            parts = []
+            for kind, snap, rows, D in ((0, cfg["mig"], (mo, mk, mq), Dm), (1, cfg["mps"], (po, pk, pq), Dp)):
+                if snap is None or not D:
+                    parts.append(np.full(1, -1, np.int32))
+                    continue
+                if kind == 0:
+                    fp.set_mig_snapshot(snap)
+                    got = fp.score_mig(*rows, want_updated=False, want_choice=False, want_first_choice=False)["first_node"]
+                else:
+                    fp.set_mps_snapshot(cfg["sizes"], snap)
+                    got = fp.score_mps(*rows, want_updated=False, want_free=False)["first_node"]
+                parts.append(got)
+                oracle_ok &= int(oracle_agrees_on_distinct_rows(pkg, cfg, kind, rows, got))
+            fp.close()
+            full = torch.from_numpy(np.concatenate(parts)).to(dev)
+        dist.broadcast(full, src=0)
+        same = torch.tensor([int(torch.equal(full, first_glob)), oracle_ok], device=dev)
+        dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        sharded_parity = {"vs_unsharded_gpu": "ok" if int(same[0]) else "MISMATCH",
+                          "vs_oracle_dedup": "ok" if int(same[1]) else "MISMATCH", "rows": int(first_all.numel())}
+        if not int(same[0]) or not int(same[1]):
+            raise SystemExit(f"bench.py: sharded scoring disagrees with the unsharded pass / the oracle: {sharded_parity}")
     sampler = ClockSampler(local_rank)
     sampler.start()
     total_ms = mig_ms = mps_ms = 0.0
@@ -309,8 +361,16 @@ def main():
         h2d += (Dm + Dp) * 4
         d2h += (Dm + Dp) * 4
     for _ in range(args.warmup):
-        step_e2e()
+        last = step_e2e()
     barrier()
+    if world > 1 and sharded_parity is not None:
+        # the end-to-end path (host buffers in, exchanged winners back on the host) against the same unsharded winners
+        want = torch.cat([full[:max(Dm, 1)][:Dm], full[max(Dm, 1):][:Dp]]).cpu()
+        e2e_same = torch.tensor([int(torch.equal(last[1], want))], device=dev)
+        dist.all_reduce(e2e_same, op=dist.ReduceOp.MIN)
+        sharded_parity["e2e_vs_unsharded_gpu"] = "ok" if int(e2e_same[0]) else "MISMATCH"
+        if not int(e2e_same[0]):
+            raise SystemExit("bench.py: the end-to-end sharded pass disagrees with the unsharded winners")
     t0 = time.perf_counter()
     for _ in range(args.steps):
         step_e2e()
@@ -364,6 +424,7 @@ def main():
                     "ms_per_step": float(e2e_t.item()) * 1e3},
             "gpu_launches": int(args.steps * ((3 if Dm else 0) + (3 if Dp else 0) + (2 if exchange.startswith("peer") else 0))),
             "exchange": exchange,
+            "sharded_parity": sharded_parity,
             "planner_latency_ms_p50": float(np.median(lat)) if lat else None,
             "planner_latency_ms_p95": float(np.percentile(lat, 95)) if lat else None,
             "planner_latency_gate_off_ms_p50": float(np.median(lat_off)) if lat_off else None,
