@@ -9,8 +9,10 @@ candidate evaluations per second (one evaluation = one iteration of pkg/gpu/mig/
 a (demand, node, GPU, allowed geometry) tuple; for MPS one greedy run per (demand, node, GPU)).
 Planner latency (Plan(snapshot, pods) through the C ABI, p50) is reported in the same line.
 
-N > 1: one process per GPU (torchrun), nodes sharded contiguously across ranks, pods replicated, one
-NCCL all-reduce(min) of the per-demand first-updating-node keys per step ("first node wins").
+N > 1: one process per GPU (torchrun), nodes sharded contiguously across ranks, pods replicated; the per-row
+"first node that would update" keys are exchanged by the library itself (the scorers' epilogues atomicMin their
+winners into every rank's buffer over NVLink, one finishing kernel reads the minimum: "first node wins"), and
+every run checks the sharded answer against an unsharded GPU pass and the CPU oracle before it is timed.
 """
 import argparse
 import json
@@ -154,6 +156,7 @@ def main():
     ap.add_argument("--pods", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-plan", action="store_true", help="skip the planner-latency section (profiling runs)")
+    ap.add_argument("--shard-of", type=int, default=1, help="one GPU, rank 0's shard of a W-rank run (ncu captures of the shard sizes)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
 
@@ -180,8 +183,8 @@ def main():
 
     planner = pkg.Planner(local_rank)
     planner.set_mig_tables(cfg["names"], cfg["geom_off"], cfg["geom_counts"])
-    mig, mig_lo = pkg.dist.shard_snapshot(cfg["mig"], rank, world)
-    mps, mps_lo = pkg.dist.shard_snapshot(cfg["mps"], rank, world)
+    mig, mig_lo = pkg.dist.shard_snapshot(cfg["mig"], rank, world if world > 1 else args.shard_of)
+    mps, mps_lo = pkg.dist.shard_snapshot(cfg["mps"], rank, world if world > 1 else args.shard_of)
     if mig is not None:
         planner.set_mig_snapshot(mig)
     if mps is not None:
@@ -195,48 +198,41 @@ def main():
     t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
     d_mo, d_mk, d_mq = t(mo), t(mk), t(mq)
     d_po, d_pk, d_pq = t(po), t(pk), t(pq)
-    first_all = torch.full((max(Dm, 1) + max(Dp, 1),), -1, dtype=torch.int32, device=dev)
-    first_m, first_p = first_all[:max(Dm, 1)], first_all[max(Dm, 1):]
-    # N > 1: the per-row "first node" keys of all shards are merged by the library's own exchange
-    # (atomicMin into every peer's buffer over NVLink + step flags); NCCL is only the cross-check
-    first_glob = torch.empty_like(first_all)
+    Dall = Dm + Dp
+    # one step = ONE library call (nosplan_score_pass_dev): both kinds grouped by one launch, scored side by side;
+    # N > 1: the scorers' epilogues fold their winners straight into every rank's exchange buffer over NVLink and a
+    # finishing kernel hands back the minimum over ranks ("first node wins" over the whole list)
+    first_glob = torch.full((max(Dall, 1),), -1, dtype=torch.int32, device=dev)
+    first_loc = torch.full((max(Dall, 1),), -1, dtype=torch.int32, device=dev)
     exchange = "none"
     if world > 1:
-        exchange = "peer atomicMin over NVLink (libnosplan)"
+        exchange = "peer atomicMin over NVLink, pushed from the scorers' epilogue (libnosplan)"
         try:
-            pkg.dist.open_exchange(planner, first_all.numel())
+            pkg.dist.open_exchange(planner, max(Dall, 1))
         except pkg.NosplanError as e:  # no peer mapping on this box: say so, use the library collective
             exchange = f"nccl all-reduce (peer mapping failed: {e})"
         flags_t = torch.tensor([0 if exchange.startswith("peer") else 1], device=dev)
         dist.all_reduce(flags_t, op=dist.ReduceOp.MAX)
         if int(flags_t.item()) and exchange.startswith("peer"):
             exchange = "nccl all-reduce (a peer could not map)"
-        if exchange.startswith("peer"):
-            planner.set_node_base(mig_lo, mps_lo)  # the scorers report global node indices
-    lo_vec = torch.cat([torch.full((max(Dm, 1),), mig_lo, dtype=torch.int32, device=dev),
-                        torch.full((max(Dp, 1),), mps_lo, dtype=torch.int32, device=dev)])
+            planner.exchange_destroy()
+        planner.set_node_base(mig_lo, mps_lo)  # the scorers report global node indices
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
-    BIG = 0x7FFFFFFF
+    PASS = pkg.nosplan.PASS_SINGLE_KEY  # every bench row has one key (checked on the device, nosplan_pass_status)
+    ptrs = (Dm, d_mo.data_ptr(), d_mk.data_ptr(), d_mq.data_ptr(), Dp, d_po.data_ptr(), d_pk.data_ptr(), d_pq.data_ptr())
 
-    def step_device(ev=None):
-        """inputs resident in HBM; returns nothing. ev = (e0, e1, e2) to time mig / mps parts."""
+    def step_device(ev=None, flags=PASS):
+        """inputs resident in HBM; ev = (e0, e1) brackets the step on the launching stream"""
         if ev:
             ev[0].record()
-        if Dm:
-            planner.score_mig_dev(Dm, d_mo.data_ptr(), d_mk.data_ptr(), d_mq.data_ptr(), first_m.data_ptr(), 0, 0, stream)
+        if world > 1 and not exchange.startswith("peer"):
+            planner.score_pass_dev(*ptrs, first_loc.data_ptr(), flags, stream)
+            first_glob.copy_(pkg.dist.merge_first_node_keys(first_loc, torch.zeros_like(first_loc)))
+        else:
+            planner.score_pass_dev(*ptrs, first_glob.data_ptr(), flags, stream)
         if ev:
             ev[1].record()
-        if Dp:
-            planner.score_mps_dev(Dp, d_po.data_ptr(), d_pk.data_ptr(), d_pq.data_ptr(), first_p.data_ptr(), 0, 0, 0, stream)
-        if world > 1:
-            # first node wins across shards: global index = local + shard offset, min over ranks
-            if exchange.startswith("peer"):
-                planner.exchange_min_dev(first_all.numel(), first_all.data_ptr(), first_glob.data_ptr(), stream)
-            else:
-                first_glob.copy_(pkg.dist.merge_first_node_keys(first_all, lo_vec))
-        if ev:
-            ev[2].record()
 
     def barrier():
         if world > 1:
@@ -247,18 +243,23 @@ def main():
         flush.zero_()
         step_device()
     barrier()
+    planner.pass_status()
     if world > 1 and exchange.startswith("peer"):
-        # cross-check of the library's exchange against the NCCL all-reduce on the same keys
-        planner.exchange_status()
-        ref = pkg.dist.merge_first_node_keys(first_all, torch.zeros_like(first_all))
+        # cross-check of the fused exchange against an NCCL all-reduce(MIN) of the separately scored shards
+        if Dm:
+            planner.score_mig_dev(Dm, d_mo.data_ptr(), d_mk.data_ptr(), d_mq.data_ptr(), first_loc.data_ptr(), 0, 0, stream)
+        if Dp:
+            planner.score_mps_dev(Dp, d_po.data_ptr(), d_pk.data_ptr(), d_pq.data_ptr(), first_loc[Dm:].data_ptr(), 0, 0, 0, stream)
+        ref = pkg.dist.merge_first_node_keys(first_loc, torch.zeros_like(first_loc))
         if not torch.equal(ref, first_glob):
             raise SystemExit("bench.py: the peer-memory exchange disagrees with the NCCL all-reduce")
     sharded_parity = None
+    full = None
     if world > 1:
         # The sharded answer must be the unsharded one: rank 0 scores the WHOLE snapshot on its GPU (one handle, no
         # exchange) and checks that against the oracle on the distinct request vectors; every rank then compares
         # what the sharded pass + exchange left in first_glob with rank 0's unsharded winners.
-        full = torch.full_like(first_all, -1)
+        full = torch.full_like(first_glob, -1)
         oracle_ok = 1
         if rank == 0:
             fp = pkg.Planner(local_rank)
@@ -266,7 +267,6 @@ def main():
             parts = []
             for kind, snap, rows, D in ((0, cfg["mig"], (mo, mk, mq), Dm), (1, cfg["mps"], (po, pk, pq), Dp)):
                 if snap is None or not D:
-                    parts.append(np.full(1, -1, np.int32))
                     continue
                 if kind == 0:
                     fp.set_mig_snapshot(snap)
@@ -277,34 +277,48 @@ def main():
                 parts.append(got)
                 oracle_ok &= int(oracle_agrees_on_distinct_rows(pkg, cfg, kind, rows, got))
             fp.close()
-            full = torch.from_numpy(np.concatenate(parts)).to(dev)
+            if parts:
+                full = torch.from_numpy(np.concatenate(parts)).to(dev)
         dist.broadcast(full, src=0)
         same = torch.tensor([int(torch.equal(full, first_glob)), oracle_ok], device=dev)
         dist.all_reduce(same, op=dist.ReduceOp.MIN)
         sharded_parity = {"vs_unsharded_gpu": "ok" if int(same[0]) else "MISMATCH",
-                          "vs_oracle_dedup": "ok" if int(same[1]) else "MISMATCH", "rows": int(first_all.numel())}
+                          "vs_oracle_dedup": "ok" if int(same[1]) else "MISMATCH", "rows": int(Dall)}
         if not int(same[0]) or not int(same[1]):
             raise SystemExit(f"bench.py: sharded scoring disagrees with the unsharded pass / the oracle: {sharded_parity}")
     sampler = ClockSampler(local_rank)
     sampler.start()
-    total_ms = mig_ms = mps_ms = 0.0
-    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(args.steps)]
+    planner.kernel_timing(True)  # CUDA events around the two dominant kernels, on the streams they run on
     barrier()
     for i in range(args.steps):
         flush.zero_()
         step_device(evs[i])
     barrier()
-    for e in evs:
-        total_ms += e[0].elapsed_time(e[2])
-        mig_ms += e[0].elapsed_time(e[1])
-        mps_ms += e[1].elapsed_time(e[2])
-    tt = torch.tensor([total_ms, mig_ms, mps_ms], dtype=torch.float64, device=dev)
-    evt = torch.tensor([float(ev_m_local), float(ev_p_local)], dtype=torch.float64, device=dev)
+    total_ms = sum(e[0].elapsed_time(e[1]) for e in evs)
+    (mig_ms, mig_n), (mps_ms, mps_n) = planner.kernel_time_ms(0), planner.kernel_time_ms(1)
+    planner.kernel_timing(False)
+    planner.pass_status()
+    # the same kernels timed alone (the two kinds one after the other): the roofline's denominator
+    planner.kernel_timing(True)
+    for i in range(min(args.steps, 20)):
+        flush.zero_()
+        step_device(None, PASS | pkg.nosplan.PASS_SERIAL)
+    barrier()
+    (mig_alone_ms, mig_alone_n), (mps_alone_ms, mps_alone_n) = planner.kernel_time_ms(0), planner.kernel_time_ms(1)
+    planner.kernel_timing(False)
+    # executed work: one pass of the counting instantiations, outside every timed region
+    step_device(None, PASS | pkg.nosplan.PASS_COUNT)
+    barrier()
+    ex_m, ex_p = planner.executed_evals()
+    tt = torch.tensor([total_ms, mig_ms / max(mig_n, 1), mps_ms / max(mps_n, 1), mig_alone_ms / max(mig_alone_n, 1),
+                       mps_alone_ms / max(mps_alone_n, 1)], dtype=torch.float64, device=dev)
+    evt = torch.tensor([float(ev_m_local), float(ev_p_local), float(ex_m), float(ex_p)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dist.all_reduce(evt, op=dist.ReduceOp.SUM)
-    total_ms, mig_ms, mps_ms = (float(x) for x in tt.tolist())
-    ev_m, ev_p = (float(x) for x in evt.tolist())
+    total_ms, mig_k_ms, mps_k_ms, mig_k_alone_ms, mps_k_alone_ms = (float(x) for x in tt.tolist())
+    ev_m, ev_p, ex_m, ex_p = (float(x) for x in evt.tolist())
     ms_per_step = total_ms / args.steps
     value = (ev_m + ev_p) / (ms_per_step * 1e-3)
 
@@ -328,26 +342,19 @@ def main():
     mig_rows = (mo, mk, mq) if mig is not None else None
     mps_rows = (po, pk, pq) if mps is not None else None
 
+    peer = exchange.startswith("peer") or world == 1
+
     def step_e2e():
-        # one C-ABI call per pass: both snapshots in, both kinds scored (side by side inside the library), winners out
+        # ONE C-ABI call per pass: both snapshots and all rows in from host memory, both kinds scored, the shards'
+        # winners exchanged on the GPUs (N > 1), global winners + the winners' per-GPU choices back in host memory
         got = planner.score_snapshot(mig, mig_rows, cfg["sizes"], mps, mps_rows)
-        out = [got]
-        keys = []
-        if mig is not None and Dm:
-            keys.append((got["mig_first_node"], mig_lo))
-        if mps is not None and Dp:
-            keys.append((got["mps_first_node"], mps_lo))
-        if world > 1 and keys:
-            # the shards' winners (host arrays, local indices) -> global keys -> exchanged on the GPUs -> host
-            k = np.concatenate([np.where(f >= 0, f + lo, -1).astype(np.int32) for f, lo in keys])
-            kin = torch.from_numpy(k).to(dev)
-            kout = first_glob[:kin.numel()]
-            if exchange.startswith("peer"):
-                planner.exchange_min_dev(kin.numel(), kin.data_ptr(), kout.data_ptr(), stream)
-            else:
-                kout.copy_(pkg.dist.merge_first_node_keys(kin, torch.zeros_like(kin)))
-            out.append(kout.cpu())
-        return out
+        keys = np.concatenate([got[k] for k in ("mig_first_node", "mps_first_node") if k in got]) if Dall else np.zeros(0, np.int32)
+        if not peer and Dall:  # no peer mapping on this box: the shards' winners go through NCCL instead
+            kin = torch.from_numpy(keys).to(dev)
+            keys = pkg.dist.merge_first_node_keys(kin, torch.zeros_like(kin)).cpu().numpy()
+        return keys
+    if not peer:
+        planner.set_node_base(mig_lo, mps_lo)
     h2d = d2h = 0
     if mig is not None:
         h2d += mig["used"].nbytes + mig["free"].nbytes + mig["model"].nbytes + mig["gpu_off"].nbytes + mig["valid"].nbytes
@@ -357,20 +364,22 @@ def main():
         h2d += mps["used"].nbytes + mps["free"].nbytes + mps["mem_gb"].nbytes + mps["gpu_off"].nbytes + mps["valid"].nbytes + mps["free_mask"].nbytes
         h2d += po.nbytes + pk.nbytes + pq.nbytes
         d2h += Dp * 4
-    if world > 1:
-        h2d += (Dm + Dp) * 4
-        d2h += (Dm + Dp) * 4
+    if not peer:
+        h2d += Dall * 4
+        d2h += Dall * 4
     for _ in range(args.warmup):
         last = step_e2e()
     barrier()
     if world > 1 and sharded_parity is not None:
         # the end-to-end path (host buffers in, exchanged winners back on the host) against the same unsharded winners
-        want = torch.cat([full[:max(Dm, 1)][:Dm], full[max(Dm, 1):][:Dp]]).cpu()
-        e2e_same = torch.tensor([int(torch.equal(last[1], want))], device=dev)
+        e2e_same = torch.tensor([int(np.array_equal(last, full.cpu().numpy()[:Dall]))], device=dev)
         dist.all_reduce(e2e_same, op=dist.ReduceOp.MIN)
         sharded_parity["e2e_vs_unsharded_gpu"] = "ok" if int(e2e_same[0]) else "MISMATCH"
         if not int(e2e_same[0]):
             raise SystemExit("bench.py: the end-to-end sharded pass disagrees with the unsharded winners")
+    elif world == 1 and Dall:
+        if not np.array_equal(last, first_glob.cpu().numpy()[:Dall]):
+            raise SystemExit("bench.py: the end-to-end pass disagrees with the device-resident pass")
     t0 = time.perf_counter()
     for _ in range(args.steps):
         step_e2e()
@@ -385,26 +394,47 @@ def main():
     # The plan is one dependency chain over the pod order: it is not sharded.  With
     # N > 1 rank 0 plans the whole snapshot on its GPU (the state is a few MB) while the others wait.
     pods = cfg["pods"]
-    lat, lat_off = [], []
+    lat, lat_off, lat_absent = [], [], []
+    absent = None
     if rank == 0 and not args.no_plan:
         pl = planner
         if world > 1:
             pl = pkg.Planner(local_rank)
             pl.set_mig_tables(cfg["names"], cfg["geom_off"], cfg["geom_counts"])
+        if world > 1 or args.shard_of > 1:
             if cfg["mig"] is not None:
                 pl.set_mig_snapshot(cfg["mig"])
             if cfg["mps"] is not None:
                 pl.set_mps_snapshot(cfg["sizes"], cfg["mps"])
+        plan_args = (pods["kind"], pods["off"], pods["key"], pods["qty"])
         for i in range(args.warmup + args.steps):
             t0 = time.perf_counter()
-            pl.plan(pods["kind"], pods["off"], pods["key"], pods["qty"], gate=True, sched=True)
+            pl.plan(*plan_args, gate=True, sched=True)
             if i >= args.warmup:
                 lat.append((time.perf_counter() - t0) * 1e3)
         for i in range(1 + min(args.steps, 3)):
             t0 = time.perf_counter()
-            pl.plan(pods["kind"], pods["off"], pods["key"], pods["qty"], gate=False, sched=True)
+            pl.plan(*plan_args, gate=False, sched=True)
             if i >= 1:
                 lat_off.append((time.perf_counter() - t0) * 1e3)
+        # reference behaviour (gate on) where the gate does NOT stop everything: one requested MIG profile is
+        # taken out of the snapshot, so its pods fall through to tryRepartition until a commit brings it back
+        if cfg["mig"] is not None:
+            mk_all = pods["key"][pods["off"][:-1]][pods["kind"] == 0]
+            if mk_all.size:
+                col = int(np.bincount(mk_all).argmax())
+                snap = {k: (v.copy() if isinstance(v, np.ndarray) else v) for k, v in cfg["mig"].items()}
+                snap["used"][:, col] = 0
+                snap["free"][:, col] = 0
+                pl.set_mig_snapshot(snap)
+                absent = cfg["names"][col]
+                for i in range(1 + min(args.steps, 5)):
+                    t0 = time.perf_counter()
+                    r_abs = pl.plan(*plan_args, gate=True, sched=True)
+                    if i >= 1:
+                        lat_absent.append((time.perf_counter() - t0) * 1e3)
+                absent = {"profile": absent, "repartitions": int((r_abs["repart_node"] >= 0).sum()),
+                          "gate_hits": int(r_abs["gate_hit"].sum())}
         if world > 1:
             pl.close()
     barrier()
@@ -412,9 +442,47 @@ def main():
     sampler.join(timeout=2)
 
     if rank == 0:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import ncu_counters
         peak, peak_src = hbm_peak()
-        mig_kernel_s = (mig_ms / args.steps) * 1e-3
-        ach = (ev_m / world) * BYTES_PER_EVAL_MIG / mig_kernel_s / 1e9 if Dm and mig_kernel_s > 0 else 0.0
+        clocks = sampler.summary()
+        props = torch.cuda.get_device_properties(local_rank)
+        sm_count = props.multi_processor_count
+        sm_hz = (clocks["sm_mhz"] or clocks["sm_max_mhz"] or 1965) * 1e6
+        issue_peak = sm_count * 4 * sm_hz  # warp-instructions per second: 4 schedulers per SM, one issue per clock each
+        nodes_tot = (int(cfg["mig"]["n_nodes"]) if cfg["mig"] else 0) + (int(cfg["mps"]["n_nodes"]) if cfg["mps"] else 0)
+        shard_world = world if world > 1 else max(args.shard_of, 1)
+        ctr = ncu_counters.lookup(args.config, nodes_tot, int(len(pods["kind"])), shard_world)  # rank 0's shard
+        src = f"profiles/kernel_counters.json@csrc {ncu_counters.csrc_sha()}"
+
+        def roof(kernel, alone_ms, in_step_ms):
+            """issue-slot roofline of one kernel: ncu's executed warp-instructions of one launch / the launch's duration
+            measured here with CUDA events (the kernel alone on the GPU), against SMs x 4 schedulers x SM clock"""
+            r = {"bound": "issue", "kernel": kernel, "unit": "warp-inst/s", "peak": issue_peak, "peak_source":
+                 f"{sm_count} SMs x 4 schedulers x {sm_hz / 1e6:.0f} MHz (median SM clock sampled during the timed region)",
+                 "kernel_ms": alone_ms, "kernel_ms_in_step": in_step_ms, "achieved": None, "frac": None, "inst_per_launch": None,
+                 "traffic": None, "source": None}
+            k = (ctr or {}).get("kernels", {}).get(kernel)
+            if k and alone_ms > 0:
+                r["inst_per_launch"] = k["inst_executed"]
+                r["achieved"] = k["inst_executed"] / (alone_ms * 1e-3)
+                r["frac"] = r["achieved"] / issue_peak
+                r["traffic"] = k.get("dram_bytes_read", 0) + k.get("dram_bytes_write", 0)
+                r["source"] = src + f" ({ctr['capture']})"
+                r["hbm"] = {"dram_bytes_per_launch": r["traffic"], "achieved_gbs": r["traffic"] / (alone_ms * 1e-3) / 1e9,
+                            "peak_gbs": peak, "peak_source": peak_src,
+                            "frac_of_measured_peak": r["traffic"] / (alone_ms * 1e-3) / 1e9 / peak}
+            else:
+                r["source"] = "no ncu capture of this workload on the kernels in the tree (tools/ncu_counters.py)"
+            return r
+        roofline = roof("mig_score16_kernel", mig_k_alone_ms, mig_k_ms)
+        roofline["mps"] = roof("mps_score1_kernel", mps_k_alone_ms, mps_k_ms)
+        # SURVEY 8(d)'s byte model (64 B state + 4 B result per (row, node, GPU), no credit for on-chip reuse) as a work
+        # rate: the tiles are read once per CTA and re-used from shared memory, so this is NOT HBM traffic
+        if Dm and mig_k_alone_ms > 0:
+            roofline["algorithmic_gbs_no_reuse"] = (ev_m / world) * BYTES_PER_EVAL_MIG / (mig_k_alone_ms * 1e-3) / 1e9
+            roofline["algorithmic_bytes_per_eval"] = BYTES_PER_EVAL_MIG
+        n_launch = (1 if Dall else 0) + (1 if Dm else 0) + (1 if Dp else 0) + (1 if (world > 1 and exchange.startswith("peer")) else 0)
         line = {
             "metric": "candidate_evaluations_per_second", "value": value, "unit": "evals/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
@@ -422,28 +490,31 @@ def main():
             "config": workload_config(cfg, args),
             "e2e": {"value": e2e_val, "unit": "evals/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "ms_per_step": float(e2e_t.item()) * 1e3},
-            "gpu_launches": int(args.steps * ((3 if Dm else 0) + (3 if Dp else 0) + (2 if exchange.startswith("peer") else 0))),
+            "gpu_launches": int(args.steps * n_launch),
+            "launches_per_step": {"rows_group2_kernel": 1 if Dall else 0, "mig_score16_kernel": 1 if Dm else 0,
+                                  "mps_score1_kernel": 1 if Dp else 0,
+                                  "xchg_finish_kernel": 1 if (world > 1 and exchange.startswith("peer")) else 0},
             "exchange": exchange,
             "sharded_parity": sharded_parity,
             "planner_latency_ms_p50": float(np.median(lat)) if lat else None,
             "planner_latency_ms_p95": float(np.percentile(lat, 95)) if lat else None,
             "planner_latency_gate_off_ms_p50": float(np.median(lat_off)) if lat_off else None,
+            "planner_latency_absent_profile_ms_p50": float(np.median(lat_absent)) if lat_absent else None,
+            "planner_absent_profile_case": absent,
             "evals_per_step": {"mig": ev_m, "mps": ev_p},
-            "evals_definition": "MIG: one per (row, node, GPU, allowed geometry) = iterations of the loop body gpu.go:168-188, "
-                                "identical rows included; its demand-independent half (CanApplyGeometry, distance, total, id rank) "
-                                "is evaluated once per snapshot (inside e2e, outside value), the demand-dependent half per tuple in "
-                                "the timed kernels.  MPS: one per (row, node, GPU) run of slicing/gpu.go:162-220",
-            # achieved/frac follow SURVEY §8(d): algorithmic bytes (no credit for on-chip reuse) / time of the MIG
-            # scorer's launches (row grouping, mig_score16_kernel, the multi-key pass, the finishing pass; CUDA
-            # events).  traffic = ncu dram__bytes_read+write per mig_score16_kernel launch of the same command
-            # (profiles/r1k_bench_cfg5.md): the tile state is re-used from shared memory, HBM is idle and the
-            # binding roof is instruction issue (ncu: issue-active 73 %, ALU pipe 72 %, LSU 40 %): frac is above 1.
-            "roofline": {"bound": "hbm", "kernel": "mig_score16_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
-                         "frac": ach / peak, "peak_source": peak_src, "traffic": 1406208 if args.config == 5 and world == 1 else None,
-                         "algorithmic_bytes_per_eval": BYTES_PER_EVAL_MIG, "kernel_ms": mig_ms / args.steps,
-                         "mps_kernel_ms": mps_ms / args.steps, "binding_roof": "instruction issue (integer pipes)",
-                         "alu_pipe_pct_of_peak_ncu": 71.9, "issue_active_pct_ncu": 72.9},
-            "clocks": sampler.summary(),
+            "evals_counted": "nominal: every (row, node, GPU, allowed geometry) tuple the reference loop gpu.go:168-188 would visit "
+                             "(MPS: every (row, node, GPU) run of slicing/gpu.go:162-220), identical rows included",
+            # what the kernels really execute: a node leaves its GPU loop once the request is covered (node.go:164-169 makes
+            # every later candidate provide 0), a GPU that already holds enough skips its candidates, and the
+            # demand-independent half of an evaluation (CanApplyGeometry, distance, total, id rank) runs once per
+            # snapshot (inside e2e, outside value)
+            "evals_executed": {"mig": ex_m, "mps": ex_p,
+                               "definition": "MIG: (row, node, GPU, candidate) tuples whose provided-count was computed by the DPX core; "
+                                             "MPS: (row, node, GPU) runs of the closed form; counted by an instrumented "
+                                             "instantiation of the same kernels in one extra pass"},
+            "value_executed": (ex_m + ex_p) / (ms_per_step * 1e-3),
+            "roofline": roofline,
+            "clocks": clocks,
         }
         if not args.no_cpu_baseline and world == 1:
             from oracle import oracle as orc

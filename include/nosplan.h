@@ -175,6 +175,45 @@ int nosplan_score_mps_dev(nosplan_t* h, int n_demands, const int32_t* dem_off, c
                           const int32_t* dem_qty, int32_t* first_node, uint8_t* updated, uint8_t* out_free,
                           uint32_t* out_free_mask, void* stream);
 
+/* A whole device-resident scoring pass in one call: the MIG rows against the MIG snapshot and the MPS rows against
+ * the MPS snapshot (same per-row semantics as nosplan_score_mig_dev / nosplan_score_mps_dev: mig/node.go:145-177,
+ * slicing/node.go:120-152), first_node[0 .. n_mig_rows) for the MIG rows and [n_mig_rows .. + n_mps_rows) for the
+ * MPS rows.  Both kinds are grouped by one launch and scored side by side (two streams, forked from and joined
+ * back into `stream`); nothing is synchronised.
+ * Without an exchange on the handle, first_node holds local indices + the node base, -1 = none.  With an open
+ * exchange (nosplan_exchange_open) the call is collective: every rank calls it with the same row counts, and
+ * first_node receives tryRepartition's answer over the WHOLE node list (mig_controller.go:146-166): the lowest
+ * global index over ranks.  With NOSPLAN_PASS_SINGLE_KEY the scorers' epilogues fold their winners straight into
+ * every rank's exchange buffer over NVLink while the other tiles are still being scored (no separate push, no local
+ * round trip), and the last scorer CTA signals the step.
+ * flags: NOSPLAN_PASS_SINGLE_KEY  every row has exactly one key (checked on the device: a row that does not is
+ *                                 reported by nosplan_pass_status, never scored wrongly); the launches for
+ *                                 rows with several keys are then left out
+ *        NOSPLAN_PASS_SERIAL      score the kinds one after the other on `stream` (for timing a kernel alone)
+ *        NOSPLAN_PASS_COUNT       measurement: count the evaluations that really execute (nosplan_executed_evals)
+ * The first call (and any call with more rows than before) sizes the grouping scratch: it may allocate and thereby
+ * synchronise the device; make it before a latency-critical loop or a stream capture.  Demand rows are validated on
+ * the device; nosplan_pass_status (synchronises the device) reports the first bad row of the last pass and
+ * exchange time-outs. */
+#define NOSPLAN_PASS_SINGLE_KEY 1
+#define NOSPLAN_PASS_SERIAL 2
+#define NOSPLAN_PASS_COUNT 4
+int nosplan_score_pass_dev(nosplan_t* h, int n_mig_rows, const int32_t* mig_off, const int32_t* mig_key, const int32_t* mig_qty,
+                           int n_mps_rows, const int32_t* mps_off, const int32_t* mps_key, const int32_t* mps_qty,
+                           int32_t* first_node, int flags, void* stream);
+int nosplan_pass_status(nosplan_t* h);
+
+/* Measurement hooks (no counterpart in the reference).  nosplan_kernel_timing(h, 1): nosplan_score_pass_dev records
+ * CUDA events on the launching stream around its two dominant kernels (mig_score16_kernel, mps_score1_kernel);
+ * nosplan_kernel_time_ms (synchronises) returns the summed duration and the number of launches of kind 0 (MIG) /
+ * 1 (MPS) since the last read, at most the last 64.  nosplan_executed_evals (synchronises) returns and clears the
+ * counts gathered by passes run with NOSPLAN_PASS_COUNT: MIG = (row, node, GPU, candidate) evaluations whose
+ * provided-count was really computed (a (row, GPU) pair that enters the candidate core counts the model's
+ * candidates), MPS = (row, node, GPU) runs of the closed form. */
+int nosplan_kernel_timing(nosplan_t* h, int enable);
+int nosplan_kernel_time_ms(nosplan_t* h, int kind, double* total_ms, int* launches);
+int nosplan_executed_evals(nosplan_t* h, int64_t* mig, int64_t* mps);
+
 /* Allocation-free MIG scorer.  It has no counterpart in the reference.
  * For callers that may not allocate device memory when they need a score (a sidecar working inside
  * a fixed buffer budget handed to it by another process's CUDA context, a control loop that cannot

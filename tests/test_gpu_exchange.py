@@ -92,6 +92,18 @@ def test_two_ranks_min_over_peer_memory():
     assert "exchange ok" in r.stdout
 
 
+@pytest.mark.parametrize("args", [["5", "512", "6000"], ["4", "96", "900"], ["3", "40", "700"]])
+def test_two_ranks_sharded_pass_equals_unsharded_oracle(args):
+    """The sharded answer (fused push from the scorers + finish) == the oracle on the whole node list."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "sharded_pass_ranks.py"), "2"] + args, capture_output=True,
+                       text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "sharded pass ok" in r.stdout
+
+
 def test_presence_counts_follow_the_working_state():
     """nosplan_presence = the sums Controller.profileAlreadyPresent looks at (mig_controller.go:121-144): used + free
     per key over valid nodes, of the snapshot and of what a plan left behind."""

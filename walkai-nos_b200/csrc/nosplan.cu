@@ -90,13 +90,26 @@ struct nosplan {
   bool mps_state_dirty = false;
 
   // scratch / staging
-  DevBuf d_in[6];    // staging for int32 host inputs
+  DevBuf d_in[6];    // staging for int32 host inputs (MIG snapshot: 0-2; read-back: 3-5)
+  DevBuf d_inp[4];   // staging of the MPS snapshot (its own, so both snapshots can be in flight)
   DevBuf d_dem[3];   // demand CSR
   DevBuf d_out[6];   // outputs
   DevBuf d_plan[32];
-  DevBuf d_status, d_rowstatus;
-  unsigned long long* h_status = nullptr;  // pinned
-  cudaEvent_t status_ev = nullptr;
+  DevBuf d_status, d_rowstatus;            // d_rowstatus: one word per kind (lowest bad demand row, ~0 = none)
+  unsigned long long* h_status = nullptr;  // pinned: [0..1] MIG pack status, [2..3] MPS pack status, [4..5] row status, [6] exchange
+  cudaEvent_t status_ev = nullptr, status_ev2 = nullptr;
+  void* h_pin = nullptr;                   // pinned staging for results (nosplan_score_snapshot)
+  size_t h_pin_cap = 0;
+
+  // nosplan_score_pass_dev: fork/join of the two kinds, CUDA events around the dominant kernels, executed-work counters
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  static constexpr int kKevPool = 64;
+  bool kernel_timing = false;
+  cudaEvent_t kev[2][kKevPool][2] = {};
+  int kev_n[2] = {0, 0};
+  DevBuf d_counter;  // [2] evaluations executed by the CNT instantiations (MIG, MPS)
+  DevBuf d_passbuf;  // local winners when the pass cannot push from the scorers
+  int occ_cache[2][2][8] = {};  // [kind][out][cw] resident CTAs per SM of the ordered scorers (0 = not asked yet)
 
   // nosplan_score_snapshot: two private lanes (child handles), the MPS one driven by a worker thread
   std::vector<int32_t> tab_geom_off, tab_geom_counts;  // what nosplan_set_mig_tables was given (for the MIG lane)
@@ -109,7 +122,8 @@ struct nosplan {
   struct {
     bool created = false, open = false;
     int rank = 0, world = 1, max_keys = 0;
-    void* local = nullptr;             // keys[2][max_keys] + flags[world]
+    int stride = 0;                    // max_keys rounded up to a multiple of 4: both halves stay 16-byte aligned
+    void* local = nullptr;             // keys[2][stride] + pushed[kMaxWorld] + read[kMaxWorld]
     size_t flags_off = 0;
     void* mapped[kMaxWorld] = {};      // peers' buffers as mapped here (own slot = local)
     XchgPeers peers;
@@ -167,23 +181,25 @@ int upload(nosplan_t* h, DevBuf& b, const void* src, size_t bytes, cudaStream_t 
 }
 
 // status words of the pack kernels: [0] lowest failing code (~0 = clean), [1] evaluations per demand row
-int status_reset(nosplan_t* h, cudaStream_t st) {
-  CU(h->d_status.reserve(16));
-  CU(cudaMemsetAsync(h->d_status.p, 0xff, 8, st));
-  CU(cudaMemsetAsync(static_cast<char*>(h->d_status.p) + 8, 0, 8, st));
+int status_reset(nosplan_t* h, int kind, cudaStream_t st) {
+  CU(h->d_status.reserve(32));
+  char* base = static_cast<char*>(h->d_status.p) + 16 * kind;
+  CU(cudaMemsetAsync(base, 0xff, 8, st));
+  CU(cudaMemsetAsync(base + 8, 0, 8, st));
   return NOSPLAN_OK;
 }
+unsigned long long* status_words(nosplan_t* h, int kind) { return h->d_status.as<unsigned long long>() + 2 * kind; }
 // the read-back is enqueued right behind the pack kernel; work enqueued after it (tables that only the
 // scorers need) is not waited for: the stream orders it before any later call
-int status_enqueue(nosplan_t* h, cudaStream_t st) {
-  CU(cudaMemcpyAsync(h->h_status, h->d_status.p, 16, cudaMemcpyDeviceToHost, st));
-  CU(cudaEventRecord(h->status_ev, st));
+int status_enqueue(nosplan_t* h, int kind, cudaStream_t st) {
+  CU(cudaMemcpyAsync(h->h_status + 2 * kind, status_words(h, kind), 16, cudaMemcpyDeviceToHost, st));
+  CU(cudaEventRecord(kind ? h->status_ev2 : h->status_ev, st));
   return NOSPLAN_OK;
 }
-int status_wait(nosplan_t* h, unsigned long long out[2]) {
-  CU(cudaEventSynchronize(h->status_ev));
-  out[0] = h->h_status[0];
-  out[1] = h->h_status[1];
+int status_wait(nosplan_t* h, int kind, unsigned long long out[2]) {
+  CU(cudaEventSynchronize(kind ? h->status_ev2 : h->status_ev));
+  out[0] = h->h_status[2 * kind];
+  out[1] = h->h_status[2 * kind + 1];
   return NOSPLAN_OK;
 }
 
@@ -254,6 +270,7 @@ int score_waves() {  // measurement knob: waves of CTAs per scorer launch
 #ifndef NOSPLAN_RB
 #define NOSPLAN_RB 2
 #endif
+constexpr unsigned long long kXchgTimeoutNs = 2000000000ull;  // a rank that waits this long for a peer gives up
 constexpr int kScoreTN = 128;
 constexpr int kScoreDS = 4;  // threads per node in the MIG scorer
 
@@ -300,10 +317,10 @@ int launch_mig_score_kernel(nosplan_t* h, const MigScoreArgs& a, dim3 grid, size
   }
 }
 
-// Groups the demand rows of one scoring call by key and cuts them into work items (rows_group_kernel, which
-// also puts first_node[] to rest); max_work = the grid extent that covers any split of the rows.
-int plan_rows(nosplan_t* h, int kind, int D, int n_keys, int chunk, const int32_t* dem_off, const int32_t* dem_key,
-              const int32_t* dem_qty, const int32_t* key_cost, int32_t* first_node, cudaStream_t st, int* max_work) {
+// ---- rows by key (rows_group_kernel / rows_group2_kernel) -----------------------------------------------------------
+// Scratch of one kind's row grouping for D rows cut into items of `chunk` rows; max_work = the grid extent that
+// covers any split of the rows.  Allocates only when a buffer has to grow.
+int reserve_rows(nosplan_t* h, int kind, int D, int n_keys, int chunk, cudaStream_t st, int* max_work) {
   auto& rp = h->rp[kind];
   *max_work = (D + chunk - 1) / chunk + n_keys;  // every key may end with a short item
   CU(rp.rows.reserve(sizeof(int32_t) * (size_t)D * (n_keys + 1)));
@@ -313,33 +330,83 @@ int plan_rows(nosplan_t* h, int kind, int D, int n_keys, int chunk, const int32_
     CU(rp.cnt.reserve(sizeof(int32_t) * (kRowBuckets + 1)));
     CU(cudaMemsetAsync(rp.cnt.p, 0, sizeof(int32_t) * (kRowBuckets + 1), st));
   }
-  CU(h->d_rowstatus.reserve(8));
-  CU(cudaMemsetAsync(h->d_rowstatus.p, 0xff, 8, st));  // "no bad row"
-  rows_group_kernel<<<(D + 255) / 256, 256, 0, st>>>(D, n_keys, chunk, NOSPLAN_MAX_DEMAND_KEYS, NOSPLAN_MAX_DEMAND_QTY, dem_off,
-                                                     dem_key, dem_qty, key_cost, rp.cnt.as<int32_t>(), rp.rows.as<int32_t>(),
-                                                     rp.work.as<int32_t>(), rp.meta.as<int32_t>(), first_node,
-                                                     h->d_rowstatus.as<unsigned long long>());
+  CU(h->d_rowstatus.reserve(16));
+  return NOSPLAN_OK;
+}
+RowsGroupArgs group_args(nosplan_t* h, int kind, int D, int n_keys, int chunk, const int32_t* dem_off, const int32_t* dem_key,
+                         const int32_t* dem_qty, const int32_t* key_cost, int32_t* first_node, bool single_only) {
+  auto& rp = h->rp[kind];
+  RowsGroupArgs g{};
+  g.D = D;
+  g.P = n_keys;
+  g.chunk = chunk;
+  g.max_keys = NOSPLAN_MAX_DEMAND_KEYS;
+  g.max_qty = NOSPLAN_MAX_DEMAND_QTY;
+  g.single_only = single_only ? 1 : 0;
+  g.dem_off = dem_off;
+  g.dem_key = dem_key;
+  g.dem_qty = dem_qty;
+  g.key_cost = key_cost;
+  g.state = rp.cnt.as<int32_t>();
+  g.rows = rp.rows.as<int32_t>();
+  g.work = rp.work.as<int32_t>();
+  g.meta = rp.meta.as<int32_t>();
+  g.first_node = first_node;
+  g.status = h->d_rowstatus.as<unsigned long long>() + kind;
+  return g;
+}
+// Groups the demand rows of one scoring call by key and cuts them into work items (rows_group_kernel, which
+// also puts first_node[] to rest).
+int plan_rows(nosplan_t* h, int kind, int D, int n_keys, int chunk, const int32_t* dem_off, const int32_t* dem_key,
+              const int32_t* dem_qty, const int32_t* key_cost, int32_t* first_node, cudaStream_t st, int* max_work) {
+  int rc = reserve_rows(h, kind, D, n_keys, chunk, st, max_work);
+  if (rc) return rc;
+  CU(cudaMemsetAsync(h->d_rowstatus.as<unsigned long long>() + kind, 0xff, 8, st));  // "no bad row"
+  rows_group_kernel<<<(D + 255) / 256, 256, 0, st>>>(group_args(h, kind, D, n_keys, chunk, dem_off, dem_key, dem_qty, key_cost, first_node, false));
   CU(cudaGetLastError());
   return NOSPLAN_OK;
 }
 
-template <int CW, bool OUT>
-int launch_mig_score16_cw(nosplan_t* h, const MigScoreArgs& a, int tiles, cudaStream_t st) {
-  auto kern = mig_score16_kernel<kScoreTN, kScoreDS, CW, OUT, NOSPLAN_RB>;
-  const size_t smem = mig_score16_smem_bytes(h->h_tables.n_models, a.gs, a.cmax, kScoreTN);
-  if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MIG scorer tile needs %zu bytes of shared memory", smem);
-  CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int occ = 0;
-  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kScoreTN * kScoreDS, smem));
-  int chunk = 16, gy = 1;
+// ---- the ordered MIG scorer: instantiation, shared memory and row chunk for the handle's tables ------------------------
+struct Mig16Launch {
+  void (*kern)(MigScore16Args) = nullptr;
+  size_t smem = 0;
+  int chunk = 64, tiles = 0;
+};
+template <int CW>
+void (*mig16_kernel_of(bool out, bool cnt))(MigScore16Args) {
+  if (out) return mig_score16_kernel<kScoreTN, kScoreDS, CW, true, NOSPLAN_RB, false>;
+  if (cnt) return mig_score16_kernel<kScoreTN, kScoreDS, CW, false, NOSPLAN_RB, true>;
+  return mig_score16_kernel<kScoreTN, kScoreDS, CW, false, NOSPLAN_RB, false>;
+}
+int mig16_prepare(nosplan_t* h, int D, bool out, bool cnt, Mig16Launch* L) {
+  const int cw = std::max(1, std::min(4, (h->cmax + 3) / 4));
+  switch (cw) {
+    case 1: L->kern = mig16_kernel_of<1>(out, cnt); break;
+    case 2: L->kern = mig16_kernel_of<2>(out, cnt); break;
+    case 3: L->kern = mig16_kernel_of<3>(out, cnt); break;
+    default: L->kern = mig16_kernel_of<4>(out, cnt); break;
+  }
+  L->smem = mig_score16_smem_bytes(h->h_tables.n_models, h->mig_gs, h->cmax, kScoreTN);
+  if (L->smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MIG scorer tile needs %zu bytes of shared memory", L->smem);
+  L->tiles = (h->mig_n + kScoreTN - 1) / kScoreTN;
+  // (the attribute belongs to the function, not to the handle: another handle may have lowered it)
+  CU(cudaFuncSetAttribute(L->kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L->smem));
+  int& occ = h->occ_cache[0][out ? 1 : 0][cw];
+  if (occ == 0) {  // resident CTAs per SM; reset when a snapshot changes the tile size
+    int o = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, L->kern, kScoreTN * kScoreDS, L->smem));
+    occ = std::max(o, 1);
+  }
+  int gy = 1;
   // at least 64 rows per work item: on a small shard the tile load would otherwise outweigh the rows
-  pick_chunks(h->sm_count, tiles, a.D, 64, &chunk, &gy, std::max(occ, 1) * score_waves());
-  chunk = std::min(chunk, kRowCap);
-  int max_work = 0;
-  int rc = plan_rows(h, 0, a.D, h->P, chunk, a.dem_off, a.dem_key, a.dem_qty, h->d_profcost.as<int32_t>(), a.first_node, st, &max_work);
-  if (rc) return rc;
+  pick_chunks(h->sm_count, L->tiles, D, 64, &L->chunk, &gy, occ * score_waves());
+  L->chunk = std::min(L->chunk, kRowCap);
+  return NOSPLAN_OK;
+}
+MigScore16Args mig16_args(nosplan_t* h, const MigScoreArgs& a) {
   auto& rp = h->rp[0];
-  MigScore16Args A;
+  MigScore16Args A{};
   A.base = a;
   A.perm = h->d_mig_perm.as<int32_t>();
   A.rankg = h->d_mig_rankg.as<uint32_t>();
@@ -347,18 +414,18 @@ int launch_mig_score16_cw(nosplan_t* h, const MigScoreArgs& a, int tiles, cudaSt
   A.rows = rp.rows.as<int32_t>();
   A.work = rp.work.as<int32_t>();
   A.meta = rp.meta.as<int32_t>();
-  kern<<<dim3(max_work, tiles), kScoreTN * kScoreDS, smem, st>>>(A);
+  return A;
+}
+int launch_mig_score16(nosplan_t* h, const MigScoreArgs& a, cudaStream_t st) {
+  Mig16Launch L;
+  int rc = mig16_prepare(h, a.D, a.updated || a.choice, false, &L);
+  if (rc) return rc;
+  int max_work = 0;
+  rc = plan_rows(h, 0, a.D, h->P, L.chunk, a.dem_off, a.dem_key, a.dem_qty, h->d_profcost.as<int32_t>(), a.first_node, st, &max_work);
+  if (rc) return rc;
+  L.kern<<<dim3(max_work, L.tiles), kScoreTN * kScoreDS, L.smem, st>>>(mig16_args(h, a));
   CU(cudaGetLastError());
   return NOSPLAN_OK;
-}
-int launch_mig_score16(nosplan_t* h, const MigScoreArgs& a, int tiles, int cw, cudaStream_t st) {
-  const bool out = a.updated || a.choice;
-  switch (cw) {
-    case 1: return out ? launch_mig_score16_cw<1, true>(h, a, tiles, st) : launch_mig_score16_cw<1, false>(h, a, tiles, st);
-    case 2: return out ? launch_mig_score16_cw<2, true>(h, a, tiles, st) : launch_mig_score16_cw<2, false>(h, a, tiles, st);
-    case 3: return out ? launch_mig_score16_cw<3, true>(h, a, tiles, st) : launch_mig_score16_cw<3, false>(h, a, tiles, st);
-    default: return out ? launch_mig_score16_cw<4, true>(h, a, tiles, st) : launch_mig_score16_cw<4, false>(h, a, tiles, st);
-  }
 }
 
 // the rows-by-key path is taken (and with it the demand rows are validated on the device)
@@ -404,7 +471,7 @@ int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
   if (!ordered) fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, -1);  // else rows_group_kernel does it
   if (d_choice) CU(cudaMemsetAsync(d_choice, 0xff, (size_t)D * h->mig_tg, st));
   if (h->mig_n > 0) {
-    MigScoreArgs a;
+    MigScoreArgs a{};
     a.T = h->d_tables.as<MigTables>();
     a.s_used = h->d_mig_sused.as<uint4>();
     a.s_free = h->d_mig_sfree.as<uint4>();
@@ -432,11 +499,10 @@ int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
     pick_chunks(h->sm_count, tiles, D, 16, &a.d_chunk, &gy);
     size_t smem = mig_score_smem(h, kScoreTN);
     if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MIG scorer tile needs %zu bytes of shared memory", smem);
-    const int cw = (h->cmax + 3) / 4;
     if (ordered) {
       // common tables: rows grouped by profile, nodes ordered per profile, 16-bit keys (nosplan_score16.cuh);
       // rows with several keys go through the general kernel below, restricted to their list
-      if ((rc = launch_mig_score16(h, a, tiles, cw, st))) return rc;
+      if ((rc = launch_mig_score16(h, a, st))) return rc;
       a.row_list = h->rp[0].rows.as<int32_t>();
       a.row_meta = h->rp[0].meta.as<int32_t>();
     }
@@ -452,7 +518,7 @@ int launch_mps_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
   const bool ordered = mps_ordered(h, D);
   if (!ordered) fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, -1);  // else rows_group_kernel does it
   if (h->mps_n > 0) {
-    MpsScoreArgs a;
+    MpsScoreArgs a{};
     a.sizes = h->d_mps_sizes.as<int32_t>();
     a.S = h->S;
     a.gp = h->d_mps_gpu0.as<MpsGpu>();
@@ -530,8 +596,11 @@ int nosplan_create(int device, nosplan_t** out) {
     return NOSPLAN_ERR_CUDA;
   }
   cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device);
-  if (cudaHostAlloc(reinterpret_cast<void**>(&h->h_status), 16, cudaHostAllocDefault) != cudaSuccess ||
-      cudaEventCreateWithFlags(&h->status_ev, cudaEventDisableTiming) != cudaSuccess) {
+  if (cudaHostAlloc(reinterpret_cast<void**>(&h->h_status), 64, cudaHostAllocDefault) != cudaSuccess ||
+      cudaEventCreateWithFlags(&h->status_ev, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&h->status_ev2, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming) != cudaSuccess) {
     nosplan_destroy(h);
     return NOSPLAN_ERR_CUDA;
   }
@@ -565,6 +634,17 @@ void nosplan_destroy(nosplan_t* h) {
   for (auto& b : h->d_plan) b.release();
   if (h->h_status) cudaFreeHost(h->h_status);
   if (h->status_ev) cudaEventDestroy(h->status_ev);
+  if (h->status_ev2) cudaEventDestroy(h->status_ev2);
+  if (h->h_pin) cudaFreeHost(h->h_pin);
+  for (auto& b : h->d_inp) b.release();
+  if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+  if (h->ev_join) cudaEventDestroy(h->ev_join);
+  for (auto& kind : h->kev)
+    for (auto& pair : kind)
+      for (cudaEvent_t e : pair)
+        if (e) cudaEventDestroy(e);
+  h->d_counter.release();
+  h->d_passbuf.release();
   if (h->stream) cudaStreamDestroy(h->stream);
   if (h->stream2) cudaStreamDestroy(h->stream2);
   delete h;
@@ -651,14 +731,20 @@ int nosplan_set_mig_tables(nosplan_t* h, int n_profiles, const char* const* prof
   for (size_t i = 0; i < (size_t)geom_off[n_models] * n_profiles; ++i) maxq = std::max(maxq, (int)geom_counts[i]);
   h->k16ok = h->cmax <= 16 && maxq <= 63;
   h->have_tables = true;
+  std::memset(h->occ_cache, 0, sizeof(h->occ_cache));
   h->have_mig = false;  // a snapshot refers to model ids of the table it was uploaded against
   return NOSPLAN_OK;
 }
 
-int nosplan_set_mig_snapshot(nosplan_t* h, int n_nodes, const int32_t* gpu_off, const uint8_t* valid,
-                             const int32_t* model, const int32_t* used, const int32_t* free_) {
-  if (!h) return NOSPLAN_ERR_ARG;
-  h->err.clear();
+}  // extern "C"
+
+namespace {
+// Everything of a snapshot upload except waiting for the device's verdict (the range checks run in the pack
+// kernels): host-side checks of the node list, copies, pack, scheduling tables, read-back of the status words.
+// The handle's sizes are set at once so that work can be enqueued behind it; *_snapshot_finish waits for the
+// status and either confirms the snapshot or drops it.
+int mig_snapshot_enqueue(nosplan_t* h, int n_nodes, const int32_t* gpu_off, const uint8_t* valid, const int32_t* model,
+                         const int32_t* used, const int32_t* free_, cudaStream_t st) {
   if (!h->have_tables) return fail(h, NOSPLAN_ERR_ARG, "nosplan_set_mig_tables must be called first");
   if (n_nodes < 0 || !gpu_off) return fail(h, NOSPLAN_ERR_ARG, "bad node list");
   const int P = h->P;
@@ -676,18 +762,19 @@ int nosplan_set_mig_snapshot(nosplan_t* h, int n_nodes, const int32_t* gpu_off, 
   if (rc) return rc;
   const int npad = std::max(32, (n_nodes + 31) / 32 * 32);
   const int gsl = std::max(gs, 1);
+  h->have_mig = false;  // the device copy is being replaced: a failed call leaves no snapshot behind
   // the arrays go up as they are; range checks, the zeroing of invalid nodes' rows and the per-GPU
   // node/slot tables are the pack kernel's work (the host only walked gpu_off)
-  if ((rc = upload(h, h->d_mig_off, gpu_off, sizeof(int32_t) * (n_nodes + 1), h->stream))) return rc;
+  if ((rc = upload(h, h->d_mig_off, gpu_off, sizeof(int32_t) * (n_nodes + 1), st))) return rc;
   CU(h->d_mig_valid.reserve(std::max(n_nodes, 1)));
   if (valid) {
-    if ((rc = upload(h, h->d_mig_valid, valid, n_nodes, h->stream))) return rc;
+    if ((rc = upload(h, h->d_mig_valid, valid, n_nodes, st))) return rc;
   } else {
-    CU(cudaMemsetAsync(h->d_mig_valid.p, 1, std::max(n_nodes, 1), h->stream));
+    CU(cudaMemsetAsync(h->d_mig_valid.p, 1, std::max(n_nodes, 1), st));
   }
-  if ((rc = upload(h, h->d_in[0], model, sizeof(int32_t) * (size_t)tg, h->stream))) return rc;
-  if ((rc = upload(h, h->d_in[1], used, sizeof(int32_t) * (size_t)tg * P, h->stream))) return rc;
-  if ((rc = upload(h, h->d_in[2], free_, sizeof(int32_t) * (size_t)tg * P, h->stream))) return rc;
+  if ((rc = upload(h, h->d_in[0], model, sizeof(int32_t) * (size_t)tg, st))) return rc;
+  if ((rc = upload(h, h->d_in[1], used, sizeof(int32_t) * (size_t)tg * P, st))) return rc;
+  if ((rc = upload(h, h->d_in[2], free_, sizeof(int32_t) * (size_t)tg * P, st))) return rc;
   CU(h->d_mig_gnode.reserve(sizeof(int32_t) * std::max(tg, 1)));
   CU(h->d_mig_gslot.reserve(sizeof(int32_t) * std::max(tg, 1)));
   CU(h->d_mig_model.reserve(std::max(tg, 1)));
@@ -699,18 +786,17 @@ int nosplan_set_mig_snapshot(nosplan_t* h, int n_nodes, const int32_t* gpu_off, 
   CU(h->d_mig_sfree.reserve(sizeof(uint4) * (size_t)gsl * npad));
   CU(h->d_mig_smodel.reserve((size_t)gsl * npad));
   CU(h->d_mig_scnt.reserve(npad));
-  if ((rc = status_reset(h, h->stream))) return rc;
-  h->have_mig = false;  // the device copy is being replaced: a failed call leaves no snapshot behind
-  mig_pack_kernel<<<(npad * gsl + 127) / 128, 128, 0, h->stream>>>(
+  if ((rc = status_reset(h, 0, st))) return rc;
+  mig_pack_kernel<<<(npad * gsl + 127) / 128, 128, 0, st>>>(
       n_nodes, P, gsl, npad, NOSPLAN_MAX_COUNT, h->d_tables.as<MigTables>(), h->d_mig_off.as<int32_t>(),
       h->d_mig_valid.as<uint8_t>(), h->d_in[0].as<int32_t>(), h->d_in[1].as<int32_t>(), h->d_in[2].as<int32_t>(),
       h->d_mig_used0.as<uint4>(), h->d_mig_free0.as<uint4>(), h->d_mig_model.as<uint8_t>(), h->d_mig_sused.as<uint4>(),
       h->d_mig_sfree.as<uint4>(), h->d_mig_smodel.as<uint8_t>(), h->d_mig_scnt.as<uint8_t>(), h->d_mig_gnode.as<int32_t>(),
-      h->d_mig_gslot.as<int32_t>(), h->d_status.as<unsigned long long>());
+      h->d_mig_gslot.as<int32_t>(), status_words(h, 0));
   CU(cudaGetLastError());
-  CU(cudaMemcpyAsync(h->d_mig_used.p, h->d_mig_used0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, h->stream));
-  CU(cudaMemcpyAsync(h->d_mig_free.p, h->d_mig_free0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, h->stream));
-  if ((rc = status_enqueue(h, h->stream))) return rc;
+  CU(cudaMemcpyAsync(h->d_mig_used.p, h->d_mig_used0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, st));
+  CU(cudaMemcpyAsync(h->d_mig_free.p, h->d_mig_free0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, st));
+  if ((rc = status_enqueue(h, 0, st))) return rc;
   if (h->k16ok) {
     // 16-bit-key scorer: the demand-independent candidate ranks of every GPU, then the node order per
     // profile (scheduling data, not results)
@@ -721,18 +807,30 @@ int nosplan_set_mig_snapshot(nosplan_t* h, int n_nodes, const int32_t* gpu_off, 
     CU(h->d_mig_cost.reserve((size_t)P * npad));
     CU(h->d_mig_perm.reserve(sizeof(int32_t) * (size_t)P * npad));
     CU(h->d_profcost.reserve(sizeof(int32_t) * 32));
-    mig_rank16_kernel<<<(npad * gsl + 127) / 128, 128, 0, h->stream>>>(
+    mig_rank16_kernel<<<(npad * gsl + 127) / 128, 128, 0, st>>>(
         h->d_tables.as<MigTables>(), npad, gsl, cwk, h->d_mig_sused.as<uint4>(), h->d_mig_sfree.as<uint4>(),
         h->d_mig_smodel.as<uint8_t>(), h->d_mig_scnt.as<uint8_t>(), h->d_mig_rankg.as<uint32_t>(), h->d_mig_ufg.as<uint16_t>(),
         h->d_mig_maskg.as<uint32_t>());
-    mig_cost_kernel<<<(npad + 127) / 128, 128, 0, h->stream>>>(n_nodes, npad, gsl, P, h->d_mig_scnt.as<uint8_t>(),
-                                                               h->d_mig_maskg.as<uint32_t>(), h->d_mig_cost.as<uint8_t>());
-    mig_perm_kernel<<<P, 1024, 0, h->stream>>>(npad, h->d_mig_cost.as<uint8_t>(), h->d_mig_perm.as<int32_t>(),
-                                               h->d_profcost.as<int32_t>());
+    mig_cost_kernel<<<(npad + 127) / 128, 128, 0, st>>>(n_nodes, npad, gsl, P, h->d_mig_scnt.as<uint8_t>(),
+                                                        h->d_mig_maskg.as<uint32_t>(), h->d_mig_cost.as<uint8_t>());
+    mig_perm_kernel<<<P, 1024, 0, st>>>(npad, h->d_mig_cost.as<uint8_t>(), h->d_mig_perm.as<int32_t>(),
+                                        h->d_profcost.as<int32_t>());
     CU(cudaGetLastError());
   }
-  unsigned long long st[2];
-  if ((rc = status_wait(h, st))) return rc;
+  if (h->mig_gs != gsl) std::memset(h->occ_cache[0], 0, sizeof(h->occ_cache[0]));  // the tile follows the GPUs per node
+  h->mig_n = n_nodes;
+  h->mig_tg = tg;
+  h->mig_gs = gsl;
+  h->mig_npad = npad;
+  h->mig_evals = 0;
+  h->mig_state_dirty = false;
+  return NOSPLAN_OK;
+}
+int mig_snapshot_finish(nosplan_t* h, const int32_t* model, const int32_t* used, const int32_t* free_) {
+  unsigned long long st[2] = {~0ull, 0ull};
+  int rc = status_wait(h, 0, st);
+  if (rc) return rc;
+  const int P = h->P;
   if (st[0] != ~0ull) {  // first bad entry in GPU order, reported as the host walk used to
     const int g = (int)(st[0] / 64), sub = (int)(st[0] % 64);
     if (sub == 0) return fail(h, NOSPLAN_ERR_RANGE, "GPU %d: model %d unknown (mark the node invalid instead)", g, model[g]);
@@ -740,22 +838,14 @@ int nosplan_set_mig_snapshot(nosplan_t* h, int n_nodes, const int32_t* gpu_off, 
     return fail(h, NOSPLAN_ERR_RANGE, "GPU %d profile %s: used %d free %d out of range [0,%d]", g, h->names[p].c_str(),
                 used[(size_t)g * P + p], free_[(size_t)g * P + p], NOSPLAN_MAX_COUNT);
   }
-  const int64_t evals = (int64_t)st[1];
-  h->mig_n = n_nodes;
-  h->mig_tg = tg;
-  h->mig_gs = gsl;
-  h->mig_npad = npad;
-  h->mig_evals = evals;
+  h->mig_evals = (int64_t)st[1];
   h->have_mig = true;
-  h->mig_state_dirty = false;
   return NOSPLAN_OK;
 }
 
-int nosplan_set_mps_snapshot(nosplan_t* h, int n_sizes, const int32_t* sizes_gb, int n_nodes, const int32_t* gpu_off,
-                             const uint8_t* valid, const int32_t* mem_gb, const int32_t* used, const int32_t* free_,
-                             const uint32_t* free_mask) {
-  if (!h) return NOSPLAN_ERR_ARG;
-  h->err.clear();
+int mps_snapshot_enqueue(nosplan_t* h, int n_sizes, const int32_t* sizes_gb, int n_nodes, const int32_t* gpu_off,
+                         const uint8_t* valid, const int32_t* mem_gb, const int32_t* used, const int32_t* free_,
+                         const uint32_t* free_mask, cudaStream_t st) {
   if (n_sizes < 1 || n_sizes > NOSPLAN_MAX_MPS_SIZES || !sizes_gb)
     return fail(h, NOSPLAN_ERR_RANGE, "n_sizes %d out of range [1,%d]", n_sizes, NOSPLAN_MAX_MPS_SIZES);
   for (int s = 0; s < n_sizes; ++s) {
@@ -776,18 +866,19 @@ int nosplan_set_mps_snapshot(nosplan_t* h, int n_sizes, const int32_t* sizes_gb,
   if (tg > 0 && (!mem_gb || !used || !free_)) return fail(h, NOSPLAN_ERR_ARG, "null state arrays");
   int rc = bind(h);
   if (rc) return rc;
-  if ((rc = upload(h, h->d_mps_sizes, sizes_gb, sizeof(int32_t) * S, h->stream))) return rc;
-  if ((rc = upload(h, h->d_mps_off, gpu_off, sizeof(int32_t) * (n_nodes + 1), h->stream))) return rc;
+  h->have_mps = false;  // a failed call leaves no snapshot behind
+  if ((rc = upload(h, h->d_mps_sizes, sizes_gb, sizeof(int32_t) * S, st))) return rc;
+  if ((rc = upload(h, h->d_mps_off, gpu_off, sizeof(int32_t) * (n_nodes + 1), st))) return rc;
   CU(h->d_mps_valid.reserve(std::max(n_nodes, 1)));
   if (valid) {
-    if ((rc = upload(h, h->d_mps_valid, valid, n_nodes, h->stream))) return rc;
+    if ((rc = upload(h, h->d_mps_valid, valid, n_nodes, st))) return rc;
   } else {
-    CU(cudaMemsetAsync(h->d_mps_valid.p, 1, std::max(n_nodes, 1), h->stream));
+    CU(cudaMemsetAsync(h->d_mps_valid.p, 1, std::max(n_nodes, 1), st));
   }
-  if ((rc = upload(h, h->d_in[0], mem_gb, sizeof(int32_t) * (size_t)tg, h->stream))) return rc;
-  if ((rc = upload(h, h->d_in[1], used, sizeof(int32_t) * (size_t)tg * S, h->stream))) return rc;
-  if ((rc = upload(h, h->d_in[2], free_, sizeof(int32_t) * (size_t)tg * S, h->stream))) return rc;
-  if (free_mask && (rc = upload(h, h->d_in[3], free_mask, sizeof(uint32_t) * (size_t)tg, h->stream))) return rc;
+  if ((rc = upload(h, h->d_inp[0], mem_gb, sizeof(int32_t) * (size_t)tg, st))) return rc;
+  if ((rc = upload(h, h->d_inp[1], used, sizeof(int32_t) * (size_t)tg * S, st))) return rc;
+  if ((rc = upload(h, h->d_inp[2], free_, sizeof(int32_t) * (size_t)tg * S, st))) return rc;
+  if (free_mask && (rc = upload(h, h->d_inp[3], free_mask, sizeof(uint32_t) * (size_t)tg, st))) return rc;
   CU(h->d_mps_gnode.reserve(sizeof(int32_t) * std::max(tg, 1)));
   CU(h->d_mps_gslot.reserve(sizeof(int32_t) * std::max(tg, 1)));
   CU(h->d_mps_gpu0.reserve(sizeof(MpsGpu) * std::max(tg, 1)));
@@ -796,34 +887,43 @@ int nosplan_set_mps_snapshot(nosplan_t* h, int n_sizes, const int32_t* sizes_gb,
   CU(h->d_mps_gpu.reserve(sizeof(MpsGpu) * std::max(tg, 1)));
   CU(h->d_mps_ulo.reserve(sizeof(uint4) * std::max(tg, 1)));
   CU(h->d_mps_uhi.reserve(sizeof(uint4) * std::max(tg, 1)));
-  if ((rc = status_reset(h, h->stream))) return rc;
-  h->have_mps = false;  // a failed call leaves no snapshot behind
+  if ((rc = status_reset(h, 1, st))) return rc;
   if (n_nodes > 0) {
-    mps_pack_kernel<<<(n_nodes + 127) / 128, 128, 0, h->stream>>>(
+    mps_pack_kernel<<<(n_nodes + 127) / 128, 128, 0, st>>>(
         n_nodes, S, NOSPLAN_MAX_COUNT, NOSPLAN_MAX_MEM_GB, h->d_mps_sizes.as<int32_t>(), h->d_mps_off.as<int32_t>(),
-        h->d_mps_valid.as<uint8_t>(), h->d_in[0].as<int32_t>(), h->d_in[1].as<int32_t>(), h->d_in[2].as<int32_t>(),
-        free_mask ? h->d_in[3].as<uint32_t>() : nullptr, h->d_mps_gpu0.as<MpsGpu>(), h->d_mps_ulo0.as<uint4>(),
-        h->d_mps_uhi0.as<uint4>(), h->d_mps_gnode.as<int32_t>(), h->d_mps_gslot.as<int32_t>(),
-        h->d_status.as<unsigned long long>());
+        h->d_mps_valid.as<uint8_t>(), h->d_inp[0].as<int32_t>(), h->d_inp[1].as<int32_t>(), h->d_inp[2].as<int32_t>(),
+        free_mask ? h->d_inp[3].as<uint32_t>() : nullptr, h->d_mps_gpu0.as<MpsGpu>(), h->d_mps_ulo0.as<uint4>(),
+        h->d_mps_uhi0.as<uint4>(), h->d_mps_gnode.as<int32_t>(), h->d_mps_gslot.as<int32_t>(), status_words(h, 1));
     CU(cudaGetLastError());
-    CU(cudaMemcpyAsync(h->d_mps_gpu.p, h->d_mps_gpu0.p, sizeof(MpsGpu) * tg, cudaMemcpyDeviceToDevice, h->stream));
-    CU(cudaMemcpyAsync(h->d_mps_ulo.p, h->d_mps_ulo0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, h->stream));
-    CU(cudaMemcpyAsync(h->d_mps_uhi.p, h->d_mps_uhi0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, h->stream));
-    if ((rc = status_enqueue(h, h->stream))) return rc;
+    CU(cudaMemcpyAsync(h->d_mps_gpu.p, h->d_mps_gpu0.p, sizeof(MpsGpu) * tg, cudaMemcpyDeviceToDevice, st));
+    CU(cudaMemcpyAsync(h->d_mps_ulo.p, h->d_mps_ulo0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, st));
+    CU(cudaMemcpyAsync(h->d_mps_uhi.p, h->d_mps_uhi0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, st));
+    if ((rc = status_enqueue(h, 1, st))) return rc;
     // node order per size for the scorer (scheduling data, see nosplan_score16.cuh)
     CU(h->d_mps_cost.reserve((size_t)S * n_nodes));
     CU(h->d_mps_perm.reserve(sizeof(int32_t) * (size_t)S * n_nodes));
     CU(h->d_mps_sizecost.reserve(sizeof(int32_t) * 32));
-    mps_cost_kernel<<<(n_nodes + 127) / 128, 128, 0, h->stream>>>(n_nodes, S, h->d_mps_sizes.as<int32_t>(), h->d_mps_off.as<int32_t>(),
-                                                                  h->d_mps_valid.as<uint8_t>(), h->d_mps_gpu0.as<MpsGpu>(),
-                                                                  h->d_mps_cost.as<uint8_t>());
-    mig_perm_kernel<<<S, 1024, 0, h->stream>>>(n_nodes, h->d_mps_cost.as<uint8_t>(), h->d_mps_perm.as<int32_t>(),
-                                               h->d_mps_sizecost.as<int32_t>());
+    mps_cost_kernel<<<(n_nodes + 127) / 128, 128, 0, st>>>(n_nodes, S, h->d_mps_sizes.as<int32_t>(), h->d_mps_off.as<int32_t>(),
+                                                           h->d_mps_valid.as<uint8_t>(), h->d_mps_gpu0.as<MpsGpu>(),
+                                                           h->d_mps_cost.as<uint8_t>());
+    mig_perm_kernel<<<S, 1024, 0, st>>>(n_nodes, h->d_mps_cost.as<uint8_t>(), h->d_mps_perm.as<int32_t>(),
+                                        h->d_mps_sizecost.as<int32_t>());
     CU(cudaGetLastError());
   }
-  if (n_nodes == 0 && (rc = status_enqueue(h, h->stream))) return rc;
-  unsigned long long st[2];
-  if ((rc = status_wait(h, st))) return rc;
+  if (n_nodes == 0 && (rc = status_enqueue(h, 1, st))) return rc;
+  h->S = S;
+  h->mps_n = n_nodes;
+  h->mps_tg = tg;
+  h->mps_gs = std::max(gs, 1);
+  h->mps_evals = 0;
+  h->mps_state_dirty = false;
+  return NOSPLAN_OK;
+}
+int mps_snapshot_finish(nosplan_t* h, const int32_t* sizes_gb, const int32_t* mem_gb, const int32_t* used, const int32_t* free_) {
+  unsigned long long st[2] = {~0ull, 0ull};
+  int rc = status_wait(h, 1, st);
+  if (rc) return rc;
+  const int S = h->S;
   if (st[0] != ~0ull) {
     const int g = (int)(st[0] / 128), sub = (int)(st[0] % 128);
     if (sub == 0) return fail(h, NOSPLAN_ERR_RANGE, "GPU %d: memory %d GB out of range", g, mem_gb[g]);
@@ -839,15 +939,31 @@ int nosplan_set_mps_snapshot(nosplan_t* h, int n_sizes, const int32_t* sizes_gb,
                   used[(size_t)g * S + s], free_[(size_t)g * S + s]);
     return fail(h, NOSPLAN_ERR_ARG, "GPU %d: free_mask misses a key with a non-zero value", g);
   }
-  const int64_t evals = (int64_t)st[1];
-  h->S = S;
-  h->mps_n = n_nodes;
-  h->mps_tg = tg;
-  h->mps_gs = std::max(gs, 1);
-  h->mps_evals = evals;
+  h->mps_evals = (int64_t)st[1];
   h->have_mps = true;
-  h->mps_state_dirty = false;
   return NOSPLAN_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int nosplan_set_mig_snapshot(nosplan_t* h, int n_nodes, const int32_t* gpu_off, const uint8_t* valid,
+                             const int32_t* model, const int32_t* used, const int32_t* free_) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  int rc = mig_snapshot_enqueue(h, n_nodes, gpu_off, valid, model, used, free_, h->stream);
+  if (rc) return rc;
+  return mig_snapshot_finish(h, model, used, free_);
+}
+
+int nosplan_set_mps_snapshot(nosplan_t* h, int n_sizes, const int32_t* sizes_gb, int n_nodes, const int32_t* gpu_off,
+                             const uint8_t* valid, const int32_t* mem_gb, const int32_t* used, const int32_t* free_,
+                             const uint32_t* free_mask) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  int rc = mps_snapshot_enqueue(h, n_sizes, sizes_gb, n_nodes, gpu_off, valid, mem_gb, used, free_, free_mask, h->stream);
+  if (rc) return rc;
+  return mps_snapshot_finish(h, sizes_gb, mem_gb, used, free_);
 }
 
 int64_t nosplan_mig_evals_per_demand(const nosplan_t* h) { return (h && h->have_mig) ? h->mig_evals : 0; }
@@ -880,6 +996,315 @@ int nosplan_score_mps_dev(nosplan_t* h, int n_demands, const int32_t* dem_off, c
   if (rc) return rc;
   return launch_mps_score(h, n_demands, dem_off, dem_key, dem_qty, first_node, updated, out_free, out_free_mask,
                           (cudaStream_t)stream, h->mps_base);
+}
+
+}  // extern "C"
+
+// ---- a whole device-resident scoring pass in one call (nosplan_score_pass_dev) ---------------------------------------
+namespace {
+
+MigScoreArgs mig_base_args(nosplan_t* h, int D, const int32_t* off, const int32_t* key, const int32_t* qty, int32_t* first, int base) {
+  MigScoreArgs a{};
+  a.T = h->d_tables.as<MigTables>();
+  a.s_used = h->d_mig_sused.as<uint4>();
+  a.s_free = h->d_mig_sfree.as<uint4>();
+  a.s_model = h->d_mig_smodel.as<uint8_t>();
+  a.s_cnt = h->d_mig_scnt.as<uint8_t>();
+  a.gpu_off = h->d_mig_off.as<int32_t>();
+  a.N = h->mig_n;
+  a.npad = h->mig_npad;
+  a.gs = h->mig_gs;
+  a.cmax = h->cmax;
+  a.k16 = h->k16ok ? 1 : 0;
+  a.tg = h->mig_tg;
+  a.D = D;
+  a.dem_off = off;
+  a.dem_key = key;
+  a.dem_qty = qty;
+  a.first_node = first;
+  a.node_base = base;
+  return a;
+}
+MpsScoreArgs mps_base_args(nosplan_t* h, int D, const int32_t* off, const int32_t* key, const int32_t* qty, int32_t* first, int base) {
+  MpsScoreArgs a{};
+  a.sizes = h->d_mps_sizes.as<int32_t>();
+  a.S = h->S;
+  a.gp = h->d_mps_gpu0.as<MpsGpu>();
+  a.gpu_off = h->d_mps_off.as<int32_t>();
+  a.valid = h->d_mps_valid.as<uint8_t>();
+  a.N = h->mps_n;
+  a.tg = h->mps_tg;
+  a.D = D;
+  a.dem_off = off;
+  a.dem_key = key;
+  a.dem_qty = qty;
+  a.first_node = first;
+  a.node_base = base;
+  a.gs = h->mps_gs;
+  a.mode = 1;
+  a.perm = h->d_mps_perm.as<int32_t>();
+  a.rows = h->rp[1].rows.as<int32_t>();
+  a.work = h->rp[1].work.as<int32_t>();
+  a.meta = h->rp[1].meta.as<int32_t>();
+  return a;
+}
+
+// CUDA events around a dominant scorer launch (nosplan_kernel_timing): a pool of pairs, summed on request
+cudaEvent_t kev_next(nosplan_t* h, int kind, int which) {
+  if (!h->kernel_timing) return nullptr;
+  const int slot = h->kev_n[kind] % nosplan::kKevPool;
+  cudaEvent_t& e = h->kev[kind][slot][which];
+  if (!e && cudaEventCreate(&e) != cudaSuccess) return nullptr;
+  if (which == 1) ++h->kev_n[kind];
+  return e;
+}
+
+// x = the handle that owns the exchange (the caller's), h = the handle that owns the snapshots
+int score_pass_enqueue(nosplan_t* h, nosplan_t* x, int Dm, const int32_t* m_off, const int32_t* m_key, const int32_t* m_qty, int Dp,
+                       const int32_t* p_off, const int32_t* p_key, const int32_t* p_qty, int32_t* first_node, int flags,
+                       cudaStream_t st) {
+  const bool have_m = Dm > 0 && h->have_mig, have_p = Dp > 0 && h->have_mps;
+  int32_t* first_m = first_node;
+  int32_t* first_p = first_node + Dm;
+  const int Dall = Dm + Dp;
+  if (Dall == 0) return NOSPLAN_OK;
+  auto& xc = x->xch;
+  const bool exchange = xc.open;
+  if (exchange && Dall > xc.max_keys) return fail(h, NOSPLAN_ERR_RANGE, "%d rows exceed the exchange buffer (%d keys)", Dall, xc.max_keys);
+  const bool single = (flags & NOSPLAN_PASS_SINGLE_KEY) != 0;
+  const bool count = (flags & NOSPLAN_PASS_COUNT) != 0;
+  const bool ord_m = !have_m || mig_ordered(h, Dm), ord_p = !have_p || mps_ordered(h, Dp);
+  // fused: the scorers fold their winners into the rank's own half of the exchange buffer and signal the step themselves
+  const bool fused = exchange && single && ord_m && ord_p && (Dm == 0 || have_m) && (Dp == 0 || have_p);
+  // rows of a kind without a snapshot have no node to offer
+  if (Dm > 0 && !have_m && !fused) fill_i32_kernel<<<(Dm + 255) / 256, 256, 0, st>>>(first_m, Dm, -1);
+  if (Dp > 0 && !have_p && !fused) fill_i32_kernel<<<(Dp + 255) / 256, 256, 0, st>>>(first_p, Dp, -1);
+  int rc;
+  if (!ord_m || !ord_p || (exchange && !fused)) {
+    // general tables / multi-key rows under an exchange: score into a local buffer, then the two exchange kernels
+    int32_t* loc = first_node;
+    if (exchange) {
+      CU(h->d_passbuf.reserve(sizeof(int32_t) * (size_t)Dall));
+      loc = h->d_passbuf.as<int32_t>();
+      if (Dm > 0 && !have_m) fill_i32_kernel<<<(Dm + 255) / 256, 256, 0, st>>>(loc, Dm, -1);
+      if (Dp > 0 && !have_p) fill_i32_kernel<<<(Dp + 255) / 256, 256, 0, st>>>(loc + Dm, Dp, -1);
+    }
+    if (have_m && (rc = launch_mig_score(h, Dm, m_off, m_key, m_qty, loc, nullptr, nullptr, st, h->mig_base))) return rc;
+    if (have_p && (rc = launch_mps_score(h, Dp, p_off, p_key, p_qty, loc + Dm, nullptr, nullptr, nullptr, st, h->mps_base))) return rc;
+    if (exchange) {
+      const uint32_t step = ++xc.step;
+      const int blocks = std::max(1, std::min((Dall + 255) / 256, h->sm_count));
+      xchg_publish_kernel<<<blocks, 256, 0, st>>>(xc.peers, xc.world, xc.rank, xc.stride, step, Dall, loc, xc.done.as<unsigned int>(),
+                                                  kXchgTimeoutNs, xc.err.as<int>());
+      xchg_finish_kernel<<<blocks, 256, 0, st>>>(xc.peers, xc.world, xc.rank, xc.stride, step, Dall, first_node, xc.done.as<unsigned int>(),
+                                                 kXchgTimeoutNs, xc.err.as<int>());
+    }
+    CU(cudaGetLastError());
+    return NOSPLAN_OK;
+  }
+  // ---- both kinds on the ordered kernels: one grouping launch, the two scorers side by side ----
+  Mig16Launch L;
+  int mw_m = 0, mw_p = 0, chunk_p = 128, tiles_p = 0;
+  if (have_m) {
+    if ((rc = mig16_prepare(h, Dm, false, count, &L))) return rc;
+    if ((rc = reserve_rows(h, 0, Dm, h->P, L.chunk, st, &mw_m))) return rc;
+  }
+  size_t smem_p = 0;
+  if (have_p) {
+    tiles_p = (h->mps_n + kScoreTN - 1) / kScoreTN;
+    int gy;
+    pick_chunks(h->sm_count, tiles_p, Dp, 128, &chunk_p, &gy, 4 * score_waves());
+    chunk_p = std::min(chunk_p, kRowCap);
+    smem_p = mps_score1_smem_bytes(h->mps_gs, h->S, kScoreTN);
+    if (smem_p > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MPS scorer tile needs %zu bytes of shared memory", smem_p);
+    if ((rc = reserve_rows(h, 1, Dp, h->S, chunk_p, st, &mw_p))) return rc;
+  }
+  CU(h->d_rowstatus.reserve(16));
+  CU(cudaMemsetAsync(h->d_rowstatus.p, 0xff, 16, st));
+  RowsGroupArgs g0{}, g1{};
+  int nb0 = 0, nb1 = 0;
+  uint32_t step = 0;
+  if (fused) {
+    step = ++xc.step;
+    int32_t* own = xc.peers.keys[xc.rank] + (size_t)(step & 1u) * xc.stride;
+    first_m = own;
+    first_p = own + Dm;
+  }
+  if (have_m) {
+    g0 = group_args(h, 0, Dm, h->P, L.chunk, m_off, m_key, m_qty, h->d_profcost.as<int32_t>(), first_m, single);
+    nb0 = (Dm + 255) / 256;
+  }
+  if (have_p) {
+    g1 = group_args(h, 1, Dp, h->S, chunk_p, p_off, p_key, p_qty, h->d_mps_sizecost.as<int32_t>(), first_p, single);
+    nb1 = (Dp + 255) / 256;
+  }
+  if (fused && step > 2u) {  // the half may be overwritten once every rank has read what it held two steps ago
+    for (RowsGroupArgs* g : {&g0, &g1}) {
+      g->wait_read = xc.peers.read[xc.rank];
+      g->wait_world = xc.world;
+      g->wait_need = step - 2u;
+      g->wait_err = xc.err.as<int>();
+    }
+  }
+  if (nb0 + nb1 > 0) rows_group2_kernel<<<nb0 + nb1, 256, 0, st>>>(g0, g1, nb0);
+  CU(cudaGetLastError());
+  PushArgs push{};
+  if (fused) {
+    push.world = xc.world;
+    push.rank = xc.rank;
+    push.step = step;
+    push.total = (have_m ? (unsigned)mw_m * (unsigned)L.tiles : 0u) + (have_p ? (unsigned)mw_p * (unsigned)tiles_p : 0u);
+    push.ticket = xc.done.as<unsigned int>();
+    for (int r = 0; r < xc.world; ++r) push.flags[r] = xc.peers.pushed[r];
+  }
+  const bool fork = have_m && have_p && !(flags & NOSPLAN_PASS_SERIAL);
+  cudaStream_t st_p = fork ? h->stream2 : st;
+  if (fork) {
+    CU(cudaEventRecord(h->ev_fork, st));
+    CU(cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
+  }
+  if (have_m) {
+    MigScore16Args A = mig16_args(h, mig_base_args(h, Dm, m_off, m_key, m_qty, first_m, h->mig_base));
+    A.push = push;
+    A.counter = count ? h->d_counter.as<unsigned long long>() : nullptr;
+    if (cudaEvent_t e = kev_next(h, 0, 0)) CU(cudaEventRecord(e, st));
+    L.kern<<<dim3(mw_m, L.tiles), kScoreTN * kScoreDS, L.smem, st>>>(A);
+    if (cudaEvent_t e = kev_next(h, 0, 1)) CU(cudaEventRecord(e, st));
+    if (!single) {  // rows with several keys: the general kernel restricted to their list (leaves at once when there are none)
+      MigScoreArgs a = A.base;
+      a.row_list = h->rp[0].rows.as<int32_t>();
+      a.row_meta = h->rp[0].meta.as<int32_t>();
+      int gy;
+      pick_chunks(h->sm_count, L.tiles, Dm, 16, &a.d_chunk, &gy);
+      const size_t smem = mig_score_smem(h, kScoreTN);
+      if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MIG scorer tile needs %zu bytes of shared memory", smem);
+      if ((rc = launch_mig_score_kernel(h, a, dim3(L.tiles, gy), smem, st))) return rc;
+    }
+  }
+  if (have_p) {
+    MpsScoreArgs a = mps_base_args(h, Dp, p_off, p_key, p_qty, first_p, h->mps_base);
+    a.push = push;
+    a.counter = count ? h->d_counter.as<unsigned long long>() + 1 : nullptr;
+    auto kern = count ? mps_score1_kernel<kScoreTN, kScoreDS, false, true> : mps_score1_kernel<kScoreTN, kScoreDS, false, false>;
+    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
+    if (cudaEvent_t e = kev_next(h, 1, 0)) CU(cudaEventRecord(e, st_p));
+    kern<<<dim3(mw_p, tiles_p), kScoreTN * kScoreDS, smem_p, st_p>>>(a);
+    if (cudaEvent_t e = kev_next(h, 1, 1)) CU(cudaEventRecord(e, st_p));
+    if (!single) {
+      a.mode = 2;
+      int gy;
+      pick_chunks(h->sm_count, tiles_p, Dp, 16, &a.d_chunk, &gy, 3 * score_waves());
+      const size_t smem = mps_score_smem_bytes(h->mps_gs, h->S, kScoreTN);
+      if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MPS scorer tile needs %zu bytes of shared memory", smem);
+      CU(cudaFuncSetAttribute(mps_score_kernel<kScoreTN, kScoreDS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      mps_score_kernel<kScoreTN, kScoreDS><<<dim3(tiles_p, gy), kScoreTN * kScoreDS, smem, st_p>>>(a);
+    }
+  }
+  CU(cudaGetLastError());
+  if (fork) {
+    CU(cudaEventRecord(h->ev_join, h->stream2));
+    CU(cudaStreamWaitEvent(st, h->ev_join, 0));
+  }
+  if (fused) {
+    const int blocks = std::max(1, std::min((Dall / 4 + 255) / 256, h->sm_count));
+    xchg_finish_kernel<<<blocks, 256, 0, st>>>(xc.peers, xc.world, xc.rank, xc.stride, step, Dall, first_node, xc.done.as<unsigned int>(),
+                                               kXchgTimeoutNs, xc.err.as<int>());
+    CU(cudaGetLastError());
+  }
+  return NOSPLAN_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int nosplan_score_pass_dev(nosplan_t* h, int n_mig_rows, const int32_t* mig_off, const int32_t* mig_key, const int32_t* mig_qty,
+                           int n_mps_rows, const int32_t* mps_off, const int32_t* mps_key, const int32_t* mps_qty,
+                           int32_t* first_node, int flags, void* stream) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  if (n_mig_rows < 0 || n_mps_rows < 0) return fail(h, NOSPLAN_ERR_ARG, "negative row count");
+  if (n_mig_rows + n_mps_rows > 0 && !first_node) return fail(h, NOSPLAN_ERR_ARG, "first_node is required");
+  if ((n_mig_rows > 0 && (!mig_off || !mig_key || !mig_qty)) || (n_mps_rows > 0 && (!mps_off || !mps_key || !mps_qty)))
+    return fail(h, NOSPLAN_ERR_ARG, "null demand arrays");
+  int rc = bind(h);
+  if (rc) return rc;
+  if ((flags & NOSPLAN_PASS_COUNT) && !h->d_counter.p) {
+    CU(h->d_counter.reserve(16));
+    CU(cudaMemset(h->d_counter.p, 0, 16));
+  }
+  return score_pass_enqueue(h, h, n_mig_rows, mig_off, mig_key, mig_qty, n_mps_rows, mps_off, mps_key, mps_qty, first_node, flags,
+                            (cudaStream_t)stream);
+}
+
+int nosplan_pass_status(nosplan_t* h) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  int rc = bind(h);
+  if (rc) return rc;
+  CU(cudaDeviceSynchronize());
+  if (h->d_rowstatus.p) {
+    unsigned long long st[2] = {~0ull, ~0ull};
+    CU(cudaMemcpy(st, h->d_rowstatus.p, 16, cudaMemcpyDeviceToHost));
+    for (int kind = 0; kind < 2; ++kind)
+      if (st[kind] != ~0ull) {
+        const int sub = (int)(st[kind] % 64);
+        return fail(h, sub == 0 || sub == kSubNotSingle ? NOSPLAN_ERR_ARG : NOSPLAN_ERR_RANGE, "%s demand row %llu rejected on the device (%s)",
+                    kind ? "MPS" : "MIG", st[kind] / 64,
+                    sub == 0 ? "dem_off not ascending" : sub == 1 ? "too many keys" : sub == kSubNotSingle ? "NOSPLAN_PASS_SINGLE_KEY set but the row does not have exactly one key"
+                    : (sub - 2) % 3 == 0 ? "key out of range" : (sub - 2) % 3 == 1 ? "keys not ascending" : "quantity out of range");
+      }
+  }
+  if (h->xch.created) {
+    int e = 0;
+    CU(cudaMemcpy(&e, h->xch.err.p, sizeof(int), cudaMemcpyDeviceToHost));
+    if (e) return fail(h, NOSPLAN_ERR_CUDA, "exchange: rank %d never signalled a step (waited 2 s)", e - 1);
+  }
+  return NOSPLAN_OK;
+}
+
+int nosplan_kernel_timing(nosplan_t* h, int enable) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  h->kernel_timing = enable != 0;
+  h->kev_n[0] = h->kev_n[1] = 0;
+  return NOSPLAN_OK;
+}
+
+int nosplan_kernel_time_ms(nosplan_t* h, int kind, double* total_ms, int* launches) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  if ((kind != 0 && kind != 1) || !total_ms || !launches) return fail(h, NOSPLAN_ERR_ARG, "bad argument");
+  int rc = bind(h);
+  if (rc) return rc;
+  CU(cudaDeviceSynchronize());
+  const int n = std::min(h->kev_n[kind], (int)nosplan::kKevPool);
+  double tot = 0;
+  for (int i = 0; i < n; ++i) {
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, h->kev[kind][i][0], h->kev[kind][i][1]));
+    tot += ms;
+  }
+  *total_ms = tot;
+  *launches = n;
+  h->kev_n[kind] = 0;
+  return NOSPLAN_OK;
+}
+
+int nosplan_executed_evals(nosplan_t* h, int64_t* mig, int64_t* mps) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  int rc = bind(h);
+  if (rc) return rc;
+  unsigned long long c[2] = {0, 0};
+  if (h->d_counter.p) {
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(c, h->d_counter.p, 16, cudaMemcpyDeviceToHost));
+    CU(cudaMemset(h->d_counter.p, 0, 16));
+  }
+  if (mig) *mig = (int64_t)c[0];
+  if (mps) *mps = (int64_t)c[1];
+  return NOSPLAN_OK;
 }
 
 int nosplan_score_mig(nosplan_t* h, int n_demands, const int32_t* dem_off, const int32_t* dem_key,
@@ -915,21 +1340,21 @@ int nosplan_score_mig(nosplan_t* h, int n_demands, const int32_t* dem_off, const
         h->d_tables.as<MigTables>(), h->d_mig_rankg.as<uint32_t>(), h->d_mig_ufg.as<uint16_t>(), h->d_mig_used0.as<uint4>(),
         h->d_mig_free0.as<uint4>(), h->d_mig_model.as<uint8_t>(), h->d_mig_off.as<int32_t>(), D, h->mig_gs, (h->cmax + 3) / 4,
         h->d_dem[0].as<int32_t>(), h->d_dem[1].as<int32_t>(), h->d_dem[2].as<int32_t>(), h->d_out[0].as<int32_t>(),
-        h->d_out[3].as<int8_t>());
+        h->d_out[3].as<int8_t>(), 0, h->mig_n);
   } else if (first_choice) {
     mig_finalize_kernel<<<(D + 127) / 128, 128, 0, st>>>(
         h->d_tables.as<MigTables>(), h->d_mig_used0.as<uint4>(), h->d_mig_free0.as<uint4>(), h->d_mig_model.as<uint8_t>(),
         h->d_mig_off.as<int32_t>(), D, h->mig_gs, h->d_dem[0].as<int32_t>(), h->d_dem[1].as<int32_t>(),
-        h->d_dem[2].as<int32_t>(), h->d_out[0].as<int32_t>(), h->d_out[3].as<int8_t>());
+        h->d_dem[2].as<int32_t>(), h->d_out[0].as<int32_t>(), h->d_out[3].as<int8_t>(), 0, h->mig_n);
   }
   CU(cudaGetLastError());
   if (first_node) CU(cudaMemcpyAsync(first_node, h->d_out[0].p, sizeof(int32_t) * D, cudaMemcpyDeviceToHost, st));
   if (first_choice) CU(cudaMemcpyAsync(first_choice, h->d_out[3].p, (size_t)D * h->mig_gs, cudaMemcpyDeviceToHost, st));
   if (updated && h->mig_n) CU(cudaMemcpyAsync(updated, h->d_out[1].p, (size_t)D * h->mig_n, cudaMemcpyDeviceToHost, st));
   if (choice && h->mig_tg) CU(cudaMemcpyAsync(choice, h->d_out[2].p, (size_t)D * h->mig_tg, cudaMemcpyDeviceToHost, st));
-  if (dev_check) CU(cudaMemcpyAsync(h->h_status, h->d_rowstatus.p, 8, cudaMemcpyDeviceToHost, st));
+  if (dev_check) CU(cudaMemcpyAsync(h->h_status + 4, h->d_rowstatus.p, 8, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
-  if (dev_check && h->h_status[0] != ~0ull) return describe_bad_row(h, h->h_status[0], dem_off, dem_key, dem_qty, h->P);
+  if (dev_check && h->h_status[4] != ~0ull) return describe_bad_row(h, h->h_status[4], dem_off, dem_key, dem_qty, h->P);
   return NOSPLAN_OK;
 }
 
@@ -969,9 +1394,9 @@ int nosplan_score_mps(nosplan_t* h, int n_demands, const int32_t* dem_off, const
     CU(cudaMemcpyAsync(out_free, h->d_out[2].p, (size_t)D * h->mps_tg * h->S, cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(out_free_mask, h->d_out[3].p, sizeof(uint32_t) * (size_t)D * h->mps_tg, cudaMemcpyDeviceToHost, st));
   }
-  if (dev_check) CU(cudaMemcpyAsync(h->h_status, h->d_rowstatus.p, 8, cudaMemcpyDeviceToHost, st));
+  if (dev_check) CU(cudaMemcpyAsync(h->h_status + 5, h->d_rowstatus.as<unsigned long long>() + 1, 8, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
-  if (dev_check && h->h_status[0] != ~0ull) return describe_bad_row(h, h->h_status[0], dem_off, dem_key, dem_qty, h->S);
+  if (dev_check && h->h_status[5] != ~0ull) return describe_bad_row(h, h->h_status[5], dem_off, dem_key, dem_qty, h->S);
   return NOSPLAN_OK;
 }
 
@@ -1611,16 +2036,16 @@ extern "C" int nosplan_exchange_create(nosplan_t* h, int rank, int world, int ma
   x.rank = rank;
   x.world = world;
   x.max_keys = max_keys;
-  x.flags_off = ((size_t)2 * max_keys * sizeof(int32_t) + 255) / 256 * 256;
-  const size_t bytes = x.flags_off + 256;
+  x.stride = (max_keys + 3) / 4 * 4;
+  x.flags_off = ((size_t)2 * x.stride * sizeof(int32_t) + 255) / 256 * 256;
+  const size_t bytes = x.flags_off + 256;  // pushed[16] + read[16] (+ padding)
   CU(cudaMalloc(&x.local, bytes));
   x.created = true;
-  CU(x.done.reserve(sizeof(unsigned int)));
+  CU(x.done.reserve(2 * sizeof(unsigned int)));
   CU(x.err.reserve(sizeof(int)));
-  fill_i32_kernel<<<(2 * max_keys + 255) / 256, 256, 0, h->stream>>>(static_cast<int32_t*>(x.local), 2 * max_keys, kNoNode);
-  CU(cudaGetLastError());
+  CU(cudaMemsetAsync(x.local, 0xff, (size_t)2 * x.stride * sizeof(int32_t), h->stream));  // -1: no node
   CU(cudaMemsetAsync(static_cast<char*>(x.local) + x.flags_off, 0, 256, h->stream));
-  CU(cudaMemsetAsync(x.done.p, 0, sizeof(unsigned int), h->stream));
+  CU(cudaMemsetAsync(x.done.p, 0, 2 * sizeof(unsigned int), h->stream));
   CU(cudaMemsetAsync(x.err.p, 0, sizeof(int), h->stream));
   CU(cudaStreamSynchronize(h->stream));  // at rest before any peer can learn the handle
   static_assert(sizeof(cudaIpcMemHandle_t) == NOSPLAN_IPC_HANDLE_BYTES, "IPC handle size");
@@ -1649,7 +2074,8 @@ extern "C" int nosplan_exchange_open(nosplan_t* h, const unsigned char* handles)
       CU(cudaIpcOpenMemHandle(&x.mapped[r], ipc, cudaIpcMemLazyEnablePeerAccess));
     }
     x.peers.keys[r] = static_cast<int32_t*>(x.mapped[r]);
-    x.peers.flags[r] = reinterpret_cast<uint32_t*>(static_cast<char*>(x.mapped[r]) + x.flags_off);
+    x.peers.pushed[r] = reinterpret_cast<uint32_t*>(static_cast<char*>(x.mapped[r]) + x.flags_off);
+    x.peers.read[r] = x.peers.pushed[r] + kMaxWorld;
   }
   x.open = true;
   x.step = 0;
@@ -1668,9 +2094,10 @@ extern "C" int nosplan_exchange_min_dev(nosplan_t* h, int n_keys, const int32_t*
   cudaStream_t st = (cudaStream_t)stream;
   const uint32_t step = ++x.step;
   const int blocks = std::max(1, std::min((n_keys + 255) / 256, h->sm_count));
-  xchg_push_kernel<<<blocks, 256, 0, st>>>(x.peers, x.world, x.rank, x.max_keys, step, n_keys, keys_in, x.done.as<unsigned int>());
-  xchg_finish_kernel<<<blocks, 256, 0, st>>>(x.peers.keys[x.rank], x.peers.flags[x.rank], x.world, x.max_keys, step, n_keys,
-                                             keys_out, 2000000000ull, x.err.as<int>());
+  xchg_publish_kernel<<<blocks, 256, 0, st>>>(x.peers, x.world, x.rank, x.stride, step, n_keys, keys_in, x.done.as<unsigned int>(),
+                                              kXchgTimeoutNs, x.err.as<int>());
+  xchg_finish_kernel<<<blocks, 256, 0, st>>>(x.peers, x.world, x.rank, x.stride, step, n_keys, keys_out, x.done.as<unsigned int>(),
+                                             kXchgTimeoutNs, x.err.as<int>());
   CU(cudaGetLastError());
   return NOSPLAN_OK;
 }
@@ -1695,35 +2122,22 @@ extern "C" int nosplan_exchange_destroy(nosplan_t* h) {
 }
 
 // ---- one call for a whole scoring pass: nosplan_score_snapshot ---------------------------------------------------
-// The four calls of a pass (two snapshots in, two scorers) are each synchronous, so their copies and
-// kernels line up one after the other.  Here the MIG half and the MPS half run side by side on two private
-// child handles (own streams and buffers): the calling thread drives the MIG lane, a worker thread that
-// lives as long as the handle drives the MPS lane.  Nothing is installed on the caller's handle.
+// Snapshot upload, packing, scheduling tables, row grouping, both scorers, the exchange (when one is open on the
+// caller's handle), the winners' per-GPU choices and the copy back are all enqueued from the calling thread on a
+// private child handle — MIG work on its first stream, MPS work on its second, joined where one needs the other —
+// and the call waits exactly once, at the end.  The device's verdicts on the inputs (range checks of both snapshots
+// and of the demand rows run inside the kernels) are read after that one wait.  Nothing is installed on the caller's handle.
 struct Lanes {
-  nosplan_t* mig = nullptr;
-  nosplan_t* mps = nullptr;
+  nosplan_t* pass = nullptr;
   uint64_t tab_version = 0;
-  std::thread worker;
-  std::mutex m;
-  std::condition_variable cv;
-  std::function<int()> job;
-  bool has_job = false, done = false, quit = false;
-  int rc = 0;
+  DevBuf d_demp[3];  // MPS demand rows (the MIG rows use the child's d_dem)
 };
 
 void lanes_release(nosplan_t* h) {
   Lanes* L = h->lanes;
   if (!L) return;
-  if (L->worker.joinable()) {
-    {
-      std::lock_guard<std::mutex> g(L->m);
-      L->quit = true;
-    }
-    L->cv.notify_all();
-    L->worker.join();
-  }
-  if (L->mig) nosplan_destroy(L->mig);
-  if (L->mps) nosplan_destroy(L->mps);
+  for (auto& b : L->d_demp) b.release();
+  if (L->pass) nosplan_destroy(L->pass);
   delete L;
   h->lanes = nullptr;
 }
@@ -1732,30 +2146,28 @@ namespace {
 int lanes_get(nosplan_t* h, Lanes** out) {
   if (!h->lanes) {
     Lanes* L = new Lanes();
-    if (nosplan_create(h->device, &L->mig) != NOSPLAN_OK || nosplan_create(h->device, &L->mps) != NOSPLAN_OK) {
-      if (L->mig) nosplan_destroy(L->mig);
-      if (L->mps) nosplan_destroy(L->mps);
+    if (nosplan_create(h->device, &L->pass) != NOSPLAN_OK) {
       delete L;
-      return fail(h, NOSPLAN_ERR_CUDA, "could not create the scoring lanes");
+      return fail(h, NOSPLAN_ERR_CUDA, "could not create the scoring lane");
     }
-    L->worker = std::thread([L] {
-      std::unique_lock<std::mutex> lk(L->m);
-      for (;;) {
-        L->cv.wait(lk, [L] { return L->has_job || L->quit; });
-        if (L->quit) return;
-        L->has_job = false;
-        std::function<int()> job = std::move(L->job);
-        lk.unlock();
-        const int rc = job();
-        lk.lock();
-        L->rc = rc;
-        L->done = true;
-        L->cv.notify_all();
-      }
-    });
     h->lanes = L;
   }
   *out = h->lanes;
+  return NOSPLAN_OK;
+}
+bool rows_single_key(const nosplan_demands_t* r) {
+  const int32_t* off = r->off;
+  int bad = 0;
+  for (int d = 0; d < r->n_rows; ++d) bad |= (off[d + 1] - off[d]) ^ 1;
+  return bad == 0;
+}
+int pin_reserve(nosplan_t* h, size_t bytes) {
+  if (bytes <= h->h_pin_cap) return NOSPLAN_OK;
+  if (h->h_pin) cudaFreeHost(h->h_pin);
+  h->h_pin = nullptr;
+  h->h_pin_cap = 0;
+  CU(cudaHostAlloc(&h->h_pin, bytes, cudaHostAllocDefault));
+  h->h_pin_cap = bytes;
   return NOSPLAN_OK;
 }
 }  // namespace
@@ -1772,45 +2184,112 @@ extern "C" int nosplan_score_snapshot(nosplan_t* h, const nosplan_mig_snapshot_t
   Lanes* L = nullptr;
   int rc = lanes_get(h, &L);
   if (rc) return rc;
-  if (mig && L->tab_version != h->tab_version) {  // the MIG lane scores against the caller's tables
+  nosplan_t* c = L->pass;
+  auto child_fail = [&](int code, const char* who) { return fail(h, code, "%s%s", who, nosplan_last_error(c)); };
+  if (mig && L->tab_version != h->tab_version) {  // the lane scores against the caller's tables
     std::vector<const char*> names;
     for (auto& n : h->names) names.push_back(n.c_str());
-    rc = nosplan_set_mig_tables(L->mig, h->P, names.data(), h->tab_models, h->tab_geom_off.data(), h->tab_geom_counts.data());
-    if (rc) return fail(h, rc, "%s", nosplan_last_error(L->mig));
+    rc = nosplan_set_mig_tables(c, h->P, names.data(), h->tab_models, h->tab_geom_off.data(), h->tab_geom_counts.data());
+    if (rc) return child_fail(rc, "MIG: ");
     L->tab_version = h->tab_version;
   }
-  int64_t ev_mig = 0, ev_mps = 0;
-  if (mps) {
-    nosplan_t* c = L->mps;
-    std::lock_guard<std::mutex> g(L->m);
-    L->job = [c, mps, mps_rows, mps_first_node, &ev_mps]() -> int {
-      int r = nosplan_set_mps_snapshot(c, mps->n_sizes, mps->sizes_gb, mps->n_nodes, mps->gpu_off, mps->valid, mps->mem_gb,
-                                       mps->used, mps->free_, mps->free_mask);
-      if (r) return r;
-      return nosplan_score_mps(c, mps_rows->n_rows, mps_rows->off, mps_rows->key, mps_rows->qty, mps_first_node, nullptr,
-                               nullptr, nullptr, &ev_mps);
-    };
-    L->has_job = true;
-    L->done = false;
-    L->cv.notify_all();
-  }
-  int rc_mig = NOSPLAN_OK;
+  c->err.clear();
+  c->mig_base = h->mig_base;
+  c->mps_base = h->mps_base;
+  const int Dm = mig ? mig_rows->n_rows : 0, Dp = mps ? mps_rows->n_rows : 0, Dall = Dm + Dp;
+  if (Dm < 0 || Dp < 0) return fail(h, NOSPLAN_ERR_ARG, "negative demand count");
+  if (mig && (rc = check_demands_head(c, Dm, mig_rows->off, mig_rows->key, mig_rows->qty))) return child_fail(rc, "MIG: ");
+  if (mps && (rc = check_demands_head(c, Dp, mps_rows->off, mps_rows->key, mps_rows->qty))) return child_fail(rc, "MPS: ");
+  cudaStream_t sm = c->stream, sp = c->stream2;
+  c->have_mig = c->have_mps = false;
   if (mig) {
-    nosplan_t* c = L->mig;
-    rc_mig = nosplan_set_mig_snapshot(c, mig->n_nodes, mig->gpu_off, mig->valid, mig->model, mig->used, mig->free_);
-    if (!rc_mig)
-      rc_mig = nosplan_score_mig(c, mig_rows->n_rows, mig_rows->off, mig_rows->key, mig_rows->qty, mig_first_node, mig_first_choice,
-                                 nullptr, nullptr, &ev_mig);
+    if ((rc = mig_snapshot_enqueue(c, mig->n_nodes, mig->gpu_off, mig->valid, mig->model, mig->used, mig->free_, sm))) return child_fail(rc, "MIG: ");
+    if (Dm > 0) {
+      const int nnz = mig_rows->off[Dm];
+      if ((rc = upload(c, c->d_dem[0], mig_rows->off, sizeof(int32_t) * (Dm + 1), sm))) return child_fail(rc, "MIG: ");
+      if ((rc = upload(c, c->d_dem[1], mig_rows->key, sizeof(int32_t) * std::max(nnz, 1), sm))) return child_fail(rc, "MIG: ");
+      if ((rc = upload(c, c->d_dem[2], mig_rows->qty, sizeof(int32_t) * std::max(nnz, 1), sm))) return child_fail(rc, "MIG: ");
+    }
   }
-  int rc_mps = NOSPLAN_OK;
   if (mps) {
-    std::unique_lock<std::mutex> lk(L->m);
-    L->cv.wait(lk, [L] { return L->done; });
-    rc_mps = L->rc;
+    if ((rc = mps_snapshot_enqueue(c, mps->n_sizes, mps->sizes_gb, mps->n_nodes, mps->gpu_off, mps->valid, mps->mem_gb, mps->used,
+                                   mps->free_, mps->free_mask, sp)))
+      return child_fail(rc, "MPS: ");
+    if (Dp > 0) {
+      const int nnz = mps_rows->off[Dp];
+      if ((rc = upload(c, L->d_demp[0], mps_rows->off, sizeof(int32_t) * (Dp + 1), sp))) return child_fail(rc, "MPS: ");
+      if ((rc = upload(c, L->d_demp[1], mps_rows->key, sizeof(int32_t) * std::max(nnz, 1), sp))) return child_fail(rc, "MPS: ");
+      if ((rc = upload(c, L->d_demp[2], mps_rows->qty, sizeof(int32_t) * std::max(nnz, 1), sp))) return child_fail(rc, "MPS: ");
+    }
+    // the pass starts on the MIG stream: it needs the MPS snapshot and rows from here on
+    if (cudaEventRecord(c->ev_join, sp) != cudaSuccess || cudaStreamWaitEvent(sm, c->ev_join, 0) != cudaSuccess)
+      return fail(h, NOSPLAN_ERR_CUDA, "stream join failed");
   }
-  if (rc_mig) return fail(h, rc_mig, "MIG: %s", nosplan_last_error(L->mig));
-  if (rc_mps) return fail(h, rc_mps, "MPS: %s", nosplan_last_error(L->mps));
-  if (n_evals) *n_evals = ev_mig + ev_mps;
+  const int gs = mig ? c->mig_gs : 1;
+  const size_t out_bytes = sizeof(int32_t) * (size_t)std::max(Dall, 1) + (mig_first_choice ? (size_t)Dm * gs : 0);
+  if ((rc = pin_reserve(c, out_bytes))) return child_fail(rc, "");
+  if (Dall > 0) {
+    if (cudaSuccess != c->d_out[0].reserve(sizeof(int32_t) * (size_t)Dall)) return fail(h, NOSPLAN_ERR_CUDA, "out of device memory");
+    // the snapshots are confirmed after the one wait at the end; until then the kernels run on what was uploaded
+    // (every value is masked or clamped while it is packed, so unchecked inputs cannot take a kernel out of bounds)
+    c->have_mig = mig != nullptr;
+    c->have_mps = mps != nullptr;
+    int flags = 0;
+    if ((!mig || rows_single_key(mig_rows)) && (!mps || rows_single_key(mps_rows))) flags |= NOSPLAN_PASS_SINGLE_KEY;
+    rc = score_pass_enqueue(c, h, Dm, c->d_dem[0].as<int32_t>(), c->d_dem[1].as<int32_t>(), c->d_dem[2].as<int32_t>(), Dp,
+                            L->d_demp[0].as<int32_t>(), L->d_demp[1].as<int32_t>(), L->d_demp[2].as<int32_t>(), c->d_out[0].as<int32_t>(),
+                            flags, sm);
+    c->have_mig = c->have_mps = false;
+    if (rc) return child_fail(rc, "");
+    if (mig_first_choice && Dm > 0) {
+      if (cudaSuccess != c->d_out[3].reserve((size_t)Dm * gs)) return fail(h, NOSPLAN_ERR_CUDA, "out of device memory");
+      if (mig_ordered(c, Dm)) {
+        mig_finalize16_kernel<<<(Dm + 127) / 128, 128, 0, sm>>>(
+            c->d_tables.as<MigTables>(), c->d_mig_rankg.as<uint32_t>(), c->d_mig_ufg.as<uint16_t>(), c->d_mig_used0.as<uint4>(),
+            c->d_mig_free0.as<uint4>(), c->d_mig_model.as<uint8_t>(), c->d_mig_off.as<int32_t>(), Dm, gs, (c->cmax + 3) / 4,
+            c->d_dem[0].as<int32_t>(), c->d_dem[1].as<int32_t>(), c->d_dem[2].as<int32_t>(), c->d_out[0].as<int32_t>(),
+            c->d_out[3].as<int8_t>(), c->mig_base, c->mig_n);
+      } else {
+        mig_finalize_kernel<<<(Dm + 127) / 128, 128, 0, sm>>>(
+            c->d_tables.as<MigTables>(), c->d_mig_used0.as<uint4>(), c->d_mig_free0.as<uint4>(), c->d_mig_model.as<uint8_t>(),
+            c->d_mig_off.as<int32_t>(), Dm, gs, c->d_dem[0].as<int32_t>(), c->d_dem[1].as<int32_t>(), c->d_dem[2].as<int32_t>(),
+            c->d_out[0].as<int32_t>(), c->d_out[3].as<int8_t>(), c->mig_base, c->mig_n);
+      }
+    }
+    char* pin = static_cast<char*>(c->h_pin);
+    if (cudaMemcpyAsync(pin, c->d_out[0].p, sizeof(int32_t) * (size_t)Dall, cudaMemcpyDeviceToHost, sm) != cudaSuccess)
+      return fail(h, NOSPLAN_ERR_CUDA, "copy back failed");
+    if (mig_first_choice && Dm > 0 &&
+        cudaMemcpyAsync(pin + sizeof(int32_t) * (size_t)Dall, c->d_out[3].p, (size_t)Dm * gs, cudaMemcpyDeviceToHost, sm) != cudaSuccess)
+      return fail(h, NOSPLAN_ERR_CUDA, "copy back failed");
+    if (c->d_rowstatus.p && cudaMemcpyAsync(c->h_status + 4, c->d_rowstatus.p, 16, cudaMemcpyDeviceToHost, sm) != cudaSuccess)
+      return fail(h, NOSPLAN_ERR_CUDA, "copy back failed");
+  }
+  c->h_status[6] = 0;
+  if (h->xch.open && cudaMemcpyAsync(c->h_status + 6, h->xch.err.p, sizeof(int), cudaMemcpyDeviceToHost, sm) != cudaSuccess)
+    return fail(h, NOSPLAN_ERR_CUDA, "copy back failed");
+  if (cudaStreamSynchronize(sm) != cudaSuccess || cudaStreamSynchronize(sp) != cudaSuccess)
+    return fail(h, NOSPLAN_ERR_CUDA, "scoring pass failed: %s", cudaGetErrorString(cudaGetLastError()));
+  // the device's verdicts
+  if (mig && (rc = mig_snapshot_finish(c, mig->model, mig->used, mig->free_))) return child_fail(rc, "MIG: ");
+  if (mps && (rc = mps_snapshot_finish(c, mps->sizes_gb, mps->mem_gb, mps->used, mps->free_))) return child_fail(rc, "MPS: ");
+  c->have_mig = c->have_mps = false;  // the lane keeps no snapshot between calls
+  if (Dall > 0 && c->d_rowstatus.p) {
+    if (Dm > 0 && c->h_status[4] != ~0ull) {
+      describe_bad_row(c, c->h_status[4], mig_rows->off, mig_rows->key, mig_rows->qty, c->P);
+      return child_fail(c->h_status[4] % 64 == 0 ? NOSPLAN_ERR_ARG : NOSPLAN_ERR_RANGE, "MIG: ");
+    }
+    if (Dp > 0 && c->h_status[5] != ~0ull) {
+      describe_bad_row(c, c->h_status[5], mps_rows->off, mps_rows->key, mps_rows->qty, c->S);
+      return child_fail(c->h_status[5] % 64 == 0 ? NOSPLAN_ERR_ARG : NOSPLAN_ERR_RANGE, "MPS: ");
+    }
+  }
+  if ((int)c->h_status[6] != 0) return fail(h, NOSPLAN_ERR_CUDA, "exchange: rank %d never signalled a step (waited 2 s)", (int)c->h_status[6] - 1);
+  const char* pin = static_cast<const char*>(c->h_pin);
+  if (Dm > 0) std::memcpy(mig_first_node, pin, sizeof(int32_t) * (size_t)Dm);
+  if (Dp > 0) std::memcpy(mps_first_node, pin + sizeof(int32_t) * (size_t)Dm, sizeof(int32_t) * (size_t)Dp);
+  if (mig_first_choice && Dm > 0) std::memcpy(mig_first_choice, pin + sizeof(int32_t) * (size_t)Dall, (size_t)Dm * gs);
+  if (n_evals) *n_evals = (int64_t)Dm * c->mig_evals + (int64_t)Dp * c->mps_evals;
   return NOSPLAN_OK;
 }
 

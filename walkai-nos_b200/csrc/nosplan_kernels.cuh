@@ -18,6 +18,20 @@ constexpr int kMaxTotalGeoms = kMaxModels * kMaxGeoms;
 constexpr int kMaxSizes = NOSPLAN_MAX_MPS_SIZES;                  // 32 bytes = two uint4 per map
 constexpr int kMaxKeys = NOSPLAN_MAX_DEMAND_KEYS;
 constexpr int kNoNode = 0x7fffffff;
+constexpr int kMaxWorld = 16;  // ranks of the first-node exchange (nosplan_xchg.cuh)
+
+// Where a scorer CTA's pass ends (nosplan_score_pass_dev).  The per-row winners always go into first_node[] with
+// a local unsigned atomicMin (-1 = no node = above every index).  world == 0: that is all.  world >= 1:
+// first_node[] is the rank's own half of the exchange buffer, and the CTA that finishes last over all scorer
+// launches of the pass tells every rank that this rank's keys of the step are complete (nosplan_xchg.cuh).
+struct PushArgs {
+  int world;
+  int rank;
+  uint32_t step;
+  unsigned int total;          // CTAs of all scorer launches of this pass (each takes one ticket)
+  unsigned int* ticket;        // zero on entry, left at zero
+  uint32_t* flags[kMaxWorld];  // every rank's pushed[world]
+};
 
 // ---- MIG geometry tables (global memory, one per handle) ---------------------------------------------
 struct MigTables {
@@ -519,14 +533,14 @@ __global__ void mig_finalize_kernel(const MigTables* __restrict__ T, const uint4
                                     const uint4* __restrict__ a_free, const uint8_t* __restrict__ a_model,
                                     const int32_t* __restrict__ gpu_off, int D, int gs, const int32_t* __restrict__ dem_off,
                                     const int32_t* __restrict__ dem_key, const int32_t* __restrict__ dem_qty,
-                                    int32_t* __restrict__ first_node, int8_t* __restrict__ first_choice) {
+                                    int32_t* __restrict__ first_node, int8_t* __restrict__ first_choice, int node_base, int N) {
   const int d = blockIdx.x * blockDim.x + threadIdx.x;
   if (d >= D) return;
-  const int fn = first_node[d];
+  const int fn = first_node[d] < 0 ? -1 : first_node[d] - node_base;  // (see mig_finalize16_kernel)
   if (!first_choice) return;
   int8_t ch[NOSPLAN_MAX_GPUS_PER_NODE];
   for (int s = 0; s < NOSPLAN_MAX_GPUS_PER_NODE; ++s) ch[s] = -1;
-  if (fn >= 0) {
+  if (fn >= 0 && fn < N) {
     const int e0 = dem_off[d], k = dem_off[d + 1] - e0;
     int pid[kMaxKeys], qty[kMaxKeys];
     for (int j = 0; j < kMaxKeys; ++j) {
@@ -805,6 +819,8 @@ struct MpsScoreArgs {
   const int32_t* rows;
   const int32_t* work;
   const int32_t* meta;
+  PushArgs push;                // mps_score1_kernel: where the per-row winners go
+  unsigned long long* counter;  // its CNT instantiation: (row, node, GPU) runs that reached the closed form
 };
 
 // Shared-memory tile: per (node, slot) the free bytes as nw = ceil(S/4) words, the key mask, and

@@ -18,6 +18,7 @@
 // The arithmetic per (row, node, GPU, candidate) is the K16 path of mig_score_kernel, unchanged.
 #pragma once
 #include "nosplan_seq.cuh"
+#include "nosplan_xchg.cuh"
 
 namespace nsp {
 
@@ -175,55 +176,77 @@ constexpr int kNoRow = 63;
 // (sub 0: dem_off descending, 1: too many keys, 2 + 3j / 3 + 3j / 4 + 3j: key j out of range / not
 // ascending / quantity out of range); the host turns the code back into its message.
 // state[0 .. kRowBuckets) = cursors, state[kRowBuckets] = ticket; all zero on entry and on exit
-__global__ void rows_group_kernel(int D, int P, int chunk, int max_keys, int max_qty, const int32_t* __restrict__ dem_off,
-                                  const int32_t* __restrict__ dem_key, const int32_t* __restrict__ dem_qty,
-                                  const int32_t* __restrict__ key_cost, int32_t* __restrict__ state,
-                                  int32_t* __restrict__ rows, int32_t* __restrict__ work, int32_t* __restrict__ meta,
-                                  int32_t* __restrict__ first_node, unsigned long long* __restrict__ status) {
+struct RowsGroupArgs {
+  int D, P, chunk, max_keys, max_qty;
+  int single_only;  // 1: a row that does not have exactly one key is an error (sub code kSubNotSingle)
+  const int32_t* dem_off;
+  const int32_t* dem_key;
+  const int32_t* dem_qty;
+  const int32_t* key_cost;
+  int32_t* state;
+  int32_t* rows;
+  int32_t* work;
+  int32_t* meta;
+  int32_t* first_node;  // put to rest (-1) here; null = leave it alone
+  unsigned long long* status;
+  // sharded pass: first_node is the rank's own half of the exchange buffer, which may only be overwritten once
+  // every rank has read what it held two steps ago (nosplan_xchg.cuh); wait_world == 0: nothing to wait for
+  const uint32_t* wait_read;
+  int wait_world;
+  uint32_t wait_need;
+  int* wait_err;
+};
+constexpr int kSubNotSingle = 62;
+
+// block = index of this CTA among the n_blocks CTAs that group this kind's rows
+__device__ __forceinline__ void rows_group_body(const RowsGroupArgs& g, int block, int n_blocks) {
   __shared__ int s_last;
-  const int d = blockIdx.x * blockDim.x + threadIdx.x;  // blockDim is a multiple of 32: whole warps reach the match
+  if (g.wait_world) wait_flags(g.wait_read, g.wait_world, g.wait_need, 2000000000ull, g.wait_err);
+  const int D = g.D, P = g.P, chunk = g.chunk;
+  const int d = block * blockDim.x + threadIdx.x;  // blockDim is a multiple of 32: whole warps reach the match
   const int lane = threadIdx.x & 31;
   int b = kNoRow;
   if (d < D) {
-    first_node[d] = -1;  // "no node"; the scorers fold winners in with an unsigned atomicMin
-    const int e0 = __ldg(dem_off + d), k = __ldg(dem_off + d + 1) - e0, nnz = __ldg(dem_off + D);
+    if (g.first_node) g.first_node[d] = -1;  // "no node"; the scorers fold winners in with an unsigned atomicMin
+    const int e0 = __ldg(g.dem_off + d), k = __ldg(g.dem_off + d + 1) - e0, nnz = __ldg(g.dem_off + D);
     int sub = -1, key0 = 0;
     if (k < 0 || e0 < 0 || e0 + k > nnz) {  // entries outside [0, dem_off[D]) are never read
       sub = 0;
-    } else if (k > max_keys) {
+    } else if (k > g.max_keys) {
       sub = 1;
     } else {
       int prev = -1;
       for (int j = 0; j < k; ++j) {
-        const int key = __ldg(dem_key + e0 + j), q = __ldg(dem_qty + e0 + j);
+        const int key = __ldg(g.dem_key + e0 + j), q = __ldg(g.dem_qty + e0 + j);
         if (key < 0 || key >= P) sub = 2 + 3 * j;
         else if (j > 0 && key <= prev) sub = 3 + 3 * j;
-        else if (q < 0 || q > max_qty) sub = 4 + 3 * j;
+        else if (q < 0 || q > g.max_qty) sub = 4 + 3 * j;
         if (sub >= 0) break;
         if (j == 0) key0 = key;
         prev = key;
       }
+      if (sub < 0 && g.single_only && k != 1) sub = kSubNotSingle;
     }
-    if (sub >= 0) atomicMin(status, (unsigned long long)d * 64ull + (unsigned long long)sub);
+    if (sub >= 0) atomicMin(g.status, (unsigned long long)d * 64ull + (unsigned long long)sub);
     else b = k == 1 ? key0 : P;
   }
   const uint32_t peers = __match_any_sync(0xffffffffu, b);  // one atomic per bucket per warp
   const int leader = __ffs(peers) - 1;
   int base = 0;
-  if (b != kNoRow && lane == leader) base = atomicAdd(&state[b], __popc(peers));
+  if (b != kNoRow && lane == leader) base = atomicAdd(&g.state[b], __popc(peers));
   base = __shfl_sync(0xffffffffu, base, leader);
-  if (b != kNoRow) rows[(size_t)b * D + base + __popc(peers & ((1u << lane) - 1u))] = d;
+  if (b != kNoRow) g.rows[(size_t)b * D + base + __popc(peers & ((1u << lane) - 1u))] = d;
   __threadfence();
   __syncthreads();
-  if (threadIdx.x == 0) s_last = atomicAdd(&state[kRowBuckets], 1) == (int)gridDim.x - 1;
+  if (threadIdx.x == 0) s_last = atomicAdd(&g.state[kRowBuckets], 1) == n_blocks - 1;
   __syncthreads();
   if (!s_last || threadIdx.x >= 32) return;
   __threadfence();
   // the last block, one warp: lane b holds bucket b
   const uint32_t full = 0xffffffffu;
-  const int my_cnt = lane < P ? __ldcg(&state[lane]) : 0;
-  const int my_cost = lane < P ? key_cost[lane] : -1;
-  const int rest = __ldcg(&state[P]);
+  const int my_cnt = lane < P ? __ldcg(&g.state[lane]) : 0;
+  const int my_cost = lane < P ? g.key_cost[lane] : -1;
+  const int rest = __ldcg(&g.state[P]);
   // work items by descending key cost (ties: lower key first): the long CTAs start first
   int rank = 0;
   for (int j = 0; j < 32; ++j) {
@@ -238,19 +261,27 @@ __global__ void rows_group_kernel(int D, int P, int chunk, int max_keys, int max
   }
   if (lane < P)
     for (int it = 0; it < my_items; ++it) {
-      work[3 * (before + it) + 0] = lane;
-      work[3 * (before + it) + 1] = lane * D + it * chunk;
-      work[3 * (before + it) + 2] = min(chunk, my_cnt - it * chunk);
+      g.work[3 * (before + it) + 0] = lane;
+      g.work[3 * (before + it) + 1] = lane * D + it * chunk;
+      g.work[3 * (before + it) + 2] = min(chunk, my_cnt - it * chunk);
     }
   int nw = lane < P ? my_items : 0;
   for (int o = 16; o; o >>= 1) nw += __shfl_xor_sync(full, nw, o);
   if (lane == 0) {
-    meta[0] = nw;
-    meta[1] = P * D;
-    meta[2] = rest;
+    g.meta[0] = nw;
+    g.meta[1] = P * D;
+    g.meta[2] = rest;
   }
   __syncwarp();
-  for (int i = lane; i <= kRowBuckets; i += 32) state[i] = 0;
+  for (int i = lane; i <= kRowBuckets; i += 32) g.state[i] = 0;
+}
+
+__global__ void rows_group_kernel(const RowsGroupArgs g) { rows_group_body(g, blockIdx.x, gridDim.x); }
+
+// both kinds of a scoring pass in one launch: the first nb0 CTAs group kind 0's rows, the rest kind 1's
+__global__ void rows_group2_kernel(const RowsGroupArgs g0, const RowsGroupArgs g1, int nb0) {
+  if ((int)blockIdx.x < nb0) rows_group_body(g0, blockIdx.x, nb0);
+  else rows_group_body(g1, blockIdx.x - nb0, gridDim.x - nb0);
 }
 
 // ---- the scorer -------------------------------------------------------------------------------------------
@@ -262,6 +293,8 @@ struct MigScore16Args {
   const int32_t* rows;        // grouped row ids
   const int32_t* work;        // work items
   const int32_t* meta;
+  PushArgs push;                  // where the per-row winners go (plain first_node[] or the exchange buffers)
+  unsigned long long* counter;    // CNT instantiation: candidate evaluations that reached the DPX core
 };
 
 // Shared memory of one CTA (all u32, addressed through 32-bit shared-window addresses):
@@ -290,10 +323,16 @@ __device__ __forceinline__ uint2 lds_v2(uint32_t saddr) {
 
 // OUT: the call wants updated[] / choice[] (the per-row stores stay out of the hot instantiation)
 // RB: demand rows a thread scores per pass over its node's GPUs
-template <int TN, int DS, int CW, bool OUT, int RB>
+// CNT: measurement instantiation — counts the (row, node, GPU, candidate) evaluations that really execute
+//      (a (row, GPU) pair that enters the candidate core counts the model's candidates), see bench.py
+template <int TN, int DS, int CW, bool OUT, int RB, bool CNT = false>
 __global__ void __launch_bounds__(TN * DS, RB > 2 ? 2 : 3) mig_score16_kernel(const MigScore16Args A) {
   const MigScoreArgs& a = A.base;
-  if ((int)blockIdx.x >= A.meta[0]) return;  // the grid is sized for the worst split of the rows
+  if ((int)blockIdx.x >= A.meta[0]) {  // the grid is sized for the worst split of the rows
+    push_finish(A.push);
+    return;
+  }
+  unsigned long long executed = 0;
   extern __shared__ __align__(16) unsigned char smem[];
   constexpr int cw = CW;
   constexpr uint32_t kSlotStride = (2 * cw + 2) * TN * 4;  // bytes
@@ -385,6 +424,12 @@ __global__ void __launch_bounds__(TN * DS, RB > 2 ? 2 : 3) mig_score16_kernel(co
       // two candidates per instruction: key = provided << 9 | rank << 4 | (15 - index) per signed 16-bit
       // lane; a lane that cannot be applied carries 0x8000 and stays below the running maximum (>= 0)
       if (most > 0) {
+        if constexpr (CNT) {
+          const int m = a.s_model[(size_t)s * a.npad + n];
+          const int cc = T->geom_off[m + 1] - T->geom_off[m];
+#pragma unroll
+          for (int r = 0; r < RB; ++r) executed += (i + r * DS < len) ? cc : 0;
+        }
         const uint32_t mo = lds_u32(ps + kMoOff);
         const uint32_t nc2 = __byte_perm(x, 0u, 0x3232u);  // -(used + free) in both lanes
         uint32_t nd[RB];
@@ -427,7 +472,12 @@ __global__ void __launch_bounds__(TN * DS, RB > 2 ? 2 : 3) mig_score16_kernel(co
   __syncthreads();
   for (int i = threadIdx.x; i < len; i += TN * DS) {
     const int v = s_first[i];
-    if (v != kNoNode) atomicMin(reinterpret_cast<unsigned*>(a.first_node) + s_row[i], (unsigned)(v + a.node_base));
+    if (v != kNoNode) push_row(A.push, a.first_node, s_row[i], v + a.node_base);
+  }
+  push_finish(A.push);
+  if constexpr (CNT) {
+    executed = __reduce_add_sync(0xffffffffu, (unsigned)executed);  // < 2^32 per warp: <= 32 lanes x rows x GPUs x 16
+    if ((threadIdx.x & 31) == 0 && executed) atomicAdd(A.counter, executed);
   }
 }
 
@@ -439,13 +489,14 @@ __global__ void mig_finalize16_kernel(const MigTables* __restrict__ T, const uin
                                       const int32_t* __restrict__ gpu_off, int D, int gs, int cw,
                                       const int32_t* __restrict__ dem_off, const int32_t* __restrict__ dem_key,
                                       const int32_t* __restrict__ dem_qty, const int32_t* __restrict__ first_node,
-                                      int8_t* __restrict__ first_choice) {
+                                      int8_t* __restrict__ first_choice, int node_base, int N) {
   const int d = blockIdx.x * blockDim.x + threadIdx.x;
   if (d >= D) return;
-  const int fn = first_node[d];
+  // first_node holds indices over the whole (possibly sharded) list: a winner on another rank has no choices here
+  const int fn = first_node[d] < 0 ? -1 : first_node[d] - node_base;
   int8_t ch[NOSPLAN_MAX_GPUS_PER_NODE];
   for (int s = 0; s < NOSPLAN_MAX_GPUS_PER_NODE; ++s) ch[s] = -1;
-  if (fn >= 0) {
+  if (fn >= 0 && fn < N) {
     const int e0 = dem_off[d], k = dem_off[d + 1] - e0;
     const int g0 = gpu_off[fn], cnt = gpu_off[fn + 1] - g0;
     if (k == 1) {
@@ -497,9 +548,13 @@ __host__ __device__ inline size_t mps_score1_smem_bytes(int gs, int S, int tn) {
   return (size_t)gs * (3 + nw) * tn * 4 + (size_t)kRowCap * 12;
 }
 
-template <int TN, int DS, bool OUT>
+template <int TN, int DS, bool OUT, bool CNT = false>
 __global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreArgs a) {
-  if ((int)blockIdx.x >= a.meta[0]) return;
+  if ((int)blockIdx.x >= a.meta[0]) {
+    push_finish(a.push);
+    return;
+  }
+  unsigned int executed = 0;
   extern __shared__ __align__(16) unsigned char smem[];
   const int nw = (a.S + 3) >> 2;
   const uint32_t slot_stride = (uint32_t)(3 + nw) * TN * 4;  // bytes
@@ -555,6 +610,7 @@ __global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreAr
       const int fj = (int)(A & 0xffu);
       const int miss = resid - fj;  // getMissingSlices
       if (miss <= 0) break;         // this GPU already provides it; the residual drops to 0
+      if constexpr (CNT) ++executed;
       const uint32_t sp = ab.y;
       const int otot = (int)(sp >> 16);
       int spare = (int)(sp & 0xffffu);
@@ -596,7 +652,12 @@ __global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreAr
   __syncthreads();
   for (int i = threadIdx.x; i < len; i += TN * DS) {
     const int v = s_first[i];
-    if (v != kNoNode) atomicMin(reinterpret_cast<unsigned*>(a.first_node) + s_row[i], (unsigned)(v + a.node_base));
+    if (v != kNoNode) push_row(a.push, a.first_node, s_row[i], v + a.node_base);
+  }
+  push_finish(a.push);
+  if constexpr (CNT) {
+    executed = __reduce_add_sync(0xffffffffu, executed);
+    if ((threadIdx.x & 31) == 0 && executed) atomicAdd(a.counter, (unsigned long long)executed);
   }
 }
 

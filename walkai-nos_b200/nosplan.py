@@ -20,6 +20,9 @@ i64p = C.POINTER(C.c_int64)
 
 PLAN_GATE = 1
 PLAN_SCHED = 2
+PASS_SINGLE_KEY = 1
+PASS_SERIAL = 2
+PASS_COUNT = 4
 
 EXPORTS = [
     "nosplan_create", "nosplan_destroy", "nosplan_last_error", "nosplan_version", "nosplan_set_mig_tables",
@@ -28,6 +31,7 @@ EXPORTS = [
     "nosplan_score_mps_dev", "nosplan_mig_evals_per_demand", "nosplan_mps_evals_per_demand", "nosplan_score_mig_static", "nosplan_diff_plan_mig",
     "nosplan_set_node_base", "nosplan_exchange_create", "nosplan_exchange_open", "nosplan_exchange_min_dev",
     "nosplan_exchange_status", "nosplan_exchange_destroy", "nosplan_score_snapshot", "nosplan_presence",
+    "nosplan_score_pass_dev", "nosplan_pass_status", "nosplan_kernel_timing", "nosplan_kernel_time_ms", "nosplan_executed_evals",
 ]
 
 
@@ -324,6 +328,30 @@ class Planner:
                                               C.c_void_p(first_ptr), C.c_void_p(updated_ptr or None),
                                               C.c_void_p(free_ptr or None), C.c_void_p(mask_ptr or None),
                                               C.c_void_p(stream or None)))
+
+    def score_pass_dev(self, Dm, m_off, m_key, m_qty, Dp, p_off, p_key, p_qty, first_ptr, flags=0, stream=0):
+        """Both kinds in one call (nosplan_score_pass_dev); pointers are device addresses (ints), 0 = none."""
+        v = lambda x: C.c_void_p(x or None)
+        self._ck(self.L.nosplan_score_pass_dev(self.h, int(Dm), v(m_off), v(m_key), v(m_qty), int(Dp), v(p_off), v(p_key), v(p_qty),
+                                               v(first_ptr), int(flags), v(stream)))
+
+    def pass_status(self):
+        self._ck(self.L.nosplan_pass_status(self.h))
+
+    def kernel_timing(self, enable: bool):
+        self._ck(self.L.nosplan_kernel_timing(self.h, 1 if enable else 0))
+
+    def kernel_time_ms(self, kind: int):
+        """(summed ms, launches) of the kind's dominant scorer kernel since the last read (synchronises)."""
+        ms, n = C.c_double(0), C.c_int(0)
+        self._ck(self.L.nosplan_kernel_time_ms(self.h, int(kind), C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    def executed_evals(self):
+        """(MIG, MPS) evaluations counted by passes run with PASS_COUNT since the last read (synchronises)."""
+        a, b = C.c_int64(0), C.c_int64(0)
+        self._ck(self.L.nosplan_executed_evals(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
 
     def score_mig_static(self, n_nodes, gpus_per_node, valid_ptr, model_ptr, used_ptr, free_ptr, D, off_ptr, key_ptr, qty_ptr,
                          first_ptr, stream=0):
