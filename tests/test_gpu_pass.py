@@ -100,12 +100,16 @@ def test_pass_measurement_hooks_cfg5_shard():
         rows_p = pkg.synth.pods_of_kind(cfg["pods"], 1)[:3]
         exp = _expected(pkg, cfg, o, rows_m, rows_p)
         p.kernel_timing(True)
-        for _ in range(3):
+        for _ in range(3):  # both kinds share one launch: its events are filed under kind 0
             assert np.array_equal(_run_pass(torch, pkg, p, rows_m, rows_p, pkg.nosplan.PASS_SINGLE_KEY), exp)
         ms, n = p.kernel_time_ms(0)
         assert n == 3 and ms > 0
-        ms, n = p.kernel_time_ms(1)
-        assert n == 3 and ms > 0
+        assert p.kernel_time_ms(1) == (0.0, 0)
+        for _ in range(2):  # the kinds one after the other: a pair of events around each scorer kernel
+            assert np.array_equal(_run_pass(torch, pkg, p, rows_m, rows_p, pkg.nosplan.PASS_SINGLE_KEY | pkg.nosplan.PASS_SERIAL), exp)
+        for kind in (0, 1):
+            ms, n = p.kernel_time_ms(kind)
+            assert n == 2 and ms > 0
         assert p.kernel_time_ms(0) == (0.0, 0)
         p.kernel_timing(False)
         # executed evaluations: counted by the measurement instantiation, same winners, never more than the nominal count

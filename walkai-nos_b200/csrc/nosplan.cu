@@ -95,7 +95,8 @@ struct nosplan {
   DevBuf d_dem[3];   // demand CSR
   DevBuf d_out[6];   // outputs
   DevBuf d_plan[32];
-  DevBuf d_status, d_rowstatus;            // d_rowstatus: one word per kind (lowest bad demand row, ~0 = none)
+  DevBuf d_status, d_rowstatus;            // d_rowstatus: one word per kind: grouping call number << 32 | ~(lowest bad row code)
+  uint32_t row_call[2] = {0, 0};           // number of the kind's last grouping call
   unsigned long long* h_status = nullptr;  // pinned: [0..1] MIG pack status, [2..3] MPS pack status, [4..5] row status, [6] exchange
   cudaEvent_t status_ev = nullptr, status_ev2 = nullptr;
   void* h_pin = nullptr;                   // pinned staging for results (nosplan_score_snapshot)
@@ -258,6 +259,15 @@ bool plain_order_forced() {  // measurement knob: NOSPLAN_PLAIN_ORDER=1 scores r
   return f;
 }
 
+int min_chunk() {  // measurement knob: fewest rows per work item of 128 nodes
+  static const int w = [] {
+    const char* e = std::getenv("NOSPLAN_MIN_CHUNK");
+    const int v = e ? std::atoi(e) : 64;
+    return v >= 8 && v <= 512 ? v : 64;
+  }();
+  return w;
+}
+
 int score_waves() {  // measurement knob: waves of CTAs per scorer launch
   static const int w = [] {
     const char* e = std::getenv("NOSPLAN_SCORE_WAVES");
@@ -271,6 +281,7 @@ int score_waves() {  // measurement knob: waves of CTAs per scorer launch
 #define NOSPLAN_RB 2
 #endif
 constexpr unsigned long long kXchgTimeoutNs = 2000000000ull;  // a rank that waits this long for a peer gives up
+constexpr int kMig16Tile = 64;  // default nodes per CTA of the ordered MIG scorer (measured: profiles/r2_sweeps.md)
 constexpr int kScoreTN = 128;
 constexpr int kScoreDS = 4;  // threads per node in the MIG scorer
 
@@ -330,8 +341,16 @@ int reserve_rows(nosplan_t* h, int kind, int D, int n_keys, int chunk, cudaStrea
     CU(rp.cnt.reserve(sizeof(int32_t) * (kRowBuckets + 1)));
     CU(cudaMemsetAsync(rp.cnt.p, 0, sizeof(int32_t) * (kRowBuckets + 1), st));
   }
-  CU(h->d_rowstatus.reserve(16));
+  if (!h->d_rowstatus.p) {
+    CU(h->d_rowstatus.reserve(16));
+    CU(cudaMemsetAsync(h->d_rowstatus.p, 0, 16, st));
+  }
   return NOSPLAN_OK;
+}
+// the row code a status word holds for the kind's last grouping call, ~0 = every row was fine
+unsigned long long row_status_code(const nosplan_t* h, int kind, unsigned long long word) {
+  if ((uint32_t)(word >> 32) != h->row_call[kind]) return ~0ull;
+  return (unsigned long long)(0xffffffffu - (uint32_t)word);
 }
 RowsGroupArgs group_args(nosplan_t* h, int kind, int D, int n_keys, int chunk, const int32_t* dem_off, const int32_t* dem_key,
                          const int32_t* dem_qty, const int32_t* key_cost, int32_t* first_node, bool single_only) {
@@ -353,6 +372,7 @@ RowsGroupArgs group_args(nosplan_t* h, int kind, int D, int n_keys, int chunk, c
   g.meta = rp.meta.as<int32_t>();
   g.first_node = first_node;
   g.status = h->d_rowstatus.as<unsigned long long>() + kind;
+  g.status_call = ++h->row_call[kind];
   return g;
 }
 // Groups the demand rows of one scoring call by key and cuts them into work items (rows_group_kernel, which
@@ -361,7 +381,6 @@ int plan_rows(nosplan_t* h, int kind, int D, int n_keys, int chunk, const int32_
               const int32_t* dem_qty, const int32_t* key_cost, int32_t* first_node, cudaStream_t st, int* max_work) {
   int rc = reserve_rows(h, kind, D, n_keys, chunk, st, max_work);
   if (rc) return rc;
-  CU(cudaMemsetAsync(h->d_rowstatus.as<unsigned long long>() + kind, 0xff, 8, st));  // "no bad row"
   rows_group_kernel<<<(D + 255) / 256, 256, 0, st>>>(group_args(h, kind, D, n_keys, chunk, dem_off, dem_key, dem_qty, key_cost, first_node, false));
   CU(cudaGetLastError());
   return NOSPLAN_OK;
@@ -371,36 +390,50 @@ int plan_rows(nosplan_t* h, int kind, int D, int n_keys, int chunk, const int32_
 struct Mig16Launch {
   void (*kern)(MigScore16Args) = nullptr;
   size_t smem = 0;
-  int chunk = 64, tiles = 0;
+  int chunk = 64, tiles = 0, tn = kScoreTN;
 };
-template <int CW>
+// nodes per CTA of the ordered MIG scorer (the CTA always has 512 threads: 512 / tile of them share a node's rows)
+int mig16_tile() {  // measurement knob: NOSPLAN_MIG_TILE=32|64|128
+  static const int t = [] {
+    const char* e = std::getenv("NOSPLAN_MIG_TILE");
+    const int v = e ? std::atoi(e) : kMig16Tile;
+    return (v == 32 || v == 64 || v == 128) ? v : kMig16Tile;
+  }();
+  return t;
+}
+template <int TN, int CW>
 void (*mig16_kernel_of(bool out, bool cnt))(MigScore16Args) {
-  if (out) return mig_score16_kernel<kScoreTN, kScoreDS, CW, true, NOSPLAN_RB, false>;
-  if (cnt) return mig_score16_kernel<kScoreTN, kScoreDS, CW, false, NOSPLAN_RB, true>;
-  return mig_score16_kernel<kScoreTN, kScoreDS, CW, false, NOSPLAN_RB, false>;
+  if (out) return mig_score16_kernel<TN, 512 / TN, CW, true, NOSPLAN_RB, false>;
+  if (cnt) return mig_score16_kernel<TN, 512 / TN, CW, false, NOSPLAN_RB, true>;
+  return mig_score16_kernel<TN, 512 / TN, CW, false, NOSPLAN_RB, false>;
+}
+template <int TN>
+void (*mig16_kernel_cw(int cw, bool out, bool cnt))(MigScore16Args) {
+  switch (cw) {
+    case 1: return mig16_kernel_of<TN, 1>(out, cnt);
+    case 2: return mig16_kernel_of<TN, 2>(out, cnt);
+    case 3: return mig16_kernel_of<TN, 3>(out, cnt);
+    default: return mig16_kernel_of<TN, 4>(out, cnt);
+  }
 }
 int mig16_prepare(nosplan_t* h, int D, bool out, bool cnt, Mig16Launch* L) {
   const int cw = std::max(1, std::min(4, (h->cmax + 3) / 4));
-  switch (cw) {
-    case 1: L->kern = mig16_kernel_of<1>(out, cnt); break;
-    case 2: L->kern = mig16_kernel_of<2>(out, cnt); break;
-    case 3: L->kern = mig16_kernel_of<3>(out, cnt); break;
-    default: L->kern = mig16_kernel_of<4>(out, cnt); break;
-  }
-  L->smem = mig_score16_smem_bytes(h->h_tables.n_models, h->mig_gs, h->cmax, kScoreTN);
+  const int tn = L->tn = mig16_tile();
+  L->kern = tn == 32 ? mig16_kernel_cw<32>(cw, out, cnt) : tn == 64 ? mig16_kernel_cw<64>(cw, out, cnt) : mig16_kernel_cw<128>(cw, out, cnt);
+  L->smem = mig_score16_smem_bytes(h->h_tables.n_models, h->mig_gs, h->cmax, tn);
   if (L->smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MIG scorer tile needs %zu bytes of shared memory", L->smem);
-  L->tiles = (h->mig_n + kScoreTN - 1) / kScoreTN;
+  L->tiles = (h->mig_n + tn - 1) / tn;
   // (the attribute belongs to the function, not to the handle: another handle may have lowered it)
   CU(cudaFuncSetAttribute(L->kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L->smem));
   int& occ = h->occ_cache[0][out ? 1 : 0][cw];
   if (occ == 0) {  // resident CTAs per SM; reset when a snapshot changes the tile size
     int o = 0;
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, L->kern, kScoreTN * kScoreDS, L->smem));
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, L->kern, 512, L->smem));
     occ = std::max(o, 1);
   }
   int gy = 1;
-  // at least 64 rows per work item: on a small shard the tile load would otherwise outweigh the rows
-  pick_chunks(h->sm_count, L->tiles, D, 64, &L->chunk, &gy, occ * score_waves());
+  // at least 64 rows per 128 nodes of a work item: on a small shard the tile load would otherwise outweigh the rows
+  pick_chunks(h->sm_count, L->tiles, D, std::min(min_chunk() * 128 / tn, kRowCap), &L->chunk, &gy, occ * score_waves());
   L->chunk = std::min(L->chunk, kRowCap);
   return NOSPLAN_OK;
 }
@@ -423,7 +456,7 @@ int launch_mig_score16(nosplan_t* h, const MigScoreArgs& a, cudaStream_t st) {
   int max_work = 0;
   rc = plan_rows(h, 0, a.D, h->P, L.chunk, a.dem_off, a.dem_key, a.dem_qty, h->d_profcost.as<int32_t>(), a.first_node, st, &max_work);
   if (rc) return rc;
-  L.kern<<<dim3(max_work, L.tiles), kScoreTN * kScoreDS, L.smem, st>>>(mig16_args(h, a));
+  L.kern<<<dim3(max_work, L.tiles), 512, L.smem, st>>>(mig16_args(h, a));
   CU(cudaGetLastError());
   return NOSPLAN_OK;
 }
@@ -431,7 +464,7 @@ int launch_mig_score16(nosplan_t* h, const MigScoreArgs& a, cudaStream_t st) {
 // the rows-by-key path is taken (and with it the demand rows are validated on the device)
 constexpr int kMaxOrderedRows = 60 * 1000 * 1000;  // rows[] positions (key * D + i) stay 32-bit
 bool mig_ordered(const nosplan_t* h, int D) {
-  return D <= kMaxOrderedRows && h->mig_n > 0 && h->k16ok && (h->cmax + 3) / 4 <= 4 && (h->mig_n + kScoreTN - 1) / kScoreTN <= 65535 &&
+  return D <= kMaxOrderedRows && h->mig_n > 0 && h->k16ok && (h->cmax + 3) / 4 <= 4 && (h->mig_n + 31) / 32 <= 65535 &&
          !wide_keys_forced() && !plain_order_forced();
 }
 bool mps_ordered(const nosplan_t* h, int D) {
@@ -1059,6 +1092,19 @@ cudaEvent_t kev_next(nosplan_t* h, int kind, int which) {
   return e;
 }
 
+template <int TN>
+void (*both_kernel_tn(int cw, bool cnt))(MigScore16Args, MpsScoreArgs, int, int, int) {
+  switch (cw) {
+    case 1: return cnt ? score_both_kernel<TN, 1, true> : score_both_kernel<TN, 1, false>;
+    case 2: return cnt ? score_both_kernel<TN, 2, true> : score_both_kernel<TN, 2, false>;
+    case 3: return cnt ? score_both_kernel<TN, 3, true> : score_both_kernel<TN, 3, false>;
+    default: return cnt ? score_both_kernel<TN, 4, true> : score_both_kernel<TN, 4, false>;
+  }
+}
+void (*both_kernel_of(int tn, int cw, bool cnt))(MigScore16Args, MpsScoreArgs, int, int, int) {
+  return tn == 32 ? both_kernel_tn<32>(cw, cnt) : tn == 64 ? both_kernel_tn<64>(cw, cnt) : both_kernel_tn<128>(cw, cnt);
+}
+
 // x = the handle that owns the exchange (the caller's), h = the handle that owns the snapshots
 int score_pass_enqueue(nosplan_t* h, nosplan_t* x, int Dm, const int32_t* m_off, const int32_t* m_key, const int32_t* m_qty, int Dp,
                        const int32_t* p_off, const int32_t* p_key, const int32_t* p_qty, int32_t* first_node, int flags,
@@ -1119,8 +1165,6 @@ int score_pass_enqueue(nosplan_t* h, nosplan_t* x, int Dm, const int32_t* m_off,
     if (smem_p > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MPS scorer tile needs %zu bytes of shared memory", smem_p);
     if ((rc = reserve_rows(h, 1, Dp, h->S, chunk_p, st, &mw_p))) return rc;
   }
-  CU(h->d_rowstatus.reserve(16));
-  CU(cudaMemsetAsync(h->d_rowstatus.p, 0xff, 16, st));
   RowsGroupArgs g0{}, g1{};
   int nb0 = 0, nb1 = 0;
   uint32_t step = 0;
@@ -1157,18 +1201,31 @@ int score_pass_enqueue(nosplan_t* h, nosplan_t* x, int Dm, const int32_t* m_off,
     push.ticket = xc.done.as<unsigned int>();
     for (int r = 0; r < xc.world; ++r) push.flags[r] = xc.peers.pushed[r];
   }
-  const bool fork = have_m && have_p && !(flags & NOSPLAN_PASS_SERIAL);
-  cudaStream_t st_p = fork ? h->stream2 : st;
-  if (fork) {
-    CU(cudaEventRecord(h->ev_fork, st));
-    CU(cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
+  // both kinds, single-key rows, nobody asked for the kinds one after the other: ONE launch scores both
+  const bool both = have_m && have_p && single && !(flags & NOSPLAN_PASS_SERIAL);
+  cudaStream_t st_p = st;
+  if (both) {
+    MigScore16Args A = mig16_args(h, mig_base_args(h, Dm, m_off, m_key, m_qty, first_m, h->mig_base));
+    MpsScoreArgs a = mps_base_args(h, Dp, p_off, p_key, p_qty, first_p, h->mps_base);
+    A.push = a.push = push;
+    A.counter = count ? h->d_counter.as<unsigned long long>() : nullptr;
+    a.counter = count ? h->d_counter.as<unsigned long long>() + 1 : nullptr;
+    const int cw = std::max(1, std::min(4, (h->cmax + 3) / 4));
+    auto kern = both_kernel_of(L.tn, cw, count);
+    const size_t smem = std::max(L.smem, smem_p);
+    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int n_mig = mw_m * L.tiles, n_mps = mw_p * tiles_p;
+    if (cudaEvent_t e = kev_next(h, 0, 0)) CU(cudaEventRecord(e, st));
+    kern<<<n_mig + n_mps, 512, smem, st>>>(A, a, mw_m, n_mig, mw_p);
+    if (cudaEvent_t e = kev_next(h, 0, 1)) CU(cudaEventRecord(e, st));
+    CU(cudaGetLastError());
   }
-  if (have_m) {
+  if (have_m && !both) {
     MigScore16Args A = mig16_args(h, mig_base_args(h, Dm, m_off, m_key, m_qty, first_m, h->mig_base));
     A.push = push;
     A.counter = count ? h->d_counter.as<unsigned long long>() : nullptr;
     if (cudaEvent_t e = kev_next(h, 0, 0)) CU(cudaEventRecord(e, st));
-    L.kern<<<dim3(mw_m, L.tiles), kScoreTN * kScoreDS, L.smem, st>>>(A);
+    L.kern<<<dim3(mw_m, L.tiles), 512, L.smem, st>>>(A);
     if (cudaEvent_t e = kev_next(h, 0, 1)) CU(cudaEventRecord(e, st));
     if (!single) {  // rows with several keys: the general kernel restricted to their list (leaves at once when there are none)
       MigScoreArgs a = A.base;
@@ -1181,7 +1238,7 @@ int score_pass_enqueue(nosplan_t* h, nosplan_t* x, int Dm, const int32_t* m_off,
       if ((rc = launch_mig_score_kernel(h, a, dim3(L.tiles, gy), smem, st))) return rc;
     }
   }
-  if (have_p) {
+  if (have_p && !both) {
     MpsScoreArgs a = mps_base_args(h, Dp, p_off, p_key, p_qty, first_p, h->mps_base);
     a.push = push;
     a.counter = count ? h->d_counter.as<unsigned long long>() + 1 : nullptr;
@@ -1201,10 +1258,6 @@ int score_pass_enqueue(nosplan_t* h, nosplan_t* x, int Dm, const int32_t* m_off,
     }
   }
   CU(cudaGetLastError());
-  if (fork) {
-    CU(cudaEventRecord(h->ev_join, h->stream2));
-    CU(cudaStreamWaitEvent(st, h->ev_join, 0));
-  }
   if (fused) {
     const int blocks = std::max(1, std::min((Dall / 4 + 255) / 256, h->sm_count));
     xchg_finish_kernel<<<blocks, 256, 0, st>>>(xc.peers, xc.world, xc.rank, xc.stride, step, Dall, first_node, xc.done.as<unsigned int>(),
@@ -1244,10 +1297,10 @@ int nosplan_pass_status(nosplan_t* h) {
   if (rc) return rc;
   CU(cudaDeviceSynchronize());
   if (h->d_rowstatus.p) {
-    unsigned long long st[2] = {~0ull, ~0ull};
+    unsigned long long st[2] = {0, 0};
     CU(cudaMemcpy(st, h->d_rowstatus.p, 16, cudaMemcpyDeviceToHost));
     for (int kind = 0; kind < 2; ++kind)
-      if (st[kind] != ~0ull) {
+      if ((st[kind] = row_status_code(h, kind, st[kind])) != ~0ull) {
         const int sub = (int)(st[kind] % 64);
         return fail(h, sub == 0 || sub == kSubNotSingle ? NOSPLAN_ERR_ARG : NOSPLAN_ERR_RANGE, "%s demand row %llu rejected on the device (%s)",
                     kind ? "MPS" : "MIG", st[kind] / 64,
@@ -1354,7 +1407,8 @@ int nosplan_score_mig(nosplan_t* h, int n_demands, const int32_t* dem_off, const
   if (choice && h->mig_tg) CU(cudaMemcpyAsync(choice, h->d_out[2].p, (size_t)D * h->mig_tg, cudaMemcpyDeviceToHost, st));
   if (dev_check) CU(cudaMemcpyAsync(h->h_status + 4, h->d_rowstatus.p, 8, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
-  if (dev_check && h->h_status[4] != ~0ull) return describe_bad_row(h, h->h_status[4], dem_off, dem_key, dem_qty, h->P);
+  if (dev_check && row_status_code(h, 0, h->h_status[4]) != ~0ull)
+    return describe_bad_row(h, row_status_code(h, 0, h->h_status[4]), dem_off, dem_key, dem_qty, h->P);
   return NOSPLAN_OK;
 }
 
@@ -1396,7 +1450,8 @@ int nosplan_score_mps(nosplan_t* h, int n_demands, const int32_t* dem_off, const
   }
   if (dev_check) CU(cudaMemcpyAsync(h->h_status + 5, h->d_rowstatus.as<unsigned long long>() + 1, 8, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
-  if (dev_check && h->h_status[5] != ~0ull) return describe_bad_row(h, h->h_status[5], dem_off, dem_key, dem_qty, h->S);
+  if (dev_check && row_status_code(h, 1, h->h_status[5]) != ~0ull)
+    return describe_bad_row(h, row_status_code(h, 1, h->h_status[5]), dem_off, dem_key, dem_qty, h->S);
   return NOSPLAN_OK;
 }
 
@@ -2275,14 +2330,9 @@ extern "C" int nosplan_score_snapshot(nosplan_t* h, const nosplan_mig_snapshot_t
   if (mps && (rc = mps_snapshot_finish(c, mps->sizes_gb, mps->mem_gb, mps->used, mps->free_))) return child_fail(rc, "MPS: ");
   c->have_mig = c->have_mps = false;  // the lane keeps no snapshot between calls
   if (Dall > 0 && c->d_rowstatus.p) {
-    if (Dm > 0 && c->h_status[4] != ~0ull) {
-      describe_bad_row(c, c->h_status[4], mig_rows->off, mig_rows->key, mig_rows->qty, c->P);
-      return child_fail(c->h_status[4] % 64 == 0 ? NOSPLAN_ERR_ARG : NOSPLAN_ERR_RANGE, "MIG: ");
-    }
-    if (Dp > 0 && c->h_status[5] != ~0ull) {
-      describe_bad_row(c, c->h_status[5], mps_rows->off, mps_rows->key, mps_rows->qty, c->S);
-      return child_fail(c->h_status[5] % 64 == 0 ? NOSPLAN_ERR_ARG : NOSPLAN_ERR_RANGE, "MPS: ");
-    }
+    const unsigned long long cm = row_status_code(c, 0, c->h_status[4]), cp = row_status_code(c, 1, c->h_status[5]);
+    if (Dm > 0 && cm != ~0ull) return child_fail(describe_bad_row(c, cm, mig_rows->off, mig_rows->key, mig_rows->qty, c->P), "MIG: ");
+    if (Dp > 0 && cp != ~0ull) return child_fail(describe_bad_row(c, cp, mps_rows->off, mps_rows->key, mps_rows->qty, c->S), "MPS: ");
   }
   if ((int)c->h_status[6] != 0) return fail(h, NOSPLAN_ERR_CUDA, "exchange: rank %d never signalled a step (waited 2 s)", (int)c->h_status[6] - 1);
   const char* pin = static_cast<const char*>(c->h_pin);

@@ -172,7 +172,7 @@ constexpr int kRowBuckets = 33;  // up to 32 keys + "any other row"
 constexpr int kNoRow = 63;
 
 // The rows are validated here as well (the host does not walk them): a row that breaks a limit of the ABI
-// joins no bucket, so no scorer ever sees it, and the lowest failing code row * 64 + sub lands in *status
+// joins no bucket, so no scorer ever sees it, and the lowest failing code row * 64 + sub of the call lands in *status
 // (sub 0: dem_off descending, 1: too many keys, 2 + 3j / 3 + 3j / 4 + 3j: key j out of range / not
 // ascending / quantity out of range); the host turns the code back into its message.
 // state[0 .. kRowBuckets) = cursors, state[kRowBuckets] = ticket; all zero on entry and on exit
@@ -188,7 +188,8 @@ struct RowsGroupArgs {
   int32_t* work;
   int32_t* meta;
   int32_t* first_node;  // put to rest (-1) here; null = leave it alone
-  unsigned long long* status;
+  unsigned long long* status;  // highest (call number << 32 | ~code) seen: never reset, the caller compares call numbers
+  uint32_t status_call;
   // sharded pass: first_node is the rank's own half of the exchange buffer, which may only be overwritten once
   // every rank has read what it held two steps ago (nosplan_xchg.cuh); wait_world == 0: nothing to wait for
   const uint32_t* wait_read;
@@ -227,7 +228,8 @@ __device__ __forceinline__ void rows_group_body(const RowsGroupArgs& g, int bloc
       }
       if (sub < 0 && g.single_only && k != 1) sub = kSubNotSingle;
     }
-    if (sub >= 0) atomicMin(g.status, (unsigned long long)d * 64ull + (unsigned long long)sub);
+    if (sub >= 0)  // the lowest code of this call wins: codes are stored inverted under the call number
+      atomicMax(g.status, ((unsigned long long)g.status_call << 32) | (unsigned long long)(0xffffffffu - ((uint32_t)d * 64u + (uint32_t)sub)));
     else b = k == 1 ? key0 : P;
   }
   const uint32_t peers = __match_any_sync(0xffffffffu, b);  // one atomic per bucket per warp
@@ -325,10 +327,12 @@ __device__ __forceinline__ uint2 lds_v2(uint32_t saddr) {
 // RB: demand rows a thread scores per pass over its node's GPUs
 // CNT: measurement instantiation — counts the (row, node, GPU, candidate) evaluations that really execute
 //      (a (row, GPU) pair that enters the candidate core counts the model's candidates), see bench.py
-template <int TN, int DS, int CW, bool OUT, int RB, bool CNT = false>
-__global__ void __launch_bounds__(TN * DS, RB > 2 ? 2 : 3) mig_score16_kernel(const MigScore16Args A) {
+// bx, by: the CTA's place in the (work item, tile) grid (the kernel's blockIdx, or derived from a linear index
+// when both kinds share one launch, score_both_kernel)
+template <int TN, int DS, int CW, bool OUT, int RB, bool CNT>
+__device__ __forceinline__ void mig_score16_body(const MigScore16Args& A, const int bx, const int by) {
   const MigScoreArgs& a = A.base;
-  if ((int)blockIdx.x >= A.meta[0]) {  // the grid is sized for the worst split of the rows
+  if (bx >= A.meta[0]) {  // the grid is sized for the worst split of the rows
     push_finish(A.push);
     return;
   }
@@ -350,12 +354,12 @@ __global__ void __launch_bounds__(TN * DS, RB > 2 ? 2 : 3) mig_score16_kernel(co
 
   // grid: x = work item (heaviest profile first), y = tile of perm[p] (heaviest nodes first), so CTAs are
   // handed out roughly longest-first
-  const int p = A.work[3 * blockIdx.x + 0];
-  const int r0 = A.work[3 * blockIdx.x + 1];
-  const int len = A.work[3 * blockIdx.x + 2];
+  const int p = A.work[3 * bx + 0];
+  const int r0 = A.work[3 * bx + 1];
+  const int len = A.work[3 * bx + 2];
   const int tid = threadIdx.x % TN;
   const int dsub = threadIdx.x / TN;
-  const int pos = blockIdx.y * TN + tid;
+  const int pos = by * TN + tid;
   const int n = pos < a.npad ? A.perm[(size_t)p * a.npad + pos] : a.N;  // positions past the nodes: nothing to do
   const int cnt = (n < a.N) ? a.s_cnt[n] : 0;
   const int g0 = (n < a.N) ? a.gpu_off[n] : 0;
@@ -481,6 +485,11 @@ __global__ void __launch_bounds__(TN * DS, RB > 2 ? 2 : 3) mig_score16_kernel(co
   }
 }
 
+template <int TN, int DS, int CW, bool OUT, int RB, bool CNT = false>
+__global__ void __launch_bounds__(TN * DS, RB > 2 ? 2 : 3) mig_score16_kernel(const MigScore16Args A) {
+  mig_score16_body<TN, DS, CW, OUT, RB, CNT>(A, blockIdx.x, blockIdx.y);
+}
+
 // The winner's per-GPU choices (nosplan_score_mig's first_choice): one thread per row re-walks the row's
 // first node with the snapshot-time rank table; rows with several keys use the general walker.
 __global__ void mig_finalize16_kernel(const MigTables* __restrict__ T, const uint32_t* __restrict__ rankg,
@@ -548,9 +557,9 @@ __host__ __device__ inline size_t mps_score1_smem_bytes(int gs, int S, int tn) {
   return (size_t)gs * (3 + nw) * tn * 4 + (size_t)kRowCap * 12;
 }
 
-template <int TN, int DS, bool OUT, bool CNT = false>
-__global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreArgs a) {
-  if ((int)blockIdx.x >= a.meta[0]) {
+template <int TN, int DS, bool OUT, bool CNT>
+__device__ __forceinline__ void mps_score1_body(const MpsScoreArgs& a, const int bx, const int by) {
+  if (bx >= a.meta[0]) {
     push_finish(a.push);
     return;
   }
@@ -562,12 +571,12 @@ __global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreAr
   int32_t* const s_row = reinterpret_cast<int32_t*>(smem + (size_t)a.gs * slot_stride);
   int32_t* const s_qty = s_row + kRowCap;
   int32_t* const s_first = s_qty + kRowCap;
-  const int sid = a.work[3 * blockIdx.x];
-  const int32_t* rl = a.rows + a.work[3 * blockIdx.x + 1];
-  const int len = a.work[3 * blockIdx.x + 2];
+  const int sid = a.work[3 * bx];
+  const int32_t* rl = a.rows + a.work[3 * bx + 1];
+  const int len = a.work[3 * bx + 2];
   const int tid = threadIdx.x % TN;
   const int dsub = threadIdx.x / TN;
-  const int pos = blockIdx.y * TN + tid;
+  const int pos = by * TN + tid;
   const int n = pos < a.N ? a.perm[(size_t)sid * a.N + pos] : a.N;
   const bool live = n < a.N && a.valid[n];
   const int g0 = n < a.N ? a.gpu_off[n] : 0;
@@ -659,6 +668,22 @@ __global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreAr
     executed = __reduce_add_sync(0xffffffffu, executed);
     if ((threadIdx.x & 31) == 0 && executed) atomicAdd(a.counter, (unsigned long long)executed);
   }
+}
+
+template <int TN, int DS, bool OUT, bool CNT = false>
+__global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreArgs a) {
+  mps_score1_body<TN, DS, OUT, CNT>(a, blockIdx.x, blockIdx.y);
+}
+
+// Both kinds of a scoring pass in ONE launch (nosplan_score_pass_dev): the first n_mig CTAs are the MIG scorer's
+// (work item, tile) grid in its own order (x fastest: heaviest profile first, heaviest nodes first), the rest the MPS
+// scorer's.  One pool of CTAs drains over the SMs, so a small shard fills the GPU without two streams and the
+// events that fork and join them.  TNM: nodes per MIG CTA; the MPS part keeps 128 nodes x 4 threads.
+template <int TNM, int CW, bool CNT>
+__global__ void __launch_bounds__(512, 3) score_both_kernel(const MigScore16Args A, const MpsScoreArgs a, int mig_x, int n_mig, int mps_x) {
+  const int i = blockIdx.x;
+  if (i < n_mig) mig_score16_body<TNM, 512 / TNM, CW, false, 2, CNT>(A, i % mig_x, i / mig_x);
+  else mps_score1_body<128, 4, false, CNT>(a, (i - n_mig) % mps_x, (i - n_mig) / mps_x);
 }
 
 }  // namespace nsp
