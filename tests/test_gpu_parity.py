@@ -325,3 +325,59 @@ def test_full_size_cfg5_properties(pkg, planner):
     both = planner.score_snapshot(cfg["mig"], c32(off, key, qty), cfg["sizes"], cfg["mps"], c32(poff, pkey, pqty))
     assert np.array_equal(both["mig_first_node"], r["first_node"]) and np.array_equal(both["mig_first_choice"], r["first_choice"])
     assert np.array_equal(both["mps_first_node"], rp["first_node"])
+
+
+# ---- reference behaviour (gate on) when the gate does not stop everything ------------------------------------------
+def _without_profiles(cfg, cols):
+    snap = {k: (v.copy() if isinstance(v, np.ndarray) else v) for k, v in cfg["mig"].items()}
+    for c in cols:
+        snap["used"][:, c] = 0
+        snap["free"][:, c] = 0
+    snap["used_mask"] = np.zeros_like(snap["used_mask"])
+    snap["free_mask"] = np.zeros_like(snap["free_mask"])
+    for k in range(snap["used"].shape[1]):
+        snap["used_mask"] |= (snap["used"][:, k] != 0).astype(np.uint32) << np.uint32(k)
+        snap["free_mask"] |= (snap["free"][:, k] != 0).astype(np.uint32) << np.uint32(k)
+    out = dict(cfg)
+    out["mig"] = snap
+    return out
+
+
+@pytest.mark.parametrize("sched", [True, False])
+@pytest.mark.parametrize("case", ["one_absent", "three_absent", "unreachable", "mps_absent"])
+def test_plan_gate_on_with_absent_profiles(pkg, planner, case, sched):
+    """Pods whose profile is absent from the whole cluster fall through the gate to tryRepartition
+    (mig_controller.go:83-98); everything else stays with the per-profile chains.  One (profile, quantity) per pod."""
+    cfg = pkg.synth.make_config(5, 512, 6000)
+    names = cfg["names"]
+    pods = {k: v.copy() for k, v in cfg["pods"].items()}
+    if case == "one_absent":
+        cfg = _without_profiles(cfg, [names.index("2g.20gb")])
+    elif case == "three_absent":
+        cfg = _without_profiles(cfg, [names.index(x) for x in ("1g.10gb", "3g.40gb", "7g.79gb")])
+    elif case == "unreachable":
+        # a profile no H100 geometry holds: absent, and no node can ever provide it (every such pod: no gate, no node)
+        cfg = _without_profiles(cfg, [names.index("4g.40gb")])
+        mig_pods = np.nonzero(pods["kind"] == 0)[0]
+        pods["key"][pods["off"][mig_pods[::7]]] = names.index("1g.5gb")
+    else:
+        mps = {k: (v.copy() if isinstance(v, np.ndarray) else v) for k, v in cfg["mps"].items()}
+        mps["used"][:, 2] = 0  # no 20 GB slice anywhere (capacity grows accordingly)
+        mps["free"][:, 2] = 0
+        mps["used_mask"] = pkg.synth._mask_of(mps["used"])
+        mps["free_mask"] = pkg.synth._mask_of(mps["free"])
+        cfg = dict(cfg)
+        cfg["mps"] = mps
+    o = _load(planner, cfg)
+    exp = _check_plan(pkg, planner, o, cfg, pods, True, sched)
+    assert (exp["gate_hit"] == 0).any() and (exp["gate_hit"] == 1).any()
+    if case != "unreachable":
+        assert (exp["repart_node"] >= 0).any()
+
+
+def test_plan_gate_on_absent_profile_full_size(pkg, planner):
+    cfg = pkg.synth.make_config(5)
+    cfg = _without_profiles(cfg, [cfg["names"].index("2g.20gb"), cfg["names"].index("3g.40gb")])
+    o = _load(planner, cfg)
+    exp = _check_plan(pkg, planner, o, cfg, cfg["pods"], True, True)
+    assert (exp["repart_node"] >= 0).sum() >= 1 and (exp["gate_hit"] == 0).any()

@@ -36,3 +36,13 @@ for r in range(reps + 3):
 for n, _ in calls:
     print(f"{n:18s} p50 {np.median(acc[n]):.3f} ms  min {min(acc[n]):.3f}")
 print(f"{'step':18s} p50 {np.median(tot):.3f} ms  min {min(tot):.3f}")
+
+# the one-call form (nosplan_score_snapshot), with NOSPLAN_TRACE=1 its own phase breakdown goes to stderr
+c32 = lambda *xs: tuple(np.ascontiguousarray(x, np.int32) for x in xs)
+one = []
+for r in range(reps + 3):
+    t0 = time.perf_counter()
+    p.score_snapshot(mig, (mo, mk, mq), cfg["sizes"], mps, (po, pk, pq))
+    if r >= 3:
+        one.append((time.perf_counter() - t0) * 1e3)
+print(f"{'score_snapshot':18s} p50 {np.median(one):.3f} ms  min {min(one):.3f}")

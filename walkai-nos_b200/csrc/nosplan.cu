@@ -99,6 +99,8 @@ struct nosplan {
   uint32_t row_call[2] = {0, 0};           // number of the kind's last grouping call
   unsigned long long* h_status = nullptr;  // pinned: [0..1] MIG pack status, [2..3] MPS pack status, [4..5] row status, [6] exchange
   cudaEvent_t status_ev = nullptr, status_ev2 = nullptr;
+  int32_t* h_limit = nullptr;              // pinned [2]: per kind, the first pod the chains could not take (nosplan_plan)
+  int32_t (*h_range)[2] = nullptr;         // pinned [2][2]: per kind, the range handed to the next chain launch
   void* h_pin = nullptr;                   // pinned staging for results (nosplan_score_snapshot)
   size_t h_pin_cap = 0;
 
@@ -629,7 +631,7 @@ int nosplan_create(int device, nosplan_t** out) {
     return NOSPLAN_ERR_CUDA;
   }
   cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device);
-  if (cudaHostAlloc(reinterpret_cast<void**>(&h->h_status), 64, cudaHostAllocDefault) != cudaSuccess ||
+  if (cudaHostAlloc(reinterpret_cast<void**>(&h->h_status), 128, cudaHostAllocDefault) != cudaSuccess ||
       cudaEventCreateWithFlags(&h->status_ev, cudaEventDisableTiming) != cudaSuccess ||
       cudaEventCreateWithFlags(&h->status_ev2, cudaEventDisableTiming) != cudaSuccess ||
       cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
@@ -637,6 +639,8 @@ int nosplan_create(int device, nosplan_t** out) {
     nosplan_destroy(h);
     return NOSPLAN_ERR_CUDA;
   }
+  h->h_limit = reinterpret_cast<int32_t*>(h->h_status + 8);              // bytes 64..71
+  h->h_range = reinterpret_cast<int32_t(*)[2]>(h->h_status + 10);       // bytes 80..95
   *out = h;
   return NOSPLAN_OK;
 }
@@ -1455,6 +1459,46 @@ int nosplan_score_mps(nosplan_t* h, int n_demands, const int32_t* dem_off, const
   return NOSPLAN_OK;
 }
 
+}  // extern "C"
+
+namespace {
+constexpr int kMaxHybridRounds = 64;
+// one kind's share of a nosplan_plan call
+struct PlanKind {
+  int kd = 0, M = 0, maxq = 1;
+  bool hybrid = false;
+  cudaStream_t st = nullptr;
+  PlanArgs pa;
+  ChainArgs ca;
+  std::function<int(int, int, int32_t*, int32_t*)> run_seq;
+  // the chains over the pods from `first` up to the next pod the gate does not stop; that pod's index comes back in
+  // h->h_limit[kd] (pinned) once the stream has drained
+  int chains_from(nosplan_t* h, int first) {
+    const int32_t range[2] = {first, M};
+    h->h_range[kd][0] = range[0];
+    h->h_range[kd][1] = range[1];
+    CU(cudaMemcpyAsync(ca.limit_out, h->h_range[kd], sizeof(range), cudaMemcpyHostToDevice, st));
+    if (ca.sched) {
+      if (kd == 0) plan_winmax_kernel<false><<<ca.n_win, 32, 0, st>>>(ca);
+      else plan_winmax_kernel<true><<<ca.n_win, 32, 0, st>>>(ca);
+    }
+    plan_find_miss_kernel<<<1, 1024, 0, st>>>(ca);
+    if (maxq <= 2) {
+      if (kd == 0) plan_chain_kernel<false, 2><<<ca.n_chains, 32, 0, st>>>(ca);
+      else plan_chain_kernel<true, 2><<<ca.n_chains, 32, 0, st>>>(ca);
+    } else {
+      if (kd == 0) plan_chain_kernel<false, kChainQ><<<ca.n_chains, 32, 0, st>>>(ca);
+      else plan_chain_kernel<true, kChainQ><<<ca.n_chains, 32, 0, st>>>(ca);
+    }
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(&h->h_limit[kd], ca.limit_out + 1, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    return NOSPLAN_OK;
+  }
+};
+}  // namespace
+
+extern "C" {
+
 int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* dem_off, const int32_t* dem_key,
                  const int32_t* dem_qty, int flags, uint8_t* gate_hit, int32_t* repart_node, int32_t* sched_node,
                  int32_t* sched_gpu) {
@@ -1536,6 +1580,7 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
   std::vector<uint8_t> o_gate[2];
   std::vector<int32_t> o_rep[2], o_node[2], o_gpu[2];
   const int32_t* out_ptr[2] = {nullptr, nullptr};
+  PlanKind pk[2];
   for (int kd = 0; kd < 2; ++kd) {
     Side& s = side[kd];
     const int M = (int)s.pod_idx.size();
@@ -1595,7 +1640,60 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
     a.sched_gpu = a.sched_node + M;
     a.gate_hit = reinterpret_cast<uint8_t*>(a.sched_gpu + M);
     const bool want_chains = s.chains_ok && (flags & NOSPLAN_PLAN_GATE) && a.tg > 0;
+    PlanKind& K = pk[kd];
+    K.M = M;
+    K.st = st;
+    K.pa = a;
+    K.kd = kd;
+    // the general path: derive the masks/bitmaps from the working state, then one sequencer warp over pods
+    // [first, first + count) of the kind
+    K.run_seq = [h, kd, b, &K](int first, int count, int32_t* present_out, int32_t* dead) -> int {
+      const PlanArgs& a = K.pa;
+      cudaStream_t st = K.st;
+      SeqArgs q;
+      std::memset(&q, 0, sizeof(q));
+      q.M = count; q.pod_sig = a.pod_sig + first; q.D = a.D; q.dem_off = a.dem_off; q.dem_key = a.dem_key; q.dem_qty = a.dem_qty;
+      q.flags = a.flags; q.N = a.N; q.tg = a.tg; q.n_keys = a.n_keys; q.gpu_off = a.gpu_off; q.valid = a.valid;
+      q.gpu_node = kd ? h->d_mps_gnode.as<int32_t>() : h->d_mig_gnode.as<int32_t>();
+      q.T = a.T; q.m_used = a.m_used; q.m_free = a.m_free; q.m_model = a.m_model;
+      q.sizes = a.sizes; q.p_gpu = a.p_gpu; q.p_used_lo = a.p_used_lo; q.p_used_hi = a.p_used_hi;
+      q.nw = (a.N + 31) / 32 + 1;
+      q.gw = (a.tg + 31) / 32 + 1;
+      const size_t n_gm = (size_t)std::max(a.tg, 1), n_nb = (size_t)a.n_keys * q.nw, n_fb = (size_t)(a.n_keys + 1) * q.gw;
+      const size_t words = 2 * n_gm + 2 * n_nb + n_fb + kMaxSizes;
+      CU(b[13].reserve(words * 4));
+      q.gm = b[13].as<uint32_t>();
+      q.f1 = q.gm + n_gm;
+      q.nbt = q.f1 + n_gm;
+      q.nu1t = q.nbt + n_nb;
+      q.fbt = q.nu1t + n_nb;
+      q.present = reinterpret_cast<int32_t*>(q.fbt + n_fb);
+      q.gate_hit = a.gate_hit + first; q.repart_node = a.repart_node + first; q.sched_node = a.sched_node + first;
+      q.sched_gpu = a.sched_gpu + first;
+      q.present_out = present_out;
+      q.dead = dead;
+      CU(cudaMemsetAsync(q.nbt, 0, (2 * n_nb + n_fb + kMaxSizes) * 4, st));
+      const size_t smem = (2 * n_nb + n_fb) * 4;
+      q.use_smem = smem <= 160 * 1024 ? 1 : 0;
+      if (a.tg > 0) {
+        if (kd == 0) seq_prep_gpu_kernel<false><<<(a.tg + 127) / 128, 128, 0, st>>>(q);
+        else seq_prep_gpu_kernel<true><<<(a.tg + 127) / 128, 128, 0, st>>>(q);
+      }
+      if (a.N > 0) seq_prep_node_kernel<<<(a.N + 127) / 128, 128, 0, st>>>(q);
+      if (kd == 0) {
+        CU(cudaFuncSetAttribute(plan_seq_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        plan_seq_kernel<false><<<1, kSeqThreads, q.use_smem ? smem : 0, st>>>(q);
+      } else {
+        CU(cudaFuncSetAttribute(plan_seq_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        plan_seq_kernel<true><<<1, kSeqThreads, q.use_smem ? smem : 0, st>>>(q);
+      }
+      CU(cudaGetLastError());
+      return NOSPLAN_OK;
+    };
     if (want_chains) {
+      // Reference behaviour (gate on), every pod one (profile, quantity): the chains own every pod the gate stops;
+      // a pod whose profile is absent ends the chains' range, goes through tryRepartition on the sequencer (one pod),
+      // and the chains go on behind it (the host loop below, one round per such pod).
       // pods grouped by requested key, planner order kept inside a group
       std::vector<int32_t> ckey, coff{0}, cpod(M), cq(M);
       std::vector<int> cnt(a.n_keys, 0), chain_of(a.n_keys, -1);
@@ -1622,21 +1720,28 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
         cpod[at] = j;
         cq[at] = row_qty[r];
       }
-      ChainArgs ca;
+      ChainArgs& ca = K.ca;
       std::memset(&ca, 0, sizeof(ca));
       ca.n_chains = (int)ckey.size();
       if ((rc = upload(h, b[8], ckey.data(), sizeof(int32_t) * ckey.size(), st))) return rc;
       if ((rc = upload(h, b[9], coff.data(), sizeof(int32_t) * coff.size(), st))) return rc;
       if ((rc = upload(h, b[10], cpod.data(), sizeof(int32_t) * M, st))) return rc;
       if ((rc = upload(h, b[11], cq.data(), sizeof(int32_t) * M, st))) return rc;
-      CU(b[12].reserve(sizeof(int32_t) * (kMaxSizes + 1)));
-      CU(cudaMemsetAsync(b[12].p, 0, sizeof(int32_t) * (kMaxSizes + 1), st));
+      // control block: present[kMaxSizes] | dead[kMaxSizes] | range[2]
+      CU(b[12].reserve(sizeof(int32_t) * (2 * kMaxSizes + 2)));
+      CU(cudaMemsetAsync(b[12].p, 0, sizeof(int32_t) * (2 * kMaxSizes + 2), st));
       ca.chain_key = b[8].as<int32_t>();
       ca.chain_off = b[9].as<int32_t>();
       ca.chain_pod = b[10].as<int32_t>();
       ca.chain_q = b[11].as<int32_t>();
       ca.present = b[12].as<int32_t>();
-      ca.eligible = ca.present + kMaxSizes;
+      ca.dead = ca.present + kMaxSizes;
+      ca.limit_out = ca.present + 2 * kMaxSizes;
+      ca.range = ca.limit_out;
+      ca.pod_sig = a.pod_sig;
+      ca.dem_off = a.dem_off;
+      ca.dem_key = a.dem_key;
+      ca.M = M;
       ca.N = a.N;
       ca.tg = a.tg;
       ca.n_keys = a.n_keys;
@@ -1654,67 +1759,38 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
       ca.repart_node = a.repart_node;
       ca.sched_node = a.sched_node;
       ca.sched_gpu = a.sched_gpu;
-      a.skip_if = ca.eligible;
       ca.n_win = (a.tg + 31) / 32;
       CU(b[14].reserve((size_t)a.n_keys * ca.n_win));
       ca.winmax = b[14].as<uint8_t>();
+      K.maxq = 1;
+      for (int q : s.qty) K.maxq = std::max(K.maxq, q);
       if (kd == 0) plan_presence_kernel<false><<<(a.tg + 255) / 256, 256, 0, st>>>(ca);
       else plan_presence_kernel<true><<<(a.tg + 255) / 256, 256, 0, st>>>(ca);
-      if (ca.sched) {
-        if (kd == 0) plan_winmax_kernel<false><<<ca.n_win, 32, 0, st>>>(ca);
-        else plan_winmax_kernel<true><<<ca.n_win, 32, 0, st>>>(ca);
-      }
-      plan_eligible_kernel<<<1, 32, 0, st>>>(ca);
-      int maxq = 1;
-      for (int q : s.qty) maxq = std::max(maxq, q);
-      if (maxq <= 2) {
-        if (kd == 0) plan_chain_kernel<false, 2><<<ca.n_chains, 32, 0, st>>>(ca);
-        else plan_chain_kernel<true, 2><<<ca.n_chains, 32, 0, st>>>(ca);
-      } else {
-        if (kd == 0) plan_chain_kernel<false, kChainQ><<<ca.n_chains, 32, 0, st>>>(ca);
-        else plan_chain_kernel<true, kChainQ><<<ca.n_chains, 32, 0, st>>>(ca);
-      }
-    }
-    {
-      // general path: derive the masks/bitmaps from the working state, then one sequencer warp
-      SeqArgs q;
-      std::memset(&q, 0, sizeof(q));
-      q.M = a.M; q.pod_sig = a.pod_sig; q.D = a.D; q.dem_off = a.dem_off; q.dem_key = a.dem_key; q.dem_qty = a.dem_qty;
-      q.flags = a.flags; q.N = a.N; q.tg = a.tg; q.n_keys = a.n_keys; q.gpu_off = a.gpu_off; q.valid = a.valid;
-      q.gpu_node = kd ? h->d_mps_gnode.as<int32_t>() : h->d_mig_gnode.as<int32_t>();
-      q.T = a.T; q.m_used = a.m_used; q.m_free = a.m_free; q.m_model = a.m_model;
-      q.sizes = a.sizes; q.p_gpu = a.p_gpu; q.p_used_lo = a.p_used_lo; q.p_used_hi = a.p_used_hi;
-      q.nw = (a.N + 31) / 32 + 1;
-      q.gw = (a.tg + 31) / 32 + 1;
-      const size_t n_gm = (size_t)std::max(a.tg, 1), n_nb = (size_t)a.n_keys * q.nw, n_fb = (size_t)(a.n_keys + 1) * q.gw;
-      const size_t words = 2 * n_gm + 2 * n_nb + n_fb + kMaxSizes;
-      CU(b[13].reserve(words * 4));
-      q.gm = b[13].as<uint32_t>();
-      q.f1 = q.gm + n_gm;
-      q.nbt = q.f1 + n_gm;
-      q.nu1t = q.nbt + n_nb;
-      q.fbt = q.nu1t + n_nb;
-      q.present = reinterpret_cast<int32_t*>(q.fbt + n_fb);
-      q.gate_hit = a.gate_hit; q.repart_node = a.repart_node; q.sched_node = a.sched_node; q.sched_gpu = a.sched_gpu;
-      q.skip_if = a.skip_if;
-      CU(cudaMemsetAsync(q.nbt, 0, (2 * n_nb + n_fb + kMaxSizes) * 4, st));
-      const size_t smem = (2 * n_nb + n_fb) * 4;
-      q.use_smem = smem <= 160 * 1024 ? 1 : 0;
-      if (a.tg > 0) {
-        if (kd == 0) seq_prep_gpu_kernel<false><<<(a.tg + 127) / 128, 128, 0, st>>>(q);
-        else seq_prep_gpu_kernel<true><<<(a.tg + 127) / 128, 128, 0, st>>>(q);
-      }
-      if (a.N > 0) seq_prep_node_kernel<<<(a.N + 127) / 128, 128, 0, st>>>(q);
-      if (kd == 0) {
-        CU(cudaFuncSetAttribute(plan_seq_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-        plan_seq_kernel<false><<<1, kSeqThreads, q.use_smem ? smem : 0, st>>>(q);
-      } else {
-        CU(cudaFuncSetAttribute(plan_seq_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-        plan_seq_kernel<true><<<1, kSeqThreads, q.use_smem ? smem : 0, st>>>(q);
-      }
+      K.hybrid = true;
+      if ((rc = K.chains_from(h, 0))) return rc;
+    } else {
+      if ((rc = K.run_seq(0, M, nullptr, nullptr))) return rc;
     }
     CU(cudaGetLastError());
     out_ptr[kd] = a.repart_node;
+  }
+  // Hybrid kinds: one round per pod that the gate does not stop.  Both kinds' first rounds are in flight by now; the
+  // later rounds (rare: a profile has to be absent from the whole cluster) run kind after kind.
+  for (int kd = 0; kd < 2; ++kd) {
+    PlanKind& K = pk[kd];
+    if (!K.hybrid) continue;
+    int rounds = 0;
+    for (;;) {
+      CU(cudaStreamSynchronize(K.st));
+      const int pos = h->h_limit[kd];
+      if (pos >= K.M) break;
+      if (++rounds > kMaxHybridRounds) {  // many absent profiles: the sequencer takes the rest in one go
+        if ((rc = K.run_seq(pos, K.M - pos, nullptr, nullptr))) return rc;
+        break;
+      }
+      if ((rc = K.run_seq(pos, 1, K.ca.present, const_cast<int32_t*>(K.ca.dead)))) return rc;
+      if ((rc = K.chains_from(h, pos + 1))) return rc;
+    }
   }
   // results back only after both kinds are in flight: a device-to-host copy into pageable memory blocks
   // the host until its stream drains, which would serialise the MIG and MPS chains
@@ -2257,6 +2333,16 @@ extern "C" int nosplan_score_snapshot(nosplan_t* h, const nosplan_mig_snapshot_t
   if (mps && (rc = check_demands_head(c, Dp, mps_rows->off, mps_rows->key, mps_rows->qty))) return child_fail(rc, "MPS: ");
   cudaStream_t sm = c->stream, sp = c->stream2;
   c->have_mig = c->have_mps = false;
+  // NOSPLAN_TRACE=1: where a pass spends its time (host clock + CUDA events on the MIG stream)
+  const bool trace = trace_on();
+  static cudaEvent_t tev[5] = {};
+  const auto t_begin = std::chrono::steady_clock::now();
+  auto mark = [&](int i) {
+    if (!trace) return;
+    if (!tev[i]) cudaEventCreate(&tev[i]);
+    cudaEventRecord(tev[i], sm);
+  };
+  mark(0);
   if (mig) {
     if ((rc = mig_snapshot_enqueue(c, mig->n_nodes, mig->gpu_off, mig->valid, mig->model, mig->used, mig->free_, sm))) return child_fail(rc, "MIG: ");
     if (Dm > 0) {
@@ -2280,6 +2366,7 @@ extern "C" int nosplan_score_snapshot(nosplan_t* h, const nosplan_mig_snapshot_t
     if (cudaEventRecord(c->ev_join, sp) != cudaSuccess || cudaStreamWaitEvent(sm, c->ev_join, 0) != cudaSuccess)
       return fail(h, NOSPLAN_ERR_CUDA, "stream join failed");
   }
+  mark(1);
   const int gs = mig ? c->mig_gs : 1;
   const size_t out_bytes = sizeof(int32_t) * (size_t)std::max(Dall, 1) + (mig_first_choice ? (size_t)Dm * gs : 0);
   if ((rc = pin_reserve(c, out_bytes))) return child_fail(rc, "");
@@ -2296,6 +2383,7 @@ extern "C" int nosplan_score_snapshot(nosplan_t* h, const nosplan_mig_snapshot_t
                             flags, sm);
     c->have_mig = c->have_mps = false;
     if (rc) return child_fail(rc, "");
+    mark(2);
     if (mig_first_choice && Dm > 0) {
       if (cudaSuccess != c->d_out[3].reserve((size_t)Dm * gs)) return fail(h, NOSPLAN_ERR_CUDA, "out of device memory");
       if (mig_ordered(c, Dm)) {
@@ -2323,8 +2411,11 @@ extern "C" int nosplan_score_snapshot(nosplan_t* h, const nosplan_mig_snapshot_t
   c->h_status[6] = 0;
   if (h->xch.open && cudaMemcpyAsync(c->h_status + 6, h->xch.err.p, sizeof(int), cudaMemcpyDeviceToHost, sm) != cudaSuccess)
     return fail(h, NOSPLAN_ERR_CUDA, "copy back failed");
+  mark(3);
+  const auto t_enq = std::chrono::steady_clock::now();
   if (cudaStreamSynchronize(sm) != cudaSuccess || cudaStreamSynchronize(sp) != cudaSuccess)
     return fail(h, NOSPLAN_ERR_CUDA, "scoring pass failed: %s", cudaGetErrorString(cudaGetLastError()));
+  const auto t_sync = std::chrono::steady_clock::now();
   // the device's verdicts
   if (mig && (rc = mig_snapshot_finish(c, mig->model, mig->used, mig->free_))) return child_fail(rc, "MIG: ");
   if (mps && (rc = mps_snapshot_finish(c, mps->sizes_gb, mps->mem_gb, mps->used, mps->free_))) return child_fail(rc, "MPS: ");
@@ -2340,6 +2431,16 @@ extern "C" int nosplan_score_snapshot(nosplan_t* h, const nosplan_mig_snapshot_t
   if (Dp > 0) std::memcpy(mps_first_node, pin + sizeof(int32_t) * (size_t)Dm, sizeof(int32_t) * (size_t)Dp);
   if (mig_first_choice && Dm > 0) std::memcpy(mig_first_choice, pin + sizeof(int32_t) * (size_t)Dall, (size_t)Dm * gs);
   if (n_evals) *n_evals = (int64_t)Dm * c->mig_evals + (int64_t)Dp * c->mps_evals;
+  if (trace && Dall > 0) {
+    auto us = [](auto a, auto b) { return std::chrono::duration<double, std::micro>(b - a).count(); };
+    float g01 = 0, g12 = 0, g23 = 0;
+    cudaEventElapsedTime(&g01, tev[0], tev[1]);
+    cudaEventElapsedTime(&g12, tev[1], tev[2]);
+    cudaEventElapsedTime(&g23, tev[2], tev[3]);
+    std::fprintf(stderr, "nosplan_score_snapshot: host enqueue %.0f us, wait %.0f us, copy out %.0f us | device: uploads + packing %.0f us, "
+                 "grouping + scoring + exchange %.0f us, choices + copy back %.0f us\n", us(t_begin, t_enq), us(t_enq, t_sync),
+                 us(t_sync, std::chrono::steady_clock::now()), g01 * 1e3, g12 * 1e3, g23 * 1e3);
+  }
   return NOSPLAN_OK;
 }
 

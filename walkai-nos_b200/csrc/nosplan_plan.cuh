@@ -83,6 +83,18 @@ struct ChainArgs {
   uint8_t* winmax;            // [n_keys][n_win] largest free count of the key among the 32 GPUs of a window
   int n_win;                  //                 (plan_winmax_kernel; an upper bound while the chains run)
   int sched;                  // 0: gate only (NOSPLAN_PLAN_SCHED off): every pod is stopped by the gate, nothing else
+  // The chains only own the pods the gate stops.  range[0..1] (device) = the kind-local pod indices [lo, hi) this
+  // launch may place: hi is the first pod whose profile is absent (plan_find_miss_kernel); that pod goes through
+  // tryRepartition on the sequencer, after which the chains continue behind it.  dead[key] != 0: the profile is
+  // absent and its last tryRepartition found no node (nothing can change that before the next commit): its pods
+  // get "not stopped by the gate, no node, not scheduled" without another search.
+  const int32_t* range;
+  const int32_t* dead;
+  const int32_t* pod_sig;     // [M] request row of every pod of the kind (plan_find_miss_kernel)
+  const int32_t* dem_off;
+  const int32_t* dem_key;
+  int M;
+  int32_t* limit_out;         // [2] device: range of the next chain launch; plan_find_miss_kernel writes [1]
   uint8_t* gate_hit;
   int32_t* repart_node;
   int32_t* sched_node;
@@ -131,12 +143,19 @@ __global__ void __launch_bounds__(32) plan_winmax_kernel(ChainArgs a) {
   }
 }
 
-__global__ void plan_eligible_kernel(ChainArgs a) {
-  // one warp: eligible iff every chain's key is present
-  bool ok = true;
-  for (int c = threadIdx.x; c < a.n_chains; c += 32) ok &= a.present[a.chain_key[c]] > 0;
-  ok = __all_sync(0xffffffffu, ok);
-  if (threadIdx.x == 0) *a.eligible = ok ? 1 : 0;
+// limit_out[1] = the first pod at or after limit_out[0] that the gate does not stop and whose profile is not known to
+// be out of reach (dead), M if there is none.  One block; limit_out[1] must hold M on entry.
+__global__ void plan_find_miss_kernel(ChainArgs a) {
+  const int lo = a.limit_out[0];
+  int mine = a.M;
+  for (int j = lo + threadIdx.x; j < a.M; j += blockDim.x) {
+    const int key = __ldg(a.dem_key + __ldg(a.dem_off + __ldg(a.pod_sig + j)));
+    if (a.present[key] <= 0 && !a.dead[key]) {
+      mine = j;
+      break;  // this thread's later pods are further down the order
+    }
+  }
+  if (mine < a.M) atomicMin(a.limit_out + 1, mine);
 }
 
 constexpr int kChainQ = 8;  // quantities 1..kChainQ each get a cursor; the host keeps larger ones off this path
@@ -145,10 +164,39 @@ constexpr int kChainQ = 8;  // quantities 1..kChainQ each get a cursor; the host
 // bookkeeping over all cursors is what a single latency-bound warp spends its time on
 template <bool MPS, int NQ>
 __global__ void __launch_bounds__(32) plan_chain_kernel(ChainArgs a) {
-  if (*a.eligible == 0) return;
   const int c = blockIdx.x, lane = threadIdx.x;
   const int key = a.chain_key[c];
-  const int j0 = a.chain_off[c], j1 = a.chain_off[c + 1];
+  int j0 = a.chain_off[c], j1 = a.chain_off[c + 1];
+  {  // the chain's pods inside [range[0], range[1]): chain_pod is ascending
+    const int lo = a.range[0], hi = a.range[1];
+    int x0 = j0, x1 = j1;
+    while (x0 < x1) {
+      const int mid = (x0 + x1) >> 1;
+      if (__ldg(a.chain_pod + mid) < lo) x0 = mid + 1;
+      else x1 = mid;
+    }
+    int y0 = x0, y1 = j1;
+    while (y0 < y1) {
+      const int mid = (y0 + y1) >> 1;
+      if (__ldg(a.chain_pod + mid) < hi) y0 = mid + 1;
+      else y1 = mid;
+    }
+    j0 = x0;
+    j1 = y0;
+  }
+  if (j0 >= j1) return;
+  if (a.present[key] <= 0) {
+    // only reachable for a dead profile (plan_find_miss_kernel stops the range at any other absent one): the gate
+    // does not stop the pod (mig_controller.go:83-86), tryRepartition finds no node, nothing of it is free
+    for (int j = j0 + lane; j < j1; j += 32) {
+      const int pod = a.chain_pod[j];
+      a.gate_hit[pod] = 0;
+      a.repart_node[pod] = -1;
+      a.sched_node[pod] = -1;
+      a.sched_gpu[pod] = -1;
+    }
+    return;
+  }
   if (!a.sched) {
     for (int j = j0 + lane; j < j1; j += 32) {
       const int pod = a.chain_pod[j];

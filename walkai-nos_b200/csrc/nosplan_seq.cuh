@@ -68,6 +68,10 @@ struct SeqArgs {
   int32_t* sched_node;
   int32_t* sched_gpu;
   const int32_t* skip_if;
+  // hybrid planning (the chains own the pods the gate stops, see ChainArgs): the profile counts after these pods, and
+  // per key "absent and no node could be repartitioned for it" (cleared by any commit, which may create any profile)
+  int32_t* present_out;
+  int32_t* dead;
 };
 
 // ---- derived masks of one GPU ----------------------------------------------------------------------------
@@ -655,8 +659,17 @@ __global__ void __launch_bounds__(kSeqThreads, 1) plan_seq_kernel(const SeqArgs 
       if (a.sched_node) a.sched_node[i] = out_node;
       if (a.sched_gpu) a.sched_gpu[i] = out_gpu;
     }
+    if (a.dead) {
+      if (out_rep >= 0) {
+        if (lane < K) a.dead[lane] = 0;  // the new geometry may hold any profile
+      } else if (lane == 0 && k == 1 && !out_gate && sh_present[key[0]] <= 0) {
+        a.dead[key[0]] = 1;
+      }
+    }
+    __syncwarp();
     SEQ_TICK(7)
   }
+  if (a.present_out && lane < K) a.present_out[lane] = sh_present[lane];
 #ifdef NOSPLAN_SEQ_PROFILE
   if (lane == 0)
     printf("seq profile (Mcycles) mps=%d search %lld load %lld commit %lld refresh %lld fit %lld addpod %lld refresh2 %lld rest %lld\n",

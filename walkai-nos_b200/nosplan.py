@@ -226,46 +226,58 @@ class Planner:
                                           _p(upd, u8p), _p(of, u8p), _p(om, u32p), C.byref(ne)))
         return dict(first_node=first, updated=upd, out_free=of, out_free_mask=om, n_evals=ne.value)
 
+    _SNAP_DT = dict(gpu_off=np.int32, valid=np.uint8, model=np.int32, used=np.int32, free=np.int32, mem_gb=np.int32,
+                    free_mask=np.uint32)
+
+    @classmethod
+    def _as_abi(cls, d, keys):
+        """The snapshot's arrays in the dtype and layout the ABI takes; arrays that already match are passed as they
+        are (pinned buffers stay pinned), the others are converted."""
+        out = []
+        for k in keys:
+            v = d.get(k)
+            if v is not None:
+                t = cls._SNAP_DT[k]
+                if v.dtype != t or not v.flags.c_contiguous:
+                    v = np.ascontiguousarray(v, t)
+            out.append(v)
+        return out
+
+    @staticmethod
+    def _rows_abi(rows):
+        return tuple(x if (x.dtype == np.int32 and x.flags.c_contiguous) else np.ascontiguousarray(x, np.int32) for x in rows)
+
     def score_snapshot(self, mig=None, mig_rows=None, sizes_gb=None, mps=None, mps_rows=None, want_first_choice=True):
         """One call for a whole scoring pass (nosplan_score_snapshot): mig / mps are snapshot dicts as for
-        set_*_snapshot, *_rows = (off, key, qty).  Nothing is installed on the handle.  Arrays of the right dtype
-        and layout are passed as they are (pinned buffers stay pinned); others are converted first."""
-        keep = []
-        _dt = dict(gpu_off=np.int32, valid=np.uint8, model=np.int32, used=np.int32, free=np.int32, mem_gb=np.int32,
-                   free_mask=np.uint32)
-        conv = lambda d: {k: (np.ascontiguousarray(v, _dt[k]) if k in _dt else v) for k, v in d.items()}
-        if mig is not None:
-            go0 = mig["gpu_off"]
-            mig = conv(mig)
-            mig_rows = tuple(np.ascontiguousarray(x, np.int32) for x in mig_rows)
-            if mig["gpu_off"] is not go0:
-                self._gs_of = None
-        if mps is not None:
-            mps = conv(mps)
-            mps_rows = tuple(np.ascontiguousarray(x, np.int32) for x in mps_rows)
+        set_*_snapshot, *_rows = (off, key, qty).  Nothing is installed on the handle.  With an exchange open on the
+        handle the winners are indices over the whole sharded node list (the call is collective)."""
         ms = ps = md = pd = None
         out = {}
         fm = ff = fp = None
+        keep = []
         if mig is not None:
             N = int(mig["n_nodes"])
-            ms = _MigSnap(N, *[_addr(mig[k]) for k in ("gpu_off", "valid", "model", "used", "free")])
-            off, key, qty = mig_rows
-            md = _Demands(len(off) - 1, _addr(off), _addr(key), _addr(qty))
-            go = mig["gpu_off"]
-            if getattr(self, "_gs_of", None) is not go:
+            arrs = self._as_abi(mig, ("gpu_off", "valid", "model", "used", "free"))
+            off, key, qty = rows = self._rows_abi(mig_rows)
+            keep += [arrs, rows]
+            ms = _MigSnap(N, *[_addr(a) for a in arrs])
+            md = _Demands(len(off) - 1, off.ctypes.data, key.ctypes.data, qty.ctypes.data)
+            go = arrs[0]
+            if getattr(self, "_gs_of", None) is not go:  # the same offsets array again: keep its widest node
                 self._gs_of, self._gs = go, (int(np.max(np.diff(go))) if N else 0)
             fm = np.empty(len(off) - 1, np.int32)
             ff = np.empty((len(off) - 1, max(self._gs, 1)), np.int8) if want_first_choice else None
-            out.update(mig_first_node=fm, mig_first_choice=ff)
+            out["mig_first_node"] = fm
+            out["mig_first_choice"] = ff
         if mps is not None:
             sizes = np.ascontiguousarray(sizes_gb, np.int32)
-            keep.append(sizes)
-            ps = _MpsSnap(len(sizes), _addr(sizes), int(mps["n_nodes"]),
-                          *[_addr(mps.get(k)) for k in ("gpu_off", "valid", "mem_gb", "used", "free", "free_mask")])
-            off, key, qty = mps_rows
-            pd = _Demands(len(off) - 1, _addr(off), _addr(key), _addr(qty))
+            arrs = self._as_abi(mps, ("gpu_off", "valid", "mem_gb", "used", "free", "free_mask"))
+            off, key, qty = rows = self._rows_abi(mps_rows)
+            keep += [sizes, arrs, rows]
+            ps = _MpsSnap(len(sizes), sizes.ctypes.data, int(mps["n_nodes"]), *[_addr(a) for a in arrs])
+            pd = _Demands(len(off) - 1, off.ctypes.data, key.ctypes.data, qty.ctypes.data)
             fp = np.empty(len(off) - 1, np.int32)
-            out.update(mps_first_node=fp)
+            out["mps_first_node"] = fp
         ne = C.c_int64(0)
         ref = lambda x: None if x is None else C.byref(x)
         self._ck(self.L.nosplan_score_snapshot(self.h, ref(ms), ref(md), _p(fm), _p(ff), ref(ps), ref(pd), _p(fp), C.byref(ne)))
