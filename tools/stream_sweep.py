@@ -51,17 +51,18 @@ for _ in range(reps):
 ev[1].record()
 torch.cuda.synchronize()
 ms = ev[0].elapsed_time(ev[1]) / reps
-# what one launch has to read per node and per profile that occurs in the rows: the snapshot-time rank table
-# (gs * 2cw words), profile p's free|cur column (gs u16), the model bytes, the node order entry, the count
-n_prof = len(set(key.tolist()))
-state_bytes = n_prof * N * (G * 6 * 4 + G * 2 + G + 4 + 1)
+# what one launch has to read per node and per pass over the node list (one pass per 4 rows of a profile on the
+# streaming kernel): the snapshot-time rank table (gs * 2cw words = 192 B), the profile's free|cur column (gs u16),
+# the model bytes, the GPU count
+passes = sum((int((key == k).sum()) + 3) // 4 for k in set(key.tolist()))
+state_bytes = passes * N * (G * 6 * 4 + G * 2 + G + 1)
 evals = D * p.mig_evals_per_demand()
 peak = 6542.1
 try:
     peak = float(json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))["hbm_gbs"])
 except Exception:
     pass
-print(json.dumps({"nodes": N, "gpus": tg, "demands": D, "ms": ms, "evals_per_s": evals / (ms * 1e-3),
+print(json.dumps({"nodes": N, "gpus": tg, "demands": D, "stream_rows_knob": os.environ.get("NOSPLAN_STREAM_ROWS", "default"), "ms": ms, "evals_per_s": evals / (ms * 1e-3),
                   "state_bytes_streamed": state_bytes, "dram_GBps": state_bytes / (ms * 1e-3) / 1e9,
                   "frac_of_hbm_peak": state_bytes / (ms * 1e-3) / 1e9 / peak,
                   "survey_8d_GBps": evals * 68 / 12 / (ms * 1e-3) / 1e9, "first_node": first.cpu().numpy()[:6].tolist()}))

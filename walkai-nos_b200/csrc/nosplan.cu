@@ -20,6 +20,7 @@
 #include "nosplan_plan.cuh"
 #include "nosplan_seq.cuh"
 #include "nosplan_score16.cuh"
+#include "nosplan_stream.cuh"
 #include "nosplan_xchg.cuh"
 
 using namespace nsp;
@@ -74,7 +75,7 @@ struct nosplan {
   DevBuf d_mig_sused, d_mig_sfree, d_mig_smodel, d_mig_scnt, d_mig_gnode, d_mig_gslot;
   bool mig_state_dirty = false;  // working copy differs from the snapshot
   DevBuf d_mig_cost, d_mig_perm;  // per-profile node order of the 16-bit-key scorer (nosplan_score16.cuh)
-  DevBuf d_mig_rankg, d_mig_ufg, d_mig_maskg;  // its snapshot-time tables
+  DevBuf d_mig_rankg, d_mig_ufg, d_mig_maskg, d_mig_modelg;  // its snapshot-time tables
   DevBuf d_profcost;
   struct RowPlan {  // per scoring call and kind: demand rows grouped by key, work items (rows_*_kernel)
     DevBuf rows, work, meta, cnt;
@@ -451,7 +452,54 @@ MigScore16Args mig16_args(nosplan_t* h, const MigScoreArgs& a) {
   A.meta = rp.meta.as<int32_t>();
   return A;
 }
+// The no-reuse regime (nosplan_stream.cuh): so few rows that a node's state is not worth staging for re-use.  The
+// rule (measured, profiles/r2_stream_sweep.md): winners only, at most 8 GPU slots per node, and at most
+// stream_rows() demand rows in the call — every kStreamRows rows of a profile cost one pass over the node list at HBM
+// speed, which beats the ordered kernel's tile staging until a profile has a few dozen rows.
+int stream_rows() {  // measurement knob: NOSPLAN_STREAM_ROWS=n (0 = never stream)
+  static const int v = [] {
+    const char* e = std::getenv("NOSPLAN_STREAM_ROWS");
+    const int x = e ? std::atoi(e) : 24;
+    return x >= 0 ? x : 24;
+  }();
+  return v;
+}
+bool mig_streaming(const nosplan_t* h, const MigScoreArgs& a) {
+  return !a.updated && !a.choice && a.D <= stream_rows() && h->mig_gs <= kStreamMaxGpus && !plain_order_forced();
+}
+int launch_mig_stream(nosplan_t* h, const MigScoreArgs& a, cudaStream_t st) {
+  const int cw = std::max(1, std::min(4, (h->cmax + 3) / 4));
+  int max_work = 0;
+  int rc = plan_rows(h, 0, a.D, h->P, kStreamRows, a.dem_off, a.dem_key, a.dem_qty, h->d_profcost.as<int32_t>(), a.first_node, st, &max_work);
+  if (rc) return rc;
+  MigStreamArgs A{};
+  A.T = a.T;
+  A.rankg = h->d_mig_rankg.as<uint32_t>();
+  A.ufg = h->d_mig_ufg.as<uint16_t>();
+  A.modelg = h->d_mig_modelg.as<uint8_t>();
+  A.s_cnt = a.s_cnt;
+  A.N = a.N;
+  A.npad = a.npad;
+  A.gs = a.gs;
+  A.dem_off = a.dem_off;
+  A.dem_qty = a.dem_qty;
+  A.rows = h->rp[0].rows.as<int32_t>();
+  A.work = h->rp[0].work.as<int32_t>();
+  A.meta = h->rp[0].meta.as<int32_t>();
+  A.first_node = a.first_node;
+  A.node_base = a.node_base;
+  const size_t smem = mig_stream_smem_bytes(h->h_tables.n_models, a.gs, cw);
+  if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "streaming scorer needs %zu bytes of shared memory", smem);
+  auto kern = cw == 1 ? mig_stream_kernel<1> : cw == 2 ? mig_stream_kernel<2> : cw == 3 ? mig_stream_kernel<3> : mig_stream_kernel<4>;
+  CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int nodes_per_cta = kStreamWarps * 32;
+  kern<<<dim3((a.npad + nodes_per_cta - 1) / nodes_per_cta, max_work), nodes_per_cta, smem, st>>>(A);
+  CU(cudaGetLastError());
+  return NOSPLAN_OK;
+}
+
 int launch_mig_score16(nosplan_t* h, const MigScoreArgs& a, cudaStream_t st) {
+  if (mig_streaming(h, a)) return launch_mig_stream(h, a, st);
   Mig16Launch L;
   int rc = mig16_prepare(h, a.D, a.updated || a.choice, false, &L);
   if (rc) return rc;
@@ -661,7 +709,7 @@ void nosplan_destroy(nosplan_t* h) {
                    &h->d_mig_used, &h->d_mig_free, &h->d_mig_sused, &h->d_mig_sfree, &h->d_mig_smodel, &h->d_mig_scnt,
                    &h->d_mps_sizes, &h->d_mps_off, &h->d_mps_valid, &h->d_mps_gpu0, &h->d_mps_ulo0, &h->d_mps_uhi0,
                    &h->d_mps_gpu, &h->d_mps_ulo, &h->d_mps_uhi, &h->d_mig_gnode, &h->d_mps_gnode, &h->d_mig_gslot, &h->d_mps_gslot, &h->d_status, &h->d_rowstatus,
-                   &h->d_mig_cost, &h->d_mig_perm, &h->d_mig_rankg, &h->d_mig_ufg, &h->d_mig_maskg, &h->d_profcost, &h->d_mps_cost, &h->d_mps_perm, &h->d_mps_sizecost,
+                   &h->d_mig_cost, &h->d_mig_perm, &h->d_mig_rankg, &h->d_mig_ufg, &h->d_mig_maskg, &h->d_mig_modelg, &h->d_profcost, &h->d_mps_cost, &h->d_mps_perm, &h->d_mps_sizecost,
                    &h->rp[0].rows, &h->rp[0].work, &h->rp[0].meta, &h->rp[0].cnt,
                    &h->rp[1].rows, &h->rp[1].work, &h->rp[1].meta, &h->rp[1].cnt};
   for (DevBuf* b : all) b->release();
@@ -841,13 +889,14 @@ int mig_snapshot_enqueue(nosplan_t* h, int n_nodes, const int32_t* gpu_off, cons
     CU(h->d_mig_rankg.reserve(sizeof(uint32_t) * (size_t)npad * gsl * 2 * cwk));
     CU(h->d_mig_ufg.reserve(sizeof(uint16_t) * (size_t)npad * 16 * gsl));
     CU(h->d_mig_maskg.reserve(sizeof(uint32_t) * (size_t)npad * gsl));
+    CU(h->d_mig_modelg.reserve((size_t)npad * gsl));
     CU(h->d_mig_cost.reserve((size_t)P * npad));
     CU(h->d_mig_perm.reserve(sizeof(int32_t) * (size_t)P * npad));
     CU(h->d_profcost.reserve(sizeof(int32_t) * 32));
     mig_rank16_kernel<<<(npad * gsl + 127) / 128, 128, 0, st>>>(
         h->d_tables.as<MigTables>(), npad, gsl, cwk, h->d_mig_sused.as<uint4>(), h->d_mig_sfree.as<uint4>(),
         h->d_mig_smodel.as<uint8_t>(), h->d_mig_scnt.as<uint8_t>(), h->d_mig_rankg.as<uint32_t>(), h->d_mig_ufg.as<uint16_t>(),
-        h->d_mig_maskg.as<uint32_t>());
+        h->d_mig_maskg.as<uint32_t>(), h->d_mig_modelg.as<uint8_t>());
     mig_cost_kernel<<<(npad + 127) / 128, 128, 0, st>>>(n_nodes, npad, gsl, P, h->d_mig_scnt.as<uint8_t>(),
                                                         h->d_mig_maskg.as<uint32_t>(), h->d_mig_cost.as<uint8_t>());
     mig_perm_kernel<<<P, 1024, 0, st>>>(npad, h->d_mig_cost.as<uint8_t>(), h->d_mig_perm.as<int32_t>(),

@@ -59,11 +59,12 @@ __global__ void mig_cost_kernel(int N, int npad, int gs, int P, const uint8_t* _
 __global__ void mig_rank16_kernel(const MigTables* __restrict__ T, int npad, int gs, int cw, const uint4* __restrict__ s_used,
                                   const uint4* __restrict__ s_free, const uint8_t* __restrict__ s_model,
                                   const uint8_t* __restrict__ s_cnt, uint32_t* __restrict__ rankg, uint16_t* __restrict__ ufg,
-                                  uint32_t* __restrict__ maskg) {
+                                  uint32_t* __restrict__ maskg, uint8_t* __restrict__ modelg) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= npad * gs) return;
   const int n = i / gs, s = i % gs;
   uint32_t* out = rankg + ((size_t)n * gs + s) * (2 * cw);
+  modelg[(size_t)n * gs + s] = s < s_cnt[n] ? s_model[(size_t)s * npad + n] : 0;  // node-major copy (mig_stream_kernel)
   if (s >= s_cnt[n]) {
     for (int w = 0; w < 2 * cw; ++w) out[w] = 0x80008000u;
     for (int p = 0; p < 16; ++p) ufg[((size_t)n * 16 + p) * gs + s] = 0;

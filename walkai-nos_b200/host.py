@@ -209,12 +209,19 @@ def build_pods(pods: List[dict], mig: Optional[Snapshot], mps: Optional[Snapshot
         if err:
             raise ValueError(err)
         n = L.noshost_pods_count(h)
-        get = lambda name, cnt, dt: (np.ctypeslib.as_array(getattr(L, f"noshost_pods_{name}")(h), shape=(max(cnt, 1),))[:cnt]
-                                     .astype(dt).copy())
+        def get(name, cnt, dt):
+            ptr = getattr(L, f"noshost_pods_{name}")(h)
+            if cnt == 0 or not ptr:  # no planner rows at all (every pod filtered out): empty std::vector, null data()
+                return np.zeros(max(cnt, 0), dt)
+            return np.ctypeslib.as_array(ptr, shape=(cnt,)).astype(dt).copy()
         off = get("off", n + 1, np.int32)
+        if off.size == 0:
+            off = np.zeros(1, np.int32)
         nnz = int(off[-1]) if n else 0
-        return dict(source=get("source", n, np.int32), kind=get("kind", n, np.uint8), off=off,
-                    key=get("key", max(nnz, 1), np.int32), qty=get("qty", max(nnz, 1), np.int32))
+        key, qty = get("key", nnz, np.int32), get("qty", nnz, np.int32)
+        if nnz == 0:
+            key, qty = np.zeros(1, np.int32), np.zeros(1, np.int32)
+        return dict(source=get("source", n, np.int32), kind=get("kind", n, np.uint8), off=off, key=key, qty=qty)
     finally:
         L.noshost_pods_free(h)
 
