@@ -107,6 +107,32 @@ int noshost_spec_annotations(const noshost_snapshot* s, int node, const int32_t*
 int noshost_node_partitioning_equal(int n_keys, int n_a, const int32_t* idx_a, const int32_t* res_a, int n_b,
                                     const int32_t* idx_b, const int32_t* res_b);
 
+/* ---- geometry tables: the loader of config/gpupartitioner/manager/known_mig_geometries.yaml
+ * (cmd/gpupartitioner/gpupartitioner.go:122-132 -> sigs.k8s.io/yaml -> AllowedMigGeometries.UnmarshalJSON,
+ * pkg/gpu/mig/allowed_geometries.go:30-59: `models` and `allowedGeometries` are both required, a list of strings and
+ * a list of {profile: quantity} maps) and AllowedMigGeometriesList.GroupByModel (:74-82: a model named by several
+ * entries keeps the last one's list).  text = the YAML document.  Returns NULL and writes the reason into err where
+ * the reference's Unmarshal returns an error.  The entry accessors give the list as parsed; the flat accessors give
+ * GroupByModel in the layout of nosplan_set_mig_tables: models in order of first appearance, profile vocabulary
+ * ascending bytewise, geom_off[n_models + 1], geom_counts[total][n_profiles].  Names and quantities are not
+ * validated here (the reference validates in SetKnownGeometries; nosplan_set_mig_tables does). */
+typedef struct noshost_tables noshost_tables;
+noshost_tables* noshost_tables_load(const char* text, char* err, int err_cap);
+void noshost_tables_free(noshost_tables* t);
+int noshost_tables_n_entries(const noshost_tables* t);
+int noshost_tables_entry_n_models(const noshost_tables* t, int e);
+const char* noshost_tables_entry_model(const noshost_tables* t, int e, int i);
+int noshost_tables_entry_n_geometries(const noshost_tables* t, int e);
+int noshost_tables_entry_geometry_size(const noshost_tables* t, int e, int g);
+const char* noshost_tables_entry_geometry_profile(const noshost_tables* t, int e, int g, int k);
+int64_t noshost_tables_entry_geometry_quantity(const noshost_tables* t, int e, int g, int k);
+int noshost_tables_n_models(const noshost_tables* t);
+const char* noshost_tables_model(const noshost_tables* t, int m);
+int noshost_tables_n_profiles(const noshost_tables* t);
+const char* noshost_tables_profile(const noshost_tables* t, int p);
+const int32_t* noshost_tables_geom_off(const noshost_tables* t);
+const int32_t* noshost_tables_geom_counts(const noshost_tables* t);
+
 #ifdef __cplusplus
 }
 #endif

@@ -492,8 +492,12 @@ int launch_mig_stream(nosplan_t* h, const MigScoreArgs& a, cudaStream_t st) {
   if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "streaming scorer needs %zu bytes of shared memory", smem);
   auto kern = cw == 1 ? mig_stream_kernel<1> : cw == 2 ? mig_stream_kernel<2> : cw == 3 ? mig_stream_kernel<3> : mig_stream_kernel<4>;
   CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int nodes_per_cta = kStreamWarps * 32;
-  kern<<<dim3((a.npad + nodes_per_cta - 1) / nodes_per_cta, max_work), nodes_per_cta, smem, st>>>(A);
+  // persistent: as many CTAs as fit at once (or fewer when the node list is short); the warps stride over the work
+  int occ = 0;
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kStreamWarps * 32, smem));
+  const long long blocks_needed = ((long long)(a.npad / 32) * std::min(max_work, std::max(1, (a.D + kStreamRows - 1) / kStreamRows + h->P)) + kStreamWarps - 1) / kStreamWarps;
+  const int grid = (int)std::max<long long>(1, std::min<long long>(blocks_needed, (long long)h->sm_count * std::max(occ, 1)));
+  kern<<<grid, kStreamWarps * 32, smem, st>>>(A);
   CU(cudaGetLastError());
   return NOSPLAN_OK;
 }
@@ -1446,7 +1450,7 @@ int nosplan_score_mig(nosplan_t* h, int n_demands, const int32_t* dem_off, const
         h->d_tables.as<MigTables>(), h->d_mig_rankg.as<uint32_t>(), h->d_mig_ufg.as<uint16_t>(), h->d_mig_used0.as<uint4>(),
         h->d_mig_free0.as<uint4>(), h->d_mig_model.as<uint8_t>(), h->d_mig_off.as<int32_t>(), D, h->mig_gs, (h->cmax + 3) / 4,
         h->d_dem[0].as<int32_t>(), h->d_dem[1].as<int32_t>(), h->d_dem[2].as<int32_t>(), h->d_out[0].as<int32_t>(),
-        h->d_out[3].as<int8_t>(), 0, h->mig_n);
+        h->d_out[3].as<int8_t>(), 0, h->mig_n, h->mig_npad);
   } else if (first_choice) {
     mig_finalize_kernel<<<(D + 127) / 128, 128, 0, st>>>(
         h->d_tables.as<MigTables>(), h->d_mig_used0.as<uint4>(), h->d_mig_free0.as<uint4>(), h->d_mig_model.as<uint8_t>(),
@@ -2440,7 +2444,7 @@ extern "C" int nosplan_score_snapshot(nosplan_t* h, const nosplan_mig_snapshot_t
             c->d_tables.as<MigTables>(), c->d_mig_rankg.as<uint32_t>(), c->d_mig_ufg.as<uint16_t>(), c->d_mig_used0.as<uint4>(),
             c->d_mig_free0.as<uint4>(), c->d_mig_model.as<uint8_t>(), c->d_mig_off.as<int32_t>(), Dm, gs, (c->cmax + 3) / 4,
             c->d_dem[0].as<int32_t>(), c->d_dem[1].as<int32_t>(), c->d_dem[2].as<int32_t>(), c->d_out[0].as<int32_t>(),
-            c->d_out[3].as<int8_t>(), c->mig_base, c->mig_n);
+            c->d_out[3].as<int8_t>(), c->mig_base, c->mig_n, c->mig_npad);
       } else {
         mig_finalize_kernel<<<(Dm + 127) / 128, 128, 0, sm>>>(
             c->d_tables.as<MigTables>(), c->d_mig_used0.as<uint4>(), c->d_mig_free0.as<uint4>(), c->d_mig_model.as<uint8_t>(),

@@ -54,7 +54,7 @@ __global__ void mig_cost_kernel(int N, int npad, int gs, int P, const uint8_t* _
 // id rank) depends only on the snapshot, so it is evaluated once when the snapshot arrives instead of in
 // the prologue of every CTA of every scoring call: per (node, slot) the rank half-words of all
 // candidates, and per (node, profile, slot) free | (used + free) << 8.
-//   rankg [npad][gs][2cw] u32, ufg [npad][16][gs] u16, maskg [npad][gs] u32 (profiles with a free device |
+//   rankg [npad][gs][2cw] u32, ufg [16][npad][gs] u16 (profile-major: a profile's column is contiguous over nodes), maskg [npad][gs] u32 (profiles with a free device |
 //   profiles some applicable geometry adds to, << 16)
 __global__ void mig_rank16_kernel(const MigTables* __restrict__ T, int npad, int gs, int cw, const uint4* __restrict__ s_used,
                                   const uint4* __restrict__ s_free, const uint8_t* __restrict__ s_model,
@@ -67,7 +67,7 @@ __global__ void mig_rank16_kernel(const MigTables* __restrict__ T, int npad, int
   modelg[(size_t)n * gs + s] = s < s_cnt[n] ? s_model[(size_t)s * npad + n] : 0;  // node-major copy (mig_stream_kernel)
   if (s >= s_cnt[n]) {
     for (int w = 0; w < 2 * cw; ++w) out[w] = 0x80008000u;
-    for (int p = 0; p < 16; ++p) ufg[((size_t)n * 16 + p) * gs + s] = 0;
+    for (int p = 0; p < 16; ++p) ufg[((size_t)p * npad + n) * gs + s] = 0;
     maskg[(size_t)n * gs + s] = 0;
     return;
   }
@@ -76,7 +76,7 @@ __global__ void mig_rank16_kernel(const MigTables* __restrict__ T, int npad, int
   const int m = s_model[(size_t)s * npad + n];
   const uint4 cur = add4(u, f);
   const int c0 = T->geom_off[m], cc = T->geom_off[m + 1] - c0;
-  for (int p = 0; p < 16; ++p) ufg[((size_t)n * 16 + p) * gs + s] = (uint16_t)(byte_of(f, p) | (byte_of(cur, p) << 8));
+  for (int p = 0; p < 16; ++p) ufg[((size_t)p * npad + n) * gs + s] = (uint16_t)(byte_of(f, p) | (byte_of(cur, p) << 8));
   uint32_t k0[16];
   uint32_t gm = 0;  // profiles some applicable geometry would add to
   for (int c = 0; c < 16; ++c) {
@@ -292,7 +292,7 @@ struct MigScore16Args {
   MigScoreArgs base;          // tables, slot-major state, demand CSR, outputs
   const int32_t* perm;        // [P][npad]
   const uint32_t* rankg;      // [npad][gs][2cw]  (mig_rank16_kernel)
-  const uint16_t* ufg;        // [npad][16][gs]
+  const uint16_t* ufg;        // [16][npad][gs]
   const int32_t* rows;        // grouped row ids
   const int32_t* work;        // work items
   const int32_t* meta;
@@ -389,7 +389,7 @@ __device__ __forceinline__ void mig_score16_body(const MigScore16Args& A, const 
     const uint32_t* src = A.rankg + ((size_t)n * a.gs + s) * (2 * cw);
 #pragma unroll
     for (int w = 0; w < 2 * cw; ++w) col[w * TN] = __ldg(src + w);
-    const uint32_t x = __ldg(A.ufg + ((size_t)n * 16 + p) * a.gs + s);  // free | (used + free) << 8
+    const uint32_t x = __ldg(A.ufg + ((size_t)p * a.npad + n) * a.gs + s);  // free | (used + free) << 8
     col[2 * cw * TN] = (x & 0xffu) | (((0u - (x >> 8)) & 0xffffu) << 16);
     col[(2 * cw + 1) * TN] = ct2_saddr + (uint32_t)a.s_model[(size_t)s * a.npad + n] * (2 * cw * 4);
   }
@@ -499,7 +499,7 @@ __global__ void mig_finalize16_kernel(const MigTables* __restrict__ T, const uin
                                       const int32_t* __restrict__ gpu_off, int D, int gs, int cw,
                                       const int32_t* __restrict__ dem_off, const int32_t* __restrict__ dem_key,
                                       const int32_t* __restrict__ dem_qty, const int32_t* __restrict__ first_node,
-                                      int8_t* __restrict__ first_choice, int node_base, int N) {
+                                      int8_t* __restrict__ first_choice, int node_base, int N, int npad) {
   const int d = blockIdx.x * blockDim.x + threadIdx.x;
   if (d >= D) return;
   // first_node holds indices over the whole (possibly sharded) list: a winner on another rank has no choices here
@@ -513,7 +513,7 @@ __global__ void mig_finalize16_kernel(const MigTables* __restrict__ T, const uin
       const int p = dem_key[e0];
       int resid = min(max(dem_qty[e0], 0), 32767);
       for (int s = 0; s < cnt && resid > 0; ++s) {
-        const uint32_t x = ufg[((size_t)fn * 16 + p) * gs + s];
+        const uint32_t x = ufg[((size_t)p * npad + fn) * gs + s];
         const int needed = resid - (int)(x & 0xffu);
         uint32_t best2 = 0;
         if (needed > 0) {

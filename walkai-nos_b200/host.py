@@ -9,7 +9,7 @@ from typing import Dict, Iterable, List, Optional, Sequence
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB = os.path.join(_HERE, "libnoshost.so")
+_LIB = os.environ.get("NOSHOST_LIB") or os.path.join(_HERE, "libnoshost.so")  # NOSHOST_LIB: the ASan/UBSan build
 _lib = None
 
 LABEL_PRODUCT = "nvidia.com/gpu.product"  # pkg/constant/constants.go:67-77
@@ -27,6 +27,11 @@ EXPORTS = [
     "noshost_snapshot_used_mask", "noshost_snapshot_free_mask", "noshost_pods_build", "noshost_pods_free",
     "noshost_pods_count", "noshost_pods_source", "noshost_pods_kind", "noshost_pods_off", "noshost_pods_key",
     "noshost_pods_qty", "noshost_pods_error", "noshost_spec_annotations", "noshost_node_partitioning_equal",
+    "noshost_tables_load", "noshost_tables_free", "noshost_tables_n_entries", "noshost_tables_entry_n_models",
+    "noshost_tables_entry_model", "noshost_tables_entry_n_geometries", "noshost_tables_entry_geometry_size",
+    "noshost_tables_entry_geometry_profile", "noshost_tables_entry_geometry_quantity", "noshost_tables_n_models",
+    "noshost_tables_model", "noshost_tables_n_profiles", "noshost_tables_profile", "noshost_tables_geom_off",
+    "noshost_tables_geom_counts",
 ]
 
 
@@ -46,8 +51,21 @@ def lib():
         for n in ("source", "off", "key", "qty"):
             getattr(L, f"noshost_pods_{n}").restype = C.POINTER(C.c_int32)
         L.noshost_pods_kind.restype = C.POINTER(C.c_uint8)
+        L.noshost_tables_load.restype = C.c_void_p
+        L.noshost_tables_load.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
+        L.noshost_tables_free.argtypes = [C.c_void_p]
+        for n, rt, extra in (("n_entries", C.c_int, 0), ("entry_n_models", C.c_int, 1), ("entry_model", C.c_char_p, 2),
+                             ("entry_n_geometries", C.c_int, 1), ("entry_geometry_size", C.c_int, 2),
+                             ("entry_geometry_profile", C.c_char_p, 3), ("entry_geometry_quantity", C.c_int64, 3),
+                             ("n_models", C.c_int, 0), ("model", C.c_char_p, 1), ("n_profiles", C.c_int, 0), ("profile", C.c_char_p, 1),
+                             ("geom_off", C.POINTER(C.c_int32), 0), ("geom_counts", C.POINTER(C.c_int32), 0)):
+            f = getattr(L, f"noshost_tables_{n}")
+            f.restype = rt
+            f.argtypes = [C.c_void_p] + [C.c_int] * extra
         for name in EXPORTS:
             f = getattr(L, name)
+            if name.startswith("noshost_tables_"):
+                continue
             if name.startswith(("noshost_snapshot_", "noshost_pods_")) and not name.endswith("_build"):
                 f.argtypes = [C.c_void_p] + ([C.c_int] if name.endswith(("key_name", "key_size")) else [])
         _lib = L
@@ -250,3 +268,37 @@ def partitioning_state_equal(a: Dict[str, List[dict]], b: Dict[str, List[dict]])
         return False
     resources = sorted({r for st in (a, b) for gs in st.values() for g in gs for r in g["resources"]})
     return all(node_partitioning_equal(gs, b.get(node, []), resources) for node, gs in a.items())
+
+
+def load_tables(text: str):
+    """known_mig_geometries.yaml -> (entries, grouped): entries = the AllowedMigGeometriesList as parsed
+    ([{"models": [...], "allowedGeometries": [{profile: qty}, ...]}, ...]); grouped = dict(models, profiles, geom_off,
+    geom_counts, tables) = GroupByModel flattened for nosplan_set_mig_tables (tables: {model: [geometry dicts]}).
+    Raises ValueError where the reference's yaml.Unmarshal returns an error (allowed_geometries.go:30-59)."""
+    L = lib()
+    err = C.create_string_buffer(256)
+    h = L.noshost_tables_load(text.encode(), err, 256)
+    if not h:
+        raise ValueError(err.value.decode())
+    h = C.c_void_p(h)
+    try:
+        entries = []
+        for e in range(L.noshost_tables_n_entries(h)):
+            models = [L.noshost_tables_entry_model(h, e, i).decode() for i in range(L.noshost_tables_entry_n_models(h, e))]
+            geoms = []
+            for g in range(L.noshost_tables_entry_n_geometries(h, e)):
+                geoms.append({L.noshost_tables_entry_geometry_profile(h, e, g, k).decode(): int(L.noshost_tables_entry_geometry_quantity(h, e, g, k))
+                              for k in range(L.noshost_tables_entry_geometry_size(h, e, g))})
+            entries.append({"models": models, "allowedGeometries": geoms})
+        models = [L.noshost_tables_model(h, m).decode() for m in range(L.noshost_tables_n_models(h))]
+        profiles = [L.noshost_tables_profile(h, p).decode() for p in range(L.noshost_tables_n_profiles(h))]
+        P = len(profiles)
+        off = np.ctypeslib.as_array(L.noshost_tables_geom_off(h), shape=(len(models) + 1,)).astype(np.int32).copy()
+        total = int(off[-1])
+        counts = (np.ctypeslib.as_array(L.noshost_tables_geom_counts(h), shape=(total * P,)).astype(np.int32).reshape(total, P).copy()
+                  if total * P else np.zeros((total, P), np.int32))
+        tables = {m: [{profiles[p]: int(counts[g, p]) for p in range(P) if counts[g, p] != 0} for g in range(off[i], off[i + 1])]
+                  for i, m in enumerate(models)}
+        return entries, dict(models=models, profiles=profiles, geom_off=off, geom_counts=counts, tables=tables)
+    finally:
+        L.noshost_tables_free(h)

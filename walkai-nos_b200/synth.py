@@ -3,10 +3,12 @@
 Deterministic: splitmix64 seeded 0x6e6f730000 + config number, consumed in the order documented in
 each function.  Used by the parity tests and by bench.py (the same arrays go to the CUDA library and
 to the CPU oracle).  Geometry tables are the reference's deployed YAML table
-(config/gpupartitioner/manager/known_mig_geometries.yaml:1-59), transcribed below as data.
+(config/gpupartitioner/manager/known_mig_geometries.yaml:1-59), shipped as data/known_mig_geometries.yaml and read
+through the native loader of libnoshost.
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, List, Tuple
 
 import numpy as np
@@ -17,29 +19,20 @@ MASK64 = (1 << 64) - 1
 MIG_PROFILES = sorted(["1g.6gb", "2g.12gb", "4g.24gb", "1g.5gb", "2g.10gb", "3g.20gb", "4g.20gb", "7g.40gb",
                        "1g.10gb", "2g.20gb", "3g.40gb", "4g.40gb", "7g.79gb"])
 
-# known_mig_geometries.yaml (order kept; the 3g.20gb entry of the 80 GB table is the file's own, :46-47)
-YAML_TABLE = [
-    (["A30"], [{"1g.6gb": 4}, {"1g.6gb": 2, "2g.12gb": 1}, {"2g.12gb": 2}, {"4g.24gb": 1}]),
-    (["A100-SXM4-40GB", "NVIDIA-A100-40GB-PCIe", "NVIDIA-A100-SXM4-40GB"], [
-        {"1g.5gb": 7}, {"1g.5gb": 5, "2g.10gb": 1}, {"1g.5gb": 3, "2g.10gb": 2}, {"1g.5gb": 1, "2g.10gb": 3},
-        {"1g.5gb": 2, "2g.10gb": 1, "3g.20gb": 1}, {"2g.10gb": 2, "3g.20gb": 1}, {"1g.5gb": 3, "3g.20gb": 1},
-        {"1g.5gb": 1, "2g.10gb": 1, "3g.20gb": 1}, {"3g.20gb": 2}, {"1g.5gb": 3, "4g.20gb": 1},
-        {"1g.5gb": 1, "2g.10gb": 1, "4g.20gb": 1}, {"7g.40gb": 1}]),
-    (["NVIDIA-A100-SXM4-80GB", "NVIDIA-A100-80GB-PCIe", "NVIDIA-H100-PCIe", "NVIDIA-H100-80GB"], [
-        {"1g.10gb": 7}, {"1g.10gb": 5, "2g.20gb": 1}, {"1g.10gb": 3, "2g.20gb": 2}, {"1g.10gb": 1, "2g.20gb": 3},
-        {"1g.10gb": 2, "2g.20gb": 1, "3g.40gb": 1}, {"2g.20gb": 2, "3g.20gb": 1}, {"1g.10gb": 3, "3g.40gb": 1},
-        {"1g.10gb": 1, "2g.20gb": 1, "3g.40gb": 1}, {"3g.40gb": 2}, {"1g.10gb": 3, "4g.40gb": 1},
-        {"1g.10gb": 1, "2g.20gb": 1, "4g.40gb": 1}, {"7g.79gb": 1}]),
-]
+_TABLE_FILE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "known_mig_geometries.yaml")
+_tables_cache = None
 
 
 def yaml_tables() -> Dict[str, List[Dict[str, int]]]:
-    """GroupByModel (pkg/gpu/mig/allowed_geometries.go:74-82)."""
-    d: Dict[str, List[Dict[str, int]]] = {}
-    for models, geoms in YAML_TABLE:
-        for m in models:
-            d[m] = geoms
-    return d
+    """The deployed geometry table (data/known_mig_geometries.yaml, the reference's
+    config/gpupartitioner/manager/known_mig_geometries.yaml:1-59) read through the native loader
+    (noshost_tables_load: AllowedMigGeometries.UnmarshalJSON + GroupByModel, pkg/gpu/mig/allowed_geometries.go:30-82)."""
+    global _tables_cache
+    if _tables_cache is None:
+        from . import host
+        with open(_TABLE_FILE) as f:
+            _tables_cache = host.load_tables(f.read())[1]["tables"]
+    return {m: [dict(g) for g in geoms] for m, geoms in _tables_cache.items()}
 
 
 def flatten_tables(tables: Dict[str, List[Dict[str, int]]], names: List[str]):
