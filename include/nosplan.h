@@ -164,6 +164,27 @@ int nosplan_diff_plan_mig(nosplan_t* h, int n_gpus, int n_profiles, const int32_
                           const int32_t* spec, const uint32_t* spec_mask, int32_t* create, int32_t* del_free,
                           int32_t* del_used);
 
+/* The same planner down to the devices: which device ids each DeleteOperation names and which CreateOperations
+ * exist (plan.go:31-92; MigConfigPlan{DeleteOperations, CreateOperations}, operation.go:25-38).
+ *   dev_off[n_gpus + 1]     CSR over the GPUs' devices; the devices of a GPU in the order of
+ *                           state.Flatten().SortByDeviceId() (plan.go:45: ascending device id) — the ids
+ *                           themselves stay with the caller, index i of these arrays stands for them
+ *   dev_profile[n_devices]  column of the device's profile, dev_status[n_devices] 0 used / 1 free / 2 unknown
+ *   spec / spec_mask        as for nosplan_diff_plan_mig
+ * Outputs:
+ *   dev_op[n_devices]  0 keep | 1 deleted: its profile is not in the GPU's spec annotations (plan.go:37-41; one
+ *                      DeleteOperation per (GPU, profile), mig.GroupDevicesByMigProfile) | 2 deleted to shrink the
+ *                      profile (:60-70, extractCandidatesForDeletion :112-137: free devices first, ascending id; one
+ *                      operation per (GPU, profile)) | 3 deleted to be re-created because the GPU gets a create
+ *                      (:73-88; one DeleteOperation per GPU)
+ *   create_new[n_gpus][n_profiles]    CreateOperation{profile, quantity} for diff > 0 (:61-64), 0 = none
+ *   create_again[n_gpus][n_profiles]  CreateOperation for the re-created free devices (:85-87), 0 = none
+ *   matches[n_gpus]    1 where MigState.Matches (mig_state.go:40-58) holds for the GPU's part of both maps; the
+ *                      reference's answer for a node is the AND over its GPUs */
+int nosplan_diff_plan_mig_devices(nosplan_t* h, int n_gpus, int n_profiles, const int32_t* dev_off, const int32_t* dev_profile,
+                                  const uint8_t* dev_status, const int32_t* spec, const uint32_t* spec_mask, uint8_t* dev_op,
+                                  int32_t* create_new, int32_t* create_again, uint8_t* matches);
+
 /* ---- device-resident variants (inputs/outputs already in HBM; used for kernel-only timing) ------------ */
 /* Same as nosplan_score_mig/_mps but every pointer is a device pointer on the handle's device and the
  * work is enqueued on `stream` (a cudaStream_t) without synchronising.  first_node must be

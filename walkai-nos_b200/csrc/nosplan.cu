@@ -467,10 +467,20 @@ int stream_rows() {  // measurement knob: NOSPLAN_STREAM_ROWS=n (0 = never strea
 bool mig_streaming(const nosplan_t* h, const MigScoreArgs& a) {
   return !a.updated && !a.choice && a.D <= stream_rows() && h->mig_gs <= kStreamMaxGpus && !plain_order_forced();
 }
+template <int CW, int RS>
+void (*stream_kernel_gs(int gs))(MigStreamArgs) { return gs == 8 ? mig_stream_kernel<CW, RS, 8> : mig_stream_kernel<CW, RS, 0>; }
+template <int CW>
+void (*stream_kernel_rs(int rs, int gs))(MigStreamArgs) {
+  return rs == 1 ? stream_kernel_gs<CW, 1>(gs) : rs == 2 ? stream_kernel_gs<CW, 2>(gs) : stream_kernel_gs<CW, kStreamRows>(gs);
+}
+void (*stream_kernel_of(int cw, int rs, int gs))(MigStreamArgs) {
+  return cw == 1 ? stream_kernel_rs<1>(rs, gs) : cw == 2 ? stream_kernel_rs<2>(rs, gs) : cw == 3 ? stream_kernel_rs<3>(rs, gs) : stream_kernel_rs<4>(rs, gs);
+}
 int launch_mig_stream(nosplan_t* h, const MigScoreArgs& a, cudaStream_t st) {
   const int cw = std::max(1, std::min(4, (h->cmax + 3) / 4));
   int max_work = 0;
-  int rc = plan_rows(h, 0, a.D, h->P, kStreamRows, a.dem_off, a.dem_key, a.dem_qty, h->d_profcost.as<int32_t>(), a.first_node, st, &max_work);
+  const int rs = a.D <= 1 ? 1 : a.D <= 2 ? 2 : kStreamRows;  // rows per work item = rows a thread carries in registers
+  int rc = plan_rows(h, 0, a.D, h->P, rs, a.dem_off, a.dem_key, a.dem_qty, h->d_profcost.as<int32_t>(), a.first_node, st, &max_work);
   if (rc) return rc;
   MigStreamArgs A{};
   A.T = a.T;
@@ -490,13 +500,19 @@ int launch_mig_stream(nosplan_t* h, const MigScoreArgs& a, cudaStream_t st) {
   A.node_base = a.node_base;
   const size_t smem = mig_stream_smem_bytes(h->h_tables.n_models, a.gs, cw);
   if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "streaming scorer needs %zu bytes of shared memory", smem);
-  auto kern = cw == 1 ? mig_stream_kernel<1> : cw == 2 ? mig_stream_kernel<2> : cw == 3 ? mig_stream_kernel<3> : mig_stream_kernel<4>;
+  auto kern = stream_kernel_of(cw, rs, a.gs);
   CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   // persistent: as many CTAs as fit at once (or fewer when the node list is short); the warps stride over the work
   int occ = 0;
   CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kStreamWarps * 32, smem));
-  const long long blocks_needed = ((long long)(a.npad / 32) * std::min(max_work, std::max(1, (a.D + kStreamRows - 1) / kStreamRows + h->P)) + kStreamWarps - 1) / kStreamWarps;
-  const int grid = (int)std::max<long long>(1, std::min<long long>(blocks_needed, (long long)h->sm_count * std::max(occ, 1)));
+  // The warps stride over (work item, block of 32 nodes) pairs.  With the grid at its maximum the last round would be
+  // partly empty (31 250 pairs over 4 736 warps: 6.6 rounds); size the grid so that every warp gets the same
+  // number of rounds, counting the items a call with D rows can have at most (the real count is on the device)
+  const long long items = std::min<long long>(max_work, std::max(1, (a.D + rs - 1) / rs));
+  const long long pairs = (long long)(a.npad / 32) * items;
+  const long long max_warps = (long long)h->sm_count * std::max(occ, 1) * kStreamWarps;
+  const long long rounds = std::max<long long>(1, (pairs + max_warps - 1) / max_warps);
+  const int grid = (int)std::max<long long>(1, (pairs + rounds * kStreamWarps - 1) / (rounds * kStreamWarps));
   kern<<<grid, kStreamWarps * 32, smem, st>>>(A);
   CU(cudaGetLastError());
   return NOSPLAN_OK;
@@ -518,7 +534,7 @@ int launch_mig_score16(nosplan_t* h, const MigScoreArgs& a, cudaStream_t st) {
 // the rows-by-key path is taken (and with it the demand rows are validated on the device)
 constexpr int kMaxOrderedRows = 60 * 1000 * 1000;  // rows[] positions (key * D + i) stay 32-bit
 bool mig_ordered(const nosplan_t* h, int D) {
-  return D <= kMaxOrderedRows && h->mig_n > 0 && h->k16ok && (h->cmax + 3) / 4 <= 4 && (h->mig_n + 31) / 32 <= 65535 &&
+  return D <= kMaxOrderedRows && h->mig_n > 0 && h->k16ok && (h->cmax + 3) / 4 <= 4 && (h->mig_n + mig16_tile() - 1) / mig16_tile() <= 65535 &&
          !wide_keys_forced() && !plain_order_forced();
 }
 bool mps_ordered(const nosplan_t* h, int D) {
@@ -593,7 +609,10 @@ int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
       a.row_list = h->rp[0].rows.as<int32_t>();
       a.row_meta = h->rp[0].meta.as<int32_t>();
     }
-    if ((rc = launch_mig_score_kernel(h, a, dim3(tiles, gy), smem, st))) return rc;
+    // after the ordered / streaming kernel only the rows with several keys are left, usually none: a small grid
+    // that strides over the tiles, so that an empty pass costs a few hundred CTAs whatever the node count
+    const int gx = ordered ? std::min(tiles, 4 * h->sm_count) : tiles;
+    if ((rc = launch_mig_score_kernel(h, a, dim3(gx, gy), smem, st))) return rc;
   }
   CU(cudaGetLastError());
   return NOSPLAN_OK;
@@ -1289,10 +1308,11 @@ int score_pass_enqueue(nosplan_t* h, nosplan_t* x, int Dm, const int32_t* m_off,
       a.row_list = h->rp[0].rows.as<int32_t>();
       a.row_meta = h->rp[0].meta.as<int32_t>();
       int gy;
-      pick_chunks(h->sm_count, L.tiles, Dm, 16, &a.d_chunk, &gy);
+      const int tiles128 = std::min((h->mig_n + kScoreTN - 1) / kScoreTN, 4 * h->sm_count);  // the kernel strides over the rest
+      pick_chunks(h->sm_count, tiles128, Dm, 16, &a.d_chunk, &gy);
       const size_t smem = mig_score_smem(h, kScoreTN);
       if (smem > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MIG scorer tile needs %zu bytes of shared memory", smem);
-      if ((rc = launch_mig_score_kernel(h, a, dim3(L.tiles, gy), smem, st))) return rc;
+      if ((rc = launch_mig_score_kernel(h, a, dim3(tiles128, gy), smem, st))) return rc;
     }
   }
   if (have_p && !both) {
@@ -2176,6 +2196,129 @@ extern "C" int nosplan_diff_plan_mig(nosplan_t* h, int n_gpus, int n_profiles, c
   CU(cudaMemcpyAsync(create, h->d_out[0].p, bytes, cudaMemcpyDeviceToHost, st));
   CU(cudaMemcpyAsync(del_free, h->d_out[1].p, bytes, cudaMemcpyDeviceToHost, st));
   CU(cudaMemcpyAsync(del_used, h->d_out[2].p, bytes, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  return NOSPLAN_OK;
+}
+
+// ---- agent-side diff planner, device level ------------------------------------------------------------------------
+// plan.NewMigConfigPlan (internal/controllers/migagent/plan/plan.go:31-92) down to which DEVICES go: one thread per
+// GPU walks the GPU's devices in the order the reference walks them (state.Flatten().SortByDeviceId(), :45 — the
+// caller sorts, ids are strings and never reach the device) and marks every device with the operation that deletes it.
+namespace {
+__global__ void mig_diff_devices_kernel(int G, int P, const int32_t* __restrict__ dev_off, const int32_t* __restrict__ dev_profile,
+                                        const uint8_t* __restrict__ dev_status, const int32_t* __restrict__ spec,
+                                        const uint32_t* __restrict__ spec_mask, uint8_t* __restrict__ dev_op,
+                                        int32_t* __restrict__ create_new, int32_t* __restrict__ create_again,
+                                        uint8_t* __restrict__ matches) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= G) return;
+  const int d0 = dev_off[g], d1 = dev_off[g + 1];
+  const uint32_t mask = spec_mask[g];
+  int cnt[kMaxProf], fre[kMaxProf], del_free[kMaxProf], del_used[kMaxProf];
+#pragma unroll
+  for (int p = 0; p < kMaxProf; ++p) cnt[p] = fre[p] = del_free[p] = del_used[p] = 0;
+  for (int d = d0; d < d1; ++d) {
+    const int p = dev_profile[d];
+    for (int q = 0; q < kMaxProf; ++q)  // (register arrays: no dynamic indexing)
+      if (q == p) {
+        cnt[q]++;
+        if (dev_status[d] == 1) fre[q]++;
+      }
+  }
+  bool any_create = false, same = true;
+#pragma unroll
+  for (int p = 0; p < kMaxProf; ++p) {
+    int c = 0;
+    if (p < P) {
+      const bool named = (mask >> p) & 1u;
+      const int want = named ? spec[(size_t)g * P + p] : 0;
+      // MigState.Matches (mig_state.go:40-58): both maps hold the same keys with the same counts; a spec
+      // annotation creates its key even with quantity 0, the state only has keys of devices that exist
+      same &= named ? (want == cnt[p] && cnt[p] > 0) : (cnt[p] == 0);
+      if (named) {
+        const int diff = want - cnt[p];  // plan.go:60
+        if (diff > 0) c = diff;
+        else if (diff < 0) {  // extractCandidatesForDeletion (:112-137): free devices first, then the others
+          del_free[p] = min(-diff, fre[p]);
+          del_used[p] = -diff - del_free[p];
+        }
+      }
+      create_new[(size_t)g * P + p] = c;
+    }
+    any_create |= c > 0;
+  }
+  int again[kMaxProf];
+#pragma unroll
+  for (int p = 0; p < kMaxProf; ++p) again[p] = 0;
+  for (int d = d0; d < d1; ++d) {
+    const int p = dev_profile[d];
+    const bool is_free = dev_status[d] == 1;
+    uint8_t op = 0;
+    if (!((mask >> p) & 1u)) {
+      op = 1;  // its profile is not named by any spec annotation of the GPU (:37-41, getResourcesNotIncludedInSpec :168-182)
+    } else {
+      for (int q = 0; q < kMaxProf; ++q)
+        if (q == p) {
+          if (is_free && del_free[q] > 0) {
+            del_free[q]--;
+            op = 2;
+          } else if (!is_free && del_used[q] > 0) {
+            del_used[q]--;
+            op = 2;
+          } else if (is_free && any_create) {  // re-created so that more creation orders are possible (:73-88)
+            again[q]++;
+            op = 3;
+          }
+        }
+    }
+    dev_op[d] = op;
+  }
+#pragma unroll
+  for (int p = 0; p < kMaxProf; ++p)
+    if (p < P) create_again[(size_t)g * P + p] = again[p];
+  matches[g] = same ? 1 : 0;
+}
+}  // namespace
+
+extern "C" int nosplan_diff_plan_mig_devices(nosplan_t* h, int n_gpus, int n_profiles, const int32_t* dev_off, const int32_t* dev_profile,
+                                             const uint8_t* dev_status, const int32_t* spec, const uint32_t* spec_mask, uint8_t* dev_op,
+                                             int32_t* create_new, int32_t* create_again, uint8_t* matches) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  if (n_gpus < 0 || n_profiles < 1 || n_profiles > NOSPLAN_MAX_MIG_PROFILES)
+    return fail(h, NOSPLAN_ERR_RANGE, "n_profiles %d out of range [1,%d]", n_profiles, NOSPLAN_MAX_MIG_PROFILES);
+  if (n_gpus == 0) return NOSPLAN_OK;
+  if (!dev_off || !spec || !spec_mask || !create_new || !create_again || !matches) return fail(h, NOSPLAN_ERR_ARG, "null argument");
+  if (dev_off[0] != 0) return fail(h, NOSPLAN_ERR_ARG, "dev_off[0] must be 0");
+  for (int g = 0; g < n_gpus; ++g)
+    if (dev_off[g + 1] < dev_off[g]) return fail(h, NOSPLAN_ERR_ARG, "dev_off not ascending at GPU %d", g);
+  const int nd = dev_off[n_gpus];
+  if (nd > 0 && (!dev_profile || !dev_status || !dev_op)) return fail(h, NOSPLAN_ERR_ARG, "null device arrays");
+  for (int d = 0; d < nd; ++d) {
+    if (dev_profile[d] < 0 || dev_profile[d] >= n_profiles) return fail(h, NOSPLAN_ERR_RANGE, "device %d: profile %d out of range", d, dev_profile[d]);
+    if (dev_status[d] > 2) return fail(h, NOSPLAN_ERR_RANGE, "device %d: status %d (0 used, 1 free, 2 unknown)", d, dev_status[d]);
+  }
+  int rc = bind(h);
+  if (rc) return rc;
+  cudaStream_t st = h->stream;
+  const size_t gp = (size_t)n_gpus * n_profiles * sizeof(int32_t);
+  if ((rc = upload(h, h->d_in[0], dev_off, sizeof(int32_t) * (n_gpus + 1), st))) return rc;
+  if ((rc = upload(h, h->d_in[1], dev_profile, sizeof(int32_t) * std::max(nd, 1), st))) return rc;
+  if ((rc = upload(h, h->d_in[2], spec, gp, st))) return rc;
+  if ((rc = upload(h, h->d_in[3], spec_mask, sizeof(uint32_t) * n_gpus, st))) return rc;
+  if ((rc = upload(h, h->d_in[4], dev_status, std::max(nd, 1), st))) return rc;
+  CU(h->d_out[0].reserve(gp));
+  CU(h->d_out[1].reserve(gp));
+  CU(h->d_out[2].reserve(std::max(nd, 1)));
+  CU(h->d_out[4].reserve(n_gpus));
+  mig_diff_devices_kernel<<<(n_gpus + 127) / 128, 128, 0, st>>>(
+      n_gpus, n_profiles, h->d_in[0].as<int32_t>(), h->d_in[1].as<int32_t>(), h->d_in[4].as<uint8_t>(), h->d_in[2].as<int32_t>(),
+      h->d_in[3].as<uint32_t>(), h->d_out[2].as<uint8_t>(), h->d_out[0].as<int32_t>(), h->d_out[1].as<int32_t>(), h->d_out[4].as<uint8_t>());
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(create_new, h->d_out[0].p, gp, cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(create_again, h->d_out[1].p, gp, cudaMemcpyDeviceToHost, st));
+  if (nd > 0) CU(cudaMemcpyAsync(dev_op, h->d_out[2].p, nd, cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(matches, h->d_out[4].p, n_gpus, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
   return NOSPLAN_OK;
 }

@@ -411,9 +411,6 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
 
   const int tid = threadIdx.x % TN;   // node of the tile
   const int dsub = threadIdx.x / TN;  // which share of the demand chunk
-  const int n = blockIdx.x * TN + tid;
-  const int cnt = (n < a.N) ? a.s_cnt[n] : 0;
-  const int g0 = (n < a.N) ? a.gpu_off[n] : 0;
   const int d_begin = blockIdx.y * a.d_chunk;
   const int32_t* rl = nullptr;
   int n_rows = a.D;
@@ -422,6 +419,14 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
     n_rows = a.row_meta[2];
     if (d_begin >= n_rows) return;  // uniform over the CTA, before any barrier
   }
+  // grid.x may be smaller than the number of tiles (a launch that usually finds no rows should not start one CTA per
+  // 128 nodes of a million-node list just to leave): the CTA then takes every gridDim.x-th tile
+  const int n_tiles = (a.N + TN - 1) / TN;
+  for (int tile_i = blockIdx.x; tile_i < n_tiles; tile_i += gridDim.x) {
+  if (tile_i != (int)blockIdx.x) __syncthreads();  // the previous tile's shared memory is still being read
+  const int n = tile_i * TN + tid;
+  const int cnt = (n < a.N) ? a.s_cnt[n] : 0;
+  const int g0 = (n < a.N) ? a.gpu_off[n] : 0;
   mig_tile_prologue<TN, DS, K16>(a, cw, tile, tid, dsub, n, cnt);
 
   const int d_end = min(n_rows, d_begin + a.d_chunk);
@@ -526,6 +531,7 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
     const unsigned wmin = __reduce_min_sync(0xffffffffu, mine);
     if (lane == 0 && wmin != 0xffffffffu) atomicMin(reinterpret_cast<unsigned*>(a.first_node) + d, wmin);
   }
+  }  // tiles of this CTA
 }
 
 // re-walks the winning node of every row to emit its per-GPU choices

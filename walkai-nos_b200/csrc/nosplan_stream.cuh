@@ -55,12 +55,15 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 
 // Persistent: the grid is a fixed number of CTAs; every warp walks the (work item, block of 32 nodes) pairs with a
 // stride of the grid's warp count, so the number of work items (only known on the device) costs no empty CTAs.
-template <int CW>
+// RS: rows of a work item (1, 2 or kStreamRows: a call with one row should not pay for four); GS: GPU slots per node as a
+// compile-time constant (8, the usual node: the copy loop's index arithmetic folds away) or 0 = read it from the arguments
+template <int CW, int RS, int GS>
 __global__ void __launch_bounds__(kStreamWarps * 32) mig_stream_kernel(const MigStreamArgs A) {
   extern __shared__ __align__(16) unsigned char smem[];
   constexpr int cw = CW;
+  constexpr int kStreamRows = RS;  // (shadows the namespace constant: the arrays below are sized for this instantiation)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int gs = A.gs;
+  const int gs = GS ? GS : A.gs;
   const int w2 = gs * cw;         // uint2 of rank table per node
   const int stride2 = w2 + 1;     // odd for the usual 8 x 3: 64-bit accesses of consecutive lanes hit distinct banks
   const MigTables* __restrict__ T = A.T;
@@ -86,9 +89,18 @@ __global__ void __launch_bounds__(kStreamWarps * 32) mig_stream_kernel(const Mig
     {
       const uint2* src = reinterpret_cast<const uint2*>(A.rankg) + (size_t)base * w2;
       const int tot = 32 * w2;
-      for (int i = lane; i < tot; i += 32) {
-        const int node = i / w2, j = i - node * w2;
-        cp_async8(s_rank_addr + (uint32_t)(node * stride2 + j) * 8u, src + i);
+      if constexpr (GS != 0) {
+#pragma unroll
+        for (int k = 0; k < GS * CW; ++k) {  // 32 * w2 / 32 copies per lane, every index a constant plus the lane
+          const int i = lane + 32 * k;
+          const int node = i / (GS * CW), j = i - node * (GS * CW);
+          cp_async8(s_rank_addr + (uint32_t)(node * (GS * CW + 1) + j) * 8u, src + i);
+        }
+      } else {
+        for (int i = lane; i < tot; i += 32) {
+          const int node = i / w2, j = i - node * w2;
+          cp_async8(s_rank_addr + (uint32_t)(node * stride2 + j) * 8u, src + i);
+        }
       }
     }
     if (item != cur_item) {  // the item's profile and rows (uniform over the warp)

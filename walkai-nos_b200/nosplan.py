@@ -31,7 +31,7 @@ EXPORTS = [
     "nosplan_score_mps_dev", "nosplan_mig_evals_per_demand", "nosplan_mps_evals_per_demand", "nosplan_score_mig_static", "nosplan_diff_plan_mig",
     "nosplan_set_node_base", "nosplan_exchange_create", "nosplan_exchange_open", "nosplan_exchange_min_dev",
     "nosplan_exchange_status", "nosplan_exchange_destroy", "nosplan_score_snapshot", "nosplan_presence",
-    "nosplan_score_pass_dev", "nosplan_pass_status", "nosplan_kernel_timing", "nosplan_kernel_time_ms", "nosplan_executed_evals",
+    "nosplan_diff_plan_mig_devices", "nosplan_score_pass_dev", "nosplan_pass_status", "nosplan_kernel_timing", "nosplan_kernel_time_ms", "nosplan_executed_evals",
 ]
 
 
@@ -328,6 +328,24 @@ class Planner:
         self._ck(self.L.nosplan_diff_plan_mig(self.h, G, P, _p(used, i32p), _p(free, i32p), _p(spec, i32p),
                                               _p(spec_mask, u32p), _p(create, i32p), _p(df, i32p), _p(du, i32p)))
         return create, df, du
+
+    def diff_plan_mig_devices(self, dev_off, dev_profile, dev_status, spec, spec_mask):
+        """plan.NewMigConfigPlan at device level (nosplan_diff_plan_mig_devices): returns dev_op [n_devices],
+        create_new / create_again [G][P], matches [G]."""
+        dev_off = np.ascontiguousarray(dev_off, np.int32)
+        G = len(dev_off) - 1
+        nd = int(dev_off[-1]) if G else 0
+        dev_profile = np.ascontiguousarray(dev_profile if nd else [0], np.int32)
+        dev_status = np.ascontiguousarray(dev_status if nd else [0], np.uint8)
+        spec = np.ascontiguousarray(spec, np.int32)
+        spec_mask = np.ascontiguousarray(spec_mask, np.uint32)
+        P = spec.shape[1]
+        op = np.zeros(max(nd, 1), np.uint8)
+        cn, ca = np.zeros((G, P), np.int32), np.zeros((G, P), np.int32)
+        m = np.zeros(max(G, 1), np.uint8)
+        self._ck(self.L.nosplan_diff_plan_mig_devices(self.h, G, P, _p(dev_off), _p(dev_profile), _p(dev_status), _p(spec), _p(spec_mask),
+                                                      _p(op), _p(cn), _p(ca), _p(m)))
+        return op[:nd], cn, ca, m[:G]
 
     # ---- device-resident (pointers are ints: torch tensor .data_ptr()) -------------------------------
     def score_mig_dev(self, D, off_ptr, key_ptr, qty_ptr, first_ptr, updated_ptr=0, choice_ptr=0, stream=0):
