@@ -1,5 +1,5 @@
 """-m gpu: the streaming MIG scorer (mig_stream_kernel: few rows, one thread per node in storage order, no CTA
-barrier) against the oracle.  It is what nosplan_score_mig / _dev run when a call has at most 24 rows, wants the
+barrier) against the oracle.  It is what nosplan_score_mig / _dev run when a call has at most 96 rows, wants the
 winners only and no node has more than 8 GPUs; the tests below stay inside that rule and check it really was taken
 by comparing with a child process that has the path switched off (NOSPLAN_STREAM_ROWS=0)."""
 import os
@@ -27,7 +27,7 @@ def test_stream_random_clusters(seed):
     p = pkg.Planner(0)
     try:
         o = T._load(p, cfg)
-        for D in (1, 2, 5, 13, 24):
+        for D in (1, 2, 5, 13, 24, 77):
             # single-key rows (the streaming kernel) and rows with 0..3 keys (the general kernel takes those of the call)
             k = rng.integers(0, len(cfg["names"]), size=D).astype(np.int32)
             q = rng.choice([1, 1, 2, 3, 7, 40, 300], size=D).astype(np.int32)
@@ -87,7 +87,7 @@ def test_stream_path_is_the_one_that_ran():
         "r = p.score_mig(off[:D + 1], key[:D], qty[:D], want_updated=False, want_choice=False)\n"
         "print('WIN', r['first_node'].tolist())\n" % ROOT)
     outs = []
-    for knob in ("24", "0"):
+    for knob in ("96", "0"):
         env = dict(os.environ, NOSPLAN_STREAM_ROWS=knob)
         r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=300)
         assert r.returncode == 0, r.stderr[-2000:]

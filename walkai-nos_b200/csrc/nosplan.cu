@@ -454,13 +454,15 @@ MigScore16Args mig16_args(nosplan_t* h, const MigScoreArgs& a) {
 }
 // The no-reuse regime (nosplan_stream.cuh): so few rows that a node's state is not worth staging for re-use.  The
 // rule (measured, profiles/r2_stream_sweep.md): winners only, at most 8 GPU slots per node, and at most
-// stream_rows() demand rows in the call — every kStreamRows rows of a profile cost one pass over the node list at HBM
-// speed, which beats the ordered kernel's tile staging until a profile has a few dozen rows.
+// stream_rows() = 96 demand rows in the call — every kStreamRows rows of a profile cost one pass over the node list at
+// HBM speed, which beats the ordered kernel's tile staging until a profile has about two dozen rows (1 M nodes, six
+// profiles: 0.41 against 1.50 ms at 24 rows, 1.32 against 1.76 ms at 96, 2.51 against 2.42 ms at 192; at 2 048 nodes
+// both forms take the same 20-30 us).
 int stream_rows() {  // measurement knob: NOSPLAN_STREAM_ROWS=n (0 = never stream)
   static const int v = [] {
     const char* e = std::getenv("NOSPLAN_STREAM_ROWS");
-    const int x = e ? std::atoi(e) : 24;
-    return x >= 0 ? x : 24;
+    const int x = e ? std::atoi(e) : 96;
+    return x >= 0 ? x : 96;
   }();
   return v;
 }
