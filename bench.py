@@ -194,6 +194,7 @@ def main():
     ap.add_argument("--pods", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-plan", action="store_true", help="skip the planner-latency section (profiling runs)")
+    ap.add_argument("--loopback-exchange", action="store_true", help="one GPU: open a one-rank exchange (measures what the exchange path costs without peers)")
     ap.add_argument("--shard-of", type=int, default=1, help="one GPU, rank 0's shard of a W-rank run (ncu captures of the shard sizes)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
@@ -255,6 +256,9 @@ def main():
             exchange = "nccl all-reduce (a peer could not map)"
             planner.exchange_destroy()
         planner.set_node_base(mig_lo, mps_lo)  # the scorers report global node indices
+    if world == 1 and args.loopback_exchange:
+        planner.exchange_open([planner.exchange_create(0, 1, max(Dall, 1))])
+        exchange = "one-rank loopback"
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
     PASS = pkg.nosplan.PASS_SINGLE_KEY  # every bench row has one key (checked on the device, nosplan_pass_status)

@@ -72,3 +72,36 @@ def test_static_scorer_rejects_sizes_beyond_its_fixed_array():
         assert e.value.code == -2
     finally:
         planner.close()
+
+
+def test_static_scorer_leaves_the_device_memory_pool_alone():
+    """The one promise of the entry point: no device memory is taken or given back by a call.  After a first call
+    (which loads the kernels' code and looks the fixed array's address up), the free-memory figure the driver reports
+    must be the same before and after further calls."""
+    import torch
+
+    import walkai_nos_b200 as pkg
+    planner = pkg.Planner(0)
+    try:
+        cfg = pkg.synth.make_config(5, 512, 800)
+        planner.set_mig_tables(cfg["names"], cfg["geom_off"], cfg["geom_counts"])
+        mig = cfg["mig"]
+        off, key, qty, _ = pkg.synth.pods_of_kind(cfg["pods"], 0)
+        D = len(off) - 1
+        dev = torch.device("cuda", 0)
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+        bufs = [t(mig[k]) for k in ("valid", "model", "used", "free")] + [t(off), t(key), t(qty)]
+        first = torch.empty(D, dtype=torch.int32, device=dev)
+        stream = torch.cuda.current_stream().cuda_stream
+        call = lambda: planner.score_mig_static(int(mig["n_nodes"]), 8, *[b.data_ptr() for b in bufs[:4]], D,
+                                                *[b.data_ptr() for b in bufs[4:]], first.data_ptr(), stream)
+        call()
+        torch.cuda.synchronize()
+        free0, _ = torch.cuda.mem_get_info(0)
+        for _ in range(5):
+            call()
+        torch.cuda.synchronize()
+        free1, _ = torch.cuda.mem_get_info(0)
+        assert free1 == free0
+    finally:
+        planner.close()

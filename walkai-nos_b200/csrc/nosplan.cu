@@ -96,6 +96,7 @@ struct nosplan {
   DevBuf d_dem[3];   // demand CSR
   DevBuf d_out[6];   // outputs
   DevBuf d_plan[32];
+  DevBuf d_rowok[2];                       // per kind: rows_check_kernel's verdict per row (scorers in input order)
   DevBuf d_status, d_rowstatus;            // d_rowstatus: one word per kind: grouping call number << 32 | ~(lowest bad row code)
   uint32_t row_call[2] = {0, 0};           // number of the kind's last grouping call
   unsigned long long* h_status = nullptr;  // pinned: [0..1] MIG pack status, [2..3] MPS pack status, [4..5] row status, [6] exchange
@@ -389,6 +390,31 @@ int plan_rows(nosplan_t* h, int kind, int D, int n_keys, int chunk, const int32_
   return NOSPLAN_OK;
 }
 
+// Scorers in input order: the rows are checked by a pre-pass instead (rows_check_kernel), which also rests first_node[].
+int check_rows(nosplan_t* h, int kind, int D, int n_keys, const int32_t* dem_off, const int32_t* dem_key, const int32_t* dem_qty,
+               int32_t* first_node, cudaStream_t st, const uint8_t** row_ok) {
+  CU(h->d_rowok[kind].reserve(std::max(D, 1)));
+  if (!h->d_rowstatus.p) {
+    CU(h->d_rowstatus.reserve(16));
+    CU(cudaMemsetAsync(h->d_rowstatus.p, 0, 16, st));
+  }
+  RowsGroupArgs g{};
+  g.D = D;
+  g.P = n_keys;
+  g.max_keys = NOSPLAN_MAX_DEMAND_KEYS;
+  g.max_qty = NOSPLAN_MAX_DEMAND_QTY;
+  g.dem_off = dem_off;
+  g.dem_key = dem_key;
+  g.dem_qty = dem_qty;
+  g.first_node = first_node;
+  g.status = h->d_rowstatus.as<unsigned long long>() + kind;
+  g.status_call = ++h->row_call[kind];
+  rows_check_kernel<<<(D + 255) / 256, 256, 0, st>>>(g, h->d_rowok[kind].as<uint8_t>());
+  CU(cudaGetLastError());
+  *row_ok = h->d_rowok[kind].as<uint8_t>();
+  return NOSPLAN_OK;
+}
+
 // ---- the ordered MIG scorer: instantiation, shared memory and row chunk for the handle's tables ------------------------
 struct Mig16Launch {
   void (*kern)(MigScore16Args) = nullptr;
@@ -573,7 +599,8 @@ int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
   if (D == 0) return NOSPLAN_OK;
   int rc = NOSPLAN_OK;
   const bool ordered = mig_ordered(h, D);
-  if (!ordered) fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, -1);  // else rows_group_kernel does it
+  const uint8_t* row_ok = nullptr;
+  if (!ordered && (rc = check_rows(h, 0, D, h->P, d_off, d_key, d_qty, d_first, st, &row_ok))) return rc;  // else rows_group_kernel does it
   if (d_choice) CU(cudaMemsetAsync(d_choice, 0xff, (size_t)D * h->mig_tg, st));
   if (h->mig_n > 0) {
     MigScoreArgs a{};
@@ -599,6 +626,7 @@ int launch_mig_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
     a.choice = d_choice;
     a.row_list = nullptr;
     a.row_meta = nullptr;
+    a.row_ok = row_ok;
     int tiles = (h->mig_n + kScoreTN - 1) / kScoreTN;
     int gy;
     pick_chunks(h->sm_count, tiles, D, 16, &a.d_chunk, &gy);
@@ -624,7 +652,11 @@ int launch_mps_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
                      int32_t* d_first, uint8_t* d_updated, uint8_t* d_free, uint32_t* d_mask, cudaStream_t st, int base = 0) {
   if (D == 0) return NOSPLAN_OK;
   const bool ordered = mps_ordered(h, D);
-  if (!ordered) fill_i32_kernel<<<(D + 255) / 256, 256, 0, st>>>(d_first, D, -1);  // else rows_group_kernel does it
+  const uint8_t* row_ok = nullptr;
+  if (!ordered) {  // else rows_group_kernel does it
+    int rc = check_rows(h, 1, D, h->S, d_off, d_key, d_qty, d_first, st, &row_ok);
+    if (rc) return rc;
+  }
   if (h->mps_n > 0) {
     MpsScoreArgs a{};
     a.sizes = h->d_mps_sizes.as<int32_t>();
@@ -644,6 +676,7 @@ int launch_mps_score(nosplan_t* h, int D, const int32_t* d_off, const int32_t* d
     a.out_free = d_free;
     a.out_mask = d_mask;
     a.gs = h->mps_gs;
+    a.row_ok = row_ok;
     int tiles = (h->mps_n + kScoreTN - 1) / kScoreTN;
     int gy;
     pick_chunks(h->sm_count, tiles, D, (ordered && !d_free) ? 128 : 16, &a.d_chunk, &gy,
@@ -747,6 +780,7 @@ void nosplan_destroy(nosplan_t* h) {
   if (h->status_ev2) cudaEventDestroy(h->status_ev2);
   if (h->h_pin) cudaFreeHost(h->h_pin);
   for (auto& b : h->d_inp) b.release();
+  for (auto& b : h->d_rowok) b.release();
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
   if (h->ev_join) cudaEventDestroy(h->ev_join);
   for (auto& kind : h->kev)
@@ -2014,7 +2048,8 @@ static __device__ __align__(256) unsigned char g_static_scratch[sizeof(StaticScr
 
 constexpr int kMaxDevices = 64;
 struct StaticSetup {
-  bool ready = false;
+  std::once_flag once;  // first calls on a device may come from different handles on different threads
+  cudaError_t rc = cudaSuccess;
   StaticScratch* ptr = nullptr;
 };
 StaticSetup g_static_setup[kMaxDevices];
@@ -2050,13 +2085,14 @@ __global__ void static_pack_kernel(StaticScratch* sc, int N, int P, int G, int n
 int static_scratch_for(nosplan_t* h, StaticScratch** out) {
   if (h->device < 0 || h->device >= kMaxDevices) return fail(h, NOSPLAN_ERR_RANGE, "device ordinal %d not supported", h->device);
   StaticSetup& st = g_static_setup[h->device];
-  if (!st.ready) {
-    // once per device, with that device current (bind() ran): the symbol's address on THIS device
+  // once per device, with that device current (bind() ran): the symbol's address on THIS device
+  std::call_once(st.once, [&st] {
     void* p = nullptr;
-    CU(cudaGetSymbolAddress(&p, g_static_scratch));
+    st.rc = cudaGetSymbolAddress(&p, g_static_scratch);
     st.ptr = reinterpret_cast<StaticScratch*>(p);
-    st.ready = true;
-  }
+  });
+  if (st.rc != cudaSuccess || !st.ptr)
+    return fail(h, NOSPLAN_ERR_CUDA, "cudaGetSymbolAddress(static scratch) failed: %s", cudaGetErrorString(st.rc));
   *out = st.ptr;
   return NOSPLAN_OK;
 }
@@ -2092,7 +2128,7 @@ extern "C" int nosplan_score_mig_static(nosplan_t* h, int n_nodes, int gpus_per_
   if (n_nodes > 0) {
     const int threads = std::max(npad, n_nodes + 1);
     static_pack_kernel<<<(threads + 127) / 128, 128, 0, st>>>(sc, n_nodes, h->P, gpus_per_node, npad, valid, model, used, free_);
-    MigScoreArgs a;
+    MigScoreArgs a{};
     a.T = h->d_tables.as<MigTables>();
     a.s_used = &sc->s_used[0][0];
     a.s_free = &sc->s_free[0][0];

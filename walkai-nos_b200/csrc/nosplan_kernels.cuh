@@ -244,6 +244,7 @@ struct MigScoreArgs {
   // optional: score only the rows row_list[row_meta[1] .. + row_meta[2]) (device-side list and counts)
   const int32_t* row_list;
   const int32_t* row_meta;
+  const uint8_t* row_ok;  // optional: rows_check_kernel's verdict per row (0 = breaks an ABI limit: skipped)
 };
 
 // Shared-memory layout of one tile (TN nodes, gs GPU slots, cw = ceil(cmax/4) words of 4 candidates):
@@ -438,6 +439,7 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
   asm("mov.u32 %0, 512;" : "=r"(k512));
   for (int di = d_begin + dsub; di < d_end; di += DS) {
     const int d = rl ? rl[di] : di;
+    if (a.row_ok && !a.row_ok[d]) continue;  // uniform over the CTA
     const int e0 = __ldg(a.dem_off + d), k = __ldg(a.dem_off + d + 1) - e0;  // uniform over the CTA
     bool any = false;
     if (k == 1) {
@@ -825,6 +827,7 @@ struct MpsScoreArgs {
   const int32_t* rows;
   const int32_t* work;
   const int32_t* meta;
+  const uint8_t* row_ok;        // optional: rows_check_kernel's verdict per row (0 = breaks an ABI limit: skipped)
   PushArgs push;                // mps_score1_kernel: where the per-row winners go
   unsigned long long* counter;  // its CNT instantiation: (row, node, GPU) runs that reached the closed form
 };
@@ -897,6 +900,7 @@ __global__ void __launch_bounds__(TN * DS, 3) mps_score_kernel(const MpsScoreArg
   const int lane = threadIdx.x & 31;
   for (int i = dsub; i < rlen; i += DS) {
     const int d = rl ? rl[i] : r0 + i;
+    if (a.row_ok && !a.row_ok[d]) continue;  // uniform over the CTA
     const int e0 = __ldg(a.dem_off + d), k = __ldg(a.dem_off + d + 1) - e0;
     bool any = false;
     if (k == 1 && !a.out_free) {

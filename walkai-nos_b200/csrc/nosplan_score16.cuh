@@ -200,6 +200,44 @@ struct RowsGroupArgs {
 };
 constexpr int kSubNotSingle = 62;
 
+// The ABI's limits on one demand row: -1 = fine, else the sub code (0: dem_off descending, 1: too many keys,
+// 2 + 3j / 3 + 3j / 4 + 3j: key j out of range / not ascending / quantity out of range, kSubNotSingle).
+__device__ __forceinline__ int row_check_sub(const RowsGroupArgs& g, int d, int* k_out, int* key0_out) {
+  const int e0 = __ldg(g.dem_off + d), k = __ldg(g.dem_off + d + 1) - e0, nnz = __ldg(g.dem_off + g.D);
+  *k_out = k;
+  *key0_out = 0;
+  if (k < 0 || e0 < 0 || e0 + k > nnz) return 0;  // entries outside [0, dem_off[D]) are never read
+  if (k > g.max_keys) return 1;
+  int prev = -1;
+  for (int j = 0; j < k; ++j) {
+    const int key = __ldg(g.dem_key + e0 + j), q = __ldg(g.dem_qty + e0 + j);
+    if (key < 0 || key >= g.P) return 2 + 3 * j;
+    if (j > 0 && key <= prev) return 3 + 3 * j;
+    if (q < 0 || q > g.max_qty) return 4 + 3 * j;
+    if (j == 0) *key0_out = key;
+    prev = key;
+  }
+  if (g.single_only && k != 1) return kSubNotSingle;
+  return -1;
+}
+__device__ __forceinline__ void row_report(const RowsGroupArgs& g, int d, int sub) {
+  // the lowest code of this call wins: codes are stored inverted under the call number
+  atomicMax(g.status, ((unsigned long long)g.status_call << 32) | (unsigned long long)(0xffffffffu - ((uint32_t)d * 64u + (uint32_t)sub)));
+}
+
+// The scorers that take the rows in input order (wide tables, NOSPLAN_PLAIN_ORDER) get the same check as a
+// pre-pass: row_ok[d] = 1 for a row inside the limits (the kernels skip the others: their winner stays -1, nothing
+// of them is indexed), the first bad row lands in *status, first_node[] is put to rest.
+__global__ void rows_check_kernel(const RowsGroupArgs g, uint8_t* __restrict__ row_ok) {
+  const int d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= g.D) return;
+  if (g.first_node) g.first_node[d] = -1;
+  int k, key0;
+  const int sub = row_check_sub(g, d, &k, &key0);
+  row_ok[d] = sub < 0 ? 1 : 0;
+  if (sub >= 0) row_report(g, d, sub);
+}
+
 // block = index of this CTA among the n_blocks CTAs that group this kind's rows
 __device__ __forceinline__ void rows_group_body(const RowsGroupArgs& g, int block, int n_blocks) {
   __shared__ int s_last;
@@ -210,27 +248,9 @@ __device__ __forceinline__ void rows_group_body(const RowsGroupArgs& g, int bloc
   int b = kNoRow;
   if (d < D) {
     if (g.first_node) g.first_node[d] = -1;  // "no node"; the scorers fold winners in with an unsigned atomicMin
-    const int e0 = __ldg(g.dem_off + d), k = __ldg(g.dem_off + d + 1) - e0, nnz = __ldg(g.dem_off + D);
-    int sub = -1, key0 = 0;
-    if (k < 0 || e0 < 0 || e0 + k > nnz) {  // entries outside [0, dem_off[D]) are never read
-      sub = 0;
-    } else if (k > g.max_keys) {
-      sub = 1;
-    } else {
-      int prev = -1;
-      for (int j = 0; j < k; ++j) {
-        const int key = __ldg(g.dem_key + e0 + j), q = __ldg(g.dem_qty + e0 + j);
-        if (key < 0 || key >= P) sub = 2 + 3 * j;
-        else if (j > 0 && key <= prev) sub = 3 + 3 * j;
-        else if (q < 0 || q > g.max_qty) sub = 4 + 3 * j;
-        if (sub >= 0) break;
-        if (j == 0) key0 = key;
-        prev = key;
-      }
-      if (sub < 0 && g.single_only && k != 1) sub = kSubNotSingle;
-    }
-    if (sub >= 0)  // the lowest code of this call wins: codes are stored inverted under the call number
-      atomicMax(g.status, ((unsigned long long)g.status_call << 32) | (unsigned long long)(0xffffffffu - ((uint32_t)d * 64u + (uint32_t)sub)));
+    int k, key0;
+    const int sub = row_check_sub(g, d, &k, &key0);
+    if (sub >= 0) row_report(g, d, sub);
     else b = k == 1 ? key0 : P;
   }
   const uint32_t peers = __match_any_sync(0xffffffffu, b);  // one atomic per bucket per warp
