@@ -98,7 +98,7 @@ class ClockSampler(threading.Thread):
                     self._sample_smi()
             except Exception:
                 pass
-            time.sleep(0.05 if self.nvml else 0.2)
+            time.sleep(0.02 if self.nvml else 0.2)
 
     def summary(self):
         if not self.rows:
@@ -359,7 +359,12 @@ def main():
     tt = torch.tensor([total_ms, (mig_ms + mps_ms) / max(mig_n, 1), 0.0, mig_alone_ms / max(mig_alone_n, 1),
                        mps_alone_ms / max(mps_alone_n, 1)], dtype=torch.float64, device=dev)
     evt = torch.tensor([float(ev_m_local), float(ev_p_local), float(ex_m), float(ex_p)], dtype=torch.float64, device=dev)
+    per_rank = None
     if world > 1:
+        allt = [torch.zeros_like(tt) for _ in range(world)]
+        dist.all_gather(allt, tt)
+        per_rank = {"step_ms": [float(x[0]) / args.steps for x in allt], "scoring_launch_ms": [float(x[1]) for x in allt],
+                    "mig_alone_ms": [float(x[3]) for x in allt], "mps_alone_ms": [float(x[4]) for x in allt]}
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dist.all_reduce(evt, op=dist.ReduceOp.SUM)
     total_ms, both_k_ms, _, mig_k_alone_ms, mps_k_alone_ms = (float(x) for x in tt.tolist())
@@ -543,6 +548,7 @@ def main():
                                   "xchg_finish_kernel": 1 if (world > 1 and exchange.startswith("peer")) else 0},
             "exchange": exchange,
             "sharded_parity": sharded_parity,
+            "per_rank": per_rank,
             "planner_latency_ms_p50": float(np.median(lat)) if lat else None,
             "planner_latency_ms_p95": float(np.percentile(lat, 95)) if lat else None,
             "planner_latency_gate_off_ms_p50": float(np.median(lat_off)) if lat_off else None,

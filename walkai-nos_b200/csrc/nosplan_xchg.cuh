@@ -33,6 +33,12 @@ struct XchgPeers {
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+// a flag store that follows ONE __threadfence_system(): the fence orders everything before it system-wide, the stores
+// themselves are then posted back to back (a release store per peer would drain the write path once per peer: 8 peers
+// cost 17 us at the end of the last scorer CTA)
+__device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   uint32_t v;
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -84,7 +90,7 @@ __device__ __forceinline__ void push_finish(const PushArgs& P) {
     if (prev == P.total - 1u) {  // every CTA's winners are ordered before this point
       *P.ticket = 0;
       __threadfence_system();
-      for (int r = 0; r < P.world; ++r) st_release_sys(P.flags[r] + P.rank, P.step);
+      for (int r = 0; r < P.world; ++r) st_relaxed_sys(P.flags[r] + P.rank, P.step);
     }
   }
 }
@@ -104,7 +110,7 @@ __global__ void xchg_publish_kernel(XchgPeers P, int world, int rank, int max_ke
     if (prev == gridDim.x - 1) {
       *done = 0;
       __threadfence_system();
-      for (int r = 0; r < world; ++r) st_release_sys(P.pushed[r] + rank, step);
+      for (int r = 0; r < world; ++r) st_relaxed_sys(P.pushed[r] + rank, step);
     }
   }
 }
@@ -117,14 +123,20 @@ __global__ void xchg_finish_kernel(XchgPeers P, int world, int rank, int max_key
   const size_t half = (size_t)(step & 1u) * (size_t)max_keys;  // max_keys is a multiple of 4: halves stay 16-byte aligned
   const int n4 = n >> 2;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * blockDim.x) {
+    // all ranks' loads are issued before the first one is used: one NVLink round trip per thread, not one per rank
+    uint4 v[kMaxWorld];
+#pragma unroll
+    for (int r = 0; r < kMaxWorld; ++r)
+      if (r < world) v[r] = ld_relaxed_sys_v4(reinterpret_cast<const uint4*>(P.keys[r] + half) + i);
     uint4 m = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
-    for (int r = 0; r < world; ++r) {
-      const uint4 v = ld_relaxed_sys_v4(reinterpret_cast<const uint4*>(P.keys[r] + half) + i);
-      m.x = min(m.x, v.x);
-      m.y = min(m.y, v.y);
-      m.z = min(m.z, v.z);
-      m.w = min(m.w, v.w);
-    }
+#pragma unroll
+    for (int r = 0; r < kMaxWorld; ++r)
+      if (r < world) {
+        m.x = min(m.x, v[r].x);
+        m.y = min(m.y, v[r].y);
+        m.z = min(m.z, v[r].z);
+        m.w = min(m.w, v[r].w);
+      }
     reinterpret_cast<uint4*>(out)[i] = m;  // 0xffffffff == -1: no rank had a node
   }
   for (int d = (n4 << 2) + blockIdx.x * blockDim.x + threadIdx.x; d < n; d += gridDim.x * blockDim.x) {
@@ -139,7 +151,7 @@ __global__ void xchg_finish_kernel(XchgPeers P, int world, int rank, int max_key
     if (prev == gridDim.x - 1) {  // every block has read: the peers may re-use this half two steps from now
       done[1] = 0;
       __threadfence_system();
-      for (int r = 0; r < world; ++r) st_release_sys(P.read[r] + rank, step);
+      for (int r = 0; r < world; ++r) st_relaxed_sys(P.read[r] + rank, step);
     }
   }
 }
