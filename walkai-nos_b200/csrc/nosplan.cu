@@ -15,6 +15,8 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "nosplan.h"
 #include "nosplan_kernels.cuh"
 #include "nosplan_plan.cuh"
@@ -26,6 +28,15 @@
 using namespace nsp;
 
 namespace {
+
+// NVTX range around a phase of an ABI call (shows up in Nsight Systems / ncu --nvtx; costs nothing without a tool)
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
+#define NSP_RANGE(name) NvtxRange nsp_range_##__LINE__(name)
 
 // grow-only device buffer
 struct DevBuf {
@@ -889,6 +900,7 @@ namespace {
 // status and either confirms the snapshot or drops it.
 int mig_snapshot_enqueue(nosplan_t* h, int n_nodes, const int32_t* gpu_off, const uint8_t* valid, const int32_t* model,
                          const int32_t* used, const int32_t* free_, cudaStream_t st) {
+  NSP_RANGE("nosplan: MIG snapshot upload + pack");
   if (!h->have_tables) return fail(h, NOSPLAN_ERR_ARG, "nosplan_set_mig_tables must be called first");
   if (n_nodes < 0 || !gpu_off) return fail(h, NOSPLAN_ERR_ARG, "bad node list");
   const int P = h->P;
@@ -972,6 +984,7 @@ int mig_snapshot_enqueue(nosplan_t* h, int n_nodes, const int32_t* gpu_off, cons
   return NOSPLAN_OK;
 }
 int mig_snapshot_finish(nosplan_t* h, const int32_t* model, const int32_t* used, const int32_t* free_) {
+  NSP_RANGE("nosplan: MIG snapshot verdict");
   unsigned long long st[2] = {~0ull, 0ull};
   int rc = status_wait(h, 0, st);
   if (rc) return rc;
@@ -991,6 +1004,7 @@ int mig_snapshot_finish(nosplan_t* h, const int32_t* model, const int32_t* used,
 int mps_snapshot_enqueue(nosplan_t* h, int n_sizes, const int32_t* sizes_gb, int n_nodes, const int32_t* gpu_off,
                          const uint8_t* valid, const int32_t* mem_gb, const int32_t* used, const int32_t* free_,
                          const uint32_t* free_mask, cudaStream_t st) {
+  NSP_RANGE("nosplan: MPS snapshot upload + pack");
   if (n_sizes < 1 || n_sizes > NOSPLAN_MAX_MPS_SIZES || !sizes_gb)
     return fail(h, NOSPLAN_ERR_RANGE, "n_sizes %d out of range [1,%d]", n_sizes, NOSPLAN_MAX_MPS_SIZES);
   for (int s = 0; s < n_sizes; ++s) {
@@ -1065,6 +1079,7 @@ int mps_snapshot_enqueue(nosplan_t* h, int n_sizes, const int32_t* sizes_gb, int
   return NOSPLAN_OK;
 }
 int mps_snapshot_finish(nosplan_t* h, const int32_t* sizes_gb, const int32_t* mem_gb, const int32_t* used, const int32_t* free_) {
+  NSP_RANGE("nosplan: MPS snapshot verdict");
   unsigned long long st[2] = {~0ull, 0ull};
   int rc = status_wait(h, 1, st);
   if (rc) return rc;
@@ -1221,6 +1236,7 @@ void (*both_kernel_of(int tn, int cw, bool cnt))(MigScore16Args, MpsScoreArgs, i
 int score_pass_enqueue(nosplan_t* h, nosplan_t* x, int Dm, const int32_t* m_off, const int32_t* m_key, const int32_t* m_qty, int Dp,
                        const int32_t* p_off, const int32_t* p_key, const int32_t* p_qty, int32_t* first_node, int flags,
                        cudaStream_t st) {
+  NSP_RANGE("nosplan: scoring pass (group, score, exchange)");
   const bool have_m = Dm > 0 && h->have_mig, have_p = Dp > 0 && h->have_mps;
   int32_t* first_m = first_node;
   int32_t* first_p = first_node + Dm;
@@ -1477,6 +1493,7 @@ int nosplan_score_mig(nosplan_t* h, int n_demands, const int32_t* dem_off, const
                       const int32_t* dem_qty, int32_t* first_node, int8_t* first_choice, uint8_t* updated, int8_t* choice,
                       int64_t* n_evals) {
   if (!h) return NOSPLAN_ERR_ARG;
+  NSP_RANGE("nosplan_score_mig");
   h->err.clear();
   if (!h->have_mig) return fail(h, NOSPLAN_ERR_ARG, "no MIG snapshot");
   // with the rows-by-key scorer the rows are validated on the device while they are grouped
@@ -1529,6 +1546,7 @@ int nosplan_score_mps(nosplan_t* h, int n_demands, const int32_t* dem_off, const
                       const int32_t* dem_qty, int32_t* first_node, uint8_t* updated, uint8_t* out_free,
                       uint32_t* out_free_mask, int64_t* n_evals) {
   if (!h) return NOSPLAN_ERR_ARG;
+  NSP_RANGE("nosplan_score_mps");
   h->err.clear();
   if (!h->have_mps) return fail(h, NOSPLAN_ERR_ARG, "no MPS snapshot");
   if ((out_free == nullptr) != (out_free_mask == nullptr)) return fail(h, NOSPLAN_ERR_ARG, "out_free and out_free_mask go together");
@@ -1619,6 +1637,8 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
   if (rc) return rc;
   const bool trace = trace_on();
   const auto t_begin = std::chrono::steady_clock::now();
+  NSP_RANGE("nosplan_plan");
+  nvtxRangePushA("nosplan_plan: host split of the pod list");
   // split by kind (order kept) and deduplicate request vectors: pods with the same vector share a row
   struct Side {
     std::vector<int32_t> pod_idx, pod_sig, off{0}, key, qty;
@@ -1676,6 +1696,8 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
     s.pod_sig.push_back(id);
   }
   const auto t_split = std::chrono::steady_clock::now();
+  nvtxRangePop();
+  NvtxRange enqueue_range("nosplan_plan: chains / sequencer");
   // reset the working state to the snapshot
   if (h->have_mig && h->mig_tg) {
     CU(cudaMemcpyAsync(h->d_mig_used.p, h->d_mig_used0.p, sizeof(uint4) * h->mig_tg, cudaMemcpyDeviceToDevice, h->stream));
@@ -2457,6 +2479,7 @@ extern "C" int nosplan_exchange_min_dev(nosplan_t* h, int n_keys, const int32_t*
   int rc = bind(h);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
+  NSP_RANGE("nosplan: first-node exchange");
   const uint32_t step = ++x.step;
   const int blocks = std::max(1, std::min((n_keys + 255) / 256, h->sm_count));
   xchg_publish_kernel<<<blocks, 256, 0, st>>>(x.peers, x.world, x.rank, x.stride, step, n_keys, keys_in, x.done.as<unsigned int>(),
@@ -2543,6 +2566,7 @@ extern "C" int nosplan_score_snapshot(nosplan_t* h, const nosplan_mig_snapshot_t
   if (!h) return NOSPLAN_ERR_ARG;
   h->err.clear();
   if (n_evals) *n_evals = 0;
+  NSP_RANGE("nosplan_score_snapshot");
   if (mig && !h->have_tables) return fail(h, NOSPLAN_ERR_ARG, "nosplan_set_mig_tables must be called first");
   if ((mig && (!mig_rows || (mig_rows->n_rows > 0 && !mig_first_node))) || (mps && (!mps_rows || (mps_rows->n_rows > 0 && !mps_first_node))))
     return fail(h, NOSPLAN_ERR_ARG, "a snapshot needs its demand rows and an output array");

@@ -9,6 +9,16 @@
 
 #include "nosplan.h"
 
+// -DNOSPLAN_CHECKS: every index into a fixed-size local or shared array, and every table index read from memory, is
+// asserted on the device (compute-sanitizer is closed on the pool this was developed on: tools/run_checked.sh runs the
+// parity suites on such a build instead; a failed assertion aborts the kernel and the C ABI reports the CUDA error).
+#ifdef NOSPLAN_CHECKS
+#include <cassert>
+#define NSP_CHECK(c) assert(c)
+#else
+#define NSP_CHECK(c) ((void)0)
+#endif
+
 namespace nsp {
 
 constexpr int kMaxProf = NOSPLAN_MAX_MIG_PROFILES;               // 16 bytes = one uint4 per map
@@ -46,6 +56,7 @@ struct MigTables {
 };
 
 __device__ __forceinline__ uint32_t byte_of(const uint4& v, int i) {
+  NSP_CHECK(i >= 0 && i < 16);
   uint32_t w = (i < 8) ? ((i < 4) ? v.x : v.y) : ((i < 12) ? v.z : v.w);
   return (w >> ((i & 3) * 8)) & 0xffu;
 }
@@ -93,6 +104,8 @@ __device__ inline bool mig_walk_node(const MigTables* __restrict__ T, const uint
                                      const uint8_t* __restrict__ model, int g0, int cnt, int k,
                                      const int* __restrict__ pid, const int* __restrict__ qty, bool commit,
                                      int8_t* choice) {
+  NSP_CHECK(k >= 0 && k <= kMaxKeys);
+  NSP_CHECK(cnt >= 0 && (choice == nullptr || cnt <= NOSPLAN_MAX_GPUS_PER_NODE));
   int resid[kMaxKeys];
 #pragma unroll
   for (int j = 0; j < kMaxKeys; ++j) resid[j] = (j < k) ? max(qty[j], 0) : 0;
@@ -104,6 +117,7 @@ __device__ inline bool mig_walk_node(const MigTables* __restrict__ T, const uint
     const uint4 f = ld_state<CG>(fr + g);
     const uint4 cur = add4(u, f);  // GetGeometry, gpu.go:84-95
     const int m = model[g];
+    NSP_CHECK(m >= 0 && m < T->n_models);
     const int c0 = T->geom_off[m], c1 = T->geom_off[m + 1];
     int best = -1;
     uint32_t best_prov = 0, best_k0 = 0;
@@ -318,7 +332,9 @@ __device__ __forceinline__ void mig_tile_prologue(const MigScoreArgs& a, int cw,
     const uint4 f = a.s_free[(size_t)s * a.npad + n];
     const int m = a.s_model[(size_t)s * a.npad + n];
     const uint4 cur = add4(u, f);
+    NSP_CHECK(m >= 0 && m < T->n_models);
     const int c0 = T->geom_off[m], cc = T->geom_off[m + 1] - c0;
+    NSP_CHECK(cc >= 0 && cc <= kMaxGeoms && cc <= 4 * cw);
     s_model[s * TN + tid] = (uint8_t)m;
 #pragma unroll
     for (int q = 0; q < 16; ++q) s_uf[(s * 16 + q) * TN + tid] = (uint16_t)(byte_of(f, q) | (byte_of(cur, q) << 8));
@@ -355,9 +371,11 @@ __device__ __forceinline__ bool mig_row_generic(const MigScoreArgs& a, int cw, c
   const uint16_t* s_uf = t.uf;
   const uint8_t* s_model = t.model;
   bool any = false;
+  NSP_CHECK(k >= 0 && k <= kMaxKeys);
   int pid[kMaxKeys], resid[kMaxKeys];
   for (int j = 0; j < kMaxKeys; ++j) {
     pid[j] = (j < k) ? __ldg(a.dem_key + e0 + j) : 0;
+    NSP_CHECK(pid[j] >= 0 && pid[j] < 16);
     resid[j] = (j < k) ? max(__ldg(a.dem_qty + e0 + j), 0) : 0;
   }
   for (int s = 0; s < cnt; ++s) {
@@ -447,6 +465,7 @@ __global__ void __launch_bounds__(TN * DS) mig_score_kernel(const MigScoreArgs a
       // Every candidate of every GPU is evaluated: provided = clamp(cand[p]-cur[p], 0, needed), then a
       // (provided, rank, lowest index) compare folded into one integer max.
       const int p = __ldg(a.dem_key + e0);
+      NSP_CHECK(p >= 0 && p < 16);
       int resid = max(__ldg(a.dem_qty + e0), 0);
       // running pointers: one add per slot instead of re-deriving every shared-memory address
       const uint16_t* uf = s_uf + (size_t)p * TN + tid;
@@ -604,6 +623,7 @@ struct MpsGpu {
 };
 
 __device__ __forceinline__ uint32_t mps_byte(const uint4& lo, const uint4& hi, int i) {
+  NSP_CHECK(i >= 0 && i < 32);
   return i < 16 ? byte_of(lo, i) : byte_of(hi, i - 16);
 }
 
@@ -616,9 +636,11 @@ __device__ __forceinline__ uint32_t mps_byte(const uint4& lo, const uint4& hi, i
 __device__ inline bool mps_gpu_update(const int* __restrict__ sz, const uint4& f0, const uint4& f1, uint32_t origmask,
                                       uint32_t cap, int k, const int* sid, const int* resid, int* created,
                                       uint32_t* restored_out) {
+  NSP_CHECK(k >= 0 && k <= kMaxKeys);
   int miss[kMaxKeys];
   bool any_missing = false;
   for (int j = 0; j < k; ++j) {
+    NSP_CHECK(sid[j] >= 0 && sid[j] < kMaxSizes);
     created[j] = 0;
     const int fj = (int)mps_byte(f0, f1, sid[j]);  // a present key holds its byte, an absent one 0
     miss[j] = max(resid[j] - fj, 0);               // getMissingSlices, :222-232
@@ -680,6 +702,7 @@ template <bool CG = false>
 __device__ inline bool mps_walk_node(const int* __restrict__ sz, int S, MpsGpu* gp, int g0, int cnt, int k,
                                      const int* __restrict__ sid, const int* __restrict__ qty, bool commit,
                                      uint8_t* out_free, uint32_t* out_mask) {
+  NSP_CHECK(k >= 0 && k <= kMaxKeys && S >= 0 && S <= kMaxSizes);
   int resid[kMaxKeys];
   for (int j = 0; j < kMaxKeys; ++j) resid[j] = (j < k) ? max(qty[j], 0) : 0;
   bool any = false;

@@ -166,6 +166,7 @@ template <bool MPS, int NQ>
 __global__ void __launch_bounds__(32) plan_chain_kernel(ChainArgs a) {
   const int c = blockIdx.x, lane = threadIdx.x;
   const int key = a.chain_key[c];
+  NSP_CHECK(key >= 0 && key < a.n_keys);
   int j0 = a.chain_off[c], j1 = a.chain_off[c + 1];
   {  // the chain's pods inside [range[0], range[1]): chain_pod is ascending
     const int lo = a.range[0], hi = a.range[1];
@@ -299,6 +300,7 @@ __global__ void __launch_bounds__(32) plan_chain_kernel(ChainArgs a) {
             if (pv <= j) lo += step;
           }
           lo = min(lo, 31);
+          NSP_CHECK(!mine || (pod32 >= 0 && pod32 < a.M));
           const int node = __shfl_sync(0xffffffffu, wnode[t], lo);
           const int slot = __shfl_sync(0xffffffffu, wslot[t], lo);
           if (mine) {

@@ -258,6 +258,7 @@ __device__ __forceinline__ void rows_group_body(const RowsGroupArgs& g, int bloc
   int base = 0;
   if (b != kNoRow && lane == leader) base = atomicAdd(&g.state[b], __popc(peers));
   base = __shfl_sync(0xffffffffu, base, leader);
+  NSP_CHECK(b == kNoRow || (b >= 0 && b <= P && base + __popc(peers & ((1u << lane) - 1u)) < D));
   if (b != kNoRow) g.rows[(size_t)b * D + base + __popc(peers & ((1u << lane) - 1u))] = d;
   __threadfence();
   __syncthreads();
@@ -378,6 +379,7 @@ __device__ __forceinline__ void mig_score16_body(const MigScore16Args& A, const 
   const int p = A.work[3 * bx + 0];
   const int r0 = A.work[3 * bx + 1];
   const int len = A.work[3 * bx + 2];
+  NSP_CHECK(p >= 0 && p < 16 && len >= 0 && len <= kRowCap && r0 >= 0);
   const int tid = threadIdx.x % TN;
   const int dsub = threadIdx.x / TN;
   const int pos = by * TN + tid;
@@ -595,6 +597,7 @@ __device__ __forceinline__ void mps_score1_body(const MpsScoreArgs& a, const int
   const int sid = a.work[3 * bx];
   const int32_t* rl = a.rows + a.work[3 * bx + 1];
   const int len = a.work[3 * bx + 2];
+  NSP_CHECK(sid >= 0 && sid < a.S && len >= 0 && len <= kRowCap);
   const int tid = threadIdx.x % TN;
   const int dsub = threadIdx.x / TN;
   const int pos = by * TN + tid;

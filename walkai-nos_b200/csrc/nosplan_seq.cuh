@@ -29,7 +29,12 @@ constexpr int kSeqThreads = 256;
 // Out of line on purpose: when the MPS per-GPU update was inlined into a sequencer that keeps a request
 // vector in local arrays, nvcc 12.9 overlaid the callee's scratch arrays with the caller's (the
 // caller's key[] read back as 0 after the call).  A real call gives it its own frame.
-__device__ __noinline__ bool seq_mps_gpu_update(const int* sz, uint4 f0, uint4 f1, uint32_t origmask, uint32_t cap, int k,
+#ifdef NOSPLAN_SEQ_INLINE  // (tools/run_checked.sh builds this variant to look for the effect described above)
+__device__ __forceinline__
+#else
+__device__ __noinline__
+#endif
+bool seq_mps_gpu_update(const int* sz, uint4 f0, uint4 f1, uint32_t origmask, uint32_t cap, int k,
                                                 const int* sid, const int* resid, int* created, uint32_t* restored) {
   return mps_gpu_update(sz, f0, f1, origmask, cap, k, sid, resid, created, restored);
 }
@@ -375,9 +380,11 @@ __global__ void __launch_bounds__(kSeqThreads, 1) plan_seq_kernel(const SeqArgs 
     }
     const int e0 = __shfl_sync(0xffffffffu, e0_32, i & 31), k = __shfl_sync(0xffffffffu, k_32, i & 31);
     __syncwarp();
+    NSP_CHECK(k >= 0 && k <= kMaxKeys);
     if (lane < kMaxKeys) {
       key[lane] = lane < k ? __ldg(a.dem_key + e0 + lane) : 0;
       qty[lane] = lane < k ? __ldg(a.dem_qty + e0 + lane) : 0;
+      NSP_CHECK(key[lane] >= 0 && key[lane] < K);
     }
     __syncwarp();
     uint32_t reqmask = 0;   // keys with a positive quantity
@@ -420,7 +427,9 @@ __global__ void __launch_bounds__(kSeqThreads, 1) plan_seq_kernel(const SeqArgs 
         }
         SEQ_TICK(0)
         if (best >= 0) {
+          NSP_CHECK(best < a.N);
           const int g0 = __ldg(a.gpu_off + best), cnt = __ldg(a.gpu_off + best + 1) - g0;
+          NSP_CHECK(cnt >= 0 && cnt <= NOSPLAN_MAX_GPUS_PER_NODE && g0 >= 0 && g0 + cnt <= a.tg);
           load_node(g0, cnt);
           const int before = node_sum(cnt);
           SEQ_TICK(1)
@@ -492,6 +501,7 @@ __global__ void __launch_bounds__(kSeqThreads, 1) plan_seq_kernel(const SeqArgs 
                 int created[kMaxKeys];
                 uint32_t restored = r[16];
                 const bool upd = seq_mps_gpu_update(sh_sz, f0, f1, r[16], r[17], k, key, resid, created, &restored);
+                for (int j = 0; j < k; ++j) NSP_CHECK(key[j] >= 0 && key[j] < K && created[j] >= 0);  // the request vector is intact
                 if (upd) {
                   uint32_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
                   uint32_t nmask = restored;
@@ -616,8 +626,11 @@ __global__ void __launch_bounds__(kSeqThreads, 1) plan_seq_kernel(const SeqArgs 
         }
         SEQ_TICK(4)
         if (found >= 0) {
+          NSP_CHECK(found < a.tg);
           const int node = __ldg(a.gpu_node + found);
+          NSP_CHECK(node >= 0 && node < a.N);
           const int g0 = __ldg(a.gpu_off + node), cnt = __ldg(a.gpu_off + node + 1) - g0;
+          NSP_CHECK(cnt > 0 && cnt <= NOSPLAN_MAX_GPUS_PER_NODE && found - g0 < cnt);
           // single-key quantity-1 pods: everything before `found` for this key is exhausted
           if (k == 1 && qty[0] == 1 && lane == 0) sh_hint[key[0]] = found >> 5;
           load_node(g0, cnt);

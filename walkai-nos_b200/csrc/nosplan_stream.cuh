@@ -127,7 +127,9 @@ __global__ void __launch_bounds__(kStreamWarps * 32) mig_stream_kernel(const Mig
       }
     }
     const int n = base + lane;
+    NSP_CHECK(n < A.npad && p >= 0 && p < 16 && len >= 1 && len <= RS);
     const int cnt = A.s_cnt[n];
+    NSP_CHECK(cnt <= gs && gs <= kStreamMaxGpus);
     // this node's column of the profile (gs x u16) and its models (gs x u8), at most kStreamMaxGpus = 8 slots:
     // two 64-bit registers and one, indexed with shifts (a register array indexed by the slot would go to local memory)
     unsigned long long uf0 = 0, uf1 = 0, md = 0;
