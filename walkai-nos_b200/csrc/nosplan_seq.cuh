@@ -26,13 +26,15 @@ namespace nsp {
 
 constexpr int kSeqThreads = 256;
 
-// Out of line on purpose: when the MPS per-GPU update was inlined into a sequencer that keeps a request
-// vector in local arrays, nvcc 12.9 overlaid the callee's scratch arrays with the caller's (the
-// caller's key[] read back as 0 after the call).  A real call gives it its own frame.
-#ifdef NOSPLAN_SEQ_INLINE  // (tools/run_checked.sh builds this variant to look for the effect described above)
-__device__ __forceinline__
-#else
+// The MPS per-GPU update as the sequencer calls it.  Round 1 kept this out of line (__noinline__) because an inlined build
+// had read the caller's request vector back as zeros after the call and blamed the compiler.  Round 2 looked for the cause
+// instead: with every local and shared array index asserted on the device (-DNOSPLAN_CHECKS) no access leaves its array in
+// any parity, limit, stress or full-size test, and the inlined build — with and without those assertions — passes the same
+// suites bit for bit (profiles/r2_sanitizer.md), so the call is inlined again.  -DNOSPLAN_SEQ_NOINLINE restores the call.
+#ifdef NOSPLAN_SEQ_NOINLINE
 __device__ __noinline__
+#else
+__device__ __forceinline__
 #endif
 bool seq_mps_gpu_update(const int* sz, uint4 f0, uint4 f1, uint32_t origmask, uint32_t cap, int k,
                                                 const int* sid, const int* resid, int* created, uint32_t* restored) {
