@@ -590,6 +590,8 @@ def main():
                                     "sample": f"first {Sm} MIG + {Sp} MPS pods x all nodes, one pass ({dt:.2f} s); "
                                               "C++ port of the Go functions (Go toolchain absent)"}
         print(json.dumps(line), flush=True)
+    if world > 1 and exchange.startswith("peer"):
+        pkg.dist.close_exchange(planner)  # status, barrier, then free: no peer may still be writing flags
     planner.close()
     if world > 1:
         dist.destroy_process_group()

@@ -113,7 +113,10 @@ int nosplan_set_mps_snapshot(nosplan_t* h, int n_sizes, const int32_t* sizes_gb,
  *   first_choice[D][max_gpus]  for that node, index of the geometry applied to each GPU, -1 = kept
  *   updated[D][N]              1 if node n would update
  *   choice[D][total_gpus]      applied geometry index per GPU for every (d, n), -1 = kept
- * n_evals (may be NULL) receives the number of candidate evaluations performed. */
+ * n_evals (may be NULL) receives the number of reference-equivalent candidate evaluations: every (row, node, GPU,
+ * allowed geometry) tuple the reference's loop would visit, n_demands x nosplan_mig_evals_per_demand.  The kernels
+ * execute fewer (a node's walk ends once the request is covered, a GPU that already holds enough skips its
+ * candidates, the demand-independent half of an evaluation is done once per snapshot): nosplan_executed_evals counts those. */
 int nosplan_score_mig(nosplan_t* h, int n_demands, const int32_t* dem_off, const int32_t* dem_key,
                       const int32_t* dem_qty, int32_t* first_node, int8_t* first_choice, uint8_t* updated,
                       int8_t* choice, int64_t* n_evals);
@@ -316,17 +319,24 @@ int nosplan_set_node_base(nosplan_t* h, int mig_first_node, int mps_first_node);
  * the node list sharded the gate is "sum over ranks > 0" (one all-reduce SUM over n_keys integers). */
 int nosplan_presence(nosplan_t* h, int kind, int64_t* count);
 
-/* The exchange itself, done by the library's own kernels over peer memory (NVLink): every rank folds
- * its keys into every rank's buffer with atomicMin and signals a per-rank step flag; no library
- * collective is involved.  Set-up (allocates; once per process group):
+/* The exchange itself, done by the library's own kernels over peer memory (NVLink), no library collective: every rank
+ * keeps its keys of a step in its OWN buffer and signals a per-rank step flag on every peer; a finishing kernel on each
+ * rank then reads all ranks' buffers with coalesced loads and keeps the minimum (csrc/nosplan_xchg.cuh).  Set-up
+ * (allocates; once per process group):
  *   1. nosplan_exchange_create on every rank -> a 64-byte CUDA IPC handle of the rank's buffer
  *   2. gather the handles of all ranks (any transport) into handles[world][64]
- *   3. nosplan_exchange_open on every rank
- * Per pass, on every rank, in the same order: nosplan_exchange_min_dev(n_keys, keys_in, keys_out):
- * keys_in[d] = this rank's global node index for row d or -1; keys_out[d] = the minimum over ranks of
- * the non-negative entries, or -1.  Device pointers; enqueued on `stream`, not synchronised; n_keys must
- * be the same on all ranks and at most max_keys.  A rank that waits more than 2 s for a peer stops
- * waiting and nosplan_exchange_status (synchronises) reports NOSPLAN_ERR_CUDA.  world <= 16. */
+ *   3. nosplan_exchange_open on every rank, then a barrier: nobody may run a pass before everybody has mapped
+ * Per pass, on every rank, in the same order: nosplan_exchange_min_dev(n_keys, keys_in, keys_out) —
+ * keys_in[d] = this rank's global node index for row d or -1; keys_out[d] = the minimum over ranks of the
+ * non-negative entries, or -1 — or nosplan_score_pass_dev / nosplan_score_snapshot, which do the same from inside the
+ * scorers.  Device pointers; enqueued on `stream`, not synchronised; n_keys must be the same on all ranks and at most
+ * max_keys.  world <= 16.
+ * Rules: all passes of a handle go down ONE stream (the step protocol is ordered by it).  A rank that waits more than
+ * 2 s for a peer gives up: that pass's results read -2, nosplan_exchange_status / nosplan_pass_status (synchronise)
+ * report NOSPLAN_ERR_CUDA, and the handle refuses further passes until the exchange is destroyed and created again on
+ * every rank — so the 2 s must cover the ranks' start-up skew (barrier before the first pass).  Before any rank calls
+ * nosplan_exchange_destroy (or nosplan_destroy), every rank must have finished its last pass (status call) and the
+ * ranks must have met at a barrier: a peer still in flight would write flags into freed memory. */
 #define NOSPLAN_IPC_HANDLE_BYTES 64
 int nosplan_exchange_create(nosplan_t* h, int rank, int world, int max_keys, unsigned char* handle_out);
 int nosplan_exchange_open(nosplan_t* h, const unsigned char* handles);

@@ -80,6 +80,7 @@ def worker(rank, world, port, cfgno, nodes, pods):
     if rank == 0:
         print(f"sharded pass ok: world {world}, cfg{cfgno} {nodes or 'full'} nodes, {D[0]}+{D[1]} rows, "
               f"{e0.elapsed_time(e1) / 30 * 1e3:.1f} us per pass incl. exchange; winners found for {(exp >= 0).mean():.2f} of the rows")
+    pkg.dist.close_exchange(p)
     p.close()
     dist.destroy_process_group()
 

@@ -60,6 +60,7 @@ def worker(rank, world, port):
     dist.barrier()
     if rank == 0:
         print(f"exchange ok: world {world}, {e0.elapsed_time(e1) / 40 * 1e3:.1f} us per exchange of {n} keys")
+    pkg.dist.close_exchange(p)
     p.close()
     dist.destroy_process_group()
 

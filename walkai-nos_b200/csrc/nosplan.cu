@@ -137,6 +137,7 @@ struct nosplan {
   int mig_base = 0, mps_base = 0;
   struct {
     bool created = false, open = false;
+    bool broken = false;               // a status call saw a time-out: the step counters of the ranks no longer agree
     int rank = 0, world = 1, max_keys = 0;
     int stride = 0;                    // max_keys rounded up to a multiple of 4: both halves stay 16-byte aligned
     void* local = nullptr;             // keys[2][stride] + pushed[kMaxWorld] + read[kMaxWorld]
@@ -1244,6 +1245,7 @@ int score_pass_enqueue(nosplan_t* h, nosplan_t* x, int Dm, const int32_t* m_off,
   if (Dall == 0) return NOSPLAN_OK;
   auto& xc = x->xch;
   const bool exchange = xc.open;
+  if (exchange && xc.broken) return fail(h, NOSPLAN_ERR_CUDA, "the exchange timed out earlier: destroy and re-create it on every rank");
   if (exchange && Dall > xc.max_keys) return fail(h, NOSPLAN_ERR_RANGE, "%d rows exceed the exchange buffer (%d keys)", Dall, xc.max_keys);
   const bool single = (flags & NOSPLAN_PASS_SINGLE_KEY) != 0;
   const bool count = (flags & NOSPLAN_PASS_COUNT) != 0;
@@ -1440,7 +1442,10 @@ int nosplan_pass_status(nosplan_t* h) {
   if (h->xch.created) {
     int e = 0;
     CU(cudaMemcpy(&e, h->xch.err.p, sizeof(int), cudaMemcpyDeviceToHost));
-    if (e) return fail(h, NOSPLAN_ERR_CUDA, "exchange: rank %d never signalled a step (waited 2 s)", e - 1);
+    if (e) {
+      h->xch.broken = true;
+      return fail(h, NOSPLAN_ERR_CUDA, "exchange: rank %d never signalled a step (waited 2 s); the results of that pass read -2", e - 1);
+    }
   }
   return NOSPLAN_OK;
 }
@@ -2474,6 +2479,7 @@ extern "C" int nosplan_exchange_min_dev(nosplan_t* h, int n_keys, const int32_t*
   h->err.clear();
   auto& x = h->xch;
   if (!x.open) return fail(h, NOSPLAN_ERR_ARG, "exchange is not open");
+  if (x.broken) return fail(h, NOSPLAN_ERR_CUDA, "the exchange timed out earlier: destroy and re-create it on every rank");
   if (n_keys < 0 || n_keys > x.max_keys) return fail(h, NOSPLAN_ERR_RANGE, "%d keys exceed the exchange buffer (%d)", n_keys, x.max_keys);
   if (n_keys > 0 && (!keys_in || !keys_out)) return fail(h, NOSPLAN_ERR_ARG, "null key arrays");
   int rc = bind(h);
@@ -2499,7 +2505,10 @@ extern "C" int nosplan_exchange_status(nosplan_t* h) {
   if (rc) return rc;
   int e = 0;
   CU(cudaMemcpy(&e, x.err.p, sizeof(int), cudaMemcpyDeviceToHost));
-  if (e) return fail(h, NOSPLAN_ERR_CUDA, "exchange: rank %d never signalled a step (waited 2 s)", e - 1);
+  if (e) {
+    x.broken = true;
+    return fail(h, NOSPLAN_ERR_CUDA, "exchange: rank %d never signalled a step (waited 2 s); the results of that pass read -2", e - 1);
+  }
   return NOSPLAN_OK;
 }
 
@@ -2683,7 +2692,10 @@ extern "C" int nosplan_score_snapshot(nosplan_t* h, const nosplan_mig_snapshot_t
     if (Dm > 0 && cm != ~0ull) return child_fail(describe_bad_row(c, cm, mig_rows->off, mig_rows->key, mig_rows->qty, c->P), "MIG: ");
     if (Dp > 0 && cp != ~0ull) return child_fail(describe_bad_row(c, cp, mps_rows->off, mps_rows->key, mps_rows->qty, c->S), "MPS: ");
   }
-  if ((int)c->h_status[6] != 0) return fail(h, NOSPLAN_ERR_CUDA, "exchange: rank %d never signalled a step (waited 2 s)", (int)c->h_status[6] - 1);
+  if ((int)c->h_status[6] != 0) {
+    h->xch.broken = true;
+    return fail(h, NOSPLAN_ERR_CUDA, "exchange: rank %d never signalled a step (waited 2 s)", (int)c->h_status[6] - 1);
+  }
   const char* pin = static_cast<const char*>(c->h_pin);
   if (Dm > 0) std::memcpy(mig_first_node, pin, sizeof(int32_t) * (size_t)Dm);
   if (Dp > 0) std::memcpy(mps_first_node, pin + sizeof(int32_t) * (size_t)Dm, sizeof(int32_t) * (size_t)Dp);

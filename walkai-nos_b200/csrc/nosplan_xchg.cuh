@@ -120,6 +120,12 @@ __global__ void xchg_finish_kernel(XchgPeers P, int world, int rank, int max_key
                                    int32_t* __restrict__ out, unsigned int* __restrict__ done,
                                    unsigned long long timeout_ns, int* __restrict__ err) {
   wait_flags(P.pushed[rank], world, step, timeout_ns, err);
+  if (*reinterpret_cast<volatile int*>(err) != 0) {
+    // a peer never completed a step (this one or an earlier one): no minimum exists.  Every key reads -2, nothing is
+    // signalled; the host sees the error at its next status call and refuses further passes until the exchange is rebuilt.
+    for (int d = blockIdx.x * blockDim.x + threadIdx.x; d < n; d += gridDim.x * blockDim.x) out[d] = -2;
+    return;
+  }
   const size_t half = (size_t)(step & 1u) * (size_t)max_keys;  // max_keys is a multiple of 4: halves stay 16-byte aligned
   const int n4 = n >> 2;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * blockDim.x) {

@@ -70,6 +70,19 @@ def open_exchange(planner, max_keys: int, group=None):
         dist.barrier(group=group)  # nobody pushes before everybody has mapped
 
 
+def close_exchange(planner, group=None):
+    """Tears the exchange down safely: every rank first confirms its last pass has finished (status call), then the
+    ranks meet at a barrier, and only then is any buffer freed — a peer still in flight would otherwise write its step
+    flag into freed memory (include/nosplan.h, "Rules")."""
+    import torch.distributed as dist
+    try:
+        planner.exchange_status()
+    finally:
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+            dist.barrier(group=group)
+        planner.exchange_destroy()
+
+
 def merge_presence(count_local, group=None):
     """count_local: int64 torch tensor [n_keys], this shard's sum of used + free per key (Planner.presence).
     Returns the cluster-wide sums after one all-reduce(SUM): Controller.profileAlreadyPresent
