@@ -188,6 +188,31 @@ int nosplan_diff_plan_mig_devices(nosplan_t* h, int n_gpus, int n_profiles, cons
                                   const uint8_t* dev_status, const int32_t* spec, const uint32_t* spec_mask, uint8_t* dev_op,
                                   int32_t* create_new, int32_t* create_again, uint8_t* matches);
 
+/* ---- batch-demand planning mode: NEW BEHAVIOUR, not in the reference ----------------------------------------------
+ * The reference's documentation still describes a planner that works on a batch of pending pods — aggregate what the
+ * batch lacks, re-partition, simulate the scheduling, keep the partitioning that makes the most pods schedulable
+ * (docs/en/docs/dynamic-gpu-partitioning/configuration.md:6-11, 19, 38; the knobs BatchWindowTimeoutSeconds /
+ * BatchWindowIdleSeconds, pkg/api/nos.nebuly.com/config/v1alpha1/gpu_partitioner_config.go:28-50, and pkg/util/batcher.go
+ * are what is left of it) — but this fork's code reconciles pod by pod.  This entry point is this project's definition of
+ * that mode, written down as executable code in oracle/batch_plan.py and built only from functions the reference still
+ * has (Node.AddPod first-fit, Node.UpdateGeometryFor); the batched scorer does the re-partitioning step of every round:
+ *   A. first-fit every pod, in order, on the devices that are free now;
+ *   B. rounds (at most max_rounds, 0 = 8): lacking[k] = what the unplaced pods still ask of profile / size k; the rows
+ *      {k: lacking[k]} are scored against every node of the round's starting state (nosplan_score_mig / _mps with full
+ *      tables); profile by profile, nodes in list order whose trial update succeeded and that no other profile took in
+ *      this round are committed until the profile's free devices on the committed nodes cover lacking[k]; the unplaced
+ *      pods are first-fitted on the new state; a round that places nobody ends the loop;
+ *   both profile orders (ascending, descending) are simulated from the state after A; the one that places more pods is
+ *   kept (ties: ascending).
+ * Pods of ONE kind per call (kind 0: keys index the MIG vocabulary, 1: the sizes), one key each, 1 <= quantity <= 8.
+ * Starts from the uploaded snapshot, which is left as it was; the planned state is read with nosplan_get_*_state.
+ * Outputs: sched_node / sched_gpu [n_pods] (-1: still pending), phase [n_pods] (1 placed in A, 2 placed after a
+ * re-partitioning, 0 pending), repartitioned [n_nodes] (1: the node's geometry was changed), order_out (0 ascending, 1
+ * descending), rounds_out. */
+int nosplan_plan_batch(nosplan_t* h, int kind, int n_pods, const int32_t* pod_key, const int32_t* pod_qty, int max_rounds,
+                       int32_t* sched_node, int32_t* sched_gpu, uint8_t* phase, uint8_t* repartitioned, int32_t* order_out,
+                       int32_t* rounds_out);
+
 /* ---- device-resident variants (inputs/outputs already in HBM; used for kernel-only timing) ------------ */
 /* Same as nosplan_score_mig/_mps but every pointer is a device pointer on the handle's device and the
  * work is enqueued on `stream` (a cudaStream_t) without synchronising.  first_node must be

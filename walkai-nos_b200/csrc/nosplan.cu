@@ -895,6 +895,46 @@ int nosplan_set_mig_tables(nosplan_t* h, int n_profiles, const char* const* prof
 }  // extern "C"
 
 namespace {
+// What the scorers derive from the packed snapshot (scheduling data and the demand-independent half of the scores):
+// re-run whenever the packed state the scorers read changes (a new snapshot; every round of the batch-demand mode).
+int mig_derive_tables(nosplan_t* h, int n_nodes, int npad, int gsl, cudaStream_t st) {
+  if (!h->k16ok) return NOSPLAN_OK;
+  // 16-bit-key scorer: the demand-independent candidate ranks of every GPU, then the node order per
+  // profile (scheduling data, not results)
+  const int P = h->P;
+  const int cwk = (h->cmax + 3) / 4;
+  CU(h->d_mig_rankg.reserve(sizeof(uint32_t) * (size_t)npad * gsl * 2 * cwk));
+  CU(h->d_mig_ufg.reserve(sizeof(uint16_t) * (size_t)npad * 16 * gsl));
+  CU(h->d_mig_maskg.reserve(sizeof(uint32_t) * (size_t)npad * gsl));
+  CU(h->d_mig_modelg.reserve((size_t)npad * gsl));
+  CU(h->d_mig_cost.reserve((size_t)P * npad));
+  CU(h->d_mig_perm.reserve(sizeof(int32_t) * (size_t)P * npad));
+  CU(h->d_profcost.reserve(sizeof(int32_t) * 32));
+  mig_rank16_kernel<<<(npad * gsl + 127) / 128, 128, 0, st>>>(
+      h->d_tables.as<MigTables>(), npad, gsl, cwk, h->d_mig_sused.as<uint4>(), h->d_mig_sfree.as<uint4>(),
+      h->d_mig_smodel.as<uint8_t>(), h->d_mig_scnt.as<uint8_t>(), h->d_mig_rankg.as<uint32_t>(), h->d_mig_ufg.as<uint16_t>(),
+      h->d_mig_maskg.as<uint32_t>(), h->d_mig_modelg.as<uint8_t>());
+  mig_cost_kernel<<<(npad + 127) / 128, 128, 0, st>>>(n_nodes, npad, gsl, P, h->d_mig_scnt.as<uint8_t>(),
+                                                      h->d_mig_maskg.as<uint32_t>(), h->d_mig_cost.as<uint8_t>());
+  mig_perm_kernel<<<P, 1024, 0, st>>>(npad, h->d_mig_cost.as<uint8_t>(), h->d_mig_perm.as<int32_t>(),
+                                      h->d_profcost.as<int32_t>());
+  CU(cudaGetLastError());
+  return NOSPLAN_OK;
+}
+int mps_derive_tables(nosplan_t* h, int n_nodes, int S, cudaStream_t st) {
+  // node order per size for the scorer (scheduling data, see nosplan_score16.cuh)
+  CU(h->d_mps_cost.reserve((size_t)S * n_nodes));
+  CU(h->d_mps_perm.reserve(sizeof(int32_t) * (size_t)S * n_nodes));
+  CU(h->d_mps_sizecost.reserve(sizeof(int32_t) * 32));
+  mps_cost_kernel<<<(n_nodes + 127) / 128, 128, 0, st>>>(n_nodes, S, h->d_mps_sizes.as<int32_t>(), h->d_mps_off.as<int32_t>(),
+                                                         h->d_mps_valid.as<uint8_t>(), h->d_mps_gpu0.as<MpsGpu>(),
+                                                         h->d_mps_cost.as<uint8_t>());
+  mig_perm_kernel<<<S, 1024, 0, st>>>(n_nodes, h->d_mps_cost.as<uint8_t>(), h->d_mps_perm.as<int32_t>(),
+                                      h->d_mps_sizecost.as<int32_t>());
+  CU(cudaGetLastError());
+  return NOSPLAN_OK;
+}
+
 // Everything of a snapshot upload except waiting for the device's verdict (the range checks run in the pack
 // kernels): host-side checks of the node list, copies, pack, scheduling tables, read-back of the status words.
 // The handle's sizes are set at once so that work can be enqueued behind it; *_snapshot_finish waits for the
@@ -954,27 +994,7 @@ int mig_snapshot_enqueue(nosplan_t* h, int n_nodes, const int32_t* gpu_off, cons
   CU(cudaMemcpyAsync(h->d_mig_used.p, h->d_mig_used0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, st));
   CU(cudaMemcpyAsync(h->d_mig_free.p, h->d_mig_free0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, st));
   if ((rc = status_enqueue(h, 0, st))) return rc;
-  if (h->k16ok) {
-    // 16-bit-key scorer: the demand-independent candidate ranks of every GPU, then the node order per
-    // profile (scheduling data, not results)
-    const int cwk = (h->cmax + 3) / 4;
-    CU(h->d_mig_rankg.reserve(sizeof(uint32_t) * (size_t)npad * gsl * 2 * cwk));
-    CU(h->d_mig_ufg.reserve(sizeof(uint16_t) * (size_t)npad * 16 * gsl));
-    CU(h->d_mig_maskg.reserve(sizeof(uint32_t) * (size_t)npad * gsl));
-    CU(h->d_mig_modelg.reserve((size_t)npad * gsl));
-    CU(h->d_mig_cost.reserve((size_t)P * npad));
-    CU(h->d_mig_perm.reserve(sizeof(int32_t) * (size_t)P * npad));
-    CU(h->d_profcost.reserve(sizeof(int32_t) * 32));
-    mig_rank16_kernel<<<(npad * gsl + 127) / 128, 128, 0, st>>>(
-        h->d_tables.as<MigTables>(), npad, gsl, cwk, h->d_mig_sused.as<uint4>(), h->d_mig_sfree.as<uint4>(),
-        h->d_mig_smodel.as<uint8_t>(), h->d_mig_scnt.as<uint8_t>(), h->d_mig_rankg.as<uint32_t>(), h->d_mig_ufg.as<uint16_t>(),
-        h->d_mig_maskg.as<uint32_t>(), h->d_mig_modelg.as<uint8_t>());
-    mig_cost_kernel<<<(npad + 127) / 128, 128, 0, st>>>(n_nodes, npad, gsl, P, h->d_mig_scnt.as<uint8_t>(),
-                                                        h->d_mig_maskg.as<uint32_t>(), h->d_mig_cost.as<uint8_t>());
-    mig_perm_kernel<<<P, 1024, 0, st>>>(npad, h->d_mig_cost.as<uint8_t>(), h->d_mig_perm.as<int32_t>(),
-                                        h->d_profcost.as<int32_t>());
-    CU(cudaGetLastError());
-  }
+  if ((rc = mig_derive_tables(h, n_nodes, npad, gsl, st))) return rc;
   if (h->mig_gs != gsl) std::memset(h->occ_cache[0], 0, sizeof(h->occ_cache[0]));  // the tile follows the GPUs per node
   h->mig_n = n_nodes;
   h->mig_tg = tg;
@@ -1059,16 +1079,7 @@ int mps_snapshot_enqueue(nosplan_t* h, int n_sizes, const int32_t* sizes_gb, int
     CU(cudaMemcpyAsync(h->d_mps_ulo.p, h->d_mps_ulo0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, st));
     CU(cudaMemcpyAsync(h->d_mps_uhi.p, h->d_mps_uhi0.p, sizeof(uint4) * tg, cudaMemcpyDeviceToDevice, st));
     if ((rc = status_enqueue(h, 1, st))) return rc;
-    // node order per size for the scorer (scheduling data, see nosplan_score16.cuh)
-    CU(h->d_mps_cost.reserve((size_t)S * n_nodes));
-    CU(h->d_mps_perm.reserve(sizeof(int32_t) * (size_t)S * n_nodes));
-    CU(h->d_mps_sizecost.reserve(sizeof(int32_t) * 32));
-    mps_cost_kernel<<<(n_nodes + 127) / 128, 128, 0, st>>>(n_nodes, S, h->d_mps_sizes.as<int32_t>(), h->d_mps_off.as<int32_t>(),
-                                                           h->d_mps_valid.as<uint8_t>(), h->d_mps_gpu0.as<MpsGpu>(),
-                                                           h->d_mps_cost.as<uint8_t>());
-    mig_perm_kernel<<<S, 1024, 0, st>>>(n_nodes, h->d_mps_cost.as<uint8_t>(), h->d_mps_perm.as<int32_t>(),
-                                        h->d_mps_sizecost.as<int32_t>());
-    CU(cudaGetLastError());
+    if ((rc = mps_derive_tables(h, n_nodes, S, st))) return rc;
   }
   if (n_nodes == 0 && (rc = status_enqueue(h, 1, st))) return rc;
   h->S = S;
@@ -2385,6 +2396,349 @@ extern "C" int nosplan_diff_plan_mig_devices(nosplan_t* h, int n_gpus, int n_pro
   if (nd > 0) CU(cudaMemcpyAsync(dev_op, h->d_out[2].p, nd, cudaMemcpyDeviceToHost, st));
   CU(cudaMemcpyAsync(matches, h->d_out[4].p, n_gpus, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
+  return NOSPLAN_OK;
+}
+
+// ---- batch-demand planning mode (NEW BEHAVIOUR: the reference only documents it; definition in oracle/batch_plan.py) ----
+namespace {
+// slot-major copies of the MIG working state for the scorers (what mig_pack_kernel makes from the host rows)
+__global__ void mig_repack_kernel(int N, int gs, int npad, const int32_t* __restrict__ gpu_off, const uint8_t* __restrict__ s_cnt,
+                                  const uint4* __restrict__ a_used, const uint4* __restrict__ a_free, uint4* __restrict__ s_used,
+                                  uint4* __restrict__ s_free) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int n = i / gs, s = i - n * gs;
+  if (n >= N || s >= s_cnt[n]) return;  // slots without a GPU and invalid nodes keep their zeros
+  const int g = gpu_off[n] + s;
+  s_used[(size_t)s * npad + n] = a_used[g];
+  s_free[(size_t)s * npad + n] = a_free[g];
+}
+
+struct BatchCtx {
+  nosplan_t* h;
+  int kd, M, N, tg, K;
+  cudaStream_t st;
+  const int32_t* key;
+  const int32_t* qty;
+  DevBuf* b;  // h->d_plan + kd * 16
+  ChainArgs ca;
+};
+
+// the scorers read the snapshot copies (*0) and the tables derived from them: make them describe the working state
+int batch_sync_scorer_state(BatchCtx& c) {
+  nosplan_t* h = c.h;
+  cudaStream_t st = c.st;
+  if (c.kd == 0) {
+    CU(cudaMemcpyAsync(h->d_mig_used0.p, h->d_mig_used.p, sizeof(uint4) * c.tg, cudaMemcpyDeviceToDevice, st));
+    CU(cudaMemcpyAsync(h->d_mig_free0.p, h->d_mig_free.p, sizeof(uint4) * c.tg, cudaMemcpyDeviceToDevice, st));
+    mig_repack_kernel<<<(c.N * h->mig_gs + 127) / 128, 128, 0, st>>>(c.N, h->mig_gs, h->mig_npad, h->d_mig_off.as<int32_t>(),
+                                                                     h->d_mig_scnt.as<uint8_t>(), h->d_mig_used0.as<uint4>(),
+                                                                     h->d_mig_free0.as<uint4>(), h->d_mig_sused.as<uint4>(),
+                                                                     h->d_mig_sfree.as<uint4>());
+    CU(cudaGetLastError());
+    return mig_derive_tables(h, c.N, h->mig_npad, h->mig_gs, st);
+  }
+  CU(cudaMemcpyAsync(h->d_mps_gpu0.p, h->d_mps_gpu.p, sizeof(MpsGpu) * c.tg, cudaMemcpyDeviceToDevice, st));
+  CU(cudaMemcpyAsync(h->d_mps_ulo0.p, h->d_mps_ulo.p, sizeof(uint4) * c.tg, cudaMemcpyDeviceToDevice, st));
+  CU(cudaMemcpyAsync(h->d_mps_uhi0.p, h->d_mps_uhi.p, sizeof(uint4) * c.tg, cudaMemcpyDeviceToDevice, st));
+  return mps_derive_tables(h, c.N, h->S, st);
+}
+
+// Node.AddPod first-fit (the chain kernels, gate ignored) for the pods `todo` (ascending indices); results into node/gpu
+int batch_first_fit(BatchCtx& c, const std::vector<int32_t>& todo, std::vector<int32_t>& node, std::vector<int32_t>& gpu) {
+  nosplan_t* h = c.h;
+  cudaStream_t st = c.st;
+  const int m = (int)todo.size();
+  if (m == 0 || c.tg == 0) return NOSPLAN_OK;
+  std::vector<int32_t> ckey, coff{0}, cpod(m), cq(m), cnt(c.K, 0), at(c.K, 0);
+  for (int j = 0; j < m; ++j) cnt[c.key[todo[j]]]++;
+  for (int k = 0; k < c.K; ++k)
+    if (cnt[k]) {
+      at[k] = coff.back();
+      ckey.push_back(k);
+      coff.push_back(coff.back() + cnt[k]);
+    }
+  int maxq = 1;
+  for (int j = 0; j < m; ++j) {
+    const int i = todo[j];
+    const int pos = at[c.key[i]]++;
+    cpod[pos] = j;  // kind-local index = position in todo (ascending: planner order kept inside a chain)
+    cq[pos] = c.qty[i];
+    maxq = std::max(maxq, (int)c.qty[i]);
+  }
+  DevBuf* b = c.b;
+  int rc;
+  if ((rc = upload(h, b[8], ckey.data(), sizeof(int32_t) * ckey.size(), st))) return rc;
+  if ((rc = upload(h, b[9], coff.data(), sizeof(int32_t) * coff.size(), st))) return rc;
+  if ((rc = upload(h, b[10], cpod.data(), sizeof(int32_t) * m, st))) return rc;
+  if ((rc = upload(h, b[11], cq.data(), sizeof(int32_t) * m, st))) return rc;
+  CU(b[12].reserve(sizeof(int32_t) * (2 * kMaxSizes + 2)));
+  CU(b[6].reserve((size_t)m * (1 + 3 * sizeof(int32_t)) + 64));
+  CU(b[14].reserve((size_t)c.K * ((c.tg + 31) / 32)));
+  ChainArgs& ca = c.ca;
+  std::memset(&ca, 0, sizeof(ca));
+  ca.n_chains = (int)ckey.size();
+  ca.chain_key = b[8].as<int32_t>();
+  ca.chain_off = b[9].as<int32_t>();
+  ca.chain_pod = b[10].as<int32_t>();
+  ca.chain_q = b[11].as<int32_t>();
+  ca.present = b[12].as<int32_t>();
+  ca.dead = ca.present + kMaxSizes;
+  ca.limit_out = ca.present + 2 * kMaxSizes;
+  ca.range = ca.limit_out;
+  ca.ignore_gate = 1;
+  ca.M = m;
+  ca.N = c.N;
+  ca.tg = c.tg;
+  ca.n_keys = c.K;
+  ca.gpu_off = c.kd ? h->d_mps_off.as<int32_t>() : h->d_mig_off.as<int32_t>();
+  ca.gpu_node = c.kd ? h->d_mps_gnode.as<int32_t>() : h->d_mig_gnode.as<int32_t>();
+  ca.gpu_slot = c.kd ? h->d_mps_gslot.as<int32_t>() : h->d_mig_gslot.as<int32_t>();
+  ca.m_used = h->d_mig_used.as<uint4>();
+  ca.m_free = h->d_mig_free.as<uint4>();
+  ca.sizes = h->d_mps_sizes.as<int32_t>();
+  ca.p_gpu = h->d_mps_gpu.as<MpsGpu>();
+  ca.p_used_lo = h->d_mps_ulo.as<uint4>();
+  ca.p_used_hi = h->d_mps_uhi.as<uint4>();
+  ca.sched = 1;
+  ca.repart_node = b[6].as<int32_t>();
+  ca.sched_node = ca.repart_node + m;
+  ca.sched_gpu = ca.sched_node + m;
+  ca.gate_hit = reinterpret_cast<uint8_t*>(ca.sched_gpu + m);
+  ca.n_win = (c.tg + 31) / 32;
+  ca.winmax = b[14].as<uint8_t>();
+  const int32_t range[2] = {0, m};
+  h->h_range[c.kd][0] = range[0];
+  h->h_range[c.kd][1] = range[1];
+  CU(cudaMemcpyAsync(ca.limit_out, h->h_range[c.kd], sizeof(range), cudaMemcpyHostToDevice, st));
+  CU(cudaMemsetAsync(ca.sched_node, 0xff, sizeof(int32_t) * 2 * (size_t)m, st));  // -1: a pod no chain step reaches stays pending
+  if (c.kd == 0) plan_winmax_kernel<false><<<ca.n_win, 32, 0, st>>>(ca);
+  else plan_winmax_kernel<true><<<ca.n_win, 32, 0, st>>>(ca);
+  if (maxq <= 2) {
+    if (c.kd == 0) plan_chain_kernel<false, 2><<<ca.n_chains, 32, 0, st>>>(ca);
+    else plan_chain_kernel<true, 2><<<ca.n_chains, 32, 0, st>>>(ca);
+  } else {
+    if (c.kd == 0) plan_chain_kernel<false, kChainQ><<<ca.n_chains, 32, 0, st>>>(ca);
+    else plan_chain_kernel<true, kChainQ><<<ca.n_chains, 32, 0, st>>>(ca);
+  }
+  CU(cudaGetLastError());
+  std::vector<int32_t> rn(m), rg(m);
+  CU(cudaMemcpyAsync(rn.data(), ca.sched_node, sizeof(int32_t) * m, cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(rg.data(), ca.sched_gpu, sizeof(int32_t) * m, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  for (int j = 0; j < m; ++j) {
+    node[todo[j]] = rn[j];
+    gpu[todo[j]] = rg[j];
+  }
+  return NOSPLAN_OK;
+}
+}  // namespace
+
+extern "C" int nosplan_plan_batch(nosplan_t* h, int kind, int n_pods, const int32_t* pod_key, const int32_t* pod_qty, int max_rounds,
+                                  int32_t* sched_node, int32_t* sched_gpu, uint8_t* phase, uint8_t* repartitioned,
+                                  int32_t* order_out, int32_t* rounds_out) {
+  if (!h) return NOSPLAN_ERR_ARG;
+  h->err.clear();
+  NSP_RANGE("nosplan_plan_batch");
+  if (kind != 0 && kind != 1) return fail(h, NOSPLAN_ERR_ARG, "kind must be 0 (MIG) or 1 (MPS)");
+  if (kind ? !h->have_mps : !h->have_mig) return fail(h, NOSPLAN_ERR_ARG, "no snapshot of that kind");
+  if (n_pods < 0 || (n_pods > 0 && (!pod_key || !pod_qty || !sched_node || !sched_gpu || !phase))) return fail(h, NOSPLAN_ERR_ARG, "null pod arrays");
+  if (max_rounds < 1) max_rounds = 8;
+  BatchCtx c{};
+  c.h = h;
+  c.kd = kind;
+  c.M = n_pods;
+  c.N = kind ? h->mps_n : h->mig_n;
+  c.tg = kind ? h->mps_tg : h->mig_tg;
+  c.K = kind ? h->S : h->P;
+  c.st = h->stream;
+  c.key = pod_key;
+  c.qty = pod_qty;
+  c.b = h->d_plan + kind * 16;
+  if (!repartitioned && c.N > 0) return fail(h, NOSPLAN_ERR_ARG, "repartitioned is required");
+  for (int i = 0; i < n_pods; ++i) {
+    if (pod_key[i] < 0 || pod_key[i] >= c.K) return fail(h, NOSPLAN_ERR_RANGE, "pod %d: key %d out of range", i, pod_key[i]);
+    if (pod_qty[i] < 1 || pod_qty[i] > kChainQ) return fail(h, NOSPLAN_ERR_RANGE, "pod %d: quantity %d outside [1,%d]", i, pod_qty[i], kChainQ);
+  }
+  int rc = bind(h);
+  if (rc) return rc;
+  cudaStream_t st = c.st;
+  const int M = n_pods, N = c.N, tg = c.tg, K = c.K;
+  if (order_out) *order_out = 0;
+  if (rounds_out) *rounds_out = 0;
+  for (int n = 0; n < N; ++n) repartitioned[n] = 0;
+  for (int i = 0; i < M; ++i) {
+    sched_node[i] = sched_gpu[i] = -1;
+    phase[i] = 0;
+  }
+  if (M == 0 || N == 0 || tg == 0) return NOSPLAN_OK;
+  // the snapshot is kept aside: the scorers' view (*0 copies, derived tables) follows the working state during the call
+  const size_t sb = kind ? sizeof(MpsGpu) * tg : sizeof(uint4) * tg;
+  DevBuf* b = c.b;
+  // b[0..2]: the snapshot; b[3..5]: state after phase A; b[15], b[7], b[13]: best final state
+  auto copy_state = [&](DevBuf& d0, DevBuf& d1, DevBuf& d2, bool from_working, bool orig) -> int {
+    // direction: working -> buffers (from_working) or buffers -> working; orig selects the *0 arrays instead of the working ones
+    void* s0 = kind ? (orig ? h->d_mps_gpu0.p : h->d_mps_gpu.p) : (orig ? h->d_mig_used0.p : h->d_mig_used.p);
+    void* s1 = kind ? (orig ? h->d_mps_ulo0.p : h->d_mps_ulo.p) : (orig ? h->d_mig_free0.p : h->d_mig_free.p);
+    void* s2 = kind ? (orig ? h->d_mps_uhi0.p : h->d_mps_uhi.p) : nullptr;
+    const size_t z1 = sizeof(uint4) * tg;
+    CU(d0.reserve(sb));
+    CU(d1.reserve(z1));
+    if (s2) CU(d2.reserve(z1));
+    if (from_working) {
+      CU(cudaMemcpyAsync(d0.p, s0, sb, cudaMemcpyDeviceToDevice, st));
+      CU(cudaMemcpyAsync(d1.p, s1, z1, cudaMemcpyDeviceToDevice, st));
+      if (s2) CU(cudaMemcpyAsync(d2.p, s2, z1, cudaMemcpyDeviceToDevice, st));
+    } else {
+      CU(cudaMemcpyAsync(s0, d0.p, sb, cudaMemcpyDeviceToDevice, st));
+      CU(cudaMemcpyAsync(s1, d1.p, z1, cudaMemcpyDeviceToDevice, st));
+      if (s2) CU(cudaMemcpyAsync(s2, d2.p, z1, cudaMemcpyDeviceToDevice, st));
+    }
+    return NOSPLAN_OK;
+  };
+  if ((rc = copy_state(b[0], b[1], b[2], true, true))) return rc;          // snapshot aside
+  if ((rc = copy_state(b[0], b[1], b[2], false, false))) return rc;        // working := snapshot
+  (kind ? h->mps_state_dirty : h->mig_state_dirty) = true;
+  // restores the handle's snapshot view whatever happens below
+  auto restore = [&]() -> int {
+    int r2 = copy_state(b[0], b[1], b[2], false, true);
+    if (r2) return r2;
+    if (!kind) {
+      mig_repack_kernel<<<(N * h->mig_gs + 127) / 128, 128, 0, st>>>(N, h->mig_gs, h->mig_npad, h->d_mig_off.as<int32_t>(),
+                                                                     h->d_mig_scnt.as<uint8_t>(), h->d_mig_used0.as<uint4>(),
+                                                                     h->d_mig_free0.as<uint4>(), h->d_mig_sused.as<uint4>(),
+                                                                     h->d_mig_sfree.as<uint4>());
+      if ((r2 = mig_derive_tables(h, N, h->mig_npad, h->mig_gs, st))) return r2;
+    } else if ((r2 = mps_derive_tables(h, N, h->S, st))) {
+      return r2;
+    }
+    CU(cudaStreamSynchronize(st));
+    return NOSPLAN_OK;
+  };
+  // ---- phase A: what fits on the devices that are free now
+  std::vector<int32_t> all(M), node_a(M, -1), gpu_a(M, -1);
+  for (int i = 0; i < M; ++i) all[i] = i;
+  if ((rc = batch_first_fit(c, all, node_a, gpu_a))) { restore(); return rc; }
+  if ((rc = copy_state(b[3], b[4], b[5], true, false))) { restore(); return rc; }
+  std::vector<int32_t> unplaced0;
+  for (int i = 0; i < M; ++i)
+    if (node_a[i] < 0) unplaced0.push_back(i);
+  // ---- phase B, both profile orders from the same state; the better one is kept
+  int best_sched = -1, best_order = 0, best_rounds = 0;
+  std::vector<int32_t> best_node, best_gpu;
+  std::vector<uint8_t> best_rep;
+  CU(b[12].reserve(sizeof(int32_t) * (2 * kMaxSizes + 2)));
+  for (int order = 0; order < 2; ++order) {
+    if ((rc = copy_state(b[3], b[4], b[5], false, false))) { restore(); return rc; }
+    std::vector<int32_t> unplaced = unplaced0, node_b(M, -1), gpu_b(M, -1);
+    std::vector<uint8_t> rep(N, 0);
+    CU(h->d_out[4].reserve(2 * (size_t)N));
+    uint8_t* d_taken = h->d_out[4].as<uint8_t>();
+    uint8_t* d_rep = d_taken + N;
+    CU(cudaMemsetAsync(d_rep, 0, N, st));
+    int rounds = 0;
+    for (int round = 0; round < max_rounds && !unplaced.empty(); ++round) {
+      std::vector<long long> lacking(K, 0);
+      for (int i : unplaced) lacking[pod_key[i]] += pod_qty[i];
+      std::vector<int32_t> off{0}, rkey, rqty, okey, oidx, olack;
+      for (int k = 0; k < K; ++k)
+        if (lacking[k] > 0) {
+          rkey.push_back(k);
+          rqty.push_back((int32_t)std::min<long long>(lacking[k], NOSPLAN_MAX_DEMAND_QTY));
+          off.push_back((int32_t)rkey.size());
+        }
+      const int D = (int)rkey.size();
+      for (int r = 0; r < D; ++r) {
+        const int rr = order ? D - 1 - r : r;
+        okey.push_back(rkey[rr]);
+        oidx.push_back(rr);
+        olack.push_back((int32_t)std::min<long long>(lacking[rkey[rr]], 0x7fffffff));
+      }
+      if ((rc = batch_sync_scorer_state(c))) { restore(); return rc; }
+      // the batched scorer: every row against every node, full tables out
+      if ((rc = upload(h, h->d_dem[0], off.data(), sizeof(int32_t) * (D + 1), st))) { restore(); return rc; }
+      if ((rc = upload(h, h->d_dem[1], rkey.data(), sizeof(int32_t) * D, st))) { restore(); return rc; }
+      if ((rc = upload(h, h->d_dem[2], rqty.data(), sizeof(int32_t) * D, st))) { restore(); return rc; }
+      CU(h->d_out[0].reserve(sizeof(int32_t) * D));
+      CU(h->d_out[1].reserve((size_t)D * N));
+      BatchCommitArgs ba{};
+      if (!kind) {
+        CU(h->d_out[2].reserve((size_t)D * tg));
+        rc = launch_mig_score(h, D, h->d_dem[0].as<int32_t>(), h->d_dem[1].as<int32_t>(), h->d_dem[2].as<int32_t>(), h->d_out[0].as<int32_t>(),
+                              h->d_out[1].as<uint8_t>(), h->d_out[2].as<int8_t>(), st);
+        ba.choice = h->d_out[2].as<int8_t>();
+      } else {
+        CU(h->d_out[2].reserve((size_t)D * tg * K));
+        CU(h->d_out[3].reserve(sizeof(uint32_t) * (size_t)D * tg));
+        rc = launch_mps_score(h, D, h->d_dem[0].as<int32_t>(), h->d_dem[1].as<int32_t>(), h->d_dem[2].as<int32_t>(), h->d_out[0].as<int32_t>(),
+                              h->d_out[1].as<uint8_t>(), h->d_out[2].as<uint8_t>(), h->d_out[3].as<uint32_t>(), st);
+        ba.out_free = h->d_out[2].as<uint8_t>();
+        ba.out_mask = h->d_out[3].as<uint32_t>();
+      }
+      if (rc) { restore(); return rc; }
+      // commit, profile by profile in this candidate's order
+      if ((rc = upload(h, b[8], okey.data(), sizeof(int32_t) * D, st))) { restore(); return rc; }
+      if ((rc = upload(h, b[9], oidx.data(), sizeof(int32_t) * D, st))) { restore(); return rc; }
+      if ((rc = upload(h, b[10], olack.data(), sizeof(int32_t) * D, st))) { restore(); return rc; }
+      CU(cudaMemsetAsync(d_taken, 0, N, st));
+      ba.D = D;
+      ba.N = N;
+      ba.tg = tg;
+      ba.n_keys = K;
+      ba.row_key = b[8].as<int32_t>();
+      ba.row_index = b[9].as<int32_t>();
+      ba.row_lacking = b[10].as<int32_t>();
+      ba.updated = h->d_out[1].as<uint8_t>();
+      ba.gpu_off = kind ? h->d_mps_off.as<int32_t>() : h->d_mig_off.as<int32_t>();
+      ba.T = h->d_tables.as<MigTables>();
+      ba.m_model = h->d_mig_model.as<uint8_t>();
+      ba.m_used = h->d_mig_used.as<uint4>();
+      ba.m_free = h->d_mig_free.as<uint4>();
+      ba.p_gpu = h->d_mps_gpu.as<MpsGpu>();
+      ba.taken = d_taken;
+      ba.repartitioned = d_rep;
+      if (kind) batch_commit_kernel<true><<<1, 32, 0, st>>>(ba);
+      else batch_commit_kernel<false><<<1, 32, 0, st>>>(ba);
+      CU(cudaGetLastError());
+      ++rounds;
+      // the round's gains are locked in: the unplaced pods are first-fitted on the new state
+      const size_t before = unplaced.size();
+      if ((rc = batch_first_fit(c, unplaced, node_b, gpu_b))) { restore(); return rc; }
+      std::vector<int32_t> still;
+      for (int i : unplaced)
+        if (node_b[i] < 0) still.push_back(i);
+      unplaced.swap(still);
+      if (unplaced.size() == before) break;
+    }
+    int sched = 0;
+    for (int i = 0; i < M; ++i) sched += node_b[i] >= 0;
+    if (sched > best_sched) {
+      best_sched = sched;
+      best_order = order;
+      best_rounds = rounds;
+      best_node = node_b;
+      best_gpu = gpu_b;
+      best_rep.resize(N);
+      CU(cudaMemcpyAsync(best_rep.data(), d_rep, N, cudaMemcpyDeviceToHost, st));
+      if ((rc = copy_state(b[15], b[7], b[13], true, false))) { restore(); return rc; }
+      CU(cudaStreamSynchronize(st));
+    }
+  }
+  if ((rc = copy_state(b[15], b[7], b[13], false, false))) { restore(); return rc; }  // working := the kept candidate's final state
+  if ((rc = restore())) return rc;
+  for (int i = 0; i < M; ++i) {
+    if (node_a[i] >= 0) {
+      sched_node[i] = node_a[i];
+      sched_gpu[i] = gpu_a[i];
+      phase[i] = 1;
+    } else if (best_node[i] >= 0) {
+      sched_node[i] = best_node[i];
+      sched_gpu[i] = best_gpu[i];
+      phase[i] = 2;
+    }
+  }
+  for (int n = 0; n < N; ++n) repartitioned[n] = best_rep[n];
+  if (order_out) *order_out = best_order;
+  if (rounds_out) *rounds_out = best_rounds;
   return NOSPLAN_OK;
 }
 

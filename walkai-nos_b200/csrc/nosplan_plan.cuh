@@ -95,6 +95,7 @@ struct ChainArgs {
   const int32_t* dem_key;
   int M;
   int32_t* limit_out;         // [2] device: range of the next chain launch; plan_find_miss_kernel writes [1]
+  int ignore_gate;            // batch-demand mode: plain first-fit for every pod of the range, whatever the gate would say
   uint8_t* gate_hit;
   int32_t* repart_node;
   int32_t* sched_node;
@@ -186,7 +187,7 @@ __global__ void __launch_bounds__(32) plan_chain_kernel(ChainArgs a) {
     j1 = y0;
   }
   if (j0 >= j1) return;
-  if (a.present[key] <= 0) {
+  if (!a.ignore_gate && a.present[key] <= 0) {
     // only reachable for a dead profile (plan_find_miss_kernel stops the range at any other absent one): the gate
     // does not stop the pod (mig_controller.go:83-86), tryRepartition finds no node, nothing of it is free
     for (int j = j0 + lane; j < j1; j += 32) {
@@ -336,6 +337,94 @@ __global__ void __launch_bounds__(32) plan_chain_kernel(ChainArgs a) {
         }
       }
       t32 += r;
+    }
+  }
+}
+
+// ---- batch-demand mode (NEW BEHAVIOUR, oracle/batch_plan.py): commit step of one round -------------------------------
+// The batched scorer has scored the rows {key: lacking[key]} against every node of the round's starting state
+// (updated[D][N] and, per GPU, the geometry it would apply / the slice layout it would leave).  One warp now walks the
+// rows in the round's order and, per row, the nodes in list order: a node whose trial update succeeded and that no row
+// took yet in this round is committed while the row's demand is not covered by the free devices of the key on the nodes
+// committed before it.  32 nodes per step: the running demand is an exclusive prefix sum over the candidates' gains.
+struct BatchCommitArgs {
+  int D, N, tg, n_keys;
+  const int32_t* row_key;      // [D] in the round's order
+  const int32_t* row_index;    // [D] row of the scorer outputs
+  const int32_t* row_lacking;  // [D]
+  const uint8_t* updated;      // [D][N]
+  const int8_t* choice;        // MIG [D][tg]
+  const uint8_t* out_free;     // MPS [D][tg][S]
+  const uint32_t* out_mask;    // MPS [D][tg]
+  const int32_t* gpu_off;
+  const MigTables* T;
+  const uint8_t* m_model;
+  uint4* m_used;
+  uint4* m_free;
+  MpsGpu* p_gpu;
+  uint8_t* taken;              // [N] zero on entry
+  uint8_t* repartitioned;      // [N] accumulated over the rounds
+};
+
+template <bool MPS>
+__global__ void __launch_bounds__(32) batch_commit_kernel(const BatchCommitArgs a) {
+  const int lane = threadIdx.x;
+  for (int r = 0; r < a.D; ++r) {
+    const int key = a.row_key[r], row = a.row_index[r];
+    int rem = a.row_lacking[r];
+    for (int base = 0; base < a.N && rem > 0; base += 32) {
+      const int n = base + lane;
+      bool cand = false;
+      int gain = 0, g0 = 0, g1 = 0;
+      if (n < a.N) {
+        cand = a.updated[(size_t)row * a.N + n] != 0 && !a.taken[n];
+        if (cand) {
+          g0 = a.gpu_off[n];
+          g1 = a.gpu_off[n + 1];
+          for (int g = g0; g < g1; ++g) {  // free devices of the key on the node after the trial update
+            if constexpr (MPS) {
+              gain += (int)a.out_free[((size_t)row * a.tg + g) * a.n_keys + key];
+            } else {
+              const int c = a.choice[(size_t)row * a.tg + g];
+              if (c >= 0) {
+                const int m = a.m_model[g];
+                gain += (int)byte_of(a.T->cand[a.T->geom_off[m] + c], key) - (int)byte_of(a.m_used[g], key);
+              } else {
+                gain += (int)byte_of(a.m_free[g], key);
+              }
+            }
+          }
+        }
+      }
+      int incl = cand ? gain : 0;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+      }
+      const int excl = incl - (cand ? gain : 0);
+      const bool commit = cand && rem - excl > 0;
+      if (commit) {
+        for (int g = g0; g < g1; ++g) {
+          if constexpr (MPS) {
+            const uint8_t* f = a.out_free + ((size_t)row * a.tg + g) * a.n_keys;
+            uint32_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            for (int s = 0; s < a.n_keys; ++s) w[s >> 2] |= (uint32_t)f[s] << ((s & 3) * 8);
+            a.p_gpu[g].f0 = make_uint4(w[0], w[1], w[2], w[3]);
+            a.p_gpu[g].f1 = make_uint4(w[4], w[5], w[6], w[7]);
+            a.p_gpu[g].fmask = a.out_mask[(size_t)row * a.tg + g];
+          } else {
+            const int c = a.choice[(size_t)row * a.tg + g];
+            if (c >= 0) a.m_free[g] = sub4(a.T->cand[a.T->geom_off[a.m_model[g]] + c], a.m_used[g]);  // ApplyGeometry
+          }
+        }
+        a.taken[n] = 1;
+        a.repartitioned[n] = 1;
+      }
+      // what the committed nodes of this step cover: the gains of the candidates up to the last committed one
+      const uint32_t cm = __ballot_sync(0xffffffffu, commit);
+      if (cm) rem -= __shfl_sync(0xffffffffu, incl, 31 - __clz(cm));
+      __syncwarp();
     }
   }
 }

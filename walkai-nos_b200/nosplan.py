@@ -31,7 +31,7 @@ EXPORTS = [
     "nosplan_score_mps_dev", "nosplan_mig_evals_per_demand", "nosplan_mps_evals_per_demand", "nosplan_score_mig_static", "nosplan_diff_plan_mig",
     "nosplan_set_node_base", "nosplan_exchange_create", "nosplan_exchange_open", "nosplan_exchange_min_dev",
     "nosplan_exchange_status", "nosplan_exchange_destroy", "nosplan_score_snapshot", "nosplan_presence",
-    "nosplan_diff_plan_mig_devices", "nosplan_score_pass_dev", "nosplan_pass_status", "nosplan_kernel_timing", "nosplan_kernel_time_ms", "nosplan_executed_evals",
+    "nosplan_diff_plan_mig_devices", "nosplan_plan_batch", "nosplan_score_pass_dev", "nosplan_pass_status", "nosplan_kernel_timing", "nosplan_kernel_time_ms", "nosplan_executed_evals",
 ]
 
 
@@ -297,6 +297,21 @@ class Planner:
         self._ck(self.L.nosplan_plan(self.h, M, _p(kind, u8p), _p(off, i32p), _p(key, i32p), _p(qty, i32p), flags,
                                      _p(gate_hit, u8p), _p(rep, i32p), _p(node, i32p), _p(gpu, i32p)))
         return dict(gate_hit=gate_hit, repart_node=rep, sched_node=node, sched_gpu=gpu)
+
+    def plan_batch(self, kind: int, pod_key, pod_qty, max_rounds: int = 0):
+        """Batch-demand planning mode (nosplan_plan_batch; new behaviour, defined in oracle/batch_plan.py)."""
+        pod_key = np.ascontiguousarray(pod_key, np.int32)
+        pod_qty = np.ascontiguousarray(pod_qty, np.int32)
+        M = len(pod_key)
+        N = (self.mps if kind else self.mig)["n_nodes"]
+        node, gpu = np.full(max(M, 1), -2, np.int32), np.full(max(M, 1), -2, np.int32)
+        phase = np.zeros(max(M, 1), np.uint8)
+        rep = np.zeros(max(N, 1), np.uint8)
+        order, rounds = C.c_int32(0), C.c_int32(0)
+        self._ck(self.L.nosplan_plan_batch(self.h, int(kind), M, _p(pod_key), _p(pod_qty), int(max_rounds), _p(node), _p(gpu),
+                                           _p(phase), _p(rep), C.byref(order), C.byref(rounds)))
+        return dict(sched_node=node[:M], sched_gpu=gpu[:M], phase=phase[:M], repartitioned=rep[:N], order=order.value,
+                    rounds=rounds.value)
 
     def get_mig_state(self):
         tg = self.mig["tg"]
