@@ -528,6 +528,8 @@ def main():
         roofline = roof("mig_score16_kernel", mig_k_alone_ms)
         roofline["mps"] = roof("mps_score1_kernel", mps_k_alone_ms)
         roofline["scoring_launch_ms_in_step"] = both_k_ms  # score_both_kernel: both scorers' CTAs in one launch
+        if Dm and Dp:
+            roofline["step_launch"] = roof("score_both_kernel", both_k_ms)  # the step's one scoring launch, timed inside the step
         # SURVEY 8(d)'s byte model (64 B state + 4 B result per (row, node, GPU), no credit for on-chip reuse) as a work
         # rate: the tiles are read once per CTA and re-used from shared memory, so this is NOT HBM traffic
         if Dm and mig_k_alone_ms > 0:

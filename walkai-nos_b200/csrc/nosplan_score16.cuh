@@ -704,10 +704,18 @@ __global__ void __launch_bounds__(TN * DS, 4) mps_score1_kernel(const MpsScoreAr
 // scorer's.  One pool of CTAs drains over the SMs, so a small shard fills the GPU without two streams and the
 // events that fork and join them.  TNM: nodes per MIG CTA; the MPS part keeps 128 nodes x 4 threads.
 template <int TNM, int CW, bool CNT>
-__global__ void __launch_bounds__(512, 3) score_both_kernel(const MigScore16Args A, const MpsScoreArgs a, int mig_x, int n_mig, int mps_x) {
-  const int i = blockIdx.x;
+__global__ void __launch_bounds__(512, 3) score_both_kernel(const MigScore16Args A, const MpsScoreArgs a, int mig_x, int n_mig, int mps_x,
+                                                            int n_mps_first) {
+  // n_mps_first: how many of the MPS scorer's CTAs are handed out before the MIG scorer's (measurement knob
+  // NOSPLAN_BOTH_ORDER: 0 = MIG first, the default; 1 = MPS first)
+  int i = blockIdx.x;
+  if (i < n_mps_first) {
+    mps_score1_body<128, 4, false, CNT>(a, i % mps_x, i / mps_x);
+    return;
+  }
+  i -= n_mps_first;
   if (i < n_mig) mig_score16_body<TNM, 512 / TNM, CW, false, 2, CNT>(A, i % mig_x, i / mig_x);
-  else mps_score1_body<128, 4, false, CNT>(a, (i - n_mig) % mps_x, (i - n_mig) / mps_x);
+  else mps_score1_body<128, 4, false, CNT>(a, (i - n_mig + n_mps_first) % mps_x, (i - n_mig + n_mps_first) / mps_x);
 }
 
 }  // namespace nsp
