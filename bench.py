@@ -144,7 +144,7 @@ def run_reference(args, cfg, rank):
     line = {
         "impl": "reference", "metric": "candidate_evaluations_per_second", "value": val, "unit": "evals/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
-        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u8/int32", "data": "synthetic",
+        "higher_is_better": True, "scaling": "weak" if args.weak else "strong", "vs_baseline": None, "dtype": "u8/int32", "data": "synthetic",
         "config": workload_config(cfg, args),
         "cpu_baseline": {"value": val, "unit": "evals/s", "cores": cores, "kind": "port",
                          "sample": f"first {Dm} MIG + {Dp} MPS pods x all nodes per step (Go reference unbuildable here: no Go toolchain)"},
@@ -192,6 +192,7 @@ def main():
     ap.add_argument("--ref-sample", type=int, default=4096)
     ap.add_argument("--nodes", type=int, default=0)
     ap.add_argument("--pods", type=int, default=0)
+    ap.add_argument("--weak", action="store_true", help="weak scaling: the config's node count PER GPU (nodes x N in all), pods unchanged; the line says scaling=weak")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-plan", action="store_true", help="skip the planner-latency section (profiling runs)")
     ap.add_argument("--loopback-exchange", action="store_true", help="one GPU: open a one-rank exchange (measures what the exchange path costs without peers)")
@@ -204,6 +205,8 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
 
     import walkai_nos_b200 as pkg
+    if args.weak and not args.nodes:
+        args.nodes = {1: 1, 2: 64, 3: 256, 4: 1024, 5: 4096}[args.config] * max(args.gpus, 1)
     cfg = pkg.synth.make_config(args.config, args.nodes, args.pods)
 
     if args.impl == "reference":
@@ -539,7 +542,7 @@ def main():
         line = {
             "metric": "candidate_evaluations_per_second", "value": value, "unit": "evals/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "u8/int32", "data": "synthetic",
+            "scaling": "weak" if args.weak else "strong", "vs_baseline": None, "dtype": "u8/int32", "data": "synthetic",
             "config": workload_config(cfg, args),
             "e2e": {"value": e2e_val, "unit": "evals/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "ms_per_step": float(e2e_t.item()) * 1e3},

@@ -80,6 +80,76 @@ def main():
           f"({n_ann / t_snap:.3g} annotations/s, Python marshalling included); {len(pods)} pod specs -> "
           f"{len(rows['off']) - 1} request rows in {t_pods * 1e3:.1f} ms")
     assert int(a["gpu_off"][-1]) == 4096 * 8
+    more_rows(rng)
+
+
+def more_rows(rng):
+    """Round-2 rows: the device-level diff planner, the table loader, the batch-demand mode and the allocation-free scorer."""
+    import torch
+    from oracle import batch_plan
+    p = pkg.Planner(0)
+    # f2 at device level: 32 768 GPUs, ~6 devices each
+    G, P = 32768, 13
+    n_dev = rng.integers(0, 8, size=G)
+    off = np.concatenate([[0], np.cumsum(n_dev)]).astype(np.int32)
+    prof = rng.integers(0, P, size=int(off[-1])).astype(np.int32)
+    status = rng.integers(0, 3, size=int(off[-1])).astype(np.uint8)
+    spec = rng.integers(0, 4, size=(G, P)).astype(np.int32)
+    mask = rng.integers(0, 1 << P, size=G).astype(np.uint32)
+    t = med(lambda: p.diff_plan_mig_devices(off, prof, status, spec, mask))
+    print(f"f2 device level, {G} GPUs / {int(off[-1])} devices: C ABI {t * 1e3:.3f} ms = {G / t:.3g} GPU rows/s")
+    # a16 loader: the deployed table
+    with open(os.path.join(os.path.dirname(pkg.__file__), "data", "known_mig_geometries.yaml")) as f:
+        text = f.read()
+    t = med(lambda: pkg.host.load_tables(text), n=50)
+    print(f"a16 loader: known_mig_geometries.yaml ({len(text)} bytes, 3 entries, 8 models) -> flat tables in {t * 1e6:.0f} us (Python marshalling included)")
+    # f4 batch-demand mode at cfg5 size, next to the CPU definition
+    cfg = pkg.synth.make_config(5)
+    p.set_mig_tables(cfg["names"], cfg["geom_off"], cfg["geom_counts"])
+    p.set_mig_snapshot(cfg["mig"])
+    p.set_mps_snapshot(cfg["sizes"], cfg["mps"])
+    o = orc.Oracle(cfg["tables"], mps_sizes=cfg["sizes"])
+    for kind, kd in (("mig", 0), ("mps", 1)):
+        off_, key, qty, _ = pkg.synth.pods_of_kind(cfg["pods"], kd)
+        M = len(off_) - 1
+        r = p.plan_batch(kd, key[:M], qty[:M])
+        t = med(lambda: p.plan_batch(kd, key[:M], qty[:M]), n=5, warm=1)
+        t0 = time.perf_counter()
+        e = batch_plan.batch_plan(o, kind, cfg[kind], key[:M], qty[:M])
+        tc = time.perf_counter() - t0
+        assert np.array_equal(r["sched_node"], e["sched_node"])
+        print(f"f4 batch mode {kind}: {M} pods x {cfg[kind]['n_nodes']} nodes: {t * 1e3:.2f} ms on the GPU ({r['rounds']} rounds, "
+              f"{int((r['phase'] == 1).sum())} placed at once + {int((r['phase'] == 2).sum())} after re-partitioning {int(r['repartitioned'].sum())} nodes, "
+              f"{int((r['phase'] == 0).sum())} pending); CPU definition {tc * 1e3:.0f} ms")
+    # the allocation-free MIG scorer next to the ordinary device-resident one (cfg5: 2048 MIG nodes, 25 000 rows)
+    mig = cfg["mig"]
+    off_, key, qty, _ = pkg.synth.pods_of_kind(cfg["pods"], 0)
+    D = len(off_) - 1
+    dev = torch.device("cuda", 0)
+    tt = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    bufs = [tt(mig[k]) for k in ("valid", "model", "used", "free")] + [tt(off_), tt(key), tt(qty)]
+    first = torch.empty(D, dtype=torch.int32, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+
+    def dev_time(f, n=20):
+        for _ in range(3):
+            f()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            f()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n
+    ts = dev_time(lambda: p.score_mig_static(int(mig["n_nodes"]), 8, *[b.data_ptr() for b in bufs[:4]], D, *[b.data_ptr() for b in bufs[4:]],
+                                             first.data_ptr(), st))
+    a = first.cpu().numpy().copy()
+    td = dev_time(lambda: p.score_mig_dev(D, bufs[4].data_ptr(), bufs[5].data_ptr(), bufs[6].data_ptr(), first.data_ptr(), 0, 0, st))
+    assert np.array_equal(a, first.cpu().numpy())
+    print(f"nosplan_score_mig_static (snapshot packed inside the call, general scorer): {ts:.3f} ms per call; nosplan_score_mig_dev "
+          f"(snapshot resident, ordered scorer): {td:.3f} ms; same winners")
+    p.close()
 
 
 if __name__ == "__main__":
