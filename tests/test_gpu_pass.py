@@ -85,6 +85,40 @@ def test_pass_equals_oracle_on_random_clusters(seed):
         p.close()
 
 
+@pytest.mark.parametrize("cfgno,nodes,pods", [(3, 40, 700), (2, 16, 300)])
+def test_status_after_a_pass_over_one_kind_only(cfgno, nodes, pods):
+    """A handle that only ever saw one kind of snapshot: the status word of the other kind was never written and must
+    read as clean (BASELINE configs[2] is MPS only, configs[1] MIG only)."""
+    import torch
+
+    import walkai_nos_b200 as pkg
+    cfg = pkg.synth.make_config(cfgno, nodes, pods)
+    p = pkg.Planner(0)
+    try:
+        p.set_mig_tables(cfg["names"], cfg["geom_off"], cfg["geom_counts"])
+        o = orc.Oracle(cfg["tables"], mps_sizes=cfg["sizes"])
+        none = (np.zeros(1, np.int32),) * 3
+        if cfg["mig"] is not None:
+            p.set_mig_snapshot(cfg["mig"])
+            rows_m, rows_p = pkg.synth.pods_of_kind(cfg["pods"], 0)[:3], none
+            req, mask = pkg.synth.csr_to_dense(*rows_m, len(cfg["names"]))
+            exp = o.score_mig(cfg["mig"], req, mask, threads=8, want_choice=False)[2]
+        else:
+            p.set_mps_snapshot(cfg["sizes"], cfg["mps"])
+            rows_m, rows_p = none, pkg.synth.pods_of_kind(cfg["pods"], 1)[:3]
+            req, mask = pkg.synth.csr_to_dense(*rows_p, len(cfg["sizes"]))
+            exp = o.score_mps(cfg["mps"], req, mask, threads=8, want_free=False)[3]
+        for with_exchange in (False, True):
+            if with_exchange:
+                p.exchange_open([p.exchange_create(0, 1, len(exp))])
+            for flags in (1, 3, 0):
+                assert np.array_equal(_run_pass(torch, pkg, p, rows_m, rows_p, flags), exp), (with_exchange, flags)
+                p.pass_status()
+        p.exchange_destroy()
+    finally:
+        p.close()
+
+
 def test_pass_measurement_hooks_cfg5_shard():
     import torch
 

@@ -1,5 +1,6 @@
 """Summarises ncu outputs into profiles/: launch list (per-kernel share) and key metrics of a full capture.
-usage: python tools/ncu_summary.py <launches.csv> <prof.ncu-rep> <out.md>"""
+usage: python tools/ncu_summary.py <launches.csv> <prof.ncu-rep | raw-page.csv> <out.md> [W:<raw.csv>:<launches.csv> ...]
+The optional W:... arguments append the same kernels on rank 0's shard of a W-rank run (tools/prof_bench.sh <tag> --shard-of W)."""
 import collections, csv, subprocess, sys
 
 launches, rep, out = sys.argv[1:4]
@@ -16,7 +17,7 @@ lines.append("## Launch list (ncu --metrics gpu__time_duration.sum --clock-contr
 lines.append("| kernel | launches | avg us | share |\n|---|---|---|---|")
 for k, v in sorted(agg.items(), key=lambda kv: -sum(kv[1])):
     lines.append(f"| `{k}` | {len(v)} | {sum(v)/len(v)/1e3:.1f} | {sum(v)/tot*100:.1f}% |")
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+raw = open(rep).read() if rep.endswith(".csv") else subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rr = list(csv.reader(raw.splitlines()))
 H = rr[0]; units = rr[1]
 want = ['gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum', 'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed',
@@ -38,5 +39,42 @@ for r in rr[2:]:
         if w in H:
             lines.append(f"| {w} | {r[H.index(w)]} | {units[H.index(w)]} |")
     lines.append("")
+shards = [a.split(":") for a in sys.argv[4:]]
+if shards:
+    lines.append("\n## The same command on rank 0's shard of a W-rank run (`bench.py --shard-of W`, one GPU; `tools/prof_bench.sh`)\n")
+    lines.append("| shard | kernel | duration (ncu) | warp-instructions | issue active | ALU pipe | DRAM read | grid | waves |\n|---|---|---|---|---|---|---|---|---|")
+    tails = []
+    for w, raw_csv, launches_csv in [("1", rep, launches)] + shards:
+        if not raw_csv.endswith(".csv"):
+            continue
+        q = list(csv.reader(open(raw_csv).read().splitlines()))
+        Hq, seen = q[0], set()
+        col = lambda r, k: r[Hq.index(k)]
+        for r in q[2:]:
+            name = col(r, "Kernel Name").split("<")[0].replace("void ", "")
+            if name in seen:
+                continue
+            seen.add(name)
+            lines.append(f"| 1/{w} | `{name}` | {float(col(r, 'gpu__time_duration.sum')):.1f} us | {float(col(r, 'smsp__inst_executed.sum')):.4g} | "
+                         f"{float(col(r, 'smsp__issue_active.avg.pct_of_peak_sustained_active')):.1f} % | "
+                         f"{float(col(r, 'sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active')):.1f} % | "
+                         f"{float(col(r, 'dram__bytes_read.sum')):.2f} {q[1][Hq.index('dram__bytes_read.sum')]} | {col(r, 'launch__grid_size')} | "
+                         f"{col(r, 'launch__waves_per_multiprocessor')} |")
+        if w != "1":
+            rows2 = [r for r in csv.reader(open(launches_csv)) if len(r) > 5]
+            h2 = [i for i, r in enumerate(rows2) if r[0] == 'ID'][0]
+            H2 = rows2[h2]
+            agg2 = collections.OrderedDict()
+            for r in rows2[h2 + 1:]:
+                agg2.setdefault(r[H2.index('Kernel Name')][:60], []).append(float(r[H2.index('Metric Value')].replace(',', '')))
+            tot2 = sum(sum(v) for v in agg2.values())
+            tails.append(f"* 1/{w}: " + "; ".join(f"`{k}` x{len(v)} avg {sum(v) / len(v) / 1e3:.1f} us ({sum(v) / tot2 * 100:.0f} %)"
+                                                  for k, v in sorted(agg2.items(), key=lambda kv: -sum(kv[1]))[:6]))
+    lines.append("\nLaunch lists of the shard runs (`ncu --metrics gpu__time_duration.sum`, cold-cache and serialised: compare shares):\n")
+    lines += tails
+MARK = "<!-- kept by tools/ncu_summary.py: everything below this line is hand-written -->"
+import os
+if os.path.exists(out) and MARK in open(out).read():
+    lines.append("\n" + MARK + open(out).read().split(MARK, 1)[1].rstrip("\n"))
 open(out, "w").write("\n".join(lines) + "\n")
 print("\n".join(lines))

@@ -103,24 +103,31 @@ def more_rows(rng):
         text = f.read()
     t = med(lambda: pkg.host.load_tables(text), n=50)
     print(f"a16 loader: known_mig_geometries.yaml ({len(text)} bytes, 3 entries, 8 models) -> flat tables in {t * 1e6:.0f} us (Python marshalling included)")
-    # f4 batch-demand mode at cfg5 size, next to the CPU definition
-    cfg = pkg.synth.make_config(5)
-    p.set_mig_tables(cfg["names"], cfg["geom_off"], cfg["geom_counts"])
-    p.set_mig_snapshot(cfg["mig"])
-    p.set_mps_snapshot(cfg["sizes"], cfg["mps"])
-    o = orc.Oracle(cfg["tables"], mps_sizes=cfg["sizes"])
-    for kind, kd in (("mig", 0), ("mps", 1)):
-        off_, key, qty, _ = pkg.synth.pods_of_kind(cfg["pods"], kd)
-        M = len(off_) - 1
-        r = p.plan_batch(kd, key[:M], qty[:M])
-        t = med(lambda: p.plan_batch(kd, key[:M], qty[:M]), n=5, warm=1)
+    # f4 batch-demand mode: parity + CPU time of the definition on a cfg5 shard, GPU time at the full cfg5 size
+    def batch_once(cfg, kind, kd, key, qty):
+        (p.set_mig_snapshot if kd == 0 else lambda s: p.set_mps_snapshot(cfg["sizes"], s))(cfg[kind])
         t0 = time.perf_counter()
-        e = batch_plan.batch_plan(o, kind, cfg[kind], key[:M], qty[:M])
-        tc = time.perf_counter() - t0
-        assert np.array_equal(r["sched_node"], e["sched_node"])
-        print(f"f4 batch mode {kind}: {M} pods x {cfg[kind]['n_nodes']} nodes: {t * 1e3:.2f} ms on the GPU ({r['rounds']} rounds, "
-              f"{int((r['phase'] == 1).sum())} placed at once + {int((r['phase'] == 2).sum())} after re-partitioning {int(r['repartitioned'].sum())} nodes, "
-              f"{int((r['phase'] == 0).sum())} pending); CPU definition {tc * 1e3:.0f} ms")
+        r = p.plan_batch(kd, key, qty)
+        return r, time.perf_counter() - t0
+    for nodes, pods, check in ((256, 3000, True), (0, 0, False)):
+        cfg = pkg.synth.make_config(5, nodes, pods)
+        p.set_mig_tables(cfg["names"], cfg["geom_off"], cfg["geom_counts"])
+        o = orc.Oracle(cfg["tables"], mps_sizes=cfg["sizes"])
+        for kind, kd in (("mig", 0), ("mps", 1)):
+            off_, key, qty, _ = pkg.synth.pods_of_kind(cfg["pods"], kd)
+            M = len(off_) - 1
+            batch_once(cfg, kind, kd, key[:M], qty[:M])
+            r, t = min((batch_once(cfg, kind, kd, key[:M], qty[:M]) for _ in range(5)), key=lambda x: x[1])
+            extra = ""
+            if check:
+                t0 = time.perf_counter()
+                e = batch_plan.batch_plan(o, kind, cfg[kind], key[:M], qty[:M])
+                extra = f"; CPU definition {(time.perf_counter() - t0) * 1e3:.0f} ms, same result"
+                assert np.array_equal(r["sched_node"], e["sched_node"]) and np.array_equal(r["repartitioned"], e["repartitioned"])
+            print(f"f4 batch mode {kind}: {M} pods x {cfg[kind]['n_nodes']} nodes: {t * 1e3:.2f} ms through the C ABI ({r['rounds']} rounds, "
+                  f"{int((r['phase'] == 1).sum())} placed at once + {int((r['phase'] == 2).sum())} after re-partitioning "
+                  f"{int(r['repartitioned'].sum())} nodes, {int((r['phase'] == 0).sum())} pending){extra}")
+    p.set_mig_snapshot(cfg["mig"])
     # the allocation-free MIG scorer next to the ordinary device-resident one (cfg5: 2048 MIG nodes, 25 000 rows)
     mig = cfg["mig"]
     off_, key, qty, _ = pkg.synth.pods_of_kind(cfg["pods"], 0)

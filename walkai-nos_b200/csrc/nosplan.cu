@@ -284,11 +284,23 @@ int min_chunk() {  // measurement knob: fewest rows per work item of 128 nodes
   return w;
 }
 
-int score_waves() {  // measurement knob: waves of CTAs per scorer launch
+// Waves of CTAs a scorer launch is split into.  Measured (profiles/r2_bench_cfg5.md, "work-item size"): a kind scored on
+// its own wants 4; the launch that carries both kinds wants 2 — its MIG and MPS CTAs fill each other's tails, so the
+// larger work items win (fewer tile loads).  NOSPLAN_SCORE_WAVES=n overrides both.
+int score_waves(bool both_kinds = false) {
   static const int w = [] {
     const char* e = std::getenv("NOSPLAN_SCORE_WAVES");
-    const int v = e ? std::atoi(e) : 4;
-    return v >= 1 && v <= 16 ? v : 4;
+    const int v = e ? std::atoi(e) : 0;
+    return v >= 1 && v <= 16 ? v : 0;
+  }();
+  return w ? w : both_kinds ? 2 : 4;
+}
+
+int mps_min_chunk() {  // measurement knob: fewest rows per MPS work item (128 nodes) in a scoring pass
+  static const int w = [] {
+    const char* e = std::getenv("NOSPLAN_MPS_MIN_CHUNK");
+    const int v = e ? std::atoi(e) : 128;
+    return v >= 8 && v <= 512 ? v : 128;
   }();
   return w;
 }
@@ -365,7 +377,7 @@ int reserve_rows(nosplan_t* h, int kind, int D, int n_keys, int chunk, cudaStrea
 }
 // the row code a status word holds for the kind's last grouping call, ~0 = every row was fine
 unsigned long long row_status_code(const nosplan_t* h, int kind, unsigned long long word) {
-  if ((uint32_t)(word >> 32) != h->row_call[kind]) return ~0ull;
+  if (h->row_call[kind] == 0 || (uint32_t)(word >> 32) != h->row_call[kind]) return ~0ull;  // call 0 = this kind was never grouped
   return (unsigned long long)(0xffffffffu - (uint32_t)word);
 }
 RowsGroupArgs group_args(nosplan_t* h, int kind, int D, int n_keys, int chunk, const int32_t* dem_off, const int32_t* dem_key,
@@ -457,7 +469,7 @@ void (*mig16_kernel_cw(int cw, bool out, bool cnt))(MigScore16Args) {
     default: return mig16_kernel_of<TN, 4>(out, cnt);
   }
 }
-int mig16_prepare(nosplan_t* h, int D, bool out, bool cnt, Mig16Launch* L) {
+int mig16_prepare(nosplan_t* h, int D, bool out, bool cnt, Mig16Launch* L, bool both_kinds = false) {
   const int cw = std::max(1, std::min(4, (h->cmax + 3) / 4));
   const int tn = L->tn = mig16_tile();
   L->kern = tn == 32 ? mig16_kernel_cw<32>(cw, out, cnt) : tn == 64 ? mig16_kernel_cw<64>(cw, out, cnt) : mig16_kernel_cw<128>(cw, out, cnt);
@@ -474,7 +486,7 @@ int mig16_prepare(nosplan_t* h, int D, bool out, bool cnt, Mig16Launch* L) {
   }
   int gy = 1;
   // at least 64 rows per 128 nodes of a work item: on a small shard the tile load would otherwise outweigh the rows
-  pick_chunks(h->sm_count, L->tiles, D, std::min(min_chunk() * 128 / tn, kRowCap), &L->chunk, &gy, occ * score_waves());
+  pick_chunks(h->sm_count, L->tiles, D, std::min(min_chunk() * 128 / tn, kRowCap), &L->chunk, &gy, occ * score_waves(both_kinds));
   L->chunk = std::min(L->chunk, kRowCap);
   return NOSPLAN_OK;
 }
@@ -1292,15 +1304,17 @@ int score_pass_enqueue(nosplan_t* h, nosplan_t* x, int Dm, const int32_t* m_off,
   // ---- both kinds on the ordered kernels: one grouping launch, the two scorers side by side ----
   Mig16Launch L;
   int mw_m = 0, mw_p = 0, chunk_p = 128, tiles_p = 0;
+  // both kinds, single-key rows, nobody asked for the kinds one after the other: ONE launch scores both
+  const bool both = have_m && have_p && single && !(flags & NOSPLAN_PASS_SERIAL);
   if (have_m) {
-    if ((rc = mig16_prepare(h, Dm, false, count, &L))) return rc;
+    if ((rc = mig16_prepare(h, Dm, false, count, &L, both))) return rc;
     if ((rc = reserve_rows(h, 0, Dm, h->P, L.chunk, st, &mw_m))) return rc;
   }
   size_t smem_p = 0;
   if (have_p) {
     tiles_p = (h->mps_n + kScoreTN - 1) / kScoreTN;
     int gy;
-    pick_chunks(h->sm_count, tiles_p, Dp, 128, &chunk_p, &gy, 4 * score_waves());
+    pick_chunks(h->sm_count, tiles_p, Dp, mps_min_chunk(), &chunk_p, &gy, 4 * score_waves(both));
     chunk_p = std::min(chunk_p, kRowCap);
     smem_p = mps_score1_smem_bytes(h->mps_gs, h->S, kScoreTN);
     if (smem_p > 200 * 1024) return fail(h, NOSPLAN_ERR_RANGE, "MPS scorer tile needs %zu bytes of shared memory", smem_p);
@@ -1342,8 +1356,6 @@ int score_pass_enqueue(nosplan_t* h, nosplan_t* x, int Dm, const int32_t* m_off,
     push.ticket = xc.done.as<unsigned int>();
     for (int r = 0; r < xc.world; ++r) push.flags[r] = xc.peers.pushed[r];
   }
-  // both kinds, single-key rows, nobody asked for the kinds one after the other: ONE launch scores both
-  const bool both = have_m && have_p && single && !(flags & NOSPLAN_PASS_SERIAL);
   cudaStream_t st_p = st;
   if (both) {
     MigScore16Args A = mig16_args(h, mig_base_args(h, Dm, m_off, m_key, m_qty, first_m, h->mig_base));
