@@ -359,7 +359,7 @@ def main():
     step_device(None, PASS | pkg.nosplan.PASS_COUNT)
     barrier()
     ex_m, ex_p = planner.executed_evals()
-    tt = torch.tensor([total_ms, (mig_ms + mps_ms) / max(mig_n, 1), 0.0, mig_alone_ms / max(mig_alone_n, 1),
+    tt = torch.tensor([total_ms, (mig_ms + mps_ms) / max(mig_n, mps_n, 1), 0.0, mig_alone_ms / max(mig_alone_n, 1),
                        mps_alone_ms / max(mps_alone_n, 1)], dtype=torch.float64, device=dev)
     evt = torch.tensor([float(ev_m_local), float(ev_p_local), float(ex_m), float(ex_p)], dtype=torch.float64, device=dev)
     per_rank = None

@@ -42,7 +42,9 @@ typedef struct nosplan nosplan_t;
 #define NOSPLAN_MAX_GEOMS 32          /* allowed geometries per model                              */
 #define NOSPLAN_MAX_MPS_SIZES 32      /* MPS vocabulary columns                                    */
 #define NOSPLAN_MAX_GPUS_PER_NODE 16
-#define NOSPLAN_MAX_COUNT 255         /* used[p] + free[p] per GPU and profile                     */
+#define NOSPLAN_MAX_COUNT 255         /* used[p] + free[p] per GPU and profile — and per GPU and MPS size: counts are
+                                         bytes on the device, a GPU cut into more than 255 slices of one size is
+                                         refused at upload, never wrapped                                        */
 #define NOSPLAN_MAX_MEM_GB 65535
 #define NOSPLAN_MAX_DEMAND_KEYS 8     /* distinct profiles one pod may request                     */
 #define NOSPLAN_MAX_DEMAND_QTY 1000000
