@@ -77,8 +77,7 @@ def test_yaml_forms_the_reference_file_could_use(host):
 
 def test_shipped_table_is_the_transcribed_reference_table(host):
     import walkai_nos_b200 as pkg
-    with open(os.path.join(os.path.dirname(pkg.__file__), "data", "known_mig_geometries.yaml")) as f:
-        entries, g = host.load_tables(f.read())
+    entries, g = host.load_tables(pkg.synth.table_yaml_text())
     gold = load_tables()["yaml"]  # tests/golden/tables.json, transcribed from the reference's YAML with its line numbers
     assert entries == [{"models": e["models"], "allowedGeometries": e["allowedGeometries"]} for e in gold]
     assert pkg.synth.yaml_tables() == g["tables"]

@@ -99,8 +99,7 @@ def more_rows(rng):
     t = med(lambda: p.diff_plan_mig_devices(off, prof, status, spec, mask))
     print(f"f2 device level, {G} GPUs / {int(off[-1])} devices: C ABI {t * 1e3:.3f} ms = {G / t:.3g} GPU rows/s")
     # a16 loader: the deployed table
-    with open(os.path.join(os.path.dirname(pkg.__file__), "data", "known_mig_geometries.yaml")) as f:
-        text = f.read()
+    text = pkg.synth.table_yaml_text()
     t = med(lambda: pkg.host.load_tables(text), n=50)
     print(f"a16 loader: known_mig_geometries.yaml ({len(text)} bytes, 3 entries, 8 models) -> flat tables in {t * 1e6:.0f} us (Python marshalling included)")
     # f4 batch-demand mode: parity + CPU time of the definition on a cfg5 shard, GPU time at the full cfg5 size

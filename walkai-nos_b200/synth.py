@@ -3,8 +3,8 @@
 Deterministic: splitmix64 seeded 0x6e6f730000 + config number, consumed in the order documented in
 each function.  Used by the parity tests and by bench.py (the same arrays go to the CUDA library and
 to the CPU oracle).  Geometry tables are the reference's deployed YAML table
-(config/gpupartitioner/manager/known_mig_geometries.yaml:1-59), shipped as data/known_mig_geometries.yaml and read
-through the native loader of libnoshost.
+(config/gpupartitioner/manager/known_mig_geometries.yaml:1-59), kept as data/mig_geometries.json, rendered into the
+reference's wire format and read through the native loader of libnoshost.
 """
 from __future__ import annotations
 
@@ -19,19 +19,34 @@ MASK64 = (1 << 64) - 1
 MIG_PROFILES = sorted(["1g.6gb", "2g.12gb", "4g.24gb", "1g.5gb", "2g.10gb", "3g.20gb", "4g.20gb", "7g.40gb",
                        "1g.10gb", "2g.20gb", "3g.40gb", "4g.40gb", "7g.79gb"])
 
-_TABLE_FILE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "known_mig_geometries.yaml")
+_TABLE_FILE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "mig_geometries.json")
 _tables_cache = None
 
 
+def table_yaml_text() -> str:
+    """The deployed geometry table (data/mig_geometries.json: the entries of the reference's
+    config/gpupartitioner/manager/known_mig_geometries.yaml:1-59) in the wire format the reference reads: a block sequence
+    of {models: [flow list], allowedGeometries: [block mappings]}."""
+    import json
+    with open(_TABLE_FILE) as f:
+        entries = json.load(f)["entries"]
+    lines = []
+    for e in entries:
+        lines.append("- models: [ " + ", ".join('"%s"' % m for m in e["models"]) + " ]")
+        lines.append("  allowedGeometries:")
+        for geom in e["allowedGeometries"]:
+            for j, (name, qty) in enumerate(geom.items()):
+                lines.append(("    - " if j == 0 else "      ") + f"{name}: {qty}")
+    return "\n".join(lines) + "\n"
+
+
 def yaml_tables() -> Dict[str, List[Dict[str, int]]]:
-    """The deployed geometry table (data/known_mig_geometries.yaml, the reference's
-    config/gpupartitioner/manager/known_mig_geometries.yaml:1-59) read through the native loader
-    (noshost_tables_load: AllowedMigGeometries.UnmarshalJSON + GroupByModel, pkg/gpu/mig/allowed_geometries.go:30-82)."""
+    """model -> allowed geometries of the deployed table, read through the native loader (noshost_tables_load:
+    AllowedMigGeometries.UnmarshalJSON + GroupByModel, pkg/gpu/mig/allowed_geometries.go:30-82)."""
     global _tables_cache
     if _tables_cache is None:
         from . import host
-        with open(_TABLE_FILE) as f:
-            _tables_cache = host.load_tables(f.read())[1]["tables"]
+        _tables_cache = host.load_tables(table_yaml_text())[1]["tables"]
     return {m: [dict(g) for g in geoms] for m, geoms in _tables_cache.items()}
 
 
