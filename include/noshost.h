@@ -20,7 +20,11 @@ extern "C" {
 #define NOSHOST_STATUS_USED 0
 #define NOSHOST_STATUS_FREE 1
 #define NOSHOST_STATUS_UNKNOWN 2
-/* ParseStatusAnnotation (annotation.go:56-85): "nos.nebuly.com/status-gpu-<idx>-<profile>-<status>" = qty */
+/* Return codes of the parsers and name scanners below: 0 = parsed, 1 = the text is not of that form (what the reference
+ * reports as an error), 2 = the name does not fit the caller's buffer with its terminator (nothing is written: a parsed
+ * name is never truncated).  Indexes and quantities are int32 in this ABI: strconv.Atoi would accept up to 64 bits, a
+ * number beyond 32 bits is answered with 1 here (the annotation is ignored) instead of being wrapped.
+ * ParseStatusAnnotation (annotation.go:56-85): "nos.nebuly.com/status-gpu-<idx>-<profile>-<status>" = qty */
 int noshost_parse_status_annotation(const char* key, const char* value, int32_t* index, char* profile, int profile_cap,
                                     int32_t* status, int32_t* quantity);
 /* ParseSpecAnnotation (annotation.go:29-54): "nos.nebuly.com/spec-gpu-<idx>-<profile>" = qty */
@@ -29,7 +33,8 @@ int noshost_parse_spec_annotation(const char* key, const char* value, int32_t* i
 /* StatusAnnotation.String / SpecAnnotation.String (annotation.go:125-127, 161-163); returns the length */
 int noshost_format_status_annotation(int32_t index, const char* profile, int32_t status, char* out, int cap);
 int noshost_format_spec_annotation(int32_t index, const char* profile, char* out, int cap);
-/* gpu.GetMemoryGB (pkg/gpu/util.go:59-73): Atoi the nvidia.com/gpu.memory label, ceil(MB / 1000) */
+/* gpu.GetMemoryGB (pkg/gpu/util.go:59-73): Atoi the nvidia.com/gpu.memory label, ceil(MB / 1000); 1 when the label does
+ * not parse or the result does not fit int32 */
 int noshost_memory_gb(const char* label, int32_t* out);
 /* mig.ExtractProfileName (pkg/gpu/mig/util.go:46-52): resource must match nvidia\.com\/mig-\d+g\.\d+gb */
 int noshost_mig_profile_of_resource(const char* resource, char* profile, int cap);

@@ -1,0 +1,156 @@
+"""No GPU: adversarial and random inputs for libnoshost's string parsers (the wire format of pkg/gpu/annotation.go:29-224,
+the resource-name scanners of pkg/gpu/mig/util.go and slicing/profile.go, the memory label of pkg/gpu/util.go:59-73, the
+geometry-table loader).  The library must answer every input with a value or an error code — never crash, never write
+past the caller's buffer — and well-formed keys must survive a format -> parse round trip.  tools/run_host_sanitizers.sh
+runs this file against the AddressSanitizer + UBSan build as well."""
+import ctypes as C
+import random
+import string
+
+import pytest
+
+import walkai_nos_b200 as pkg
+
+host = pkg.host
+PREFIX_STATUS = "nos.nebuly.com/status-gpu-"
+PREFIX_SPEC = "nos.nebuly.com/spec-gpu-"
+ALPHABET = string.ascii_letters + string.digits + "-._/: \t\"'[]{}#,\\%+" + "é中"
+
+
+def _rand(rng, n):
+    return "".join(rng.choice(ALPHABET) for _ in range(n))
+
+
+def _mutations(rng, s):
+    yield s
+    for _ in range(6):
+        i = rng.randrange(len(s) + 1)
+        yield s[:i] + _rand(rng, rng.randrange(1, 4)) + s[i:]       # insertion
+        if s:
+            j = rng.randrange(len(s))
+            yield s[:j] + s[j + 1:]                                  # deletion
+            yield s[:j]                                              # truncation
+    yield s * 3
+    yield s + "9" * 40                                               # digits that overflow an int
+
+
+def test_annotation_parsers_survive_garbage():
+    rng = random.Random(20261107)
+    seeds = [PREFIX_STATUS + "0-1g.10gb-used", PREFIX_STATUS + "12-7g.79gb-free", PREFIX_SPEC + "3-2g.20gb", PREFIX_STATUS + "1-10gb-used",
+             PREFIX_SPEC + "0-40gb", PREFIX_STATUS, PREFIX_SPEC, "", "-", "nos.nebuly.com/", PREFIX_STATUS + "-1-1g.5gb-used",
+             PREFIX_STATUS + "0--used", PREFIX_STATUS + "99999999999999999999-1g.5gb-free", PREFIX_SPEC + "0-" + "x" * 400]
+    values = ["1", "0", "-1", "", " 1", "1 ", "+3", "007", "2147483647", "2147483648", "99999999999999999999", "1e3", "0x10", "one", "١"]
+    n = 0
+    for seed in seeds:
+        for key in _mutations(rng, seed):
+            for value in values + [_rand(rng, rng.randrange(0, 12))]:
+                for parse in (host.parse_status_annotation, host.parse_spec_annotation):
+                    r = parse(key, value)
+                    n += 1
+                    if r is not None:  # accepted (strconv.Atoi takes signs, so negative numbers parse, annotation.go:43-50):
+                        # the numbers are what the text says and the profile fits the caller's buffer
+                        assert int(value) == r["quantity"] and -2**31 <= r["index"] < 2**31 and len(r["profile"]) < 256
+    assert n > 5000
+
+
+def test_small_output_buffers_are_respected():
+    L = host.lib()
+    idx, st, q = C.c_int32(), C.c_int32(), C.c_int32()
+    key = (PREFIX_STATUS + "0-" + "p" * 100 + "-used").encode()
+    for cap in (0, 1, 2, 8, 100, 101, 102):
+        buf = C.create_string_buffer(b"\xaa" * 128, 128)
+        rc = L.noshost_parse_status_annotation(key, b"1", C.byref(idx), buf, cap, C.byref(st), C.byref(q))
+        assert buf.raw[cap:] == b"\xaa" * (128 - cap), cap          # nothing written past the capacity given
+        if cap <= 100:
+            assert rc == 2 and buf.raw == b"\xaa" * 128, cap          # a name that does not fit is refused, not truncated
+        else:
+            assert rc == 0 and buf.raw[:cap].find(b"\0") == 100, cap  # the 100-byte name and its terminator
+    for cap in (0, 1, 5, 30):
+        buf = C.create_string_buffer(b"\xaa" * 128, 128)
+        L.noshost_format_status_annotation(7, b"1g.10gb", 1, buf, cap)
+        assert buf.raw[cap:] == b"\xaa" * (128 - cap), cap
+        buf = C.create_string_buffer(b"\xaa" * 128, 128)
+        L.noshost_format_spec_annotation(7, b"1g.10gb", buf, cap)
+        assert buf.raw[cap:] == b"\xaa" * (128 - cap), cap
+        buf = C.create_string_buffer(b"\xaa" * 128, 128)
+        rc = L.noshost_mig_profile_of_resource(b"nvidia.com/mig-1g.10gb", buf, cap)
+        assert buf.raw[cap:] == b"\xaa" * (128 - cap) and rc == (0 if cap > 7 else 2), cap
+        buf = C.create_string_buffer(b"\xaa" * 128, 128)
+        rc = L.noshost_mps_profile_of_resource(b"nvidia.com/gpu-10gb", buf, cap)
+        assert buf.raw[cap:] == b"\xaa" * (128 - cap) and rc == (0 if cap > 4 else 2), cap
+
+
+def test_format_parse_round_trip():
+    rng = random.Random(7)
+    for _ in range(500):
+        index = rng.randrange(0, 64)
+        profile = rng.choice(pkg.synth.MIG_PROFILES + ["5gb", "10gb", "40gb"])
+        status = rng.choice(["used", "free"])
+        q = rng.randrange(0, 50)
+        k = host.format_status_annotation(index, profile, status)
+        assert host.parse_status_annotation(k, str(q)) == dict(index=index, profile=profile, status=status, quantity=q)
+        k = host.format_spec_annotation(index, profile)
+        assert host.parse_spec_annotation(k, str(q)) == dict(index=index, profile=profile, quantity=q)
+
+
+def test_scalar_scanners_survive_garbage():
+    rng = random.Random(11)
+    seeds = ["nvidia.com/mig-1g.10gb", "nvidia.com/gpu-10gb", "nvidia.com/gpu", "nvidia.com/mig-", "nvidia.com/gpu-gb", "40960", "81920", "1gb",
+             "999999999999gb", "-5gb", "0gb", "", "gb"]
+    n = 0
+    for seed in seeds:
+        for s in _mutations(rng, seed):
+            r = host.mig_profile_of_resource(s)
+            assert r is None or (len(r) < 256 and s.endswith(r))
+            r = host.mps_profile_of_resource(s)
+            assert r is None or (len(r) < 256 and s.endswith(r))
+            assert -2**31 <= host.mps_profile_size_gb(s) < 2**31   # Atoi of what is between the prefix and "gb", else 0
+                                                                   # (slicing/profile.go:52-59; "-5gb" is -5 there too)
+            g = host.memory_gb(s)
+            assert g is None or g >= 0
+            n += 1
+    assert n > 200
+
+
+def test_snapshot_builder_survives_garbage_nodes():
+    rng = random.Random(3)
+    for kind in ("mig", "mps"):
+        nodes = []
+        for i in range(60):
+            ann = {}
+            for _ in range(rng.randrange(0, 8)):
+                seed = rng.choice([PREFIX_STATUS + "0-1g.10gb-used", PREFIX_STATUS + "1-10gb-free", PREFIX_SPEC + "0-2g.20gb", "other/annotation"])
+                ann[rng.choice(list(_mutations(rng, seed)))] = rng.choice(["1", "2", "x", "", "-3", "99999999999"])
+            labels = {}
+            if rng.random() < 0.8:
+                labels[host.LABEL_PRODUCT] = rng.choice(["NVIDIA-A100-80GB-PCIe", "NVIDIA-H100-80GB", "A30", _rand(rng, 6), ""])
+            if rng.random() < 0.8:
+                labels[host.LABEL_COUNT] = rng.choice(["8", "1", "0", "-2", "x", "16", "17", "4000000000", ""])
+            if rng.random() < 0.8:
+                labels[host.LABEL_MEMORY] = rng.choice(["81920", "40960", "0", "-1", "abc", "1e9", ""])
+            nodes.append(dict(name=f"n{i}", labels=labels, annotations=ann))
+        s = host.Snapshot(kind, nodes, model_names=["A30", "NVIDIA-A100-80GB-PCIe", "NVIDIA-H100-80GB"])
+        a = s.arrays()
+        assert a["n_nodes"] == len(nodes) and len(a["gpu_off"]) == len(nodes) + 1
+        assert (a["gpu_off"][1:] >= a["gpu_off"][:-1]).all() and a["gpu_off"][-1] == s.tg
+        # a status annotation whose value is "-3" gives a count of -3 here as it does in extractGPUs (mig/node.go:65-100 does
+        # not look at the sign); nosplan_set_*_snapshot is where such a count is refused (NOSPLAN_ERR_RANGE)
+        assert a["used"].min() >= -3 and a["free"].min() >= -3 and a["used"].max() <= 2 and a["free"].max() <= 2
+        s.close()
+
+
+def test_table_loader_survives_garbage():
+    rng = random.Random(5)
+    good = pkg.synth.table_yaml_text()
+    n_ok = 0
+    for text in list(_mutations(rng, good)) * 8 + ["", "\n", "- ", "-", "- models:", "- models: [", "- models: [ a ]\n  allowedGeometries:",
+                                                   "- models: [ a ]\n  allowedGeometries:\n    - : 1\n", "\t- models: [ a ]", "- models: [ a ]\n allowedGeometries:\n  - p: 99999999999999999999\n",
+                                                   "- models: [ " + "m, " * 500 + "z ]\n  allowedGeometries:\n    - p: 1\n", "x" * 5000, "- " * 3000]:
+        try:
+            entries, g = host.load_tables(text)
+        except ValueError as e:
+            assert str(e)  # an error always carries its reason
+            continue
+        n_ok += 1
+        assert len(g["geom_off"]) == len(g["models"]) + 1
+    assert n_ok >= 1

@@ -18,7 +18,13 @@ const char kStatusPrefix[] = "nos.nebuly.com/status-gpu";  // v1alpha1/annotatio
 const char kMigResourcePrefix[] = "nvidia.com/mig-";       // pkg/constant/constants.go:46
 const char kGpuResourcePrefix[] = "nvidia.com/gpu-";       // slicing/profile.go:30
 
+constexpr long long kMaxLabelGpuCount = 4096;  // nvidia.com/gpu.count above this marks the node invalid (see snapshot_build)
+
 bool has_prefix(const std::string& s, const char* p) { return s.rfind(p, 0) == 0; }
+
+// The C ABI carries indexes and quantities as int32.  strconv.Atoi accepts up to 64 bits; a number that does not fit
+// 32 bits is treated here as a parse failure (the annotation is ignored) instead of being truncated.
+bool fits_i32(long long v) { return v >= INT32_MIN && v <= INT32_MAX; }
 
 // strconv.Atoi: optional sign, decimal digits, nothing else; error on overflow
 bool go_atoi(const std::string& s, long long* out) {
@@ -98,6 +104,9 @@ int mps_size_of(const std::string& name) {  // slicing/profile.go:52-59
   return 0;
 }
 
+// a parsed name either fits the caller's buffer with its terminator or the call fails: never a truncated name
+bool fits_out(const std::string& s, const char* out, int cap) { return out && cap > 0 && (int)s.size() < cap; }
+
 int copy_out(const std::string& s, char* out, int cap) {
   if (out && cap > 0) std::snprintf(out, cap, "%s", s.c_str());
   return (int)s.size();
@@ -115,8 +124,8 @@ bool parse_status(const std::string& key, const std::string& value, StatusAnn* a
   auto parts = split(key, '-');
   if (parts.size() != 5) return false;
   long long q, idx;
-  if (!go_atoi(value, &q)) return false;
-  if (!go_atoi(parts[2], &idx)) return false;
+  if (!go_atoi(value, &q) || !fits_i32(q)) return false;
+  if (!go_atoi(parts[2], &idx) || !fits_i32(idx)) return false;
   std::string st = lower(parts[4]);  // pkg/resource/device.go:28-39
   int s;
   if (st == "free") s = NOSHOST_STATUS_FREE;
@@ -135,8 +144,8 @@ bool parse_spec(const std::string& key, const std::string& value, int* index, st
   auto parts = split(key, '-');
   if (parts.size() != 4) return false;
   long long q, idx;
-  if (!go_atoi(value, &q)) return false;
-  if (!go_atoi(parts[2], &idx)) return false;
+  if (!go_atoi(value, &q) || !fits_i32(q)) return false;
+  if (!go_atoi(parts[2], &idx) || !fits_i32(idx)) return false;
   *index = (int)idx;
   *profile = parts[3];
   *qty = (int)q;
@@ -168,6 +177,7 @@ int noshost_parse_status_annotation(const char* key, const char* value, int32_t*
                                     int32_t* status, int32_t* quantity) {
   StatusAnn a;
   if (!key || !value || !parse_status(key, value, &a)) return 1;
+  if (!fits_out(a.profile, profile, profile_cap)) return 2;
   *index = a.index;
   *status = a.status;
   *quantity = a.qty;
@@ -180,6 +190,7 @@ int noshost_parse_spec_annotation(const char* key, const char* value, int32_t* i
   int idx, q;
   std::string p;
   if (!key || !value || !parse_spec(key, value, &idx, &p, &q)) return 1;
+  if (!fits_out(p, profile, profile_cap)) return 2;
   *index = idx;
   *quantity = q;
   copy_out(p, profile, profile_cap);
@@ -198,21 +209,27 @@ int noshost_format_spec_annotation(int32_t index, const char* profile, char* out
 int noshost_memory_gb(const char* label, int32_t* out) {
   long long mb;
   if (!label || !go_atoi(label, &mb)) return 1;
-  *out = (int32_t)std::ceil((double)mb / 1000.0);  // the path's only floating-point operation
+  const double gb = std::ceil((double)mb / 1000.0);  // the path's only floating-point operation
+  if (gb < (double)INT32_MIN || gb > (double)INT32_MAX) return 1;  // does not fit the ABI's int32
+  *out = (int32_t)gb;
   return 0;
 }
 
 int noshost_mig_profile_of_resource(const char* resource, char* profile, int cap) {
   std::string r = resource ? resource : "";
   if (!matches_mig_resource(r)) return 1;
-  copy_out(has_prefix(r, kMigResourcePrefix) ? r.substr(sizeof(kMigResourcePrefix) - 1) : r, profile, cap);
+  const std::string name = has_prefix(r, kMigResourcePrefix) ? r.substr(sizeof(kMigResourcePrefix) - 1) : r;
+  if (!fits_out(name, profile, cap)) return 2;
+  copy_out(name, profile, cap);
   return 0;
 }
 
 int noshost_mps_profile_of_resource(const char* resource, char* profile, int cap) {
   std::string r = resource ? resource : "";
   if (!matches_mps_resource(r)) return 1;
-  copy_out(has_prefix(r, kGpuResourcePrefix) ? r.substr(sizeof(kGpuResourcePrefix) - 1) : r, profile, cap);
+  const std::string name = has_prefix(r, kGpuResourcePrefix) ? r.substr(sizeof(kGpuResourcePrefix) - 1) : r;
+  if (!fits_out(name, profile, cap)) return 2;
+  copy_out(name, profile, cap);
   return 0;
 }
 
@@ -245,6 +262,9 @@ noshost_snapshot* noshost_snapshot_build(int kind, int n_nodes, const char* cons
     if (!product[n] || !count[n]) continue;
     long long cnt;
     if (!go_atoi(count[n], &cnt)) continue;
+    // the loop below materialises every "missing" GPU up to the label's count: a label no machine can carry is refused
+    // (the node stays invalid) rather than allowed to allocate without bound
+    if (cnt > kMaxLabelGpuCount) continue;
     int32_t mem = 0;
     if (kind == NOSHOST_KIND_MPS && (!memory[n] || noshost_memory_gb(memory[n], &mem))) continue;
     // ParseNodeAnnotations (annotation.go:87-101): spec first, then status; the rest ignored
