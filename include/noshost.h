@@ -85,7 +85,10 @@ typedef struct noshost_pods noshost_pods;
 /* Per pod: pending/scheduled/unschedulable flags, priority (0 when unset), creation time, "ns/name".
  * Containers of pod i: [cont_off[i], cont_off[i+1]); cont_init[c] != 0 marks an init container; the
  * resource requests of container c: res_name/res_qty [res_off[c], res_off[c+1]).
- * vocab: the snapshot(s) the demand keys must index (either may be NULL). */
+ * vocab: the snapshot(s) the demand keys must index (either may be NULL).
+ * The arrays are checked before they are used (offsets ascending from >= 0, no null resource name; a pod without a
+ * name sorts as ""); request quantities are summed with saturation and must fit int32 in the end.  A refusal leaves
+ * count 0 and its reason in noshost_pods_error. */
 noshost_pods* noshost_pods_build(int n_pods, const uint8_t* pending, const uint8_t* scheduled, const uint8_t* unschedulable,
                                  const int32_t* priority, const int64_t* created, const char* const* name,
                                  const int32_t* cont_off, const uint8_t* cont_init, const int32_t* res_off,

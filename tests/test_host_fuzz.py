@@ -154,3 +154,70 @@ def test_table_loader_survives_garbage():
         n_ok += 1
         assert len(g["geom_off"]) == len(g["models"]) + 1
     assert n_ok >= 1
+
+
+def _vocab():
+    nodes = [dict(name="n0", labels={host.LABEL_PRODUCT: "NVIDIA-H100-80GB", host.LABEL_COUNT: "2", host.LABEL_MEMORY: "81920"},
+                  annotations={PREFIX_STATUS + "0-1g.10gb-free": "2", PREFIX_STATUS + "1-10gb-free": "1"})]
+    mig = host.Snapshot("mig", nodes, model_names=["NVIDIA-H100-80GB"], extra_names=pkg.synth.MIG_PROFILES)
+    mps = host.Snapshot("mps", nodes, extra_sizes=[5, 10, 20, 40])
+    return mig, mps
+
+
+def test_pod_rows_survive_garbage_specs():
+    rng = random.Random(13)
+    mig, mps = _vocab()
+    names = ["nvidia.com/mig-1g.10gb", "nvidia.com/mig-2g.20gb", "nvidia.com/gpu-10gb", "nvidia.com/gpu-40gb", "cpu", "memory", "nvidia.com/gpu",
+             "nvidia.com/mig-9g.99gb", "nvidia.com/gpu-7gb", "nvidia.com/mig-", ""]
+    qtys = [0, 1, 2, 7, -1, 2**31 - 1, 2**31, 2**62, 2**63 - 1, -2**63]
+    accepted = refused = 0
+    for _ in range(400):
+        pods = []
+        for i in range(rng.randrange(0, 6)):
+            mk = lambda: {rng.choice(list(_mutations(rng, rng.choice(names)))) if rng.random() < 0.2 else rng.choice(names): rng.choice(qtys)
+                          for _ in range(rng.randrange(0, 4))}
+            pods.append(dict(name=rng.choice(["ns/a", "ns/b", "", "x" * 300]), priority=rng.choice([0, 5, -5, 2**31 - 1]),
+                             created=rng.choice([0, 1, -1, 2**62]), phase=rng.choice(["Pending", "Running"]),
+                             node_name=rng.choice(["", "n0"]), unschedulable=rng.random() < 0.8,
+                             containers=[mk() for _ in range(rng.randrange(0, 3))], init_containers=[mk() for _ in range(rng.randrange(0, 2))]))
+        try:
+            r = host.build_pods(pods, mig, mps)
+        except ValueError as e:
+            assert str(e)
+            refused += 1
+            continue
+        accepted += 1
+        n = len(r["source"])
+        assert len(r["off"]) == n + 1 and (r["off"][1:] >= r["off"][:-1]).all()
+        assert ((r["source"] >= 0) & (r["source"] < max(len(pods), 1))).all()
+    assert accepted > 50 and refused > 50
+    mig.close()
+    mps.close()
+
+
+def test_pod_builder_refuses_broken_csr_arrays():
+    L = host.lib()
+    mig, mps = _vocab()
+    u8 = lambda *v: (C.c_uint8 * len(v))(*v)
+    i32 = lambda *v: (C.c_int32 * len(v))(*v)
+    i64 = lambda *v: (C.c_int64 * len(v))(*v)
+    strs = lambda *v: (C.c_char_p * len(v))(*v)
+    good = dict(n=1, pending=u8(1), sched=u8(0), unsched=u8(1), prio=i32(0), created=i64(0), name=strs(b"ns/p"), cont_off=i32(0, 1),
+                cont_init=u8(0), res_off=i32(0, 1), res_name=strs(b"nvidia.com/mig-1g.10gb"), res_qty=i64(1))
+
+    def call(**kw):
+        a = dict(good, **kw)
+        h = C.c_void_p(L.noshost_pods_build(a["n"], a["pending"], a["sched"], a["unsched"], a["prio"], a["created"], a["name"], a["cont_off"],
+                                            a["cont_init"], a["res_off"], a["res_name"], a["res_qty"], mig.h, mps.h))
+        err, n = L.noshost_pods_error(h).decode(), L.noshost_pods_count(h)
+        L.noshost_pods_free(h)
+        return err, n
+    assert call() == ("", 1)
+    for kw in (dict(n=-1), dict(cont_off=i32(1, 0)), dict(cont_off=i32(-1, 1)), dict(res_off=i32(1, 0)), dict(res_off=i32(-4, 1)),
+               dict(res_name=strs(None)), dict(name=None), dict(cont_off=None), dict(res_off=None), dict(res_qty=None)):
+        err, n = call(**kw)
+        assert err and n == 0, kw
+    assert call(name=strs(None)) == ("", 1)          # a pod without a name sorts as ""
+    assert call(res_qty=i64(2**40))[0]               # does not fit the planner's int32
+    mig.close()
+    mps.close()

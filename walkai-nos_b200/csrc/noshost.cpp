@@ -389,6 +389,39 @@ noshost_pods* noshost_pods_build(int n_pods, const uint8_t* pending, const uint8
     int kind;
     std::vector<std::pair<int, int>> kv;  // (key id, qty), ascending key
   };
+  // the CSR arrays come from the caller: walk them once before anything is indexed through them
+  auto bad_input = [&](const std::string& why) {
+    out->err = why;
+    out->key.push_back(0);
+    out->qty.push_back(0);
+    return out;
+  };
+  if (n_pods < 0) return bad_input("negative pod count");
+  if (n_pods > 0 && (!pending || !scheduled || !unschedulable || !priority || !created || !name || !cont_off))
+    return bad_input("null pod arrays");
+  if (n_pods > 0) {
+    if (cont_off[0] < 0) return bad_input("cont_off[0] is negative");
+    for (int i = 0; i < n_pods; ++i)
+      if (cont_off[i + 1] < cont_off[i]) return bad_input("cont_off not ascending at pod " + std::to_string(i));
+    const int n_cont = cont_off[n_pods];
+    if (n_cont > 0 && (!cont_init || !res_off)) return bad_input("null container arrays");
+    if (n_cont > 0) {
+      if (res_off[0] < 0) return bad_input("res_off[0] is negative");
+      for (int c = 0; c < n_cont; ++c)
+        if (res_off[c + 1] < res_off[c]) return bad_input("res_off not ascending at container " + std::to_string(c));
+      const int n_res = res_off[n_cont];
+      if (n_res > 0 && (!res_name || !res_qty)) return bad_input("null resource arrays");
+      for (int r = 0; r < n_res; ++r)
+        if (!res_name[r]) return bad_input("resource " + std::to_string(r) + " has no name");
+    }
+  }
+  auto name_of = [&](int i) { return name[i] ? name[i] : ""; };
+  // quantities are int64 on the wire (resource.Quantity.Value() saturates there too); sums saturate instead of wrapping
+  auto sat_add = [](long long a, long long b) {
+    long long r;
+    if (__builtin_add_overflow(a, b, &r)) return b > 0 ? (long long)INT64_MAX : (long long)INT64_MIN;
+    return r;
+  };
   std::vector<int> order;
   for (int i = 0; i < n_pods; ++i)
     if (pending[i] && !scheduled[i] && unschedulable[i]) order.push_back(i);  // shouldConsiderPod
@@ -396,7 +429,7 @@ noshost_pods* noshost_pods_build(int n_pods, const uint8_t* pending, const uint8
   std::stable_sort(order.begin(), order.end(), [&](int a, int b) {
     if (priority[a] != priority[b]) return priority[a] > priority[b];
     if (created[a] != created[b]) return created[a] < created[b];
-    return std::strcmp(name[a], name[b]) < 0;
+    return std::strcmp(name_of(a), name_of(b)) < 0;
   });
   for (int i : order) {
     // ComputePodRequest: sum over containers, element-wise max with the init containers
@@ -408,7 +441,7 @@ noshost_pods* noshost_pods_build(int n_pods, const uint8_t* pending, const uint8
           if (it == initmax.end()) initmax[res_name[r]] = res_qty[r];  // quota.Max: a key on one side only keeps its value
           else it->second = std::max<long long>(it->second, res_qty[r]);
         } else {
-          sum[res_name[r]] += res_qty[r];
+          sum[res_name[r]] = sat_add(sum[res_name[r]], res_qty[r]);
         }
       }
     std::map<std::string, long long> total = sum;
@@ -428,7 +461,7 @@ noshost_pods* noshost_pods_build(int n_pods, const uint8_t* pending, const uint8
           bad = true;
           break;
         }
-        mreq[mig->name_id.at(p)] += e.second;
+        mreq[mig->name_id.at(p)] = sat_add(mreq[mig->name_id.at(p)], e.second);
       } else if (matches_mps_resource(e.first)) {
         std::string p = has_prefix(e.first, kGpuResourcePrefix) ? e.first.substr(sizeof(kGpuResourcePrefix) - 1) : e.first;
         int sz = mps_size_of(p);
@@ -437,9 +470,15 @@ noshost_pods* noshost_pods_build(int n_pods, const uint8_t* pending, const uint8
           bad = true;
           break;
         }
-        preq[mps->size_id.at(sz)] += e.second;
+        preq[mps->size_id.at(sz)] = sat_add(preq[mps->size_id.at(sz)], e.second);
       }
     }
+    for (auto* rq : {&mreq, &preq})
+      for (auto& e : *rq)
+        if (!bad && !fits_i32(e.second)) {  // int(quantity.Value()) is 64 bits in Go; the planner ABI carries int32
+          out->err = std::string("pod ") + name_of(i) + ": a requested quantity does not fit 32 bits";
+          bad = true;
+        }
     if (bad) break;
     for (int kd = 0; kd < 2; ++kd) {
       auto& rq = kd ? preq : mreq;
