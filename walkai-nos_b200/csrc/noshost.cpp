@@ -492,6 +492,13 @@ noshost_pods* noshost_pods_build(int n_pods, const uint8_t* pending, const uint8
       out->off.push_back((int32_t)out->key.size());
     }
   }
+  if (!out->err.empty()) {  // a refusal returns no rows at all, not the ones built before the offending pod
+    out->source.clear();
+    out->kind.clear();
+    out->key.clear();
+    out->qty.clear();
+    out->off.assign(1, 0);
+  }
   if (out->key.empty()) {
     out->key.push_back(0);
     out->qty.push_back(0);
