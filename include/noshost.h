@@ -55,7 +55,11 @@ typedef struct noshost_snapshot noshost_snapshot;
  * are profile names that must be in the vocabulary besides those found in annotations (table and pod
  * profiles).  MPS: extra_sizes are slice sizes requested by pods.  A node for which the reference's
  * NewNode returns an error is kept with valid = 0 and no GPUs.  GPUs of a node: annotated GPUs by
- * ascending index, then the "missing" ones with index len..count-1 (node.go:89-96, quirk kept). */
+ * ascending index, then the "missing" ones with index len..count-1 (node.go:89-96, quirk kept); a gpu.count label above
+ * 4096 leaves the node invalid instead of materialising that many GPUs.
+ * Returns NULL when the arguments cannot be used (unknown kind, negative count, a required array missing, ann_off not
+ * ascending from >= 0) or memory runs out; a NULL key, value, model or extra name is skipped.  Every accessor below
+ * answers a NULL handle or an index outside the snapshot with 0 / "" / NULL. */
 noshost_snapshot* noshost_snapshot_build(int kind, int n_nodes, const char* const* product, const char* const* count,
                                          const char* const* memory, const int32_t* ann_off, const char* const* ann_key,
                                          const char* const* ann_val, int n_models, const char* const* model_names,
@@ -106,7 +110,8 @@ const char* noshost_pods_error(const noshost_pods* p);     /* "" or why a reques
 /* ---- plan output: BuildNodePartitioning (internal/partitioning/mig/state.go:25-45) + getGPUSpecAnnotationList
  * (internal/partitioning/mig/partitioner.go:74-91): spec annotations of node n from the planned state.
  * Writes "key=value\n" lines ("nos.nebuly.com/spec-gpu-<idx>-<profile>=<qty>", quantity > 0 only, GPUs in
- * snapshot order, profiles ascending) into out; returns the length needed (call again if > cap). */
+ * snapshot order, profiles ascending) into out; returns the length needed (call again if > cap), or -1 for a NULL
+ * argument or a node index outside the snapshot. */
 int noshost_spec_annotations(const noshost_snapshot* s, int node, const int32_t* used, const int32_t* free_, char* out,
                              int cap);
 /* state.NodePartitioning.Equal (internal/partitioning/state/partitioning.go:33-38): same multiset of
@@ -123,7 +128,8 @@ int noshost_node_partitioning_equal(int n_keys, int n_a, const int32_t* idx_a, c
  * the reference's Unmarshal returns an error.  The entry accessors give the list as parsed; the flat accessors give
  * GroupByModel in the layout of nosplan_set_mig_tables: models in order of first appearance, profile vocabulary
  * ascending bytewise, geom_off[n_models + 1], geom_counts[total][n_profiles].  Names and quantities are not
- * validated here (the reference validates in SetKnownGeometries; nosplan_set_mig_tables does). */
+ * validated here (the reference validates in SetKnownGeometries; nosplan_set_mig_tables does).  The reason is cut to
+ * err_cap bytes including its terminator; accessors answer a NULL handle or an index outside the table with 0 / "" / NULL. */
 typedef struct noshost_tables noshost_tables;
 noshost_tables* noshost_tables_load(const char* text, char* err, int err_cap);
 void noshost_tables_free(noshost_tables* t);

@@ -221,3 +221,64 @@ def test_pod_builder_refuses_broken_csr_arrays():
     assert call(res_qty=i64(2**40))[0]               # does not fit the planner's int32
     mig.close()
     mps.close()
+
+
+def test_snapshot_builder_refuses_broken_arguments():
+    L = host.lib()
+    strs = lambda *v: (C.c_char_p * max(len(v), 1))(*v)
+    i32 = lambda *v: (C.c_int32 * max(len(v), 1))(*v)
+    good = dict(kind=0, n=1, product=strs(b"A30"), count=strs(b"1"), memory=strs(b"24576"), ann_off=i32(0, 1),
+                ann_key=strs((PREFIX_STATUS + "0-1g.6gb-free").encode()), ann_val=strs(b"4"), n_models=1, models=strs(b"A30"),
+                n_names=0, names=None, n_sizes=0, sizes=None)
+
+    def call(**kw):
+        a = dict(good, **kw)
+        h = L.noshost_snapshot_build(a["kind"], a["n"], a["product"], a["count"], a["memory"], a["ann_off"], a["ann_key"], a["ann_val"],
+                                     a["n_models"], a["models"], a["n_names"], a["names"], a["n_sizes"], a["sizes"])
+        h = C.c_void_p(h)
+        out = (bool(h.value), L.noshost_snapshot_n_nodes(h), L.noshost_snapshot_total_gpus(h))
+        if h.value:
+            L.noshost_snapshot_free(h)
+        return out
+    assert call() == (True, 1, 1)
+    for kw in (dict(kind=2), dict(n=-1), dict(product=None), dict(count=None), dict(ann_off=None), dict(ann_off=i32(1, 0)), dict(ann_off=i32(-1, 0)),
+               dict(ann_key=None), dict(ann_val=None), dict(n_models=-1), dict(n_models=1, models=None), dict(n_names=2, names=None),
+               dict(n_sizes=1, sizes=None), dict(kind=1, memory=None)):
+        assert call(**kw) == (False, 0, 0), kw           # a null handle answers like an empty snapshot
+    assert call(ann_key=strs(None)) == (True, 1, 1)      # a null key is not an annotation: the GPU comes from the count label
+    assert call(models=strs(None)) == (True, 1, 0)       # no model table entry: the node is invalid (NewGPU: unknown model)
+    # the accessors of a null handle and out-of-range indexes
+    assert L.noshost_snapshot_key_name(None, 0) == b"" and L.noshost_snapshot_key_size(None, 3) == 0
+    s = host.Snapshot("mig", [dict(labels={host.LABEL_PRODUCT: "A30", host.LABEL_COUNT: "1"}, annotations={})], model_names=["A30"],
+                      extra_names=["1g.6gb"])
+    assert L.noshost_snapshot_key_name(s.h, 99) == b"" and L.noshost_snapshot_key_name(s.h, -1) == b""
+    z = i32(0)
+    assert L.noshost_spec_annotations(s.h, 5, z, z, None, 0) == -1 and L.noshost_spec_annotations(s.h, -1, z, z, None, 0) == -1
+    assert L.noshost_spec_annotations(None, 0, z, z, None, 0) == -1 and L.noshost_spec_annotations(s.h, 0, None, z, None, 0) == -1
+    s.close()
+    # NodePartitioning.Equal with empty and null sides
+    assert L.noshost_node_partitioning_equal(3, 0, None, None, 0, None, None) == 1
+    assert L.noshost_node_partitioning_equal(3, 1, None, None, 1, None, None) == 0
+    assert L.noshost_node_partitioning_equal(-1, 1, z, z, 1, z, z) == 0
+
+
+def test_table_accessors_are_bounds_checked():
+    L = host.lib()
+    err = C.create_string_buffer(64)
+    L.noshost_tables_load.restype = C.c_void_p
+    t = C.c_void_p(L.noshost_tables_load(pkg.synth.table_yaml_text().encode(), err, 64))
+    assert t.value and L.noshost_tables_n_entries(t) == 3
+    L.noshost_tables_entry_model.restype = L.noshost_tables_entry_geometry_profile.restype = C.c_char_p
+    L.noshost_tables_model.restype = L.noshost_tables_profile.restype = C.c_char_p
+    L.noshost_tables_entry_geometry_quantity.restype = C.c_int64
+    for e, g, k in ((-1, 0, 0), (3, 0, 0), (0, -1, 0), (0, 99, 0), (0, 0, -1), (0, 0, 99)):
+        assert L.noshost_tables_entry_geometry_profile(t, e, g, k) == b"" and L.noshost_tables_entry_geometry_quantity(t, e, g, k) == 0
+    assert L.noshost_tables_entry_n_models(t, 7) == 0 and L.noshost_tables_entry_model(t, 0, 9) == b"" and L.noshost_tables_entry_n_geometries(t, -2) == 0
+    assert L.noshost_tables_entry_geometry_size(t, 0, 50) == 0 and L.noshost_tables_model(t, 100) == b"" and L.noshost_tables_profile(t, -1) == b""
+    assert L.noshost_tables_entry_geometry_profile(t, 0, 0, 0) == b"1g.6gb" and L.noshost_tables_entry_geometry_quantity(t, 0, 0, 0) == 4
+    L.noshost_tables_free(t)
+    assert L.noshost_tables_n_entries(None) == 0 and L.noshost_tables_n_models(None) == 0 and L.noshost_tables_model(None, 0) == b""
+    # an error text longer than the caller's buffer is cut, not overrun
+    small = C.create_string_buffer(b"\xaa" * 32, 32)
+    assert not L.noshost_tables_load(b"- models: 3\n", small, 8)
+    assert small.raw[8:] == b"\xaa" * 24 and small.raw[:8].find(b"\0") >= 0

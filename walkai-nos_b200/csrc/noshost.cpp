@@ -239,7 +239,18 @@ noshost_snapshot* noshost_snapshot_build(int kind, int n_nodes, const char* cons
                                          const char* const* memory, const int32_t* ann_off, const char* const* ann_key,
                                          const char* const* ann_val, int n_models, const char* const* model_names,
                                          int n_extra_names, const char* const* extra_names, int n_extra_sizes,
-                                         const int32_t* extra_sizes) {
+                                         const int32_t* extra_sizes) try {
+  // arguments first: nothing below indexes through an array that was not looked at here
+  if ((kind != NOSHOST_KIND_MIG && kind != NOSHOST_KIND_MPS) || n_nodes < 0 || n_models < 0 || n_extra_names < 0 || n_extra_sizes < 0)
+    return nullptr;
+  if (n_nodes > 0 && (!product || !count || !ann_off || (kind == NOSHOST_KIND_MPS && !memory))) return nullptr;
+  if ((n_models > 0 && !model_names) || (n_extra_names > 0 && !extra_names) || (n_extra_sizes > 0 && !extra_sizes)) return nullptr;
+  if (n_nodes > 0) {
+    if (ann_off[0] < 0) return nullptr;
+    for (int n = 0; n < n_nodes; ++n)
+      if (ann_off[n + 1] < ann_off[n]) return nullptr;
+    if (ann_off[n_nodes] > 0 && (!ann_key || !ann_val)) return nullptr;
+  }
   struct Gpu {
     int index;
     std::map<std::string, int> used, free_;
@@ -250,11 +261,13 @@ noshost_snapshot* noshost_snapshot_build(int kind, int n_nodes, const char* cons
     std::vector<Gpu> gpus;
   };
   std::map<std::string, int> model_id;
-  for (int m = 0; m < n_models; ++m) model_id[model_names[m]] = m;
+  for (int m = 0; m < n_models; ++m)
+    if (model_names[m]) model_id[model_names[m]] = m;
   std::vector<Node> nodes(n_nodes);
   std::set<std::string> names;
   std::set<int> sizes;
-  for (int i = 0; i < n_extra_names; ++i) names.insert(extra_names[i]);
+  for (int i = 0; i < n_extra_names; ++i)
+    if (extra_names[i]) names.insert(extra_names[i]);
   for (int i = 0; i < n_extra_sizes; ++i) sizes.insert(extra_sizes[i]);
   for (int n = 0; n < n_nodes; ++n) {
     Node& nd = nodes[n];
@@ -270,6 +283,7 @@ noshost_snapshot* noshost_snapshot_build(int kind, int n_nodes, const char* cons
     // ParseNodeAnnotations (annotation.go:87-101): spec first, then status; the rest ignored
     std::map<int, Gpu> by_index;  // GroupByGpuIndex; canonical order = ascending index
     for (int a = ann_off[n]; a < ann_off[n + 1]; ++a) {
+      if (!ann_key[a] || !ann_val[a]) continue;  // not an annotation
       int idx, q;
       std::string p;
       if (parse_spec(ann_key[a], ann_val[a], &idx, &p, &q)) continue;
@@ -360,23 +374,27 @@ noshost_snapshot* noshost_snapshot_build(int kind, int n_nodes, const char* cons
     s->gpu_off.push_back((int32_t)s->model.size());
   }
   return s;
+} catch (...) {  // out of memory while building: no C++ exception crosses the C boundary
+  return nullptr;
 }
 
 void noshost_snapshot_free(noshost_snapshot* s) { delete s; }
-int noshost_snapshot_n_nodes(const noshost_snapshot* s) { return (int)s->valid.size(); }
-int noshost_snapshot_total_gpus(const noshost_snapshot* s) { return (int)s->model.size(); }
-int noshost_snapshot_n_keys(const noshost_snapshot* s) { return (int)s->key_names.size(); }
-const char* noshost_snapshot_key_name(const noshost_snapshot* s, int k) { return s->key_names[k].c_str(); }
-int noshost_snapshot_key_size(const noshost_snapshot* s, int k) { return s->key_sizes[k]; }
-const int32_t* noshost_snapshot_gpu_off(const noshost_snapshot* s) { return s->gpu_off.data(); }
-const uint8_t* noshost_snapshot_valid(const noshost_snapshot* s) { return s->valid.data(); }
-const int32_t* noshost_snapshot_model(const noshost_snapshot* s) { return s->model.data(); }
-const int32_t* noshost_snapshot_mem_gb(const noshost_snapshot* s) { return s->mem.data(); }
-const int32_t* noshost_snapshot_gpu_index(const noshost_snapshot* s) { return s->gpu_index.data(); }
-const int32_t* noshost_snapshot_used(const noshost_snapshot* s) { return s->used.data(); }
-const int32_t* noshost_snapshot_free_(const noshost_snapshot* s) { return s->free_.data(); }
-const uint32_t* noshost_snapshot_used_mask(const noshost_snapshot* s) { return s->used_mask.data(); }
-const uint32_t* noshost_snapshot_free_mask(const noshost_snapshot* s) { return s->free_mask.data(); }
+int noshost_snapshot_n_nodes(const noshost_snapshot* s) { return s ? (int)s->valid.size() : 0; }
+int noshost_snapshot_total_gpus(const noshost_snapshot* s) { return s ? (int)s->model.size() : 0; }
+int noshost_snapshot_n_keys(const noshost_snapshot* s) { return s ? (int)s->key_names.size() : 0; }
+const char* noshost_snapshot_key_name(const noshost_snapshot* s, int k) {
+  return s && k >= 0 && k < (int)s->key_names.size() ? s->key_names[k].c_str() : "";
+}
+int noshost_snapshot_key_size(const noshost_snapshot* s, int k) { return s && k >= 0 && k < (int)s->key_sizes.size() ? s->key_sizes[k] : 0; }
+const int32_t* noshost_snapshot_gpu_off(const noshost_snapshot* s) { return s ? s->gpu_off.data() : nullptr; }
+const uint8_t* noshost_snapshot_valid(const noshost_snapshot* s) { return s ? s->valid.data() : nullptr; }
+const int32_t* noshost_snapshot_model(const noshost_snapshot* s) { return s ? s->model.data() : nullptr; }
+const int32_t* noshost_snapshot_mem_gb(const noshost_snapshot* s) { return s ? s->mem.data() : nullptr; }
+const int32_t* noshost_snapshot_gpu_index(const noshost_snapshot* s) { return s ? s->gpu_index.data() : nullptr; }
+const int32_t* noshost_snapshot_used(const noshost_snapshot* s) { return s ? s->used.data() : nullptr; }
+const int32_t* noshost_snapshot_free_(const noshost_snapshot* s) { return s ? s->free_.data() : nullptr; }
+const uint32_t* noshost_snapshot_used_mask(const noshost_snapshot* s) { return s ? s->used_mask.data() : nullptr; }
+const uint32_t* noshost_snapshot_free_mask(const noshost_snapshot* s) { return s ? s->free_mask.data() : nullptr; }
 
 noshost_pods* noshost_pods_build(int n_pods, const uint8_t* pending, const uint8_t* scheduled, const uint8_t* unschedulable,
                                  const int32_t* priority, const int64_t* created, const char* const* name,
@@ -517,11 +535,12 @@ const char* noshost_pods_error(const noshost_pods* p) { return p->err.c_str(); }
 
 int noshost_spec_annotations(const noshost_snapshot* s, int node, const int32_t* used, const int32_t* free_, char* out,
                              int cap) {
+  if (!s || !used || !free_ || node < 0 || node >= (int)s->valid.size()) return -1;
   const int K = (int)s->key_names.size();
   std::string txt;
   for (int g = s->gpu_off[node]; g < s->gpu_off[node + 1]; ++g)
     for (int k = 0; k < K; ++k) {
-      const int q = used[(size_t)g * K + k] + free_[(size_t)g * K + k];  // GetGeometry
+      const long long q = (long long)used[(size_t)g * K + k] + free_[(size_t)g * K + k];  // GetGeometry
       if (q <= 0) continue;                                             // state.go:33-35
       txt += std::string(kSpecPrefix) + "-" + std::to_string(s->gpu_index[g]) + "-" + s->key_names[k] + "=" +
              std::to_string(q) + "\n";
@@ -533,6 +552,8 @@ int noshost_spec_annotations(const noshost_snapshot* s, int node, const int32_t*
 int noshost_node_partitioning_equal(int n_keys, int n_a, const int32_t* idx_a, const int32_t* res_a, int n_b,
                                     const int32_t* idx_b, const int32_t* res_b) {
   if (n_a != n_b) return 0;  // partitioning.go:34-36
+  if (n_a <= 0) return 1;    // two empty lists
+  if (n_keys < 0 || !idx_a || !idx_b || (n_keys > 0 && (!res_a || !res_b))) return 0;
   auto rows = [&](int n, const int32_t* idx, const int32_t* res) {
     std::vector<std::vector<int32_t>> v;
     for (int i = 0; i < n; ++i) {

@@ -345,18 +345,48 @@ noshost_tables* noshost_tables_load(const char* text, char* err, int err_cap) {
 }
 
 void noshost_tables_free(noshost_tables* t) { delete t; }
-int noshost_tables_n_entries(const noshost_tables* t) { return (int)t->entries.size(); }
-int noshost_tables_entry_n_models(const noshost_tables* t, int e) { return (int)t->entries[e].models.size(); }
-const char* noshost_tables_entry_model(const noshost_tables* t, int e, int i) { return t->entries[e].models[i].c_str(); }
-int noshost_tables_entry_n_geometries(const noshost_tables* t, int e) { return (int)t->entries[e].geoms.size(); }
-int noshost_tables_entry_geometry_size(const noshost_tables* t, int e, int g) { return (int)t->entries[e].geoms[g].size(); }
-const char* noshost_tables_entry_geometry_profile(const noshost_tables* t, int e, int g, int k) { return t->entries[e].geoms[g][k].first.c_str(); }
-int64_t noshost_tables_entry_geometry_quantity(const noshost_tables* t, int e, int g, int k) { return t->entries[e].geoms[g][k].second; }
-int noshost_tables_n_models(const noshost_tables* t) { return (int)t->models.size(); }
-const char* noshost_tables_model(const noshost_tables* t, int m) { return t->models[m].c_str(); }
-int noshost_tables_n_profiles(const noshost_tables* t) { return (int)t->profiles.size(); }
-const char* noshost_tables_profile(const noshost_tables* t, int p) { return t->profiles[p].c_str(); }
-const int32_t* noshost_tables_geom_off(const noshost_tables* t) { return t->geom_off.data(); }
-const int32_t* noshost_tables_geom_counts(const noshost_tables* t) { return t->geom_counts.data(); }
+
+// Accessors: a null handle or an index outside the table answers 0 / "" / NULL, never reads outside a vector.
+namespace {
+const Entry* entry_of(const noshost_tables* t, int e) { return t && e >= 0 && e < (int)t->entries.size() ? &t->entries[e] : nullptr; }
+const std::pair<std::string, long long>* cell_of(const noshost_tables* t, int e, int g, int k) {
+  const Entry* en = entry_of(t, e);
+  if (!en || g < 0 || g >= (int)en->geoms.size() || k < 0 || k >= (int)en->geoms[g].size()) return nullptr;
+  return &en->geoms[g][k];
+}
+}  // namespace
+int noshost_tables_n_entries(const noshost_tables* t) { return t ? (int)t->entries.size() : 0; }
+int noshost_tables_entry_n_models(const noshost_tables* t, int e) {
+  const Entry* en = entry_of(t, e);
+  return en ? (int)en->models.size() : 0;
+}
+const char* noshost_tables_entry_model(const noshost_tables* t, int e, int i) {
+  const Entry* en = entry_of(t, e);
+  return en && i >= 0 && i < (int)en->models.size() ? en->models[i].c_str() : "";
+}
+int noshost_tables_entry_n_geometries(const noshost_tables* t, int e) {
+  const Entry* en = entry_of(t, e);
+  return en ? (int)en->geoms.size() : 0;
+}
+int noshost_tables_entry_geometry_size(const noshost_tables* t, int e, int g) {
+  const Entry* en = entry_of(t, e);
+  return en && g >= 0 && g < (int)en->geoms.size() ? (int)en->geoms[g].size() : 0;
+}
+const char* noshost_tables_entry_geometry_profile(const noshost_tables* t, int e, int g, int k) {
+  const auto* c = cell_of(t, e, g, k);
+  return c ? c->first.c_str() : "";
+}
+int64_t noshost_tables_entry_geometry_quantity(const noshost_tables* t, int e, int g, int k) {
+  const auto* c = cell_of(t, e, g, k);
+  return c ? c->second : 0;
+}
+int noshost_tables_n_models(const noshost_tables* t) { return t ? (int)t->models.size() : 0; }
+const char* noshost_tables_model(const noshost_tables* t, int m) { return t && m >= 0 && m < (int)t->models.size() ? t->models[m].c_str() : ""; }
+int noshost_tables_n_profiles(const noshost_tables* t) { return t ? (int)t->profiles.size() : 0; }
+const char* noshost_tables_profile(const noshost_tables* t, int p) {
+  return t && p >= 0 && p < (int)t->profiles.size() ? t->profiles[p].c_str() : "";
+}
+const int32_t* noshost_tables_geom_off(const noshost_tables* t) { return t ? t->geom_off.data() : nullptr; }
+const int32_t* noshost_tables_geom_counts(const noshost_tables* t) { return t ? t->geom_counts.data() : nullptr; }
 
 }  // extern "C"

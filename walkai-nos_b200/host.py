@@ -148,6 +148,8 @@ class Snapshot:
             0 if kind == "mig" else 1, len(nodes), _strs(product), _strs(count), _strs(memory),
             off.ctypes.data_as(C.POINTER(C.c_int32)), _strs(keys), _strs(vals), len(models), _strs(models), len(en), _strs(en),
             len(list(extra_sizes)), es.ctypes.data_as(C.POINTER(C.c_int32))))
+        if not self.h.value:
+            raise ValueError("noshost_snapshot_build refused its arguments")
         self.n_nodes = L.noshost_snapshot_n_nodes(self.h)
         self.tg = L.noshost_snapshot_total_gpus(self.h)
         self.K = L.noshost_snapshot_n_keys(self.h)
