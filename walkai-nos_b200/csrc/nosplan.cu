@@ -114,8 +114,17 @@ struct nosplan {
   cudaEvent_t status_ev = nullptr, status_ev2 = nullptr;
   int32_t* h_limit = nullptr;              // pinned [2]: per kind, the first pod the chains could not take (nosplan_plan)
   int32_t (*h_range)[2] = nullptr;         // pinned [2][2]: per kind, the range handed to the next chain launch
-  void* h_pin = nullptr;                   // pinned staging for results (nosplan_score_snapshot)
+  void* h_pin = nullptr;                   // pinned staging for results (nosplan_score_snapshot, nosplan_plan)
   size_t h_pin_cap = 0;
+  // nosplan_plan's split of the pod list by kind, kept between calls: 50 000 pods are 0.8 MB of host arrays, and fresh
+  // vectors cost more in page faults than the split itself
+  struct PlanSide {
+    std::vector<int32_t> pod_idx, pod_sig, off, key, qty;
+    std::map<std::vector<int32_t>, int> sigs;           // general case
+    std::vector<int> single;                             // [key * (kChainQ+1) + qty] -> row, single-key fast lookup
+    int n_sigs = 0;
+    bool chains_ok = true;                               // every pod: one key, 1 <= qty <= kChainQ
+  } plan_side[2];
 
   // nosplan_score_pass_dev: fork/join of the two kinds, CUDA events around the dominant kernels, executed-work counters
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
@@ -824,12 +833,12 @@ int nosplan_set_mig_tables(nosplan_t* h, int n_profiles, const char* const* prof
                            const int32_t* geom_off, const int32_t* geom_counts) {
   if (!h) return NOSPLAN_ERR_ARG;
   h->err.clear();
-  if (!profile_names || !geom_off || (!geom_counts && n_models > 0 && geom_off[n_models] > 0))
-    return fail(h, NOSPLAN_ERR_ARG, "null argument");
+  if (!profile_names || !geom_off) return fail(h, NOSPLAN_ERR_ARG, "null argument");
   if (n_profiles < 1 || n_profiles > NOSPLAN_MAX_MIG_PROFILES)
     return fail(h, NOSPLAN_ERR_RANGE, "n_profiles %d out of range [1,%d]", n_profiles, NOSPLAN_MAX_MIG_PROFILES);
   if (n_models < 1) return fail(h, NOSPLAN_ERR_CONFIG, "no known configs provided");  // known_configs.go:165-167
   if (n_models > NOSPLAN_MAX_MODELS) return fail(h, NOSPLAN_ERR_RANGE, "too many models (%d > %d)", n_models, NOSPLAN_MAX_MODELS);
+  if (!geom_counts && geom_off[n_models] > 0) return fail(h, NOSPLAN_ERR_ARG, "null argument");  // (n_models is in range here)
   std::vector<std::string> names(n_profiles);
   for (int p = 0; p < n_profiles; ++p) {
     names[p] = profile_names[p] ? profile_names[p] : "";
@@ -1653,6 +1662,10 @@ struct PlanKind {
 };
 }  // namespace
 
+namespace {
+int pin_reserve(nosplan_t* h, size_t bytes);  // defined with nosplan_score_snapshot
+}
+
 extern "C" {
 
 int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* dem_off, const int32_t* dem_key,
@@ -1669,18 +1682,28 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
   NSP_RANGE("nosplan_plan");
   nvtxRangePushA("nosplan_plan: host split of the pod list");
   // split by kind (order kept) and deduplicate request vectors: pods with the same vector share a row
-  struct Side {
-    std::vector<int32_t> pod_idx, pod_sig, off{0}, key, qty;
-    std::map<std::vector<int32_t>, int> sigs;           // general case
-    std::vector<int> single;                             // [key * (kChainQ+1) + qty] -> row, single-key fast lookup
-    int n_sigs = 0;
-    bool chains_ok = true;                               // every pod: one key, 1 <= qty <= kChainQ
-  } side[2];
-  for (int kd = 0; kd < 2; ++kd) side[kd].single.assign((size_t)(kd ? NOSPLAN_MAX_MPS_SIZES : NOSPLAN_MAX_MIG_PROFILES) * (kChainQ + 1), -1);
+  using Side = nosplan::PlanSide;
+  Side* const side = h->plan_side;
+  int n_side[2] = {0, 0};  // pods of each kind so far (the arrays are sized for all of them and cut afterwards)
+  for (int kd = 0; kd < 2; ++kd) {
+    Side& s = side[kd];
+    s.pod_idx.resize(n_pods);
+    s.pod_sig.resize(n_pods);
+    s.off.assign(1, 0);
+    s.key.clear();
+    s.qty.clear();
+    s.sigs.clear();
+    s.single.assign((size_t)(kd ? NOSPLAN_MAX_MPS_SIZES : NOSPLAN_MAX_MIG_PROFILES) * (kChainQ + 1), -1);
+    s.n_sigs = 0;
+    s.chains_ok = true;
+  }
+  // (tables indexed by the kind, not branches on it: the kinds alternate at random and a branch on them mispredicts)
+  const bool have_kind[2] = {h->have_mig, h->have_mps};
+  const int keys_of_kind[2] = {h->P, h->S};
   for (int i = 0; i < n_pods; ++i) {
     const int kd = kind[i] ? 1 : 0;
-    const int n_keys = kd ? h->S : h->P;
-    if (kd ? !h->have_mps : !h->have_mig) {
+    const int n_keys = keys_of_kind[kd];
+    if (!have_kind[kd]) {
       // no nodes of that kind: the controller returns before doing anything (mig_controller.go:78-81)
       if (gate_hit) gate_hit[i] = 0;
       if (repart_node) repart_node[i] = -1;
@@ -1721,8 +1744,13 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
       }
       s.off.push_back((int32_t)s.key.size());
     }
-    s.pod_idx.push_back(i);
-    s.pod_sig.push_back(id);
+    const int c = n_side[kd]++;
+    s.pod_idx[c] = i;
+    s.pod_sig[c] = id;
+  }
+  for (int kd = 0; kd < 2; ++kd) {
+    side[kd].pod_idx.resize(n_side[kd]);
+    side[kd].pod_sig.resize(n_side[kd]);
   }
   const auto t_split = std::chrono::steady_clock::now();
   nvtxRangePop();
@@ -1737,8 +1765,6 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
     CU(cudaMemcpyAsync(h->d_mps_ulo.p, h->d_mps_ulo0.p, sizeof(uint4) * h->mps_tg, cudaMemcpyDeviceToDevice, h->stream2));
     CU(cudaMemcpyAsync(h->d_mps_uhi.p, h->d_mps_uhi0.p, sizeof(uint4) * h->mps_tg, cudaMemcpyDeviceToDevice, h->stream2));
   }
-  std::vector<uint8_t> o_gate[2];
-  std::vector<int32_t> o_rep[2], o_node[2], o_gpu[2];
   const int32_t* out_ptr[2] = {nullptr, nullptr};
   PlanKind pk[2];
   for (int kd = 0; kd < 2; ++kd) {
@@ -1954,19 +1980,20 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
   }
   // results back only after both kinds are in flight: a device-to-host copy into pageable memory blocks
   // the host until its stream drains, which would serialise the MIG and MPS chains
+  // (the four result arrays of a kind lie back to back on the device: repart_node, sched_node, sched_gpu as int32 [M],
+  // then gate_hit as bytes [M]; one copy per kind into pinned memory)
+  size_t pin_off[2] = {0, 0}, pin_bytes = 0;
+  for (int kd = 0; kd < 2; ++kd) {
+    pin_off[kd] = pin_bytes;
+    pin_bytes += ((size_t)side[kd].pod_idx.size() * 13 + 15) / 16 * 16;
+  }
+  if ((rc = pin_reserve(h, std::max<size_t>(pin_bytes, 16)))) return rc;
+  char* const pin = static_cast<char*>(h->h_pin);
   for (int kd = 0; kd < 2; ++kd) {
     const int M = (int)side[kd].pod_idx.size();
     if (M == 0) continue;
     cudaStream_t st = kd ? h->stream2 : h->stream;
-    o_rep[kd].resize(M);
-    o_node[kd].resize(M);
-    o_gpu[kd].resize(M);
-    o_gate[kd].resize(M);
-    const int32_t* rep = out_ptr[kd];
-    CU(cudaMemcpyAsync(o_rep[kd].data(), rep, sizeof(int32_t) * M, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(o_node[kd].data(), rep + M, sizeof(int32_t) * M, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(o_gpu[kd].data(), rep + 2 * (size_t)M, sizeof(int32_t) * M, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(o_gate[kd].data(), reinterpret_cast<const uint8_t*>(rep + 3 * (size_t)M), M, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(pin + pin_off[kd], out_ptr[kd], (size_t)M * 13, cudaMemcpyDeviceToHost, st));
   }
   const auto t_enq = std::chrono::steady_clock::now();
   CU(cudaStreamSynchronize(h->stream));
@@ -1979,12 +2006,17 @@ int nosplan_plan(nosplan_t* h, int n_pods, const uint8_t* kind, const int32_t* d
   }
   for (int kd = 0; kd < 2; ++kd) {
     Side& s = side[kd];
-    for (size_t j = 0; j < s.pod_idx.size(); ++j) {
+    const size_t M = s.pod_idx.size();
+    const int32_t* o_rep = reinterpret_cast<const int32_t*>(pin + pin_off[kd]);
+    const int32_t* o_node = o_rep + M;
+    const int32_t* o_gpu = o_rep + 2 * M;
+    const uint8_t* o_gate = reinterpret_cast<const uint8_t*>(o_rep + 3 * M);
+    for (size_t j = 0; j < M; ++j) {
       const int i = s.pod_idx[j];
-      if (gate_hit) gate_hit[i] = o_gate[kd][j];
-      if (repart_node) repart_node[i] = o_rep[kd][j];
-      if (sched_node) sched_node[i] = o_node[kd][j];
-      if (sched_gpu) sched_gpu[i] = o_gpu[kd][j];
+      if (gate_hit) gate_hit[i] = o_gate[j];
+      if (repart_node) repart_node[i] = o_rep[j];
+      if (sched_node) sched_node[i] = o_node[j];
+      if (sched_gpu) sched_gpu[i] = o_gpu[j];
     }
   }
   return NOSPLAN_OK;
