@@ -282,3 +282,23 @@ def test_table_accessors_are_bounds_checked():
     small = C.create_string_buffer(b"\xaa" * 32, 32)
     assert not L.noshost_tables_load(b"- models: 3\n", small, 8)
     assert small.raw[8:] == b"\xaa" * 24 and small.raw[:8].find(b"\0") >= 0
+
+
+def test_null_arguments_of_the_small_entry_points():
+    L = host.lib()
+    buf = C.create_string_buffer(64)
+    assert L.noshost_format_status_annotation(3, None, 1, buf, 64) > 0 and buf.value == (PREFIX_STATUS + "3--free").encode()
+    assert L.noshost_format_spec_annotation(3, None, buf, 64) > 0 and buf.value == (PREFIX_SPEC + "3-").encode()
+    assert L.noshost_pods_count(None) == 0
+    L.noshost_pods_error.restype = C.c_char_p
+    assert L.noshost_pods_error(None) == b"null handle"
+    out = C.c_int32(7)
+    assert L.noshost_memory_gb(None, C.byref(out)) == 1 and out.value == 7
+    assert L.noshost_mps_profile_size_gb(None) == 0
+    assert L.noshost_mig_profile_of_resource(None, buf, 64) == 1 and L.noshost_mps_profile_of_resource(None, buf, 64) == 1
+    idx, st, q = C.c_int32(), C.c_int32(), C.c_int32()
+    assert L.noshost_parse_status_annotation(None, b"1", C.byref(idx), buf, 64, C.byref(st), C.byref(q)) == 1
+    assert L.noshost_parse_spec_annotation(b"x", None, C.byref(idx), buf, 64, C.byref(q)) == 1
+    L.noshost_snapshot_free(None)
+    L.noshost_pods_free(None)
+    L.noshost_tables_free(None)

@@ -199,11 +199,11 @@ int noshost_parse_spec_annotation(const char* key, const char* value, int32_t* i
 
 int noshost_format_status_annotation(int32_t index, const char* profile, int32_t status, char* out, int cap) {
   const char* st = status == NOSHOST_STATUS_FREE ? "free" : status == NOSHOST_STATUS_USED ? "used" : "unknown";
-  return copy_out(std::string(kStatusPrefix) + "-" + std::to_string(index) + "-" + profile + "-" + st, out, cap);
+  return copy_out(std::string(kStatusPrefix) + "-" + std::to_string(index) + "-" + (profile ? profile : "") + "-" + st, out, cap);
 }
 
 int noshost_format_spec_annotation(int32_t index, const char* profile, char* out, int cap) {
-  return copy_out(std::string(kSpecPrefix) + "-" + std::to_string(index) + "-" + profile, out, cap);
+  return copy_out(std::string(kSpecPrefix) + "-" + std::to_string(index) + "-" + (profile ? profile : ""), out, cap);
 }
 
 int noshost_memory_gb(const char* label, int32_t* out) {
@@ -525,13 +525,14 @@ noshost_pods* noshost_pods_build(int n_pods, const uint8_t* pending, const uint8
 }
 
 void noshost_pods_free(noshost_pods* p) { delete p; }
-int noshost_pods_count(const noshost_pods* p) { return (int)p->source.size(); }
-const int32_t* noshost_pods_source(const noshost_pods* p) { return p->source.data(); }
-const uint8_t* noshost_pods_kind(const noshost_pods* p) { return p->kind.data(); }
-const int32_t* noshost_pods_off(const noshost_pods* p) { return p->off.data(); }
-const int32_t* noshost_pods_key(const noshost_pods* p) { return p->key.data(); }
-const int32_t* noshost_pods_qty(const noshost_pods* p) { return p->qty.data(); }
-const char* noshost_pods_error(const noshost_pods* p) { return p->err.c_str(); }
+// (a null handle answers like an empty result)
+int noshost_pods_count(const noshost_pods* p) { return p ? (int)p->source.size() : 0; }
+const int32_t* noshost_pods_source(const noshost_pods* p) { return p ? p->source.data() : nullptr; }
+const uint8_t* noshost_pods_kind(const noshost_pods* p) { return p ? p->kind.data() : nullptr; }
+const int32_t* noshost_pods_off(const noshost_pods* p) { return p ? p->off.data() : nullptr; }
+const int32_t* noshost_pods_key(const noshost_pods* p) { return p ? p->key.data() : nullptr; }
+const int32_t* noshost_pods_qty(const noshost_pods* p) { return p ? p->qty.data() : nullptr; }
+const char* noshost_pods_error(const noshost_pods* p) { return p ? p->err.c_str() : "null handle"; }
 
 int noshost_spec_annotations(const noshost_snapshot* s, int node, const int32_t* used, const int32_t* free_, char* out,
                              int cap) {
